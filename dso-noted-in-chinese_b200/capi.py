@@ -1,0 +1,303 @@
+"""ctypes binding of libdso_b200.so (the C ABI in include/dso_b200.h).
+
+This is plumbing for the tests and bench.py; the product is the shared library.  Loading fails loudly
+when the library has not been built, and every compute call raises DsoError when there is no CUDA device:
+there is no CPU fallback anywhere in this package.
+"""
+import ctypes as C
+import os
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libdso_b200.so")
+MAX_LEVELS, MAX_FRAMES, MAX_HYP, MAX_PASSES = 6, 8, 32, 8
+
+f32p = np.ctypeslib.ndpointer(dtype=np.float32, flags="C_CONTIGUOUS")
+f64p = np.ctypeslib.ndpointer(dtype=np.float64, flags="C_CONTIGUOUS")
+i32p = np.ctypeslib.ndpointer(dtype=np.int32, flags="C_CONTIGUOUS")
+u8p = np.ctypeslib.ndpointer(dtype=np.uint8, flags="C_CONTIGUOUS")
+vp = C.c_void_p
+
+
+class DsoError(RuntimeError):
+    pass
+
+
+class TrackOpts(C.Structure):
+    _fields_ = [("huberTH", C.c_float), ("coarseCutoffTH", C.c_float), ("affineOptModeA", C.c_float),
+                ("affineOptModeB", C.c_float), ("maxIterations", C.c_int * 5)]
+
+
+class TrackResult(C.Structure):
+    _fields_ = [("ok", C.c_int), ("reserved", C.c_int), ("pose", C.c_double * 12), ("aff_a", C.c_double),
+                ("aff_b", C.c_double), ("lastResiduals", C.c_double * 5), ("lastFlowIndicators", C.c_double * 3),
+                ("n_passes", C.c_int), ("pass_level", C.c_int * MAX_PASSES), ("pass_rmse", C.c_double * MAX_PASSES),
+                ("n_iterations", C.c_int), ("n_evals", C.c_int), ("trace_len", C.c_int), ("trace", C.c_ubyte * 256),
+                ("point_evals", C.c_double)]
+
+
+class Precalc(C.Structure):
+    _fields_ = [("PRE_RTll_0", C.c_float * 9), ("PRE_tTll_0", C.c_float * 3), ("PRE_KRKiTll", C.c_float * 9),
+                ("PRE_KtTll", C.c_float * 3), ("PRE_aff_mode", C.c_float * 2), ("PRE_b0_mode", C.c_float), ("pad", C.c_float)]
+
+
+# every symbol include/dso_b200.h declares: name -> (restype, argtypes)
+SIGNATURES = {
+    "dso_b200_create": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(vp)]),
+    "dso_b200_destroy": (None, [vp]),
+    "dso_b200_last_error": (C.c_char_p, []),
+    "dso_b200_stream": (vp, [vp]),
+    "dso_b200_sync": (C.c_int, [vp]),
+    "dso_b200_host_alloc": (vp, [C.c_size_t]),
+    "dso_b200_host_free": (None, [vp]),
+    "dso_b200_launch_count": (C.c_longlong, [vp]),
+    "dso_b200_make_images": (C.c_int, [vp, C.c_int, vp, C.c_int, C.c_int, C.c_int, vp, C.POINTER(vp), C.POINTER(vp)]),
+    "dso_b200_make_images_dev": (C.c_int, [vp, C.c_int, vp, C.c_int, C.c_int, C.c_int, vp]),
+    "dso_b200_tracker_set_ref": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float,
+                                           i32p, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), C.POINTER(vp),
+                                           C.c_double, C.c_double, C.c_float]),
+    "dso_b200_calc_res": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, f64p, C.c_double, C.c_double, C.c_float, C.c_float, f64p]),
+    "dso_b200_calc_gs": (C.c_int, [vp, C.c_int, f64p, f64p]),
+    "dso_b200_calc_res_debug": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, f64p, C.c_double, C.c_double, C.c_float, C.c_float, u8p, f32p]),
+    "dso_b200_track_opts_default": (None, [C.POINTER(TrackOpts)]),
+    "dso_b200_track_batched": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, f64p, C.c_double, C.c_double, C.c_float, C.c_int,
+                                         C.POINTER(TrackOpts), C.POINTER(TrackResult)]),
+    "dso_b200_track_replay_abort": (C.c_int, [C.POINTER(TrackResult), f64p, f64p]),
+    "dso_b200_track_hostloop": (C.c_int, [vp, C.c_int, C.c_int, f64p, C.c_double, C.c_double, C.c_float, C.c_int, vp,
+                                          C.POINTER(TrackOpts), C.POINTER(TrackResult)]),
+    "dso_b200_ba_set_window": (C.c_int, [vp, C.c_int, i32p, C.c_int, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float, f32p]),
+    "dso_b200_ba_set_glue": (C.c_int, [vp, vp, f64p, f64p, f32p, f32p]),
+    "dso_b200_ba_set_points": (C.c_int, [vp, C.c_int, f32p, f32p, f32p, f32p, f32p, f32p, i32p, f32p, f32p]),
+    "dso_b200_ba_set_residuals": (C.c_int, [vp, C.c_int, i32p, i32p, i32p, f64p, u8p, u8p]),
+    "dso_b200_ba_linearize": (C.c_int, [vp, vp, vp, vp, vp, vp, vp, vp]),
+    "dso_b200_ba_apply_res": (C.c_int, [vp, vp, vp]),
+    "dso_b200_ba_accumulate_A": (C.c_int, [vp, f64p, f64p, C.POINTER(C.c_int), vp, vp, vp]),
+    "dso_b200_ba_accumulate_SC": (C.c_int, [vp, f64p, f64p, vp, vp, vp]),
+    "dso_b200_ba_step": (C.c_int, [vp, f64p, f64p, f64p, f64p, C.POINTER(C.c_double), C.POINTER(C.c_int)]),
+}
+
+_LIB = None
+
+
+def load():
+    """Loads the shared library (no CUDA call is made)."""
+    global _LIB
+    if _LIB is None:
+        if not os.path.exists(LIB_PATH):
+            raise DsoError("%s not built: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                           "(there is no CPU fallback)" % LIB_PATH)
+        L = C.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(L, name)
+            fn.restype = res
+            fn.argtypes = args
+        _LIB = L
+    return _LIB
+
+
+def _ptrs(arrs):
+    a = (vp * len(arrs))()
+    for i, x in enumerate(arrs):
+        a[i] = None if x is None else x.ctypes.data
+    return a
+
+
+def _opt(a):
+    return None if a is None else a.ctypes.data
+
+
+class Context:
+    def __init__(self, device=0, max_w=640, max_h=480, n_frame_slots=10):
+        self.L = load()
+        h = vp()
+        self._check(self.L.dso_b200_create(device, max_w, max_h, n_frame_slots, C.byref(h)))
+        self.h = h
+        self.max_w, self.max_h = max_w, max_h
+
+    def _check(self, rc):
+        if rc != 0:
+            raise DsoError("dso_b200 error %d: %s" % (rc, self.L.dso_b200_last_error().decode()))
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.dso_b200_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @property
+    def stream(self):
+        return self.L.dso_b200_stream(self.h)
+
+    def sync(self):
+        self._check(self.L.dso_b200_sync(self.h))
+
+    def launch_count(self):
+        return self.L.dso_b200_launch_count(self.h)
+
+    # ---- K1 ----
+    def make_images(self, slot, color, levels, B=None, want_host=True):
+        """color: [h,w] float32 (numpy) -> (dIp list [h_l,w_l,3], absgrad list [h_l,w_l]) or None."""
+        color = np.ascontiguousarray(color, dtype=np.float32)
+        h, w = color.shape
+        Bp = None
+        if B is not None:
+            B = np.ascontiguousarray(B, dtype=np.float32)
+            Bp = B.ctypes.data
+        if want_host:
+            dIp = [np.zeros((h >> l, w >> l, 3), dtype=np.float32) for l in range(levels)]
+            ab = [np.zeros((h >> l, w >> l), dtype=np.float32) for l in range(levels)]
+            self._check(self.L.dso_b200_make_images(self.h, slot, color.ctypes.data, w, h, levels, Bp, _ptrs(dIp), _ptrs(ab)))
+            return dIp, ab
+        self._check(self.L.dso_b200_make_images(self.h, slot, color.ctypes.data, w, h, levels, Bp, None, None))
+        return None
+
+    def make_images_ptr(self, slot, host_ptr, w, h, levels):
+        """host pointer variant (e.g. pinned memory), no copy back."""
+        self._check(self.L.dso_b200_make_images(self.h, slot, host_ptr, w, h, levels, None, None, None))
+
+    def make_images_dev(self, slot, dev_ptr, w, h, levels, B=None):
+        Bp = None
+        if B is not None:
+            B = np.ascontiguousarray(B, dtype=np.float32)
+            Bp = B.ctypes.data
+        self._check(self.L.dso_b200_make_images_dev(self.h, slot, dev_ptr, w, h, levels, Bp))
+
+    # ---- K2 ----
+    def tracker_set_ref(self, trk, w, h, levels, K, clouds, ref_a, ref_b, ref_exposure):
+        """clouds: per level (u, v, idepth, color) float32 arrays."""
+        fx, fy, cx, cy = K
+        n = np.array([len(c[0]) for c in clouds], dtype=np.int32)
+        cl = [[np.ascontiguousarray(a, dtype=np.float32) for a in c] for c in clouds]
+        self._check(self.L.dso_b200_tracker_set_ref(self.h, trk, w, h, levels, fx, fy, cx, cy, n,
+                                                    _ptrs([c[0] for c in cl]), _ptrs([c[1] for c in cl]),
+                                                    _ptrs([c[2] for c in cl]), _ptrs([c[3] for c in cl]),
+                                                    ref_a, ref_b, ref_exposure))
+
+    def calc_res(self, trk, slot, lvl, pose12, a, b, cutoff, new_exposure=1.0):
+        out = np.zeros(6)
+        self._check(self.L.dso_b200_calc_res(self.h, trk, slot, lvl, np.ascontiguousarray(pose12, dtype=np.float64),
+                                             a, b, new_exposure, cutoff, out))
+        return out
+
+    def calc_gs(self, trk):
+        H = np.zeros(64)
+        b = np.zeros(8)
+        self._check(self.L.dso_b200_calc_gs(self.h, trk, H, b))
+        return H.reshape(8, 8), b
+
+    def calc_res_debug(self, trk, slot, lvl, n, pose12, a, b, cutoff, new_exposure=1.0):
+        st = np.zeros(n + 16, dtype=np.uint8)
+        wp = np.zeros((n + 1) * 8, dtype=np.float32)
+        self._check(self.L.dso_b200_calc_res_debug(self.h, trk, slot, lvl, np.ascontiguousarray(pose12, dtype=np.float64),
+                                                   a, b, new_exposure, cutoff, st, wp))
+        return st[:n], wp[:n * 8].reshape(n, 8)
+
+    def default_opts(self):
+        o = TrackOpts()
+        self.L.dso_b200_track_opts_default(C.byref(o))
+        return o
+
+    def track_hostloop(self, trk, slot, pose12, a, b, coarsest, min_res=None, new_exposure=1.0, opts=None):
+        res = TrackResult()
+        mr = None
+        if min_res is not None:
+            mr = np.ascontiguousarray(min_res, dtype=np.float64)
+        self._check(self.L.dso_b200_track_hostloop(self.h, trk, slot, np.ascontiguousarray(pose12, dtype=np.float64), a, b,
+                                                   new_exposure, coarsest, _opt(mr), None if opts is None else C.byref(opts),
+                                                   C.byref(res)))
+        return res
+
+    def track_batched(self, trk, slot, poses12, a, b, coarsest, new_exposure=1.0, opts=None):
+        poses12 = np.ascontiguousarray(poses12, dtype=np.float64).reshape(-1, 12)
+        n = poses12.shape[0]
+        res = (TrackResult * n)()
+        self._check(self.L.dso_b200_track_batched(self.h, trk, slot, n, poses12.reshape(-1), a, b, new_exposure, coarsest,
+                                                  None if opts is None else C.byref(opts), res))
+        return list(res)
+
+    def replay_abort(self, res, min_res):
+        lr = np.zeros(5)
+        ok = self.L.dso_b200_track_replay_abort(C.byref(res), np.ascontiguousarray(min_res, dtype=np.float64), lr)
+        return ok, lr
+
+    # ---- K3-K5 ----
+    def ba_set_window(self, slots, w, h, K, frameEnergyTH):
+        fx, fy, cx, cy = K
+        slots = np.ascontiguousarray(slots, dtype=np.int32)
+        self.nF = len(slots)
+        self._check(self.L.dso_b200_ba_set_window(self.h, len(slots), slots, w, h, fx, fy, cx, cy,
+                                                  np.ascontiguousarray(frameEnergyTH, dtype=np.float32)))
+
+    def ba_set_glue(self, precalc28, adHost, adTarget, adHTdeltaF, cDeltaF):
+        pre = np.ascontiguousarray(precalc28, dtype=np.float32)
+        self._check(self.L.dso_b200_ba_set_glue(self.h, pre.ctypes.data, np.ascontiguousarray(adHost, dtype=np.float64).reshape(-1),
+                                                np.ascontiguousarray(adTarget, dtype=np.float64).reshape(-1),
+                                                np.ascontiguousarray(adHTdeltaF, dtype=np.float32).reshape(-1),
+                                                np.ascontiguousarray(cDeltaF, dtype=np.float32)))
+
+    def ba_set_points(self, W):
+        self.nP = W.nP
+        self._check(self.L.dso_b200_ba_set_points(self.h, W.nP, W.u, W.v, W.idepth_scaled, W.idepth_zero_scaled,
+                                                  W.color.reshape(-1), W.weights.reshape(-1), W.host, W.priorF, W.deltaF))
+
+    def ba_set_residuals(self, W):
+        self.nR = W.nR
+        self._check(self.L.dso_b200_ba_set_residuals(self.h, W.nR, W.res_point, W.res_target, W.res_state, W.res_energy,
+                                                     W.res_isLinearized, W.res_isActive))
+
+    def ba_linearize(self, want_J=True):
+        nR = self.nR
+        out = dict(newState=np.zeros(nR, dtype=np.int32), newEnergy=np.zeros(nR, dtype=np.float32),
+                   newEnergyWithOutlier=np.zeros(nR, dtype=np.float32), centerProjectedTo=np.zeros(nR * 3, dtype=np.float32),
+                   projectedTo=np.zeros(nR * 16, dtype=np.float32), J=np.zeros(nR * 74 if want_J else 1, dtype=np.float32))
+        tot = np.zeros(1)
+        self._check(self.L.dso_b200_ba_linearize(self.h, out["newState"].ctypes.data, out["newEnergy"].ctypes.data,
+                                                 out["newEnergyWithOutlier"].ctypes.data, out["centerProjectedTo"].ctypes.data,
+                                                 out["projectedTo"].ctypes.data, out["J"].ctypes.data if want_J else None,
+                                                 tot.ctypes.data))
+        out["total"] = float(tot[0])
+        if want_J:
+            out["J"] = out["J"].reshape(nR, 74)
+        out["centerProjectedTo"] = out["centerProjectedTo"].reshape(nR, 3)
+        out["projectedTo"] = out["projectedTo"].reshape(nR, 8, 2)
+        return out
+
+    def ba_apply_res(self):
+        act = np.zeros(self.nR, dtype=np.uint8)
+        jp = np.zeros(self.nR * 8, dtype=np.float32)
+        self._check(self.L.dso_b200_ba_apply_res(self.h, act.ctypes.data, jp.ctypes.data))
+        return act, jp.reshape(self.nR, 8)
+
+    def ba_accumulate_A(self):
+        N = 8 * self.nF + 4
+        H = np.zeros(N * N)
+        b = np.zeros(N)
+        n = C.c_int(0)
+        Hdd = np.zeros(self.nP, dtype=np.float32)
+        bd = np.zeros(self.nP, dtype=np.float32)
+        Hcd = np.zeros(self.nP * 4, dtype=np.float32)
+        self._check(self.L.dso_b200_ba_accumulate_A(self.h, H, b, C.byref(n), Hdd.ctypes.data, bd.ctypes.data, Hcd.ctypes.data))
+        return dict(H=H.reshape(N, N), b=b, resInA=n.value, Hdd=Hdd, bd=bd, Hcd=Hcd.reshape(self.nP, 4))
+
+    def ba_accumulate_SC(self):
+        N = 8 * self.nF + 4
+        H = np.zeros(N * N)
+        b = np.zeros(N)
+        HdiF = np.zeros(self.nP, dtype=np.float32)
+        bdSumF = np.zeros(self.nP, dtype=np.float32)
+        ih = np.zeros(self.nP, dtype=np.float32)
+        self._check(self.L.dso_b200_ba_accumulate_SC(self.h, H, b, HdiF.ctypes.data, bdSumF.ctypes.data, ih.ctypes.data))
+        return dict(H=H.reshape(N, N), b=b, HdiF=HdiF, bdSumF=bdSumF, idepth_hessian=ih)
+
+    def ba_step(self):
+        N = 8 * self.nF + 4
+        HA, bA, HS, bS = np.zeros(N * N), np.zeros(N), np.zeros(N * N), np.zeros(N)
+        e = C.c_double(0)
+        n = C.c_int(0)
+        self._check(self.L.dso_b200_ba_step(self.h, HA, bA, HS, bS, C.byref(e), C.byref(n)))
+        return dict(H_A=HA.reshape(N, N), b_A=bA, H_sc=HS.reshape(N, N), b_sc=bS, energy=e.value, resInA=n.value)

@@ -1,0 +1,211 @@
+// Context management and the K1 entry points of the C ABI (include/dso_b200.h).
+#include "common.cuh"
+#include <cstdarg>
+
+static thread_local char g_err[512] = "";
+
+void dso_set_error(const char* fmt, ...)
+{
+	va_list ap;
+	va_start(ap, fmt);
+	vsnprintf(g_err, sizeof(g_err), fmt, ap);
+	va_end(ap);
+}
+
+extern "C" const char* dso_b200_last_error(void) { return g_err; }
+
+static size_t pyr_pixels(int w, int h, int levels)
+{
+	size_t s = 0;
+	for (int l = 0; l < levels; l++) s += (size_t)(w >> l) * (h >> l);
+	return s;
+}
+static size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+extern "C" int dso_b200_create(int device, int max_w, int max_h, int n_frame_slots, dso_b200_ctx** out)
+{
+	ARG_CHECK(out && max_w >= 16 && max_h >= 16 && n_frame_slots >= 1 && n_frame_slots <= 64, "bad arguments");
+	int ndev = 0;
+	cudaError_t e = cudaGetDeviceCount(&ndev);
+	if (e != cudaSuccess || ndev == 0)
+	{
+		dso_set_error("no CUDA device available (%s); this library has no CPU fallback", cudaGetErrorString(e));
+		return DSO_B200_E_CUDA;
+	}
+	ARG_CHECK(device >= 0 && device < ndev, "device index out of range");
+	CK(cudaSetDevice(device));
+	cudaDeviceProp prop;
+	CK(cudaGetDeviceProperties(&prop, device));
+	if (prop.major < 10)
+	{
+		dso_set_error("device %d is sm_%d%d; this library is built for sm_100a only", device, prop.major, prop.minor);
+		return DSO_B200_E_CUDA;
+	}
+	dso_b200_ctx* ctx = new dso_b200_ctx();
+	memset(ctx, 0, sizeof(*ctx));
+	ctx->device = device;
+	ctx->sm_count = prop.multiProcessorCount;
+	ctx->max_w = max_w; ctx->max_h = max_h; ctx->n_slots = n_frame_slots;
+	CK(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+
+	// frame slots: per level a float4 image and (for l >= 1) a float intensity plane
+	ctx->slots = new FrameSlot[n_frame_slots];
+	for (int s = 0; s < n_frame_slots; s++)
+	{
+		FrameSlot& F = ctx->slots[s];
+		memset(&F, 0, sizeof(F));
+		size_t bytes = 0;
+		for (int l = 0; l < MAXL; l++)
+		{
+			size_t n = (size_t)(max_w >> l) * (max_h >> l);
+			bytes += align_up(n * sizeof(float4), 256);
+			if (l >= 1) bytes += align_up(n * sizeof(float), 256);
+		}
+		CK(cudaMalloc(&F.base, bytes));
+		char* p = (char*)F.base;
+		for (int l = 0; l < MAXL; l++)
+		{
+			size_t n = (size_t)(max_w >> l) * (max_h >> l);
+			F.pyr[l] = (float4*)p; p += align_up(n * sizeof(float4), 256);
+			if (l >= 1) { F.inten[l] = (float*)p; p += align_up(n * sizeof(float), 256); }
+		}
+	}
+	// staging: input image, host-layout outputs, LUT
+	size_t npx0 = (size_t)max_w * max_h;
+	CK(cudaMalloc(&ctx->d_color, align_up(npx0 * sizeof(float), 256)));
+	for (int l = 0; l < MAXL; l++)
+	{
+		size_t n = (size_t)(max_w >> l) * (max_h >> l);
+		CK(cudaMalloc(&ctx->d_aos[l], align_up(3 * n * sizeof(float), 256)));
+		CK(cudaMalloc(&ctx->d_abs[l], align_up(n * sizeof(float), 256)));
+	}
+	CK(cudaMalloc(&ctx->d_Blut, 256 * sizeof(float)));
+
+	// tracker slots
+	for (int t = 0; t < 2; t++)
+	{
+		TrackerSlot& T = ctx->trk[t];
+		T.cap_points = npx0;
+		size_t bytes = 0;
+		for (int l = 0; l < MAXL; l++) bytes += align_up((size_t)(max_w >> l) * (max_h >> l) * sizeof(float4), 256);
+		CK(cudaMalloc(&T.base, bytes));
+		char* p = (char*)T.base;
+		for (int l = 0; l < MAXL; l++) { T.pc[l] = (float4*)p; p += align_up((size_t)(max_w >> l) * (max_h >> l) * sizeof(float4), 256); }
+		CK(cudaMalloc(&T.d_sums, S_COUNT * sizeof(float)));
+		CK(cudaMalloc(&T.d_partials, (size_t)ctx->sm_count * 4 * S_COUNT * sizeof(float)));
+		CK(cudaMalloc(&T.d_ticket, sizeof(unsigned int)));
+		CK(cudaMemset(T.d_ticket, 0, sizeof(unsigned int)));
+		CK(cudaHostAlloc((void**)&T.h_sums, S_COUNT * sizeof(float), cudaHostAllocDefault));
+		CK(cudaMalloc(&T.d_track_in, 4096 * 2));
+		CK(cudaMalloc(&T.d_track_out, sizeof(dso_b200_track_result) * DSO_B200_MAX_HYP));
+		CK(cudaHostAlloc(&T.h_track_in, 4096 * 2, cudaHostAllocDefault));
+		CK(cudaHostAlloc(&T.h_track_out, sizeof(dso_b200_track_result) * DSO_B200_MAX_HYP, cudaHostAllocDefault));
+		T.last_lvl = -1;
+	}
+	int rc = ba_create(ctx);
+	if (rc) return rc;
+	*out = ctx;
+	return 0;
+}
+
+extern "C" void dso_b200_destroy(dso_b200_ctx* ctx)
+{
+	if (!ctx) return;
+	cudaSetDevice(ctx->device);
+	cudaStreamSynchronize(ctx->stream);
+	ba_destroy(ctx);
+	for (int s = 0; s < ctx->n_slots; s++) cudaFree(ctx->slots[s].base);
+	delete[] ctx->slots;
+	cudaFree(ctx->d_color);
+	for (int l = 0; l < MAXL; l++) { cudaFree(ctx->d_aos[l]); cudaFree(ctx->d_abs[l]); }
+	cudaFree(ctx->d_Blut);
+	for (int t = 0; t < 2; t++)
+	{
+		TrackerSlot& T = ctx->trk[t];
+		cudaFree(T.base); cudaFree(T.d_sums); cudaFree(T.d_partials); cudaFree(T.d_ticket);
+		cudaFreeHost(T.h_sums); cudaFree(T.d_track_in); cudaFree(T.d_track_out);
+		cudaFreeHost(T.h_track_in); cudaFreeHost(T.h_track_out);
+	}
+	cudaStreamDestroy(ctx->stream);
+	delete ctx;
+}
+
+extern "C" void* dso_b200_stream(dso_b200_ctx* ctx) { return ctx ? (void*)ctx->stream : nullptr; }
+extern "C" int dso_b200_sync(dso_b200_ctx* ctx)
+{
+	ARG_CHECK(ctx, "null context");
+	CK(cudaStreamSynchronize(ctx->stream));
+	return 0;
+}
+extern "C" void* dso_b200_host_alloc(size_t bytes)
+{
+	void* p = nullptr;
+	if (cudaHostAlloc(&p, bytes, cudaHostAllocDefault) != cudaSuccess) { dso_set_error("cudaHostAlloc(%zu) failed", bytes); return nullptr; }
+	return p;
+}
+extern "C" void dso_b200_host_free(void* p) { if (p) cudaFreeHost(p); }
+extern "C" long long dso_b200_launch_count(dso_b200_ctx* ctx) { return ctx ? ctx->launches : -1; }
+
+static int check_image_args(dso_b200_ctx* ctx, int frame_slot, const float* color, int w, int h, int levels)
+{
+	ARG_CHECK(ctx && color, "null argument");
+	ARG_CHECK(frame_slot >= 0 && frame_slot < ctx->n_slots, "frame slot out of range");
+	ARG_CHECK(w >= 16 && h >= 16 && w <= ctx->max_w && h <= ctx->max_h, "image size out of range");
+	ARG_CHECK(levels >= 1 && levels <= MAXL, "levels out of range");
+	ARG_CHECK((w >> (levels - 1)) >= 2 && (h >> (levels - 1)) >= 2, "too many levels for this size");
+	return 0;
+}
+
+static int upload_lut(dso_b200_ctx* ctx, const float* B_lut, const float** d_lut)
+{
+	*d_lut = nullptr;
+	if (B_lut)
+	{
+		CK(cudaMemcpyAsync(ctx->d_Blut, B_lut, 256 * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+		*d_lut = ctx->d_Blut;
+	}
+	return 0;
+}
+
+extern "C" int dso_b200_make_images_dev(dso_b200_ctx* ctx, int frame_slot, const float* color_dev, int w, int h, int levels,
+                                        const float* B_lut_host)
+{
+	int rc = check_image_args(ctx, frame_slot, color_dev, w, h, levels);
+	if (rc) return rc;
+	CK(cudaSetDevice(ctx->device));
+	const float* d_lut;
+	rc = upload_lut(ctx, B_lut_host, &d_lut);
+	if (rc) return rc;
+	return pyramid_build(ctx, ctx->slots[frame_slot], color_dev, w, h, levels, d_lut, false);
+}
+
+extern "C" int dso_b200_make_images(dso_b200_ctx* ctx, int frame_slot, const float* color_host, int w, int h, int levels,
+                                    const float* B_lut, float* const* dIp_out, float* const* absgrad_out)
+{
+	int rc = check_image_args(ctx, frame_slot, color_host, w, h, levels);
+	if (rc) return rc;
+	CK(cudaSetDevice(ctx->device));
+	FrameSlot& F = ctx->slots[frame_slot];
+	const float* d_lut;
+	rc = upload_lut(ctx, B_lut, &d_lut);
+	if (rc) return rc;
+	bool want_host = false;
+	if (dIp_out) for (int l = 0; l < levels; l++) want_host |= (dIp_out[l] != nullptr);
+	if (absgrad_out) for (int l = 0; l < levels; l++) want_host |= (absgrad_out[l] != nullptr);
+	CK(cudaMemcpyAsync(ctx->d_color, color_host, (size_t)w * h * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+	rc = pyramid_build(ctx, F, ctx->d_color, w, h, levels, d_lut, want_host);
+	if (rc) return rc;
+	if (want_host)
+	{
+		for (int l = 0; l < levels; l++)
+		{
+			size_t n = (size_t)(w >> l) * (h >> l);
+			if (dIp_out && dIp_out[l])
+				CK(cudaMemcpyAsync(dIp_out[l], ctx->d_aos[l], 3 * n * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+			if (absgrad_out && absgrad_out[l])
+				CK(cudaMemcpyAsync(absgrad_out[l], ctx->d_abs[l], n * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+		}
+	}
+	CK(cudaStreamSynchronize(ctx->stream));
+	return 0;
+}

@@ -1,0 +1,118 @@
+// Shared declarations of the dso_b200 CUDA library (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdio>
+#include <cstring>
+#include <cstdlib>
+#include <cmath>
+#include <vector>
+#include "../../include/dso_b200.h"
+
+#define MAXL DSO_B200_MAX_LEVELS
+#define MAXF DSO_B200_MAX_FRAMES
+
+void dso_set_error(const char* fmt, ...);
+
+#define CK(call)                                                                                   \
+	do {                                                                                           \
+		cudaError_t e_ = (call);                                                                   \
+		if (e_ != cudaSuccess) {                                                                   \
+			dso_set_error("%s:%d %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_));    \
+			return DSO_B200_E_CUDA;                                                                \
+		}                                                                                          \
+	} while (0)
+
+#define ARG_CHECK(cond, msg)                                                   \
+	do {                                                                       \
+		if (!(cond)) { dso_set_error("%s: %s", __func__, msg); return DSO_B200_E_ARG; } \
+	} while (0)
+
+// Exactly-rounded float helpers: the masks and counts of the reference are decided by float
+// comparisons, so every operation feeding them is a separate IEEE op (never contracted to FMA).
+__device__ __forceinline__ float fmul(float a, float b) { return __fmul_rn(a, b); }
+__device__ __forceinline__ float fadd(float a, float b) { return __fadd_rn(a, b); }
+__device__ __forceinline__ float fsub(float a, float b) { return __fsub_rn(a, b); }
+__device__ __forceinline__ float fdiv(float a, float b) { return __fdiv_rn(a, b); }
+// Eigen's unrolled 3-term redux: c0 + (c1 + c2)
+__device__ __forceinline__ float dot3e(float a0, float b0, float a1, float b1, float a2, float b2)
+{
+	return fadd(fmul(a0, b0), fadd(fmul(a1, b1), fmul(a2, b2)));
+}
+
+// ---- device pyramid of one frame ------------------------------------------------------------------
+// pyr[l]: float4 (I, dx, dy, absSquaredGrad) per pixel -- one 16-byte gather per texel for the tracker
+// and BA.  inten[l]: plain float intensity plane (inten[0] is the uploaded image).
+struct FrameSlot
+{
+	int w, h, levels;
+	bool valid;
+	void* base;
+	float4* pyr[MAXL];
+	float* inten[MAXL];
+};
+
+struct TrackerSlot
+{
+	int levels;
+	int w[MAXL], h[MAXL];
+	float fx[MAXL], fy[MAXL], cx[MAXL], cy[MAXL];
+	float Ki[MAXL][9];
+	int pc_n[MAXL];
+	float4* pc[MAXL];          // (u, v, idepth, color) per reference point
+	void* base;
+	size_t cap_points;         // per level capacity
+	double ref_a, ref_b;
+	float ref_exposure;
+	bool valid;
+	// last calc_res bookkeeping for calc_gs
+	int last_lvl;
+	int last_warped_n;          // padded to a multiple of 4 like buf_warped_n
+	float* d_sums;              // device: reduced sums of the last evaluation
+	float* d_partials;          // device: per-CTA partials
+	unsigned int* d_ticket;
+	float* h_sums;              // pinned
+	// batched tracker workspace
+	void* d_track_in;
+	void* d_track_out;
+	void* h_track_in;
+	void* h_track_out;
+};
+
+struct BAWorkspace;
+
+struct dso_b200_ctx
+{
+	int device;
+	int sm_count;
+	cudaStream_t stream;
+	int max_w, max_h;
+	int n_slots;
+	FrameSlot* slots;
+	// staging for host-layout outputs of makeImages
+	float* d_aos[MAXL];
+	float* d_abs[MAXL];
+	float* d_Blut;
+	float* d_color;            // landing zone of the uploaded input image
+	TrackerSlot trk[2];
+	BAWorkspace* ba;
+	long long launches;
+};
+
+// sums layout of one tracker evaluation
+enum
+{
+	S_E = 0,          // energy
+	S_FLOW_T = 1,     // sumSquaredShiftT
+	S_FLOW_RT = 2,    // sumSquaredShiftRT
+	S_FLOW_N = 3,     // sumSquaredShiftNum
+	S_NTERMS = 4,     // numTermsInE        (exact integer in float: < 2^24)
+	S_NSAT = 5,       // numSaturated
+	S_NWARP = 6,      // numTermsInWarped (unpadded)
+	S_ACC = 8,        // 44 values: upper triangle of the 8x8 (36, row-major r<=c) then J^T r (8)
+	S_COUNT = 52
+};
+
+int pyramid_build(dso_b200_ctx* ctx, FrameSlot& fs, const float* color_dev, int w, int h, int levels,
+                  const float* d_Blut, bool host_layout);
+int ba_create(dso_b200_ctx* ctx);
+void ba_destroy(dso_b200_ctx* ctx);

@@ -1,0 +1,152 @@
+// Double-precision pieces of the coarse tracker's LM step, usable from host and device:
+// 8x8 LDL^T solve (Eigen::LDLT semantics: diagonal pivoting, CoarseTracker.cpp:618), SE3 exponential
+// and composition (Sophus SE3::exp / operator*, CoarseTracker.cpp:661), AffLight::fromToVecExposure
+// (util/NumType.h:176-189) and the float conversions of CoarseTracker.cpp:375-378.
+#pragma once
+#include <cuda_runtime.h>
+#include <math.h>
+
+#define HD __host__ __device__ __forceinline__
+
+struct Pose
+{
+	double R[9];
+	double t[3];
+};
+
+HD void pose_identity(Pose& p)
+{
+	for (int i = 0; i < 9; i++) p.R[i] = (i % 4 == 0) ? 1.0 : 0.0;
+	p.t[0] = p.t[1] = p.t[2] = 0.0;
+}
+HD void pose_from12(Pose& p, const double* v)
+{
+	for (int i = 0; i < 9; i++) p.R[i] = v[i];
+	for (int i = 0; i < 3; i++) p.t[i] = v[9 + i];
+}
+HD void pose_to12(const Pose& p, double* v)
+{
+	for (int i = 0; i < 9; i++) v[i] = p.R[i];
+	for (int i = 0; i < 3; i++) v[9 + i] = p.t[i];
+}
+// c = a * b
+HD void pose_mul(const Pose& a, const Pose& b, Pose& c)
+{
+	Pose o;
+	for (int r = 0; r < 3; r++)
+	{
+		for (int k = 0; k < 3; k++)
+			o.R[r * 3 + k] = a.R[r * 3 + 0] * b.R[k] + a.R[r * 3 + 1] * b.R[3 + k] + a.R[r * 3 + 2] * b.R[6 + k];
+		o.t[r] = a.R[r * 3 + 0] * b.t[0] + a.R[r * 3 + 1] * b.t[1] + a.R[r * 3 + 2] * b.t[2] + a.t[r];
+	}
+	c = o;
+}
+// xi = (translation part u[3], rotation part w[3]);  R = I + A W + B W^2,  t = (I + B W + C W^2) u
+HD void se3_exp(const double* xi, Pose& o)
+{
+	const double ux = xi[0], uy = xi[1], uz = xi[2];
+	const double wx = xi[3], wy = xi[4], wz = xi[5];
+	const double th2 = wx * wx + wy * wy + wz * wz;
+	const double th = sqrt(th2);
+	double A, B, C;
+	if (th < 1e-5)
+	{
+		A = 1.0 - th2 / 6.0 + th2 * th2 / 120.0;
+		B = 0.5 - th2 / 24.0 + th2 * th2 / 720.0;
+		C = 1.0 / 6.0 - th2 / 120.0 + th2 * th2 / 5040.0;
+	}
+	else
+	{
+		double s, c;
+#ifdef __CUDA_ARCH__
+		sincos(th, &s, &c);
+#else
+		s = sin(th); c = cos(th);
+#endif
+		A = s / th;
+		B = (1.0 - c) / th2;
+		C = (th - s) / (th2 * th);
+	}
+	// W = hat(w), W2 = W*W = w w^T - th2 I
+	const double W[9] = { 0, -wz, wy, wz, 0, -wx, -wy, wx, 0 };
+	const double W2[9] = { wx * wx - th2, wx * wy, wx * wz, wx * wy, wy * wy - th2, wy * wz, wx * wz, wy * wz, wz * wz - th2 };
+	const double u[3] = { ux, uy, uz };
+	for (int i = 0; i < 9; i++) o.R[i] = ((i % 4 == 0) ? 1.0 : 0.0) + A * W[i] + B * W2[i];
+	for (int r = 0; r < 3; r++)
+	{
+		double s = 0;
+		for (int c = 0; c < 3; c++) s += (((r == c) ? 1.0 : 0.0) + B * W[r * 3 + c] + C * W2[r * 3 + c]) * u[c];
+		o.t[r] = s;
+	}
+}
+
+// AffLight::fromToVecExposure (NumType.h:176-189)
+HD void aff_from_to(float exposureF, float exposureT, double Fa, double Fb, double Ta, double Tb, double& a, double& b)
+{
+	if (exposureF == 0 || exposureT == 0) exposureT = exposureF = 1;
+	a = exp(Ta - Fa) * exposureT / exposureF;
+	b = Tb - a * Fb;
+}
+
+// LDL^T with diagonal pivoting on the (not yet updated) diagonal, as Eigen's unblocked LDLT does;
+// A row-major with row stride 8, n <= 8.  Solves A x = rhs.
+HD void ldlt_solve(const double* Ain, const double* rhs, double* x, int n)
+{
+	double A[64];
+	int tr[8];
+	for (int i = 0; i < n; i++) for (int j = 0; j < n; j++) A[i * 8 + j] = Ain[i * 8 + j];
+	for (int k = 0; k < n; k++)
+	{
+		int p = k;
+		double best = fabs(A[k * 8 + k]);
+		for (int i = k + 1; i < n; i++) { double v = fabs(A[i * 8 + i]); if (v > best) { best = v; p = i; } }
+		tr[k] = p;
+		if (p != k)
+		{
+			for (int j = 0; j < n; j++) { double t = A[k * 8 + j]; A[k * 8 + j] = A[p * 8 + j]; A[p * 8 + j] = t; }
+			for (int i = 0; i < n; i++) { double t = A[i * 8 + k]; A[i * 8 + k] = A[i * 8 + p]; A[i * 8 + p] = t; }
+		}
+		for (int j = 0; j < k; j++) A[k * 8 + k] -= A[k * 8 + j] * A[k * 8 + j] * A[j * 8 + j];
+		const double d = A[k * 8 + k];
+		for (int i = k + 1; i < n; i++)
+		{
+			double s = A[i * 8 + k];
+			for (int j = 0; j < k; j++) s -= A[i * 8 + j] * A[k * 8 + j] * A[j * 8 + j];
+			s = (fabs(d) > 0.0) ? s / d : 0.0;
+			A[i * 8 + k] = s;
+			A[k * 8 + i] = s;
+		}
+	}
+	double y[8];
+	for (int i = 0; i < n; i++) y[i] = rhs[i];
+	for (int k = 0; k < n; k++) { double t = y[k]; y[k] = y[tr[k]]; y[tr[k]] = t; }
+	for (int i = 0; i < n; i++) for (int j = 0; j < i; j++) y[i] -= A[i * 8 + j] * y[j];
+	for (int i = 0; i < n; i++)
+	{
+		const double d = A[i * 8 + i];
+		y[i] = (fabs(d) > 2.2250738585072014e-308) ? y[i] / d : 0.0;
+	}
+	for (int i = n - 1; i >= 0; i--) for (int j = i + 1; j < n; j++) y[i] -= A[j * 8 + i] * y[j];
+	for (int k = n - 1; k >= 0; k--) { double t = y[k]; y[k] = y[tr[k]]; y[tr[k]] = t; }
+	for (int i = 0; i < n; i++) x[i] = y[i];
+}
+
+// Eigen's fixed-size float 3x3 product: each coefficient is c0 + (c1 + c2)
+HD float dot3h(float a0, float b0, float a1, float b1, float a2, float b2)
+{
+#ifdef __CUDA_ARCH__
+	return __fadd_rn(__fmul_rn(a0, b0), __fadd_rn(__fmul_rn(a1, b1), __fmul_rn(a2, b2)));
+#else
+	volatile float p0 = a0 * b0, p1 = a1 * b1, p2 = a2 * b2;   // volatile: keep the host compiler from contracting
+	volatile float s12 = p1 + p2;
+	return p0 + s12;
+#endif
+}
+HD void mat33f_mul(const float* A, const float* B, float* C)
+{
+	float T[9];
+	for (int r = 0; r < 3; r++)
+		for (int c = 0; c < 3; c++)
+			T[r * 3 + c] = dot3h(A[r * 3 + 0], B[c], A[r * 3 + 1], B[3 + c], A[r * 3 + 2], B[6 + c]);
+	for (int i = 0; i < 9; i++) C[i] = T[i];
+}

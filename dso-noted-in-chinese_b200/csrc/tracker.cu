@@ -1,0 +1,825 @@
+// K2 -- frame-to-keyframe tracker, replaces CoarseTracker::calcRes / calcGSSSE / trackNewestCoarse
+// (reference: FullSystem/CoarseTracker.cpp:296-354, 359-520, 551-747).
+//
+// One evaluation = for every reference point: warp, bounds test, bilinear sample of the new frame's
+// float4 (I,dx,dy,.) texels, affine-corrected residual, Huber weight, cut-off, and the weighted outer
+// product of the 8-DoF Jacobian [6 pose, a, b | r] -- calcRes and calcGSSSE fused, so the reference's
+// buf_warped_* arrays never exist.  Everything that decides a mask or a count is computed with
+// individually rounded float ops in the reference's evaluation order (bit-exact vs. its SSE2 build);
+// the 44 sums of J^T W J / J^T W r are FP32 per thread, then a fixed-order warp-shuffle / shared-memory
+// / cluster tree (deterministic, no atomics on data).
+//
+//   track_eval_kernel        one evaluation, grid-wide, last-CTA-done final sum (drop-in for the two
+//                            private methods; host drives the LM loop)
+//   track_persistent_kernel  the whole coarse-to-fine LM loop of trackNewestCoarse for up to 32 pose
+//                            hypotheses, one thread-block cluster per hypothesis; partial sums are
+//                            exchanged through distributed shared memory, the 8x8 LDL^T solve and the
+//                            SE3 update run in FP64 on the device; no host round trip until all
+//                            levels are done.
+//
+// Roofline: gather-bound (L2 at VGA, HBM for the large sweeps): per point 16 B of cloud + 4 x 16 B
+// texels, ~170 flop.
+#include "common.cuh"
+#include "lm_math.cuh"
+#include <cooperative_groups.h>
+namespace cg = cooperative_groups;
+
+#define SCALE_XI_ROT 1.0f
+#define SCALE_XI_TRANS 0.5f
+#define SCALE_A 10.0f
+#define SCALE_B 1000.0f
+
+#define EVAL_THREADS 256
+#define PERS_THREADS 512
+#define MAX_CLUSTER 16
+
+struct EvalParams
+{
+	float RKi[9], t[3], Ki[9];
+	float affLL0, affLL1;
+	float fx, fy, cx, cy;
+	float wl_m3, hl_m3;
+	int wl, n, lvl0;
+	float cutoffTH, maxEnergy, huberTH;
+	float b0;
+};
+
+struct TrackLevels
+{
+	int levels;
+	int w[MAXL], h[MAXL];
+	float fx[MAXL], fy[MAXL], cx[MAXL], cy[MAXL];
+	float Ki[MAXL][9];
+	const float4* pc[MAXL];
+	int pc_n[MAXL];
+	const float4* img[MAXL];
+	double ref_a, ref_b;
+	float ref_exposure, new_exposure;
+};
+
+// CoarseTracker.cpp:375-378, 385 : pose/affine (double) -> the float quantities of one calcRes call
+HD void make_eval_params(const TrackLevels& TL, int lvl, const Pose& refToNew, double aff_a, double aff_b,
+                         float cutoffTH, float huberTH, EvalParams& P)
+{
+	float Rf[9];
+	for (int i = 0; i < 9; i++) Rf[i] = (float)refToNew.R[i];
+	mat33f_mul(Rf, TL.Ki[lvl], P.RKi);
+	for (int i = 0; i < 3; i++) P.t[i] = (float)refToNew.t[i];
+	for (int i = 0; i < 9; i++) P.Ki[i] = TL.Ki[lvl][i];
+	double a, b;
+	aff_from_to(TL.ref_exposure, TL.new_exposure, TL.ref_a, TL.ref_b, aff_a, aff_b, a, b);
+	P.affLL0 = (float)a; P.affLL1 = (float)b;
+	P.fx = TL.fx[lvl]; P.fy = TL.fy[lvl]; P.cx = TL.cx[lvl]; P.cy = TL.cy[lvl];
+	P.wl = TL.w[lvl];
+	P.wl_m3 = (float)(TL.w[lvl] - 3); P.hl_m3 = (float)(TL.h[lvl] - 3);
+	P.n = TL.pc_n[lvl];
+	P.lvl0 = (lvl == 0);
+	P.cutoffTH = cutoffTH;
+	P.huberTH = huberTH;
+#ifdef __CUDA_ARCH__
+	P.maxEnergy = __fsub_rn(__fmul_rn(__fmul_rn(2.0f, huberTH), cutoffTH), __fmul_rn(huberTH, huberTH));
+#else
+	{ volatile float t0 = 2 * huberTH; volatile float t1 = t0 * cutoffTH; volatile float t2 = huberTH * huberTH; P.maxEnergy = t1 - t2; }
+#endif
+	P.b0 = (float)TL.ref_b;
+}
+
+__device__ __forceinline__ void proj3(const float* M, float x, float y, const float* t, float id, float sgn, float* pt)
+{
+#pragma unroll
+	for (int r = 0; r < 3; r++)
+	{
+		float p = dot3e(M[r * 3], x, M[r * 3 + 1], y, M[r * 3 + 2], 1.0f);
+		float tid = fmul(t[r], id);
+		pt[r] = sgn > 0 ? fadd(p, tid) : fsub(p, tid);
+	}
+}
+
+// One reference point of calcRes (CoarseTracker.cpp:402-486) + its calcGSSSE contribution (:313-334).
+template <bool DEBUG>
+__device__ __forceinline__ void eval_point(const float4 pc, int i, const EvalParams& P, const float4* __restrict__ img,
+                                           float* acc, unsigned char* status, float* warped)
+{
+	const float id = pc.z, x = pc.x, y = pc.y;
+	float pt[3];
+	proj3(P.RKi, x, y, P.t, id, 1.f, pt);                // :408
+	const float u = fdiv(pt[0], pt[2]);
+	const float v = fdiv(pt[1], pt[2]);
+	const float Ku = fadd(fmul(P.fx, u), P.cx);
+	const float Kv = fadd(fmul(P.fy, v), P.cy);
+	const float new_idepth = fdiv(id, pt[2]);
+
+	if (P.lvl0 && (i & 31) == 0)                         // :416-447 flow indicators
+	{
+		float q[3];
+		proj3(P.Ki, x, y, P.t, id, 1.f, q);
+		float KuT = fadd(fmul(P.fx, fdiv(q[0], q[2])), P.cx), KvT = fadd(fmul(P.fy, fdiv(q[1], q[2])), P.cy);
+		proj3(P.Ki, x, y, P.t, id, -1.f, q);
+		float KuT2 = fadd(fmul(P.fx, fdiv(q[0], q[2])), P.cx), KvT2 = fadd(fmul(P.fy, fdiv(q[1], q[2])), P.cy);
+		proj3(P.RKi, x, y, P.t, id, -1.f, q);
+		float Ku3 = fadd(fmul(P.fx, fdiv(q[0], q[2])), P.cx), Kv3 = fadd(fmul(P.fy, fdiv(q[1], q[2])), P.cy);
+		float a0 = fsub(KuT, x), a1 = fsub(KvT, y), b0 = fsub(KuT2, x), b1 = fsub(KvT2, y);
+		float c0 = fsub(Ku, x), c1 = fsub(Kv, y), d0 = fsub(Ku3, x), d1 = fsub(Kv3, y);
+		acc[S_FLOW_T] += fadd(fmul(a0, a0), fmul(a1, a1));
+		acc[S_FLOW_T] += fadd(fmul(b0, b0), fmul(b1, b1));
+		acc[S_FLOW_RT] += fadd(fmul(c0, c0), fmul(c1, c1));
+		acc[S_FLOW_RT] += fadd(fmul(d0, d0), fmul(d1, d1));
+		acc[S_FLOW_N] += 2.f;
+	}
+
+	if (DEBUG) status[i] = 0;
+	if (!(Ku > 2.f && Kv > 2.f && Ku < P.wl_m3 && Kv < P.hl_m3 && new_idepth > 0.f)) return;   // :449
+
+	// getInterpolatedElement33, util/globalFuncs.h:75-89, on the float4 texel layout
+	const int ix = (int)Ku, iy = (int)Kv;
+	const float dx = fsub(Ku, (float)ix), dy = fsub(Kv, (float)iy);
+	const float dxdy = fmul(dx, dy);
+	const float w11 = dxdy, w01 = fsub(dy, dxdy), w10 = fsub(dx, dxdy);
+	const float w00 = fadd(fsub(fsub(1.f, dx), dy), dxdy);
+	const float4* bp = img + ix + iy * P.wl;
+	const float4 p00 = __ldg(bp), p10 = __ldg(bp + 1), p01 = __ldg(bp + P.wl), p11 = __ldg(bp + 1 + P.wl);
+	const float h0 = fadd(fadd(fadd(fmul(w11, p11.x), fmul(w01, p01.x)), fmul(w10, p10.x)), fmul(w00, p00.x));
+	const float h1 = fadd(fadd(fadd(fmul(w11, p11.y), fmul(w01, p01.y)), fmul(w10, p10.y)), fmul(w00, p00.y));
+	const float h2 = fadd(fadd(fadd(fmul(w11, p11.z), fmul(w01, p01.z)), fmul(w10, p10.z)), fmul(w00, p00.z));
+	if (!isfinite(h0)) return;                           // :456
+	const float refColor = pc.w;
+	const float residual = fsub(h0, fadd(fmul(P.affLL0, refColor), P.affLL1));   // :458
+	const float ar = fabsf(residual);
+	const float hw = ar < P.huberTH ? 1.f : fdiv(P.huberTH, ar);                  // :459
+
+	if (ar > P.cutoffTH)                                 // :462-468
+	{
+		acc[S_E] += P.maxEnergy;
+		acc[S_NTERMS] += 1.f;
+		acc[S_NSAT] += 1.f;
+		if (DEBUG) status[i] = 1;
+		return;
+	}
+	acc[S_E] += fmul(fmul(fmul(hw, residual), residual), fsub(2.f, hw));   // :473
+	acc[S_NTERMS] += 1.f;
+	acc[S_NWARP] += 1.f;
+	if (DEBUG)
+	{
+		status[i] = 2;
+		float* wp = warped + 8 * (size_t)i;
+		wp[0] = new_idepth; wp[1] = u; wp[2] = v; wp[3] = h1; wp[4] = h2; wp[5] = residual; wp[6] = hw; wp[7] = refColor;
+	}
+	// calcGSSSE :313-334
+	const float gx = fmul(h1, P.fx), gy = fmul(h2, P.fy);
+	float J[9];
+	J[0] = fmul(new_idepth, gx);
+	J[1] = fmul(new_idepth, gy);
+	J[2] = -fmul(new_idepth, fadd(fmul(u, gx), fmul(v, gy)));
+	J[3] = -fadd(fmul(fmul(u, v), gx), fmul(gy, fadd(1.f, fmul(v, v))));
+	J[4] = fadd(fmul(fmul(u, v), gy), fmul(gx, fadd(1.f, fmul(u, u))));
+	J[5] = fsub(fmul(u, gy), fmul(v, gx));
+	J[6] = fmul(P.affLL0, fsub(P.b0, refColor));
+	J[7] = -1.f;
+	J[8] = residual;
+	int k = S_ACC;
+#pragma unroll
+	for (int r = 0; r < 8; r++)
+	{
+		const float Jw = fmul(J[r], hw);
+#pragma unroll
+		for (int c = r; c < 8; c++) { acc[k] = fmaf(Jw, J[c], acc[k]); k++; }
+	}
+#pragma unroll
+	for (int r = 0; r < 8; r++) { acc[k] = fmaf(fmul(J[r], hw), J[8], acc[k]); k++; }
+}
+
+// Fixed-order CTA reduction of S_COUNT per-thread sums: xor-butterfly inside each warp, then the
+// warps in index order.  Result in s_out[0..S_COUNT) (valid after the trailing __syncthreads).
+template <int NWARPS>
+__device__ __forceinline__ void block_reduce(float* acc, float (*s_w)[S_COUNT], float* s_out)
+{
+	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+	for (int k = 0; k < S_COUNT; k++)
+	{
+		float v = acc[k];
+#pragma unroll
+		for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+		acc[k] = v;
+	}
+	if (lane == 0)
+	{
+#pragma unroll
+		for (int k = 0; k < S_COUNT; k++) s_w[warp][k] = acc[k];
+	}
+	__syncthreads();
+	if (threadIdx.x < S_COUNT)
+	{
+		float s = 0.f;
+#pragma unroll
+		for (int w = 0; w < NWARPS; w++) s += s_w[w][threadIdx.x];
+		s_out[threadIdx.x] = s;
+	}
+	__syncthreads();
+}
+
+// ---- K2a ------------------------------------------------------------------------------------------
+template <bool DEBUG>
+__global__ void __launch_bounds__(EVAL_THREADS) track_eval_kernel(EvalParams P, const float4* __restrict__ pts,
+                                                                  const float4* __restrict__ img, float* partials,
+                                                                  unsigned int* ticket, float* sums_out,
+                                                                  unsigned char* status, float* warped)
+{
+	__shared__ float s_w[EVAL_THREADS / 32][S_COUNT];
+	__shared__ float s_out[S_COUNT];
+	__shared__ bool s_last;
+	float acc[S_COUNT];
+#pragma unroll
+	for (int k = 0; k < S_COUNT; k++) acc[k] = 0.f;
+	for (int i = blockIdx.x * EVAL_THREADS + threadIdx.x; i < P.n; i += gridDim.x * EVAL_THREADS)
+		eval_point<DEBUG>(__ldg(pts + i), i, P, img, acc, status, warped);
+	block_reduce<EVAL_THREADS / 32>(acc, s_w, s_out);
+	if (threadIdx.x < S_COUNT) partials[blockIdx.x * S_COUNT + threadIdx.x] = s_out[threadIdx.x];
+	__threadfence();
+	__syncthreads();
+	if (threadIdx.x == 0)
+	{
+		unsigned int t = atomicAdd(ticket, 1u);
+		s_last = (t == gridDim.x - 1);
+	}
+	__syncthreads();
+	if (s_last)
+	{
+		__threadfence();
+		if (threadIdx.x < S_COUNT)
+		{
+			float s = 0.f;
+			for (unsigned b = 0; b < gridDim.x; b++) s += __ldcg(partials + b * S_COUNT + threadIdx.x);
+			sums_out[threadIdx.x] = s;
+		}
+		if (threadIdx.x == 0) *ticket = 0;
+	}
+}
+
+// ---- LM bookkeeping shared by the host loop and the persistent kernel --------------------------------
+struct EvalResult
+{
+	double E, n, flowT, flowRT, sat;   // Vec6 rs of calcRes (:511-519); rs[3] is always 0
+	double H[64], b[8];                // calcGSSSE output (:338-353)
+};
+
+// sums of one evaluation -> the reference's Vec6 and scaled H, b
+HD void sums_to_result(const float* s, EvalResult& r)
+{
+	r.E = (double)s[S_E];
+	r.n = (double)s[S_NTERMS];
+	r.flowT = (double)s[S_FLOW_T] / ((double)s[S_FLOW_N] + 0.1);    // float / (float + 0.1) -> double
+	r.flowRT = (double)s[S_FLOW_RT] / ((double)s[S_FLOW_N] + 0.1);
+	r.sat = (double)(s[S_NSAT] / s[S_NTERMS]);                       // numSaturated / (float)numTermsInE
+	const int nw = (int)s[S_NWARP];
+	const int npad = (nw + 3) & ~3;                                  // :488-499 padding to a multiple of 4
+	const float invn = 1.0f / (float)npad;
+	const float sc[8] = { SCALE_XI_ROT, SCALE_XI_ROT, SCALE_XI_ROT, SCALE_XI_TRANS, SCALE_XI_TRANS, SCALE_XI_TRANS, SCALE_A, SCALE_B };
+	int k = S_ACC;
+	for (int i = 0; i < 8; i++)
+		for (int j = i; j < 8; j++)
+		{
+			double v = (double)s[k++] * (double)invn;
+			v *= (double)sc[j];
+			v *= (double)sc[i];
+			r.H[i * 8 + j] = v;
+			r.H[j * 8 + i] = v;
+		}
+	for (int i = 0; i < 8; i++) r.b[i] = (double)s[k++] * (double)invn * (double)sc[i];
+}
+
+// State machine of trackNewestCoarse (CoarseTracker.cpp:551-747): feed it the result of each
+// evaluation, it answers with the next evaluation to run (pose, affine, level, cut-off) or "done".
+struct LM
+{
+	dso_b200_track_opts opt;
+	int lvl, iteration, phase, haveRepeated, done, aborted;
+	float levelCutoffRepeat, lambda;
+	Pose cur, nw;
+	double a_cur, b_cur, a_new, b_new;
+	double resOldE, resOldN, resOldFlowT, resOldFlowRT;
+	double H[64], b[8];
+	double incnorm;
+	double minRes[5];
+	double ref_a, ref_b;            // lastRef_aff_g2l
+	float ref_exposure, new_exposure;
+	dso_b200_track_result* out;
+
+	// request produced for the caller
+	int req_lvl; float req_cutoff; Pose req_pose; double req_a, req_b;
+
+	HD void request(int l, const Pose& p, double a, double b_)
+	{
+		req_lvl = l; req_pose = p; req_a = a; req_b = b_;
+		req_cutoff = opt.coarseCutoffTH * levelCutoffRepeat;
+	}
+	HD void init(const dso_b200_track_opts& o, const TrackLevels& TL, const double* pose12, double a0, double b0,
+	             int coarsestLvl, const double* minResForAbort, dso_b200_track_result* res)
+	{
+		opt = o; out = res;
+		ref_a = TL.ref_a; ref_b = TL.ref_b; ref_exposure = TL.ref_exposure; new_exposure = TL.new_exposure;
+		pose_from12(cur, pose12); a_cur = a0; b_cur = b0;
+		haveRepeated = 0; done = 0; aborted = 0;
+		for (int i = 0; i < 5; i++) minRes[i] = minResForAbort ? minResForAbort[i] : NAN;
+		out->ok = 0; out->reserved = -1;
+		for (int i = 0; i < 12; i++) out->pose[i] = pose12[i];
+		out->aff_a = a0; out->aff_b = b0;
+		for (int i = 0; i < 5; i++) out->lastResiduals[i] = NAN;        // :563
+		for (int i = 0; i < 3; i++) out->lastFlowIndicators[i] = 1000;  // :564
+		out->n_passes = 0; out->n_iterations = 0; out->n_evals = 0; out->trace_len = 0; out->point_evals = 0;
+		start_level(coarsestLvl);
+	}
+	HD void start_level(int l)
+	{
+		lvl = l; phase = 0; levelCutoffRepeat = 1; iteration = 0;
+		request(lvl, cur, a_cur, b_cur);   // :584
+	}
+	// :613-665 solve for the increment and propose the new state
+	HD void propose()
+	{
+		double Hl[64], nb[8], inc[8];
+		for (int i = 0; i < 64; i++) Hl[i] = H[i];
+		for (int i = 0; i < 8; i++) Hl[i * 8 + i] *= (1 + lambda);
+		for (int i = 0; i < 8; i++) nb[i] = -b[i];
+		ldlt_solve(Hl, nb, inc, 8);
+		const bool fixA = opt.affineOptModeA < 0, fixB = opt.affineOptModeB < 0;
+		if (fixA && fixB) { ldlt_solve(Hl, nb, inc, 6); inc[6] = inc[7] = 0; }
+		if (!fixA && fixB) { ldlt_solve(Hl, nb, inc, 7); inc[7] = 0; }
+		if (fixA && !fixB)
+		{
+			double Hs[64], bs[8], is[8];
+			for (int i = 0; i < 64; i++) Hs[i] = Hl[i];
+			for (int i = 0; i < 8; i++) bs[i] = nb[i];
+			for (int i = 0; i < 8; i++) Hs[i * 8 + 6] = Hs[i * 8 + 7];
+			for (int i = 0; i < 8; i++) Hs[6 * 8 + i] = Hs[7 * 8 + i];
+			bs[6] = bs[7];
+			ldlt_solve(Hs, bs, is, 7);
+			for (int i = 0; i < 6; i++) inc[i] = is[i];
+			inc[6] = 0; inc[7] = is[6];
+		}
+		float extrapFac = 1;
+		const float lambdaExtrapolationLimit = 0.001f;
+		if (lambda < lambdaExtrapolationLimit) extrapFac = sqrtf(sqrtf(lambdaExtrapolationLimit / lambda));   // :650
+		double nrm = 0;
+		for (int i = 0; i < 8; i++) { inc[i] *= extrapFac; nrm += inc[i] * inc[i]; }
+		incnorm = sqrt(nrm);
+		double is[8];
+		for (int i = 0; i < 8; i++) is[i] = inc[i];
+		for (int i = 0; i < 3; i++) is[i] *= SCALE_XI_ROT;
+		for (int i = 3; i < 6; i++) is[i] *= SCALE_XI_TRANS;
+		is[6] *= SCALE_A; is[7] *= SCALE_B;
+		double sum = 0;
+		for (int i = 0; i < 8; i++) sum += is[i];
+		if (!isfinite(sum)) for (int i = 0; i < 8; i++) is[i] = 0;   // :659
+		Pose e;
+		se3_exp(is, e);
+		pose_mul(e, cur, nw);                                          // :661
+		a_new = a_cur + is[6]; b_new = b_cur + is[7];
+		request(lvl, nw, a_new, b_new);                                // :667
+	}
+	HD void finish_level()
+	{
+		const float rmse = sqrtf((float)(resOldE / resOldN));          // :710
+		out->lastResiduals[lvl] = rmse;
+		out->lastFlowIndicators[0] = resOldFlowT; out->lastFlowIndicators[1] = 0; out->lastFlowIndicators[2] = resOldFlowRT;
+		if (out->n_passes < DSO_B200_MAX_PASSES) { out->pass_level[out->n_passes] = lvl; out->pass_rmse[out->n_passes] = rmse; out->n_passes++; }
+		if (out->lastResiduals[lvl] > 1.5 * minRes[lvl]) { done = 1; aborted = 1; out->ok = 0; out->reserved = lvl; return; }   // :713
+		int next = lvl - 1;
+		if (levelCutoffRepeat > 1 && !haveRepeated) { next = lvl; haveRepeated = 1; }   // :717-722
+		if (next < 0) { finalize(); return; }
+		start_level(next);
+	}
+	HD void finalize()
+	{
+		done = 1;
+		pose_to12(cur, out->pose);                                     // :727-728
+		out->aff_a = a_cur; out->aff_b = b_cur;
+		out->ok = 1;
+		if ((opt.affineOptModeA != 0 && (fabsf((float)out->aff_a) > 1.2f)) || (opt.affineOptModeB != 0 && (fabsf((float)out->aff_b) > 200.f)))
+		{ out->ok = 0; return; }
+		double ra, rb;
+		aff_from_to(ref_exposure, new_exposure, ref_a, ref_b, out->aff_a, out->aff_b, ra, rb);   // :735-739
+		if ((opt.affineOptModeA == 0 && (fabsf(logf((float)ra)) > 1.5f)) || (opt.affineOptModeB == 0 && (fabsf((float)rb) > 200.f)))
+		{ out->ok = 0; return; }
+		if (opt.affineOptModeA < 0) out->aff_a = 0;
+		if (opt.affineOptModeB < 0) out->aff_b = 0;
+	}
+	// feed one evaluation result; afterwards either done!=0 or req_* holds the next evaluation
+	HD void step(const EvalResult& r, int n_points)
+	{
+		out->n_evals++; out->point_evals += n_points;
+		if (phase == 0)
+		{
+			if (r.sat > 0.6 && levelCutoffRepeat < 50)                 // :586-593
+			{
+				levelCutoffRepeat *= 2;
+				request(lvl, cur, a_cur, b_cur);
+				return;
+			}
+			resOldE = r.E; resOldN = r.n; resOldFlowT = r.flowT; resOldFlowRT = r.flowRT;
+			for (int i = 0; i < 64; i++) H[i] = r.H[i];
+			for (int i = 0; i < 8; i++) b[i] = r.b[i];
+			lambda = 0.01f;
+			iteration = 0;
+			phase = 1;
+			if (iteration >= opt.maxIterations[lvl]) { finish_level(); return; }
+			propose();
+			return;
+		}
+		const bool accept = (r.E / r.n) < (resOldE / resOldN);         // :669
+		if (out->trace_len < 256) out->trace[out->trace_len++] = accept ? 1 : 0;
+		out->n_iterations++;
+		if (accept)
+		{
+			for (int i = 0; i < 64; i++) H[i] = r.H[i];
+			for (int i = 0; i < 8; i++) b[i] = r.b[i];
+			resOldE = r.E; resOldN = r.n; resOldFlowT = r.flowT; resOldFlowRT = r.flowRT;
+			a_cur = a_new; b_cur = b_new; cur = nw;
+			lambda *= 0.5f;
+		}
+		else
+		{
+			lambda *= 4;
+			if (lambda < 0.001f) lambda = 0.001f;
+		}
+		iteration++;
+		if (!(incnorm > 1e-3) || iteration >= opt.maxIterations[lvl]) { finish_level(); return; }   // :700, :613
+		propose();
+	}
+};
+
+// ---- K2b ------------------------------------------------------------------------------------------
+struct TrackIn
+{
+	double pose[12];
+	double aff_a, aff_b;
+	double minRes[5];
+};
+
+__global__ void __launch_bounds__(PERS_THREADS, 1)
+track_persistent_kernel(TrackLevels TL, dso_b200_track_opts opt, const TrackIn* __restrict__ in,
+                        dso_b200_track_result* out, int coarsestLvl, int smem_pts_cap)
+{
+	cg::cluster_group cluster = cg::this_cluster();
+	const unsigned CS = cluster.num_blocks();
+	const unsigned rank = cluster.block_rank();
+	const int hyp = blockIdx.x / CS;
+	const int tid = threadIdx.x;
+
+	__shared__ EvalParams sP;
+	__shared__ int sDone, sLvl, sRestage;
+	__shared__ float s_w[PERS_THREADS / 32][S_COUNT];
+	__shared__ float s_part[S_COUNT];
+	__shared__ float xchg[2][MAX_CLUSTER][S_COUNT];
+	__shared__ float s_tot[S_COUNT];
+	__shared__ dso_b200_track_result s_res;
+	extern __shared__ float4 s_pts[];
+
+	LM lm;   // meaningful in thread 0 only; every CTA of the cluster runs the identical sequence
+	if (tid == 0)
+	{
+		lm.init(opt, TL, in[hyp].pose, in[hyp].aff_a, in[hyp].aff_b, coarsestLvl, in[hyp].minRes, &s_res);
+		make_eval_params(TL, lm.req_lvl, lm.req_pose, lm.req_a, lm.req_b, lm.req_cutoff, opt.huberTH, sP);
+		sDone = 0; sLvl = lm.req_lvl; sRestage = 1;
+	}
+	__syncthreads();
+	int buf = 0;
+	int staged_lvl = -1;
+	while (true)
+	{
+		const int lvl = sLvl;
+		const int n = TL.pc_n[lvl];
+		const int per = (n + CS - 1) / CS;
+		const int beg = min((int)rank * per, n), end = min(beg + per, n);
+		const float4* __restrict__ gp = TL.pc[lvl];
+		const bool use_smem = (end - beg) <= smem_pts_cap;
+		if (use_smem && staged_lvl != lvl)
+		{
+			for (int i = beg + tid; i < end; i += PERS_THREADS) s_pts[i - beg] = __ldg(gp + i);
+			staged_lvl = lvl;
+			__syncthreads();
+		}
+		const EvalParams P = sP;
+		const float4* __restrict__ img = TL.img[lvl];
+		float acc[S_COUNT];
+#pragma unroll
+		for (int k = 0; k < S_COUNT; k++) acc[k] = 0.f;
+		if (use_smem)
+			for (int i = beg + tid; i < end; i += PERS_THREADS) eval_point<false>(s_pts[i - beg], i, P, img, acc, nullptr, nullptr);
+		else
+			for (int i = beg + tid; i < end; i += PERS_THREADS) eval_point<false>(__ldg(gp + i), i, P, img, acc, nullptr, nullptr);
+		block_reduce<PERS_THREADS / 32>(acc, s_w, s_part);
+		// push this CTA's partial into every CTA of the cluster (distributed shared memory)
+		for (unsigned idx = tid; idx < CS * S_COUNT; idx += PERS_THREADS)
+		{
+			unsigned r = idx / S_COUNT, k = idx - r * S_COUNT;
+			float* dst = cluster.map_shared_rank(&xchg[buf][rank][k], r);
+			*dst = s_part[k];
+		}
+		cluster.sync();
+		if (tid < S_COUNT)
+		{
+			float s = 0.f;
+			for (unsigned r = 0; r < CS; r++) s += xchg[buf][r][tid];
+			s_tot[tid] = s;
+		}
+		__syncthreads();
+		if (tid == 0)
+		{
+			EvalResult er;
+			sums_to_result(s_tot, er);
+			lm.step(er, n);
+			if (lm.done) sDone = 1;
+			else
+			{
+				make_eval_params(TL, lm.req_lvl, lm.req_pose, lm.req_a, lm.req_b, lm.req_cutoff, opt.huberTH, sP);
+				sLvl = lm.req_lvl;
+			}
+		}
+		__syncthreads();
+		if (sDone) break;
+		buf ^= 1;
+	}
+	if (rank == 0)
+	{
+		// copy the result struct out with all threads (plain words)
+		const int nwords = sizeof(dso_b200_track_result) / 4;
+		const unsigned int* src = reinterpret_cast<const unsigned int*>(&s_res);
+		unsigned int* dst = reinterpret_cast<unsigned int*>(out + hyp);
+		for (int i = tid; i < nwords; i += PERS_THREADS) dst[i] = src[i];
+	}
+}
+
+// ---- host side ------------------------------------------------------------------------------------
+static void fill_levels(dso_b200_ctx* ctx, TrackerSlot& T, const FrameSlot* fs, float new_exposure, TrackLevels& TL)
+{
+	memset(&TL, 0, sizeof(TL));
+	TL.levels = T.levels;
+	for (int l = 0; l < T.levels; l++)
+	{
+		TL.w[l] = T.w[l]; TL.h[l] = T.h[l];
+		TL.fx[l] = T.fx[l]; TL.fy[l] = T.fy[l]; TL.cx[l] = T.cx[l]; TL.cy[l] = T.cy[l];
+		memcpy(TL.Ki[l], T.Ki[l], 36);
+		TL.pc[l] = T.pc[l]; TL.pc_n[l] = T.pc_n[l];
+		TL.img[l] = fs ? fs->pyr[l] : nullptr;
+	}
+	TL.ref_a = T.ref_a; TL.ref_b = T.ref_b; TL.ref_exposure = T.ref_exposure; TL.new_exposure = new_exposure;
+}
+
+// Eigen's compute_inverse<Matrix3f> (cofactors of column 0, determinant by expansion along it), as used by
+// CoarseTracker::makeK (CoarseTracker.cpp:125)
+static float cof33(const float* m, int i, int j)
+{
+	int i1 = (i + 1) % 3, i2 = (i + 2) % 3, j1 = (j + 1) % 3, j2 = (j + 2) % 3;
+	volatile float a = m[i1 * 3 + j1] * m[i2 * 3 + j2];
+	volatile float b = m[i1 * 3 + j2] * m[i2 * 3 + j1];
+	return a - b;
+}
+static void mat33f_inverse(const float* m, float* out)
+{
+	float c0 = cof33(m, 0, 0), c1 = cof33(m, 1, 0), c2 = cof33(m, 2, 0);
+	float det = dot3h(c0, m[0], c1, m[3], c2, m[6]);
+	float invdet = 1.0f / det;
+	out[0] = c0 * invdet; out[1] = c1 * invdet; out[2] = c2 * invdet;
+	out[3] = cof33(m, 0, 1) * invdet; out[4] = cof33(m, 1, 1) * invdet; out[5] = cof33(m, 2, 1) * invdet;
+	out[6] = cof33(m, 0, 2) * invdet; out[7] = cof33(m, 1, 2) * invdet; out[8] = cof33(m, 2, 2) * invdet;
+}
+
+extern "C" void dso_b200_track_opts_default(dso_b200_track_opts* o)
+{
+	o->huberTH = 9; o->coarseCutoffTH = 20; o->affineOptModeA = 1e12f; o->affineOptModeB = 1e8f;
+	const int mi[5] = { 10, 20, 50, 50, 50 };
+	for (int i = 0; i < 5; i++) o->maxIterations[i] = mi[i];
+}
+
+extern "C" int dso_b200_tracker_set_ref(dso_b200_ctx* ctx, int trk, int w, int h, int levels,
+                                        float fx, float fy, float cx, float cy,
+                                        const int* pc_n, const float* const* pc_u, const float* const* pc_v,
+                                        const float* const* pc_idepth, const float* const* pc_color,
+                                        double ref_aff_a, double ref_aff_b, float ref_ab_exposure)
+{
+	ARG_CHECK(ctx && (trk == 0 || trk == 1), "bad tracker slot");
+	ARG_CHECK(levels >= 1 && levels <= MAXL && w <= ctx->max_w && h <= ctx->max_h, "bad size / levels");
+	CK(cudaSetDevice(ctx->device));
+	TrackerSlot& T = ctx->trk[trk];
+	// makeK, CoarseTracker.cpp:102-131
+	T.levels = levels;
+	T.w[0] = w; T.h[0] = h; T.fx[0] = fx; T.fy[0] = fy; T.cx[0] = cx; T.cy[0] = cy;
+	for (int l = 1; l < levels; l++)
+	{
+		T.w[l] = w >> l; T.h[l] = h >> l;
+		T.fx[l] = T.fx[l - 1] * 0.5;
+		T.fy[l] = T.fy[l - 1] * 0.5;
+		T.cx[l] = (T.cx[0] + 0.5) / ((int)1 << l) - 0.5;
+		T.cy[l] = (T.cy[0] + 0.5) / ((int)1 << l) - 0.5;
+	}
+	for (int l = 0; l < levels; l++)
+	{
+		float K[9] = { T.fx[l], 0, T.cx[l], 0, T.fy[l], T.cy[l], 0, 0, 1 };
+		mat33f_inverse(K, T.Ki[l]);
+	}
+	// clouds: SoA host arrays -> one float4 per point, packed on the host, one copy per level
+	std::vector<float4> tmp;
+	for (int l = 0; l < levels; l++)
+	{
+		int n = pc_n[l];
+		ARG_CHECK(n >= 0 && (size_t)n <= T.cap_points, "pc_n exceeds capacity");
+		T.pc_n[l] = n;
+		tmp.resize(n);
+		for (int i = 0; i < n; i++) tmp[i] = make_float4(pc_u[l][i], pc_v[l][i], pc_idepth[l][i], pc_color[l][i]);
+		if (n) CK(cudaMemcpyAsync(T.pc[l], tmp.data(), sizeof(float4) * n, cudaMemcpyHostToDevice, ctx->stream));
+		CK(cudaStreamSynchronize(ctx->stream));
+	}
+	T.ref_a = ref_aff_a; T.ref_b = ref_aff_b; T.ref_exposure = ref_ab_exposure;
+	T.valid = true; T.last_lvl = -1; T.last_warped_n = 0;
+	return 0;
+}
+
+static int check_eval_args(dso_b200_ctx* ctx, int trk, int frame_slot, int lvl)
+{
+	ARG_CHECK(ctx && (trk == 0 || trk == 1) && ctx->trk[trk].valid, "tracker reference not set");
+	ARG_CHECK(frame_slot >= 0 && frame_slot < ctx->n_slots && ctx->slots[frame_slot].valid, "frame slot empty");
+	const TrackerSlot& T = ctx->trk[trk];
+	const FrameSlot& F = ctx->slots[frame_slot];
+	ARG_CHECK(lvl >= 0 && lvl < T.levels && lvl < F.levels, "bad level");
+	ARG_CHECK(F.w == T.w[0] && F.h == T.h[0], "frame / tracker size mismatch");
+	return 0;
+}
+
+static int grid_for(const dso_b200_ctx* ctx, int n)
+{
+	int g = (n + EVAL_THREADS - 1) / EVAL_THREADS;
+	int cap = ctx->sm_count * 4;
+	if (g > cap) g = cap;
+	if (g < 1) g = 1;
+	return g;
+}
+
+static int run_eval(dso_b200_ctx* ctx, int trk, int frame_slot, int lvl, const Pose& pose, double a, double b,
+                    float new_exposure, float cutoffTH, float huberTH, bool debug, unsigned char* d_status, float* d_warped)
+{
+	TrackerSlot& T = ctx->trk[trk];
+	TrackLevels TL;
+	fill_levels(ctx, T, &ctx->slots[frame_slot], new_exposure, TL);
+	EvalParams P;
+	make_eval_params(TL, lvl, pose, a, b, cutoffTH, huberTH, P);
+	int g = grid_for(ctx, P.n);
+	if (debug)
+		track_eval_kernel<true><<<g, EVAL_THREADS, 0, ctx->stream>>>(P, T.pc[lvl], TL.img[lvl], T.d_partials, T.d_ticket, T.d_sums, d_status, d_warped);
+	else
+		track_eval_kernel<false><<<g, EVAL_THREADS, 0, ctx->stream>>>(P, T.pc[lvl], TL.img[lvl], T.d_partials, T.d_ticket, T.d_sums, nullptr, nullptr);
+	ctx->launches++;
+	CK(cudaGetLastError());
+	CK(cudaMemcpyAsync(T.h_sums, T.d_sums, sizeof(float) * S_COUNT, cudaMemcpyDeviceToHost, ctx->stream));
+	CK(cudaStreamSynchronize(ctx->stream));
+	T.last_lvl = lvl;
+	return 0;
+}
+
+extern "C" int dso_b200_calc_res(dso_b200_ctx* ctx, int trk, int frame_slot, int lvl, const double* refToNew12,
+                                 double aff_a, double aff_b, float new_ab_exposure, float cutoffTH, double* out6)
+{
+	int rc = check_eval_args(ctx, trk, frame_slot, lvl);
+	if (rc) return rc;
+	CK(cudaSetDevice(ctx->device));
+	Pose p; pose_from12(p, refToNew12);
+	rc = run_eval(ctx, trk, frame_slot, lvl, p, aff_a, aff_b, new_ab_exposure, cutoffTH, 9.0f, false, nullptr, nullptr);
+	if (rc) return rc;
+	EvalResult er;
+	sums_to_result(ctx->trk[trk].h_sums, er);
+	out6[0] = er.E; out6[1] = er.n; out6[2] = er.flowT; out6[3] = 0; out6[4] = er.flowRT; out6[5] = er.sat;
+	return 0;
+}
+
+extern "C" int dso_b200_calc_gs(dso_b200_ctx* ctx, int trk, double* H64, double* b8)
+{
+	ARG_CHECK(ctx && (trk == 0 || trk == 1) && ctx->trk[trk].valid && ctx->trk[trk].last_lvl >= 0, "no preceding calc_res");
+	EvalResult er;
+	sums_to_result(ctx->trk[trk].h_sums, er);
+	memcpy(H64, er.H, sizeof(er.H));
+	memcpy(b8, er.b, sizeof(er.b));
+	return 0;
+}
+
+extern "C" int dso_b200_calc_res_debug(dso_b200_ctx* ctx, int trk, int frame_slot, int lvl, const double* refToNew12,
+                                       double aff_a, double aff_b, float new_ab_exposure, float cutoffTH,
+                                       unsigned char* status_out, float* warped8_out)
+{
+	int rc = check_eval_args(ctx, trk, frame_slot, lvl);
+	if (rc) return rc;
+	CK(cudaSetDevice(ctx->device));
+	TrackerSlot& T = ctx->trk[trk];
+	int n = T.pc_n[lvl];
+	unsigned char* d_status = nullptr; float* d_warped = nullptr;
+	CK(cudaMalloc(&d_status, n + 16));
+	CK(cudaMalloc(&d_warped, sizeof(float) * 8 * (size_t)(n + 1)));
+	CK(cudaMemsetAsync(d_warped, 0, sizeof(float) * 8 * (size_t)(n + 1), ctx->stream));
+	Pose p; pose_from12(p, refToNew12);
+	rc = run_eval(ctx, trk, frame_slot, lvl, p, aff_a, aff_b, new_ab_exposure, cutoffTH, 9.0f, true, d_status, d_warped);
+	if (!rc)
+	{
+		cudaMemcpy(status_out, d_status, n, cudaMemcpyDeviceToHost);
+		cudaMemcpy(warped8_out, d_warped, sizeof(float) * 8 * (size_t)n, cudaMemcpyDeviceToHost);
+	}
+	cudaFree(d_status); cudaFree(d_warped);
+	return rc;
+}
+
+extern "C" int dso_b200_track_hostloop(dso_b200_ctx* ctx, int trk, int frame_slot, const double* pose12_init,
+                                       double aff_a_init, double aff_b_init, float new_ab_exposure, int coarsestLvl,
+                                       const double* minResForAbort5, const dso_b200_track_opts* opts,
+                                       dso_b200_track_result* out)
+{
+	int rc = check_eval_args(ctx, trk, frame_slot, coarsestLvl);
+	if (rc) return rc;
+	ARG_CHECK(coarsestLvl < 5, "coarsestLvl must be < 5 (CoarseTracker.cpp:561)");
+	CK(cudaSetDevice(ctx->device));
+	dso_b200_track_opts o;
+	if (opts) o = *opts; else dso_b200_track_opts_default(&o);
+	LM lm;
+	TrackLevels TL0;
+	fill_levels(ctx, ctx->trk[trk], &ctx->slots[frame_slot], new_ab_exposure, TL0);
+	lm.init(o, TL0, pose12_init, aff_a_init, aff_b_init, coarsestLvl, minResForAbort5, out);
+	while (!lm.done)
+	{
+		rc = run_eval(ctx, trk, frame_slot, lm.req_lvl, lm.req_pose, lm.req_a, lm.req_b, new_ab_exposure, lm.req_cutoff, o.huberTH, false, nullptr, nullptr);
+		if (rc) return rc;
+		EvalResult er;
+		sums_to_result(ctx->trk[trk].h_sums, er);
+		lm.step(er, ctx->trk[trk].pc_n[lm.req_lvl]);
+	}
+	return 0;
+}
+
+extern "C" int dso_b200_track_replay_abort(const dso_b200_track_result* r, const double* minRes, double* lastRes)
+{
+	double lr[5];
+	for (int i = 0; i < 5; i++) lr[i] = NAN;
+	int ok = 1;
+	for (int p = 0; p < r->n_passes; p++)
+	{
+		int l = r->pass_level[p];
+		lr[l] = r->pass_rmse[p];
+		if (lr[l] > 1.5 * minRes[l]) { ok = 0; break; }
+	}
+	if (ok) ok = r->ok;
+	if (lastRes) for (int i = 0; i < 5; i++) lastRes[i] = lr[i];
+	return ok;
+}
+
+extern "C" int dso_b200_track_batched(dso_b200_ctx* ctx, int trk, int frame_slot, int nHyp, const double* pose12_init,
+                                      double aff_a_init, double aff_b_init, float new_ab_exposure, int coarsestLvl,
+                                      const dso_b200_track_opts* opts, dso_b200_track_result* out)
+{
+	int rc = check_eval_args(ctx, trk, frame_slot, coarsestLvl);
+	if (rc) return rc;
+	ARG_CHECK(nHyp >= 1 && nHyp <= DSO_B200_MAX_HYP, "nHyp out of range");
+	ARG_CHECK(coarsestLvl < 5, "coarsestLvl must be < 5 (CoarseTracker.cpp:561)");
+	CK(cudaSetDevice(ctx->device));
+	TrackerSlot& T = ctx->trk[trk];
+	dso_b200_track_opts o;
+	if (opts) o = *opts; else dso_b200_track_opts_default(&o);
+	TrackIn* hin = (TrackIn*)T.h_track_in;
+	for (int i = 0; i < nHyp; i++)
+	{
+		memcpy(hin[i].pose, pose12_init + 12 * i, 96);
+		hin[i].aff_a = aff_a_init; hin[i].aff_b = aff_b_init;
+		for (int k = 0; k < 5; k++) hin[i].minRes[k] = NAN;
+	}
+	CK(cudaMemcpyAsync(T.d_track_in, hin, sizeof(TrackIn) * nHyp, cudaMemcpyHostToDevice, ctx->stream));
+	TrackLevels TL;
+	fill_levels(ctx, T, &ctx->slots[frame_slot], new_ab_exposure, TL);
+
+	// cluster size: as many CTAs per hypothesis as fit on the device, power of two, <= 8 (portable)
+	int cs = 8;
+	while (cs > 1 && nHyp * cs > ctx->sm_count) cs >>= 1;
+	int max_n = 0;
+	for (int l = 0; l <= coarsestLvl; l++) max_n = T.pc_n[l] > max_n ? T.pc_n[l] : max_n;
+	int per = (max_n + cs - 1) / cs;
+	size_t smem_cap_bytes = 160 * 1024;
+	int cap = (int)std::min<size_t>((size_t)per, smem_cap_bytes / sizeof(float4));
+	size_t dyn = (size_t)cap * sizeof(float4);
+	static bool attr_set = false;
+	if (!attr_set)
+	{
+		CK(cudaFuncSetAttribute(track_persistent_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_cap_bytes));
+		attr_set = true;
+	}
+	cudaLaunchConfig_t cfg;
+	memset(&cfg, 0, sizeof(cfg));
+	cfg.gridDim = dim3(nHyp * cs, 1, 1);
+	cfg.blockDim = dim3(PERS_THREADS, 1, 1);
+	cfg.dynamicSmemBytes = dyn;
+	cfg.stream = ctx->stream;
+	cudaLaunchAttribute at[1];
+	at[0].id = cudaLaunchAttributeClusterDimension;
+	at[0].val.clusterDim.x = cs; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+	cfg.attrs = at; cfg.numAttrs = 1;
+	CK(cudaLaunchKernelEx(&cfg, track_persistent_kernel, TL, o, (const TrackIn*)T.d_track_in,
+	                      (dso_b200_track_result*)T.d_track_out, coarsestLvl, cap));
+	ctx->launches++;
+	CK(cudaMemcpyAsync(T.h_track_out, T.d_track_out, sizeof(dso_b200_track_result) * nHyp, cudaMemcpyDeviceToHost, ctx->stream));
+	CK(cudaStreamSynchronize(ctx->stream));
+	memcpy(out, T.h_track_out, sizeof(dso_b200_track_result) * nHyp);
+	return 0;
+}

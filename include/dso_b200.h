@@ -1,0 +1,200 @@
+/* dso_b200 -- C ABI of the B200 (sm_100a) implementation of DSO's photometric Gauss-Newton hot path.
+ *
+ * The reference (akawincent/DSO-noted-in-chinese) has no FFI layer: the drop-in boundary is the C++
+ * member-function surface listed below.  Every entry point here replaces one of those members and
+ * cites it (paths relative to the reference tree).  The C++ classes in
+ * dso-noted-in-chinese_b200/host/ keep the reference signatures and forward to these calls.
+ *
+ * Conventions
+ *   - every function returns 0 on success, <0 on error (DSO_B200_E_*); dso_b200_last_error() gives the
+ *     message for the calling thread.  There is no CPU fallback: without a CUDA device every compute
+ *     call fails with DSO_B200_E_CUDA.
+ *   - matrices are row-major; poses are 12 doubles: R (3x3 row-major) followed by t.
+ *   - "host" pointers are ordinary (ideally pinned, see dso_b200_host_alloc) CPU memory; "dev"
+ *     pointers are CUDA device memory owned by the caller.
+ *   - all work of a context is issued on the context's stream; calls that return data to host
+ *     memory synchronise that stream before returning, *_async/_dev variants do not.
+ */
+#ifndef DSO_B200_H
+#define DSO_B200_H
+#include <stddef.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DSO_B200_MAX_LEVELS 6      /* PYR_LEVELS, util/settings.h:50 */
+#define DSO_B200_MAX_FRAMES 8      /* window size at optimise time, FullSystem.cpp:1102-1152 */
+#define DSO_B200_MAX_HYP 32        /* FullSystem.cpp:311-354 builds 31 pose priors */
+#define DSO_B200_MAX_PASSES 8      /* level passes of one trackNewestCoarse (levels + one repeat) */
+
+#define DSO_B200_E_ARG (-1)
+#define DSO_B200_E_CUDA (-2)
+#define DSO_B200_E_STATE (-3)
+#define DSO_B200_E_LIMIT (-4)
+
+typedef struct dso_b200_ctx dso_b200_ctx;
+
+/* ---- context ----------------------------------------------------------------------------------- */
+/* One context per FullSystem (FullSystem/FullSystem.h:141): owns the stream, n_frame_slots device
+ * pyramids of at most max_w x max_h, two tracker slots (coarseTracker / coarseTracker_forNewKF,
+ * FullSystem.h:286-287) and one BA workspace. */
+int dso_b200_create(int device, int max_w, int max_h, int n_frame_slots, dso_b200_ctx** out);
+void dso_b200_destroy(dso_b200_ctx* ctx);
+const char* dso_b200_last_error(void);
+/* cudaStream_t of the context (so callers can order their own work / record events on it). */
+void* dso_b200_stream(dso_b200_ctx* ctx);
+int dso_b200_sync(dso_b200_ctx* ctx);
+/* pinned host memory for image / result buffers (cudaHostAlloc / cudaFreeHost) */
+void* dso_b200_host_alloc(size_t bytes);
+void dso_b200_host_free(void* p);
+/* number of kernels this library has launched on this context since creation */
+long long dso_b200_launch_count(dso_b200_ctx* ctx);
+
+/* ---- K1: FrameHessian::makeImages (FullSystem/HessianBlocks.cpp:137-211, decl HessianBlocks.h:282) */
+/* color: w*h irradiance floats (ImageAndExposure::image).  B_lut: 256 floats (CalibHessian::B,
+ * HessianBlocks.h:399) or NULL (= the "HCalib==0 / setting_gammaWeightsPixelSelect!=1" branch).
+ * dIp_out[l]: 3*w_l*h_l floats in the reference's Eigen::Vector3f AoS layout, absgrad_out[l]: w_l*h_l
+ * floats; either array (or single entries) may be NULL to skip the device->host copy.  The device
+ * pyramid stays resident in frame_slot for the tracker and BA.  Rows 0 and h_l-1 of dx, dy and
+ * absSquaredGrad, which the reference leaves uninitialised, are written as 0. */
+int dso_b200_make_images(dso_b200_ctx* ctx, int frame_slot, const float* color_host, int w, int h, int levels,
+                         const float* B_lut, float* const* dIp_out, float* const* absgrad_out);
+/* same, input already in device memory, nothing copied back, no synchronisation */
+int dso_b200_make_images_dev(dso_b200_ctx* ctx, int frame_slot, const float* color_dev, int w, int h, int levels,
+                             const float* B_lut_host);
+
+/* ---- K2: CoarseTracker (FullSystem/CoarseTracker.{h,cpp}) ---------------------------------------- */
+/* CoarseTracker::makeK (CoarseTracker.cpp:102-131) + the result of setCoarseTrackingRef /
+ * makeCoarseDepthL0 (:135-292, :523-537): per-level clouds pc_u/pc_v/pc_idepth/pc_color with pc_n,
+ * level-0 intrinsics, and the reference frame's affine parameters and exposure. trk is 0 or 1. */
+int dso_b200_tracker_set_ref(dso_b200_ctx* ctx, int trk, int w, int h, int levels,
+                             float fx, float fy, float cx, float cy,
+                             const int* pc_n, const float* const* pc_u, const float* const* pc_v,
+                             const float* const* pc_idepth, const float* const* pc_color,
+                             double ref_aff_a, double ref_aff_b, float ref_ab_exposure);
+
+/* CoarseTracker::calcRes (CoarseTracker.cpp:359-520, decl CoarseTracker.h:100), fused with the
+ * accumulation of calcGSSSE so that no warped buffers are materialised.
+ * out6 = [E, numTermsInE, flowT, 0, flowRT, saturatedRatio] as the reference's Vec6. */
+int dso_b200_calc_res(dso_b200_ctx* ctx, int trk, int frame_slot, int lvl, const double* refToNew12,
+                      double aff_a, double aff_b, float new_ab_exposure, float cutoffTH, double* out6);
+/* CoarseTracker::calcGSSSE (CoarseTracker.cpp:296-354, decl CoarseTracker.h:101): H (8x8) and b of
+ * the points kept by the last dso_b200_calc_res on this tracker slot, with the 1/n and SCALE_*
+ * factors applied exactly as :338-353 (n = padded buf_warped_n). */
+int dso_b200_calc_gs(dso_b200_ctx* ctx, int trk, double* H64, double* b8);
+/* Debug / parity: per reference point of level lvl of the last calc_res, in cloud order:
+ * status (0 skipped, 1 saturated, 2 kept) and the 8 values the reference appends to buf_warped_*
+ * (idepth,u,v,dx,dy,residual,weight,refColor; CoarseTracker.cpp:476-483).  Re-runs the evaluation. */
+int dso_b200_calc_res_debug(dso_b200_ctx* ctx, int trk, int frame_slot, int lvl, const double* refToNew12,
+                            double aff_a, double aff_b, float new_ab_exposure, float cutoffTH,
+                            unsigned char* status_out, float* warped8_out);
+
+typedef struct
+{
+	float huberTH;            /* setting_huberTH = 9 (util/settings.cpp:138) */
+	float coarseCutoffTH;     /* setting_coarseCutoffTH = 20 (:146) */
+	float affineOptModeA;     /* setting_affineOptModeA = 1e12 (:124) */
+	float affineOptModeB;     /* setting_affineOptModeB = 1e8 (:125) */
+	int maxIterations[5];     /* {10,20,50,50,50}, CoarseTracker.cpp:569 */
+} dso_b200_track_opts;
+void dso_b200_track_opts_default(dso_b200_track_opts* o);
+
+typedef struct
+{
+	int ok;                          /* what trackNewestCoarse returns when minResForAbort is all-NaN */
+	int reserved;
+	double pose[12];                 /* lastToNew_out */
+	double aff_a, aff_b;             /* aff_g2l_out */
+	double lastResiduals[5];         /* CoarseTracker::lastResiduals (NaN where a level was not run) */
+	double lastFlowIndicators[3];    /* CoarseTracker::lastFlowIndicators */
+	int n_passes;                    /* level passes executed; the RMSE after each pass lets the caller */
+	int pass_level[DSO_B200_MAX_PASSES];   /* replay the abort test of CoarseTracker.cpp:713 for any */
+	double pass_rmse[DSO_B200_MAX_PASSES]; /* minResForAbort (FullSystem.cpp:380-442) */
+	int n_iterations;
+	int n_evals;
+	int trace_len;
+	unsigned char trace[256];        /* accept(1) / reject(0) per LM iteration */
+	double point_evals;
+} dso_b200_track_result;
+
+/* CoarseTracker::trackNewestCoarse (CoarseTracker.cpp:551-747, decl CoarseTracker.h:51-55) for nHyp
+ * initial poses at once (the priors of FullSystem::trackNewCoarse, FullSystem.cpp:311-354): the whole
+ * coarse-to-fine LM loop runs inside one persistent kernel, one thread-block cluster per hypothesis.
+ * Every hypothesis is run to completion with no abort; use dso_b200_track_replay_abort for the
+ * reference's sequential early-out semantics. */
+int dso_b200_track_batched(dso_b200_ctx* ctx, int trk, int frame_slot, int nHyp, const double* pose12_init,
+                           double aff_a_init, double aff_b_init, float new_ab_exposure, int coarsestLvl,
+                           const dso_b200_track_opts* opts, dso_b200_track_result* out);
+/* Applies CoarseTracker.cpp:713 to a finished result: returns 1 if trackNewestCoarse would have
+ * returned true for this minResForAbort, 0 if it would have aborted (lastResiduals5_out then holds
+ * what CoarseTracker::lastResiduals would contain at the abort). */
+int dso_b200_track_replay_abort(const dso_b200_track_result* r, const double* minResForAbort5,
+                                double* lastResiduals5_out);
+/* Same LM loop driven from the host with one dso_b200_calc_res/calc_gs pair per evaluation
+ * (validation path for the private-method drop-ins; one hypothesis, honours minResForAbort). */
+int dso_b200_track_hostloop(dso_b200_ctx* ctx, int trk, int frame_slot, const double* pose12_init,
+                            double aff_a_init, double aff_b_init, float new_ab_exposure, int coarsestLvl,
+                            const double* minResForAbort5, const dso_b200_track_opts* opts,
+                            dso_b200_track_result* out);
+
+/* ---- K3-K5: windowed BA --------------------------------------------------------------------------- */
+/* FrameFramePrecalc (HessianBlocks.h:73-103) fields read by PointFrameResidual::linearize. */
+typedef struct
+{
+	float PRE_RTll_0[9];
+	float PRE_tTll_0[3];
+	float PRE_KRKiTll[9];
+	float PRE_KtTll[3];
+	float PRE_aff_mode[2];
+	float PRE_b0_mode;
+	float pad;
+} dso_b200_precalc;
+
+/* Window description: nF frames whose level-0 images live in frame_slots[i] (target->dI), calibration
+ * CalibHessian::fxl..cyl (HessianBlocks.h:361-368), per-frame frameEnergyTH (HessianBlocks.h:136). */
+int dso_b200_ba_set_window(dso_b200_ctx* ctx, int nF, const int* frame_slots, int w, int h,
+                           float fx, float fy, float cx, float cy, const float* frameEnergyTH);
+/* Per-iteration glue computed on the host exactly as the reference does (FrameFramePrecalc::set,
+ * HessianBlocks.cpp:213-250; EnergyFunctional::setAdjointsF / setDeltaF, EnergyFunctional.cpp:47-114,
+ * 178-205).  precalc[h*nF+t]; adHost/adTarget[(h+t*nF)*64] doubles; adHTdeltaF[(h+t*nF)*8]; cDeltaF[4]. */
+int dso_b200_ba_set_glue(dso_b200_ctx* ctx, const dso_b200_precalc* precalc, const double* adHost,
+                         const double* adTarget, const float* adHTdeltaF, const float* cDeltaF4);
+/* PointHessian fields (HessianBlocks.h:431-444) + EFPoint::priorF/deltaF (EnergyFunctionalStructs.h:111-112);
+ * points must be grouped by host frame in EnergyFunctional::allPoints order. */
+int dso_b200_ba_set_points(dso_b200_ctx* ctx, int nP, const float* u, const float* v, const float* idepth_scaled,
+                           const float* idepth_zero_scaled, const float* color8, const float* weights8,
+                           const int* host, const float* priorF, const float* deltaF);
+/* PointFrameResidual graph (Residuals.h:56-112) in EFPoint::residualsAll order: point, target,
+ * state_state (0 IN, 1 OOB, 2 OUTLIER), state_energy, EFResidual::isLinearized / isActive. */
+int dso_b200_ba_set_residuals(dso_b200_ctx* ctx, int nR, const int* point, const int* target, const int* state_state,
+                              const double* state_energy, const unsigned char* isLinearized,
+                              const unsigned char* isActive);
+/* PointFrameResidual::linearize (FullSystem/Residuals.cpp:78-291) over all residuals =
+ * FullSystem::linearizeAll_Reductor (FullSystemOptimize.cpp:52-60).  Outputs (each may be NULL):
+ * state_NewState, state_NewEnergy, state_NewEnergyWithOutlier, centerProjectedTo (nR*3),
+ * projectedTo (nR*16), RawResidualJacobian (nR*74 floats: resF8 Jpdxi0(6) Jpdxi1(6) Jpdc0(4) Jpdc1(4)
+ * Jpdd(2) JIdx0(8) JIdx1(8) JabF0(8) JabF1(8) JIdx2(4) JabJIdx(4) Jab2(4)), and the energy sum. */
+int dso_b200_ba_linearize(dso_b200_ctx* ctx, int* newState, float* newEnergy, float* newEnergyWithOutlier,
+                          float* centerProjectedTo3, float* projectedTo16, float* J74, double* energy_sum);
+/* PointFrameResidual::applyRes(true) for all residuals (Residuals.cpp:323-347) including
+ * EFResidual::takeDataF (EnergyFunctionalStructs.cpp:39-49).  Outputs may be NULL. */
+int dso_b200_ba_apply_res(dso_b200_ctx* ctx, unsigned char* isActive_out, float* JpJdF8_out);
+/* EnergyFunctional::accumulateAF_MT (OptimizationBackend/EnergyFunctional.cpp:209-232):
+ * AccumulatedTopHessianSSE::addPoint<0> (AccumulatedTopHessian.cpp:39-177) + stitchDoubleMT
+ * (AccumulatedTopHessian.h:91-139).  H: (8nF+4)^2 doubles, b: 8nF+4.  Per-point outputs may be NULL. */
+int dso_b200_ba_accumulate_A(dso_b200_ctx* ctx, double* H, double* b, int* resInA,
+                             float* Hdd_accAF, float* bd_accAF, float* Hcd_accAF4);
+/* EnergyFunctional::accumulateSCF_MT (EnergyFunctional.cpp:257-274): AccumulatedSCHessianSSE::addPoint
+ * (AccumulatedSCHessian.cpp:35-85) + stitchDoubleMT (AccumulatedSCHessian.h:93-135). */
+int dso_b200_ba_accumulate_SC(dso_b200_ctx* ctx, double* H_sc, double* b_sc,
+                              float* HdiF, float* bdSumF, float* idepth_hessian);
+/* linearize -> applyRes(true) -> accumulateAF -> accumulateSCF back to back with a single
+ * synchronisation; H_A/b_A/H_sc/b_sc as above (one GN iteration's worth of FullSystem::optimize,
+ * FullSystemOptimize.cpp:455-486 + EnergyFunctional.cpp:816-820). */
+int dso_b200_ba_step(dso_b200_ctx* ctx, double* H_A, double* b_A, double* H_sc, double* b_sc,
+                     double* energy_sum, int* resInA);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

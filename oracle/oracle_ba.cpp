@@ -1,0 +1,1040 @@
+// TEST INFRASTRUCTURE ONLY -- CPU oracle (see dso_oracle.h). PARITY UNPINNED (no reference fixtures exist).
+// Restates the windowed-BA part of the hot path: FrameFramePrecalc::set, setAdjointsF/setDeltaF,
+// PointFrameResidual::linearize, applyRes/takeDataF, AccumulatedTopHessianSSE::addPoint<0> + stitch,
+// AccumulatedSCHessianSSE::addPoint + stitch, with the reference's three-tier float accumulators.
+// Compile with -ffp-contract=off.
+#include "dso_oracle.h"
+#include "oracle_math.h"
+#include <vector>
+#include <thread>
+#include <mutex>
+#include <condition_variable>
+#include <atomic>
+#include <functional>
+#include <cstdio>
+
+using namespace orc;
+
+#define CPARS 4
+#define patternNum 8
+// settings.cpp:274 (pattern 8) / settings.h:215-218
+static const int patternP[8][2] = { {0,-2}, {-1,-1}, {1,-1}, {-2,0}, {0,0}, {2,0}, {-1,1}, {0,2} };
+// HessianBlocks.h:54-61
+#define SCALE_IDEPTH 1.0f
+#define SCALE_XI_ROT 1.0f
+#define SCALE_XI_TRANS 0.5f
+#define SCALE_F 50.0f
+#define SCALE_C 50.0f
+#define SCALE_A 10.0f
+#define SCALE_B 1000.0f
+// settings.cpp:103,110,124-125
+static const float setting_outlierTHSumComponent = 50 * 50;
+static const float setting_huberTH = 9;
+static const float setting_affineOptModeA = 1e12f;
+static const float setting_affineOptModeB = 1e8f;
+
+enum { ST_IN = 0, ST_OOB = 1, ST_OUTLIER = 2 };
+
+// RawResidualJacobian, RawResidualJacobian.h:40-79, flattened to 74 floats
+struct RawJ
+{
+	float resF[8];
+	float Jpdxi[2][6];
+	float Jpdc[2][4];
+	float Jpdd[2];
+	float JIdx[2][8];
+	float JabF[2][8];
+	float JIdx2[4];   // row-major 2x2
+	float JabJIdx[4];
+	float Jab2[4];
+};
+static_assert(sizeof(RawJ) == 74 * 4, "RawJ must be 74 packed floats");
+
+// ---- accumulators ----------------------------------------------------------------------------
+// AccumulatorApprox, MatrixAccumulators.h:579-956
+struct AccApprox
+{
+	float Data[60], Data1k[60], Data1m[60];
+	float TR[32], TR1k[32], TR1m[32];
+	float BR[8], BR1k[8], BR1m[8];
+	float numIn1, numIn1k, numIn1m;
+	size_t num;
+	float H[13][13];
+	void initialize()
+	{
+		memset(Data, 0, sizeof(Data)); memset(Data1k, 0, sizeof(Data1k)); memset(Data1m, 0, sizeof(Data1m));
+		memset(TR, 0, sizeof(TR)); memset(TR1k, 0, sizeof(TR1k)); memset(TR1m, 0, sizeof(TR1m));
+		memset(BR, 0, sizeof(BR)); memset(BR1k, 0, sizeof(BR1k)); memset(BR1m, 0, sizeof(BR1m));
+		num = 0; numIn1 = numIn1k = numIn1m = 0;
+	}
+	void shiftUp(bool force)
+	{
+		if (numIn1 > 1000 || force)
+		{
+			for (int i = 0; i < 60; i++) Data1k[i] = Data[i] + Data1k[i];
+			for (int i = 0; i < 32; i++) TR1k[i] = TR[i] + TR1k[i];
+			for (int i = 0; i < 8; i++) BR1k[i] = BR[i] + BR1k[i];
+			numIn1k += numIn1; numIn1 = 0;
+			memset(Data, 0, sizeof(Data)); memset(TR, 0, sizeof(TR)); memset(BR, 0, sizeof(BR));
+		}
+		if (numIn1k > 1000 || force)
+		{
+			for (int i = 0; i < 60; i++) Data1m[i] = Data1k[i] + Data1m[i];
+			for (int i = 0; i < 32; i++) TR1m[i] = TR1k[i] + TR1m[i];
+			for (int i = 0; i < 8; i++) BR1m[i] = BR1k[i] + BR1m[i];
+			numIn1m += numIn1k; numIn1k = 0;
+			memset(Data1k, 0, sizeof(Data1k)); memset(TR1k, 0, sizeof(TR1k)); memset(BR1k, 0, sizeof(BR1k));
+		}
+	}
+	// update(x4,x6,y4,y6,a,b,c), :738-842
+	void update(const float* x4, const float* x6, const float* y4, const float* y6, float a, float b, float c)
+	{
+		float x[10], y[10];
+		for (int i = 0; i < 4; i++) { x[i] = x4[i]; y[i] = y4[i]; }
+		for (int i = 0; i < 6; i++) { x[4 + i] = x6[i]; y[4 + i] = y6[i]; }
+		int idx = 0;
+		for (int r = 0; r < 10; r++)
+			for (int cc = r; cc < 10; cc++)
+			{
+				Data[idx] += a * x[cc] * x[r] + c * y[cc] * y[r] + b * (x[cc] * y[r] + y[cc] * x[r]);
+				idx++;
+			}
+		num++; numIn1++;
+		shiftUp(false);
+	}
+	// updateTopRight, :845-897
+	void updateTopRight(const float* x4, const float* x6, const float* y4, const float* y6,
+	                    float TR00, float TR10, float TR01, float TR11, float TR02, float TR12)
+	{
+		for (int i = 0; i < 10; i++)
+		{
+			float xi = i < 4 ? x4[i] : x6[i - 4];
+			float yi = i < 4 ? y4[i] : y6[i - 4];
+			TR[3 * i + 0] += xi * TR00 + yi * TR10;
+			TR[3 * i + 1] += xi * TR01 + yi * TR11;
+			TR[3 * i + 2] += xi * TR02 + yi * TR12;
+		}
+	}
+	// updateBotRight, :899-913
+	void updateBotRight(float a00, float a01, float a02, float a11, float a12, float a22)
+	{
+		BR[0] += a00; BR[1] += a01; BR[2] += a02; BR[3] += a11; BR[4] += a12; BR[5] += a22;
+	}
+	// finish, :605-640
+	void finish()
+	{
+		memset(H, 0, sizeof(H));
+		shiftUp(true);
+		int idx = 0;
+		for (int r = 0; r < 10; r++) for (int c = r; c < 10; c++) { H[r][c] = H[c][r] = Data1m[idx]; idx++; }
+		idx = 0;
+		for (int r = 0; r < 10; r++) for (int c = 0; c < 3; c++) { H[r][c + 10] = H[c + 10][r] = TR1m[idx]; idx++; }
+		H[10][10] = BR1m[0];
+		H[10][11] = H[11][10] = BR1m[1];
+		H[10][12] = H[12][10] = BR1m[2];
+		H[11][11] = BR1m[3];
+		H[11][12] = H[12][11] = BR1m[4];
+		H[12][12] = BR1m[5];
+		num = numIn1 + numIn1k + numIn1m;
+	}
+};
+
+// AccumulatorXX<i,j> / AccumulatorX<i>, MatrixAccumulators.h:34-87, 172-232
+template <int I, int Jn>
+struct AccXX
+{
+	float A[I][Jn], A1k[I][Jn], A1m[I][Jn];
+	float numIn1, numIn1k, numIn1m;
+	size_t num;
+	void initialize() { memset(A, 0, sizeof(A)); memset(A1k, 0, sizeof(A1k)); memset(A1m, 0, sizeof(A1m)); num = 0; numIn1 = numIn1k = numIn1m = 0; }
+	void shiftUp(bool force)
+	{
+		if (numIn1 > 1000 || force)
+		{
+			for (int i = 0; i < I; i++) for (int j = 0; j < Jn; j++) { A1k[i][j] += A[i][j]; A[i][j] = 0; }
+			numIn1k += numIn1; numIn1 = 0;
+		}
+		if (numIn1k > 1000 || force)
+		{
+			for (int i = 0; i < I; i++) for (int j = 0; j < Jn; j++) { A1m[i][j] += A1k[i][j]; A1k[i][j] = 0; }
+			numIn1m += numIn1k; numIn1k = 0;
+		}
+	}
+	void finish() { shiftUp(true); num = numIn1 + numIn1k + numIn1m; }
+	// A += w*L*R^T : outer product of the evaluated (w*L) with R
+	void update(const float* L, const float* R, float w)
+	{
+		float wL[I];
+		for (int i = 0; i < I; i++) wL[i] = w * L[i];
+		for (int j = 0; j < Jn; j++) for (int i = 0; i < I; i++) A[i][j] += R[j] * wL[i];
+		numIn1++;
+		shiftUp(false);
+	}
+};
+template <int I>
+struct AccX
+{
+	float A[I], A1k[I], A1m[I];
+	float numIn1, numIn1k, numIn1m;
+	size_t num;
+	void initialize() { memset(A, 0, sizeof(A)); memset(A1k, 0, sizeof(A1k)); memset(A1m, 0, sizeof(A1m)); num = 0; numIn1 = numIn1k = numIn1m = 0; }
+	void shiftUp(bool force)
+	{
+		if (numIn1 > 1000 || force) { for (int i = 0; i < I; i++) { A1k[i] += A[i]; A[i] = 0; } numIn1k += numIn1; numIn1 = 0; }
+		if (numIn1k > 1000 || force) { for (int i = 0; i < I; i++) { A1m[i] += A1k[i]; A1k[i] = 0; } numIn1m += numIn1k; numIn1k = 0; }
+	}
+	void finish() { shiftUp(true); num = numIn1 + numIn1k + numIn1m; }
+	void update(const float* L, float w) { for (int i = 0; i < I; i++) A[i] += w * L[i]; numIn1++; shiftUp(false); }
+};
+
+// ---- a small persistent worker pool standing in for IndexThreadReduce (util/IndexThreadReduce.h) ----
+// Workers take chunks of `step` indices from [first,end) until the range is exhausted.
+class Pool
+{
+public:
+	explicit Pool(int n) : nthreads(n), stop(false), generation(0), pending(0)
+	{
+		for (int i = 0; i < n; i++) workers.emplace_back([this, i] { loop(i); });
+	}
+	~Pool()
+	{
+		{ std::unique_lock<std::mutex> lk(m); stop = true; generation++; }
+		cv.notify_all();
+		for (auto& t : workers) t.join();
+	}
+	void reduce(const std::function<void(int, int, int)>& fn, int first, int end, int step)
+	{
+		if (step == 0) step = (end - first + nthreads - 1) / nthreads;
+		if (step <= 0) step = 1;
+		{
+			std::unique_lock<std::mutex> lk(m);
+			job = fn; next = first; jend = end; jstep = step; pending = nthreads; generation++;
+		}
+		cv.notify_all();
+		std::unique_lock<std::mutex> lk(m);
+		done.wait(lk, [this] { return pending == 0; });
+	}
+	int nthreads;
+private:
+	void loop(int tid)
+	{
+		unsigned long seen = 0;
+		while (true)
+		{
+			{
+				std::unique_lock<std::mutex> lk(m);
+				cv.wait(lk, [&] { return generation != seen; });
+				seen = generation;
+				if (stop) return;
+			}
+			while (true)
+			{
+				int lo;
+				{
+					std::unique_lock<std::mutex> lk(m);   // the reference also hands out chunks under a mutex
+					lo = next; next += jstep;
+				}
+				if (lo >= jend) break;
+				job(lo, std::min(lo + jstep, jend), tid);
+			}
+			{
+				std::unique_lock<std::mutex> lk(m);
+				if (--pending == 0) done.notify_all();
+			}
+		}
+	}
+	std::vector<std::thread> workers;
+	std::mutex m;
+	std::condition_variable cv, done;
+	bool stop;
+	unsigned long generation;
+	int pending;
+	std::function<void(int, int, int)> job;
+	int next, jend, jstep;
+};
+
+// ---- state -------------------------------------------------------------------------------------
+struct Frame
+{
+	SE3d evalPT, PRE_worldToCam, PRE_camToWorld;
+	double state[10], state_zero[10], state_scaled[10];
+	float ab_exposure, frameEnergyTH;
+	const float* dI;
+};
+struct Precalc
+{
+	float RTll[9], tTll[3], RTll_0[9], tTll_0[3], KRKiTll[9], RKiTll[9], KtTll[3], aff_mode[2], b0_mode, distanceLL;
+};
+struct Pt
+{
+	float u, v, idepth_scaled, idepth_zero_scaled, color[8], weights[8];
+	int host;
+	float priorF, deltaF;
+	std::vector<int> residualsAll;
+	float Hdd_accAF, bd_accAF, Hcd_accAF[4];
+	float Hdd_accLF, bd_accLF, Hcd_accLF[4];
+	float HdiF, bdSumF, idepth_hessian;
+};
+struct Res
+{
+	int point, host, target;
+	int state_state, state_NewState;
+	double state_energy, state_NewEnergy, state_NewEnergyWithOutlier;
+	RawJ J;      // PointFrameResidual::J
+	RawJ efJ;    // EFResidual::J
+	bool isLinearized, isActive;
+	float JpJdF[8];
+	float res_toZeroF[8];
+	float centerProjectedTo[3];
+	float projectedTo[8][2];
+};
+
+struct dso_oracle_ba
+{
+	int w, h, nF;
+	float fxl, fyl, cxl, cyl, fxli, fyli, cxli, cyli;   // CalibHessian::value_scaledf / value_scaledi
+	float wM3G, hM3G;
+	double calibDelta[4];
+	std::vector<Frame> frames;
+	std::vector<Precalc> pre;                // [h*nF+t]
+	std::vector<double> adHost, adTarget;    // [ (h+t*nF)*64 ]
+	std::vector<float> adHostF, adTargetF, adHTdeltaF;
+	float cDeltaF[4];
+	std::vector<Pt> points;
+	std::vector<Res> res;
+	Pool* pool; int poolN;
+	dso_oracle_ba() : pool(0), poolN(0) {}
+	Pool* getPool(int n) { if (!pool || poolN != n) { delete pool; pool = new Pool(n); poolN = n; } return pool; }
+};
+
+extern "C" dso_oracle_ba* dso_oracle_ba_create(int w, int h, int nF, float fx, float fy, float cx, float cy)
+{
+	dso_oracle_ba* B = new dso_oracle_ba();
+	B->w = w; B->h = h; B->nF = nF;
+	// CalibHessian::setValueScaled, HessianBlocks.h:383-397
+	B->fxl = fx; B->fyl = fy; B->cxl = cx; B->cyl = cy;
+	B->fxli = 1.0f / fx; B->fyli = 1.0f / fy; B->cxli = -cx / fx; B->cyli = -cy / fy;
+	B->wM3G = w - 3; B->hM3G = h - 3;   // globalCalib.cpp:70-71
+	B->frames.resize(nF);
+	for (int i = 0; i < 4; i++) B->calibDelta[i] = 0;
+	return B;
+}
+extern "C" void dso_oracle_ba_destroy(dso_oracle_ba* B) { delete B->pool; delete B; }
+
+extern "C" void dso_oracle_ba_set_frame(dso_oracle_ba* B, int idx, const double* evalPT12, const double* state10,
+                                        const double* state_zero10, float ab_exposure, float frameEnergyTH, const float* dI)
+{
+	Frame& f = B->frames[idx];
+	f.evalPT = SE3d::from12(evalPT12);
+	memcpy(f.state, state10, 80); memcpy(f.state_zero, state_zero10, 80);
+	// FrameHessian::setState, HessianBlocks.h:183-199
+	for (int i = 0; i < 3; i++) f.state_scaled[i] = SCALE_XI_TRANS * f.state[i];
+	for (int i = 3; i < 6; i++) f.state_scaled[i] = SCALE_XI_ROT * f.state[i];
+	f.state_scaled[6] = SCALE_A * f.state[6]; f.state_scaled[7] = SCALE_B * f.state[7];
+	f.state_scaled[8] = SCALE_A * f.state[8]; f.state_scaled[9] = SCALE_B * f.state[9];
+	f.PRE_worldToCam = se3_exp(f.state_scaled) * f.evalPT;
+	f.PRE_camToWorld = se3_inverse(f.PRE_worldToCam);
+	f.ab_exposure = ab_exposure; f.frameEnergyTH = frameEnergyTH; f.dI = dI;
+}
+extern "C" void dso_oracle_ba_set_calib_delta(dso_oracle_ba* B, const double* d) { memcpy(B->calibDelta, d, 32); }
+
+static void fromToVecExposure(float exposureF, float exposureT, double Fa, double Fb, double Ta, double Tb, double* out)
+{
+	if (exposureF == 0 || exposureT == 0) exposureT = exposureF = 1;
+	double a = exp(Ta - Fa) * exposureT / exposureF;
+	double b = Tb - a * Fb;
+	out[0] = a; out[1] = b;
+}
+
+extern "C" void dso_oracle_ba_prepare(dso_oracle_ba* B)
+{
+	int nF = B->nF;
+	B->pre.assign(nF * nF, Precalc());
+	B->adHost.assign(nF * nF * 64, 0); B->adTarget.assign(nF * nF * 64, 0);
+	B->adHostF.assign(nF * nF * 64, 0); B->adTargetF.assign(nF * nF * 64, 0);
+	B->adHTdeltaF.assign(nF * nF * 8, 0);
+	float K[9] = { B->fxl, 0, B->cxl, 0, B->fyl, B->cyl, 0, 0, 1 };
+	float Kinv[9];
+	mat33f_inverse(K, Kinv);
+	for (int h = 0; h < nF; h++)
+		for (int t = 0; t < nF; t++)
+		{
+			const Frame& host = B->frames[h]; const Frame& target = B->frames[t];
+			// FrameFramePrecalc::set, HessianBlocks.cpp:213-250
+			Precalc& P = B->pre[h * nF + t];
+			SE3d leftToLeft_0 = target.evalPT * se3_inverse(host.evalPT);
+			for (int i = 0; i < 9; i++) P.RTll_0[i] = (float)leftToLeft_0.R[i];
+			for (int i = 0; i < 3; i++) P.tTll_0[i] = (float)leftToLeft_0.t[i];
+			SE3d leftToLeft = target.PRE_worldToCam * host.PRE_camToWorld;
+			for (int i = 0; i < 9; i++) P.RTll[i] = (float)leftToLeft.R[i];
+			for (int i = 0; i < 3; i++) P.tTll[i] = (float)leftToLeft.t[i];
+			P.distanceLL = (float)std::sqrt(leftToLeft.t[0] * leftToLeft.t[0] + leftToLeft.t[1] * leftToLeft.t[1] + leftToLeft.t[2] * leftToLeft.t[2]);
+			float KR[9];
+			mat33f_mul(K, P.RTll, KR);
+			mat33f_mul(KR, Kinv, P.KRKiTll);
+			mat33f_mul(P.RTll, Kinv, P.RKiTll);
+			mat33f_vec(K, P.tTll, P.KtTll);
+			double aff[2];
+			fromToVecExposure(host.ab_exposure, target.ab_exposure, host.state_scaled[6], host.state_scaled[7],
+			                  target.state_scaled[6], target.state_scaled[7], aff);
+			P.aff_mode[0] = (float)aff[0]; P.aff_mode[1] = (float)aff[1];
+			P.b0_mode = host.state_zero[7] * SCALE_B;   // aff_g2l_0().b
+
+			// setAdjointsF, EnergyFunctional.cpp:57-94
+			SE3d hostToTarget = leftToLeft_0;
+			double Ad[36];
+			se3_adj(hostToTarget, Ad);
+			double* AH = &B->adHost[(h + t * nF) * 64];
+			double* AT = &B->adTarget[(h + t * nF) * 64];
+			for (int i = 0; i < 64; i++) { AH[i] = (i % 9 == 0); AT[i] = (i % 9 == 0); }
+			for (int r = 0; r < 6; r++) for (int c = 0; c < 6; c++) AH[r * 8 + c] = -Ad[c * 6 + r];
+			double a0[2];
+			fromToVecExposure(host.ab_exposure, target.ab_exposure, host.state_zero[6] * SCALE_A, host.state_zero[7] * SCALE_B,
+			                  target.state_zero[6] * SCALE_A, target.state_zero[7] * SCALE_B, a0);
+			float affLL0 = (float)a0[0];
+			AT[6 * 8 + 6] = -affLL0;
+			AH[6 * 8 + 6] = affLL0;
+			AT[7 * 8 + 7] = -1;
+			AH[7 * 8 + 7] = affLL0;
+			for (int c = 0; c < 8; c++)
+			{
+				for (int r = 0; r < 3; r++) { AH[r * 8 + c] *= SCALE_XI_TRANS; AT[r * 8 + c] *= SCALE_XI_TRANS; }
+				for (int r = 3; r < 6; r++) { AH[r * 8 + c] *= SCALE_XI_ROT; AT[r * 8 + c] *= SCALE_XI_ROT; }
+				AH[6 * 8 + c] *= SCALE_A; AT[6 * 8 + c] *= SCALE_A;
+				AH[7 * 8 + c] *= SCALE_B; AT[7 * 8 + c] *= SCALE_B;
+			}
+			for (int i = 0; i < 64; i++) { B->adHostF[(h + t * nF) * 64 + i] = (float)AH[i]; B->adTargetF[(h + t * nF) * 64 + i] = (float)AT[i]; }
+		}
+	// setDeltaF, EnergyFunctional.cpp:178-193 (row vector times 8x8, float; only consumed by the
+	// linearised-residual mode, which is outside this oracle's scope, so plain left-to-right sums)
+	for (int h = 0; h < nF; h++)
+		for (int t = 0; t < nF; t++)
+		{
+			int idx = h + t * nF;
+			for (int c = 0; c < 8; c++)
+			{
+				float s0 = 0, s1 = 0;
+				for (int r = 0; r < 8; r++)
+				{
+					s0 += (float)(B->frames[h].state[r] - B->frames[h].state_zero[r]) * B->adHostF[idx * 64 + r * 8 + c];
+					s1 += (float)(B->frames[t].state[r] - B->frames[t].state_zero[r]) * B->adTargetF[idx * 64 + r * 8 + c];
+				}
+				B->adHTdeltaF[idx * 8 + c] = s0 + s1;
+			}
+		}
+	for (int i = 0; i < 4; i++) B->cDeltaF[i] = (float)B->calibDelta[i];
+}
+
+extern "C" void dso_oracle_ba_get_glue(const dso_oracle_ba* B, float* precalc, double* adHost, double* adTarget,
+                                       float* adHTdeltaF, float* cDeltaF4)
+{
+	int nF = B->nF;
+	if (precalc)
+		for (int i = 0; i < nF * nF; i++)
+		{
+			const Precalc& P = B->pre[i];
+			float* o = precalc + 28 * i;
+			memcpy(o, P.RTll_0, 36); memcpy(o + 9, P.tTll_0, 12); memcpy(o + 12, P.KRKiTll, 36); memcpy(o + 21, P.KtTll, 12);
+			o[24] = P.aff_mode[0]; o[25] = P.aff_mode[1]; o[26] = P.b0_mode; o[27] = 0;
+		}
+	if (adHost) memcpy(adHost, B->adHost.data(), sizeof(double) * nF * nF * 64);
+	if (adTarget) memcpy(adTarget, B->adTarget.data(), sizeof(double) * nF * nF * 64);
+	if (adHTdeltaF) memcpy(adHTdeltaF, B->adHTdeltaF.data(), sizeof(float) * nF * nF * 8);
+	if (cDeltaF4) memcpy(cDeltaF4, B->cDeltaF, 16);
+}
+
+extern "C" void dso_oracle_ba_set_points(dso_oracle_ba* B, int nP, const float* u, const float* v, const float* idepth_scaled,
+                                         const float* idepth_zero_scaled, const float* color8, const float* weights8,
+                                         const int* host, const float* priorF, const float* deltaF)
+{
+	B->points.assign(nP, Pt());
+	for (int i = 0; i < nP; i++)
+	{
+		Pt& p = B->points[i];
+		p.u = u[i]; p.v = v[i]; p.idepth_scaled = idepth_scaled[i]; p.idepth_zero_scaled = idepth_zero_scaled[i];
+		memcpy(p.color, color8 + 8 * i, 32); memcpy(p.weights, weights8 + 8 * i, 32);
+		p.host = host[i]; p.priorF = priorF[i]; p.deltaF = deltaF[i];
+		p.Hdd_accAF = p.bd_accAF = 0; p.Hdd_accLF = p.bd_accLF = 0;
+		for (int k = 0; k < 4; k++) p.Hcd_accAF[k] = p.Hcd_accLF[k] = 0;
+		p.HdiF = p.bdSumF = p.idepth_hessian = 0;
+	}
+}
+
+extern "C" void dso_oracle_ba_set_residuals(dso_oracle_ba* B, int nR, const int* point, const int* target, const int* state_state,
+                                            const double* state_energy, const unsigned char* isLinearized, const unsigned char* isActive)
+{
+	B->res.assign(nR, Res());
+	for (auto& p : B->points) p.residualsAll.clear();
+	for (int i = 0; i < nR; i++)
+	{
+		Res& r = B->res[i];
+		memset(&r, 0, sizeof(Res));
+		r.point = point[i]; r.target = target[i]; r.host = B->points[point[i]].host;
+		r.state_state = state_state[i];
+		r.state_NewState = ST_OUTLIER;   // resetOOB, Residuals.h:97-105
+		r.state_energy = state_energy ? state_energy[i] : 0;
+		r.state_NewEnergy = r.state_energy;
+		r.isLinearized = isLinearized ? isLinearized[i] != 0 : false;
+		r.isActive = isActive ? isActive[i] != 0 : false;
+		B->points[point[i]].residualsAll.push_back(i);
+	}
+}
+
+// getInterpolatedElement33, globalFuncs.h:75-89
+static inline void interp33(const float* mat, float x, float y, int width, float* out)
+{
+	int ix = (int)x;
+	int iy = (int)y;
+	float dx = x - ix;
+	float dy = y - iy;
+	float dxdy = dx * dy;
+	const float* bp = mat + 3 * (ix + iy * width);
+	float w11 = dxdy, w01 = dy - dxdy, w10 = dx - dxdy, w00 = 1 - dx - dy + dxdy;
+	for (int c = 0; c < 3; c++)
+		out[c] = w11 * bp[3 * (1 + width) + c] + w01 * bp[3 * width + c] + w10 * bp[3 + c] + w00 * bp[c];
+}
+
+// PointFrameResidual::linearize, Residuals.cpp:78-291
+static double linearize(dso_oracle_ba* B, Res& R)
+{
+	R.state_NewEnergyWithOutlier = -1;
+	if (R.state_state == ST_OOB) { R.state_NewState = ST_OOB; return R.state_energy; }
+	const Pt& point = B->points[R.point];
+	const Frame& host = B->frames[R.host];
+	const Frame& target = B->frames[R.target];
+	const Precalc* precalc = &B->pre[R.host * B->nF + R.target];
+	float energyLeft = 0;
+	const float* dIl = target.dI;
+	const float* PRE_KRKiTll = precalc->KRKiTll;
+	const float* PRE_KtTll = precalc->KtTll;
+	const float* PRE_RTll_0 = precalc->RTll_0;
+	const float* PRE_tTll_0 = precalc->tTll_0;
+	const float* color = point.color;
+	const float* weights = point.weights;
+	float affLL[2] = { precalc->aff_mode[0], precalc->aff_mode[1] };
+	float b0 = precalc->b0_mode;
+	const float fxl = B->fxl, fyl = B->fyl, cxl = B->cxl, cyl = B->cyl, fxli = B->fxli, fyli = B->fyli;
+#define R0(r, c) PRE_RTll_0[(r) * 3 + (c)]
+
+	float d_xi_x[6], d_xi_y[6], d_C_x[4], d_C_y[4], d_d_x, d_d_y;
+	{
+		float drescale, u, v, new_idepth, Ku, Kv, KliP[3];
+		// projectPoint (8-arg form), ResidualProjections.h:69-101, dx = dy = 0
+		KliP[0] = (point.u + 0 - cxl) * fxli;
+		KliP[1] = (point.v + 0 - cyl) * fyli;
+		KliP[2] = 1;
+		float ptp[3];
+		for (int r = 0; r < 3; r++)
+			ptp[r] = dot3_eigen(R0(r, 0), KliP[0], R0(r, 1), KliP[1], R0(r, 2), KliP[2]) + PRE_tTll_0[r] * point.idepth_zero_scaled;
+		drescale = 1.0f / ptp[2];
+		new_idepth = point.idepth_zero_scaled * drescale;
+		bool ok = true;
+		if (!(drescale > 0)) ok = false;
+		if (ok)
+		{
+			u = ptp[0] * drescale;
+			v = ptp[1] * drescale;
+			Ku = u * fxl + cxl;
+			Kv = v * fyl + cyl;
+			ok = Ku > 1.1f && Kv > 1.1f && Ku < B->wM3G && Kv < B->hM3G;
+		}
+		if (!ok) { R.state_NewState = ST_OOB; return R.state_energy; }
+
+		R.centerProjectedTo[0] = Ku; R.centerProjectedTo[1] = Kv; R.centerProjectedTo[2] = new_idepth;
+
+		// :131-132
+		d_d_x = drescale * (PRE_tTll_0[0] - PRE_tTll_0[2] * u) * SCALE_IDEPTH * fxl;
+		d_d_y = drescale * (PRE_tTll_0[1] - PRE_tTll_0[2] * v) * SCALE_IDEPTH * fyl;
+		// :138-156
+		d_C_x[2] = drescale * (R0(2, 0) * u - R0(0, 0));
+		d_C_x[3] = fxl * drescale * (R0(2, 1) * u - R0(0, 1)) * fyli;
+		d_C_x[0] = KliP[0] * d_C_x[2];
+		d_C_x[1] = KliP[1] * d_C_x[3];
+		d_C_y[2] = fyl * drescale * (R0(2, 0) * v - R0(1, 0)) * fxli;
+		d_C_y[3] = drescale * (R0(2, 1) * v - R0(1, 1));
+		d_C_y[0] = KliP[0] * d_C_y[2];
+		d_C_y[1] = KliP[1] * d_C_y[3];
+		d_C_x[0] = (d_C_x[0] + u) * SCALE_F;
+		d_C_x[1] *= SCALE_F;
+		d_C_x[2] = (d_C_x[2] + 1) * SCALE_C;
+		d_C_x[3] *= SCALE_C;
+		d_C_y[0] *= SCALE_F;
+		d_C_y[1] = (d_C_y[1] + v) * SCALE_F;
+		d_C_y[2] *= SCALE_C;
+		d_C_y[3] = (d_C_y[3] + 1) * SCALE_C;
+		// :159-171
+		d_xi_x[0] = new_idepth * fxl;
+		d_xi_x[1] = 0;
+		d_xi_x[2] = -new_idepth * u * fxl;
+		d_xi_x[3] = -u * v * fxl;
+		d_xi_x[4] = (1 + u * u) * fxl;
+		d_xi_x[5] = -v * fxl;
+		d_xi_y[0] = 0;
+		d_xi_y[1] = new_idepth * fyl;
+		d_xi_y[2] = -new_idepth * v * fyl;
+		d_xi_y[3] = -(1 + v * v) * fyl;
+		d_xi_y[4] = u * v * fyl;
+		d_xi_y[5] = u * fyl;
+	}
+	RawJ* J = &R.J;
+	for (int i = 0; i < 6; i++) { J->Jpdxi[0][i] = d_xi_x[i]; J->Jpdxi[1][i] = d_xi_y[i]; }
+	for (int i = 0; i < 4; i++) { J->Jpdc[0][i] = d_C_x[i]; J->Jpdc[1][i] = d_C_y[i]; }
+	J->Jpdd[0] = d_d_x; J->Jpdd[1] = d_d_y;
+
+	float JIdxJIdx_00 = 0, JIdxJIdx_11 = 0, JIdxJIdx_10 = 0;
+	float JabJIdx_00 = 0, JabJIdx_01 = 0, JabJIdx_10 = 0, JabJIdx_11 = 0;
+	float JabJab_00 = 0, JabJab_01 = 0, JabJab_11 = 0;
+	float wJI2_sum = 0;
+
+	for (int idx = 0; idx < patternNum; idx++)
+	{
+		float Ku, Kv;
+		// projectPoint (7-arg form), ResidualProjections.h:55-65
+		{
+			float up = point.u + patternP[idx][0], vp = point.v + patternP[idx][1];
+			float ptp[3];
+			for (int r = 0; r < 3; r++)
+				ptp[r] = dot3_eigen(PRE_KRKiTll[r * 3], up, PRE_KRKiTll[r * 3 + 1], vp, PRE_KRKiTll[r * 3 + 2], 1.0f) + PRE_KtTll[r] * point.idepth_scaled;
+			Ku = ptp[0] / ptp[2];
+			Kv = ptp[1] / ptp[2];
+			if (!(Ku > 1.1f && Kv > 1.1f && Ku < B->wM3G && Kv < B->hM3G))
+			{ R.state_NewState = ST_OOB; return R.state_energy; }
+		}
+		R.projectedTo[idx][0] = Ku;
+		R.projectedTo[idx][1] = Kv;
+
+		float hitColor[3];
+		interp33(dIl, Ku, Kv, B->w, hitColor);
+		float residual = hitColor[0] - (float)(affLL[0] * color[idx] + affLL[1]);
+		float drdA = (color[idx] - b0);
+		if (!std::isfinite((float)hitColor[0]))
+		{ R.state_NewState = ST_OOB; return R.state_energy; }
+
+		float w = sqrtf(setting_outlierTHSumComponent / (setting_outlierTHSumComponent + (hitColor[1] * hitColor[1] + hitColor[2] * hitColor[2])));
+		w = 0.5f * (w + weights[idx]);
+		float hw = fabsf(residual) < setting_huberTH ? 1 : setting_huberTH / fabsf(residual);
+		energyLeft += w * w * hw * residual * residual * (2 - hw);
+		{
+			if (hw < 1) hw = sqrtf(hw);
+			hw = hw * w;
+			hitColor[1] *= hw;
+			hitColor[2] *= hw;
+			J->resF[idx] = residual * hw;
+			J->JIdx[0][idx] = hitColor[1];
+			J->JIdx[1][idx] = hitColor[2];
+			J->JabF[0][idx] = drdA * hw;
+			J->JabF[1][idx] = hw;
+			JIdxJIdx_00 += hitColor[1] * hitColor[1];
+			JIdxJIdx_11 += hitColor[2] * hitColor[2];
+			JIdxJIdx_10 += hitColor[1] * hitColor[2];
+			JabJIdx_00 += drdA * hw * hitColor[1];
+			JabJIdx_01 += drdA * hw * hitColor[2];
+			JabJIdx_10 += hw * hitColor[1];
+			JabJIdx_11 += hw * hitColor[2];
+			JabJab_00 += drdA * drdA * hw * hw;
+			JabJab_01 += drdA * hw * hw;
+			JabJab_11 += hw * hw;
+			wJI2_sum += hw * hw * (hitColor[1] * hitColor[1] + hitColor[2] * hitColor[2]);
+			if (setting_affineOptModeA < 0) J->JabF[0][idx] = 0;
+			if (setting_affineOptModeB < 0) J->JabF[1][idx] = 0;
+		}
+	}
+	J->JIdx2[0] = JIdxJIdx_00; J->JIdx2[1] = JIdxJIdx_10; J->JIdx2[2] = JIdxJIdx_10; J->JIdx2[3] = JIdxJIdx_11;
+	J->JabJIdx[0] = JabJIdx_00; J->JabJIdx[1] = JabJIdx_01; J->JabJIdx[2] = JabJIdx_10; J->JabJIdx[3] = JabJIdx_11;
+	J->Jab2[0] = JabJab_00; J->Jab2[1] = JabJab_01; J->Jab2[2] = JabJab_01; J->Jab2[3] = JabJab_11;
+
+	R.state_NewEnergyWithOutlier = energyLeft;
+	float th = std::max<float>(host.frameEnergyTH, target.frameEnergyTH);
+	if (energyLeft > th || wJI2_sum < 2)
+	{
+		energyLeft = th;
+		R.state_NewState = ST_OUTLIER;
+	}
+	else
+		R.state_NewState = ST_IN;
+	R.state_NewEnergy = energyLeft;
+	return energyLeft;
+#undef R0
+}
+
+static void export_linearize(dso_oracle_ba* B, int* newState, float* newEnergy, float* newEnergyWithOutlier,
+                             float* cpt, float* proj, float* J74)
+{
+	int nR = (int)B->res.size();
+	for (int i = 0; i < nR; i++)
+	{
+		const Res& r = B->res[i];
+		if (newState) newState[i] = r.state_NewState;
+		if (newEnergy) newEnergy[i] = (float)r.state_NewEnergy;
+		if (newEnergyWithOutlier) newEnergyWithOutlier[i] = (float)r.state_NewEnergyWithOutlier;
+		if (cpt) memcpy(cpt + 3 * i, r.centerProjectedTo, 12);
+		if (proj) memcpy(proj + 16 * i, r.projectedTo, 64);
+		if (J74) memcpy(J74 + 74 * i, &r.J, sizeof(RawJ));
+	}
+}
+
+extern "C" double dso_oracle_ba_linearize(dso_oracle_ba* B, int* newState, float* newEnergy, float* newEnergyWithOutlier,
+                                          float* cpt, float* proj, float* J74, double* energy_ret)
+{
+	// linearizeAll_Reductor, FullSystemOptimize.cpp:52-60 (single-thread branch :171-176)
+	double stats0 = 0;
+	int nR = (int)B->res.size();
+	for (int k = 0; k < nR; k++)
+	{
+		double e = linearize(B, B->res[k]);
+		if (energy_ret) energy_ret[k] = e;
+		stats0 += e;
+	}
+	export_linearize(B, newState, newEnergy, newEnergyWithOutlier, cpt, proj, J74);
+	return stats0;
+}
+
+extern "C" double dso_oracle_ba_linearize_mt(dso_oracle_ba* B, int nthreads)
+{
+	// multi-thread branch, FullSystemOptimize.cpp:164: static split, step = ceil(n/NUM_THREADS)
+	Pool* pool = B->getPool(nthreads);
+	std::vector<double> stats(nthreads, 0.0);
+	pool->reduce([&](int lo, int hi, int tid) { for (int k = lo; k < hi; k++) stats[tid] += linearize(B, B->res[k]); },
+	             0, (int)B->res.size(), 0);
+	double s = 0; for (double v : stats) s += v;
+	return s;
+}
+
+// applyRes(true), Residuals.cpp:323-347 + EFResidual::takeDataF, EnergyFunctionalStructs.cpp:39-49
+extern "C" void dso_oracle_ba_apply_res(dso_oracle_ba* B, unsigned char* isActive_out, float* JpJdF_out)
+{
+	int nR = (int)B->res.size();
+	for (int i = 0; i < nR; i++)
+	{
+		Res& r = B->res[i];
+		if (r.state_state != ST_OOB)
+		{
+			if (r.state_NewState == ST_IN)
+			{
+				r.isActive = true;
+				std::swap(r.J, r.efJ);
+				const RawJ* J = &r.efJ;
+				float JI_JI_Jd[2];
+				JI_JI_Jd[0] = J->JIdx2[0] * J->Jpdd[0] + J->JIdx2[1] * J->Jpdd[1];
+				JI_JI_Jd[1] = J->JIdx2[2] * J->Jpdd[0] + J->JIdx2[3] * J->Jpdd[1];
+				for (int k = 0; k < 6; k++)
+					r.JpJdF[k] = J->Jpdxi[0][k] * JI_JI_Jd[0] + J->Jpdxi[1][k] * JI_JI_Jd[1];
+				r.JpJdF[6] = J->JabJIdx[0] * J->Jpdd[0] + J->JabJIdx[1] * J->Jpdd[1];
+				r.JpJdF[7] = J->JabJIdx[2] * J->Jpdd[0] + J->JabJIdx[3] * J->Jpdd[1];
+			}
+			else
+				r.isActive = false;
+			r.state_state = r.state_NewState;
+			r.state_energy = r.state_NewEnergy;
+		}
+		if (isActive_out) isActive_out[i] = r.isActive;
+		if (JpJdF_out) memcpy(JpJdF_out + 8 * i, r.JpJdF, 32);
+	}
+}
+
+// AccumulatedTopHessianSSE::addPoint<0>, AccumulatedTopHessian.cpp:39-177
+static void addPointA(dso_oracle_ba* B, Pt& p, AccApprox* acc, int* nres)
+{
+	int nF = B->nF;
+	float bd_acc = 0, Hdd_acc = 0, Hcd_acc[4] = { 0, 0, 0, 0 };
+	for (int ri : p.residualsAll)
+	{
+		Res& r = B->res[ri];
+		if (r.isLinearized || !r.isActive) continue;
+		const RawJ* rJ = &r.efJ;
+		int htIDX = r.host + r.target * nF;
+		const float* resApprox = rJ->resF;
+		float JI_r[2] = { 0, 0 }, Jab_r[2] = { 0, 0 }, rr = 0;
+		for (int i = 0; i < patternNum; i++)
+		{
+			JI_r[0] += resApprox[i] * rJ->JIdx[0][i];
+			JI_r[1] += resApprox[i] * rJ->JIdx[1][i];
+			Jab_r[0] += resApprox[i] * rJ->JabF[0][i];
+			Jab_r[1] += resApprox[i] * rJ->JabF[1][i];
+			rr += resApprox[i] * resApprox[i];
+		}
+		acc[htIDX].update(rJ->Jpdc[0], rJ->Jpdxi[0], rJ->Jpdc[1], rJ->Jpdxi[1], rJ->JIdx2[0], rJ->JIdx2[1], rJ->JIdx2[3]);
+		acc[htIDX].updateBotRight(rJ->Jab2[0], rJ->Jab2[1], Jab_r[0], rJ->Jab2[3], Jab_r[1], rr);
+		acc[htIDX].updateTopRight(rJ->Jpdc[0], rJ->Jpdxi[0], rJ->Jpdc[1], rJ->Jpdxi[1],
+		                          rJ->JabJIdx[0], rJ->JabJIdx[1], rJ->JabJIdx[2], rJ->JabJIdx[3], JI_r[0], JI_r[1]);
+		float Ji2_Jpdd[2];
+		Ji2_Jpdd[0] = rJ->JIdx2[0] * rJ->Jpdd[0] + rJ->JIdx2[1] * rJ->Jpdd[1];
+		Ji2_Jpdd[1] = rJ->JIdx2[2] * rJ->Jpdd[0] + rJ->JIdx2[3] * rJ->Jpdd[1];
+		bd_acc += JI_r[0] * rJ->Jpdd[0] + JI_r[1] * rJ->Jpdd[1];
+		Hdd_acc += Ji2_Jpdd[0] * rJ->Jpdd[0] + Ji2_Jpdd[1] * rJ->Jpdd[1];
+		for (int k = 0; k < 4; k++) Hcd_acc[k] += rJ->Jpdc[0][k] * Ji2_Jpdd[0] + rJ->Jpdc[1][k] * Ji2_Jpdd[1];
+		(*nres)++;
+	}
+	p.Hdd_accAF = Hdd_acc; p.bd_accAF = bd_acc;
+	for (int k = 0; k < 4; k++) p.Hcd_accAF[k] = Hcd_acc[k];
+}
+
+static inline void mm8(const double* A, const double* Bm, double* C, bool transB)
+{
+	for (int i = 0; i < 8; i++)
+		for (int j = 0; j < 8; j++)
+		{
+			double s = 0;
+			for (int k = 0; k < 8; k++) s += A[i * 8 + k] * (transB ? Bm[j * 8 + k] : Bm[k * 8 + j]);
+			C[i * 8 + j] = s;
+		}
+}
+
+// stitchDoubleInternal, AccumulatedTopHessian.cpp:259-325 (usePrior=false for accSSE_top_A)
+static void stitchA(dso_oracle_ba* B, std::vector<std::vector<AccApprox>>& accs, int toAggregate, double* H, double* b, int kmin, int kmax)
+{
+	int nF = B->nF, N = 8 * nF + CPARS;
+	for (int k = kmin; k < kmax; k++)
+	{
+		int h = k % nF, t = k / nF;
+		int hIdx = CPARS + h * 8, tIdx = CPARS + t * 8, aidx = h + nF * t;
+		double accH[13][13];
+		memset(accH, 0, sizeof(accH));
+		for (int tid2 = 0; tid2 < toAggregate; tid2++)
+		{
+			accs[tid2][aidx].finish();
+			if (accs[tid2][aidx].num == 0) continue;
+			for (int i = 0; i < 13; i++) for (int j = 0; j < 13; j++) accH[i][j] += (double)accs[tid2][aidx].H[i][j];
+		}
+		const double* AH = &B->adHost[aidx * 64];
+		const double* AT = &B->adTarget[aidx * 64];
+		double A88[64], T1[64], T2[64];
+		for (int i = 0; i < 8; i++) for (int j = 0; j < 8; j++) A88[i * 8 + j] = accH[CPARS + i][CPARS + j];
+		mm8(AH, A88, T1, false); mm8(T1, AH, T2, true);
+		for (int i = 0; i < 8; i++) for (int j = 0; j < 8; j++) H[(hIdx + i) * N + hIdx + j] += T2[i * 8 + j];
+		mm8(AT, A88, T1, false); mm8(T1, AT, T2, true);
+		for (int i = 0; i < 8; i++) for (int j = 0; j < 8; j++) H[(tIdx + i) * N + tIdx + j] += T2[i * 8 + j];
+		mm8(AH, A88, T1, false); mm8(T1, AT, T2, true);
+		for (int i = 0; i < 8; i++) for (int j = 0; j < 8; j++) H[(hIdx + i) * N + tIdx + j] += T2[i * 8 + j];
+		for (int i = 0; i < 8; i++)
+			for (int j = 0; j < CPARS; j++)
+			{
+				double sh = 0, st = 0;
+				for (int q = 0; q < 8; q++) { sh += AH[i * 8 + q] * accH[CPARS + q][j]; st += AT[i * 8 + q] * accH[CPARS + q][j]; }
+				H[(hIdx + i) * N + j] += sh;
+				H[(tIdx + i) * N + j] += st;
+			}
+		for (int i = 0; i < CPARS; i++) for (int j = 0; j < CPARS; j++) H[i * N + j] += accH[i][j];
+		for (int i = 0; i < 8; i++)
+		{
+			double sh = 0, st = 0;
+			for (int q = 0; q < 8; q++) { sh += AH[i * 8 + q] * accH[CPARS + q][CPARS + 8]; st += AT[i * 8 + q] * accH[CPARS + q][CPARS + 8]; }
+			b[hIdx + i] += sh;
+			b[tIdx + i] += st;
+		}
+		for (int i = 0; i < CPARS; i++) b[i] += accH[i][CPARS + 8];
+	}
+}
+
+// accumulateAF_MT, EnergyFunctional.cpp:209-232 + stitchDoubleMT, AccumulatedTopHessian.h:91-139
+extern "C" void dso_oracle_ba_accumulate_A(dso_oracle_ba* B, int MT, int nthreads, double* H, double* b, int* resInA,
+                                           float* Hdd, float* bd, float* Hcd4)
+{
+	int nF = B->nF, N = 8 * nF + CPARS, nP = (int)B->points.size();
+	int T = MT ? nthreads : 1;
+	std::vector<std::vector<AccApprox>> accs(T, std::vector<AccApprox>(nF * nF));
+	std::vector<int> nres(T, 0);
+	for (auto& a : accs) for (auto& x : a) x.initialize();
+	memset(H, 0, sizeof(double) * N * N); memset(b, 0, sizeof(double) * N);
+	if (MT)
+	{
+		Pool* pool = B->getPool(nthreads);
+		pool->reduce([&](int lo, int hi, int tid) { for (int i = lo; i < hi; i++) addPointA(B, B->points[i], accs[tid].data(), &nres[tid]); }, 0, nP, 50);
+		std::vector<std::vector<double>> Hs(T, std::vector<double>(N * N, 0.0)), bs(T, std::vector<double>(N, 0.0));
+		pool->reduce([&](int lo, int hi, int tid) { stitchA(B, accs, T, Hs[tid].data(), bs[tid].data(), lo, hi); }, 0, nF * nF, 0);
+		for (int i = 0; i < T; i++)
+		{
+			for (int k = 0; k < N * N; k++) H[k] += Hs[i][k];
+			for (int k = 0; k < N; k++) b[k] += bs[i][k];
+			if (i > 0) nres[0] += nres[i];
+		}
+	}
+	else
+	{
+		for (int i = 0; i < nP; i++) addPointA(B, B->points[i], accs[0].data(), &nres[0]);
+		stitchA(B, accs, 1, H, b, 0, nF * nF);
+	}
+	// "make diagonal by copying over parts", AccumulatedTopHessian.h:126-138
+	for (int h = 0; h < nF; h++)
+	{
+		int hIdx = CPARS + h * 8;
+		for (int i = 0; i < CPARS; i++) for (int j = 0; j < 8; j++) H[i * N + hIdx + j] = H[(hIdx + j) * N + i];
+		for (int t = h + 1; t < nF; t++)
+		{
+			int tIdx = CPARS + t * 8;
+			for (int i = 0; i < 8; i++) for (int j = 0; j < 8; j++) H[(hIdx + i) * N + tIdx + j] += H[(tIdx + j) * N + hIdx + i];
+			for (int i = 0; i < 8; i++) for (int j = 0; j < 8; j++) H[(tIdx + i) * N + hIdx + j] = H[(hIdx + j) * N + tIdx + i];
+		}
+	}
+	if (resInA) *resInA = nres[0];
+	for (int i = 0; i < nP; i++)
+	{
+		if (Hdd) Hdd[i] = B->points[i].Hdd_accAF;
+		if (bd) bd[i] = B->points[i].bd_accAF;
+		if (Hcd4) memcpy(Hcd4 + 4 * i, B->points[i].Hcd_accAF, 16);
+	}
+}
+
+struct SCAcc
+{
+	std::vector<AccXX<8, CPARS>> accE;
+	std::vector<AccX<8>> accEB;
+	std::vector<AccXX<8, 8>> accD;
+	AccXX<CPARS, CPARS> accHcc;
+	AccX<CPARS> accbc;
+	void setZero(int n)
+	{
+		accE.resize(n * n); accEB.resize(n * n); accD.resize(n * n * n);
+		accHcc.initialize(); accbc.initialize();
+		for (auto& a : accE) a.initialize();
+		for (auto& a : accEB) a.initialize();
+		for (auto& a : accD) a.initialize();
+	}
+};
+
+// AccumulatedSCHessianSSE::addPoint, AccumulatedSCHessian.cpp:35-85
+static void addPointSC(dso_oracle_ba* B, Pt& p, bool shiftPriorToZero, SCAcc& S)
+{
+	int nF = B->nF;
+	int ngoodres = 0;
+	for (int ri : p.residualsAll) if (B->res[ri].isActive) ngoodres++;
+	if (ngoodres == 0)
+	{
+		p.HdiF = 0; p.bdSumF = 0; p.idepth_hessian = 0;
+		return;
+	}
+	float H = p.Hdd_accAF + p.Hdd_accLF + p.priorF;
+	if (H < 1e-10) H = 1e-10;
+	p.idepth_hessian = H;
+	p.HdiF = 1.0 / H;
+	p.bdSumF = p.bd_accAF + p.bd_accLF;
+	if (shiftPriorToZero) p.bdSumF += p.priorF * p.deltaF;
+	float Hcd[4];
+	for (int k = 0; k < 4; k++) Hcd[k] = p.Hcd_accAF[k] + p.Hcd_accLF[k];
+	S.accHcc.update(Hcd, Hcd, p.HdiF);
+	S.accbc.update(Hcd, p.bdSumF * p.HdiF);
+	int nFrames2 = nF * nF;
+	for (int r1i : p.residualsAll)
+	{
+		Res& r1 = B->res[r1i];
+		if (!r1.isActive) continue;
+		int r1ht = r1.host + r1.target * nF;
+		for (int r2i : p.residualsAll)
+		{
+			Res& r2 = B->res[r2i];
+			if (!r2.isActive) continue;
+			S.accD[r1ht + r2.target * nFrames2].update(r1.JpJdF, r2.JpJdF, p.HdiF);
+		}
+		S.accE[r1ht].update(r1.JpJdF, Hcd, p.HdiF);
+		S.accEB[r1ht].update(r1.JpJdF, p.HdiF * p.bdSumF);
+	}
+}
+
+// stitchDoubleInternal, AccumulatedSCHessian.cpp:86-165
+static void stitchSC(dso_oracle_ba* B, std::vector<SCAcc>& S, int toAggregate, double* H, double* b, int kmin, int kmax)
+{
+	int nf = B->nF, N = 8 * nf + CPARS, nframes2 = nf * nf;
+	for (int k = kmin; k < kmax; k++)
+	{
+		int i = k % nf, j = k / nf;
+		int iIdx = CPARS + i * 8, jIdx = CPARS + j * 8, ijIdx = i + nf * j;
+		double Hpc[8][CPARS], bp[8];
+		memset(Hpc, 0, sizeof(Hpc)); memset(bp, 0, sizeof(bp));
+		for (int tid2 = 0; tid2 < toAggregate; tid2++)
+		{
+			S[tid2].accE[ijIdx].finish();
+			S[tid2].accEB[ijIdx].finish();
+			for (int r = 0; r < 8; r++) { for (int c = 0; c < CPARS; c++) Hpc[r][c] += (double)S[tid2].accE[ijIdx].A1m[r][c]; bp[r] += (double)S[tid2].accEB[ijIdx].A1m[r]; }
+		}
+		const double* AHij = &B->adHost[ijIdx * 64];
+		const double* ATij = &B->adTarget[ijIdx * 64];
+		for (int r = 0; r < 8; r++)
+		{
+			for (int c = 0; c < CPARS; c++)
+			{
+				double sh = 0, st = 0;
+				for (int q = 0; q < 8; q++) { sh += AHij[r * 8 + q] * Hpc[q][c]; st += ATij[r * 8 + q] * Hpc[q][c]; }
+				H[(iIdx + r) * N + c] += sh;
+				H[(jIdx + r) * N + c] += st;
+			}
+			double sh = 0, st = 0;
+			for (int q = 0; q < 8; q++) { sh += AHij[r * 8 + q] * bp[q]; st += ATij[r * 8 + q] * bp[q]; }
+			b[iIdx + r] += sh;
+			b[jIdx + r] += st;
+		}
+		for (int k2 = 0; k2 < nf; k2++)
+		{
+			int kIdx = CPARS + k2 * 8;
+			int ijkIdx = ijIdx + k2 * nframes2;
+			int ikIdx = i + nf * k2;
+			double accDM[64];
+			memset(accDM, 0, sizeof(accDM));
+			for (int tid2 = 0; tid2 < toAggregate; tid2++)
+			{
+				S[tid2].accD[ijkIdx].finish();
+				if (S[tid2].accD[ijkIdx].num == 0) continue;
+				for (int r = 0; r < 8; r++) for (int c = 0; c < 8; c++) accDM[r * 8 + c] += (double)S[tid2].accD[ijkIdx].A1m[r][c];
+			}
+			const double* AHik = &B->adHost[ikIdx * 64];
+			const double* ATik = &B->adTarget[ikIdx * 64];
+			double T1[64], T2[64];
+			mm8(AHij, accDM, T1, false); mm8(T1, AHik, T2, true);
+			for (int r = 0; r < 8; r++) for (int c = 0; c < 8; c++) H[(iIdx + r) * N + iIdx + c] += T2[r * 8 + c];
+			mm8(ATij, accDM, T1, false); mm8(T1, ATik, T2, true);
+			for (int r = 0; r < 8; r++) for (int c = 0; c < 8; c++) H[(jIdx + r) * N + kIdx + c] += T2[r * 8 + c];
+			mm8(ATij, accDM, T1, false); mm8(T1, AHik, T2, true);
+			for (int r = 0; r < 8; r++) for (int c = 0; c < 8; c++) H[(jIdx + r) * N + iIdx + c] += T2[r * 8 + c];
+			mm8(AHij, accDM, T1, false); mm8(T1, ATik, T2, true);
+			for (int r = 0; r < 8; r++) for (int c = 0; c < 8; c++) H[(iIdx + r) * N + kIdx + c] += T2[r * 8 + c];
+		}
+	}
+	if (kmin == 0)
+	{
+		for (int tid2 = 0; tid2 < toAggregate; tid2++)
+		{
+			S[tid2].accHcc.finish();
+			S[tid2].accbc.finish();
+			for (int r = 0; r < CPARS; r++) { for (int c = 0; c < CPARS; c++) H[r * N + c] += (double)S[tid2].accHcc.A1m[r][c]; b[r] += (double)S[tid2].accbc.A1m[r]; }
+		}
+	}
+}
+
+// accumulateSCF_MT, EnergyFunctional.cpp:257-274 + stitchDoubleMT, AccumulatedSCHessian.h:93-135
+extern "C" void dso_oracle_ba_accumulate_SC(dso_oracle_ba* B, int MT, int nthreads, double* H, double* b,
+                                            float* HdiF, float* bdSumF, float* idepth_hessian)
+{
+	int nF = B->nF, N = 8 * nF + CPARS, nP = (int)B->points.size();
+	int T = MT ? nthreads : 1;
+	std::vector<SCAcc> S(T);
+	for (auto& s : S) s.setZero(nF);
+	memset(H, 0, sizeof(double) * N * N); memset(b, 0, sizeof(double) * N);
+	if (MT)
+	{
+		Pool* pool = B->getPool(nthreads);
+		pool->reduce([&](int lo, int hi, int tid) { for (int i = lo; i < hi; i++) addPointSC(B, B->points[i], true, S[tid]); }, 0, nP, 50);
+		std::vector<std::vector<double>> Hs(T, std::vector<double>(N * N, 0.0)), bs(T, std::vector<double>(N, 0.0));
+		pool->reduce([&](int lo, int hi, int tid) { stitchSC(B, S, T, Hs[tid].data(), bs[tid].data(), lo, hi); }, 0, nF * nF, 0);
+		for (int i = 0; i < T; i++)
+		{
+			for (int k = 0; k < N * N; k++) H[k] += Hs[i][k];
+			for (int k = 0; k < N; k++) b[k] += bs[i][k];
+		}
+	}
+	else
+	{
+		// EnergyFunctional.cpp:268-272: ST branch also passes shiftPriorToZero = true
+		for (int i = 0; i < nP; i++) addPointSC(B, B->points[i], true, S[0]);
+		stitchSC(B, S, 1, H, b, 0, nF * nF);
+	}
+	for (int h = 0; h < nF; h++)
+	{
+		int hIdx = CPARS + h * 8;
+		for (int i = 0; i < CPARS; i++) for (int j = 0; j < 8; j++) H[i * N + hIdx + j] = H[(hIdx + j) * N + i];
+	}
+	for (int i = 0; i < nP; i++)
+	{
+		if (HdiF) HdiF[i] = B->points[i].HdiF;
+		if (bdSumF) bdSumF[i] = B->points[i].bdSumF;
+		if (idepth_hessian) idepth_hessian[i] = B->points[i].idepth_hessian;
+	}
+}

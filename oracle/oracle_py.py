@@ -1,0 +1,249 @@
+"""TEST INFRASTRUCTURE ONLY -- ctypes binding of the CPU oracle (oracle/libdso_oracle.so).
+
+May be imported by tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs,
+never by the product package.  PARITY UNPINNED: see oracle/dso_oracle.h.
+"""
+import ctypes as C
+import os
+import subprocess
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = None
+
+f32p = np.ctypeslib.ndpointer(dtype=np.float32, flags="C_CONTIGUOUS")
+f64p = np.ctypeslib.ndpointer(dtype=np.float64, flags="C_CONTIGUOUS")
+i32p = np.ctypeslib.ndpointer(dtype=np.int32, flags="C_CONTIGUOUS")
+u8p = np.ctypeslib.ndpointer(dtype=np.uint8, flags="C_CONTIGUOUS")
+
+
+class TrackResult(C.Structure):
+    _fields_ = [("ok", C.c_int), ("aborted_level", C.c_int), ("pose", C.c_double * 12),
+                ("aff_a", C.c_double), ("aff_b", C.c_double), ("lastResiduals", C.c_double * 5),
+                ("lastFlowIndicators", C.c_double * 3), ("n_passes", C.c_int), ("pass_level", C.c_int * 8),
+                ("pass_rmse", C.c_double * 8), ("n_iterations", C.c_int), ("n_evals", C.c_int),
+                ("trace_len", C.c_int), ("trace", C.c_ubyte * 256), ("point_evals", C.c_double)]
+
+
+def build(force=False):
+    so = os.path.join(_HERE, "libdso_oracle.so")
+    srcs = [os.path.join(_HERE, f) for f in ("oracle_tracker.cpp", "oracle_ba.cpp", "oracle_math.h", "dso_oracle.h", "Makefile")]
+    if force or not os.path.exists(so) or any(os.path.getmtime(s) > os.path.getmtime(so) for s in srcs):
+        subprocess.check_call(["make", "-C", _HERE, "CXX=g++"], stdout=subprocess.DEVNULL)
+    return so
+
+
+def lib():
+    global _LIB
+    if _LIB is None:
+        so = os.path.join(_HERE, "libdso_oracle.so")
+        if not os.path.exists(so):
+            build()
+        L = C.CDLL(so)
+        vp = C.c_void_p
+        L.dso_oracle_make_images.argtypes = [f32p, C.c_int, C.c_int, C.c_int, vp, C.POINTER(vp), C.POINTER(vp)]
+        L.dso_oracle_tracker_create.restype = vp
+        L.dso_oracle_tracker_create.argtypes = [C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float]
+        L.dso_oracle_tracker_destroy.argtypes = [vp]
+        L.dso_oracle_tracker_get_K.argtypes = [vp, C.c_int] + [C.POINTER(C.c_float)] * 4 + [vp]
+        L.dso_oracle_tracker_set_ref.argtypes = [vp, C.c_int, f32p, f32p, f32p, f32p, C.POINTER(vp), C.c_double, C.c_double, C.c_float]
+        L.dso_oracle_tracker_set_cloud.argtypes = [vp, C.c_int, C.c_int, f32p, f32p, f32p, f32p]
+        L.dso_oracle_tracker_set_ref_aff.argtypes = [vp, C.c_double, C.c_double, C.c_float]
+        L.dso_oracle_tracker_get_cloud.restype = C.c_int
+        L.dso_oracle_tracker_get_cloud.argtypes = [vp, C.c_int, vp, vp, vp, vp]
+        L.dso_oracle_tracker_set_new_frame.argtypes = [vp, C.POINTER(vp), C.c_float]
+        L.dso_oracle_calc_res.argtypes = [vp, C.c_int, f64p, C.c_double, C.c_double, C.c_float, f64p]
+        L.dso_oracle_calc_gs.argtypes = [vp, C.c_int, C.c_double, C.c_double, f64p, f64p]
+        L.dso_oracle_get_warped.restype = C.c_int
+        L.dso_oracle_get_warped.argtypes = [vp, C.POINTER(vp)]
+        L.dso_oracle_get_point_status.argtypes = [vp, u8p]
+        L.dso_oracle_track_newest_coarse.argtypes = [vp, f64p, C.c_double, C.c_double, C.c_int, f64p, C.POINTER(TrackResult)]
+        L.dso_oracle_ba_create.restype = vp
+        L.dso_oracle_ba_create.argtypes = [C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float]
+        L.dso_oracle_ba_destroy.argtypes = [vp]
+        L.dso_oracle_ba_set_frame.argtypes = [vp, C.c_int, f64p, f64p, f64p, C.c_float, C.c_float, f32p]
+        L.dso_oracle_ba_set_calib_delta.argtypes = [vp, f64p]
+        L.dso_oracle_ba_prepare.argtypes = [vp]
+        L.dso_oracle_ba_get_glue.argtypes = [vp, f32p, f64p, f64p, f32p, f32p]
+        L.dso_oracle_ba_set_points.argtypes = [vp, C.c_int, f32p, f32p, f32p, f32p, f32p, f32p, i32p, f32p, f32p]
+        L.dso_oracle_ba_set_residuals.argtypes = [vp, C.c_int, i32p, i32p, i32p, f64p, u8p, u8p]
+        L.dso_oracle_ba_linearize.restype = C.c_double
+        L.dso_oracle_ba_linearize.argtypes = [vp, i32p, f32p, f32p, f32p, f32p, f32p, f64p]
+        L.dso_oracle_ba_linearize_mt.restype = C.c_double
+        L.dso_oracle_ba_linearize_mt.argtypes = [vp, C.c_int]
+        L.dso_oracle_ba_apply_res.argtypes = [vp, u8p, f32p]
+        L.dso_oracle_ba_accumulate_A.argtypes = [vp, C.c_int, C.c_int, f64p, f64p, C.POINTER(C.c_int), f32p, f32p, f32p]
+        L.dso_oracle_ba_accumulate_SC.argtypes = [vp, C.c_int, C.c_int, f64p, f64p, f32p, f32p, f32p]
+        _LIB = L
+    return _LIB
+
+
+def _ptr_array(arrs):
+    a = (C.c_void_p * len(arrs))()
+    for i, x in enumerate(arrs):
+        a[i] = x.ctypes.data
+    return a
+
+
+def make_images(color, levels, B=None):
+    """Returns (dIp list of [h_l, w_l, 3] float32, absgrad list of [h_l, w_l] float32); untouched elements are 0."""
+    h, w = color.shape
+    color = np.ascontiguousarray(color, dtype=np.float32)
+    dIp = [np.zeros((h >> l, w >> l, 3), dtype=np.float32) for l in range(levels)]
+    ab = [np.zeros((h >> l, w >> l), dtype=np.float32) for l in range(levels)]
+    Bp = None
+    if B is not None:
+        B = np.ascontiguousarray(B, dtype=np.float32)
+        Bp = B.ctypes.data
+    lib().dso_oracle_make_images(color, w, h, levels, Bp, _ptr_array(dIp), _ptr_array(ab))
+    return dIp, ab
+
+
+class Tracker:
+    def __init__(self, w, h, levels, fx, fy, cx, cy):
+        self.L = lib()
+        self.w, self.h, self.levels = w, h, levels
+        self.p = self.L.dso_oracle_tracker_create(w, h, levels, fx, fy, cx, cy)
+        self._keep = []
+
+    def __del__(self):
+        if getattr(self, "p", None):
+            self.L.dso_oracle_tracker_destroy(self.p)
+            self.p = None
+
+    def get_K(self, lvl):
+        v = [C.c_float() for _ in range(4)]
+        Ki = np.zeros(9, dtype=np.float32)
+        self.L.dso_oracle_tracker_get_K(self.p, lvl, *[C.byref(x) for x in v], Ki.ctypes.data)
+        return [x.value for x in v], Ki
+
+    def set_ref(self, cu, cv, cid, hdi, ref_dIp, ref_a, ref_b, ref_exposure):
+        self._ref = [np.ascontiguousarray(x, dtype=np.float32) for x in ref_dIp]
+        self.L.dso_oracle_tracker_set_ref(self.p, len(cu), cu, cv, cid, hdi, _ptr_array(self._ref), ref_a, ref_b, ref_exposure)
+
+    def set_cloud(self, lvl, u, v, idepth, color):
+        self.L.dso_oracle_tracker_set_cloud(self.p, lvl, len(u), u, v, idepth, color)
+
+    def set_ref_aff(self, a, b, exposure):
+        self.L.dso_oracle_tracker_set_ref_aff(self.p, a, b, exposure)
+
+    def get_cloud(self, lvl):
+        n = self.L.dso_oracle_tracker_get_cloud(self.p, lvl, None, None, None, None)
+        arrs = [np.zeros(n, dtype=np.float32) for _ in range(4)]
+        self.L.dso_oracle_tracker_get_cloud(self.p, lvl, *[a.ctypes.data for a in arrs])
+        return arrs
+
+    def set_new_frame(self, dIp, exposure=1.0):
+        self._new = [np.ascontiguousarray(x, dtype=np.float32) for x in dIp]
+        self.L.dso_oracle_tracker_set_new_frame(self.p, _ptr_array(self._new), exposure)
+
+    def calc_res(self, lvl, pose12, a, b, cutoff):
+        out = np.zeros(6)
+        self.L.dso_oracle_calc_res(self.p, lvl, np.ascontiguousarray(pose12, dtype=np.float64), a, b, cutoff, out)
+        return out
+
+    def calc_gs(self, lvl, a, b):
+        H = np.zeros(64)
+        bb = np.zeros(8)
+        self.L.dso_oracle_calc_gs(self.p, lvl, a, b, H, bb)
+        return H.reshape(8, 8), bb
+
+    def get_warped(self):
+        bufs = [np.zeros(self.w * self.h + 8, dtype=np.float32) for _ in range(8)]
+        n = self.L.dso_oracle_get_warped(self.p, _ptr_array(bufs))
+        return n, [b[:n] for b in bufs]
+
+    def get_point_status(self, n):
+        s = np.zeros(self.w * self.h, dtype=np.uint8)
+        self.L.dso_oracle_get_point_status(self.p, s)
+        return s[:n]
+
+    def track(self, pose12, a, b, coarsest, min_res_for_abort=None):
+        if min_res_for_abort is None:
+            min_res_for_abort = np.full(5, np.nan)
+        res = TrackResult()
+        self.L.dso_oracle_track_newest_coarse(self.p, np.ascontiguousarray(pose12, dtype=np.float64), a, b, coarsest,
+                                              np.ascontiguousarray(min_res_for_abort, dtype=np.float64), C.byref(res))
+        return res
+
+
+class BA:
+    def __init__(self, W, dI_list):
+        """W: synthetic.Window; dI_list: per frame level-0 AoS image [h,w,3] float32."""
+        self.L = lib()
+        fx, fy, cx, cy = W.K
+        self.nF, self.nP, self.nR = W.nF, W.nP, W.nR
+        self.p = self.L.dso_oracle_ba_create(W.w, W.h, W.nF, fx, fy, cx, cy)
+        self._dI = [np.ascontiguousarray(x, dtype=np.float32) for x in dI_list]
+        for i in range(W.nF):
+            self.L.dso_oracle_ba_set_frame(self.p, i, np.ascontiguousarray(W.evalPT[i]), np.ascontiguousarray(W.state[i]),
+                                           np.ascontiguousarray(W.state_zero[i]), float(W.ab_exposure[i]),
+                                           float(W.frameEnergyTH[i]), self._dI[i].reshape(-1))
+        self.L.dso_oracle_ba_set_calib_delta(self.p, np.ascontiguousarray(W.calib_delta, dtype=np.float64))
+        self.L.dso_oracle_ba_prepare(self.p)
+        self.L.dso_oracle_ba_set_points(self.p, W.nP, W.u, W.v, W.idepth_scaled, W.idepth_zero_scaled,
+                                        W.color.reshape(-1), W.weights.reshape(-1), W.host, W.priorF, W.deltaF)
+        self.set_residuals(W)
+
+    def set_residuals(self, W):
+        self.L.dso_oracle_ba_set_residuals(self.p, W.nR, W.res_point, W.res_target, W.res_state, W.res_energy,
+                                           W.res_isLinearized, W.res_isActive)
+
+    def __del__(self):
+        if getattr(self, "p", None):
+            self.L.dso_oracle_ba_destroy(self.p)
+            self.p = None
+
+    def glue(self):
+        nF = self.nF
+        pre = np.zeros(nF * nF * 28, dtype=np.float32)
+        adH = np.zeros(nF * nF * 64)
+        adT = np.zeros(nF * nF * 64)
+        adHTd = np.zeros(nF * nF * 8, dtype=np.float32)
+        cD = np.zeros(4, dtype=np.float32)
+        self.L.dso_oracle_ba_get_glue(self.p, pre, adH, adT, adHTd, cD)
+        return dict(precalc=pre.reshape(nF * nF, 28), adHost=adH.reshape(nF * nF, 8, 8), adTarget=adT.reshape(nF * nF, 8, 8),
+                    adHTdeltaF=adHTd.reshape(nF * nF, 8), cDeltaF=cD)
+
+    def linearize(self):
+        nR = self.nR
+        out = dict(newState=np.zeros(nR, dtype=np.int32), newEnergy=np.zeros(nR, dtype=np.float32),
+                   newEnergyWithOutlier=np.zeros(nR, dtype=np.float32), centerProjectedTo=np.zeros(nR * 3, dtype=np.float32),
+                   projectedTo=np.zeros(nR * 16, dtype=np.float32), J=np.zeros(nR * 74, dtype=np.float32),
+                   energy=np.zeros(nR, dtype=np.float64))
+        out["total"] = self.L.dso_oracle_ba_linearize(self.p, out["newState"], out["newEnergy"], out["newEnergyWithOutlier"],
+                                                      out["centerProjectedTo"], out["projectedTo"], out["J"], out["energy"])
+        out["J"] = out["J"].reshape(nR, 74)
+        out["centerProjectedTo"] = out["centerProjectedTo"].reshape(nR, 3)
+        out["projectedTo"] = out["projectedTo"].reshape(nR, 8, 2)
+        return out
+
+    def linearize_mt(self, nthreads):
+        return self.L.dso_oracle_ba_linearize_mt(self.p, nthreads)
+
+    def apply_res(self):
+        act = np.zeros(self.nR, dtype=np.uint8)
+        jp = np.zeros(self.nR * 8, dtype=np.float32)
+        self.L.dso_oracle_ba_apply_res(self.p, act, jp)
+        return act, jp.reshape(self.nR, 8)
+
+    def accumulate_A(self, MT=False, nthreads=6):
+        N = 8 * self.nF + 4
+        H = np.zeros(N * N)
+        b = np.zeros(N)
+        n = C.c_int(0)
+        Hdd = np.zeros(self.nP, dtype=np.float32)
+        bd = np.zeros(self.nP, dtype=np.float32)
+        Hcd = np.zeros(self.nP * 4, dtype=np.float32)
+        self.L.dso_oracle_ba_accumulate_A(self.p, int(MT), nthreads, H, b, C.byref(n), Hdd, bd, Hcd)
+        return dict(H=H.reshape(N, N), b=b, resInA=n.value, Hdd=Hdd, bd=bd, Hcd=Hcd.reshape(self.nP, 4))
+
+    def accumulate_SC(self, MT=False, nthreads=6):
+        N = 8 * self.nF + 4
+        H = np.zeros(N * N)
+        b = np.zeros(N)
+        HdiF = np.zeros(self.nP, dtype=np.float32)
+        bdSumF = np.zeros(self.nP, dtype=np.float32)
+        ih = np.zeros(self.nP, dtype=np.float32)
+        self.L.dso_oracle_ba_accumulate_SC(self.p, int(MT), nthreads, H, b, HdiF, bdSumF, ih)
+        return dict(H=H.reshape(N, N), b=b, HdiF=HdiF, bdSumF=bdSumF, idepth_hessian=ih)
