@@ -103,7 +103,9 @@ __device__ __forceinline__ void grad_px(float c, float l, float r, float u, floa
 	if (Blut)
 	{
 		// CalibHessian::getBGradOnly, HessianBlocks.h:402-410
-		int ci = (int)fadd(c, 0.5f);
+		// int c = color + 0.5f; a non-finite / out-of-range value converts to INT_MIN on x86 (cvttss2si), i.e. clamps to 5
+		const float cf = fadd(c, 0.5f);
+		int ci = (cf >= -2147483648.f && cf < 2147483648.f) ? (int)cf : 5;
 		ci = ci < 5 ? 5 : (ci > 250 ? 250 : ci);
 		float gw = fsub(__ldg(Blut + ci + 1), __ldg(Blut + ci));
 		ab = fmul(ab, fmul(gw, gw));   // :207
