@@ -62,6 +62,11 @@ SIGNATURES = {
     "dso_b200_track_opts_default": (None, [C.POINTER(TrackOpts)]),
     "dso_b200_track_batched": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, f64p, C.c_double, C.c_double, C.c_float, C.c_int,
                                          C.POINTER(TrackOpts), C.POINTER(TrackResult)]),
+    "dso_b200_track_batched_async": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, f64p, C.c_double, C.c_double, C.c_float, C.c_int,
+                                               C.POINTER(TrackOpts)]),
+    "dso_b200_track_fetch": (C.c_int, [vp, C.c_int, C.c_int, C.POINTER(TrackResult)]),
+    "dso_b200_track_frame": (C.c_int, [vp, C.c_int, C.c_int, vp, C.c_int, C.c_int, C.c_int, C.c_int, f64p, C.c_double, C.c_double,
+                                       C.c_float, C.c_int, C.POINTER(TrackOpts), C.POINTER(TrackResult)]),
     "dso_b200_track_replay_abort": (C.c_int, [C.POINTER(TrackResult), f64p, f64p]),
     "dso_b200_track_hostloop": (C.c_int, [vp, C.c_int, C.c_int, f64p, C.c_double, C.c_double, C.c_float, C.c_int, vp,
                                           C.POINTER(TrackOpts), C.POINTER(TrackResult)]),
@@ -218,6 +223,36 @@ class Context:
         res = (TrackResult * n)()
         self._check(self.L.dso_b200_track_batched(self.h, trk, slot, n, poses12.reshape(-1), a, b, new_exposure, coarsest,
                                                   None if opts is None else C.byref(opts), res))
+        return list(res)
+
+    def track_kernel_only(self, trk, slot, n_hyp, coarsest, new_exposure=1.0):
+        f = self.L.dso_b200_track_batched_async
+        old = f.argtypes
+        f.argtypes = old[:4] + [vp] + old[5:]
+        try:
+            self._check(f(self.h, trk, slot, n_hyp, None, 0.0, 0.0, new_exposure, coarsest, None))
+        finally:
+            f.argtypes = old
+
+    def track_batched_async(self, trk, slot, poses12, a, b, coarsest, new_exposure=1.0, opts=None):
+        poses12 = np.ascontiguousarray(poses12, dtype=np.float64).reshape(-1, 12)
+        self._check(self.L.dso_b200_track_batched_async(self.h, trk, slot, poses12.shape[0], poses12.reshape(-1), a, b,
+                                                        new_exposure, coarsest, None if opts is None else C.byref(opts)))
+
+    def track_fetch(self, trk, n=1):
+        res = (TrackResult * n)()
+        self._check(self.L.dso_b200_track_fetch(self.h, trk, n, res))
+        return list(res)
+
+    def track_frame(self, trk, slot, color_ptr, w, h, levels, poses12, a, b, coarsest, new_exposure=1.0, opts=None):
+        """color_ptr: host address of w*h floats (numpy array or pinned pointer)"""
+        if isinstance(color_ptr, np.ndarray):
+            color_ptr = color_ptr.ctypes.data
+        poses12 = np.ascontiguousarray(poses12, dtype=np.float64).reshape(-1, 12)
+        n = poses12.shape[0]
+        res = (TrackResult * n)()
+        self._check(self.L.dso_b200_track_frame(self.h, trk, slot, color_ptr, w, h, levels, n, poses12.reshape(-1), a, b,
+                                                new_exposure, coarsest, None if opts is None else C.byref(opts), res))
         return list(res)
 
     def replay_abort(self, res, min_res):

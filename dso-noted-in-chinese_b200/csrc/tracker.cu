@@ -767,9 +767,11 @@ extern "C" int dso_b200_track_replay_abort(const dso_b200_track_result* r, const
 	return ok;
 }
 
-extern "C" int dso_b200_track_batched(dso_b200_ctx* ctx, int trk, int frame_slot, int nHyp, const double* pose12_init,
-                                      double aff_a_init, double aff_b_init, float new_ab_exposure, int coarsestLvl,
-                                      const dso_b200_track_opts* opts, dso_b200_track_result* out)
+// Enqueue (no synchronisation): upload of the initial poses, the persistent kernel, download of the
+// results into the slot's pinned buffer.
+static int enqueue_track(dso_b200_ctx* ctx, int trk, int frame_slot, int nHyp, const double* pose12_init,
+                         double aff_a_init, double aff_b_init, float new_ab_exposure, int coarsestLvl,
+                         const dso_b200_track_opts* opts)
 {
 	int rc = check_eval_args(ctx, trk, frame_slot, coarsestLvl);
 	if (rc) return rc;
@@ -779,14 +781,19 @@ extern "C" int dso_b200_track_batched(dso_b200_ctx* ctx, int trk, int frame_slot
 	TrackerSlot& T = ctx->trk[trk];
 	dso_b200_track_opts o;
 	if (opts) o = *opts; else dso_b200_track_opts_default(&o);
-	TrackIn* hin = (TrackIn*)T.h_track_in;
-	for (int i = 0; i < nHyp; i++)
+	// pageable staging: cudaMemcpyAsync returns once the source has been copied to the driver's staging
+	// area, so back-to-back asynchronous calls may reuse it
+	TrackIn hin[DSO_B200_MAX_HYP];
+	if (pose12_init)
 	{
-		memcpy(hin[i].pose, pose12_init + 12 * i, 96);
-		hin[i].aff_a = aff_a_init; hin[i].aff_b = aff_b_init;
-		for (int k = 0; k < 5; k++) hin[i].minRes[k] = NAN;
+		for (int i = 0; i < nHyp; i++)
+		{
+			memcpy(hin[i].pose, pose12_init + 12 * i, 96);
+			hin[i].aff_a = aff_a_init; hin[i].aff_b = aff_b_init;
+			for (int k = 0; k < 5; k++) hin[i].minRes[k] = NAN;
+		}
+		CK(cudaMemcpyAsync(T.d_track_in, hin, sizeof(TrackIn) * nHyp, cudaMemcpyHostToDevice, ctx->stream));
 	}
-	CK(cudaMemcpyAsync(T.d_track_in, hin, sizeof(TrackIn) * nHyp, cudaMemcpyHostToDevice, ctx->stream));
 	TrackLevels TL;
 	fill_levels(ctx, T, &ctx->slots[frame_slot], new_ab_exposure, TL);
 
@@ -799,14 +806,13 @@ extern "C" int dso_b200_track_batched(dso_b200_ctx* ctx, int trk, int frame_slot
 	size_t smem_cap_bytes = 160 * 1024;
 	int cap = (int)std::min<size_t>((size_t)per, smem_cap_bytes / sizeof(float4));
 	size_t dyn = (size_t)cap * sizeof(float4);
-	static bool attr_set = false;
-	if (!attr_set)
+	static bool attr_set[64] = { false };
+	if (!attr_set[ctx->device & 63])
 	{
 		CK(cudaFuncSetAttribute(track_persistent_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_cap_bytes));
-		attr_set = true;
+		attr_set[ctx->device & 63] = true;
 	}
-	cudaLaunchConfig_t cfg;
-	memset(&cfg, 0, sizeof(cfg));
+	cudaLaunchConfig_t cfg = {};
 	cfg.gridDim = dim3(nHyp * cs, 1, 1);
 	cfg.blockDim = dim3(PERS_THREADS, 1, 1);
 	cfg.dynamicSmemBytes = dyn;
@@ -818,8 +824,47 @@ extern "C" int dso_b200_track_batched(dso_b200_ctx* ctx, int trk, int frame_slot
 	CK(cudaLaunchKernelEx(&cfg, track_persistent_kernel, TL, o, (const TrackIn*)T.d_track_in,
 	                      (dso_b200_track_result*)T.d_track_out, coarsestLvl, cap));
 	ctx->launches++;
-	CK(cudaMemcpyAsync(T.h_track_out, T.d_track_out, sizeof(dso_b200_track_result) * nHyp, cudaMemcpyDeviceToHost, ctx->stream));
-	CK(cudaStreamSynchronize(ctx->stream));
-	memcpy(out, T.h_track_out, sizeof(dso_b200_track_result) * nHyp);
+	if (pose12_init)
+		CK(cudaMemcpyAsync(T.h_track_out, T.d_track_out, sizeof(dso_b200_track_result) * nHyp, cudaMemcpyDeviceToHost, ctx->stream));
 	return 0;
+}
+
+extern "C" int dso_b200_track_batched_async(dso_b200_ctx* ctx, int trk, int frame_slot, int nHyp, const double* pose12_init,
+                                            double aff_a_init, double aff_b_init, float new_ab_exposure, int coarsestLvl,
+                                            const dso_b200_track_opts* opts)
+{
+	return enqueue_track(ctx, trk, frame_slot, nHyp, pose12_init, aff_a_init, aff_b_init, new_ab_exposure, coarsestLvl, opts);
+}
+
+extern "C" int dso_b200_track_fetch(dso_b200_ctx* ctx, int trk, int nHyp, dso_b200_track_result* out)
+{
+	ARG_CHECK(ctx && (trk == 0 || trk == 1) && out && nHyp >= 1 && nHyp <= DSO_B200_MAX_HYP, "bad arguments");
+	CK(cudaStreamSynchronize(ctx->stream));
+	memcpy(out, ctx->trk[trk].h_track_out, sizeof(dso_b200_track_result) * nHyp);
+	return 0;
+}
+
+extern "C" int dso_b200_track_batched(dso_b200_ctx* ctx, int trk, int frame_slot, int nHyp, const double* pose12_init,
+                                      double aff_a_init, double aff_b_init, float new_ab_exposure, int coarsestLvl,
+                                      const dso_b200_track_opts* opts, dso_b200_track_result* out)
+{
+	int rc = enqueue_track(ctx, trk, frame_slot, nHyp, pose12_init, aff_a_init, aff_b_init, new_ab_exposure, coarsestLvl, opts);
+	if (rc) return rc;
+	return dso_b200_track_fetch(ctx, trk, nHyp, out);
+}
+
+extern "C" int dso_b200_track_frame(dso_b200_ctx* ctx, int trk, int frame_slot, const float* color_host, int w, int h,
+                                    int levels, int nHyp, const double* pose12_init, double aff_a_init, double aff_b_init,
+                                    float new_ab_exposure, int coarsestLvl, const dso_b200_track_opts* opts,
+                                    dso_b200_track_result* out)
+{
+	ARG_CHECK(ctx && color_host && frame_slot >= 0 && frame_slot < ctx->n_slots, "bad arguments");
+	ARG_CHECK(w >= 16 && h >= 16 && w <= ctx->max_w && h <= ctx->max_h && levels >= 1 && levels <= MAXL, "bad image size / levels");
+	CK(cudaSetDevice(ctx->device));
+	CK(cudaMemcpyAsync(ctx->d_color, color_host, (size_t)w * h * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+	int rc = pyramid_build(ctx, ctx->slots[frame_slot], ctx->d_color, w, h, levels, nullptr, false);
+	if (rc) return rc;
+	rc = enqueue_track(ctx, trk, frame_slot, nHyp, pose12_init, aff_a_init, aff_b_init, new_ab_exposure, coarsestLvl, opts);
+	if (rc) return rc;
+	return dso_b200_track_fetch(ctx, trk, nHyp, out);
 }

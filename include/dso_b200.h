@@ -125,6 +125,21 @@ typedef struct
 int dso_b200_track_batched(dso_b200_ctx* ctx, int trk, int frame_slot, int nHyp, const double* pose12_init,
                            double aff_a_init, double aff_b_init, float new_ab_exposure, int coarsestLvl,
                            const dso_b200_track_opts* opts, dso_b200_track_result* out);
+/* Asynchronous form of dso_b200_track_batched: enqueues the work on the context's stream and returns;
+ * dso_b200_track_fetch waits for the stream and copies out the results of the most recent call on trk.
+ * With pose12_init == NULL only the kernel is enqueued: it re-uses the initial poses uploaded by the
+ * previous call and leaves its results on the device (used to time the kernel alone). */
+int dso_b200_track_batched_async(dso_b200_ctx* ctx, int trk, int frame_slot, int nHyp, const double* pose12_init,
+                                 double aff_a_init, double aff_b_init, float new_ab_exposure, int coarsestLvl,
+                                 const dso_b200_track_opts* opts);
+int dso_b200_track_fetch(dso_b200_ctx* ctx, int trk, int nHyp, dso_b200_track_result* out);
+/* One frame end to end -- what FullSystem::addActiveFrame does per frame (FullSystem.cpp:860 makeImages,
+ * :905 trackNewCoarse -> :387 trackNewestCoarse): upload of the image from host memory, pyramid into
+ * frame_slot, nHyp hypotheses, download of the results; one synchronisation at the end. */
+int dso_b200_track_frame(dso_b200_ctx* ctx, int trk, int frame_slot, const float* color_host, int w, int h,
+                         int levels, int nHyp, const double* pose12_init, double aff_a_init, double aff_b_init,
+                         float new_ab_exposure, int coarsestLvl, const dso_b200_track_opts* opts,
+                         dso_b200_track_result* out);
 /* Applies CoarseTracker.cpp:713 to a finished result: returns 1 if trackNewestCoarse would have
  * returned true for this minResForAbort, 0 if it would have aborted (lastResiduals5_out then holds
  * what CoarseTracker::lastResiduals would contain at the abort). */

@@ -85,12 +85,16 @@ def _ptr_array(arrs):
     return a
 
 
-def make_images(color, levels, B=None):
-    """Returns (dIp list of [h_l, w_l, 3] float32, absgrad list of [h_l, w_l] float32); untouched elements are 0."""
+def make_images(color, levels, B=None, out=None):
+    """Returns (dIp list of [h_l, w_l, 3] float32, absgrad list of [h_l, w_l] float32); untouched elements are 0.
+    out: a previous return value to overwrite (skips the allocation, as the reference's new[] does not zero)."""
     h, w = color.shape
     color = np.ascontiguousarray(color, dtype=np.float32)
-    dIp = [np.zeros((h >> l, w >> l, 3), dtype=np.float32) for l in range(levels)]
-    ab = [np.zeros((h >> l, w >> l), dtype=np.float32) for l in range(levels)]
+    if out is not None:
+        dIp, ab = out
+    else:
+        dIp = [np.zeros((h >> l, w >> l, 3), dtype=np.float32) for l in range(levels)]
+        ab = [np.zeros((h >> l, w >> l), dtype=np.float32) for l in range(levels)]
     Bp = None
     if B is not None:
         B = np.ascontiguousarray(B, dtype=np.float32)
