@@ -456,6 +456,307 @@ struct TrackIn
 	double minRes[5];
 };
 
+// LM state of one hypothesis, in shared memory.  The serial dependency chain of trackNewestCoarse
+// (solve -> exp -> warp -> reduce -> accept?) is the latency floor of this kernel, so the step between
+// two evaluations is executed by one warp with lane-parallel sections instead of one thread.
+struct LMS
+{
+	double H[64], b[8], Hn[64], bn[8];
+	double curR[9], curT[3], nwR[9], nwT[3], eR[9], eT[3];
+	double a_cur, b_cur, a_new, b_new;
+	double resOldE, resOldN, resOldFlowT, resOldFlowRT;
+	double newE, newN, newFlowT, newFlowRT, newSat;
+	double incnorm;
+	double minRes[5];
+	float lambda, levelCutoffRepeat;
+	int lvl, iteration, phase, haveRepeated, done;
+	int req_new;       // 1: the next evaluation uses (nwR,nwT,a_new,b_new), 0: the current state
+};
+
+__device__ __forceinline__ double shfl_d(double v, int src) { return __shfl_sync(0xffffffffu, v, src); }
+// reciprocal to ~1e-15 relative: float seed + two Newton steps (no IEEE division on the critical path)
+__device__ __forceinline__ double fast_rcp(double x)
+{
+	double r = (double)__frcp_rn((float)x);
+	r = r * fma(-x, r, 2.0);
+	r = r * fma(-x, r, 2.0);
+	return r;
+}
+
+// accept the latest evaluation as the new linearisation point (CoarseTracker.cpp:595 / :687-688)
+__device__ __forceinline__ void lm_take_new(LMS& S, int lane)
+{
+	for (int i = lane; i < 64; i += 32) S.H[i] = S.Hn[i];
+	if (lane < 8) S.b[lane] = S.bn[lane];
+	if (lane == 0) { S.resOldE = S.newE; S.resOldN = S.newN; S.resOldFlowT = S.newFlowT; S.resOldFlowRT = S.newFlowRT; }
+	__syncwarp();
+}
+
+// :613-665: damped solve (warp-parallel elimination, one lane per row; H + lambda*diag is SPD so no
+// pivoting is needed -- Eigen's pivoted LDLT gives the same solution up to rounding), SE3 update
+__device__ __forceinline__ void lm_propose(LMS& S, int lane)
+{
+	const int i = lane & 7;
+	const double damp = (double)(1.f + S.lambda);
+	double row[8], rp[8], x[8];
+#pragma unroll
+	for (int j = 0; j < 8; j++) row[j] = S.H[i * 8 + j] * ((j == i) ? damp : 1.0);
+	double rhs = -S.b[i];
+#pragma unroll
+	for (int k = 0; k < 8; k++)
+	{
+		const double piv = shfl_d(row[k], k);
+		rp[k] = fast_rcp(piv);
+		const double f = row[k] * rp[k];
+		const double prhs = shfl_d(rhs, k);
+		const bool act = i > k;
+#pragma unroll
+		for (int j = k + 1; j < 8; j++)
+		{
+			const double pj = shfl_d(row[j], k);
+			if (act) row[j] = fma(-f, pj, row[j]);
+		}
+		if (act) rhs = fma(-f, prhs, rhs);
+	}
+#pragma unroll
+	for (int k = 7; k >= 0; k--)
+	{
+		const double xk = shfl_d(rhs, k) * rp[k];
+		x[k] = xk;
+		if (i < k) rhs = fma(-row[k], xk, rhs);
+	}
+	// every lane now holds the full increment: the rest is uniform scalar work
+	float extrapFac = 1.f;
+	if (S.lambda < 0.001f) extrapFac = sqrtf(sqrtf(0.001f / S.lambda));   // :650
+	double nrm = 0, sum = 0, is[8];
+#pragma unroll
+	for (int k = 0; k < 8; k++) { x[k] *= (double)extrapFac; nrm = fma(x[k], x[k], nrm); }
+	const double scl[8] = { SCALE_XI_ROT, SCALE_XI_ROT, SCALE_XI_ROT, SCALE_XI_TRANS, SCALE_XI_TRANS, SCALE_XI_TRANS, SCALE_A, SCALE_B };
+#pragma unroll
+	for (int k = 0; k < 8; k++) { is[k] = x[k] * scl[k]; sum += is[k]; }
+	if (!isfinite(sum))                                                    // :659
+	{
+#pragma unroll
+		for (int k = 0; k < 8; k++) is[k] = 0;
+	}
+	Pose e;
+	se3_exp(is, e);
+	// uniform values in every lane: lane l stores entry l (static register indexing only)
+#pragma unroll
+	for (int k = 0; k < 9; k++) if (lane == k) S.eR[k] = e.R[k];
+#pragma unroll
+	for (int k = 0; k < 3; k++) if (lane == 9 + k) S.eT[k] = e.t[k];
+	if (lane == 0)
+	{
+		S.incnorm = sqrt(nrm);
+		S.a_new = S.a_cur + is[6];
+		S.b_new = S.b_cur + is[7];
+		S.req_new = 1;
+	}
+	__syncwarp();
+	// refToNew_new = exp(inc) * refToNew_current (:661), lane-parallel
+	if (lane < 9)
+	{
+		const int r = lane / 3, c = lane - 3 * r;
+		S.nwR[lane] = S.eR[r * 3 + 0] * S.curR[c] + S.eR[r * 3 + 1] * S.curR[3 + c] + S.eR[r * 3 + 2] * S.curR[6 + c];
+	}
+	else if (lane < 12)
+	{
+		const int r = lane - 9;
+		S.nwT[r] = S.eR[r * 3 + 0] * S.curT[0] + S.eR[r * 3 + 1] * S.curT[1] + S.eR[r * 3 + 2] * S.curT[2] + S.eT[r];
+	}
+	__syncwarp();
+}
+
+// CoarseTracker.cpp:375-378 for the requested state, lane-parallel (same arithmetic as make_eval_params)
+__device__ __forceinline__ void lm_build_params(const LMS& S, const TrackLevels& TL, const dso_b200_track_opts& opt,
+                                                EvalParams& P, int lane)
+{
+	const int lvl = S.lvl;
+	const double* R = S.req_new ? S.nwR : S.curR;
+	const double* T = S.req_new ? S.nwT : S.curT;
+	if (lane < 9)
+	{
+		const int r = lane / 3, c = lane - 3 * r;
+		P.RKi[lane] = dot3e((float)R[r * 3 + 0], TL.Ki[lvl][c], (float)R[r * 3 + 1], TL.Ki[lvl][3 + c], (float)R[r * 3 + 2], TL.Ki[lvl][6 + c]);
+		P.Ki[lane] = TL.Ki[lvl][lane];
+	}
+	else if (lane < 12) P.t[lane - 9] = (float)T[lane - 9];
+	else if (lane == 12)
+	{
+		double a, b;
+		aff_from_to(TL.ref_exposure, TL.new_exposure, TL.ref_a, TL.ref_b, S.req_new ? S.a_new : S.a_cur, S.req_new ? S.b_new : S.b_cur, a, b);
+		P.affLL0 = (float)a; P.affLL1 = (float)b;
+	}
+	else if (lane == 13)
+	{
+		const float cutoff = opt.coarseCutoffTH * S.levelCutoffRepeat;
+		P.fx = TL.fx[lvl]; P.fy = TL.fy[lvl]; P.cx = TL.cx[lvl]; P.cy = TL.cy[lvl];
+		P.wl = TL.w[lvl];
+		P.wl_m3 = (float)(TL.w[lvl] - 3); P.hl_m3 = (float)(TL.h[lvl] - 3);
+		P.n = TL.pc_n[lvl];
+		P.lvl0 = (lvl == 0);
+		P.cutoffTH = cutoff;
+		P.huberTH = opt.huberTH;
+		P.maxEnergy = fsub(fmul(fmul(2.0f, opt.huberTH), cutoff), fmul(opt.huberTH, opt.huberTH));
+		P.b0 = (float)TL.ref_b;
+	}
+	__syncwarp();
+}
+
+// :708-722 + :727-746
+__device__ __forceinline__ void lm_finish_level(LMS& S, const TrackLevels& TL, const dso_b200_track_opts& opt,
+                                                dso_b200_track_result* out, int lane)
+{
+	if (lane == 0)
+	{
+		const int lvl = S.lvl;
+		const float rmse = sqrtf((float)(S.resOldE / S.resOldN));          // :710
+		out->lastResiduals[lvl] = rmse;
+		out->lastFlowIndicators[0] = S.resOldFlowT; out->lastFlowIndicators[1] = 0; out->lastFlowIndicators[2] = S.resOldFlowRT;
+		if (out->n_passes < DSO_B200_MAX_PASSES) { out->pass_level[out->n_passes] = lvl; out->pass_rmse[out->n_passes] = rmse; out->n_passes++; }
+		if ((double)rmse > 1.5 * S.minRes[lvl]) { S.done = 1; out->ok = 0; out->reserved = lvl; }   // :713
+		else
+		{
+			int next = lvl - 1;
+			if (S.levelCutoffRepeat > 1 && !S.haveRepeated) { next = lvl; S.haveRepeated = 1; }   // :717-722
+			if (next < 0)
+			{
+				S.done = 1;
+				for (int i = 0; i < 9; i++) out->pose[i] = S.curR[i];
+				for (int i = 0; i < 3; i++) out->pose[9 + i] = S.curT[i];
+				out->aff_a = S.a_cur; out->aff_b = S.b_cur;
+				out->ok = 1;
+				if ((opt.affineOptModeA != 0 && (fabsf((float)S.a_cur) > 1.2f)) || (opt.affineOptModeB != 0 && (fabsf((float)S.b_cur) > 200.f)))
+					out->ok = 0;
+				else
+				{
+					double ra, rb;
+					aff_from_to(TL.ref_exposure, TL.new_exposure, TL.ref_a, TL.ref_b, S.a_cur, S.b_cur, ra, rb);
+					if ((opt.affineOptModeA == 0 && (fabsf(logf((float)ra)) > 1.5f)) || (opt.affineOptModeB == 0 && (fabsf((float)rb) > 200.f)))
+						out->ok = 0;
+				}
+			}
+			else
+			{
+				S.lvl = next; S.phase = 0; S.levelCutoffRepeat = 1; S.iteration = 0; S.req_new = 0;   // :584
+			}
+		}
+	}
+	__syncwarp();
+}
+
+// One step of the trackNewestCoarse state machine, executed by warp 0 of every CTA of the cluster
+// (identical inputs -> identical decisions, so no broadcast is needed).
+__device__ __forceinline__ void lm_step_warp(LMS& S, const float* s_tot, const TrackLevels& TL, const dso_b200_track_opts& opt,
+                                             dso_b200_track_result* out, EvalParams& P, int n_points, int lane)
+{
+	// sums -> Vec6 + scaled H, b (sums_to_result, lane-parallel)
+	{
+		const int nw = (int)s_tot[S_NWARP];
+		const int npad = (nw + 3) & ~3;
+		const float invn = fdiv(1.0f, (float)npad);
+		for (int idx = lane; idx < 44; idx += 32)
+		{
+			if (idx < 36)
+			{
+				int i = 0, rem = idx;
+				while (rem >= 8 - i) { rem -= 8 - i; i++; }
+				const int j = i + rem;
+				const float si = i < 3 ? SCALE_XI_ROT : (i < 6 ? SCALE_XI_TRANS : (i == 6 ? SCALE_A : SCALE_B));
+				const float sj = j < 3 ? SCALE_XI_ROT : (j < 6 ? SCALE_XI_TRANS : (j == 6 ? SCALE_A : SCALE_B));
+				double v = (double)s_tot[S_ACC + idx] * (double)invn;
+				v *= (double)sj;
+				v *= (double)si;
+				S.Hn[i * 8 + j] = v; S.Hn[j * 8 + i] = v;
+			}
+			else
+			{
+				const int i = idx - 36;
+				const float si = i < 3 ? SCALE_XI_ROT : (i < 6 ? SCALE_XI_TRANS : (i == 6 ? SCALE_A : SCALE_B));
+				S.bn[i] = (double)s_tot[S_ACC + idx] * (double)invn * (double)si;
+			}
+		}
+		if (lane == 0)
+		{
+			S.newE = (double)s_tot[S_E];
+			S.newN = (double)s_tot[S_NTERMS];
+			S.newFlowT = (double)s_tot[S_FLOW_T] / ((double)s_tot[S_FLOW_N] + 0.1);
+			S.newFlowRT = (double)s_tot[S_FLOW_RT] / ((double)s_tot[S_FLOW_N] + 0.1);
+			S.newSat = (double)fdiv(s_tot[S_NSAT], s_tot[S_NTERMS]);
+			out->n_evals++; out->point_evals += n_points;
+		}
+		__syncwarp();
+	}
+	bool level_done = false;
+	if (S.phase == 0)
+	{
+		if (S.newSat > 0.6 && S.levelCutoffRepeat < 50)                        // :586-593
+		{
+			if (lane == 0) { S.levelCutoffRepeat *= 2; S.req_new = 0; }
+			__syncwarp();
+			lm_build_params(S, TL, opt, P, lane);
+			return;
+		}
+		lm_take_new(S, lane);
+		if (lane == 0) { S.lambda = 0.01f; S.iteration = 0; S.phase = 1; }
+		__syncwarp();
+		level_done = (S.iteration >= opt.maxIterations[S.lvl]);
+	}
+	else
+	{
+		const bool accept = (S.newE / S.newN) < (S.resOldE / S.resOldN);       // :669
+		if (lane == 0)
+		{
+			if (out->trace_len < 256) out->trace[out->trace_len++] = accept ? 1 : 0;
+			out->n_iterations++;
+		}
+		if (accept)
+		{
+			lm_take_new(S, lane);
+			if (lane < 9) S.curR[lane] = S.nwR[lane];
+			else if (lane < 12) S.curT[lane - 9] = S.nwT[lane - 9];
+			if (lane == 12) { S.a_cur = S.a_new; S.b_cur = S.b_new; S.lambda *= 0.5f; }
+		}
+		else if (lane == 0)
+		{
+			float l = S.lambda * 4;
+			if (l < 0.001f) l = 0.001f;
+			S.lambda = l;
+		}
+		if (lane == 1) S.iteration++;
+		__syncwarp();
+		level_done = (!(S.incnorm > 1e-3) || S.iteration >= opt.maxIterations[S.lvl]);   // :700, :613
+	}
+	if (level_done)
+	{
+		lm_finish_level(S, TL, opt, out, lane);
+		if (S.done) return;
+		lm_build_params(S, TL, opt, P, lane);
+		return;
+	}
+	lm_propose(S, lane);
+	lm_build_params(S, TL, opt, P, lane);
+}
+
+// Fixed-tree warp reduction of S_COUNT (<= 64) values with recursive halving: 62 shuffles instead of
+// 5 per value.  On return lane l holds the warp sums of entries 2l and 2l+1 in v[0], v[1].
+__device__ __forceinline__ void warp_reduce_halving(float* v, int lane)
+{
+#pragma unroll
+	for (int m = 64, o = 16; o >= 1; m >>= 1, o >>= 1)
+	{
+		const bool hi = (lane & o) != 0;
+#pragma unroll
+		for (int j = 0; j < m / 2; j++)
+		{
+			const float send = hi ? v[j] : v[j + m / 2];
+			const float keep = hi ? v[j + m / 2] : v[j];
+			v[j] = keep + __shfl_xor_sync(0xffffffffu, send, o);
+		}
+	}
+}
+
 __global__ void __launch_bounds__(PERS_THREADS, 1)
 track_persistent_kernel(TrackLevels TL, dso_b200_track_opts opt, const TrackIn* __restrict__ in,
                         dso_b200_track_result* out, int coarsestLvl, int smem_pts_cap)
@@ -464,30 +765,43 @@ track_persistent_kernel(TrackLevels TL, dso_b200_track_opts opt, const TrackIn* 
 	const unsigned CS = cluster.num_blocks();
 	const unsigned rank = cluster.block_rank();
 	const int hyp = blockIdx.x / CS;
-	const int tid = threadIdx.x;
+	const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
 	__shared__ EvalParams sP;
-	__shared__ int sDone, sLvl, sRestage;
-	__shared__ float s_w[PERS_THREADS / 32][S_COUNT];
-	__shared__ float s_part[S_COUNT];
+	__shared__ LMS S;
+	__shared__ float s_w[PERS_THREADS / 32][64];
 	__shared__ float xchg[2][MAX_CLUSTER][S_COUNT];
 	__shared__ float s_tot[S_COUNT];
 	__shared__ dso_b200_track_result s_res;
 	extern __shared__ float4 s_pts[];
 
-	LM lm;   // meaningful in thread 0 only; every CTA of the cluster runs the identical sequence
-	if (tid == 0)
+	if (warp == 0)
 	{
-		lm.init(opt, TL, in[hyp].pose, in[hyp].aff_a, in[hyp].aff_b, coarsestLvl, in[hyp].minRes, &s_res);
-		make_eval_params(TL, lm.req_lvl, lm.req_pose, lm.req_a, lm.req_b, lm.req_cutoff, opt.huberTH, sP);
-		sDone = 0; sLvl = lm.req_lvl; sRestage = 1;
+		if (lane == 0)
+		{
+			const TrackIn& I = in[hyp];
+			for (int i = 0; i < 9; i++) S.curR[i] = I.pose[i];
+			for (int i = 0; i < 3; i++) S.curT[i] = I.pose[9 + i];
+			S.a_cur = I.aff_a; S.b_cur = I.aff_b;
+			for (int i = 0; i < 5; i++) S.minRes[i] = I.minRes[i];
+			S.haveRepeated = 0; S.done = 0; S.incnorm = 0; S.lambda = 0.01f;
+			S.lvl = coarsestLvl; S.phase = 0; S.levelCutoffRepeat = 1; S.iteration = 0; S.req_new = 0;
+			s_res.ok = 0; s_res.reserved = -1;
+			for (int i = 0; i < 12; i++) s_res.pose[i] = I.pose[i];
+			s_res.aff_a = I.aff_a; s_res.aff_b = I.aff_b;
+			for (int i = 0; i < 5; i++) s_res.lastResiduals[i] = NAN;        // :563
+			for (int i = 0; i < 3; i++) s_res.lastFlowIndicators[i] = 1000;  // :564
+			s_res.n_passes = 0; s_res.n_iterations = 0; s_res.n_evals = 0; s_res.trace_len = 0; s_res.point_evals = 0;
+		}
+		__syncwarp();
+		lm_build_params(S, TL, opt, sP, lane);
 	}
 	__syncthreads();
 	int buf = 0;
 	int staged_lvl = -1;
 	while (true)
 	{
-		const int lvl = sLvl;
+		const int lvl = S.lvl;
 		const int n = TL.pc_n[lvl];
 		const int per = (n + CS - 1) / CS;
 		const int beg = min((int)rank * per, n), end = min(beg + per, n);
@@ -501,20 +815,24 @@ track_persistent_kernel(TrackLevels TL, dso_b200_track_opts opt, const TrackIn* 
 		}
 		const EvalParams P = sP;
 		const float4* __restrict__ img = TL.img[lvl];
-		float acc[S_COUNT];
+		float acc[64];
 #pragma unroll
-		for (int k = 0; k < S_COUNT; k++) acc[k] = 0.f;
+		for (int k = 0; k < 64; k++) acc[k] = 0.f;
 		if (use_smem)
 			for (int i = beg + tid; i < end; i += PERS_THREADS) eval_point<false>(s_pts[i - beg], i, P, img, acc, nullptr, nullptr);
 		else
 			for (int i = beg + tid; i < end; i += PERS_THREADS) eval_point<false>(__ldg(gp + i), i, P, img, acc, nullptr, nullptr);
-		block_reduce<PERS_THREADS / 32>(acc, s_w, s_part);
-		// push this CTA's partial into every CTA of the cluster (distributed shared memory)
-		for (unsigned idx = tid; idx < CS * S_COUNT; idx += PERS_THREADS)
+		warp_reduce_halving(acc, lane);
+		s_w[warp][2 * lane] = acc[0];
+		s_w[warp][2 * lane + 1] = acc[1];
+		__syncthreads();
+		// CTA partial (warps in index order), pushed into every CTA of the cluster through DSMEM
+		if (tid < S_COUNT)
 		{
-			unsigned r = idx / S_COUNT, k = idx - r * S_COUNT;
-			float* dst = cluster.map_shared_rank(&xchg[buf][rank][k], r);
-			*dst = s_part[k];
+			float s = 0.f;
+#pragma unroll
+			for (int w = 0; w < PERS_THREADS / 32; w++) s += s_w[w][tid];
+			for (unsigned r = 0; r < CS; r++) *cluster.map_shared_rank(&xchg[buf][rank][tid], r) = s;
 		}
 		cluster.sync();
 		if (tid < S_COUNT)
@@ -524,25 +842,13 @@ track_persistent_kernel(TrackLevels TL, dso_b200_track_opts opt, const TrackIn* 
 			s_tot[tid] = s;
 		}
 		__syncthreads();
-		if (tid == 0)
-		{
-			EvalResult er;
-			sums_to_result(s_tot, er);
-			lm.step(er, n);
-			if (lm.done) sDone = 1;
-			else
-			{
-				make_eval_params(TL, lm.req_lvl, lm.req_pose, lm.req_a, lm.req_b, lm.req_cutoff, opt.huberTH, sP);
-				sLvl = lm.req_lvl;
-			}
-		}
+		if (warp == 0) lm_step_warp(S, s_tot, TL, opt, &s_res, sP, n, lane);
 		__syncthreads();
-		if (sDone) break;
+		if (S.done) break;
 		buf ^= 1;
 	}
 	if (rank == 0)
 	{
-		// copy the result struct out with all threads (plain words)
 		const int nwords = sizeof(dso_b200_track_result) / 4;
 		const unsigned int* src = reinterpret_cast<const unsigned int*>(&s_res);
 		unsigned int* dst = reinterpret_cast<unsigned int*>(out + hyp);
@@ -781,6 +1087,8 @@ static int enqueue_track(dso_b200_ctx* ctx, int trk, int frame_slot, int nHyp, c
 	TrackerSlot& T = ctx->trk[trk];
 	dso_b200_track_opts o;
 	if (opts) o = *opts; else dso_b200_track_opts_default(&o);
+	ARG_CHECK(!(o.affineOptModeA < 0) && !(o.affineOptModeB < 0),
+	          "fixed-affine modes (CoarseTracker.cpp:621-643) are only implemented in dso_b200_track_hostloop");
 	// pageable staging: cudaMemcpyAsync returns once the source has been copied to the driver's staging
 	// area, so back-to-back asynchronous calls may reuse it
 	TrackIn hin[DSO_B200_MAX_HYP];
