@@ -216,7 +216,7 @@ def workload_config(wl, args):
                         "1 pose hypothesis, %d-level pyramid (reference default at VGA, SURVEY F4), default settings" % wl["levels"],
             "width": W.w, "height": W.h, "levels": wl["levels"], "key_frames": W.nF, "active_points": int(W.nP),
             "reference_points": int(wl["ref_points"]), "pc_n": [int(len(c[0])) for c in wl["clouds"]],
-            "ring_frames": len(wl["frames"]), "l2": "flushed between timed steps (256 MiB memset)",
+            "ring_frames": len(wl["frames"]), "l2": "NOT flushed (diagnostic run)" if args.no_flush else "flushed between timed steps (256 MiB memset)",
             "step": "one trackNewestCoarse call on a new frame", "parallelism": "replicas x%d" % args.gpus}
 
 
@@ -249,6 +249,8 @@ def run_ours(args):
     flush = torch.empty(64 * 1024 * 1024, dtype=torch.float32, device=device)   # 256 MiB > 126 MB L2
 
     def flush_l2():
+        if args.no_flush:
+            return
         with torch.cuda.stream(stream):
             flush.zero_()
 
@@ -372,6 +374,7 @@ def main():
     ap.add_argument("--tracker-points", type=int, default=2000, help="active points in the key-frame window")
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-flush", action="store_true", help="diagnostic only: keep L2 warm between steps (not a valid bench line)")
     args = ap.parse_args()
     if args.warmup < 3:
         args.warmup = 3

@@ -67,6 +67,7 @@ SIGNATURES = {
     "dso_b200_track_fetch": (C.c_int, [vp, C.c_int, C.c_int, C.POINTER(TrackResult)]),
     "dso_b200_track_frame": (C.c_int, [vp, C.c_int, C.c_int, vp, C.c_int, C.c_int, C.c_int, C.c_int, f64p, C.c_double, C.c_double,
                                        C.c_float, C.c_int, C.POINTER(TrackOpts), C.POINTER(TrackResult)]),
+    "dso_b200_track_phase_cycles": (C.c_int, [vp, C.c_int, vp]),
     "dso_b200_track_replay_abort": (C.c_int, [C.POINTER(TrackResult), f64p, f64p]),
     "dso_b200_track_hostloop": (C.c_int, [vp, C.c_int, C.c_int, f64p, C.c_double, C.c_double, C.c_float, C.c_int, vp,
                                           C.POINTER(TrackOpts), C.POINTER(TrackResult)]),
@@ -254,6 +255,11 @@ class Context:
         self._check(self.L.dso_b200_track_frame(self.h, trk, slot, color_ptr, w, h, levels, n, poses12.reshape(-1), a, b,
                                                 new_exposure, coarsest, None if opts is None else C.byref(opts), res))
         return list(res)
+
+    def phase_cycles(self, enable=True, read=False):
+        out = np.zeros(7, dtype=np.int64)
+        self._check(self.L.dso_b200_track_phase_cycles(self.h, int(enable), out.ctypes.data if read else None))
+        return out
 
     def replay_abort(self, res, min_res):
         lr = np.zeros(5)

@@ -119,6 +119,7 @@ extern "C" void dso_b200_destroy(dso_b200_ctx* ctx)
 	cudaFree(ctx->d_color);
 	for (int l = 0; l < MAXL; l++) { cudaFree(ctx->d_aos[l]); cudaFree(ctx->d_abs[l]); }
 	cudaFree(ctx->d_Blut);
+	if (ctx->d_phase_cycles) cudaFree(ctx->d_phase_cycles);
 	for (int t = 0; t < 2; t++)
 	{
 		TrackerSlot& T = ctx->trk[t];

@@ -96,6 +96,7 @@ struct dso_b200_ctx
 	TrackerSlot trk[2];
 	BAWorkspace* ba;
 	long long launches;
+	void* d_phase_cycles;      // optional: per-phase cycle counters of the persistent tracker (debug)
 };
 
 // sums layout of one tracker evaluation

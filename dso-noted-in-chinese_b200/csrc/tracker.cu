@@ -30,7 +30,7 @@ namespace cg = cooperative_groups;
 #define SCALE_B 1000.0f
 
 #define EVAL_THREADS 256
-#define PERS_THREADS 512
+#define PERS_THREADS 256
 #define MAX_CLUSTER 16
 
 struct EvalParams
@@ -458,19 +458,18 @@ struct TrackIn
 
 // LM state of one hypothesis, in shared memory.  The serial dependency chain of trackNewestCoarse
 // (solve -> exp -> warp -> reduce -> accept?) is the latency floor of this kernel, so the step between
-// two evaluations is executed by one warp with lane-parallel sections instead of one thread.
+// two evaluations is executed by one warp: per-lane rows / pose entries in registers, uniform scalar
+// work replicated in every lane (no divergent sections), shuffles instead of shared-memory round trips.
 struct LMS
 {
-	double H[64], b[8], Hn[64], bn[8];
-	double curR[9], curT[3], nwR[9], nwT[3], eR[9], eT[3];
+	double H[64], b[8];
+	double cur[12], nw[12];                       // R (row-major 9) then t
 	double a_cur, b_cur, a_new, b_new;
 	double resOldE, resOldN, resOldFlowT, resOldFlowRT;
-	double newE, newN, newFlowT, newFlowRT, newSat;
 	double incnorm;
 	double minRes[5];
 	float lambda, levelCutoffRepeat;
 	int lvl, iteration, phase, haveRepeated, done;
-	int req_new;       // 1: the next evaluation uses (nwR,nwT,a_new,b_new), 0: the current state
 };
 
 __device__ __forceinline__ double shfl_d(double v, int src) { return __shfl_sync(0xffffffffu, v, src); }
@@ -482,261 +481,244 @@ __device__ __forceinline__ double fast_rcp(double x)
 	r = r * fma(-x, r, 2.0);
 	return r;
 }
-
-// accept the latest evaluation as the new linearisation point (CoarseTracker.cpp:595 / :687-688)
-__device__ __forceinline__ void lm_take_new(LMS& S, int lane)
+__device__ __forceinline__ float scale_of(int i)
 {
-	for (int i = lane; i < 64; i += 32) S.H[i] = S.Hn[i];
-	if (lane < 8) S.b[lane] = S.bn[lane];
-	if (lane == 0) { S.resOldE = S.newE; S.resOldN = S.newN; S.resOldFlowT = S.newFlowT; S.resOldFlowRT = S.newFlowRT; }
-	__syncwarp();
+	return i < 3 ? SCALE_XI_ROT : (i < 6 ? SCALE_XI_TRANS : (i == 6 ? SCALE_A : SCALE_B));
 }
 
-// :613-665: damped solve (warp-parallel elimination, one lane per row; H + lambda*diag is SPD so no
-// pivoting is needed -- Eigen's pivoted LDLT gives the same solution up to rounding), SE3 update
-__device__ __forceinline__ void lm_propose(LMS& S, int lane)
+// SE3 exponential coefficients A = sin(t)/t, B = (1-cos t)/t^2, C = (t - sin t)/t^3 as series in t^2
+// (|t| < 0.5 for any LM increment; truncation error < 1e-16), falling back to sincos otherwise.
+__device__ __forceinline__ void exp_coeffs(double th2, double& A, double& B, double& C)
 {
-	const int i = lane & 7;
-	const double damp = (double)(1.f + S.lambda);
-	double row[8], rp[8], x[8];
-#pragma unroll
-	for (int j = 0; j < 8; j++) row[j] = S.H[i * 8 + j] * ((j == i) ? damp : 1.0);
-	double rhs = -S.b[i];
-#pragma unroll
-	for (int k = 0; k < 8; k++)
+	if (th2 < 0.25)
 	{
-		const double piv = shfl_d(row[k], k);
-		rp[k] = fast_rcp(piv);
-		const double f = row[k] * rp[k];
-		const double prhs = shfl_d(rhs, k);
-		const bool act = i > k;
-#pragma unroll
-		for (int j = k + 1; j < 8; j++)
-		{
-			const double pj = shfl_d(row[j], k);
-			if (act) row[j] = fma(-f, pj, row[j]);
-		}
-		if (act) rhs = fma(-f, prhs, rhs);
-	}
-#pragma unroll
-	for (int k = 7; k >= 0; k--)
-	{
-		const double xk = shfl_d(rhs, k) * rp[k];
-		x[k] = xk;
-		if (i < k) rhs = fma(-row[k], xk, rhs);
-	}
-	// every lane now holds the full increment: the rest is uniform scalar work
-	float extrapFac = 1.f;
-	if (S.lambda < 0.001f) extrapFac = sqrtf(sqrtf(0.001f / S.lambda));   // :650
-	double nrm = 0, sum = 0, is[8];
-#pragma unroll
-	for (int k = 0; k < 8; k++) { x[k] *= (double)extrapFac; nrm = fma(x[k], x[k], nrm); }
-	const double scl[8] = { SCALE_XI_ROT, SCALE_XI_ROT, SCALE_XI_ROT, SCALE_XI_TRANS, SCALE_XI_TRANS, SCALE_XI_TRANS, SCALE_A, SCALE_B };
-#pragma unroll
-	for (int k = 0; k < 8; k++) { is[k] = x[k] * scl[k]; sum += is[k]; }
-	if (!isfinite(sum))                                                    // :659
-	{
-#pragma unroll
-		for (int k = 0; k < 8; k++) is[k] = 0;
-	}
-	Pose e;
-	se3_exp(is, e);
-	// uniform values in every lane: lane l stores entry l (static register indexing only)
-#pragma unroll
-	for (int k = 0; k < 9; k++) if (lane == k) S.eR[k] = e.R[k];
-#pragma unroll
-	for (int k = 0; k < 3; k++) if (lane == 9 + k) S.eT[k] = e.t[k];
-	if (lane == 0)
-	{
-		S.incnorm = sqrt(nrm);
-		S.a_new = S.a_cur + is[6];
-		S.b_new = S.b_cur + is[7];
-		S.req_new = 1;
-	}
-	__syncwarp();
-	// refToNew_new = exp(inc) * refToNew_current (:661), lane-parallel
-	if (lane < 9)
-	{
-		const int r = lane / 3, c = lane - 3 * r;
-		S.nwR[lane] = S.eR[r * 3 + 0] * S.curR[c] + S.eR[r * 3 + 1] * S.curR[3 + c] + S.eR[r * 3 + 2] * S.curR[6 + c];
-	}
-	else if (lane < 12)
-	{
-		const int r = lane - 9;
-		S.nwT[r] = S.eR[r * 3 + 0] * S.curT[0] + S.eR[r * 3 + 1] * S.curT[1] + S.eR[r * 3 + 2] * S.curT[2] + S.eT[r];
-	}
-	__syncwarp();
-}
-
-// CoarseTracker.cpp:375-378 for the requested state, lane-parallel (same arithmetic as make_eval_params)
-__device__ __forceinline__ void lm_build_params(const LMS& S, const TrackLevels& TL, const dso_b200_track_opts& opt,
-                                                EvalParams& P, int lane)
-{
-	const int lvl = S.lvl;
-	const double* R = S.req_new ? S.nwR : S.curR;
-	const double* T = S.req_new ? S.nwT : S.curT;
-	if (lane < 9)
-	{
-		const int r = lane / 3, c = lane - 3 * r;
-		P.RKi[lane] = dot3e((float)R[r * 3 + 0], TL.Ki[lvl][c], (float)R[r * 3 + 1], TL.Ki[lvl][3 + c], (float)R[r * 3 + 2], TL.Ki[lvl][6 + c]);
-		P.Ki[lane] = TL.Ki[lvl][lane];
-	}
-	else if (lane < 12) P.t[lane - 9] = (float)T[lane - 9];
-	else if (lane == 12)
-	{
-		double a, b;
-		aff_from_to(TL.ref_exposure, TL.new_exposure, TL.ref_a, TL.ref_b, S.req_new ? S.a_new : S.a_cur, S.req_new ? S.b_new : S.b_cur, a, b);
-		P.affLL0 = (float)a; P.affLL1 = (float)b;
-	}
-	else if (lane == 13)
-	{
-		const float cutoff = opt.coarseCutoffTH * S.levelCutoffRepeat;
-		P.fx = TL.fx[lvl]; P.fy = TL.fy[lvl]; P.cx = TL.cx[lvl]; P.cy = TL.cy[lvl];
-		P.wl = TL.w[lvl];
-		P.wl_m3 = (float)(TL.w[lvl] - 3); P.hl_m3 = (float)(TL.h[lvl] - 3);
-		P.n = TL.pc_n[lvl];
-		P.lvl0 = (lvl == 0);
-		P.cutoffTH = cutoff;
-		P.huberTH = opt.huberTH;
-		P.maxEnergy = fsub(fmul(fmul(2.0f, opt.huberTH), cutoff), fmul(opt.huberTH, opt.huberTH));
-		P.b0 = (float)TL.ref_b;
-	}
-	__syncwarp();
-}
-
-// :708-722 + :727-746
-__device__ __forceinline__ void lm_finish_level(LMS& S, const TrackLevels& TL, const dso_b200_track_opts& opt,
-                                                dso_b200_track_result* out, int lane)
-{
-	if (lane == 0)
-	{
-		const int lvl = S.lvl;
-		const float rmse = sqrtf((float)(S.resOldE / S.resOldN));          // :710
-		out->lastResiduals[lvl] = rmse;
-		out->lastFlowIndicators[0] = S.resOldFlowT; out->lastFlowIndicators[1] = 0; out->lastFlowIndicators[2] = S.resOldFlowRT;
-		if (out->n_passes < DSO_B200_MAX_PASSES) { out->pass_level[out->n_passes] = lvl; out->pass_rmse[out->n_passes] = rmse; out->n_passes++; }
-		if ((double)rmse > 1.5 * S.minRes[lvl]) { S.done = 1; out->ok = 0; out->reserved = lvl; }   // :713
-		else
-		{
-			int next = lvl - 1;
-			if (S.levelCutoffRepeat > 1 && !S.haveRepeated) { next = lvl; S.haveRepeated = 1; }   // :717-722
-			if (next < 0)
-			{
-				S.done = 1;
-				for (int i = 0; i < 9; i++) out->pose[i] = S.curR[i];
-				for (int i = 0; i < 3; i++) out->pose[9 + i] = S.curT[i];
-				out->aff_a = S.a_cur; out->aff_b = S.b_cur;
-				out->ok = 1;
-				if ((opt.affineOptModeA != 0 && (fabsf((float)S.a_cur) > 1.2f)) || (opt.affineOptModeB != 0 && (fabsf((float)S.b_cur) > 200.f)))
-					out->ok = 0;
-				else
-				{
-					double ra, rb;
-					aff_from_to(TL.ref_exposure, TL.new_exposure, TL.ref_a, TL.ref_b, S.a_cur, S.b_cur, ra, rb);
-					if ((opt.affineOptModeA == 0 && (fabsf(logf((float)ra)) > 1.5f)) || (opt.affineOptModeB == 0 && (fabsf((float)rb) > 200.f)))
-						out->ok = 0;
-				}
-			}
-			else
-			{
-				S.lvl = next; S.phase = 0; S.levelCutoffRepeat = 1; S.iteration = 0; S.req_new = 0;   // :584
-			}
-		}
-	}
-	__syncwarp();
-}
-
-// One step of the trackNewestCoarse state machine, executed by warp 0 of every CTA of the cluster
-// (identical inputs -> identical decisions, so no broadcast is needed).
-__device__ __forceinline__ void lm_step_warp(LMS& S, const float* s_tot, const TrackLevels& TL, const dso_b200_track_opts& opt,
-                                             dso_b200_track_result* out, EvalParams& P, int n_points, int lane)
-{
-	// sums -> Vec6 + scaled H, b (sums_to_result, lane-parallel)
-	{
-		const int nw = (int)s_tot[S_NWARP];
-		const int npad = (nw + 3) & ~3;
-		const float invn = fdiv(1.0f, (float)npad);
-		for (int idx = lane; idx < 44; idx += 32)
-		{
-			if (idx < 36)
-			{
-				int i = 0, rem = idx;
-				while (rem >= 8 - i) { rem -= 8 - i; i++; }
-				const int j = i + rem;
-				const float si = i < 3 ? SCALE_XI_ROT : (i < 6 ? SCALE_XI_TRANS : (i == 6 ? SCALE_A : SCALE_B));
-				const float sj = j < 3 ? SCALE_XI_ROT : (j < 6 ? SCALE_XI_TRANS : (j == 6 ? SCALE_A : SCALE_B));
-				double v = (double)s_tot[S_ACC + idx] * (double)invn;
-				v *= (double)sj;
-				v *= (double)si;
-				S.Hn[i * 8 + j] = v; S.Hn[j * 8 + i] = v;
-			}
-			else
-			{
-				const int i = idx - 36;
-				const float si = i < 3 ? SCALE_XI_ROT : (i < 6 ? SCALE_XI_TRANS : (i == 6 ? SCALE_A : SCALE_B));
-				S.bn[i] = (double)s_tot[S_ACC + idx] * (double)invn * (double)si;
-			}
-		}
-		if (lane == 0)
-		{
-			S.newE = (double)s_tot[S_E];
-			S.newN = (double)s_tot[S_NTERMS];
-			S.newFlowT = (double)s_tot[S_FLOW_T] / ((double)s_tot[S_FLOW_N] + 0.1);
-			S.newFlowRT = (double)s_tot[S_FLOW_RT] / ((double)s_tot[S_FLOW_N] + 0.1);
-			S.newSat = (double)fdiv(s_tot[S_NSAT], s_tot[S_NTERMS]);
-			out->n_evals++; out->point_evals += n_points;
-		}
-		__syncwarp();
-	}
-	bool level_done = false;
-	if (S.phase == 0)
-	{
-		if (S.newSat > 0.6 && S.levelCutoffRepeat < 50)                        // :586-593
-		{
-			if (lane == 0) { S.levelCutoffRepeat *= 2; S.req_new = 0; }
-			__syncwarp();
-			lm_build_params(S, TL, opt, P, lane);
-			return;
-		}
-		lm_take_new(S, lane);
-		if (lane == 0) { S.lambda = 0.01f; S.iteration = 0; S.phase = 1; }
-		__syncwarp();
-		level_done = (S.iteration >= opt.maxIterations[S.lvl]);
+		A = 1.0 + th2 * (-1.0 / 6 + th2 * (1.0 / 120 + th2 * (-1.0 / 5040 + th2 * (1.0 / 362880 + th2 * (-1.0 / 39916800 + th2 * (1.0 / 6227020800.0 + th2 * (-1.0 / 1307674368000.0)))))));
+		B = 0.5 + th2 * (-1.0 / 24 + th2 * (1.0 / 720 + th2 * (-1.0 / 40320 + th2 * (1.0 / 3628800 + th2 * (-1.0 / 479001600 + th2 * (1.0 / 87178291200.0 + th2 * (-1.0 / 20922789888000.0)))))));
+		C = 1.0 / 6 + th2 * (-1.0 / 120 + th2 * (1.0 / 5040 + th2 * (-1.0 / 362880 + th2 * (1.0 / 39916800 + th2 * (-1.0 / 6227020800.0 + th2 * (1.0 / 1307674368000.0 + th2 * (-1.0 / 355687428096000.0)))))));
 	}
 	else
 	{
-		const bool accept = (S.newE / S.newN) < (S.resOldE / S.resOldN);       // :669
+		const double th = sqrt(th2);
+		double s, c;
+		sincos(th, &s, &c);
+		A = s / th; B = (1.0 - c) / th2; C = (th - s) / (th2 * th);
+	}
+}
+
+// One step of the trackNewestCoarse state machine (CoarseTracker.cpp:584-722), executed by warp 0 of
+// every CTA of the cluster on identical inputs (so all CTAs take identical decisions, no broadcast).
+// Consumes the sums of the evaluation just finished, leaves either S.done or the next EvalParams in P.
+__device__ __forceinline__ void lm_step_warp(LMS& S, const float* s_tot, const TrackLevels& TL, const dso_b200_track_opts& opt,
+                                             dso_b200_track_result* out, EvalParams& P, int n_points, int lane)
+{
+	const int i = lane & 7;
+	// ---- sums -> this lane's row of the scaled H, b (:338-353) and the Vec6 (:511-519) ----
+	const int nwarp = (int)s_tot[S_NWARP];
+	const float invn = fdiv(1.0f, (float)((nwarp + 3) & ~3));
+	const double si = (double)invn * (double)scale_of(i);
+	double hn[8];
+#pragma unroll
+	for (int j = 0; j < 8; j++)
+	{
+		const int a = i < j ? i : j, b = i < j ? j : i;
+		const int idx = a * 8 - ((a * (a - 1)) >> 1) + (b - a);
+		hn[j] = (double)s_tot[S_ACC + idx] * si * (double)scale_of(j);
+	}
+	const double bn = (double)s_tot[S_ACC + 36 + i] * si;
+	const double newE = (double)s_tot[S_E], newN = (double)s_tot[S_NTERMS];
+	const double newFlowT = (double)s_tot[S_FLOW_T] / ((double)s_tot[S_FLOW_N] + 0.1);
+	const double newFlowRT = (double)s_tot[S_FLOW_RT] / ((double)s_tot[S_FLOW_N] + 0.1);
+	const double newSat = (double)fdiv(s_tot[S_NSAT], s_tot[S_NTERMS]);
+
+	// uniform copies of the scalar state
+	int lvl = S.lvl, phase = S.phase, iteration = S.iteration;
+	float lambda = S.lambda, rep = S.levelCutoffRepeat;
+	double a_cur = S.a_cur, b_cur = S.b_cur;
+	bool take = false, use_new = false, level_done = false, propose = false;
+
+	if (phase == 0)
+	{
+		if (newSat > 0.6 && rep < 50) rep *= 2;                                // :586-593: same state, larger cut-off
+		else { take = true; lambda = 0.01f; iteration = 0; phase = 1; level_done = (0 >= opt.maxIterations[lvl]); propose = !level_done; }
+	}
+	else
+	{
+		const bool accept = (newE / newN) < (S.resOldE / S.resOldN);           // :669
+		if (accept)
+		{
+			take = true;
+			a_cur = S.a_new; b_cur = S.b_new;
+			if (lane < 12) S.cur[lane] = S.nw[lane];
+			lambda *= 0.5f;
+		}
+		else { lambda *= 4; if (lambda < 0.001f) lambda = 0.001f; }
+		iteration++;
+		level_done = (!(S.incnorm > 1e-3) || iteration >= opt.maxIterations[lvl]);   // :700, :613
+		propose = !level_done;
 		if (lane == 0)
 		{
 			if (out->trace_len < 256) out->trace[out->trace_len++] = accept ? 1 : 0;
 			out->n_iterations++;
 		}
-		if (accept)
-		{
-			lm_take_new(S, lane);
-			if (lane < 9) S.curR[lane] = S.nwR[lane];
-			else if (lane < 12) S.curT[lane - 9] = S.nwT[lane - 9];
-			if (lane == 12) { S.a_cur = S.a_new; S.b_cur = S.b_new; S.lambda *= 0.5f; }
-		}
-		else if (lane == 0)
-		{
-			float l = S.lambda * 4;
-			if (l < 0.001f) l = 0.001f;
-			S.lambda = l;
-		}
-		if (lane == 1) S.iteration++;
-		__syncwarp();
-		level_done = (!(S.incnorm > 1e-3) || S.iteration >= opt.maxIterations[S.lvl]);   // :700, :613
 	}
+	double resOldE = S.resOldE, resOldN = S.resOldN, resOldFlowT = S.resOldFlowT, resOldFlowRT = S.resOldFlowRT;
+	if (take)
+	{
+		resOldE = newE; resOldN = newN; resOldFlowT = newFlowT; resOldFlowRT = newFlowRT;
+		if (lane < 8)
+		{
+#pragma unroll
+			for (int j = 0; j < 8; j++) S.H[i * 8 + j] = hn[j];
+			S.b[i] = bn;
+		}
+	}
+	__syncwarp();
+
+	bool done = false;
 	if (level_done)
 	{
-		lm_finish_level(S, TL, opt, out, lane);
-		if (S.done) return;
-		lm_build_params(S, TL, opt, P, lane);
-		return;
+		// :708-722 (+ :727-746 when the finest level is finished)
+		const float rmse = sqrtf((float)(resOldE / resOldN));
+		const bool abort = (double)rmse > 1.5 * S.minRes[lvl];
+		int next = lvl - 1;
+		int haveRepeated = S.haveRepeated;
+		if (rep > 1 && !haveRepeated) { next = lvl; haveRepeated = 1; }
+		if (lane == 0)
+		{
+			out->lastResiduals[lvl] = rmse;
+			out->lastFlowIndicators[0] = resOldFlowT; out->lastFlowIndicators[1] = 0; out->lastFlowIndicators[2] = resOldFlowRT;
+			if (out->n_passes < DSO_B200_MAX_PASSES) { out->pass_level[out->n_passes] = lvl; out->pass_rmse[out->n_passes] = rmse; out->n_passes++; }
+			S.haveRepeated = haveRepeated;
+			if (abort) { out->ok = 0; out->reserved = lvl; }
+			else if (next < 0)
+			{
+				for (int k = 0; k < 12; k++) out->pose[k] = S.cur[k];
+				out->aff_a = a_cur; out->aff_b = b_cur;
+				int ok = 1;
+				if ((opt.affineOptModeA != 0 && (fabsf((float)a_cur) > 1.2f)) || (opt.affineOptModeB != 0 && (fabsf((float)b_cur) > 200.f))) ok = 0;
+				else
+				{
+					double ra, rb;
+					aff_from_to(TL.ref_exposure, TL.new_exposure, TL.ref_a, TL.ref_b, a_cur, b_cur, ra, rb);
+					if ((opt.affineOptModeA == 0 && (fabsf(logf((float)ra)) > 1.5f)) || (opt.affineOptModeB == 0 && (fabsf((float)rb) > 200.f))) ok = 0;
+				}
+				out->ok = ok;
+			}
+		}
+		done = abort || next < 0;
+		lvl = next; phase = 0; rep = 1; iteration = 0;                         // :584 of the next level pass
 	}
-	lm_propose(S, lane);
-	lm_build_params(S, TL, opt, P, lane);
+
+	double a_req = a_cur, b_req = b_cur;
+	double pe = (lane < 12) ? S.cur[lane] : 0.0;       // this lane's pose entry of the state to evaluate next
+	double incnorm = S.incnorm;
+	if (propose)
+	{
+		// ---- :613-665: damped solve, one lane per row; H + lambda*diag(H) is SPD, so plain elimination
+		// (Eigen's pivoted LDLT gives the same solution up to rounding) ----
+		const double damp = (double)(1.f + lambda);
+		double row[8], rp[8], x[8];
+#pragma unroll
+		for (int j = 0; j < 8; j++) row[j] = take ? hn[j] : S.H[i * 8 + j];
+		double rhs = -(take ? bn : S.b[i]);
+#pragma unroll
+		for (int j = 0; j < 8; j++) if (j == i) row[j] *= damp;
+#pragma unroll
+		for (int k = 0; k < 8; k++)
+		{
+			const double piv = shfl_d(row[k], k);
+			rp[k] = fast_rcp(piv);
+			const double f = (i > k) ? row[k] * rp[k] : 0.0;
+			const double prhs = shfl_d(rhs, k);
+#pragma unroll
+			for (int j = k + 1; j < 8; j++) row[j] = fma(-f, shfl_d(row[j], k), row[j]);
+			rhs = fma(-f, prhs, rhs);
+		}
+#pragma unroll
+		for (int k = 7; k >= 0; k--)
+		{
+			const double xk = shfl_d(rhs, k) * rp[k];
+			x[k] = xk;
+			rhs = fma((i < k) ? -row[k] : 0.0, xk, rhs);
+		}
+		float extrapFac = 1.f;
+		if (lambda < 0.001f) extrapFac = sqrtf(sqrtf(0.001f / lambda));       // :650
+		double nrm = 0, sum = 0, is[8];
+#pragma unroll
+		for (int k = 0; k < 8; k++) { x[k] *= (double)extrapFac; nrm = fma(x[k], x[k], nrm); is[k] = x[k] * (double)scale_of(k); sum += is[k]; }
+		if (!isfinite(sum))                                                    // :659
+		{
+#pragma unroll
+			for (int k = 0; k < 8; k++) is[k] = 0;
+		}
+		incnorm = sqrt(nrm);
+		a_req = a_cur + is[6]; b_req = b_cur + is[7];
+		// exp(inc) (Sophus SE3::exp): R = I + A W + B W^2, t = (I + B W + C W^2) u
+		const double wx = is[3], wy = is[4], wz = is[5];
+		const double th2 = wx * wx + wy * wy + wz * wz;
+		double A, B, C;
+		exp_coeffs(th2, A, B, C);
+		// this lane's row r of exp(inc) (R lanes: r = lane/3, t lanes: r = lane-9)
+		const int r = (lane < 9) ? lane / 3 : (lane < 12 ? lane - 9 : 0);
+		const int c = (lane < 9) ? lane - 3 * r : 0;
+		const double wr = r == 0 ? wx : (r == 1 ? wy : wz);
+		// W row r = (0,-wz,wy),(wz,0,-wx),(-wy,wx,0); W^2 row r = wr*w - th2*e_r
+		const double W0 = r == 0 ? 0.0 : (r == 1 ? wz : -wy);
+		const double W1 = r == 0 ? -wz : (r == 1 ? 0.0 : wx);
+		const double W2 = r == 0 ? wy : (r == 1 ? -wx : 0.0);
+		const double Q0 = wr * wx - (r == 0 ? th2 : 0.0), Q1 = wr * wy - (r == 1 ? th2 : 0.0), Q2 = wr * wz - (r == 2 ? th2 : 0.0);
+		const double e0 = (r == 0 ? 1.0 : 0.0) + A * W0 + B * Q0;
+		const double e1 = (r == 1 ? 1.0 : 0.0) + A * W1 + B * Q1;
+		const double e2 = (r == 2 ? 1.0 : 0.0) + A * W2 + B * Q2;
+		const double v0 = (r == 0 ? 1.0 : 0.0) + B * W0 + C * Q0;
+		const double v1 = (r == 1 ? 1.0 : 0.0) + B * W1 + C * Q1;
+		const double v2 = (r == 2 ? 1.0 : 0.0) + B * W2 + C * Q2;
+		const double et = v0 * is[0] + v1 * is[1] + v2 * is[2];
+		// refToNew_new = exp(inc) * refToNew_current (:661): entry (r,c) = sum_k e[r][k] cur[k][c]; t_r = sum_k e[r][k] t_k + et_r
+		const int src0 = (lane < 9) ? c : 9, src1 = (lane < 9) ? 3 + c : 10, src2 = (lane < 9) ? 6 + c : 11;
+		const double c0 = shfl_d(pe, src0), c1 = shfl_d(pe, src1), c2 = shfl_d(pe, src2);
+		double ne = e0 * c0 + e1 * c1 + e2 * c2;
+		if (lane >= 9) ne += et;
+		pe = ne;
+		if (lane < 12) S.nw[lane] = ne;
+		use_new = true;
+	}
+
+	// ---- CoarseTracker.cpp:375-378 + :385 for the state to evaluate next (skipped when done) ----
+	if (!done)
+	{
+		const int r = (lane < 9) ? lane / 3 : 0, c = (lane < 9) ? lane - 3 * r : 0;
+		const float R0 = (float)shfl_d(pe, 3 * r), R1 = (float)shfl_d(pe, 3 * r + 1), R2 = (float)shfl_d(pe, 3 * r + 2);
+		const float rk = dot3e(R0, TL.Ki[lvl][c], R1, TL.Ki[lvl][3 + c], R2, TL.Ki[lvl][6 + c]);
+		double a, b;
+		aff_from_to(TL.ref_exposure, TL.new_exposure, TL.ref_a, TL.ref_b, a_req, b_req, a, b);
+		if (lane < 9) { P.RKi[lane] = rk; P.Ki[lane] = TL.Ki[lvl][lane]; }
+		else if (lane < 12) P.t[lane - 9] = (float)pe;
+		if (lane == 12)
+		{
+			const float cutoff = opt.coarseCutoffTH * rep;
+			P.affLL0 = (float)a; P.affLL1 = (float)b;
+			P.fx = TL.fx[lvl]; P.fy = TL.fy[lvl]; P.cx = TL.cx[lvl]; P.cy = TL.cy[lvl];
+			P.wl = TL.w[lvl];
+			P.wl_m3 = (float)(TL.w[lvl] - 3); P.hl_m3 = (float)(TL.h[lvl] - 3);
+			P.n = TL.pc_n[lvl];
+			P.lvl0 = (lvl == 0);
+			P.cutoffTH = cutoff;
+			P.huberTH = opt.huberTH;
+			P.maxEnergy = fsub(fmul(fmul(2.0f, opt.huberTH), cutoff), fmul(opt.huberTH, opt.huberTH));
+			P.b0 = (float)TL.ref_b;
+		}
+	}
+	if (lane == 0)
+	{
+		S.lvl = lvl; S.phase = phase; S.iteration = iteration; S.lambda = lambda; S.levelCutoffRepeat = rep;
+		S.a_cur = a_cur; S.b_cur = b_cur;
+		if (use_new) { S.a_new = a_req; S.b_new = b_req; S.incnorm = incnorm; }
+		S.resOldE = resOldE; S.resOldN = resOldN; S.resOldFlowT = resOldFlowT; S.resOldFlowRT = resOldFlowRT;
+		S.done = done ? 1 : 0;
+		out->n_evals++; out->point_evals += n_points;
+	}
+	__syncwarp();
 }
 
 // Fixed-tree warp reduction of S_COUNT (<= 64) values with recursive halving: 62 shuffles instead of
@@ -757,19 +739,25 @@ __device__ __forceinline__ void warp_reduce_halving(float* v, int lane)
 	}
 }
 
-__global__ void __launch_bounds__(PERS_THREADS, 1)
+// phase_cycles (optional, debug): SM cycles spent by thread 0 of CTA 0 in [point evaluation, CTA
+// reduction, cluster exchange + barrier, LM step], number of evaluations, whole kernel cycles and ns.
+template <int NT>
+__global__ void __launch_bounds__(NT, 1)
 track_persistent_kernel(TrackLevels TL, dso_b200_track_opts opt, const TrackIn* __restrict__ in,
-                        dso_b200_track_result* out, int coarsestLvl, int smem_pts_cap)
+                        dso_b200_track_result* out, int coarsestLvl, int smem_pts_cap, long long* phase_cycles)
 {
 	cg::cluster_group cluster = cg::this_cluster();
 	const unsigned CS = cluster.num_blocks();
 	const unsigned rank = cluster.block_rank();
 	const int hyp = blockIdx.x / CS;
 	const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+	long long tph[5] = { 0, 0, 0, 0, 0 };
+	long long tc0 = 0, tk0 = 0, tg0 = 0;
+	if (phase_cycles) { tk0 = clock64(); asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tg0)); }
 
 	__shared__ EvalParams sP;
 	__shared__ LMS S;
-	__shared__ float s_w[PERS_THREADS / 32][64];
+	__shared__ float s_w[NT / 32][64];
 	__shared__ float xchg[2][MAX_CLUSTER][S_COUNT];
 	__shared__ float s_tot[S_COUNT];
 	__shared__ dso_b200_track_result s_res;
@@ -780,21 +768,23 @@ track_persistent_kernel(TrackLevels TL, dso_b200_track_opts opt, const TrackIn* 
 		if (lane == 0)
 		{
 			const TrackIn& I = in[hyp];
-			for (int i = 0; i < 9; i++) S.curR[i] = I.pose[i];
-			for (int i = 0; i < 3; i++) S.curT[i] = I.pose[9 + i];
-			S.a_cur = I.aff_a; S.b_cur = I.aff_b;
+			for (int i = 0; i < 12; i++) S.cur[i] = I.pose[i];
+			S.a_cur = I.aff_a; S.b_cur = I.aff_b; S.a_new = I.aff_a; S.b_new = I.aff_b;
 			for (int i = 0; i < 5; i++) S.minRes[i] = I.minRes[i];
 			S.haveRepeated = 0; S.done = 0; S.incnorm = 0; S.lambda = 0.01f;
-			S.lvl = coarsestLvl; S.phase = 0; S.levelCutoffRepeat = 1; S.iteration = 0; S.req_new = 0;
+			S.lvl = coarsestLvl; S.phase = 0; S.levelCutoffRepeat = 1; S.iteration = 0;
+			S.resOldE = 0; S.resOldN = 1; S.resOldFlowT = 0; S.resOldFlowRT = 0;
 			s_res.ok = 0; s_res.reserved = -1;
 			for (int i = 0; i < 12; i++) s_res.pose[i] = I.pose[i];
 			s_res.aff_a = I.aff_a; s_res.aff_b = I.aff_b;
 			for (int i = 0; i < 5; i++) s_res.lastResiduals[i] = NAN;        // :563
 			for (int i = 0; i < 3; i++) s_res.lastFlowIndicators[i] = 1000;  // :564
 			s_res.n_passes = 0; s_res.n_iterations = 0; s_res.n_evals = 0; s_res.trace_len = 0; s_res.point_evals = 0;
+			// CoarseTracker.cpp:375-385 for the very first evaluation (:584)
+			Pose p0; pose_from12(p0, I.pose);
+			make_eval_params(TL, coarsestLvl, p0, I.aff_a, I.aff_b, opt.coarseCutoffTH, opt.huberTH, sP);
 		}
 		__syncwarp();
-		lm_build_params(S, TL, opt, sP, lane);
 	}
 	__syncthreads();
 	int buf = 0;
@@ -809,19 +799,21 @@ track_persistent_kernel(TrackLevels TL, dso_b200_track_opts opt, const TrackIn* 
 		const bool use_smem = (end - beg) <= smem_pts_cap;
 		if (use_smem && staged_lvl != lvl)
 		{
-			for (int i = beg + tid; i < end; i += PERS_THREADS) s_pts[i - beg] = __ldg(gp + i);
+			for (int i = beg + tid; i < end; i += NT) s_pts[i - beg] = __ldg(gp + i);
 			staged_lvl = lvl;
 			__syncthreads();
 		}
 		const EvalParams P = sP;
 		const float4* __restrict__ img = TL.img[lvl];
+		if (phase_cycles) { __syncthreads(); tc0 = clock64(); }
 		float acc[64];
 #pragma unroll
 		for (int k = 0; k < 64; k++) acc[k] = 0.f;
 		if (use_smem)
-			for (int i = beg + tid; i < end; i += PERS_THREADS) eval_point<false>(s_pts[i - beg], i, P, img, acc, nullptr, nullptr);
+			for (int i = beg + tid; i < end; i += NT) eval_point<false>(s_pts[i - beg], i, P, img, acc, nullptr, nullptr);
 		else
-			for (int i = beg + tid; i < end; i += PERS_THREADS) eval_point<false>(__ldg(gp + i), i, P, img, acc, nullptr, nullptr);
+			for (int i = beg + tid; i < end; i += NT) eval_point<false>(__ldg(gp + i), i, P, img, acc, nullptr, nullptr);
+		if (phase_cycles) { __syncthreads(); long long t = clock64(); tph[0] += t - tc0; tc0 = t; }
 		warp_reduce_halving(acc, lane);
 		s_w[warp][2 * lane] = acc[0];
 		s_w[warp][2 * lane + 1] = acc[1];
@@ -831,9 +823,10 @@ track_persistent_kernel(TrackLevels TL, dso_b200_track_opts opt, const TrackIn* 
 		{
 			float s = 0.f;
 #pragma unroll
-			for (int w = 0; w < PERS_THREADS / 32; w++) s += s_w[w][tid];
+			for (int w = 0; w < NT / 32; w++) s += s_w[w][tid];
 			for (unsigned r = 0; r < CS; r++) *cluster.map_shared_rank(&xchg[buf][rank][tid], r) = s;
 		}
+		if (phase_cycles) { long long t = clock64(); tph[1] += t - tc0; tc0 = t; }
 		cluster.sync();
 		if (tid < S_COUNT)
 		{
@@ -842,8 +835,10 @@ track_persistent_kernel(TrackLevels TL, dso_b200_track_opts opt, const TrackIn* 
 			s_tot[tid] = s;
 		}
 		__syncthreads();
+		if (phase_cycles) { long long t = clock64(); tph[2] += t - tc0; tc0 = t; }
 		if (warp == 0) lm_step_warp(S, s_tot, TL, opt, &s_res, sP, n, lane);
 		__syncthreads();
+		if (phase_cycles) { long long t = clock64(); tph[3] += t - tc0; tph[4]++; }
 		if (S.done) break;
 		buf ^= 1;
 	}
@@ -852,7 +847,14 @@ track_persistent_kernel(TrackLevels TL, dso_b200_track_opts opt, const TrackIn* 
 		const int nwords = sizeof(dso_b200_track_result) / 4;
 		const unsigned int* src = reinterpret_cast<const unsigned int*>(&s_res);
 		unsigned int* dst = reinterpret_cast<unsigned int*>(out + hyp);
-		for (int i = tid; i < nwords; i += PERS_THREADS) dst[i] = src[i];
+		for (int i = tid; i < nwords; i += NT) dst[i] = src[i];
+	}
+	if (phase_cycles && blockIdx.x == 0 && tid == 0)
+	{
+		for (int k = 0; k < 5; k++) phase_cycles[k] = tph[k];
+		long long tg1; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tg1));
+		phase_cycles[5] = clock64() - tk0;
+		phase_cycles[6] = tg1 - tg0;
 	}
 }
 
@@ -1105,8 +1107,9 @@ static int enqueue_track(dso_b200_ctx* ctx, int trk, int frame_slot, int nHyp, c
 	TrackLevels TL;
 	fill_levels(ctx, T, &ctx->slots[frame_slot], new_ab_exposure, TL);
 
-	// cluster size: as many CTAs per hypothesis as fit on the device, power of two, <= 8 (portable)
-	int cs = 8;
+	// cluster size: as many CTAs per hypothesis as fit on the device, power of two, <= 16 (non-portable size,
+	// allowed explicitly below; measured best at 256 threads x 16 CTAs for one VGA hypothesis)
+	int cs = 16;
 	while (cs > 1 && nHyp * cs > ctx->sm_count) cs >>= 1;
 	int max_n = 0;
 	for (int l = 0; l <= coarsestLvl; l++) max_n = T.pc_n[l] > max_n ? T.pc_n[l] : max_n;
@@ -1114,23 +1117,41 @@ static int enqueue_track(dso_b200_ctx* ctx, int trk, int frame_slot, int nHyp, c
 	size_t smem_cap_bytes = 160 * 1024;
 	int cap = (int)std::min<size_t>((size_t)per, smem_cap_bytes / sizeof(float4));
 	size_t dyn = (size_t)cap * sizeof(float4);
-	static bool attr_set[64] = { false };
-	if (!attr_set[ctx->device & 63])
+	// tuning knobs (debug): threads per CTA and cluster size
+	static int env_threads = -1, env_cluster = -1;
+	if (env_threads < 0)
 	{
-		CK(cudaFuncSetAttribute(track_persistent_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_cap_bytes));
-		attr_set[ctx->device & 63] = true;
+		const char* e = getenv("DSO_B200_TRACK_THREADS"); env_threads = e ? atoi(e) : 0;
+		e = getenv("DSO_B200_TRACK_CLUSTER"); env_cluster = e ? atoi(e) : 0;
+	}
+	int nt = env_threads ? env_threads : PERS_THREADS;
+	if (env_cluster) cs = env_cluster;
+	while (cs > 1 && nHyp * cs > ctx->sm_count) cs >>= 1;
+	per = (max_n + cs - 1) / cs;
+	cap = (int)std::min<size_t>((size_t)per, smem_cap_bytes / sizeof(float4));
+	dyn = (size_t)cap * sizeof(float4);
+	void (*kern)(TrackLevels, dso_b200_track_opts, const TrackIn*, dso_b200_track_result*, int, int, long long*) =
+		nt == 128 ? track_persistent_kernel<128> : (nt == 512 ? track_persistent_kernel<512> : track_persistent_kernel<256>);
+	if (nt != 128 && nt != 512) nt = 256;
+	static bool attr_set[64][3] = { { false } };
+	const int ki = nt == 128 ? 0 : (nt == 256 ? 1 : 2);
+	if (!attr_set[ctx->device & 63][ki])
+	{
+		CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_cap_bytes));
+		CK(cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+		attr_set[ctx->device & 63][ki] = true;
 	}
 	cudaLaunchConfig_t cfg = {};
 	cfg.gridDim = dim3(nHyp * cs, 1, 1);
-	cfg.blockDim = dim3(PERS_THREADS, 1, 1);
+	cfg.blockDim = dim3(nt, 1, 1);
 	cfg.dynamicSmemBytes = dyn;
 	cfg.stream = ctx->stream;
 	cudaLaunchAttribute at[1];
 	at[0].id = cudaLaunchAttributeClusterDimension;
 	at[0].val.clusterDim.x = cs; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
 	cfg.attrs = at; cfg.numAttrs = 1;
-	CK(cudaLaunchKernelEx(&cfg, track_persistent_kernel, TL, o, (const TrackIn*)T.d_track_in,
-	                      (dso_b200_track_result*)T.d_track_out, coarsestLvl, cap));
+	CK(cudaLaunchKernelEx(&cfg, kern, TL, o, (const TrackIn*)T.d_track_in,
+	                      (dso_b200_track_result*)T.d_track_out, coarsestLvl, cap, (long long*)ctx->d_phase_cycles));
 	ctx->launches++;
 	if (pose12_init)
 		CK(cudaMemcpyAsync(T.h_track_out, T.d_track_out, sizeof(dso_b200_track_result) * nHyp, cudaMemcpyDeviceToHost, ctx->stream));
@@ -1142,6 +1163,20 @@ extern "C" int dso_b200_track_batched_async(dso_b200_ctx* ctx, int trk, int fram
                                             const dso_b200_track_opts* opts)
 {
 	return enqueue_track(ctx, trk, frame_slot, nHyp, pose12_init, aff_a_init, aff_b_init, new_ab_exposure, coarsestLvl, opts);
+}
+
+extern "C" int dso_b200_track_phase_cycles(dso_b200_ctx* ctx, int enable, long long* cycles7)
+{
+	ARG_CHECK(ctx, "null context");
+	CK(cudaSetDevice(ctx->device));
+	if (enable && !ctx->d_phase_cycles) { CK(cudaMalloc(&ctx->d_phase_cycles, 64)); CK(cudaMemset(ctx->d_phase_cycles, 0, 64)); }
+	if (cycles7 && ctx->d_phase_cycles)
+	{
+		CK(cudaStreamSynchronize(ctx->stream));
+		CK(cudaMemcpy(cycles7, ctx->d_phase_cycles, 56, cudaMemcpyDeviceToHost));
+	}
+	if (!enable && ctx->d_phase_cycles) { cudaFree(ctx->d_phase_cycles); ctx->d_phase_cycles = nullptr; }
+	return 0;
 }
 
 extern "C" int dso_b200_track_fetch(dso_b200_ctx* ctx, int trk, int nHyp, dso_b200_track_result* out)

@@ -1,0 +1,29 @@
+"""Per-phase cycle breakdown of the persistent tracker (debug aid; run on the GPU box)."""
+import os
+import sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np
+import bench
+import __graft_entry__ as entry
+
+pkg = entry.load_package()
+wl = bench.build_workload(0, 6, 2000)
+W, levels = wl["W"], wl["levels"]
+ctx = pkg.Context(0, W.w, W.h, 10)
+ctx.tracker_set_ref(0, W.w, W.h, levels, W.K, wl["clouds"], wl["a0"], wl["b0"], 1.0)
+for k in range(6):
+    ctx.make_images(1 + k, wl["frames"][k][0], levels, want_host=False)
+ctx.phase_cycles(True)
+for k in range(6):
+    a, b = wl["affs"][k]
+    r = ctx.track_batched(0, 1 + k, wl["inits"][k], a, b, levels - 1)[0]
+    c = ctx.phase_cycles(True, read=True)
+    n = max(c[4], 1)
+    print("frame", k, "evals", r.n_evals, "cycles/eval: eval %.0f reduce %.0f xchg %.0f lm %.0f total %.0f" %
+          (c[0] / n, c[1] / n, c[2] / n, c[3] / n, c[:4].sum() / n), "| kernel cycles", c[5], "ns", c[6])
+hy = np.stack([wl["inits"][2]] * 31)
+ctx.track_batched(0, 3, hy, *wl["affs"][2], levels - 1)
+c = ctx.phase_cycles(True, read=True)
+n = max(c[4], 1)
+print("31 hyps: cycles/eval: eval %.0f reduce %.0f xchg %.0f lm %.0f total %.0f" % (c[0] / n, c[1] / n, c[2] / n, c[3] / n, c[:4].sum() / n),
+      "| kernel ns", c[6])
