@@ -1,0 +1,152 @@
+// Host-side mirror of the reference's C++ class surface for the hot path (namespace dso), forwarding to the
+// C ABI of include/dso_b200.h.  Same member names, argument meaning and failure behaviour as the reference:
+// there are no status codes on this surface -- a non-zero C-ABI return aborts (there is no CPU fallback).
+//
+// The reference builds on Eigen/Sophus types that are not available in this image, so the value types
+// below (SE3, AffLight, Vec5, Mat88 ...) are minimal PODs with the reference's names; in the real tree the
+// maintainer keeps Eigen/Sophus and uses the two-line converters shown in INTEGRATION.md instead.
+#pragma once
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <cmath>
+#include <vector>
+#include "../../include/dso_b200.h"
+
+namespace dso
+{
+#define DSO_B200_CHECK(call)                                                                      \
+	do { int rc_ = (call); if (rc_ != 0) { fprintf(stderr, "dso_b200: %s failed (%d): %s\n", #call, rc_, dso_b200_last_error()); abort(); } } while (0)
+
+struct SE3 { double R[9]; double t[3]; SE3() { for (int i = 0; i < 9; i++) R[i] = (i % 4 == 0); t[0] = t[1] = t[2] = 0; } };
+struct AffLight { double a, b; AffLight(double a_ = 0, double b_ = 0) : a(a_), b(b_) {} };   // util/NumType.h:166-197
+struct Vec5 { double v[5]; double& operator[](int i) { return v[i]; } const double& operator[](int i) const { return v[i]; } };
+struct Vec3 { double v[3]; double& operator[](int i) { return v[i]; } };
+struct Vec6 { double v[6]; double& operator[](int i) { return v[i]; } };
+struct Vec8 { double v[8]; double& operator[](int i) { return v[i]; } };
+struct Mat88 { double m[64]; double& operator()(int r, int c) { return m[r * 8 + c]; } };
+
+static inline void pose12(const SE3& T, double* p) { memcpy(p, T.R, 72); memcpy(p + 9, T.t, 24); }
+static inline void from12(const double* p, SE3& T) { memcpy(T.R, p, 72); memcpy(T.t, p + 9, 24); }
+
+// CalibHessian (FullSystem/HessianBlocks.h:322-410): only what the hot path reads
+struct CalibHessian
+{
+	float value_scaledf[4];
+	float B[256];
+	float& fxl() { return value_scaledf[0]; }
+	float& fyl() { return value_scaledf[1]; }
+	float& cxl() { return value_scaledf[2]; }
+	float& cyl() { return value_scaledf[3]; }
+};
+
+// One device context per FullSystem (FullSystem.h:141); shared by the classes below.
+struct DeviceContext
+{
+	dso_b200_ctx* ctx;
+	int w, h, levels;
+	DeviceContext(int device, int w_, int h_, int levels_, int n_frame_slots) : ctx(0), w(w_), h(h_), levels(levels_)
+	{ DSO_B200_CHECK(dso_b200_create(device, w_, h_, n_frame_slots, &ctx)); }
+	~DeviceContext() { dso_b200_destroy(ctx); }
+};
+
+// FrameHessian (FullSystem/HessianBlocks.h:105-320): pyramid ownership as in the reference (new[] / delete[])
+struct FrameHessian
+{
+	DeviceContext* dev;
+	int frame_slot;                 // device pyramid of this frame
+	float* dIp[DSO_B200_MAX_LEVELS];           // Eigen::Vector3f* in the reference: 3 floats per pixel
+	float* absSquaredGrad[DSO_B200_MAX_LEVELS];
+	float* dI;
+	float ab_exposure;
+	float frameEnergyTH;
+	FrameHessian(DeviceContext* d, int slot) : dev(d), frame_slot(slot), dI(0), ab_exposure(1), frameEnergyTH(8 * 8 * 8)
+	{ for (int i = 0; i < DSO_B200_MAX_LEVELS; i++) { dIp[i] = 0; absSquaredGrad[i] = 0; } }
+	~FrameHessian() { for (int i = 0; i < DSO_B200_MAX_LEVELS; i++) { delete[] dIp[i]; delete[] absSquaredGrad[i]; } }
+
+	// void FrameHessian::makeImages(float* color, CalibHessian* HCalib)   HessianBlocks.cpp:137
+	void makeImages(float* color, CalibHessian* HCalib)
+	{
+		for (int i = 0; i < dev->levels; i++)
+		{
+			size_t n = (size_t)(dev->w >> i) * (dev->h >> i);
+			dIp[i] = new float[3 * n];
+			absSquaredGrad[i] = new float[n];
+		}
+		dI = dIp[0];
+		DSO_B200_CHECK(dso_b200_make_images(dev->ctx, frame_slot, color, dev->w, dev->h, dev->levels,
+		                                    HCalib ? HCalib->B : 0, dIp, absSquaredGrad));
+	}
+};
+
+// CoarseTracker (FullSystem/CoarseTracker.h:44-127)
+class CoarseTracker
+{
+public:
+	CoarseTracker(DeviceContext* d, int slot) : lastRef(0), newFrame(0), lastRef_aff_g2l(0, 0), firstCoarseRMSE(-1), dev(d), trk(slot)
+	{ for (int i = 0; i < 5; i++) lastResiduals[i] = NAN; for (int i = 0; i < 3; i++) lastFlowIndicators[i] = 1000; fx0 = fy0 = cx0 = cy0 = 0; }
+
+	// void makeK(CalibHessian* HCalib)   CoarseTracker.cpp:102 (the per-level K pyramid is derived inside the library)
+	void makeK(CalibHessian* HCalib) { fx0 = HCalib->fxl(); fy0 = HCalib->fyl(); cx0 = HCalib->cxl(); cy0 = HCalib->cyl(); }
+
+	// void setCoarseTrackingRef(std::vector<FrameHessian*>)   CoarseTracker.cpp:523: makeCoarseDepthL0 (:135-292) stays on the
+	// host; its per-level outputs pc_u/pc_v/pc_idepth/pc_color/pc_n are uploaded here.
+	void setCoarseTrackingRef(FrameHessian* lastRef_, AffLight ref_aff, const int* pc_n, const float* const* pc_u,
+	                          const float* const* pc_v, const float* const* pc_idepth, const float* const* pc_color)
+	{
+		lastRef = lastRef_; lastRef_aff_g2l = ref_aff; firstCoarseRMSE = -1;
+		DSO_B200_CHECK(dso_b200_tracker_set_ref(dev->ctx, trk, dev->w, dev->h, dev->levels, fx0, fy0, cx0, cy0, pc_n, pc_u, pc_v,
+		                                        pc_idepth, pc_color, ref_aff.a, ref_aff.b, lastRef_->ab_exposure));
+	}
+
+	// bool trackNewestCoarse(FrameHessian*, SE3&, AffLight&, int coarsestLvl, Vec5 minResForAbort, Output3DWrapper* = 0)
+	// CoarseTracker.cpp:551.  The whole LM loop runs in one persistent kernel; the abort test (:713) is replayed.
+	bool trackNewestCoarse(FrameHessian* newFrameHessian, SE3& lastToNew_out, AffLight& aff_g2l_out, int coarsestLvl,
+	                       Vec5 minResForAbort, void* wrap = 0)
+	{
+		(void)wrap;
+		newFrame = newFrameHessian;
+		double p[12];
+		pose12(lastToNew_out, p);
+		dso_b200_track_result r;
+		DSO_B200_CHECK(dso_b200_track_batched(dev->ctx, trk, newFrame->frame_slot, 1, p, aff_g2l_out.a, aff_g2l_out.b,
+		                                      newFrame->ab_exposure, coarsestLvl, 0, &r));
+		double lr[5];
+		int ok = dso_b200_track_replay_abort(&r, minResForAbort.v, lr);
+		for (int i = 0; i < 5; i++) lastResiduals[i] = lr[i];
+		for (int i = 0; i < 3; i++) lastFlowIndicators[i] = r.lastFlowIndicators[i];
+		bool aborted = false;
+		for (int q = 0; q < r.n_passes; q++) if (r.pass_rmse[q] > 1.5 * minResForAbort[r.pass_level[q]]) aborted = true;
+		if (!aborted) { from12(r.pose, lastToNew_out); aff_g2l_out.a = r.aff_a; aff_g2l_out.b = r.aff_b; }   // :727-728
+		return ok != 0;
+	}
+
+	// Vec6 calcRes(int lvl, const SE3& refToNew, AffLight aff_g2l, float cutoffTH)   CoarseTracker.cpp:359
+	Vec6 calcRes(int lvl, const SE3& refToNew, AffLight aff_g2l, float cutoffTH)
+	{
+		double p[12];
+		pose12(refToNew, p);
+		Vec6 rs;
+		DSO_B200_CHECK(dso_b200_calc_res(dev->ctx, trk, newFrame->frame_slot, lvl, p, aff_g2l.a, aff_g2l.b, newFrame->ab_exposure, cutoffTH, rs.v));
+		return rs;
+	}
+	// void calcGSSSE(int lvl, Mat88& H_out, Vec8& b_out, const SE3& refToNew, AffLight aff_g2l)   CoarseTracker.cpp:296
+	void calcGSSSE(int lvl, Mat88& H_out, Vec8& b_out, const SE3& refToNew, AffLight aff_g2l)
+	{
+		(void)lvl; (void)refToNew; (void)aff_g2l;   // always follows calcRes on the same state (:584-595, :667-687)
+		DSO_B200_CHECK(dso_b200_calc_gs(dev->ctx, trk, H_out.m, b_out.v));
+	}
+
+	FrameHessian* lastRef;
+	FrameHessian* newFrame;
+	AffLight lastRef_aff_g2l;
+	double lastResiduals[5];       // Vec5
+	double lastFlowIndicators[3];  // Vec3
+	double firstCoarseRMSE;
+private:
+	DeviceContext* dev;
+	int trk;
+	float fx0, fy0, cx0, cy0;
+};
+
+}   // namespace dso
