@@ -58,6 +58,9 @@ SIGNATURES = {
                                            C.c_double, C.c_double, C.c_float]),
     "dso_b200_calc_res": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, f64p, C.c_double, C.c_double, C.c_float, C.c_float, f64p]),
     "dso_b200_calc_gs": (C.c_int, [vp, C.c_int, f64p, f64p]),
+    "dso_b200_calc_res_noalloc": (C.c_int, [vp, C.c_int, vp, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float,
+                                            f64p, C.c_double, C.c_double, C.c_float, C.c_double, C.c_double, C.c_float, C.c_float,
+                                            vp, vp]),
     "dso_b200_calc_res_debug": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, f64p, C.c_double, C.c_double, C.c_float, C.c_float, u8p, f32p]),
     "dso_b200_track_opts_default": (None, [C.POINTER(TrackOpts)]),
     "dso_b200_track_batched": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, f64p, C.c_double, C.c_double, C.c_float, C.c_int,
@@ -99,6 +102,20 @@ def load():
             fn.argtypes = args
         _LIB = L
     return _LIB
+
+
+NOALLOC_MAX_POINTS = 65536
+
+
+def calc_res_noalloc(cloud_ptr, n_points, frame_ptr, w, h, is_level0, K_level, pose12, ref_a, ref_b, ref_exposure,
+                     a, b, new_exposure, cutoff, stream, sums_ptr):
+    """Raw call of dso_b200_calc_res_noalloc (device addresses as ints); returns (rc, error text)."""
+    L = load()
+    fx, fy, cx, cy = K_level
+    rc = L.dso_b200_calc_res_noalloc(cloud_ptr, n_points, frame_ptr, w, h, int(is_level0), fx, fy, cx, cy,
+                                     np.ascontiguousarray(pose12, dtype=np.float64), ref_a, ref_b, ref_exposure,
+                                     a, b, new_exposure, cutoff, stream, sums_ptr)
+    return rc, L.dso_b200_last_error().decode()
 
 
 def _ptrs(arrs):

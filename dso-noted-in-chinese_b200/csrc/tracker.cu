@@ -1211,3 +1211,81 @@ extern "C" int dso_b200_track_frame(dso_b200_ctx* ctx, int trk, int frame_slot, 
 	if (rc) return rc;
 	return dso_b200_track_fetch(ctx, trk, nHyp, out);
 }
+
+// ---- evaluation without any allocation -----------------------------------------------------------------
+// dso_b200_calc_res_noalloc: one calcRes + calcGSSSE pass for callers that must not allocate (see the header).
+// The per-CTA partial sums and the "last CTA done" ticket that track_eval_kernel needs live in this fixed
+// array instead of cudaMalloc'ed context memory.  It exists once per GPU that loads the library and is
+// shared by every call, so calls that overlap on a GPU race on it.
+#define NOALLOC_MAX_CTAS (DSO_B200_NOALLOC_MAX_POINTS / EVAL_THREADS)
+#define NOALLOC_TICKET_FLOATS 64                       /* 256 bytes: the ticket word, padded */
+static __device__ __align__(256) float g_noalloc_scratch[NOALLOC_TICKET_FLOATS + NOALLOC_MAX_CTAS * S_COUNT];
+
+// In host code `g_noalloc_scratch` is only a handle for the runtime, not a device address; the address the
+// kernel must be given comes from cudaGetSymbolAddress, looked up once per device with that device current.
+static float* noalloc_scratch_ptr(int device)
+{
+	static float* ptrs[64] = { nullptr };
+	if (device < 0 || device >= 64) { dso_set_error("dso_b200_calc_res_noalloc: device index %d not supported", device); return nullptr; }
+	if (!ptrs[device])
+	{
+		float* p = nullptr;
+		cudaError_t e = cudaGetSymbolAddress((void**)&p, g_noalloc_scratch);
+		if (e != cudaSuccess || !p)
+		{
+			dso_set_error("dso_b200_calc_res_noalloc: cudaGetSymbolAddress failed on device %d: %s", device, cudaGetErrorString(e));
+			return nullptr;
+		}
+		ptrs[device] = p;
+	}
+	return ptrs[device];
+}
+
+extern "C" int dso_b200_calc_res_noalloc(const float* cloud_dev, int n_points, const float* frame_dev, int w, int h,
+                                         int is_level0, float fx, float fy, float cx, float cy,
+                                         const double* refToNew12, double ref_aff_a, double ref_aff_b, float ref_ab_exposure,
+                                         double aff_a, double aff_b, float new_ab_exposure, float cutoffTH,
+                                         void* stream, float* sums52_dev)
+{
+	ARG_CHECK(cloud_dev && frame_dev && refToNew12 && sums52_dev, "null pointer argument");
+	ARG_CHECK(n_points >= 0 && w >= 8 && h >= 8, "bad sizes");
+	if (n_points > DSO_B200_NOALLOC_MAX_POINTS)
+	{
+		dso_set_error("dso_b200_calc_res_noalloc: n_points = %d exceeds DSO_B200_NOALLOC_MAX_POINTS = %d (the scratch array is "
+		              "fixed-size); use dso_b200_calc_res with a context for larger clouds", n_points, DSO_B200_NOALLOC_MAX_POINTS);
+		return DSO_B200_E_LIMIT;
+	}
+	ARG_CHECK(((reinterpret_cast<size_t>(cloud_dev) | reinterpret_cast<size_t>(frame_dev)) & 15) == 0, "cloud_dev / frame_dev must be 16-byte aligned");
+	int device = -1;
+	CK(cudaGetDevice(&device));
+	float* scratch = noalloc_scratch_ptr(device);
+	if (!scratch) return DSO_B200_E_CUDA;
+	cudaStream_t st = (cudaStream_t)stream;
+
+	// the same float quantities as CoarseTracker.cpp:375-385, for this single level
+	TrackLevels TL;
+	memset(&TL, 0, sizeof(TL));
+	TL.levels = 1;
+	TL.w[0] = w; TL.h[0] = h; TL.fx[0] = fx; TL.fy[0] = fy; TL.cx[0] = cx; TL.cy[0] = cy;
+	const float K[9] = { fx, 0, cx, 0, fy, cy, 0, 0, 1 };
+	mat33f_inverse(K, TL.Ki[0]);
+	TL.pc_n[0] = n_points;
+	TL.ref_a = ref_aff_a; TL.ref_b = ref_aff_b; TL.ref_exposure = ref_ab_exposure; TL.new_exposure = new_ab_exposure;
+	Pose pose; pose_from12(pose, refToNew12);
+	EvalParams P;
+	make_eval_params(TL, 0, pose, aff_a, aff_b, cutoffTH, 9.0f, P);
+	P.lvl0 = is_level0 ? 1 : 0;
+
+	// the array keeps whatever the previous call left: the ticket must start at zero (the partials are
+	// fully rewritten by this launch before anything reads them)
+	unsigned int* ticket = reinterpret_cast<unsigned int*>(scratch);
+	float* partials = scratch + NOALLOC_TICKET_FLOATS;
+	CK(cudaMemsetAsync(ticket, 0, NOALLOC_TICKET_FLOATS * sizeof(float), st));
+	int g = (n_points + EVAL_THREADS - 1) / EVAL_THREADS;
+	if (g < 1) g = 1;
+	track_eval_kernel<false><<<g, EVAL_THREADS, 0, st>>>(P, reinterpret_cast<const float4*>(cloud_dev),
+	                                                     reinterpret_cast<const float4*>(frame_dev), partials, ticket, sums52_dev,
+	                                                     nullptr, nullptr);
+	CK(cudaGetLastError());
+	return 0;
+}

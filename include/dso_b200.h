@@ -82,6 +82,42 @@ int dso_b200_calc_res(dso_b200_ctx* ctx, int trk, int frame_slot, int lvl, const
  * the points kept by the last dso_b200_calc_res on this tracker slot, with the 1/n and SCALE_*
  * factors applied exactly as :338-353 (n = padded buf_warped_n). */
 int dso_b200_calc_gs(dso_b200_ctx* ctx, int trk, double* H64, double* b8);
+/* calcRes + calcGSSSE for callers that cannot allocate GPU memory.  (No counterpart in the reference: it
+ * exists because of how this library is embedded, not because of anything DSO does.)
+ *
+ * Who needs it: DSO's tracking thread has a per-frame deadline and shares the GPU with the mapping thread's
+ * bundle-adjustment work.  cudaMalloc / cudaFree stall the whole device while they run and can fail when
+ * another component (the mapper, a host application's memory pool) already owns the memory, so a tracker
+ * embedded in such a process is often forbidden from allocating after start-up -- and creating a
+ * dso_b200_ctx (which reserves pyramids, clouds and work buffers) counts as allocating.  This entry point
+ * needs no context: the caller hands in its own device buffers, and the only work memory the kernel needs
+ * (per-block partial sums and a completion counter) is a fixed array compiled into the library.  It calls
+ * no cudaMalloc, cudaFree or other allocating routine.
+ *
+ * Inputs (device memory of the current CUDA device, 16-byte aligned):
+ *   cloud_dev  n_points x 4 floats (u, v, idepth, color), the reference cloud of one pyramid level
+ *   frame_dev  w*h x 4 floats (I, dx, dy, unused), that level of the new frame
+ *   fx,fy,cx,cy intrinsics of THAT level; is_level0 != 0 enables the flow indicators (CoarseTracker.cpp:416)
+ *   pose / affine / exposure / cut-off as for dso_b200_calc_res; stream is a cudaStream_t (NULL = default)
+ * Output: sums52_dev, 52 floats in device memory, written asynchronously on `stream`:
+ *   [0] E  [1] sumSquaredShiftT  [2] sumSquaredShiftRT  [3] sumSquaredShiftNum  [4] numTermsInE  [5] numSaturated
+ *   [6] numTermsInWarped (unpadded)  [8..43] upper triangle (row-major, r<=c) of sum w*J*J^T  [44..51] sum w*J*r
+ *   i.e. the reference's Vec6 is [E, [4], [1]/([3]+0.1), 0, [2]/([3]+0.1), [5]/[4]] and H, b follow from
+ *   [8..51] times 1/n (n = [6] rounded up to a multiple of 4) and the SCALE_* factors of CoarseTracker.cpp:338-353.
+ *
+ * Limits and rules:
+ *   - n_points <= DSO_B200_NOALLOC_MAX_POINTS; larger clouds are rejected with DSO_B200_E_LIMIT.
+ *   - the fixed array (about 53 KB) is held by every GPU that loads the library until the process exits.
+ *   - all calls share that array and it keeps the previous call's contents (this function clears the part
+ *     that must start at zero); two calls that overlap on one GPU -- different streams or threads -- race.
+ *   - the first call on each device looks up the array's device address; make that first call before
+ *     starting any stream capture. */
+#define DSO_B200_NOALLOC_MAX_POINTS 65536
+int dso_b200_calc_res_noalloc(const float* cloud_dev, int n_points, const float* frame_dev, int w, int h,
+                              int is_level0, float fx, float fy, float cx, float cy,
+                              const double* refToNew12, double ref_aff_a, double ref_aff_b, float ref_ab_exposure,
+                              double aff_a, double aff_b, float new_ab_exposure, float cutoffTH,
+                              void* stream, float* sums52_dev);
 /* Debug / parity: per reference point of level lvl of the last calc_res, in cloud order:
  * status (0 skipped, 1 saturated, 2 kept) and the 8 values the reference appends to buf_warped_*
  * (idepth,u,v,dx,dy,residual,weight,refColor; CoarseTracker.cpp:476-483).  Re-runs the evaluation. */
