@@ -1,15 +1,1218 @@
-// K3-K5 placeholder translation unit (filled in by the BA kernels).
+// K3-K5 -- windowed photometric BA: linearisation fused with the top-Hessian and Schur-complement
+// accumulation (reference: FullSystem/Residuals.cpp:78-347, OptimizationBackend/AccumulatedTopHessian.{h,cpp},
+// AccumulatedSCHessian.{h,cpp}, EnergyFunctional.cpp:209-274, EnergyFunctionalStructs.cpp:39-49).
+//
+//   ba_linearize_kernel     PointFrameResidual::linearize: 8 lanes per residual (one per pattern pixel), the
+//                           8-term sums taken in index order through shuffles, so energies, state decisions
+//                           and the RawResidualJacobian are bit-identical to the reference's scalar loop.
+//   ba_apply_res_kernel     applyRes(true) + EFResidual::takeDataF (the J "swap" is a per-residual buffer flip).
+//   ba_accum_top_kernel     addPoint<0>: residuals pre-sorted by (host,target); one CTA per chunk of 64
+//                           residuals of one pair stages them in shared memory, then thread e owns entry e of the
+//                           13x13 block and sums it over the chunk in order -- no atomics, no cross-thread reduce.
+//   ba_point_sums_kernel    per-point Hdd / bd / Hcd in residualsAll order.
+//   ba_stitch_top_kernel    stitchDoubleInternal + symmetrisation: chunk partials summed in index order in FP64,
+//                           adjoint sandwiches in FP64, pairs visited in the reference's order.
+//   ba_schur_*              AccumulatedSCHessianSSE::addPoint as per-host "sum_p w_p a_p a_p^T" with thread-owned
+//                           output entries over chunks of 16 points, then two FP64 stitch stages that write every
+//                           contribution to scratch and gather them per output block in a fixed order.
+// All of it is FP32 gather/outer-product work bound by L2 latency at the window sizes of BASELINE configs[1]
+// (12 k residuals x ~850 B), HBM-bound only for the 100 k-point sweep.
 #include "common.cuh"
-struct BAWorkspace { int dummy; };
-int ba_create(dso_b200_ctx* ctx) { ctx->ba = nullptr; return 0; }
-void ba_destroy(dso_b200_ctx* ctx) { (void)ctx; }
-#define NOT_YET { dso_set_error("%s: BA kernels not built into this library yet", __func__); return DSO_B200_E_STATE; }
-extern "C" int dso_b200_ba_set_window(dso_b200_ctx*, int, const int*, int, int, float, float, float, float, const float*) NOT_YET
-extern "C" int dso_b200_ba_set_glue(dso_b200_ctx*, const dso_b200_precalc*, const double*, const double*, const float*, const float*) NOT_YET
-extern "C" int dso_b200_ba_set_points(dso_b200_ctx*, int, const float*, const float*, const float*, const float*, const float*, const float*, const int*, const float*, const float*) NOT_YET
-extern "C" int dso_b200_ba_set_residuals(dso_b200_ctx*, int, const int*, const int*, const int*, const double*, const unsigned char*, const unsigned char*) NOT_YET
-extern "C" int dso_b200_ba_linearize(dso_b200_ctx*, int*, float*, float*, float*, float*, float*, double*) NOT_YET
-extern "C" int dso_b200_ba_apply_res(dso_b200_ctx*, unsigned char*, float*) NOT_YET
-extern "C" int dso_b200_ba_accumulate_A(dso_b200_ctx*, double*, double*, int*, float*, float*, float*) NOT_YET
-extern "C" int dso_b200_ba_accumulate_SC(dso_b200_ctx*, double*, double*, float*, float*, float*) NOT_YET
-extern "C" int dso_b200_ba_step(dso_b200_ctx*, double*, double*, double*, double*, double*, int*) NOT_YET
+#include <algorithm>
+
+#define CPARS 4
+#define CHUNK_R 64
+#define CHUNK_P 16
+#define NTOP 91           // 55 + 30 + 6 unique entries of the 13x13 block
+#define NTOP_PAD 96
+#define JSZ 74
+#define ST_IN 0
+#define ST_OOB 1
+#define ST_OUTLIER 2
+#define SCALE_IDEPTH 1.0f
+#define SCALE_F 50.0f
+#define SCALE_C 50.0f
+#define OUTLIER_TH_SUM 2500.0f     // setting_outlierTHSumComponent = 50*50
+#define HUBER_TH 9.0f              // setting_huberTH
+
+// offsets into the flattened RawResidualJacobian (RawResidualJacobian.h:40-79)
+#define J_RESF 0
+#define J_PDXI0 8
+#define J_PDXI1 14
+#define J_PDC0 20
+#define J_PDC1 24
+#define J_PDD 28
+#define J_IDX0 30
+#define J_IDX1 38
+#define J_AB0 46
+#define J_AB1 54
+#define J_IDX2 62
+#define J_ABIDX 66
+#define J_AB2 70
+
+__constant__ int c_pattern[8][2] = { {0,-2}, {-1,-1}, {1,-1}, {-2,0}, {0,0}, {2,0}, {-1,1}, {0,2} };   // settings.cpp:274
+
+struct BAParams
+{
+	int nF, w, h, nR, nP;
+	float fx, fy, cx, cy, fxi, fyi, wM3G, hM3G;
+	float frameEnergyTH[MAXF];
+	const float4* img[MAXF];
+};
+
+struct BAWorkspace
+{
+	BAParams P;
+	bool window_set, glue_set, points_set, res_set, lin_done, top_done;
+	float* d_precalc; double* d_adHost; double* d_adTarget;
+	// points
+	int capP;
+	float4* d_pt; float* d_color; float* d_weights; int* d_phost; float* d_priorF; float* d_deltaF; int* d_res_begin;
+	float* d_Hdd; float* d_bd; float* d_Hcd; float* d_HdiF; float* d_bdSumF; float* d_idh;
+	// residuals
+	int capR;
+	int* d_rpoint; int* d_rtarget; int* d_state; int* d_newState; double* d_energy; float* d_newEnergy; float* d_newEnergyWO;
+	unsigned char* d_isLin; unsigned char* d_isAct; unsigned char* d_efsel;
+	float* d_cpt; float* d_proj; float* d_J[2]; float* d_JpJdF; float* d_contrib; double* d_resEnergy;
+	int* d_perm;
+	// chunks (top): residuals sorted by pair; (schur): points by host
+	int nChunks, capChunks; int* d_chunk_start; int* d_chunk_cnt; int* d_pair_chunk_begin;   // [nF*nF+1]
+	float* d_topPartials; int* d_chunk_nres;
+	int nPC, capPC; int* d_pc_start; int* d_pc_cnt; int* d_pc_host; int* d_host_pc_begin;     // [nF+1]
+	float* d_scPartials; int scN;
+	double* d_scContrib;       // stage-1 contributions
+	// outputs
+	double* d_HA; double* d_bA; double* d_HS; double* d_bS; double* d_energy_blocks; double* d_scalars;   // [0] energy sum, [1] resInA
+	double* h_out;             // pinned: HA, bA, HS, bS, scalars
+	std::vector<int> h_rpoint, h_res_begin, h_phost;
+};
+
+static size_t al(size_t v) { return (v + 255) / 256 * 256; }
+
+int ba_create(dso_b200_ctx* ctx)
+{
+	BAWorkspace* W = new BAWorkspace();
+	memset(&W->P, 0, sizeof(W->P));
+	W->window_set = W->glue_set = W->points_set = W->res_set = W->lin_done = W->top_done = false;
+	W->capP = W->capR = W->capChunks = W->capPC = 0;
+	W->nChunks = W->nPC = 0;
+	const int N = 8 * MAXF + CPARS;
+	CK(cudaMalloc(&W->d_precalc, MAXF * MAXF * 28 * sizeof(float)));
+	CK(cudaMalloc(&W->d_adHost, MAXF * MAXF * 64 * sizeof(double)));
+	CK(cudaMalloc(&W->d_adTarget, MAXF * MAXF * 64 * sizeof(double)));
+	CK(cudaMalloc(&W->d_pair_chunk_begin, (MAXF * MAXF + 1) * sizeof(int)));
+	CK(cudaMalloc(&W->d_host_pc_begin, (MAXF + 1) * sizeof(int)));
+	CK(cudaMalloc(&W->d_HA, (size_t)N * N * sizeof(double)));
+	CK(cudaMalloc(&W->d_bA, N * sizeof(double)));
+	CK(cudaMalloc(&W->d_HS, (size_t)N * N * sizeof(double)));
+	CK(cudaMalloc(&W->d_bS, N * sizeof(double)));
+	CK(cudaMalloc(&W->d_scalars, 8 * sizeof(double)));
+	// stage-1 contributions: per (i,j): C1,C2 (64 each), C3,C4 (MAXF*64 each), CEh,CEt (32 each), Cbh,Cbt (8 each)
+	CK(cudaMalloc(&W->d_scContrib, (size_t)MAXF * MAXF * (128 + 2 * MAXF * 64 + 64 + 16) * sizeof(double)));
+	CK(cudaHostAlloc((void**)&W->h_out, (2 * (size_t)N * N + 2 * N + 8) * sizeof(double), cudaHostAllocDefault));
+	W->d_energy_blocks = nullptr;
+	ctx->ba = W;
+	return 0;
+}
+
+static void free_points(BAWorkspace* W)
+{
+	if (!W->capP) return;
+	cudaFree(W->d_pt); cudaFree(W->d_color); cudaFree(W->d_weights); cudaFree(W->d_phost); cudaFree(W->d_priorF); cudaFree(W->d_deltaF);
+	cudaFree(W->d_res_begin); cudaFree(W->d_Hdd); cudaFree(W->d_bd); cudaFree(W->d_Hcd); cudaFree(W->d_HdiF); cudaFree(W->d_bdSumF); cudaFree(W->d_idh);
+	if (W->capPC) { cudaFree(W->d_pc_start); cudaFree(W->d_pc_cnt); cudaFree(W->d_pc_host); cudaFree(W->d_scPartials); }
+	W->capP = 0; W->capPC = 0;
+}
+static void free_res(BAWorkspace* W)
+{
+	if (!W->capR) return;
+	cudaFree(W->d_rpoint); cudaFree(W->d_rtarget); cudaFree(W->d_state); cudaFree(W->d_newState); cudaFree(W->d_energy); cudaFree(W->d_newEnergy);
+	cudaFree(W->d_newEnergyWO); cudaFree(W->d_isLin); cudaFree(W->d_isAct); cudaFree(W->d_efsel); cudaFree(W->d_cpt); cudaFree(W->d_proj);
+	cudaFree(W->d_J[0]); cudaFree(W->d_J[1]); cudaFree(W->d_JpJdF); cudaFree(W->d_contrib); cudaFree(W->d_resEnergy); cudaFree(W->d_perm);
+	cudaFree(W->d_energy_blocks);
+	if (W->capChunks) { cudaFree(W->d_chunk_start); cudaFree(W->d_chunk_cnt); cudaFree(W->d_topPartials); cudaFree(W->d_chunk_nres); }
+	W->capR = 0; W->capChunks = 0;
+}
+
+void ba_destroy(dso_b200_ctx* ctx)
+{
+	BAWorkspace* W = ctx->ba;
+	if (!W) return;
+	free_points(W); free_res(W);
+	cudaFree(W->d_precalc); cudaFree(W->d_adHost); cudaFree(W->d_adTarget); cudaFree(W->d_pair_chunk_begin); cudaFree(W->d_host_pc_begin);
+	cudaFree(W->d_HA); cudaFree(W->d_bA); cudaFree(W->d_HS); cudaFree(W->d_bS); cudaFree(W->d_scalars); cudaFree(W->d_scContrib);
+	cudaFreeHost(W->h_out);
+	delete W;
+	ctx->ba = nullptr;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// getInterpolatedElement33 (util/globalFuncs.h:75-89) on float4 texels
+__device__ __forceinline__ void interp33(const float4* __restrict__ img, float x, float y, int width, float& h0, float& h1, float& h2)
+{
+	const int ix = (int)x, iy = (int)y;
+	const float dx = fsub(x, (float)ix), dy = fsub(y, (float)iy);
+	const float dxdy = fmul(dx, dy);
+	const float w11 = dxdy, w01 = fsub(dy, dxdy), w10 = fsub(dx, dxdy), w00 = fadd(fsub(fsub(1.f, dx), dy), dxdy);
+	const float4* bp = img + ix + iy * width;
+	const float4 p00 = __ldg(bp), p10 = __ldg(bp + 1), p01 = __ldg(bp + width), p11 = __ldg(bp + 1 + width);
+	h0 = fadd(fadd(fadd(fmul(w11, p11.x), fmul(w01, p01.x)), fmul(w10, p10.x)), fmul(w00, p00.x));
+	h1 = fadd(fadd(fadd(fmul(w11, p11.y), fmul(w01, p01.y)), fmul(w10, p10.y)), fmul(w00, p00.y));
+	h2 = fadd(fadd(fadd(fmul(w11, p11.z), fmul(w01, p01.z)), fmul(w10, p10.z)), fmul(w00, p00.z));
+}
+
+// sum of the 8 lanes of a residual group in index order 0..7 (the reference's scalar "+=" loop)
+__device__ __forceinline__ float seq8(float v, int base)
+{
+	float s = __shfl_sync(0xffffffffu, v, base);
+#pragma unroll
+	for (int k = 1; k < 8; k++) s = fadd(s, __shfl_sync(0xffffffffu, v, base + k));
+	return s;
+}
+
+// PointFrameResidual::linearize, Residuals.cpp:78-291
+__global__ void __launch_bounds__(256) ba_linearize_kernel(BAParams B, const float* __restrict__ precalc, const float4* __restrict__ pt,
+                                                           const float* __restrict__ color, const float* __restrict__ weights,
+                                                           const int* __restrict__ phost, const int* __restrict__ rpoint,
+                                                           const int* __restrict__ rtarget, const int* __restrict__ state,
+                                                           const double* __restrict__ state_energy, const unsigned char* __restrict__ efsel,
+                                                           float* J0, float* J1, int* newState, float* newEnergy, float* newEnergyWO,
+                                                           float* cpt, float* proj, double* resEnergy)
+{
+	__shared__ float sJ[32][JSZ + 2];
+	const int tid = threadIdx.x, lane = tid & 31, g = tid >> 3, idx = tid & 7, base = lane & ~7;
+	const int r = blockIdx.x * 32 + g;
+	const bool valid = r < B.nR;
+	const int rr = valid ? r : 0;
+	const int p = rpoint[rr], t = rtarget[rr], h = phost[p];
+	const int st = state[rr];
+	const float4 P4 = __ldg(pt + p);            // u, v, idepth_scaled, idepth_zero_scaled
+	const float* pre = precalc + (size_t)(h * B.nF + t) * 28;
+	const float* R0 = pre;        // PRE_RTll_0
+	const float* t0 = pre + 9;    // PRE_tTll_0
+	const float* KRKi = pre + 12; // PRE_KRKiTll
+	const float* Kt = pre + 21;   // PRE_KtTll
+	const float affLL0 = pre[24], affLL1 = pre[25], b0 = pre[26];
+
+	// ---- centre projection at the FEJ point, projectPoint (ResidualProjections.h:69-101), dx = dy = 0 ----
+	const float Kl0 = fmul(fsub(fadd(P4.x, 0.f), B.cx), B.fxi);
+	const float Kl1 = fmul(fsub(fadd(P4.y, 0.f), B.cy), B.fyi);
+	float ptp[3];
+#pragma unroll
+	for (int k = 0; k < 3; k++) ptp[k] = fadd(dot3e(R0[k * 3], Kl0, R0[k * 3 + 1], Kl1, R0[k * 3 + 2], 1.f), fmul(t0[k], P4.w));
+	const float drescale = fdiv(1.0f, ptp[2]);
+	const float new_idepth = fmul(P4.w, drescale);
+	const float u = fmul(ptp[0], drescale), v = fmul(ptp[1], drescale);
+	const float Kuc = fadd(fmul(u, B.fx), B.cx), Kvc = fadd(fmul(v, B.fy), B.cy);
+	const bool centre_ok = (drescale > 0.f) && (Kuc > 1.1f && Kvc > 1.1f && Kuc < B.wM3G && Kvc < B.hM3G);
+
+	// ---- this lane's pattern pixel, projectPoint (ResidualProjections.h:55-65) ----
+	const float up = fadd(P4.x, (float)c_pattern[idx][0]), vp = fadd(P4.y, (float)c_pattern[idx][1]);
+	float q[3];
+#pragma unroll
+	for (int k = 0; k < 3; k++) q[k] = fadd(dot3e(KRKi[k * 3], up, KRKi[k * 3 + 1], vp, KRKi[k * 3 + 2], 1.f), fmul(Kt[k], P4.z));
+	const float Ku = fdiv(q[0], q[2]), Kv = fdiv(q[1], q[2]);
+	bool bad = !(Ku > 1.1f && Kv > 1.1f && Ku < B.wM3G && Kv < B.hM3G);
+	float h0 = 0.f, h1 = 0.f, h2 = 0.f;
+	const bool sample = valid && st != ST_OOB && centre_ok && !bad;
+	if (sample)
+	{
+		interp33(B.img[t], Ku, Kv, B.w, h0, h1, h2);
+		if (!isfinite(h0)) bad = true;
+	}
+	const unsigned badmask = (__ballot_sync(0xffffffffu, bad) >> base) & 0xffu;
+	const bool oob = (st == ST_OOB) || !centre_ok || badmask != 0;
+
+	const float col = __ldg(color + 8 * (size_t)p + idx), wgt = __ldg(weights + 8 * (size_t)p + idx);
+	const float residual = fsub(h0, fadd(fmul(affLL0, col), affLL1));
+	const float drdA = fsub(col, b0);
+	float wv = __fsqrt_rn(fdiv(OUTLIER_TH_SUM, fadd(OUTLIER_TH_SUM, fadd(fmul(h1, h1), fmul(h2, h2)))));
+	wv = fmul(0.5f, fadd(wv, wgt));
+	const float ar = fabsf(residual);
+	float hw = ar < HUBER_TH ? 1.f : fdiv(HUBER_TH, ar);
+	const float e_i = fmul(fmul(fmul(fmul(fmul(wv, wv), hw), residual), residual), fsub(2.f, hw));   // :219
+	if (hw < 1.f) hw = __fsqrt_rn(hw);
+	hw = fmul(hw, wv);
+	const float g1 = fmul(h1, hw), g2 = fmul(h2, hw);
+	const float resF = fmul(residual, hw);
+	const float ja = fmul(drdA, hw);
+
+	const float energy = seq8(e_i, base);
+	const float JI00 = seq8(fmul(g1, g1), base), JI11 = seq8(fmul(g2, g2), base), JI10 = seq8(fmul(g1, g2), base);
+	const float JA00 = seq8(fmul(ja, g1), base), JA01 = seq8(fmul(ja, g2), base), JA10 = seq8(fmul(hw, g1), base), JA11 = seq8(fmul(hw, g2), base);
+	const float AA00 = seq8(fmul(fmul(fmul(drdA, drdA), hw), hw), base), AA01 = seq8(fmul(fmul(drdA, hw), hw), base), AA11 = seq8(fmul(hw, hw), base);
+	const float wJI2 = seq8(fmul(fmul(hw, hw), fadd(fmul(g1, g1), fmul(g2, g2))), base);
+
+	if (valid)
+	{
+		if (oob)
+		{
+			// :82-83, :119-121, :197-198, :209-210: state OOB, energy of the previous state, nothing else touched
+			if (idx == 0)
+			{
+				newState[r] = ST_OOB;
+				newEnergyWO[r] = -1.f;
+				resEnergy[r] = state_energy[r];
+				if (st != ST_OOB && centre_ok) { cpt[3 * r] = Kuc; cpt[3 * r + 1] = Kvc; cpt[3 * r + 2] = new_idepth; }   // :124 precedes the pattern loop
+			}
+		}
+		else
+		{
+			const float th = fmaxf(B.frameEnergyTH[h], B.frameEnergyTH[t]);
+			const bool outlier = (energy > th) || (wJI2 < 2.f);                 // :278
+			const float eLeft = outlier ? th : energy;
+			proj[16 * (size_t)r + 2 * idx] = Ku; proj[16 * (size_t)r + 2 * idx + 1] = Kv;
+			float* s = sJ[g];
+			s[J_RESF + idx] = resF; s[J_IDX0 + idx] = g1; s[J_IDX1 + idx] = g2; s[J_AB0 + idx] = ja; s[J_AB1 + idx] = hw;
+			if (idx == 0)
+			{
+				newState[r] = outlier ? ST_OUTLIER : ST_IN;
+				newEnergy[r] = eLeft; newEnergyWO[r] = energy; resEnergy[r] = (double)eLeft;
+				cpt[3 * r] = Kuc; cpt[3 * r + 1] = Kvc; cpt[3 * r + 2] = new_idepth;
+				// d_xi_x, :159-164
+				s[J_PDXI0 + 0] = fmul(new_idepth, B.fx); s[J_PDXI0 + 1] = 0.f; s[J_PDXI0 + 2] = fmul(fmul(-new_idepth, u), B.fx);
+				s[J_PDXI0 + 3] = fmul(fmul(-u, v), B.fx); s[J_PDXI0 + 4] = fmul(fadd(1.f, fmul(u, u)), B.fx); s[J_PDXI0 + 5] = fmul(-v, B.fx);
+			}
+			else if (idx == 1)
+			{
+				// d_xi_y, :166-171
+				s[J_PDXI1 + 0] = 0.f; s[J_PDXI1 + 1] = fmul(new_idepth, B.fy); s[J_PDXI1 + 2] = fmul(fmul(-new_idepth, v), B.fy);
+				s[J_PDXI1 + 3] = fmul(-fadd(1.f, fmul(v, v)), B.fy); s[J_PDXI1 + 4] = fmul(fmul(u, v), B.fy); s[J_PDXI1 + 5] = fmul(u, B.fy);
+			}
+			else if (idx == 2)
+			{
+				// d_C_x, :138-151
+				float c2 = fmul(drescale, fsub(fmul(R0[6], u), R0[0]));
+				float c3 = fmul(fmul(fmul(B.fx, drescale), fsub(fmul(R0[7], u), R0[1])), B.fyi);
+				float c0 = fmul(Kl0, c2), c1 = fmul(Kl1, c3);
+				s[J_PDC0 + 0] = fmul(fadd(c0, u), SCALE_F); s[J_PDC0 + 1] = fmul(c1, SCALE_F);
+				s[J_PDC0 + 2] = fmul(fadd(c2, 1.f), SCALE_C); s[J_PDC0 + 3] = fmul(c3, SCALE_C);
+			}
+			else if (idx == 3)
+			{
+				// d_C_y, :143-156
+				float c2 = fmul(fmul(fmul(B.fy, drescale), fsub(fmul(R0[6], v), R0[3])), B.fxi);
+				float c3 = fmul(drescale, fsub(fmul(R0[7], v), R0[4]));
+				float c0 = fmul(Kl0, c2), c1 = fmul(Kl1, c3);
+				s[J_PDC1 + 0] = fmul(c0, SCALE_F); s[J_PDC1 + 1] = fmul(fadd(c1, v), SCALE_F);
+				s[J_PDC1 + 2] = fmul(c2, SCALE_C); s[J_PDC1 + 3] = fmul(fadd(c3, 1.f), SCALE_C);
+			}
+			else if (idx == 4)
+			{
+				// d_d, :131-132
+				s[J_PDD + 0] = fmul(fmul(fmul(drescale, fsub(t0[0], fmul(t0[2], u))), SCALE_IDEPTH), B.fx);
+				s[J_PDD + 1] = fmul(fmul(fmul(drescale, fsub(t0[1], fmul(t0[2], v))), SCALE_IDEPTH), B.fy);
+				s[J_IDX2 + 0] = JI00; s[J_IDX2 + 1] = JI10; s[J_IDX2 + 2] = JI10; s[J_IDX2 + 3] = JI11;
+			}
+			else if (idx == 5) { s[J_ABIDX + 0] = JA00; s[J_ABIDX + 1] = JA01; s[J_ABIDX + 2] = JA10; s[J_ABIDX + 3] = JA11; }
+			else if (idx == 6) { s[J_AB2 + 0] = AA00; s[J_AB2 + 1] = AA01; s[J_AB2 + 2] = AA01; s[J_AB2 + 3] = AA11; }
+		}
+	}
+	__syncwarp();
+	if (valid && !oob)
+	{
+		// PointFrameResidual::J is the buffer EFResidual is not holding
+		float* dst = (efsel[r] ? J0 : J1) + (size_t)r * JSZ;
+		for (int k = idx; k < JSZ; k += 8) dst[k] = sJ[g][k];
+	}
+}
+
+// applyRes(true), Residuals.cpp:323-347 + EFResidual::takeDataF, EnergyFunctionalStructs.cpp:39-49
+__global__ void ba_apply_res_kernel(int nR, int* state, const int* __restrict__ newState, double* state_energy, const float* __restrict__ newEnergy,
+                                    unsigned char* isAct, unsigned char* efsel, const float* J0, const float* J1, float* JpJdF)
+{
+	const int r = blockIdx.x * blockDim.x + threadIdx.x;
+	if (r >= nR) return;
+	if (state[r] == ST_OOB) return;                       // can never go back from OOB
+	const int ns = newState[r];
+	if (ns == ST_IN)
+	{
+		isAct[r] = 1;
+		const unsigned char sel = efsel[r] ^ 1;            // std::swap(J, data->J)
+		efsel[r] = sel;
+		const float* J = (sel ? J1 : J0) + (size_t)r * JSZ;
+		const float d0 = J[J_PDD], d1 = J[J_PDD + 1];
+		const float a0 = fadd(fmul(J[J_IDX2 + 0], d0), fmul(J[J_IDX2 + 1], d1));
+		const float a1 = fadd(fmul(J[J_IDX2 + 2], d0), fmul(J[J_IDX2 + 3], d1));
+		float* o = JpJdF + 8 * (size_t)r;
+#pragma unroll
+		for (int k = 0; k < 6; k++) o[k] = fadd(fmul(J[J_PDXI0 + k], a0), fmul(J[J_PDXI1 + k], a1));
+		o[6] = fadd(fmul(J[J_ABIDX + 0], d0), fmul(J[J_ABIDX + 1], d1));
+		o[7] = fadd(fmul(J[J_ABIDX + 2], d0), fmul(J[J_ABIDX + 3], d1));
+	}
+	else
+		isAct[r] = 0;
+	state[r] = ns;
+	state_energy[r] = (double)newEnergy[r];
+}
+
+// deterministic double sum of per-residual energies: fixed tree per block, blocks summed in order by one thread
+__global__ void ba_energy_blocks_kernel(int n, const double* __restrict__ e, double* blocks)
+{
+	__shared__ double s[256];
+	const int i = blockIdx.x * 256 + threadIdx.x;
+	s[threadIdx.x] = i < n ? e[i] : 0.0;
+	__syncthreads();
+	for (int o = 128; o > 0; o >>= 1) { if ((int)threadIdx.x < o) s[threadIdx.x] += s[threadIdx.x + o]; __syncthreads(); }
+	if (threadIdx.x == 0) blocks[blockIdx.x] = s[0];
+}
+__global__ void ba_energy_final_kernel(int nb, const double* __restrict__ blocks, double* out)
+{
+	if (threadIdx.x == 0 && blockIdx.x == 0) { double s = 0; for (int i = 0; i < nb; i++) s += blocks[i]; out[0] = s; }
+}
+
+// AccumulatedTopHessianSSE::addPoint<0>, AccumulatedTopHessian.cpp:39-160, one chunk of one (host,target) pair
+__global__ void __launch_bounds__(128) ba_accum_top_kernel(const int* __restrict__ perm, const int* __restrict__ chunk_start,
+                                                           const int* __restrict__ chunk_cnt, const unsigned char* __restrict__ isAct,
+                                                           const unsigned char* __restrict__ isLin, const unsigned char* __restrict__ efsel,
+                                                           const float* __restrict__ J0, const float* __restrict__ J1, float* contrib,
+                                                           float* partials, int* chunk_nres)
+{
+	__shared__ float sx[CHUNK_R][10], sy[CHUNK_R][10], sw[CHUNK_R][16];   // sw: a,b,c | TR00,TR10,TR01,TR11,TR02,TR12 | BR0..5
+	__shared__ int s_n;
+	const int chunk = blockIdx.x, tid = threadIdx.x;
+	const int start = chunk_start[chunk], cnt = chunk_cnt[chunk];
+	if (tid == 0) s_n = 0;
+	__syncthreads();
+	if (tid < cnt)
+	{
+		const int r = perm[start + tid];
+		const bool act = isAct[r] && !isLin[r];                             // :57
+		float x[10], y[10], w[15];
+		if (act)
+		{
+			const float* J = (efsel[r] ? J1 : J0) + (size_t)r * JSZ;
+#pragma unroll
+			for (int k = 0; k < 4; k++) { x[k] = J[J_PDC0 + k]; y[k] = J[J_PDC1 + k]; }
+#pragma unroll
+			for (int k = 0; k < 6; k++) { x[4 + k] = J[J_PDXI0 + k]; y[4 + k] = J[J_PDXI1 + k]; }
+			float JI_r0 = 0.f, JI_r1 = 0.f, Jab_r0 = 0.f, Jab_r1 = 0.f, rr = 0.f;   // :107-118
+#pragma unroll
+			for (int i = 0; i < 8; i++)
+			{
+				const float ri = J[J_RESF + i];
+				JI_r0 = fadd(JI_r0, fmul(ri, J[J_IDX0 + i]));
+				JI_r1 = fadd(JI_r1, fmul(ri, J[J_IDX1 + i]));
+				Jab_r0 = fadd(Jab_r0, fmul(ri, J[J_AB0 + i]));
+				Jab_r1 = fadd(Jab_r1, fmul(ri, J[J_AB1 + i]));
+				rr = fadd(rr, fmul(ri, ri));
+			}
+			w[0] = J[J_IDX2 + 0]; w[1] = J[J_IDX2 + 1]; w[2] = J[J_IDX2 + 3];
+			w[3] = J[J_ABIDX + 0]; w[4] = J[J_ABIDX + 1]; w[5] = J[J_ABIDX + 2]; w[6] = J[J_ABIDX + 3]; w[7] = JI_r0; w[8] = JI_r1;
+			w[9] = J[J_AB2 + 0]; w[10] = J[J_AB2 + 1]; w[11] = Jab_r0; w[12] = J[J_AB2 + 3]; w[13] = Jab_r1; w[14] = rr;
+			// :142-150 per-point terms of this residual
+			const float d0 = J[J_PDD], d1 = J[J_PDD + 1];
+			const float q0 = fadd(fmul(J[J_IDX2 + 0], d0), fmul(J[J_IDX2 + 1], d1));
+			const float q1 = fadd(fmul(J[J_IDX2 + 2], d0), fmul(J[J_IDX2 + 3], d1));
+			float* c = contrib + 6 * (size_t)r;
+			c[0] = fadd(fmul(JI_r0, d0), fmul(JI_r1, d1));
+			c[1] = fadd(fmul(q0, d0), fmul(q1, d1));
+#pragma unroll
+			for (int k = 0; k < 4; k++) c[2 + k] = fadd(fmul(J[J_PDC0 + k], q0), fmul(J[J_PDC1 + k], q1));
+			atomicAdd(&s_n, 1);
+		}
+		else
+		{
+#pragma unroll
+			for (int k = 0; k < 10; k++) { x[k] = 0.f; y[k] = 0.f; }
+#pragma unroll
+			for (int k = 0; k < 15; k++) w[k] = 0.f;
+		}
+#pragma unroll
+		for (int k = 0; k < 10; k++) { sx[tid][k] = x[k]; sy[tid][k] = y[k]; }
+#pragma unroll
+		for (int k = 0; k < 15; k++) sw[tid][k] = w[k];
+	}
+	__syncthreads();
+	if (tid < NTOP)
+	{
+		float acc = 0.f;
+		if (tid < 55)
+		{
+			int r = 0, rem = tid;
+			while (rem >= 10 - r) { rem -= 10 - r; r++; }
+			const int c = r + rem;
+			for (int i = 0; i < cnt; i++)
+			{
+				const float a = sw[i][0], b = sw[i][1], cc = sw[i][2];
+				const float xc = sx[i][c], xr = sx[i][r], yc = sy[i][c], yr = sy[i][r];
+				// MatrixAccumulators.h:738-842: a*x[c]*x[r] + c*y[c]*y[r] + b*(x[c]*y[r] + y[c]*x[r])
+				const float term = fadd(fadd(fmul(fmul(a, xc), xr), fmul(fmul(cc, yc), yr)), fmul(b, fadd(fmul(xc, yr), fmul(yc, xr))));
+				acc = fadd(acc, term);
+			}
+		}
+		else if (tid < 85)
+		{
+			const int i10 = (tid - 55) / 3, k = (tid - 55) - 3 * i10;
+			for (int i = 0; i < cnt; i++)
+				acc = fadd(acc, fadd(fmul(sx[i][i10], sw[i][3 + 2 * k]), fmul(sy[i][i10], sw[i][4 + 2 * k])));   // :845-897: x*TRk0 + y*TRk1
+		}
+		else
+		{
+			const int k = tid - 85;
+			for (int i = 0; i < cnt; i++) acc = fadd(acc, sw[i][9 + k]);        // :899-913
+		}
+		partials[(size_t)chunk * NTOP_PAD + tid] = acc;
+	}
+	if (tid == 0) chunk_nres[chunk] = s_n;
+}
+
+// TopRight argument order of updateTopRight (AccumulatedTopHessian.cpp:134-139): TR00=JabJIdx(0,0), TR10=JabJIdx(0,1),
+// TR01=JabJIdx(1,0), TR11=JabJIdx(1,1), TR02=JI_r[0], TR12=JI_r[1]  -> sw[3..8] above is already in (k0,k1) pairs.
+
+// per-point sums in EFPoint::residualsAll order, AccumulatedTopHessian.cpp:142-160
+__global__ void ba_point_sums_kernel(int nP, const int* __restrict__ res_begin, const unsigned char* __restrict__ isAct,
+                                     const unsigned char* __restrict__ isLin, const float* __restrict__ contrib,
+                                     float* Hdd, float* bd, float* Hcd)
+{
+	const int p = blockIdx.x * blockDim.x + threadIdx.x;
+	if (p >= nP) return;
+	float bd_acc = 0.f, Hdd_acc = 0.f, h0 = 0.f, h1 = 0.f, h2 = 0.f, h3 = 0.f;
+	for (int r = res_begin[p]; r < res_begin[p + 1]; r++)
+	{
+		if (!isAct[r] || isLin[r]) continue;
+		const float* c = contrib + 6 * (size_t)r;
+		bd_acc = fadd(bd_acc, c[0]); Hdd_acc = fadd(Hdd_acc, c[1]);
+		h0 = fadd(h0, c[2]); h1 = fadd(h1, c[3]); h2 = fadd(h2, c[4]); h3 = fadd(h3, c[5]);
+	}
+	Hdd[p] = Hdd_acc; bd[p] = bd_acc;
+	Hcd[4 * p] = h0; Hcd[4 * p + 1] = h1; Hcd[4 * p + 2] = h2; Hcd[4 * p + 3] = h3;
+}
+
+// index of entry (i,j) of the symmetric 13x13 block in the 91-vector written by ba_accum_top_kernel
+__device__ __forceinline__ int top_index(int i, int j)
+{
+	if (i > j) { int t = i; i = j; j = t; }
+	if (j < 10) return i * 10 - (i * (i - 1)) / 2 + (j - i);
+	if (i < 10) return 55 + 3 * i + (j - 10);
+	// bottom-right 3x3: (10,10)->0 (10,11)->1 (10,12)->2 (11,11)->3 (11,12)->4 (12,12)->5
+	const int a = i - 10, b = j - 10;
+	return 85 + (a == 0 ? b : (a == 1 ? 2 + b : 5));
+}
+
+// stitchDoubleInternal (AccumulatedTopHessian.cpp:259-310, tid = -1 branch) + AccumulatedTopHessian.h:126-138
+__global__ void __launch_bounds__(256) ba_stitch_top_kernel(int nF, const int* __restrict__ pair_chunk_begin, const float* __restrict__ partials,
+                                                            const int* __restrict__ chunk_nres, const double* __restrict__ adHost,
+                                                            const double* __restrict__ adTarget, double* Hout, double* bout, double* scalars)
+{
+	extern __shared__ double sm[];
+	const int N = 8 * nF + CPARS;
+	double* H = sm;                 // N*N
+	double* b = H + N * N;          // N
+	double* accH = b + N;           // 169
+	double* AH = accH + 176;        // 64
+	double* AT = AH + 64;           // 64
+	double* T1 = AT + 64;           // 3*64
+	__shared__ int s_nres;
+	const int tid = threadIdx.x;
+	for (int i = tid; i < N * N + N; i += 256) sm[i] = 0.0;
+	if (tid == 0) s_nres = 0;
+	__syncthreads();
+	for (int k = 0; k < nF * nF; k++)
+	{
+		const int h = k % nF, t = k / nF;
+		const int hIdx = CPARS + h * 8, tIdx = CPARS + t * 8;
+		const int cb = pair_chunk_begin[k], ce = pair_chunk_begin[k + 1];
+		if (cb == ce) continue;      // acc.num == 0
+		if (tid < 169)
+		{
+			const int i = tid / 13, j = tid - 13 * i;
+			const int e = top_index(i, j);
+			double s = 0.0;
+			for (int c = cb; c < ce; c++) s += (double)partials[(size_t)c * NTOP_PAD + e];
+			accH[tid] = s;
+		}
+		else if (tid < 169 + 64) AH[tid - 169] = adHost[(size_t)k * 64 + tid - 169];
+		if (tid >= 192) AT[tid - 192] = adTarget[(size_t)k * 64 + tid - 192];
+		if (tid == 0) { int n = 0; for (int c = cb; c < ce; c++) n += chunk_nres[c]; s_nres += n; }
+		__syncthreads();
+		if (tid < 192)
+		{
+			const int s = tid >> 6, o = tid & 63, i = o >> 3, j = o & 7;
+			const double* L = (s == 1) ? AT : AH;
+			double v = 0.0;
+#pragma unroll
+			for (int q = 0; q < 8; q++) v += L[i * 8 + q] * accH[(CPARS + q) * 13 + CPARS + j];
+			T1[s * 64 + o] = v;
+		}
+		__syncthreads();
+		if (tid < 192)
+		{
+			const int s = tid >> 6, o = tid & 63, i = o >> 3, j = o & 7;
+			const double* R = (s == 0) ? AH : AT;
+			double v = 0.0;
+#pragma unroll
+			for (int q = 0; q < 8; q++) v += T1[s * 64 + i * 8 + q] * R[j * 8 + q];
+			const int ro = (s == 1) ? tIdx : hIdx, co = (s == 0) ? hIdx : tIdx;
+			H[(ro + i) * N + co + j] += v;
+		}
+		else
+		{
+			const int o = tid - 192;   // 64 threads: calibration columns, 32 for host rows, 32 for target rows
+			const int s = o >> 5, i = (o & 31) >> 2, j = o & 3;
+			const double* L = s ? AT : AH;
+			double v = 0.0;
+#pragma unroll
+			for (int q = 0; q < 8; q++) v += L[i * 8 + q] * accH[(CPARS + q) * 13 + j];
+			H[((s ? tIdx : hIdx) + i) * N + j] += v;
+		}
+		__syncthreads();
+		if (tid < 16)
+		{
+			const int s = tid >> 3, i = tid & 7;
+			const double* L = s ? AT : AH;
+			double v = 0.0;
+#pragma unroll
+			for (int q = 0; q < 8; q++) v += L[i * 8 + q] * accH[(CPARS + q) * 13 + CPARS + 8];
+			b[(s ? tIdx : hIdx) + i] += v;
+		}
+		else if (tid < 32) { const int i = (tid - 16) >> 2, j = (tid - 16) & 3; H[i * N + j] += accH[i * 13 + j]; }
+		else if (tid < 36) b[tid - 32] += accH[(tid - 32) * 13 + CPARS + 8];
+		__syncthreads();
+	}
+	// "make diagonal by copying over parts"
+	for (int e = tid; e < nF * 32; e += 256)
+	{
+		const int h = e / 32, i = (e % 32) / 8, j = e % 8;
+		H[i * N + CPARS + h * 8 + j] = H[(CPARS + h * 8 + j) * N + i];
+	}
+	__syncthreads();
+	for (int e = tid; e < nF * nF * 64; e += 256)
+	{
+		const int h = e / (nF * 64), t = (e / 64) % nF, i = (e % 64) / 8, j = e % 8;
+		if (t > h) H[(CPARS + h * 8 + i) * N + CPARS + t * 8 + j] += H[(CPARS + t * 8 + j) * N + CPARS + h * 8 + i];
+	}
+	__syncthreads();
+	for (int e = tid; e < nF * nF * 64; e += 256)
+	{
+		const int h = e / (nF * 64), t = (e / 64) % nF, i = (e % 64) / 8, j = e % 8;
+		if (t > h) H[(CPARS + t * 8 + i) * N + CPARS + h * 8 + j] = H[(CPARS + h * 8 + j) * N + CPARS + t * 8 + i];
+	}
+	__syncthreads();
+	for (int i = tid; i < N * N; i += 256) Hout[i] = H[i];
+	for (int i = tid; i < N; i += 256) bout[i] = b[i];
+	if (tid == 0) scalars[1] = (double)s_nres;
+}
+
+// AccumulatedSCHessianSSE::addPoint (AccumulatedSCHessian.cpp:35-60): per-point inverse Hessian and b
+__global__ void ba_schur_prep_kernel(int nP, const int* __restrict__ res_begin, const unsigned char* __restrict__ isAct,
+                                     const float* __restrict__ Hdd, const float* __restrict__ bd, const float* __restrict__ priorF,
+                                     const float* __restrict__ deltaF, float* HdiF, float* bdSumF, float* idh)
+{
+	const int p = blockIdx.x * blockDim.x + threadIdx.x;
+	if (p >= nP) return;
+	int ngood = 0;
+	for (int r = res_begin[p]; r < res_begin[p + 1]; r++) ngood += isAct[r] ? 1 : 0;
+	if (ngood == 0) { HdiF[p] = 0.f; bdSumF[p] = 0.f; idh[p] = 0.f; return; }
+	float H = fadd(fadd(Hdd[p], 0.f), priorF[p]);        // Hdd_accAF + Hdd_accLF + priorF
+	if (H < 1e-10) H = 1e-10;
+	idh[p] = H;
+	HdiF[p] = (float)(1.0 / (double)H);
+	float bs = fadd(bd[p], 0.f);
+	bs = fadd(bs, fmul(priorF[p], deltaF[p]));            // shiftPriorToZero = true (EnergyFunctional.cpp:263, 271)
+	bdSumF[p] = bs;
+}
+
+// accD / accE / accEB / accHcc / accbc contributions of one chunk of points of one host frame
+// (AccumulatedSCHessian.cpp:64-84): thread-owned output entries, points visited in order.
+__global__ void __launch_bounds__(256) ba_schur_accum_kernel(int nF, const int* __restrict__ pc_start, const int* __restrict__ pc_cnt,
+                                                             const int* __restrict__ res_begin, const int* __restrict__ rtarget,
+                                                             const unsigned char* __restrict__ isAct, const float* __restrict__ JpJdF,
+                                                             const float* __restrict__ HdiF, const float* __restrict__ bdSumF,
+                                                             const float* __restrict__ Hcd, float* partials, int scN)
+{
+	__shared__ float sa[CHUNK_P][MAXF * 8];     // JpJdF by target slot (0 when inactive)
+	__shared__ float swa[CHUNK_P][MAXF * 8];    // HdiF * JpJdF
+	__shared__ float sh[CHUNK_P][8];            // Hcd[4], w, w*bdSum, w*Hcd handled on the fly
+	const int chunk = blockIdx.x, tid = threadIdx.x;
+	const int start = pc_start[chunk], cnt = pc_cnt[chunk];
+	for (int i = tid; i < CHUNK_P * MAXF * 8; i += 256) { (&sa[0][0])[i] = 0.f; (&swa[0][0])[i] = 0.f; }
+	__syncthreads();
+	if (tid < cnt)
+	{
+		const int p = start + tid;
+		const float w = HdiF[p];
+		sh[tid][0] = Hcd[4 * p]; sh[tid][1] = Hcd[4 * p + 1]; sh[tid][2] = Hcd[4 * p + 2]; sh[tid][3] = Hcd[4 * p + 3];
+		sh[tid][4] = w; sh[tid][5] = fmul(w, bdSumF[p]);
+		for (int r = res_begin[p]; r < res_begin[p + 1]; r++)
+		{
+			if (!isAct[r]) continue;
+			const int t = rtarget[r];
+#pragma unroll
+			for (int k = 0; k < 8; k++) { const float a = JpJdF[8 * (size_t)r + k]; sa[tid][t * 8 + k] = a; swa[tid][t * 8 + k] = fmul(w, a); }
+		}
+	}
+	__syncthreads();
+	const int nD = nF * nF * 64, nE = nF * 32, nEB = nF * 8;
+	float* out = partials + (size_t)chunk * scN;
+	for (int e = tid; e < nD + nE + nEB + 20; e += 256)
+	{
+		float acc = 0.f;
+		if (e < nD)
+		{
+			const int t1 = e / (nF * 64), t2 = (e / 64) % nF, i = (e % 64) / 8, j = e % 8;
+			for (int p = 0; p < cnt; p++) acc = fadd(acc, fmul(sa[p][t2 * 8 + j], swa[p][t1 * 8 + i]));       // A += (w L) R^T
+		}
+		else if (e < nD + nE)
+		{
+			const int o = e - nD, t = o / 32, i = (o % 32) / 4, c = o % 4;
+			for (int p = 0; p < cnt; p++) acc = fadd(acc, fmul(sh[p][c], swa[p][t * 8 + i]));                   // accE: L = JpJdF, R = Hcd
+		}
+		else if (e < nD + nE + nEB)
+		{
+			const int o = e - nD - nE;
+			for (int p = 0; p < cnt; p++) acc = fadd(acc, fmul(sh[p][5], sa[p][o]));                            // accEB: (HdiF*bdSumF) * JpJdF
+		}
+		else if (e < nD + nE + nEB + 16)
+		{
+			const int o = e - nD - nE - nEB, i = o / 4, j = o % 4;
+			for (int p = 0; p < cnt; p++) acc = fadd(acc, fmul(sh[p][j], fmul(sh[p][4], sh[p][i])));            // accHcc: (w Hcd) Hcd^T
+		}
+		else
+		{
+			const int i = e - nD - nE - nEB - 16;
+			for (int p = 0; p < cnt; p++) acc = fadd(acc, fmul(sh[p][5], sh[p][i]));                            // accbc: (bdSumF*HdiF) * Hcd
+		}
+		out[e] = acc;
+	}
+}
+
+// contribution buffer layout per (i,j): [C1 64][C2 64][C3 MAXF*64][C4 MAXF*64][CEh 32][CEt 32][Cbh 8][Cbt 8]
+#define SCC_STRIDE (128 + 2 * MAXF * 64 + 64 + 16)
+#define SCC_C1 0
+#define SCC_C2 64
+#define SCC_C3 128
+#define SCC_C4 (128 + MAXF * 64)
+#define SCC_CEH (128 + 2 * MAXF * 64)
+#define SCC_CET (SCC_CEH + 32)
+#define SCC_CBH (SCC_CEH + 64)
+#define SCC_CBT (SCC_CEH + 72)
+
+__device__ __forceinline__ void mm8(const double* A, const double* Bm, double* C, bool transB, int o)
+{
+	const int i = o >> 3, j = o & 7;
+	double v = 0.0;
+#pragma unroll
+	for (int q = 0; q < 8; q++) v += A[i * 8 + q] * (transB ? Bm[j * 8 + q] : Bm[q * 8 + j]);
+	C[o] = v;
+}
+
+// stage 1 of stitchDoubleInternal (AccumulatedSCHessian.cpp:86-165) for the pair (i = host, j = target):
+// every adjoint sandwich that involves accD[i,j,*], accE[i,j], accEB[i,j], written out as separate contributions.
+__global__ void __launch_bounds__(64) ba_schur_stage1_kernel(int nF, const int* __restrict__ host_pc_begin, const float* __restrict__ partials,
+                                                             int scN, const double* __restrict__ adHost, const double* __restrict__ adTarget,
+                                                             double* contrib)
+{
+	__shared__ double D[64], S1[64], Q[64], AHij[64], ATij[64], AHik[64], ATik[64], E[32], EB[8];
+	const int i = blockIdx.x % nF, j = blockIdx.x / nF, o = threadIdx.x;
+	const int ij = i + nF * j;
+	const int cb = host_pc_begin[i], ce = host_pc_begin[i + 1];
+	const int nD = nF * nF * 64, nE = nF * 32;
+	double* out = contrib + (size_t)ij * SCC_STRIDE;
+	AHij[o] = adHost[(size_t)ij * 64 + o]; ATij[o] = adTarget[(size_t)ij * 64 + o];
+	S1[o] = 0.0;
+	if (o < 32) { double s = 0.0; for (int c = cb; c < ce; c++) s += (double)partials[(size_t)c * scN + nD + j * 32 + o]; E[o] = s; }
+	if (o < 8) { double s = 0.0; for (int c = cb; c < ce; c++) s += (double)partials[(size_t)c * scN + nD + nE + j * 8 + o]; EB[o] = s; }
+	__syncthreads();
+	for (int k = 0; k < nF; k++)
+	{
+		const int ik = i + nF * k;
+		double s = 0.0;
+		for (int c = cb; c < ce; c++) s += (double)partials[(size_t)c * scN + (j * nF + k) * 64 + o];
+		D[o] = s;
+		AHik[o] = adHost[(size_t)ik * 64 + o]; ATik[o] = adTarget[(size_t)ik * 64 + o];
+		__syncthreads();
+		{
+			const int r = o >> 3, c = o & 7;
+			double v = 0.0, q = 0.0;
+#pragma unroll
+			for (int m = 0; m < 8; m++) { v += D[r * 8 + m] * AHik[c * 8 + m]; q += D[r * 8 + m] * ATik[c * 8 + m]; }
+			S1[o] += v;            // sum_k D[i,j,k] adHost[i,k]^T
+			Q[o] = q;              // D[i,j,k] adTarget[i,k]^T
+		}
+		__syncthreads();
+		mm8(ATij, Q, out + SCC_C3 + k * 64, false, o);   // -> block (j,k)
+		mm8(AHij, Q, out + SCC_C4 + k * 64, false, o);   // -> block (i,k)
+		__syncthreads();
+	}
+	mm8(AHij, S1, out + SCC_C1, false, o);               // -> block (i,i)
+	mm8(ATij, S1, out + SCC_C2, false, o);               // -> block (j,i)
+	if (o < 32)
+	{
+		const int r = o >> 2, c = o & 3;
+		double vh = 0.0, vt = 0.0;
+#pragma unroll
+		for (int m = 0; m < 8; m++) { vh += AHij[r * 8 + m] * E[m * 4 + c]; vt += ATij[r * 8 + m] * E[m * 4 + c]; }
+		out[SCC_CEH + o] = vh; out[SCC_CET + o] = vt;
+	}
+	if (o < 8)
+	{
+		double vh = 0.0, vt = 0.0;
+#pragma unroll
+		for (int m = 0; m < 8; m++) { vh += AHij[o * 8 + m] * EB[m]; vt += ATij[o * 8 + m] * EB[m]; }
+		out[SCC_CBH + o] = vh; out[SCC_CBT + o] = vt;
+	}
+}
+
+// stage 2: gather the contributions of every output block in a fixed order
+__global__ void __launch_bounds__(64) ba_schur_gather_kernel(int nF, int nPC, const float* __restrict__ partials, int scN,
+                                                             const double* __restrict__ contrib, double* Hout, double* bout)
+{
+	const int N = 8 * nF + CPARS, o = threadIdx.x;
+	if ((int)blockIdx.x < nF * nF)
+	{
+		const int r = blockIdx.x / nF, c = blockIdx.x % nF;
+		double v = 0.0;
+		if (r == c) for (int j = 0; j < nF; j++) v += contrib[(size_t)(r + nF * j) * SCC_STRIDE + SCC_C1 + o];
+		v += contrib[(size_t)(c + nF * r) * SCC_STRIDE + SCC_C2 + o];                                     // i = c, j = r
+		for (int i = 0; i < nF; i++) v += contrib[(size_t)(i + nF * r) * SCC_STRIDE + SCC_C3 + c * 64 + o];   // j = r, k = c
+		for (int j = 0; j < nF; j++) v += contrib[(size_t)(r + nF * j) * SCC_STRIDE + SCC_C4 + c * 64 + o];   // i = r, k = c
+		Hout[(CPARS + r * 8 + (o >> 3)) * N + CPARS + c * 8 + (o & 7)] = v;
+	}
+	else
+	{
+		// calibration rows / columns, b, Hcc, bc
+		const int nD = nF * nF * 64, nE = nF * 32, nEB = nF * 8;
+		for (int e = o; e < nF * 32; e += 64)
+		{
+			const int r = e / 32, q = e % 32;
+			double v = 0.0;
+			for (int j = 0; j < nF; j++) v += contrib[(size_t)(r + nF * j) * SCC_STRIDE + SCC_CEH + q];
+			for (int i = 0; i < nF; i++) v += contrib[(size_t)(i + nF * r) * SCC_STRIDE + SCC_CET + q];
+			const int row = CPARS + r * 8 + (q >> 2), col = q & 3;
+			Hout[row * N + col] = v;
+			Hout[col * N + row] = v;                                  // AccumulatedSCHessian.h:130-134
+		}
+		for (int e = o; e < nF * 8; e += 64)
+		{
+			const int r = e / 8, q = e % 8;
+			double v = 0.0;
+			for (int j = 0; j < nF; j++) v += contrib[(size_t)(r + nF * j) * SCC_STRIDE + SCC_CBH + q];
+			for (int i = 0; i < nF; i++) v += contrib[(size_t)(i + nF * r) * SCC_STRIDE + SCC_CBT + q];
+			bout[CPARS + e] = v;
+		}
+		if (o < 20)
+		{
+			double v = 0.0;
+			for (int c = 0; c < nPC; c++) v += (double)partials[(size_t)c * scN + nD + nE + nEB + o];
+			if (o < 16) Hout[(o >> 2) * N + (o & 3)] = v; else bout[o - 16] = v;
+		}
+	}
+}
+
+// ---- host side --------------------------------------------------------------------------------------------
+#define BA_CHECK(cond, msg) do { if (!(cond)) { dso_set_error("%s: %s", __func__, msg); return DSO_B200_E_STATE; } } while (0)
+
+extern "C" int dso_b200_ba_set_window(dso_b200_ctx* ctx, int nF, const int* frame_slots, int w, int h,
+                                      float fx, float fy, float cx, float cy, const float* frameEnergyTH)
+{
+	ARG_CHECK(ctx && ctx->ba && frame_slots && frameEnergyTH, "null argument");
+	ARG_CHECK(nF >= 2 && nF <= MAXF, "nF must be 2..8");
+	BAWorkspace* W = ctx->ba;
+	BAParams& P = W->P;
+	for (int i = 0; i < nF; i++)
+	{
+		ARG_CHECK(frame_slots[i] >= 0 && frame_slots[i] < ctx->n_slots && ctx->slots[frame_slots[i]].valid, "frame slot empty");
+		ARG_CHECK(ctx->slots[frame_slots[i]].w == w && ctx->slots[frame_slots[i]].h == h, "frame size mismatch");
+		P.img[i] = ctx->slots[frame_slots[i]].pyr[0];
+		P.frameEnergyTH[i] = frameEnergyTH[i];
+	}
+	P.nF = nF; P.w = w; P.h = h;
+	// CalibHessian::setValueScaled, HessianBlocks.h:383-397; globalCalib.cpp:70-71
+	P.fx = fx; P.fy = fy; P.cx = cx; P.cy = cy;
+	P.fxi = 1.0f / fx; P.fyi = 1.0f / fy;
+	P.wM3G = (float)(w - 3); P.hM3G = (float)(h - 3);
+	W->window_set = true; W->glue_set = false; W->res_set = false; W->lin_done = false; W->top_done = false;
+	return 0;
+}
+
+extern "C" int dso_b200_ba_set_glue(dso_b200_ctx* ctx, const dso_b200_precalc* precalc, const double* adHost,
+                                    const double* adTarget, const float* adHTdeltaF, const float* cDeltaF4)
+{
+	ARG_CHECK(ctx && ctx->ba && precalc && adHost && adTarget, "null argument");
+	(void)adHTdeltaF; (void)cDeltaF4;   // only read by the linearised-residual mode (addPoint<1>), not implemented (N2)
+	BAWorkspace* W = ctx->ba;
+	BA_CHECK(W->window_set, "call dso_b200_ba_set_window first");
+	CK(cudaSetDevice(ctx->device));
+	const int n2 = W->P.nF * W->P.nF;
+	CK(cudaMemcpyAsync(W->d_precalc, precalc, (size_t)n2 * sizeof(dso_b200_precalc), cudaMemcpyHostToDevice, ctx->stream));
+	CK(cudaMemcpyAsync(W->d_adHost, adHost, (size_t)n2 * 64 * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+	CK(cudaMemcpyAsync(W->d_adTarget, adTarget, (size_t)n2 * 64 * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+	CK(cudaStreamSynchronize(ctx->stream));
+	W->glue_set = true;
+	return 0;
+}
+
+extern "C" int dso_b200_ba_set_points(dso_b200_ctx* ctx, int nP, const float* u, const float* v, const float* idepth_scaled,
+                                      const float* idepth_zero_scaled, const float* color8, const float* weights8,
+                                      const int* host, const float* priorF, const float* deltaF)
+{
+	ARG_CHECK(ctx && ctx->ba && u && v && idepth_scaled && idepth_zero_scaled && color8 && weights8 && host && priorF && deltaF, "null argument");
+	ARG_CHECK(nP >= 1, "nP must be >= 1");
+	BAWorkspace* W = ctx->ba;
+	BA_CHECK(W->window_set, "call dso_b200_ba_set_window first");
+	CK(cudaSetDevice(ctx->device));
+	const int nF = W->P.nF;
+	for (int i = 0; i < nP; i++)
+	{
+		ARG_CHECK(host[i] >= 0 && host[i] < nF, "point host out of range");
+		ARG_CHECK(i == 0 || host[i] >= host[i - 1], "points must be grouped by host frame (EnergyFunctional::allPoints order)");
+	}
+	if (nP > W->capP)
+	{
+		free_points(W);
+		const size_t n = (size_t)nP;
+		CK(cudaMalloc(&W->d_pt, n * sizeof(float4))); CK(cudaMalloc(&W->d_color, n * 8 * sizeof(float))); CK(cudaMalloc(&W->d_weights, n * 8 * sizeof(float)));
+		CK(cudaMalloc(&W->d_phost, n * sizeof(int))); CK(cudaMalloc(&W->d_priorF, n * sizeof(float))); CK(cudaMalloc(&W->d_deltaF, n * sizeof(float)));
+		CK(cudaMalloc(&W->d_res_begin, (n + 1) * sizeof(int)));
+		CK(cudaMalloc(&W->d_Hdd, n * sizeof(float))); CK(cudaMalloc(&W->d_bd, n * sizeof(float))); CK(cudaMalloc(&W->d_Hcd, n * 4 * sizeof(float)));
+		CK(cudaMalloc(&W->d_HdiF, n * sizeof(float))); CK(cudaMalloc(&W->d_bdSumF, n * sizeof(float))); CK(cudaMalloc(&W->d_idh, n * sizeof(float)));
+		W->capP = nP;
+	}
+	std::vector<float4> pt(nP);
+	for (int i = 0; i < nP; i++) pt[i] = make_float4(u[i], v[i], idepth_scaled[i], idepth_zero_scaled[i]);
+	CK(cudaMemcpyAsync(W->d_pt, pt.data(), (size_t)nP * sizeof(float4), cudaMemcpyHostToDevice, ctx->stream));
+	CK(cudaMemcpyAsync(W->d_color, color8, (size_t)nP * 8 * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+	CK(cudaMemcpyAsync(W->d_weights, weights8, (size_t)nP * 8 * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+	CK(cudaMemcpyAsync(W->d_phost, host, (size_t)nP * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+	CK(cudaMemcpyAsync(W->d_priorF, priorF, (size_t)nP * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+	CK(cudaMemcpyAsync(W->d_deltaF, deltaF, (size_t)nP * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+	// Schur chunks: CHUNK_P consecutive points of one host
+	std::vector<int> pcs, pcc, pch, hb(nF + 1, 0);
+	int i = 0;
+	for (int hst = 0; hst < nF; hst++)
+	{
+		hb[hst] = (int)pcs.size();
+		while (i < nP && host[i] == hst)
+		{
+			int j = i;
+			while (j < nP && host[j] == hst && j - i < CHUNK_P) j++;
+			pcs.push_back(i); pcc.push_back(j - i); pch.push_back(hst);
+			i = j;
+		}
+	}
+	hb[nF] = (int)pcs.size();
+	W->nPC = (int)pcs.size();
+	W->scN = nF * nF * 64 + nF * 32 + nF * 8 + 20;
+	W->scN = (W->scN + 3) & ~3;
+	if (W->nPC > W->capPC)
+	{
+		if (W->capPC) { cudaFree(W->d_pc_start); cudaFree(W->d_pc_cnt); cudaFree(W->d_pc_host); cudaFree(W->d_scPartials); }
+		CK(cudaMalloc(&W->d_pc_start, W->nPC * sizeof(int))); CK(cudaMalloc(&W->d_pc_cnt, W->nPC * sizeof(int))); CK(cudaMalloc(&W->d_pc_host, W->nPC * sizeof(int)));
+		CK(cudaMalloc(&W->d_scPartials, (size_t)W->nPC * (MAXF * MAXF * 64 + MAXF * 40 + 24) * sizeof(float)));
+		W->capPC = W->nPC;
+	}
+	CK(cudaMemcpyAsync(W->d_pc_start, pcs.data(), pcs.size() * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+	CK(cudaMemcpyAsync(W->d_pc_cnt, pcc.data(), pcc.size() * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+	CK(cudaMemcpyAsync(W->d_pc_host, pch.data(), pch.size() * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+	CK(cudaMemcpyAsync(W->d_host_pc_begin, hb.data(), (nF + 1) * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+	CK(cudaStreamSynchronize(ctx->stream));
+	W->h_phost.assign(host, host + nP);
+	W->P.nP = nP;
+	W->points_set = true; W->res_set = false; W->lin_done = false; W->top_done = false;
+	return 0;
+}
+
+extern "C" int dso_b200_ba_set_residuals(dso_b200_ctx* ctx, int nR, const int* point, const int* target, const int* state_state,
+                                         const double* state_energy, const unsigned char* isLinearized, const unsigned char* isActive)
+{
+	ARG_CHECK(ctx && ctx->ba && point && target && state_state, "null argument");
+	ARG_CHECK(nR >= 1, "nR must be >= 1");
+	BAWorkspace* W = ctx->ba;
+	BA_CHECK(W->points_set, "call dso_b200_ba_set_points first");
+	CK(cudaSetDevice(ctx->device));
+	const int nF = W->P.nF, nP = W->P.nP;
+	std::vector<int> rb(nP + 1, 0);
+	for (int i = 0; i < nR; i++)
+	{
+		ARG_CHECK(point[i] >= 0 && point[i] < nP && target[i] >= 0 && target[i] < nF, "residual point / target out of range");
+		ARG_CHECK(i == 0 || point[i] >= point[i - 1], "residuals must be grouped by point (EFPoint::residualsAll order)");
+		ARG_CHECK(target[i] != W->h_phost[point[i]], "residual target equals its host");
+		if (isLinearized && isLinearized[i] && isActive && isActive[i])
+		{
+			dso_set_error("dso_b200_ba_set_residuals: active linearised residuals (addPoint<1>, fixLinearizationF) are not implemented (SURVEY N2)");
+			return DSO_B200_E_STATE;
+		}
+		rb[point[i] + 1]++;
+	}
+	for (int p = 0; p < nP; p++) rb[p + 1] += rb[p];
+	if (nR > W->capR)
+	{
+		free_res(W);
+		const size_t n = (size_t)nR;
+		CK(cudaMalloc(&W->d_rpoint, n * sizeof(int))); CK(cudaMalloc(&W->d_rtarget, n * sizeof(int))); CK(cudaMalloc(&W->d_state, n * sizeof(int)));
+		CK(cudaMalloc(&W->d_newState, n * sizeof(int))); CK(cudaMalloc(&W->d_energy, n * sizeof(double))); CK(cudaMalloc(&W->d_newEnergy, n * sizeof(float)));
+		CK(cudaMalloc(&W->d_newEnergyWO, n * sizeof(float))); CK(cudaMalloc(&W->d_isLin, n)); CK(cudaMalloc(&W->d_isAct, n)); CK(cudaMalloc(&W->d_efsel, n));
+		CK(cudaMalloc(&W->d_cpt, n * 3 * sizeof(float))); CK(cudaMalloc(&W->d_proj, n * 16 * sizeof(float)));
+		CK(cudaMalloc(&W->d_J[0], n * JSZ * sizeof(float))); CK(cudaMalloc(&W->d_J[1], n * JSZ * sizeof(float)));
+		CK(cudaMalloc(&W->d_JpJdF, n * 8 * sizeof(float))); CK(cudaMalloc(&W->d_contrib, n * 6 * sizeof(float))); CK(cudaMalloc(&W->d_resEnergy, n * sizeof(double)));
+		CK(cudaMalloc(&W->d_perm, n * sizeof(int)));
+		CK(cudaMalloc(&W->d_energy_blocks, ((n + 255) / 256) * sizeof(double)));
+		W->capR = nR;
+	}
+	// pair-sorted permutation (stable: keeps point order inside a pair, the reference's accumulation order)
+	std::vector<int> perm(nR), key(nR);
+	for (int i = 0; i < nR; i++) { perm[i] = i; key[i] = W->h_phost[point[i]] + nF * target[i]; }
+	std::stable_sort(perm.begin(), perm.end(), [&](int a, int b) { return key[a] < key[b]; });
+	std::vector<int> cs, cc, pcb(nF * nF + 1, 0);
+	int i = 0;
+	for (int k = 0; k < nF * nF; k++)
+	{
+		pcb[k] = (int)cs.size();
+		while (i < nR && key[perm[i]] == k)
+		{
+			int j = i;
+			while (j < nR && key[perm[j]] == k && j - i < CHUNK_R) j++;
+			cs.push_back(i); cc.push_back(j - i);
+			i = j;
+		}
+	}
+	pcb[nF * nF] = (int)cs.size();
+	W->nChunks = (int)cs.size();
+	if (W->nChunks > W->capChunks)
+	{
+		if (W->capChunks) { cudaFree(W->d_chunk_start); cudaFree(W->d_chunk_cnt); cudaFree(W->d_topPartials); cudaFree(W->d_chunk_nres); }
+		CK(cudaMalloc(&W->d_chunk_start, W->nChunks * sizeof(int))); CK(cudaMalloc(&W->d_chunk_cnt, W->nChunks * sizeof(int)));
+		CK(cudaMalloc(&W->d_topPartials, (size_t)W->nChunks * NTOP_PAD * sizeof(float))); CK(cudaMalloc(&W->d_chunk_nres, W->nChunks * sizeof(int)));
+		W->capChunks = W->nChunks;
+	}
+	std::vector<double> en(nR, 0.0);
+	std::vector<float> nen(nR, 0.f);
+	std::vector<unsigned char> lin(nR, 0), act(nR, 0);
+	for (int k = 0; k < nR; k++)
+	{
+		if (state_energy) en[k] = state_energy[k];
+		nen[k] = (float)en[k];
+		if (isLinearized) lin[k] = isLinearized[k];
+		if (isActive) act[k] = isActive[k];
+	}
+	cudaStream_t s = ctx->stream;
+	CK(cudaMemcpyAsync(W->d_rpoint, point, (size_t)nR * sizeof(int), cudaMemcpyHostToDevice, s));
+	CK(cudaMemcpyAsync(W->d_rtarget, target, (size_t)nR * sizeof(int), cudaMemcpyHostToDevice, s));
+	CK(cudaMemcpyAsync(W->d_state, state_state, (size_t)nR * sizeof(int), cudaMemcpyHostToDevice, s));
+	CK(cudaMemcpyAsync(W->d_energy, en.data(), (size_t)nR * sizeof(double), cudaMemcpyHostToDevice, s));
+	CK(cudaMemcpyAsync(W->d_newEnergy, nen.data(), (size_t)nR * sizeof(float), cudaMemcpyHostToDevice, s));
+	CK(cudaMemcpyAsync(W->d_isLin, lin.data(), (size_t)nR, cudaMemcpyHostToDevice, s));
+	CK(cudaMemcpyAsync(W->d_isAct, act.data(), (size_t)nR, cudaMemcpyHostToDevice, s));
+	CK(cudaMemcpyAsync(W->d_perm, perm.data(), (size_t)nR * sizeof(int), cudaMemcpyHostToDevice, s));
+	CK(cudaMemcpyAsync(W->d_res_begin, rb.data(), (size_t)(nP + 1) * sizeof(int), cudaMemcpyHostToDevice, s));
+	CK(cudaMemcpyAsync(W->d_chunk_start, cs.data(), cs.size() * sizeof(int), cudaMemcpyHostToDevice, s));
+	CK(cudaMemcpyAsync(W->d_chunk_cnt, cc.data(), cc.size() * sizeof(int), cudaMemcpyHostToDevice, s));
+	CK(cudaMemcpyAsync(W->d_pair_chunk_begin, pcb.data(), pcb.size() * sizeof(int), cudaMemcpyHostToDevice, s));
+	CK(cudaMemsetAsync(W->d_efsel, 0, nR, s));
+	{ std::vector<int> ns(nR, ST_OUTLIER); CK(cudaMemcpyAsync(W->d_newState, ns.data(), (size_t)nR * sizeof(int), cudaMemcpyHostToDevice, s)); CK(cudaStreamSynchronize(s)); }   // resetOOB, Residuals.h:97-105
+	CK(cudaMemsetAsync(W->d_newEnergyWO, 0, (size_t)nR * sizeof(float), s));
+	CK(cudaMemsetAsync(W->d_cpt, 0, (size_t)nR * 3 * sizeof(float), s));
+	CK(cudaMemsetAsync(W->d_proj, 0, (size_t)nR * 16 * sizeof(float), s));
+	CK(cudaMemsetAsync(W->d_J[0], 0, (size_t)nR * JSZ * sizeof(float), s));
+	CK(cudaMemsetAsync(W->d_J[1], 0, (size_t)nR * JSZ * sizeof(float), s));
+	CK(cudaMemsetAsync(W->d_JpJdF, 0, (size_t)nR * 8 * sizeof(float), s));
+	CK(cudaMemsetAsync(W->d_contrib, 0, (size_t)nR * 6 * sizeof(float), s));
+	CK(cudaStreamSynchronize(s));
+	W->P.nR = nR;
+	W->res_set = true; W->lin_done = false; W->top_done = false;
+	return 0;
+}
+
+static int enqueue_linearize(dso_b200_ctx* ctx)
+{
+	BAWorkspace* W = ctx->ba;
+	const int nR = W->P.nR;
+	ba_linearize_kernel<<<(nR + 31) / 32, 256, 0, ctx->stream>>>(W->P, W->d_precalc, W->d_pt, W->d_color, W->d_weights, W->d_phost, W->d_rpoint,
+	                                                           W->d_rtarget, W->d_state, W->d_energy, W->d_efsel, W->d_J[0], W->d_J[1],
+	                                                           W->d_newState, W->d_newEnergy, W->d_newEnergyWO, W->d_cpt, W->d_proj, W->d_resEnergy);
+	const int nb = (nR + 255) / 256;
+	ba_energy_blocks_kernel<<<nb, 256, 0, ctx->stream>>>(nR, W->d_resEnergy, W->d_energy_blocks);
+	ba_energy_final_kernel<<<1, 32, 0, ctx->stream>>>(nb, W->d_energy_blocks, W->d_scalars);
+	ctx->launches += 3;
+	CK(cudaGetLastError());
+	W->lin_done = true;
+	return 0;
+}
+
+static int enqueue_apply(dso_b200_ctx* ctx)
+{
+	BAWorkspace* W = ctx->ba;
+	const int nR = W->P.nR;
+	ba_apply_res_kernel<<<(nR + 255) / 256, 256, 0, ctx->stream>>>(nR, W->d_state, W->d_newState, W->d_energy, W->d_newEnergy, W->d_isAct, W->d_efsel,
+	                                                             W->d_J[0], W->d_J[1], W->d_JpJdF);
+	ctx->launches++;
+	CK(cudaGetLastError());
+	W->top_done = false;
+	return 0;
+}
+
+static int enqueue_top(dso_b200_ctx* ctx)
+{
+	BAWorkspace* W = ctx->ba;
+	const int nF = W->P.nF, N = 8 * nF + CPARS;
+	ba_accum_top_kernel<<<W->nChunks, 128, 0, ctx->stream>>>(W->d_perm, W->d_chunk_start, W->d_chunk_cnt, W->d_isAct, W->d_isLin, W->d_efsel,
+	                                                       W->d_J[0], W->d_J[1], W->d_contrib, W->d_topPartials, W->d_chunk_nres);
+	ba_point_sums_kernel<<<(W->P.nP + 127) / 128, 128, 0, ctx->stream>>>(W->P.nP, W->d_res_begin, W->d_isAct, W->d_isLin, W->d_contrib, W->d_Hdd, W->d_bd, W->d_Hcd);
+	const size_t smem = ((size_t)N * N + N + 176 + 64 + 64 + 192) * sizeof(double);
+	static bool attr = false;
+	if (!attr) { CK(cudaFuncSetAttribute(ba_stitch_top_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024)); attr = true; }
+	ba_stitch_top_kernel<<<1, 256, smem, ctx->stream>>>(nF, W->d_pair_chunk_begin, W->d_topPartials, W->d_chunk_nres, W->d_adHost, W->d_adTarget,
+	                                                  W->d_HA, W->d_bA, W->d_scalars);
+	ctx->launches += 3;
+	CK(cudaGetLastError());
+	W->top_done = true;
+	return 0;
+}
+
+static int enqueue_schur(dso_b200_ctx* ctx)
+{
+	BAWorkspace* W = ctx->ba;
+	const int nF = W->P.nF, nP = W->P.nP;
+	ba_schur_prep_kernel<<<(nP + 127) / 128, 128, 0, ctx->stream>>>(nP, W->d_res_begin, W->d_isAct, W->d_Hdd, W->d_bd, W->d_priorF, W->d_deltaF,
+	                                                              W->d_HdiF, W->d_bdSumF, W->d_idh);
+	ba_schur_accum_kernel<<<W->nPC, 256, 0, ctx->stream>>>(nF, W->d_pc_start, W->d_pc_cnt, W->d_res_begin, W->d_rtarget, W->d_isAct, W->d_JpJdF,
+	                                                     W->d_HdiF, W->d_bdSumF, W->d_Hcd, W->d_scPartials, W->scN);
+	ba_schur_stage1_kernel<<<nF * nF, 64, 0, ctx->stream>>>(nF, W->d_host_pc_begin, W->d_scPartials, W->scN, W->d_adHost, W->d_adTarget, W->d_scContrib);
+	ba_schur_gather_kernel<<<nF * nF + 1, 64, 0, ctx->stream>>>(nF, W->nPC, W->d_scPartials, W->scN, W->d_scContrib, W->d_HS, W->d_bS);
+	ctx->launches += 4;
+	CK(cudaGetLastError());
+	return 0;
+}
+
+static int check_ready(dso_b200_ctx* ctx, const char* fn)
+{
+	if (!ctx || !ctx->ba) { dso_set_error("%s: null context", fn); return DSO_B200_E_ARG; }
+	BAWorkspace* W = ctx->ba;
+	if (!(W->window_set && W->glue_set && W->points_set && W->res_set))
+	{
+		dso_set_error("%s: window, glue, points and residuals must be set first", fn);
+		return DSO_B200_E_STATE;
+	}
+	return 0;
+}
+
+extern "C" int dso_b200_ba_linearize(dso_b200_ctx* ctx, int* newState, float* newEnergy, float* newEnergyWithOutlier,
+                                     float* centerProjectedTo3, float* projectedTo16, float* J74, double* energy_sum)
+{
+	int rc = check_ready(ctx, __func__);
+	if (rc) return rc;
+	CK(cudaSetDevice(ctx->device));
+	BAWorkspace* W = ctx->ba;
+	const size_t nR = W->P.nR;
+	rc = enqueue_linearize(ctx);
+	if (rc) return rc;
+	cudaStream_t s = ctx->stream;
+	if (newState) CK(cudaMemcpyAsync(newState, W->d_newState, nR * sizeof(int), cudaMemcpyDeviceToHost, s));
+	if (newEnergy) CK(cudaMemcpyAsync(newEnergy, W->d_newEnergy, nR * sizeof(float), cudaMemcpyDeviceToHost, s));
+	if (newEnergyWithOutlier) CK(cudaMemcpyAsync(newEnergyWithOutlier, W->d_newEnergyWO, nR * sizeof(float), cudaMemcpyDeviceToHost, s));
+	if (centerProjectedTo3) CK(cudaMemcpyAsync(centerProjectedTo3, W->d_cpt, nR * 3 * sizeof(float), cudaMemcpyDeviceToHost, s));
+	if (projectedTo16) CK(cudaMemcpyAsync(projectedTo16, W->d_proj, nR * 16 * sizeof(float), cudaMemcpyDeviceToHost, s));
+	if (energy_sum) CK(cudaMemcpyAsync(energy_sum, W->d_scalars, sizeof(double), cudaMemcpyDeviceToHost, s));
+	CK(cudaStreamSynchronize(s));
+	if (J74)
+	{
+		// PointFrameResidual::J of residual r is buffer (1 - efsel[r])
+		std::vector<unsigned char> sel(nR);
+		std::vector<float> j0(nR * JSZ), j1(nR * JSZ);
+		CK(cudaMemcpy(sel.data(), W->d_efsel, nR, cudaMemcpyDeviceToHost));
+		CK(cudaMemcpy(j0.data(), W->d_J[0], nR * JSZ * sizeof(float), cudaMemcpyDeviceToHost));
+		CK(cudaMemcpy(j1.data(), W->d_J[1], nR * JSZ * sizeof(float), cudaMemcpyDeviceToHost));
+		for (size_t r = 0; r < nR; r++) memcpy(J74 + r * JSZ, (sel[r] ? j0.data() : j1.data()) + r * JSZ, JSZ * sizeof(float));
+	}
+	return 0;
+}
+
+extern "C" int dso_b200_ba_apply_res(dso_b200_ctx* ctx, unsigned char* isActive_out, float* JpJdF8_out)
+{
+	int rc = check_ready(ctx, __func__);
+	if (rc) return rc;
+	BAWorkspace* W = ctx->ba;
+	BA_CHECK(W->lin_done, "call dso_b200_ba_linearize first");
+	CK(cudaSetDevice(ctx->device));
+	rc = enqueue_apply(ctx);
+	if (rc) return rc;
+	const size_t nR = W->P.nR;
+	if (isActive_out) CK(cudaMemcpyAsync(isActive_out, W->d_isAct, nR, cudaMemcpyDeviceToHost, ctx->stream));
+	if (JpJdF8_out) CK(cudaMemcpyAsync(JpJdF8_out, W->d_JpJdF, nR * 8 * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+	CK(cudaStreamSynchronize(ctx->stream));
+	W->lin_done = false;
+	return 0;
+}
+
+extern "C" int dso_b200_ba_accumulate_A(dso_b200_ctx* ctx, double* H, double* b, int* resInA,
+                                        float* Hdd_accAF, float* bd_accAF, float* Hcd_accAF4)
+{
+	int rc = check_ready(ctx, __func__);
+	if (rc) return rc;
+	ARG_CHECK(H && b, "null output");
+	CK(cudaSetDevice(ctx->device));
+	BAWorkspace* W = ctx->ba;
+	rc = enqueue_top(ctx);
+	if (rc) return rc;
+	const int N = 8 * W->P.nF + CPARS;
+	const size_t nP = W->P.nP;
+	cudaStream_t s = ctx->stream;
+	CK(cudaMemcpyAsync(W->h_out, W->d_HA, (size_t)N * N * sizeof(double), cudaMemcpyDeviceToHost, s));
+	CK(cudaMemcpyAsync(W->h_out + N * N, W->d_bA, N * sizeof(double), cudaMemcpyDeviceToHost, s));
+	CK(cudaMemcpyAsync(W->h_out + N * N + N, W->d_scalars, 2 * sizeof(double), cudaMemcpyDeviceToHost, s));
+	if (Hdd_accAF) CK(cudaMemcpyAsync(Hdd_accAF, W->d_Hdd, nP * sizeof(float), cudaMemcpyDeviceToHost, s));
+	if (bd_accAF) CK(cudaMemcpyAsync(bd_accAF, W->d_bd, nP * sizeof(float), cudaMemcpyDeviceToHost, s));
+	if (Hcd_accAF4) CK(cudaMemcpyAsync(Hcd_accAF4, W->d_Hcd, nP * 4 * sizeof(float), cudaMemcpyDeviceToHost, s));
+	CK(cudaStreamSynchronize(s));
+	memcpy(H, W->h_out, (size_t)N * N * sizeof(double));
+	memcpy(b, W->h_out + N * N, N * sizeof(double));
+	if (resInA) *resInA = (int)W->h_out[N * N + N + 1];
+	return 0;
+}
+
+extern "C" int dso_b200_ba_accumulate_SC(dso_b200_ctx* ctx, double* H_sc, double* b_sc,
+                                         float* HdiF, float* bdSumF, float* idepth_hessian)
+{
+	int rc = check_ready(ctx, __func__);
+	if (rc) return rc;
+	ARG_CHECK(H_sc && b_sc, "null output");
+	BAWorkspace* W = ctx->ba;
+	BA_CHECK(W->top_done, "call dso_b200_ba_accumulate_A first (it produces Hdd/bd/Hcd, as in EnergyFunctional::solveSystemF)");
+	CK(cudaSetDevice(ctx->device));
+	rc = enqueue_schur(ctx);
+	if (rc) return rc;
+	const int N = 8 * W->P.nF + CPARS;
+	const size_t nP = W->P.nP;
+	cudaStream_t s = ctx->stream;
+	CK(cudaMemcpyAsync(W->h_out, W->d_HS, (size_t)N * N * sizeof(double), cudaMemcpyDeviceToHost, s));
+	CK(cudaMemcpyAsync(W->h_out + N * N, W->d_bS, N * sizeof(double), cudaMemcpyDeviceToHost, s));
+	if (HdiF) CK(cudaMemcpyAsync(HdiF, W->d_HdiF, nP * sizeof(float), cudaMemcpyDeviceToHost, s));
+	if (bdSumF) CK(cudaMemcpyAsync(bdSumF, W->d_bdSumF, nP * sizeof(float), cudaMemcpyDeviceToHost, s));
+	if (idepth_hessian) CK(cudaMemcpyAsync(idepth_hessian, W->d_idh, nP * sizeof(float), cudaMemcpyDeviceToHost, s));
+	CK(cudaStreamSynchronize(s));
+	memcpy(H_sc, W->h_out, (size_t)N * N * sizeof(double));
+	memcpy(b_sc, W->h_out + N * N, N * sizeof(double));
+	return 0;
+}
+
+extern "C" int dso_b200_ba_step(dso_b200_ctx* ctx, double* H_A, double* b_A, double* H_sc, double* b_sc,
+                                double* energy_sum, int* resInA)
+{
+	int rc = check_ready(ctx, __func__);
+	if (rc) return rc;
+	ARG_CHECK(H_A && b_A && H_sc && b_sc, "null output");
+	CK(cudaSetDevice(ctx->device));
+	BAWorkspace* W = ctx->ba;
+	if ((rc = enqueue_linearize(ctx))) return rc;
+	if ((rc = enqueue_apply(ctx))) return rc;
+	if ((rc = enqueue_top(ctx))) return rc;
+	if ((rc = enqueue_schur(ctx))) return rc;
+	const int N = 8 * W->P.nF + CPARS;
+	const size_t NN = (size_t)N * N;
+	cudaStream_t s = ctx->stream;
+	CK(cudaMemcpyAsync(W->h_out, W->d_HA, NN * sizeof(double), cudaMemcpyDeviceToHost, s));
+	CK(cudaMemcpyAsync(W->h_out + NN, W->d_bA, N * sizeof(double), cudaMemcpyDeviceToHost, s));
+	CK(cudaMemcpyAsync(W->h_out + NN + N, W->d_HS, NN * sizeof(double), cudaMemcpyDeviceToHost, s));
+	CK(cudaMemcpyAsync(W->h_out + 2 * NN + N, W->d_bS, N * sizeof(double), cudaMemcpyDeviceToHost, s));
+	CK(cudaMemcpyAsync(W->h_out + 2 * NN + 2 * N, W->d_scalars, 2 * sizeof(double), cudaMemcpyDeviceToHost, s));
+	CK(cudaStreamSynchronize(s));
+	memcpy(H_A, W->h_out, NN * sizeof(double));
+	memcpy(b_A, W->h_out + NN, N * sizeof(double));
+	memcpy(H_sc, W->h_out + NN + N, NN * sizeof(double));
+	memcpy(b_sc, W->h_out + 2 * NN + N, N * sizeof(double));
+	if (energy_sum) *energy_sum = W->h_out[2 * NN + 2 * N];
+	if (resInA) *resInA = (int)W->h_out[2 * NN + 2 * N + 1];
+	W->lin_done = false;
+	return 0;
+}

@@ -195,7 +195,7 @@ class Window:
 
 
 def make_window(seed=0, w=640, h=480, nF=7, n_points=2000, kf_step_t=0.06, kf_step_deg=1.5,
-                pose_noise=1e-3, depth_noise=0.02, grad_th=50.0):
+                pose_noise=3e-4, depth_noise=0.005, grad_th=50.0):
     """Builds BASELINE.json configs[1]: nF key frames, ~n_points active points, all host->target residuals."""
     sc = Scene(seed, w, h)
     rng = np.random.default_rng(seed + 1000)

@@ -1,0 +1,106 @@
+"""K3-K5 parity: PointFrameResidual::linearize / applyRes / accumulateAF_MT / accumulateSCF_MT on the GPU vs the
+oracle's single-thread branch (the reference's deterministic path).
+
+Bars: states, energies and the RawResidualJacobian bit-exact (the 8-term sums are taken in the reference's order);
+H and b <= 1e-4 relative per entry (relative to max(|H_ij|, sqrt(H_ii H_jj)); b_i relative to max|b|).
+"""
+import numpy as np
+import pytest
+from helpers import rel_err_matrix
+
+pytestmark = pytest.mark.gpu
+
+
+def _setup(pkg, oracle, W):
+    pyr = [oracle.make_images(img, 1)[0][0] for img in W.images]
+    B = oracle.BA(W, pyr)
+    ctx = pkg.Context(0, W.w, W.h, W.nF + 1)
+    for i, img in enumerate(W.images):
+        ctx.make_images(i, img, 1, want_host=False)
+    ctx.ba_set_window(np.arange(W.nF), W.w, W.h, W.K, W.frameEnergyTH)
+    g = B.glue()
+    ctx.ba_set_glue(g["precalc"], g["adHost"], g["adTarget"], g["adHTdeltaF"], g["cDeltaF"])
+    ctx.ba_set_points(W)
+    ctx.ba_set_residuals(W)
+    return B, ctx
+
+
+def _check_system(Hg, bg, Ho, bo, tol=1e-4):
+    assert rel_err_matrix(Hg, Ho).max() <= tol
+    assert np.abs(bg - bo).max() <= tol * np.abs(bo).max()
+
+
+@pytest.mark.parametrize("which", ["small", "vga"])
+def test_ba_pipeline_parity(pkg, oracle, window_small, window_vga, which):
+    W = window_small if which == "small" else window_vga
+    B, ctx = _setup(pkg, oracle, W)
+    lo = B.linearize()
+    lg = ctx.ba_linearize()
+    assert np.array_equal(lo["newState"], lg["newState"])
+    ok = lo["newState"] != 1
+    assert np.array_equal(lo["newEnergy"].view(np.uint32), lg["newEnergy"].view(np.uint32))
+    assert np.array_equal(lo["newEnergyWithOutlier"].view(np.uint32), lg["newEnergyWithOutlier"].view(np.uint32))
+    assert np.array_equal(lo["J"][ok].view(np.uint32), lg["J"][ok].view(np.uint32))
+    assert np.array_equal(lo["projectedTo"][ok].view(np.uint32), lg["projectedTo"][ok].view(np.uint32))
+    assert np.array_equal(lo["centerProjectedTo"].view(np.uint32), lg["centerProjectedTo"].view(np.uint32))
+    assert abs(lo["total"] - lg["total"]) <= 1e-10 * abs(lo["total"])
+    assert (lo["newState"] == 0).sum() > 0.3 * W.nR and (lo["newState"] == 1).sum() > 0     # IN and OOB both exercised
+
+    ao, jo = B.apply_res()
+    ag, jg = ctx.ba_apply_res()
+    assert np.array_equal(ao, ag)
+    assert np.array_equal(jo[ao == 1].view(np.uint32), jg[ag == 1].view(np.uint32))
+
+    Ao = B.accumulate_A(False)
+    Ag = ctx.ba_accumulate_A()
+    assert Ao["resInA"] == Ag["resInA"] == int(ao.sum())
+    assert np.array_equal(Ao["Hdd"].view(np.uint32), Ag["Hdd"].view(np.uint32))
+    assert np.array_equal(Ao["bd"].view(np.uint32), Ag["bd"].view(np.uint32))
+    assert np.array_equal(Ao["Hcd"].view(np.uint32), Ag["Hcd"].view(np.uint32))
+    _check_system(Ag["H"], Ag["b"], Ao["H"], Ao["b"])
+    assert np.allclose(Ag["H"], Ag["H"].T, rtol=0, atol=1e-9 * np.abs(Ag["H"]).max())
+
+    So = B.accumulate_SC(False)
+    Sg = ctx.ba_accumulate_SC()
+    assert np.array_equal(So["HdiF"].view(np.uint32), Sg["HdiF"].view(np.uint32))
+    assert np.array_equal(So["bdSumF"].view(np.uint32), Sg["bdSumF"].view(np.uint32))
+    assert np.array_equal(So["idepth_hessian"].view(np.uint32), Sg["idepth_hessian"].view(np.uint32))
+    _check_system(Sg["H"], Sg["b"], So["H"], So["b"])
+
+    # second GN-style pass: states now carry over (OOB stays OOB, J buffers flip back)
+    lo2, lg2 = B.linearize(), ctx.ba_linearize()
+    assert np.array_equal(lo2["newState"], lg2["newState"])
+    ok2 = lo2["newState"] != 1
+    assert np.array_equal(lo2["J"][ok2].view(np.uint32), lg2["J"][ok2].view(np.uint32))
+    B.apply_res(); ctx.ba_apply_res()
+    Ao2, Ag2 = B.accumulate_A(False), ctx.ba_accumulate_A()
+    _check_system(Ag2["H"], Ag2["b"], Ao2["H"], Ao2["b"])
+    ctx.close()
+
+
+def test_ba_fused_step_equals_separate_calls(pkg, oracle, window_small):
+    W = window_small
+    B, ctx = _setup(pkg, oracle, W)
+    st = ctx.ba_step()
+    B.linearize(); B.apply_res()
+    Ao, So = B.accumulate_A(False), B.accumulate_SC(False)
+    _check_system(st["H_A"], st["b_A"], Ao["H"], Ao["b"])
+    _check_system(st["H_sc"], st["b_sc"], So["H"], So["b"])
+    assert st["resInA"] == Ao["resInA"]
+    ctx.close()
+
+
+def test_ba_input_validation(pkg, oracle, window_small):
+    import copy
+    W = copy.copy(window_small)
+    B, ctx = _setup(pkg, oracle, W)
+    W2 = copy.copy(W)
+    W2.res_point = W.res_point[::-1].copy()           # not grouped by point
+    with pytest.raises(pkg.DsoError):
+        ctx.ba_set_residuals(W2)
+    W3 = copy.copy(W)
+    W3.res_isLinearized = np.ones(W.nR, dtype=np.uint8)
+    W3.res_isActive = np.ones(W.nR, dtype=np.uint8)   # active linearised residuals: not implemented (N2), must fail loudly
+    with pytest.raises(pkg.DsoError):
+        ctx.ba_set_residuals(W3)
+    ctx.close()
