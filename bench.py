@@ -185,6 +185,70 @@ def cpu_baseline(wl, budget_s=12.0):
             "ms_per_frame_track": dt / n * 1e3, "ms_per_frame_make_images": dt_img * 1e3}
 
 
+
+def ba_gpu_bench(pkg, W, dev, steps, warmup, flush_l2, torch, device):
+    """window BA linearize + Schur (BASELINE metric 2) through dso_b200_ba_step: ms per step"""
+    ctx = pkg.Context(dev, W.w, W.h, W.nF + 1)
+    for i, img in enumerate(W.images):
+        ctx.make_images(i, img, 1, want_host=False)
+    ctx.ba_set_window(np.arange(W.nF), W.w, W.h, W.K, W.frameEnergyTH)
+    ctx.ba_set_frames(W)
+    ctx.ba_set_points(W)
+    ctx.ba_set_residuals(W)
+    stream = torch.cuda.ExternalStream(ctx.stream, device=device)
+    for _ in range(warmup):
+        st = ctx.ba_step()
+    l0 = ctx.launch_count()
+    wall, dev_ms = 0.0, 0.0
+    for _ in range(steps):
+        flush_l2(stream)
+        ctx.sync()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0 = time.perf_counter()
+        e0.record(stream)
+        st = ctx.ba_step()
+        e1.record(stream)
+        wall += time.perf_counter() - t0
+        e1.synchronize()
+        dev_ms += e0.elapsed_time(e1)
+    launches = ctx.launch_count() - l0
+    N = 8 * W.nF + 4
+    out = {"metric": "window BA linearize+Schur ms", "unit": "ms", "higher_is_better": False,
+           "value": dev_ms / steps, "e2e_ms": wall / steps * 1e3, "steps": steps,
+           "workload": "configs[1]: %d key frames, %d active points, %d residuals (%d active), %dx%d system; "
+                       "linearizeAll + applyRes + accumulateAF + accumulateSCF per step" % (W.nF, W.nP, W.nR, st["resInA"], N, N),
+           "gpu_launches_per_step": launches / steps, "d2h_bytes_per_step": 2 * (N * N + N) * 8 + 16,
+           "algorithmic_bytes_per_step": int(W.nR * 850)}
+    ctx.close()
+    return out
+
+
+def ba_cpu_bench(W, seconds=4.0):
+    """the same step on the host with the oracle port: reference thread-pool branch (NUM_THREADS = 6), all cores, and 1 thread"""
+    O = entry.load_oracle()
+    pyr = [O.make_images(img, 1)[0][0] for img in W.images]
+    res = {}
+    for name, mt, nt in (("mt6", True, 6), ("mt_all", True, os.cpu_count()), ("st", False, 1)):
+        B = O.BA(W, pyr)
+
+        def step():
+            if mt:
+                B.linearize_mt(nt)
+            else:
+                B.L.dso_oracle_ba_linearize(B.p, None, None, None, None, None, None, None)
+            B.L.dso_oracle_ba_apply_res(B.p, None, None)
+            B.accumulate_A(mt, nt)
+            B.accumulate_SC(mt, nt)
+        step()
+        t0 = time.perf_counter()
+        n = 0
+        while time.perf_counter() - t0 < seconds / 3:
+            step()
+            n += 1
+        res[name] = {"ms": (time.perf_counter() - t0) / n * 1e3, "threads": nt, "steps": n}
+    return res
+
+
 def run_reference(args):
     dist, world, rank, local = dist_setup(args.gpus)
     if rank != 0:
@@ -248,10 +312,10 @@ def run_ours(args):
         ctx.make_images_ptr(1 + k, p, W.w, W.h, levels)
     flush = torch.empty(64 * 1024 * 1024, dtype=torch.float32, device=device)   # 256 MiB > 126 MB L2
 
-    def flush_l2():
+    def flush_l2(st=None):
         if args.no_flush:
             return
-        with torch.cuda.stream(stream):
+        with torch.cuda.stream(st if st is not None else stream):
             flush.zero_()
 
     coarsest = levels - 1
@@ -339,9 +403,14 @@ def run_ours(args):
     total_steps = reduce_sum(dist, float(args.steps), device)
     conv = reduce_sum(dist, float(ok), device)
 
+    ba = ba_gpu_bench(pkg, W, dev, max(5, min(args.steps, 50)), args.warmup, flush_l2, torch, device)
+    ba_ms = reduce_max(dist, ba["value"], device)
+    ba["value"] = ba_ms
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
         cpu = cpu_baseline(wl, args.cpu_seconds)
+        cpu["ba"] = ba_cpu_bench(W, 6.0)
+        ba["cpu_ms_reference_threads6"] = cpu["ba"]["mt6"]["ms"]
     if rank == 0:
         tr = pkg.capi.TrackResult
         line = {"metric": METRIC, "value": total_steps / t_value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
@@ -351,7 +420,7 @@ def run_ours(args):
                         "d2h_bytes_per_step": ctypes.sizeof(tr), "ms_per_step": t_e2e / args.steps * 1e3,
                         "api": "dso_b200_track_frame (H2D image from pinned host memory, K1, K2, D2H result, 1 sync)",
                         "tracked_ok": conv / total_steps},
-                "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu, "clocks": clocks,
+                "gpu_launches": int(launches), "ba": ba, "roofline": roofline, "cpu_baseline": cpu, "clocks": clocks,
                 "wall_s_timed_region": t_wall1 - t_wall0,
                 "lm": {"evals_per_frame": float(np.mean([r.n_evals for r in results])),
                        "iterations_per_frame": float(np.mean([r.n_iterations for r in results])),

@@ -76,6 +76,7 @@ SIGNATURES = {
                                           C.POINTER(TrackOpts), C.POINTER(TrackResult)]),
     "dso_b200_ba_set_window": (C.c_int, [vp, C.c_int, i32p, C.c_int, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float, f32p]),
     "dso_b200_ba_set_glue": (C.c_int, [vp, vp, f64p, f64p, f32p, f32p]),
+    "dso_b200_ba_set_frames": (C.c_int, [vp, f64p, f64p, f64p, f32p, vp, vp, vp]),
     "dso_b200_ba_set_points": (C.c_int, [vp, C.c_int, f32p, f32p, f32p, f32p, f32p, f32p, i32p, f32p, f32p]),
     "dso_b200_ba_set_residuals": (C.c_int, [vp, C.c_int, i32p, i32p, i32p, f64p, u8p, u8p]),
     "dso_b200_ba_linearize": (C.c_int, [vp, vp, vp, vp, vp, vp, vp, vp]),
@@ -297,6 +298,21 @@ class Context:
                                                 np.ascontiguousarray(adTarget, dtype=np.float64).reshape(-1),
                                                 np.ascontiguousarray(adHTdeltaF, dtype=np.float32).reshape(-1),
                                                 np.ascontiguousarray(cDeltaF, dtype=np.float32)))
+
+    def ba_set_frames(self, W, want_out=False):
+        nF = self.nF
+        ev = np.ascontiguousarray(W.evalPT, dtype=np.float64).reshape(-1)
+        st = np.ascontiguousarray(W.state, dtype=np.float64).reshape(-1)
+        sz = np.ascontiguousarray(W.state_zero, dtype=np.float64).reshape(-1)
+        ex = np.ascontiguousarray(W.ab_exposure, dtype=np.float32)
+        if not want_out:
+            self._check(self.L.dso_b200_ba_set_frames(self.h, ev, st, sz, ex, None, None, None))
+            return None
+        pre = np.zeros(nF * nF * 28, dtype=np.float32)
+        adH = np.zeros(nF * nF * 64)
+        adT = np.zeros(nF * nF * 64)
+        self._check(self.L.dso_b200_ba_set_frames(self.h, ev, st, sz, ex, pre.ctypes.data, adH.ctypes.data, adT.ctypes.data))
+        return dict(precalc=pre.reshape(nF * nF, 28), adHost=adH.reshape(nF * nF, 8, 8), adTarget=adT.reshape(nF * nF, 8, 8))
 
     def ba_set_points(self, W):
         self.nP = W.nP

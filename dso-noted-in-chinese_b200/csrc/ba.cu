@@ -18,6 +18,7 @@
 // All of it is FP32 gather/outer-product work bound by L2 latency at the window sizes of BASELINE configs[1]
 // (12 k residuals x ~850 B), HBM-bound only for the 100 k-point sweep.
 #include "common.cuh"
+#include "lm_math.cuh"
 #include <algorithm>
 
 #define CPARS 4
@@ -1012,6 +1013,116 @@ extern "C" int dso_b200_ba_set_residuals(dso_b200_ctx* ctx, int nR, const int* p
 	W->P.nR = nR;
 	W->res_set = true; W->lin_done = false; W->top_done = false;
 	return 0;
+}
+
+
+// ---- host-side glue: FrameFramePrecalc::set + EnergyFunctional::setAdjointsF ------------------
+static void pose_inverse(const Pose& a, Pose& o)
+{
+	for (int r = 0; r < 3; r++) for (int c = 0; c < 3; c++) o.R[r * 3 + c] = a.R[c * 3 + r];
+	for (int r = 0; r < 3; r++) o.t[r] = -(o.R[r * 3] * a.t[0] + o.R[r * 3 + 1] * a.t[1] + o.R[r * 3 + 2] * a.t[2]);
+}
+// Eigen's compute_inverse<Matrix3f> (cofactors of column 0, determinant by expansion along it)
+static float cof33h(const float* m, int i, int j)
+{
+	int i1 = (i + 1) % 3, i2 = (i + 2) % 3, j1 = (j + 1) % 3, j2 = (j + 2) % 3;
+	volatile float a = m[i1 * 3 + j1] * m[i2 * 3 + j2];
+	volatile float b = m[i1 * 3 + j2] * m[i2 * 3 + j1];
+	return a - b;
+}
+static void mat33f_inverse_h(const float* m, float* out)
+{
+	float c0 = cof33h(m, 0, 0), c1 = cof33h(m, 1, 0), c2 = cof33h(m, 2, 0);
+	float det = dot3h(c0, m[0], c1, m[3], c2, m[6]);
+	float invdet = 1.0f / det;
+	out[0] = c0 * invdet; out[1] = c1 * invdet; out[2] = c2 * invdet;
+	out[3] = cof33h(m, 0, 1) * invdet; out[4] = cof33h(m, 1, 1) * invdet; out[5] = cof33h(m, 2, 1) * invdet;
+	out[6] = cof33h(m, 0, 2) * invdet; out[7] = cof33h(m, 1, 2) * invdet; out[8] = cof33h(m, 2, 2) * invdet;
+}
+
+extern "C" int dso_b200_ba_set_frames(dso_b200_ctx* ctx, const double* evalPT12, const double* state10, const double* state_zero10,
+                                      const float* ab_exposure, dso_b200_precalc* precalc_out, double* adHost_out, double* adTarget_out)
+{
+	ARG_CHECK(ctx && ctx->ba && evalPT12 && state10 && state_zero10 && ab_exposure, "null argument");
+	BAWorkspace* W = ctx->ba;
+	BA_CHECK(W->window_set, "call dso_b200_ba_set_window first");
+	const int nF = W->P.nF;
+	const float SXT = 0.5f, SXR = 1.0f, SA = 10.0f, SB = 1000.0f;   // SCALE_XI_TRANS, SCALE_XI_ROT, SCALE_A, SCALE_B (HessianBlocks.h:54-61)
+	std::vector<Pose> evalPT(nF), w2c(nF), c2w(nF);
+	std::vector<double> scaled(nF * 10);
+	for (int f = 0; f < nF; f++)
+	{
+		pose_from12(evalPT[f], evalPT12 + 12 * f);
+		const double* st = state10 + 10 * f;
+		double* sc = &scaled[10 * f];
+		// FrameHessian::setState, HessianBlocks.h:183-199
+		for (int i = 0; i < 3; i++) sc[i] = SXT * st[i];
+		for (int i = 3; i < 6; i++) sc[i] = SXR * st[i];
+		sc[6] = SA * st[6]; sc[7] = SB * st[7]; sc[8] = SA * st[8]; sc[9] = SB * st[9];
+		Pose e;
+		se3_exp(sc, e);
+		pose_mul(e, evalPT[f], w2c[f]);
+		pose_inverse(w2c[f], c2w[f]);
+	}
+	std::vector<dso_b200_precalc> pre(nF * nF);
+	std::vector<double> adH((size_t)nF * nF * 64), adT((size_t)nF * nF * 64);
+	const float K[9] = { W->P.fx, 0, W->P.cx, 0, W->P.fy, W->P.cy, 0, 0, 1 };
+	float Kinv[9];
+	mat33f_inverse_h(K, Kinv);
+	for (int h = 0; h < nF; h++)
+		for (int t = 0; t < nF; t++)
+		{
+			// FrameFramePrecalc::set, HessianBlocks.cpp:213-250
+			dso_b200_precalc& P = pre[h * nF + t];
+			Pose inv, l0, l;
+			pose_inverse(evalPT[h], inv);
+			pose_mul(evalPT[t], inv, l0);
+			pose_mul(w2c[t], c2w[h], l);
+			float RTll[9], tTll[3], KR[9];
+			for (int i = 0; i < 9; i++) { P.PRE_RTll_0[i] = (float)l0.R[i]; RTll[i] = (float)l.R[i]; }
+			for (int i = 0; i < 3; i++) { P.PRE_tTll_0[i] = (float)l0.t[i]; tTll[i] = (float)l.t[i]; }
+			mat33f_mul(K, RTll, KR);
+			mat33f_mul(KR, Kinv, P.PRE_KRKiTll);
+			for (int r = 0; r < 3; r++) P.PRE_KtTll[r] = dot3h(K[r * 3], tTll[0], K[r * 3 + 1], tTll[1], K[r * 3 + 2], tTll[2]);
+			double a, b;
+			aff_from_to(ab_exposure[h], ab_exposure[t], scaled[10 * h + 6], scaled[10 * h + 7], scaled[10 * t + 6], scaled[10 * t + 7], a, b);
+			P.PRE_aff_mode[0] = (float)a; P.PRE_aff_mode[1] = (float)b;
+			P.PRE_b0_mode = (float)(state_zero10[10 * h + 7] * SB);
+			P.pad = 0;
+			// setAdjointsF, EnergyFunctional.cpp:57-94: AH = -Adj(hostToTarget)^T, AT = I (6x6), affine rows, SCALE_* on rows
+			double* AH = &adH[(size_t)(h + t * nF) * 64];
+			double* AT = &adT[(size_t)(h + t * nF) * 64];
+			for (int i = 0; i < 64; i++) { AH[i] = (i % 9 == 0) ? 1.0 : 0.0; AT[i] = (i % 9 == 0) ? 1.0 : 0.0; }
+			// Sophus Adj = [[R, hat(t) R], [0, R]]
+			double Ad[36];
+			const double* R = l0.R; const double* tt = l0.t;
+			const double Th[9] = { 0, -tt[2], tt[1], tt[2], 0, -tt[0], -tt[1], tt[0], 0 };
+			for (int i = 0; i < 36; i++) Ad[i] = 0;
+			for (int r = 0; r < 3; r++)
+				for (int c = 0; c < 3; c++)
+				{
+					Ad[r * 6 + c] = R[r * 3 + c];
+					Ad[(r + 3) * 6 + 3 + c] = R[r * 3 + c];
+					Ad[r * 6 + 3 + c] = Th[r * 3] * R[c] + Th[r * 3 + 1] * R[3 + c] + Th[r * 3 + 2] * R[6 + c];
+				}
+			for (int r = 0; r < 6; r++) for (int c = 0; c < 6; c++) AH[r * 8 + c] = -Ad[c * 6 + r];
+			double a0, b0;
+			aff_from_to(ab_exposure[h], ab_exposure[t], state_zero10[10 * h + 6] * SA, state_zero10[10 * h + 7] * SB,
+			            state_zero10[10 * t + 6] * SA, state_zero10[10 * t + 7] * SB, a0, b0);
+			const float affLL0 = (float)a0;
+			AT[6 * 8 + 6] = -affLL0; AH[6 * 8 + 6] = affLL0; AT[7 * 8 + 7] = -1; AH[7 * 8 + 7] = affLL0;
+			for (int c = 0; c < 8; c++)
+			{
+				for (int r = 0; r < 3; r++) { AH[r * 8 + c] *= SXT; AT[r * 8 + c] *= SXT; }
+				for (int r = 3; r < 6; r++) { AH[r * 8 + c] *= SXR; AT[r * 8 + c] *= SXR; }
+				AH[6 * 8 + c] *= SA; AT[6 * 8 + c] *= SA;
+				AH[7 * 8 + c] *= SB; AT[7 * 8 + c] *= SB;
+			}
+		}
+	if (precalc_out) memcpy(precalc_out, pre.data(), pre.size() * sizeof(dso_b200_precalc));
+	if (adHost_out) memcpy(adHost_out, adH.data(), adH.size() * sizeof(double));
+	if (adTarget_out) memcpy(adTarget_out, adT.data(), adT.size() * sizeof(double));
+	return dso_b200_ba_set_glue(ctx, pre.data(), adH.data(), adT.data(), nullptr, nullptr);
 }
 
 static int enqueue_linearize(dso_b200_ctx* ctx)

@@ -215,6 +215,14 @@ int dso_b200_ba_set_window(dso_b200_ctx* ctx, int nF, const int* frame_slots, in
  * 178-205).  precalc[h*nF+t]; adHost/adTarget[(h+t*nF)*64] doubles; adHTdeltaF[(h+t*nF)*8]; cDeltaF[4]. */
 int dso_b200_ba_set_glue(dso_b200_ctx* ctx, const dso_b200_precalc* precalc, const double* adHost,
                          const double* adTarget, const float* adHTdeltaF, const float* cDeltaF4);
+/* The same glue computed inside the library from the frames' states, then uploaded: FrameHessian::setState
+ * (HessianBlocks.h:183-199: state -> state_scaled, PRE_worldToCam = exp(w2c_leftEps) * worldToCam_evalPT),
+ * FrameFramePrecalc::set for every host/target pair (HessianBlocks.cpp:213-250) and
+ * EnergyFunctional::setAdjointsF (EnergyFunctional.cpp:47-114).  Per frame: worldToCam_evalPT (12 doubles),
+ * state and state_zero (10 doubles each, unscaled), ab_exposure.  The *_out arrays (may be NULL) return the
+ * computed glue in the layout of dso_b200_ba_set_glue. */
+int dso_b200_ba_set_frames(dso_b200_ctx* ctx, const double* evalPT12, const double* state10, const double* state_zero10,
+                           const float* ab_exposure, dso_b200_precalc* precalc_out, double* adHost_out, double* adTarget_out);
 /* PointHessian fields (HessianBlocks.h:431-444) + EFPoint::priorF/deltaF (EnergyFunctionalStructs.h:111-112);
  * points must be grouped by host frame in EnergyFunctional::allPoints order. */
 int dso_b200_ba_set_points(dso_b200_ctx* ctx, int nP, const float* u, const float* v, const float* idepth_scaled,

@@ -68,10 +68,10 @@ def lib():
         L.dso_oracle_ba_set_points.argtypes = [vp, C.c_int, f32p, f32p, f32p, f32p, f32p, f32p, i32p, f32p, f32p]
         L.dso_oracle_ba_set_residuals.argtypes = [vp, C.c_int, i32p, i32p, i32p, f64p, u8p, u8p]
         L.dso_oracle_ba_linearize.restype = C.c_double
-        L.dso_oracle_ba_linearize.argtypes = [vp, i32p, f32p, f32p, f32p, f32p, f32p, f64p]
+        L.dso_oracle_ba_linearize.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp]
         L.dso_oracle_ba_linearize_mt.restype = C.c_double
         L.dso_oracle_ba_linearize_mt.argtypes = [vp, C.c_int]
-        L.dso_oracle_ba_apply_res.argtypes = [vp, u8p, f32p]
+        L.dso_oracle_ba_apply_res.argtypes = [vp, vp, vp]
         L.dso_oracle_ba_accumulate_A.argtypes = [vp, C.c_int, C.c_int, f64p, f64p, C.POINTER(C.c_int), f32p, f32p, f32p]
         L.dso_oracle_ba_accumulate_SC.argtypes = [vp, C.c_int, C.c_int, f64p, f64p, f32p, f32p, f32p]
         _LIB = L
@@ -215,8 +215,8 @@ class BA:
                    newEnergyWithOutlier=np.zeros(nR, dtype=np.float32), centerProjectedTo=np.zeros(nR * 3, dtype=np.float32),
                    projectedTo=np.zeros(nR * 16, dtype=np.float32), J=np.zeros(nR * 74, dtype=np.float32),
                    energy=np.zeros(nR, dtype=np.float64))
-        out["total"] = self.L.dso_oracle_ba_linearize(self.p, out["newState"], out["newEnergy"], out["newEnergyWithOutlier"],
-                                                      out["centerProjectedTo"], out["projectedTo"], out["J"], out["energy"])
+        out["total"] = self.L.dso_oracle_ba_linearize(self.p, *[out[k].ctypes.data for k in
+                                                      ("newState", "newEnergy", "newEnergyWithOutlier", "centerProjectedTo", "projectedTo", "J", "energy")])
         out["J"] = out["J"].reshape(nR, 74)
         out["centerProjectedTo"] = out["centerProjectedTo"].reshape(nR, 3)
         out["projectedTo"] = out["projectedTo"].reshape(nR, 8, 2)
@@ -228,7 +228,7 @@ class BA:
     def apply_res(self):
         act = np.zeros(self.nR, dtype=np.uint8)
         jp = np.zeros(self.nR * 8, dtype=np.float32)
-        self.L.dso_oracle_ba_apply_res(self.p, act, jp)
+        self.L.dso_oracle_ba_apply_res(self.p, act.ctypes.data, jp.ctypes.data)
         return act, jp.reshape(self.nR, 8)
 
     def accumulate_A(self, MT=False, nthreads=6):
