@@ -10,8 +10,10 @@
 //                           residuals of one pair stages them in shared memory, then thread e owns entry e of the
 //                           13x13 block and sums it over the chunk in order -- no atomics, no cross-thread reduce.
 //   ba_point_sums_kernel    per-point Hdd / bd / Hcd in residualsAll order.
-//   ba_stitch_top_kernel    stitchDoubleInternal + symmetrisation: chunk partials summed in index order in FP64,
-//                           adjoint sandwiches in FP64, pairs visited in the reference's order.
+//   ba_reduce_partials / ba_top_pair / ba_top_gather
+//                           stitchDoubleInternal + symmetrisation: chunk partials summed in index order in FP64, one CTA
+//                           per (host,target) pair does its adjoint sandwiches in FP64, every output block then gathers
+//                           its contributions in the reference's pair order.
 //   ba_schur_*              AccumulatedSCHessianSSE::addPoint as per-host "sum_p w_p a_p a_p^T" with thread-owned
 //                           output entries over chunks of 16 points, then two FP64 stitch stages that write every
 //                           contribution to scratch and gather them per output block in a fixed order.
@@ -82,13 +84,13 @@ struct BAWorkspace
 	int nPC, capPC; int* d_pc_start; int* d_pc_cnt; int* d_pc_host; int* d_host_pc_begin;     // [nF+1]
 	float* d_scPartials; int scN;
 	double* d_scContrib;       // stage-1 contributions
+	double* d_scRed; double* d_topRed; double* d_topContrib;
 	// outputs
 	double* d_HA; double* d_bA; double* d_HS; double* d_bS; double* d_energy_blocks; double* d_scalars;   // [0] energy sum, [1] resInA
 	double* h_out;             // pinned: HA, bA, HS, bS, scalars
 	std::vector<int> h_rpoint, h_res_begin, h_phost;
 };
 
-static size_t al(size_t v) { return (v + 255) / 256 * 256; }
 
 int ba_create(dso_b200_ctx* ctx)
 {
@@ -110,6 +112,9 @@ int ba_create(dso_b200_ctx* ctx)
 	CK(cudaMalloc(&W->d_scalars, 8 * sizeof(double)));
 	// stage-1 contributions: per (i,j): C1,C2 (64 each), C3,C4 (MAXF*64 each), CEh,CEt (32 each), Cbh,Cbt (8 each)
 	CK(cudaMalloc(&W->d_scContrib, (size_t)MAXF * MAXF * (128 + 2 * MAXF * 64 + 64 + 16) * sizeof(double)));
+	CK(cudaMalloc(&W->d_scRed, (size_t)MAXF * (MAXF * MAXF * 64 + MAXF * 40) * sizeof(double)));
+	CK(cudaMalloc(&W->d_topRed, (size_t)MAXF * MAXF * NTOP_PAD * sizeof(double)));
+	CK(cudaMalloc(&W->d_topContrib, (size_t)MAXF * MAXF * 292 * sizeof(double)));
 	CK(cudaHostAlloc((void**)&W->h_out, (2 * (size_t)N * N + 2 * N + 8) * sizeof(double), cudaHostAllocDefault));
 	W->d_energy_blocks = nullptr;
 	ctx->ba = W;
@@ -141,7 +146,7 @@ void ba_destroy(dso_b200_ctx* ctx)
 	if (!W) return;
 	free_points(W); free_res(W);
 	cudaFree(W->d_precalc); cudaFree(W->d_adHost); cudaFree(W->d_adTarget); cudaFree(W->d_pair_chunk_begin); cudaFree(W->d_host_pc_begin);
-	cudaFree(W->d_HA); cudaFree(W->d_bA); cudaFree(W->d_HS); cudaFree(W->d_bS); cudaFree(W->d_scalars); cudaFree(W->d_scContrib);
+	cudaFree(W->d_HA); cudaFree(W->d_bA); cudaFree(W->d_HS); cudaFree(W->d_bS); cudaFree(W->d_scalars); cudaFree(W->d_scContrib); cudaFree(W->d_scRed); cudaFree(W->d_topRed); cudaFree(W->d_topContrib);
 	cudaFreeHost(W->h_out);
 	delete W;
 	ctx->ba = nullptr;
@@ -491,108 +496,138 @@ __device__ __forceinline__ int top_index(int i, int j)
 	return 85 + (a == 0 ? b : (a == 1 ? 2 + b : 5));
 }
 
-// stitchDoubleInternal (AccumulatedTopHessian.cpp:259-310, tid = -1 branch) + AccumulatedTopHessian.h:126-138
-__global__ void __launch_bounds__(256) ba_stitch_top_kernel(int nF, const int* __restrict__ pair_chunk_begin, const float* __restrict__ partials,
-                                                            const int* __restrict__ chunk_nres, const double* __restrict__ adHost,
-                                                            const double* __restrict__ adTarget, double* Hout, double* bout, double* scalars)
+// sum of the per-chunk partials of every group (pair or host) in chunk order, FP64: one thread per entry
+__global__ void ba_reduce_partials_kernel(const float* __restrict__ partials, int stride, int nEntries,
+                                          const int* __restrict__ group_begin, double* out)
 {
-	extern __shared__ double sm[];
-	const int N = 8 * nF + CPARS;
-	double* H = sm;                 // N*N
-	double* b = H + N * N;          // N
-	double* accH = b + N;           // 169
-	double* AH = accH + 176;        // 64
-	double* AT = AH + 64;           // 64
-	double* T1 = AT + 64;           // 3*64
-	__shared__ int s_nres;
-	const int tid = threadIdx.x;
-	for (int i = tid; i < N * N + N; i += 256) sm[i] = 0.0;
-	if (tid == 0) s_nres = 0;
+	const int e = blockIdx.x * blockDim.x + threadIdx.x, g = blockIdx.y;
+	if (e >= nEntries) return;
+	double s = 0.0;
+	for (int c = group_begin[g]; c < group_begin[g + 1]; c++) s += (double)partials[(size_t)c * stride + e];
+	out[(size_t)g * nEntries + e] = s;
+}
+
+// contribution layout per (host,target) pair: [HH 64][TT 64][HT 64][CH 32][CT 32][BH 8][BT 8][CC 16][BC 4]
+#define TC_STRIDE 292
+#define TC_HH 0
+#define TC_TT 64
+#define TC_HT 128
+#define TC_CH 192
+#define TC_CT 224
+#define TC_BH 256
+#define TC_BT 264
+#define TC_CC 272
+#define TC_BC 288
+
+// stitchDoubleInternal (AccumulatedTopHessian.cpp:259-310) for one pair: the adjoint sandwiches of its 13x13 block
+__global__ void __launch_bounds__(256) ba_top_pair_kernel(int nF, const double* __restrict__ topRed, const double* __restrict__ adHost,
+                                                          const double* __restrict__ adTarget, double* contrib)
+{
+	__shared__ double accH[176], AH[64], AT[64], T1[192];
+	const int k = blockIdx.x, tid = threadIdx.x;
+	double* out = contrib + (size_t)k * TC_STRIDE;
+	if (tid < 169) { const int i = tid / 13, j = tid - 13 * i; accH[tid] = topRed[(size_t)k * NTOP_PAD + top_index(i, j)]; }
+	else if (tid < 233) AH[tid - 169] = adHost[(size_t)k * 64 + tid - 169];
+	if (tid >= 192) AT[tid - 192] = adTarget[(size_t)k * 64 + tid - 192];
 	__syncthreads();
-	for (int k = 0; k < nF * nF; k++)
+	if (tid < 192)
 	{
-		const int h = k % nF, t = k / nF;
-		const int hIdx = CPARS + h * 8, tIdx = CPARS + t * 8;
-		const int cb = pair_chunk_begin[k], ce = pair_chunk_begin[k + 1];
-		if (cb == ce) continue;      // acc.num == 0
-		if (tid < 169)
-		{
-			const int i = tid / 13, j = tid - 13 * i;
-			const int e = top_index(i, j);
-			double s = 0.0;
-			for (int c = cb; c < ce; c++) s += (double)partials[(size_t)c * NTOP_PAD + e];
-			accH[tid] = s;
-		}
-		else if (tid < 169 + 64) AH[tid - 169] = adHost[(size_t)k * 64 + tid - 169];
-		if (tid >= 192) AT[tid - 192] = adTarget[(size_t)k * 64 + tid - 192];
-		if (tid == 0) { int n = 0; for (int c = cb; c < ce; c++) n += chunk_nres[c]; s_nres += n; }
-		__syncthreads();
-		if (tid < 192)
-		{
-			const int s = tid >> 6, o = tid & 63, i = o >> 3, j = o & 7;
-			const double* L = (s == 1) ? AT : AH;
-			double v = 0.0;
+		const int s = tid >> 6, o = tid & 63, i = o >> 3, j = o & 7;
+		const double* L = (s == 1) ? AT : AH;
+		double v = 0.0;
 #pragma unroll
-			for (int q = 0; q < 8; q++) v += L[i * 8 + q] * accH[(CPARS + q) * 13 + CPARS + j];
-			T1[s * 64 + o] = v;
-		}
-		__syncthreads();
-		if (tid < 192)
-		{
-			const int s = tid >> 6, o = tid & 63, i = o >> 3, j = o & 7;
-			const double* R = (s == 0) ? AH : AT;
-			double v = 0.0;
+		for (int q = 0; q < 8; q++) v += L[i * 8 + q] * accH[(CPARS + q) * 13 + CPARS + j];
+		T1[s * 64 + o] = v;
+	}
+	else
+	{
+		const int o = tid - 192, s = o >> 5, i = (o & 31) >> 2, j = o & 3;   // calibration columns
+		const double* L = s ? AT : AH;
+		double v = 0.0;
 #pragma unroll
-			for (int q = 0; q < 8; q++) v += T1[s * 64 + i * 8 + q] * R[j * 8 + q];
-			const int ro = (s == 1) ? tIdx : hIdx, co = (s == 0) ? hIdx : tIdx;
-			H[(ro + i) * N + co + j] += v;
+		for (int q = 0; q < 8; q++) v += L[i * 8 + q] * accH[(CPARS + q) * 13 + j];
+		out[(s ? TC_CT : TC_CH) + (o & 31)] = v;
+	}
+	__syncthreads();
+	if (tid < 192)
+	{
+		const int s = tid >> 6, o = tid & 63, i = o >> 3, j = o & 7;
+		const double* R = (s == 0) ? AH : AT;          // s=0: AH A AH^T, s=1: AT A AT^T, s=2: AH A AT^T
+		double v = 0.0;
+#pragma unroll
+		for (int q = 0; q < 8; q++) v += T1[s * 64 + i * 8 + q] * R[j * 8 + q];
+		out[(s == 0 ? TC_HH : (s == 1 ? TC_TT : TC_HT)) + o] = v;
+	}
+	else if (tid < 208)
+	{
+		const int o = tid - 192, s = o >> 3, i = o & 7;
+		const double* L = s ? AT : AH;
+		double v = 0.0;
+#pragma unroll
+		for (int q = 0; q < 8; q++) v += L[i * 8 + q] * accH[(CPARS + q) * 13 + CPARS + 8];
+		out[(s ? TC_BT : TC_BH) + i] = v;
+	}
+	else if (tid < 224) { const int o = tid - 208; out[TC_CC + o] = accH[(o >> 2) * 13 + (o & 3)]; }
+	else if (tid < 228) out[TC_BC + tid - 224] = accH[(tid - 224) * 13 + CPARS + 8];
+}
+
+// gather per output block in a fixed order, including "make diagonal by copying over parts" (AccumulatedTopHessian.h:126-138)
+__global__ void __launch_bounds__(64) ba_top_gather_kernel(int nF, int nChunks, const int* __restrict__ chunk_nres,
+                                                           const double* __restrict__ contrib, double* Hout, double* bout, double* scalars)
+{
+	const int N = 8 * nF + CPARS, o = threadIdx.x, i = o >> 3, j = o & 7;
+	if ((int)blockIdx.x < nF * nF)
+	{
+		const int r = blockIdx.x / nF, c = blockIdx.x % nF;
+		double v = 0.0;
+		if (r == c)
+		{
+			for (int k = 0; k < nF * nF; k++)      // the reference's pair order k = h + nF*t
+			{
+				const int h = k % nF, t = k / nF;
+				if (h == r) v += contrib[(size_t)k * TC_STRIDE + TC_HH + o];
+				if (t == r) v += contrib[(size_t)k * TC_STRIDE + TC_TT + o];
+			}
 		}
 		else
+			v = contrib[(size_t)(r + nF * c) * TC_STRIDE + TC_HT + o] + contrib[(size_t)(c + nF * r) * TC_STRIDE + TC_HT + j * 8 + i];
+		Hout[(CPARS + r * 8 + i) * N + CPARS + c * 8 + j] = v;
+	}
+	else
+	{
+		for (int e = o; e < nF * 32; e += 64)
 		{
-			const int o = tid - 192;   // 64 threads: calibration columns, 32 for host rows, 32 for target rows
-			const int s = o >> 5, i = (o & 31) >> 2, j = o & 3;
-			const double* L = s ? AT : AH;
+			const int r = e / 32, q = e % 32;
 			double v = 0.0;
-#pragma unroll
-			for (int q = 0; q < 8; q++) v += L[i * 8 + q] * accH[(CPARS + q) * 13 + j];
-			H[((s ? tIdx : hIdx) + i) * N + j] += v;
+			for (int k = 0; k < nF * nF; k++)
+			{
+				const int h = k % nF, t = k / nF;
+				if (h == r) v += contrib[(size_t)k * TC_STRIDE + TC_CH + q];
+				if (t == r) v += contrib[(size_t)k * TC_STRIDE + TC_CT + q];
+			}
+			const int row = CPARS + r * 8 + (q >> 2), col = q & 3;
+			Hout[row * N + col] = v; Hout[col * N + row] = v;
 		}
-		__syncthreads();
-		if (tid < 16)
+		for (int e = o; e < nF * 8; e += 64)
 		{
-			const int s = tid >> 3, i = tid & 7;
-			const double* L = s ? AT : AH;
+			const int r = e / 8, q = e % 8;
 			double v = 0.0;
-#pragma unroll
-			for (int q = 0; q < 8; q++) v += L[i * 8 + q] * accH[(CPARS + q) * 13 + CPARS + 8];
-			b[(s ? tIdx : hIdx) + i] += v;
+			for (int k = 0; k < nF * nF; k++)
+			{
+				const int h = k % nF, t = k / nF;
+				if (h == r) v += contrib[(size_t)k * TC_STRIDE + TC_BH + q];
+				if (t == r) v += contrib[(size_t)k * TC_STRIDE + TC_BT + q];
+			}
+			bout[CPARS + e] = v;
 		}
-		else if (tid < 32) { const int i = (tid - 16) >> 2, j = (tid - 16) & 3; H[i * N + j] += accH[i * 13 + j]; }
-		else if (tid < 36) b[tid - 32] += accH[(tid - 32) * 13 + CPARS + 8];
-		__syncthreads();
+		if (o < 20)
+		{
+			double v = 0.0;
+			for (int k = 0; k < nF * nF; k++) v += contrib[(size_t)k * TC_STRIDE + TC_CC + o];
+			if (o < 16) Hout[(o >> 2) * N + (o & 3)] = v; else bout[o - 16] = v;
+		}
+		if (o == 32) { int n = 0; for (int c = 0; c < nChunks; c++) n += chunk_nres[c]; scalars[1] = (double)n; }
 	}
-	// "make diagonal by copying over parts"
-	for (int e = tid; e < nF * 32; e += 256)
-	{
-		const int h = e / 32, i = (e % 32) / 8, j = e % 8;
-		H[i * N + CPARS + h * 8 + j] = H[(CPARS + h * 8 + j) * N + i];
-	}
-	__syncthreads();
-	for (int e = tid; e < nF * nF * 64; e += 256)
-	{
-		const int h = e / (nF * 64), t = (e / 64) % nF, i = (e % 64) / 8, j = e % 8;
-		if (t > h) H[(CPARS + h * 8 + i) * N + CPARS + t * 8 + j] += H[(CPARS + t * 8 + j) * N + CPARS + h * 8 + i];
-	}
-	__syncthreads();
-	for (int e = tid; e < nF * nF * 64; e += 256)
-	{
-		const int h = e / (nF * 64), t = (e / 64) % nF, i = (e % 64) / 8, j = e % 8;
-		if (t > h) H[(CPARS + t * 8 + i) * N + CPARS + h * 8 + j] = H[(CPARS + h * 8 + j) * N + CPARS + t * 8 + i];
-	}
-	__syncthreads();
-	for (int i = tid; i < N * N; i += 256) Hout[i] = H[i];
-	for (int i = tid; i < N; i += 256) bout[i] = b[i];
-	if (tid == 0) scalars[1] = (double)s_nres;
 }
 
 // AccumulatedSCHessianSSE::addPoint (AccumulatedSCHessian.cpp:35-60): per-point inverse Hessian and b
@@ -700,27 +735,25 @@ __device__ __forceinline__ void mm8(const double* A, const double* Bm, double* C
 
 // stage 1 of stitchDoubleInternal (AccumulatedSCHessian.cpp:86-165) for the pair (i = host, j = target):
 // every adjoint sandwich that involves accD[i,j,*], accE[i,j], accEB[i,j], written out as separate contributions.
-__global__ void __launch_bounds__(64) ba_schur_stage1_kernel(int nF, const int* __restrict__ host_pc_begin, const float* __restrict__ partials,
-                                                             int scN, const double* __restrict__ adHost, const double* __restrict__ adTarget,
+__global__ void __launch_bounds__(64) ba_schur_stage1_kernel(int nF, const double* __restrict__ scRed, int nRed,
+                                                             const double* __restrict__ adHost, const double* __restrict__ adTarget,
                                                              double* contrib)
 {
 	__shared__ double D[64], S1[64], Q[64], AHij[64], ATij[64], AHik[64], ATik[64], E[32], EB[8];
 	const int i = blockIdx.x % nF, j = blockIdx.x / nF, o = threadIdx.x;
 	const int ij = i + nF * j;
-	const int cb = host_pc_begin[i], ce = host_pc_begin[i + 1];
 	const int nD = nF * nF * 64, nE = nF * 32;
+	const double* red = scRed + (size_t)i * nRed;      // chunk partials of host i, already summed
 	double* out = contrib + (size_t)ij * SCC_STRIDE;
 	AHij[o] = adHost[(size_t)ij * 64 + o]; ATij[o] = adTarget[(size_t)ij * 64 + o];
 	S1[o] = 0.0;
-	if (o < 32) { double s = 0.0; for (int c = cb; c < ce; c++) s += (double)partials[(size_t)c * scN + nD + j * 32 + o]; E[o] = s; }
-	if (o < 8) { double s = 0.0; for (int c = cb; c < ce; c++) s += (double)partials[(size_t)c * scN + nD + nE + j * 8 + o]; EB[o] = s; }
+	if (o < 32) E[o] = red[nD + j * 32 + o];
+	if (o < 8) EB[o] = red[nD + nE + j * 8 + o];
 	__syncthreads();
 	for (int k = 0; k < nF; k++)
 	{
 		const int ik = i + nF * k;
-		double s = 0.0;
-		for (int c = cb; c < ce; c++) s += (double)partials[(size_t)c * scN + (j * nF + k) * 64 + o];
-		D[o] = s;
+		D[o] = red[(j * nF + k) * 64 + o];
 		AHik[o] = adHost[(size_t)ik * 64 + o]; ATik[o] = adTarget[(size_t)ik * 64 + o];
 		__syncthreads();
 		{
@@ -975,6 +1008,7 @@ extern "C" int dso_b200_ba_set_residuals(dso_b200_ctx* ctx, int nR, const int* p
 		if (W->capChunks) { cudaFree(W->d_chunk_start); cudaFree(W->d_chunk_cnt); cudaFree(W->d_topPartials); cudaFree(W->d_chunk_nres); }
 		CK(cudaMalloc(&W->d_chunk_start, W->nChunks * sizeof(int))); CK(cudaMalloc(&W->d_chunk_cnt, W->nChunks * sizeof(int)));
 		CK(cudaMalloc(&W->d_topPartials, (size_t)W->nChunks * NTOP_PAD * sizeof(float))); CK(cudaMalloc(&W->d_chunk_nres, W->nChunks * sizeof(int)));
+		CK(cudaMemset(W->d_topPartials, 0, (size_t)W->nChunks * NTOP_PAD * sizeof(float)));
 		W->capChunks = W->nChunks;
 	}
 	std::vector<double> en(nR, 0.0);
@@ -1156,16 +1190,15 @@ static int enqueue_apply(dso_b200_ctx* ctx)
 static int enqueue_top(dso_b200_ctx* ctx)
 {
 	BAWorkspace* W = ctx->ba;
-	const int nF = W->P.nF, N = 8 * nF + CPARS;
-	ba_accum_top_kernel<<<W->nChunks, 128, 0, ctx->stream>>>(W->d_perm, W->d_chunk_start, W->d_chunk_cnt, W->d_isAct, W->d_isLin, W->d_efsel,
-	                                                       W->d_J[0], W->d_J[1], W->d_contrib, W->d_topPartials, W->d_chunk_nres);
-	ba_point_sums_kernel<<<(W->P.nP + 127) / 128, 128, 0, ctx->stream>>>(W->P.nP, W->d_res_begin, W->d_isAct, W->d_isLin, W->d_contrib, W->d_Hdd, W->d_bd, W->d_Hcd);
-	const size_t smem = ((size_t)N * N + N + 176 + 64 + 64 + 192) * sizeof(double);
-	static bool attr = false;
-	if (!attr) { CK(cudaFuncSetAttribute(ba_stitch_top_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024)); attr = true; }
-	ba_stitch_top_kernel<<<1, 256, smem, ctx->stream>>>(nF, W->d_pair_chunk_begin, W->d_topPartials, W->d_chunk_nres, W->d_adHost, W->d_adTarget,
-	                                                  W->d_HA, W->d_bA, W->d_scalars);
-	ctx->launches += 3;
+	const int nF = W->P.nF;
+	cudaStream_t st = ctx->stream;
+	ba_accum_top_kernel<<<W->nChunks, 128, 0, st>>>(W->d_perm, W->d_chunk_start, W->d_chunk_cnt, W->d_isAct, W->d_isLin, W->d_efsel,
+	                                              W->d_J[0], W->d_J[1], W->d_contrib, W->d_topPartials, W->d_chunk_nres);
+	ba_point_sums_kernel<<<(W->P.nP + 127) / 128, 128, 0, st>>>(W->P.nP, W->d_res_begin, W->d_isAct, W->d_isLin, W->d_contrib, W->d_Hdd, W->d_bd, W->d_Hcd);
+	ba_reduce_partials_kernel<<<dim3(1, nF * nF), NTOP_PAD, 0, st>>>(W->d_topPartials, NTOP_PAD, NTOP_PAD, W->d_pair_chunk_begin, W->d_topRed);
+	ba_top_pair_kernel<<<nF * nF, 256, 0, st>>>(nF, W->d_topRed, W->d_adHost, W->d_adTarget, W->d_topContrib);
+	ba_top_gather_kernel<<<nF * nF + 1, 64, 0, st>>>(nF, W->nChunks, W->d_chunk_nres, W->d_topContrib, W->d_HA, W->d_bA, W->d_scalars);
+	ctx->launches += 5;
 	CK(cudaGetLastError());
 	W->top_done = true;
 	return 0;
@@ -1179,9 +1212,11 @@ static int enqueue_schur(dso_b200_ctx* ctx)
 	                                                              W->d_HdiF, W->d_bdSumF, W->d_idh);
 	ba_schur_accum_kernel<<<W->nPC, 256, 0, ctx->stream>>>(nF, W->d_pc_start, W->d_pc_cnt, W->d_res_begin, W->d_rtarget, W->d_isAct, W->d_JpJdF,
 	                                                     W->d_HdiF, W->d_bdSumF, W->d_Hcd, W->d_scPartials, W->scN);
-	ba_schur_stage1_kernel<<<nF * nF, 64, 0, ctx->stream>>>(nF, W->d_host_pc_begin, W->d_scPartials, W->scN, W->d_adHost, W->d_adTarget, W->d_scContrib);
+	const int nRed = nF * nF * 64 + nF * 32 + nF * 8;
+	ba_reduce_partials_kernel<<<dim3((nRed + 255) / 256, nF), 256, 0, ctx->stream>>>(W->d_scPartials, W->scN, nRed, W->d_host_pc_begin, W->d_scRed);
+	ba_schur_stage1_kernel<<<nF * nF, 64, 0, ctx->stream>>>(nF, W->d_scRed, nRed, W->d_adHost, W->d_adTarget, W->d_scContrib);
 	ba_schur_gather_kernel<<<nF * nF + 1, 64, 0, ctx->stream>>>(nF, W->nPC, W->d_scPartials, W->scN, W->d_scContrib, W->d_HS, W->d_bS);
-	ctx->launches += 4;
+	ctx->launches += 5;
 	CK(cudaGetLastError());
 	return 0;
 }
