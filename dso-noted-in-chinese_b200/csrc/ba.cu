@@ -582,11 +582,10 @@ __global__ void __launch_bounds__(64) ba_top_gather_kernel(int nF, int nChunks, 
 		double v = 0.0;
 		if (r == c)
 		{
-			for (int k = 0; k < nF * nF; k++)      // the reference's pair order k = h + nF*t
+			for (int q = 0; q < nF; q++)           // pairs with host r, then pairs with target r (fixed order)
 			{
-				const int h = k % nF, t = k / nF;
-				if (h == r) v += contrib[(size_t)k * TC_STRIDE + TC_HH + o];
-				if (t == r) v += contrib[(size_t)k * TC_STRIDE + TC_TT + o];
+				v += contrib[(size_t)(r + nF * q) * TC_STRIDE + TC_HH + o];
+				v += contrib[(size_t)(q + nF * r) * TC_STRIDE + TC_TT + o];
 			}
 		}
 		else
@@ -599,11 +598,10 @@ __global__ void __launch_bounds__(64) ba_top_gather_kernel(int nF, int nChunks, 
 		{
 			const int r = e / 32, q = e % 32;
 			double v = 0.0;
-			for (int k = 0; k < nF * nF; k++)
+			for (int m = 0; m < nF; m++)
 			{
-				const int h = k % nF, t = k / nF;
-				if (h == r) v += contrib[(size_t)k * TC_STRIDE + TC_CH + q];
-				if (t == r) v += contrib[(size_t)k * TC_STRIDE + TC_CT + q];
+				v += contrib[(size_t)(r + nF * m) * TC_STRIDE + TC_CH + q];
+				v += contrib[(size_t)(m + nF * r) * TC_STRIDE + TC_CT + q];
 			}
 			const int row = CPARS + r * 8 + (q >> 2), col = q & 3;
 			Hout[row * N + col] = v; Hout[col * N + row] = v;
@@ -612,11 +610,10 @@ __global__ void __launch_bounds__(64) ba_top_gather_kernel(int nF, int nChunks, 
 		{
 			const int r = e / 8, q = e % 8;
 			double v = 0.0;
-			for (int k = 0; k < nF * nF; k++)
+			for (int m = 0; m < nF; m++)
 			{
-				const int h = k % nF, t = k / nF;
-				if (h == r) v += contrib[(size_t)k * TC_STRIDE + TC_BH + q];
-				if (t == r) v += contrib[(size_t)k * TC_STRIDE + TC_BT + q];
+				v += contrib[(size_t)(r + nF * m) * TC_STRIDE + TC_BH + q];
+				v += contrib[(size_t)(m + nF * r) * TC_STRIDE + TC_BT + q];
 			}
 			bout[CPARS + e] = v;
 		}
