@@ -465,8 +465,8 @@ struct LMS
 	double H[64], b[8];
 	double cur[12], nw[12];                       // R (row-major 9) then t
 	double a_cur, b_cur, a_new, b_new;
-	double resOldE, resOldN, resOldFlowT, resOldFlowRT;
-	double incnorm;
+	double resOldE, resOldN, resOldFlowT, resOldFlowRT, resOldFlowN;   // flow sums kept raw
+	double incnorm;                 // squared norm of the last increment
 	double minRes[5];
 	float lambda, levelCutoffRepeat;
 	int lvl, iteration, phase, haveRepeated, done;
@@ -509,8 +509,9 @@ __device__ __forceinline__ void exp_coeffs(double th2, double& A, double& B, dou
 // every CTA of the cluster on identical inputs (so all CTAs take identical decisions, no broadcast).
 // Consumes the sums of the evaluation just finished, leaves either S.done or the next EvalParams in P.
 __device__ __forceinline__ void lm_step_warp(LMS& S, const float* s_tot, const TrackLevels& TL, const dso_b200_track_opts& opt,
-                                             dso_b200_track_result* out, EvalParams& P, int n_points, int lane)
+                                             dso_b200_track_result* out, EvalParams& P, int n_points, int lane, long long* lmt)
 {
+	long long q0 = lmt ? clock64() : 0;
 	const int i = lane & 7;
 	// ---- sums -> this lane's row of the scaled H, b (:338-353) and the Vec6 (:511-519) ----
 	const int nwarp = (int)s_tot[S_NWARP];
@@ -526,9 +527,9 @@ __device__ __forceinline__ void lm_step_warp(LMS& S, const float* s_tot, const T
 	}
 	const double bn = (double)s_tot[S_ACC + 36 + i] * si;
 	const double newE = (double)s_tot[S_E], newN = (double)s_tot[S_NTERMS];
-	const double newFlowT = (double)s_tot[S_FLOW_T] / ((double)s_tot[S_FLOW_N] + 0.1);
-	const double newFlowRT = (double)s_tot[S_FLOW_RT] / ((double)s_tot[S_FLOW_N] + 0.1);
-	const double newSat = (double)fdiv(s_tot[S_NSAT], s_tot[S_NTERMS]);
+	// flow indicators are only read when a level finishes: keep the raw sums, divide there (:514-516)
+	const double newFlowT = (double)s_tot[S_FLOW_T], newFlowRT = (double)s_tot[S_FLOW_RT];
+	const double newFlowN = (double)s_tot[S_FLOW_N];
 
 	// uniform copies of the scalar state
 	int lvl = S.lvl, phase = S.phase, iteration = S.iteration;
@@ -538,12 +539,15 @@ __device__ __forceinline__ void lm_step_warp(LMS& S, const float* s_tot, const T
 
 	if (phase == 0)
 	{
+		const double newSat = (double)fdiv(s_tot[S_NSAT], s_tot[S_NTERMS]);     // :517
 		if (newSat > 0.6 && rep < 50) rep *= 2;                                // :586-593: same state, larger cut-off
 		else { take = true; lambda = 0.01f; iteration = 0; phase = 1; level_done = (0 >= opt.maxIterations[lvl]); propose = !level_done; }
 	}
 	else
 	{
-		const bool accept = (newE / newN) < (S.resOldE / S.resOldN);           // :669
+		// :669  (E'/n' < E/n) evaluated as E'*n < E*n' (n, n' >= 0; equal up to a 1-ulp tie of the two quotients,
+		// and false like the reference's NaN comparison when a count is 0) -- keeps two FP64 divisions off the chain
+		const bool accept = (newE * S.resOldN) < (S.resOldE * newN);
 		if (accept)
 		{
 			take = true;
@@ -553,7 +557,7 @@ __device__ __forceinline__ void lm_step_warp(LMS& S, const float* s_tot, const T
 		}
 		else { lambda *= 4; if (lambda < 0.001f) lambda = 0.001f; }
 		iteration++;
-		level_done = (!(S.incnorm > 1e-3) || iteration >= opt.maxIterations[lvl]);   // :700, :613
+		level_done = (!(S.incnorm > 1e-6) || iteration >= opt.maxIterations[lvl]);   // :700 (|inc| > 1e-3 on the squared norm), :613
 		propose = !level_done;
 		if (lane == 0)
 		{
@@ -561,10 +565,10 @@ __device__ __forceinline__ void lm_step_warp(LMS& S, const float* s_tot, const T
 			out->n_iterations++;
 		}
 	}
-	double resOldE = S.resOldE, resOldN = S.resOldN, resOldFlowT = S.resOldFlowT, resOldFlowRT = S.resOldFlowRT;
+	double resOldE = S.resOldE, resOldN = S.resOldN, resOldFlowT = S.resOldFlowT, resOldFlowRT = S.resOldFlowRT, resOldFlowN = S.resOldFlowN;
 	if (take)
 	{
-		resOldE = newE; resOldN = newN; resOldFlowT = newFlowT; resOldFlowRT = newFlowRT;
+		resOldE = newE; resOldN = newN; resOldFlowT = newFlowT; resOldFlowRT = newFlowRT; resOldFlowN = newFlowN;
 		if (lane < 8)
 		{
 #pragma unroll
@@ -586,7 +590,8 @@ __device__ __forceinline__ void lm_step_warp(LMS& S, const float* s_tot, const T
 		if (lane == 0)
 		{
 			out->lastResiduals[lvl] = rmse;
-			out->lastFlowIndicators[0] = resOldFlowT; out->lastFlowIndicators[1] = 0; out->lastFlowIndicators[2] = resOldFlowRT;
+			out->lastFlowIndicators[0] = resOldFlowT / (resOldFlowN + 0.1); out->lastFlowIndicators[1] = 0;
+			out->lastFlowIndicators[2] = resOldFlowRT / (resOldFlowN + 0.1);
 			if (out->n_passes < DSO_B200_MAX_PASSES) { out->pass_level[out->n_passes] = lvl; out->pass_rmse[out->n_passes] = rmse; out->n_passes++; }
 			S.haveRepeated = haveRepeated;
 			if (abort) { out->ok = 0; out->reserved = lvl; }
@@ -609,6 +614,7 @@ __device__ __forceinline__ void lm_step_warp(LMS& S, const float* s_tot, const T
 		lvl = next; phase = 0; rep = 1; iteration = 0;                         // :584 of the next level pass
 	}
 
+	if (lmt) { long long q = clock64(); lmt[0] += q - q0; q0 = q; }
 	double a_req = a_cur, b_req = b_cur;
 	double pe = (lane < 12) ? S.cur[lane] : 0.0;       // this lane's pose entry of the state to evaluate next
 	double incnorm = S.incnorm;
@@ -641,6 +647,7 @@ __device__ __forceinline__ void lm_step_warp(LMS& S, const float* s_tot, const T
 			x[k] = xk;
 			rhs = fma((i < k) ? -row[k] : 0.0, xk, rhs);
 		}
+		if (lmt) { long long q = clock64(); lmt[1] += q - q0; q0 = q; }
 		float extrapFac = 1.f;
 		if (lambda < 0.001f) extrapFac = sqrtf(sqrtf(0.001f / lambda));       // :650
 		double nrm = 0, sum = 0, is[8];
@@ -651,7 +658,7 @@ __device__ __forceinline__ void lm_step_warp(LMS& S, const float* s_tot, const T
 #pragma unroll
 			for (int k = 0; k < 8; k++) is[k] = 0;
 		}
-		incnorm = sqrt(nrm);
+		incnorm = nrm;
 		a_req = a_cur + is[6]; b_req = b_cur + is[7];
 		// exp(inc) (Sophus SE3::exp): R = I + A W + B W^2, t = (I + B W + C W^2) u
 		const double wx = is[3], wy = is[4], wz = is[5];
@@ -684,6 +691,7 @@ __device__ __forceinline__ void lm_step_warp(LMS& S, const float* s_tot, const T
 		use_new = true;
 	}
 
+	if (lmt) { long long q = clock64(); lmt[2] += q - q0; q0 = q; }
 	// ---- CoarseTracker.cpp:375-378 + :385 for the state to evaluate next (skipped when done) ----
 	if (!done)
 	{
@@ -691,7 +699,8 @@ __device__ __forceinline__ void lm_step_warp(LMS& S, const float* s_tot, const T
 		const float R0 = (float)shfl_d(pe, 3 * r), R1 = (float)shfl_d(pe, 3 * r + 1), R2 = (float)shfl_d(pe, 3 * r + 2);
 		const float rk = dot3e(R0, TL.Ki[lvl][c], R1, TL.Ki[lvl][3 + c], R2, TL.Ki[lvl][6 + c]);
 		double a, b;
-		aff_from_to(TL.ref_exposure, TL.new_exposure, TL.ref_a, TL.ref_b, a_req, b_req, a, b);
+		if (TL.ref_exposure == 1.f && TL.new_exposure == 1.f) { a = exp(a_req - TL.ref_a); b = b_req - a * TL.ref_b; }   // e*1/1 == e exactly
+		else aff_from_to(TL.ref_exposure, TL.new_exposure, TL.ref_a, TL.ref_b, a_req, b_req, a, b);
 		if (lane < 9) { P.RKi[lane] = rk; P.Ki[lane] = TL.Ki[lvl][lane]; }
 		else if (lane < 12) P.t[lane - 9] = (float)pe;
 		if (lane == 12)
@@ -714,11 +723,12 @@ __device__ __forceinline__ void lm_step_warp(LMS& S, const float* s_tot, const T
 		S.lvl = lvl; S.phase = phase; S.iteration = iteration; S.lambda = lambda; S.levelCutoffRepeat = rep;
 		S.a_cur = a_cur; S.b_cur = b_cur;
 		if (use_new) { S.a_new = a_req; S.b_new = b_req; S.incnorm = incnorm; }
-		S.resOldE = resOldE; S.resOldN = resOldN; S.resOldFlowT = resOldFlowT; S.resOldFlowRT = resOldFlowRT;
+		S.resOldE = resOldE; S.resOldN = resOldN; S.resOldFlowT = resOldFlowT; S.resOldFlowRT = resOldFlowRT; S.resOldFlowN = resOldFlowN;
 		S.done = done ? 1 : 0;
 		out->n_evals++; out->point_evals += n_points;
 	}
 	__syncwarp();
+	if (lmt) { long long q = clock64(); lmt[3] += q - q0; }
 }
 
 // Fixed-tree warp reduction of S_COUNT (<= 64) values with recursive halving: 62 shuffles instead of
@@ -753,6 +763,7 @@ track_persistent_kernel(TrackLevels TL, dso_b200_track_opts opt, const TrackIn* 
 	const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 	long long tph[5] = { 0, 0, 0, 0, 0 };
 	long long tc0 = 0, tk0 = 0, tg0 = 0;
+	long long lmt[4] = { 0, 0, 0, 0 };   // LM step split: sums+control, solve, exp+pose, params+stores
 	if (phase_cycles) { tk0 = clock64(); asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tg0)); }
 
 	__shared__ EvalParams sP;
@@ -773,7 +784,7 @@ track_persistent_kernel(TrackLevels TL, dso_b200_track_opts opt, const TrackIn* 
 			for (int i = 0; i < 5; i++) S.minRes[i] = I.minRes[i];
 			S.haveRepeated = 0; S.done = 0; S.incnorm = 0; S.lambda = 0.01f;
 			S.lvl = coarsestLvl; S.phase = 0; S.levelCutoffRepeat = 1; S.iteration = 0;
-			S.resOldE = 0; S.resOldN = 1; S.resOldFlowT = 0; S.resOldFlowRT = 0;
+			S.resOldE = 0; S.resOldN = 1; S.resOldFlowT = 0; S.resOldFlowRT = 0; S.resOldFlowN = 0;
 			s_res.ok = 0; s_res.reserved = -1;
 			for (int i = 0; i < 12; i++) s_res.pose[i] = I.pose[i];
 			s_res.aff_a = I.aff_a; s_res.aff_b = I.aff_b;
@@ -836,7 +847,7 @@ track_persistent_kernel(TrackLevels TL, dso_b200_track_opts opt, const TrackIn* 
 		}
 		__syncthreads();
 		if (phase_cycles) { long long t = clock64(); tph[2] += t - tc0; tc0 = t; }
-		if (warp == 0) lm_step_warp(S, s_tot, TL, opt, &s_res, sP, n, lane);
+		if (warp == 0) lm_step_warp(S, s_tot, TL, opt, &s_res, sP, n, lane, phase_cycles ? lmt : nullptr);
 		__syncthreads();
 		if (phase_cycles) { long long t = clock64(); tph[3] += t - tc0; tph[4]++; }
 		if (S.done) break;
@@ -855,6 +866,7 @@ track_persistent_kernel(TrackLevels TL, dso_b200_track_opts opt, const TrackIn* 
 		long long tg1; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tg1));
 		phase_cycles[5] = clock64() - tk0;
 		phase_cycles[6] = tg1 - tg0;
+		for (int k = 0; k < 4; k++) phase_cycles[8 + k] = lmt[k];
 	}
 }
 
@@ -1169,11 +1181,11 @@ extern "C" int dso_b200_track_phase_cycles(dso_b200_ctx* ctx, int enable, long l
 {
 	ARG_CHECK(ctx, "null context");
 	CK(cudaSetDevice(ctx->device));
-	if (enable && !ctx->d_phase_cycles) { CK(cudaMalloc(&ctx->d_phase_cycles, 64)); CK(cudaMemset(ctx->d_phase_cycles, 0, 64)); }
+	if (enable && !ctx->d_phase_cycles) { CK(cudaMalloc(&ctx->d_phase_cycles, 128)); CK(cudaMemset(ctx->d_phase_cycles, 0, 128)); }
 	if (cycles7 && ctx->d_phase_cycles)
 	{
 		CK(cudaStreamSynchronize(ctx->stream));
-		CK(cudaMemcpy(cycles7, ctx->d_phase_cycles, 56, cudaMemcpyDeviceToHost));
+		CK(cudaMemcpy(cycles7, ctx->d_phase_cycles, 96, cudaMemcpyDeviceToHost));
 	}
 	if (!enable && ctx->d_phase_cycles) { cudaFree(ctx->d_phase_cycles); ctx->d_phase_cycles = nullptr; }
 	return 0;

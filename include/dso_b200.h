@@ -179,7 +179,8 @@ int dso_b200_track_frame(dso_b200_ctx* ctx, int trk, int frame_slot, const float
 /* Profiling aid (no counterpart in the reference): with enable != 0 the persistent kernel records, for
  * thread 0 of CTA 0 of the last launch, the SM cycles spent in [point evaluation, CTA reduction, cluster
  * exchange + barrier, LM step], the number of evaluations, and the whole kernel in SM cycles and in ns;
- * cycles7 (7 values, may be NULL) receives them. */
+ * cycles7 (12 values, may be NULL) receives them; [8..11] split the LM step into sums+control, solve,
+ * exponential+pose update, parameter build. */
 int dso_b200_track_phase_cycles(dso_b200_ctx* ctx, int enable, long long* cycles7);
 /* Applies CoarseTracker.cpp:713 to a finished result: returns 1 if trackNewestCoarse would have
  * returned true for this minResForAbort, 0 if it would have aborted (lastResiduals5_out then holds
