@@ -84,6 +84,52 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
+def cpu_kind():
+    """The timed CPU baseline is the oracle port.  oracle/_ref/libdso_ref.so (the reference's own sources built against
+    stand-in Eigen/Sophus/Boost headers) produces bit-identical results, but the stand-in Eigen is an eager, unvectorised
+    mini-library, so timing it would flatter the GPU; it is reported separately as `reference_build`."""
+    return ("oracle", "port")
+
+
+def reference_build_sample(wl, seconds=3.0):
+    """frames/s of the reference's own sources (stand-in headers) on the same ring, for information only"""
+    O = entry.load_oracle()
+    if not O.ref_available():
+        return None
+    W, levels = wl["W"], wl["levels"]
+    t = O.Tracker(W.w, W.h, levels, *W.K, kind="ref")
+    syn = entry.load_package().synthetic
+    cu, cv, cid, hdi = syn.tracker_reference_inputs(W)
+    ref_pyr = O.make_images(W.images[-1], levels)
+    t.set_ref(cu, cv, cid, hdi, [x.reshape(-1) for x in ref_pyr[0]], wl["a0"], wl["b0"], 1.0)
+    nfr = len(wl["frames"])
+    pyr = [O.make_images(wl["frames"][k][0], levels) for k in range(nfr)]
+    t0 = time.perf_counter()
+    n = 0
+    while time.perf_counter() - t0 < seconds:
+        k = n % nfr
+        t.set_new_frame([x.reshape(-1) for x in pyr[k][0]], 1.0)
+        a, b = wl["affs"][k]
+        t.track(wl["inits"][k], a, b, levels - 1)
+        n += 1
+    return {"value": n / (time.perf_counter() - t0), "unit": UNIT,
+            "note": "unmodified reference sources + stand-in (eager, scalar) Eigen: slower than a real Eigen build would be; not used as the baseline"}
+
+
+class quiet_stdout:
+    """the reference prints from setGlobalCalib / trackNewestCoarse; keep bench's stdout to the one JSON line"""
+
+    def __enter__(self):
+        sys.stdout.flush()
+        self.saved = os.dup(1)
+        os.dup2(2, 1)
+
+    def __exit__(self, *a):
+        sys.stdout.flush()
+        os.dup2(self.saved, 1)
+        os.close(self.saved)
+
+
 def build_workload(seed, n_frames, tracker_points):
     """Window (configs[1]) + reference cloud + a ring of follow-up frames with constant-velocity priors."""
     pkg = entry.load_package()
@@ -92,7 +138,7 @@ def build_workload(seed, n_frames, tracker_points):
     W = syn.make_window(seed=seed, n_points=tracker_points)
     levels = syn.pyr_levels_for(W.w, W.h)
     ref_pyr = O.make_images(W.images[-1], levels)
-    trk = O.Tracker(W.w, W.h, levels, *W.K)
+    trk = O.Tracker(W.w, W.h, levels, *W.K, kind=cpu_kind()[0])
     cu, cv, cid, hdi = syn.tracker_reference_inputs(W)
     a0, b0 = W.aff_true[-1]
     trk.set_ref(cu, cv, cid, hdi, [x.reshape(-1) for x in ref_pyr[0]], a0, b0, 1.0)
@@ -150,7 +196,7 @@ def reduce_sum(dist, value, device):
 def cpu_track_once(wl, k, O, with_images):
     trk = wl["oracle_tracker"]
     if with_images:
-        pyr = wl["cpu_scratch"] = O.make_images(wl["frames"][k][0], wl["levels"], out=wl.get("cpu_scratch"))
+        pyr = wl["cpu_scratch"] = O.make_images(wl["frames"][k][0], wl["levels"], out=wl.get("cpu_scratch"), kind=cpu_kind()[0])
     else:
         pyr = wl["cpu_pyr"][k]
     trk.set_new_frame([x.reshape(-1) for x in pyr[0]], 1.0)
@@ -175,10 +221,10 @@ def cpu_baseline(wl, budget_s=12.0):
     m = 0
     scratch = O.make_images(wl["frames"][0][0], wl["levels"])
     while time.perf_counter() - t1 < 3.0:
-        O.make_images(wl["frames"][m % nfr][0], wl["levels"], out=scratch)
+        O.make_images(wl["frames"][m % nfr][0], wl["levels"], out=scratch, kind=cpu_kind()[0])
         m += 1
     dt_img = (time.perf_counter() - t1) / m
-    return {"value": n / dt, "unit": UNIT, "cores": 1, "kind": "port",
+    return {"value": n / dt, "unit": UNIT, "cores": 1, "kind": cpu_kind()[1],
             "sample": "%d trackNewestCoarse calls over the same %d-frame ring in %.1f s, pyramid precomputed; "
                       "makeImages alone %.3f ms/frame; reference tracker is single-threaded (SURVEY F6); host has %d cores"
                       % (n, nfr, dt, dt_img * 1e3, os.cpu_count()),
@@ -229,7 +275,7 @@ def ba_cpu_bench(W, seconds=4.0):
     pyr = [O.make_images(img, 1)[0][0] for img in W.images]
     res = {}
     for name, mt, nt in (("mt6", True, 6), ("mt_all", True, os.cpu_count()), ("st", False, 1)):
-        B = O.BA(W, pyr)
+        B = O.BA(W, pyr, kind=cpu_kind()[0])
 
         def step():
             if mt:
@@ -254,22 +300,27 @@ def run_reference(args):
     if int(os.environ.get("RANK", "0")) != 0:
         return
     O = entry.load_oracle()
-    wl = build_workload(0, args.frames, args.tracker_points)
-    nfr = len(wl["frames"])
-    for k in range(args.warmup):
-        cpu_track_once(wl, k % nfr, O, True)
-    t0 = time.perf_counter()
-    for k in range(args.steps):
-        cpu_track_once(wl, k % nfr, O, True)
-    dt = time.perf_counter() - t0
+    with quiet_stdout():
+        wl = build_workload(0, args.frames, args.tracker_points)
+        nfr = len(wl["frames"])
+        for k in range(args.warmup):
+            cpu_track_once(wl, k % nfr, O, True)
+        t0 = time.perf_counter()
+        for k in range(args.steps):
+            cpu_track_once(wl, k % nfr, O, True)
+        dt = time.perf_counter() - t0
     v = args.steps / dt
     line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(wl, args),
-            "cpu_baseline": {"value": v, "unit": UNIT, "cores": 1, "kind": "port",
+            "cpu_baseline": {"value": v, "unit": UNIT, "cores": 1, "kind": cpu_kind()[1],
                              "sample": "%d frames, each makeImages + trackNewestCoarse on 1 host thread (the reference tracker "
-                                       "never uses its thread pool); oracle port because the reference needs Eigen/Sophus/Boost, "
-                                       "absent from this image; host has %d cores" % (args.steps, os.cpu_count())},
+                                       "never uses its thread pool); %s; host has %d cores"
+                                       % (args.steps, "the reference's own sources compiled against stand-in Eigen/Sophus/Boost headers "
+                                          "(oracle/refbuild)" if cpu_kind()[1] == "reference" else
+                                          "oracle port, bit-identical to the reference's own sources built in oracle/refbuild "
+                                          "(tests/test_oracle_vs_reference.py) and faster than that build's stand-in Eigen",
+                                          os.cpu_count())},
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line))
 
@@ -293,7 +344,8 @@ def run_ours(args):
     torch.cuda.set_device(dev)
     device = torch.device("cuda", dev)
     pkg = entry.load_package()
-    wl = build_workload(rank, args.frames, args.tracker_points)
+    with quiet_stdout():
+        wl = build_workload(rank, args.frames, args.tracker_points)
     W, levels = wl["W"], wl["levels"]
     nfr = len(wl["frames"])
     ctx = pkg.Context(dev, W.w, W.h, nfr + 2)
@@ -408,8 +460,10 @@ def run_ours(args):
     ba["value"] = ba_ms
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
-        cpu = cpu_baseline(wl, args.cpu_seconds)
-        cpu["ba"] = ba_cpu_bench(W, 6.0)
+        with quiet_stdout():
+            cpu = cpu_baseline(wl, args.cpu_seconds)
+            cpu["ba"] = ba_cpu_bench(W, 6.0)
+            cpu["reference_build"] = reference_build_sample(wl)
         ba["cpu_ms_reference_threads6"] = cpu["ba"]["mt6"]["ms"]
     if rank == 0:
         tr = pkg.capi.TrackResult

@@ -65,12 +65,18 @@ struct SE3d
 	static SE3d from12(const double* p) { SE3d T; memcpy(T.R, p, 72); memcpy(T.t, p + 9, 24); return T; }
 	void to12(double* p) const { memcpy(p, R, 72); memcpy(p + 9, t, 24); }
 };
+// 3-term products in the order Eigen's fixed-size redux uses (also in double): c0 + (c1 + c2)
+static inline double dot3d(double a0, double b0, double a1, double b1, double a2, double b2)
+{
+	double p0 = a0 * b0, p1 = a1 * b1, p2 = a2 * b2;
+	return p0 + (p1 + p2);
+}
 static inline void mat33d_mul(const double* A, const double* B, double* C)
 {
 	double T[9];
 	for (int r = 0; r < 3; r++)
 		for (int c = 0; c < 3; c++)
-			T[r * 3 + c] = A[r * 3 + 0] * B[c] + A[r * 3 + 1] * B[3 + c] + A[r * 3 + 2] * B[6 + c];
+			T[r * 3 + c] = dot3d(A[r * 3 + 0], B[c], A[r * 3 + 1], B[3 + c], A[r * 3 + 2], B[6 + c]);
 	memcpy(C, T, sizeof(T));
 }
 static inline SE3d operator*(const SE3d& a, const SE3d& b)
@@ -78,7 +84,7 @@ static inline SE3d operator*(const SE3d& a, const SE3d& b)
 	SE3d o;
 	mat33d_mul(a.R, b.R, o.R);
 	for (int r = 0; r < 3; r++)
-		o.t[r] = a.R[r * 3 + 0] * b.t[0] + a.R[r * 3 + 1] * b.t[1] + a.R[r * 3 + 2] * b.t[2] + a.t[r];
+		o.t[r] = dot3d(a.R[r * 3 + 0], b.t[0], a.R[r * 3 + 1], b.t[1], a.R[r * 3 + 2], b.t[2]) + a.t[r];
 	return o;
 }
 static inline SE3d se3_inverse(const SE3d& a)
@@ -86,7 +92,7 @@ static inline SE3d se3_inverse(const SE3d& a)
 	SE3d o;
 	for (int r = 0; r < 3; r++) for (int c = 0; c < 3; c++) o.R[r * 3 + c] = a.R[c * 3 + r];
 	for (int r = 0; r < 3; r++)
-		o.t[r] = -(o.R[r * 3 + 0] * a.t[0] + o.R[r * 3 + 1] * a.t[1] + o.R[r * 3 + 2] * a.t[2]);
+		o.t[r] = -dot3d(o.R[r * 3 + 0], a.t[0], o.R[r * 3 + 1], a.t[1], o.R[r * 3 + 2], a.t[2]);
 	return o;
 }
 static inline void hat3(const double* w, double* W)
@@ -127,12 +133,9 @@ static inline SE3d se3_exp(const double* xi)
 	}
 	for (int r = 0; r < 3; r++)
 	{
-		o.t[r] = 0;
-		for (int c = 0; c < 3; c++)
-		{
-			double I = (r == c);
-			o.t[r] += (I + B * W[r * 3 + c] + C * W2[r * 3 + c]) * u[c];
-		}
+		double V[3];
+		for (int c = 0; c < 3; c++) V[c] = (r == c ? 1.0 : 0.0) + B * W[r * 3 + c] + C * W2[r * 3 + c];
+		o.t[r] = dot3d(V[0], u[0], V[1], u[1], V[2], u[2]);
 	}
 	return o;
 }
@@ -163,12 +166,9 @@ static inline void se3_log(const SE3d& T, double* xi)
 	}
 	for (int r = 0; r < 3; r++)
 	{
-		xi[r] = 0;
-		for (int cc = 0; cc < 3; cc++)
-		{
-			double I = (r == cc);
-			xi[r] += (I - 0.5 * W[r * 3 + cc] + k * W2[r * 3 + cc]) * T.t[cc];
-		}
+		double V[3];
+		for (int cc = 0; cc < 3; cc++) V[cc] = (r == cc ? 1.0 : 0.0) - 0.5 * W[r * 3 + cc] + k * W2[r * 3 + cc];
+		xi[r] = dot3d(V[0], T.t[0], V[1], T.t[1], V[2], T.t[2]);
 	}
 	xi[3] = w[0]; xi[4] = w[1]; xi[5] = w[2];
 }

@@ -9,7 +9,6 @@ import subprocess
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-_LIB = None
 
 f32p = np.ctypeslib.ndpointer(dtype=np.float32, flags="C_CONTIGUOUS")
 f64p = np.ctypeslib.ndpointer(dtype=np.float64, flags="C_CONTIGUOUS")
@@ -33,49 +32,77 @@ def build(force=False):
     return so
 
 
-def lib():
-    global _LIB
-    if _LIB is None:
+class _Proxy:
+    """Maps the dso_oracle_* names onto another library that exports the same C signatures under a different
+    prefix (oracle/_ref/libdso_ref.so: the unmodified reference sources built by oracle/refbuild)."""
+
+    def __init__(self, cdll, prefix):
+        self._cdll, self._prefix = cdll, prefix
+
+    def __getattr__(self, name):
+        return getattr(self._cdll, name.replace("dso_oracle_", self._prefix))
+
+
+REF_SO = os.path.join(_HERE, "_ref", "libdso_ref.so")
+_LIBS = {}
+
+
+def ref_available():
+    return os.path.exists(REF_SO)
+
+
+def lib(kind="oracle"):
+    if kind in _LIBS:
+        return _LIBS[kind]
+    if kind == "oracle":
         so = os.path.join(_HERE, "libdso_oracle.so")
         if not os.path.exists(so):
             build()
         L = C.CDLL(so)
-        vp = C.c_void_p
-        L.dso_oracle_make_images.argtypes = [f32p, C.c_int, C.c_int, C.c_int, vp, C.POINTER(vp), C.POINTER(vp)]
-        L.dso_oracle_tracker_create.restype = vp
-        L.dso_oracle_tracker_create.argtypes = [C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float]
-        L.dso_oracle_tracker_destroy.argtypes = [vp]
-        L.dso_oracle_tracker_get_K.argtypes = [vp, C.c_int] + [C.POINTER(C.c_float)] * 4 + [vp]
-        L.dso_oracle_tracker_set_ref.argtypes = [vp, C.c_int, f32p, f32p, f32p, f32p, C.POINTER(vp), C.c_double, C.c_double, C.c_float]
-        L.dso_oracle_tracker_set_cloud.argtypes = [vp, C.c_int, C.c_int, f32p, f32p, f32p, f32p]
-        L.dso_oracle_tracker_set_ref_aff.argtypes = [vp, C.c_double, C.c_double, C.c_float]
-        L.dso_oracle_tracker_get_cloud.restype = C.c_int
-        L.dso_oracle_tracker_get_cloud.argtypes = [vp, C.c_int, vp, vp, vp, vp]
-        L.dso_oracle_tracker_set_new_frame.argtypes = [vp, C.POINTER(vp), C.c_float]
-        L.dso_oracle_calc_res.argtypes = [vp, C.c_int, f64p, C.c_double, C.c_double, C.c_float, f64p]
-        L.dso_oracle_calc_gs.argtypes = [vp, C.c_int, C.c_double, C.c_double, f64p, f64p]
-        L.dso_oracle_get_warped.restype = C.c_int
-        L.dso_oracle_get_warped.argtypes = [vp, C.POINTER(vp)]
-        L.dso_oracle_get_point_status.argtypes = [vp, u8p]
-        L.dso_oracle_track_newest_coarse.argtypes = [vp, f64p, C.c_double, C.c_double, C.c_int, f64p, C.POINTER(TrackResult)]
-        L.dso_oracle_ba_create.restype = vp
-        L.dso_oracle_ba_create.argtypes = [C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float]
-        L.dso_oracle_ba_destroy.argtypes = [vp]
-        L.dso_oracle_ba_set_frame.argtypes = [vp, C.c_int, f64p, f64p, f64p, C.c_float, C.c_float, f32p]
-        L.dso_oracle_ba_set_calib_delta.argtypes = [vp, f64p]
-        L.dso_oracle_ba_prepare.argtypes = [vp]
-        L.dso_oracle_ba_get_glue.argtypes = [vp, f32p, f64p, f64p, f32p, f32p]
-        L.dso_oracle_ba_set_points.argtypes = [vp, C.c_int, f32p, f32p, f32p, f32p, f32p, f32p, i32p, f32p, f32p]
-        L.dso_oracle_ba_set_residuals.argtypes = [vp, C.c_int, i32p, i32p, i32p, f64p, u8p, u8p]
-        L.dso_oracle_ba_linearize.restype = C.c_double
-        L.dso_oracle_ba_linearize.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp]
-        L.dso_oracle_ba_linearize_mt.restype = C.c_double
-        L.dso_oracle_ba_linearize_mt.argtypes = [vp, C.c_int]
-        L.dso_oracle_ba_apply_res.argtypes = [vp, vp, vp]
-        L.dso_oracle_ba_accumulate_A.argtypes = [vp, C.c_int, C.c_int, f64p, f64p, C.POINTER(C.c_int), f32p, f32p, f32p]
-        L.dso_oracle_ba_accumulate_SC.argtypes = [vp, C.c_int, C.c_int, f64p, f64p, f32p, f32p, f32p]
-        _LIB = L
-    return _LIB
+    else:
+        if not ref_available():
+            raise RuntimeError("oracle/_ref/libdso_ref.so not built (make -C oracle/refbuild; needs /root/reference)")
+        L = _Proxy(C.CDLL(REF_SO), "dso_ref_")
+    vp = C.c_void_p
+
+    def sig(name, argtypes, restype=None):
+        try:
+            f = getattr(L, name)
+        except AttributeError:
+            return          # the reference build has no counterpart for a few debug helpers
+        f.argtypes = argtypes
+        if restype is not None:
+            f.restype = restype
+
+    sig("dso_oracle_make_images", [f32p, C.c_int, C.c_int, C.c_int, vp, C.POINTER(vp), C.POINTER(vp)])
+    sig("dso_oracle_tracker_create", [C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float], vp)
+    sig("dso_oracle_tracker_destroy", [vp])
+    sig("dso_oracle_tracker_get_K", [vp, C.c_int] + [C.POINTER(C.c_float)] * 4 + [vp])
+    sig("dso_oracle_tracker_set_ref", [vp, C.c_int, f32p, f32p, f32p, f32p, C.POINTER(vp), C.c_double, C.c_double, C.c_float])
+    sig("dso_oracle_tracker_set_cloud", [vp, C.c_int, C.c_int, f32p, f32p, f32p, f32p])
+    sig("dso_oracle_tracker_set_ref_aff", [vp, C.c_double, C.c_double, C.c_float])
+    sig("dso_oracle_tracker_get_cloud", [vp, C.c_int, vp, vp, vp, vp], C.c_int)
+    sig("dso_oracle_tracker_set_new_frame", [vp, C.POINTER(vp), C.c_float])
+    sig("dso_oracle_calc_res", [vp, C.c_int, f64p, C.c_double, C.c_double, C.c_float, f64p])
+    sig("dso_oracle_calc_gs", [vp, C.c_int, C.c_double, C.c_double, f64p, f64p])
+    sig("dso_oracle_get_warped", [vp, C.POINTER(vp)], C.c_int)
+    sig("dso_oracle_get_point_status", [vp, u8p])
+    sig("dso_oracle_track_newest_coarse", [vp, f64p, C.c_double, C.c_double, C.c_int, f64p, C.POINTER(TrackResult)])
+    sig("dso_oracle_ba_create", [C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float], vp)
+    sig("dso_oracle_ba_destroy", [vp])
+    sig("dso_oracle_ba_set_frame", [vp, C.c_int, f64p, f64p, f64p, C.c_float, C.c_float, f32p])
+    sig("dso_oracle_ba_set_calib_delta", [vp, f64p])
+    sig("dso_oracle_ba_prepare", [vp])
+    sig("dso_oracle_ba_get_glue", [vp, f32p, f64p, f64p, f32p, f32p])
+    sig("dso_oracle_ba_set_points", [vp, C.c_int, f32p, f32p, f32p, f32p, f32p, f32p, i32p, f32p, f32p])
+    sig("dso_oracle_ba_set_residuals", [vp, C.c_int, i32p, i32p, i32p, f64p, u8p, u8p])
+    sig("dso_oracle_ba_linearize", [vp, vp, vp, vp, vp, vp, vp, vp], C.c_double)
+    sig("dso_oracle_ba_linearize_mt", [vp, C.c_int], C.c_double)
+    sig("dso_oracle_ba_apply_res", [vp, vp, vp])
+    sig("dso_oracle_ba_accumulate_A", [vp, C.c_int, C.c_int, f64p, f64p, C.POINTER(C.c_int), f32p, f32p, f32p])
+    sig("dso_oracle_ba_accumulate_SC", [vp, C.c_int, C.c_int, f64p, f64p, f32p, f32p, f32p])
+    _LIBS[kind] = L
+    return L
 
 
 def _ptr_array(arrs):
@@ -85,7 +112,7 @@ def _ptr_array(arrs):
     return a
 
 
-def make_images(color, levels, B=None, out=None):
+def make_images(color, levels, B=None, out=None, kind="oracle"):
     """Returns (dIp list of [h_l, w_l, 3] float32, absgrad list of [h_l, w_l] float32); untouched elements are 0.
     out: a previous return value to overwrite (skips the allocation, as the reference's new[] does not zero)."""
     h, w = color.shape
@@ -99,13 +126,13 @@ def make_images(color, levels, B=None, out=None):
     if B is not None:
         B = np.ascontiguousarray(B, dtype=np.float32)
         Bp = B.ctypes.data
-    lib().dso_oracle_make_images(color, w, h, levels, Bp, _ptr_array(dIp), _ptr_array(ab))
+    lib(kind).dso_oracle_make_images(color, w, h, levels, Bp, _ptr_array(dIp), _ptr_array(ab))
     return dIp, ab
 
 
 class Tracker:
-    def __init__(self, w, h, levels, fx, fy, cx, cy):
-        self.L = lib()
+    def __init__(self, w, h, levels, fx, fy, cx, cy, kind="oracle"):
+        self.L = lib(kind)
         self.w, self.h, self.levels = w, h, levels
         self.p = self.L.dso_oracle_tracker_create(w, h, levels, fx, fy, cx, cy)
         self._keep = []
@@ -172,9 +199,9 @@ class Tracker:
 
 
 class BA:
-    def __init__(self, W, dI_list):
+    def __init__(self, W, dI_list, kind="oracle"):
         """W: synthetic.Window; dI_list: per frame level-0 AoS image [h,w,3] float32."""
-        self.L = lib()
+        self.L = lib(kind)
         fx, fy, cx, cy = W.K
         self.nF, self.nP, self.nR = W.nF, W.nP, W.nR
         self.p = self.L.dso_oracle_ba_create(W.w, W.h, W.nF, fx, fy, cx, cy)

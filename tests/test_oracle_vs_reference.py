@@ -1,0 +1,134 @@
+"""Pins the oracle restatement against the REAL reference code: oracle/_ref/libdso_ref.so is the reference's own
+translation units (CoarseTracker.cpp, HessianBlocks.cpp, Residuals.cpp, EnergyFunctional*.cpp, Accumulated*.cpp,
+MatrixAccumulators.h, ...) compiled unmodified from /root/reference against stand-in Eigen/Sophus/Boost headers
+(oracle/refbuild).  Everything the reference computes in its own source is compared bit for bit; only results that
+pass through the stand-in third-party arithmetic (LDLT / SE3::exp inside trackNewestCoarse) get a tolerance."""
+import numpy as np
+import pytest
+from helpers import flat
+
+import __graft_entry__ as g
+
+O = g.load_oracle()
+pytestmark = pytest.mark.skipif(not O.ref_available(), reason="oracle/_ref/libdso_ref.so not built (needs /root/reference)")
+
+
+def bits(a):
+    return np.ascontiguousarray(a).view(np.uint32 if a.dtype == np.float32 else np.uint64)
+
+
+@pytest.mark.parametrize("w,h,levels", [(640, 480, 4), (320, 240, 3), (424, 320, 3)])
+def test_make_images_bit_exact(w, h, levels):
+    rng = np.random.default_rng(w)
+    img = rng.uniform(0, 255, (h, w)).astype(np.float32)
+    B = (np.arange(256, dtype=np.float32) ** 1.05).astype(np.float32)
+    for lut in (None, B):
+        d0, a0 = O.make_images(img, levels, lut)
+        d1, a1 = O.make_images(img, levels, lut, kind="ref")
+        for l in range(levels):
+            assert np.array_equal(bits(d0[l]), bits(d1[l])) and np.array_equal(bits(a0[l]), bits(a1[l]))
+
+
+@pytest.fixture(scope="module")
+def trackers(pkg, window_small):
+    W = window_small
+    syn = pkg.synthetic
+    levels = syn.pyr_levels_for(W.w, W.h)
+    ref_pyr = O.make_images(W.images[-1], levels)
+    cu, cv, cid, hdi = syn.tracker_reference_inputs(W)
+    a0, b0 = W.aff_true[-1]
+    frames = syn.tracking_sequence(W, 2)
+    out = []
+    for kind in ("oracle", "ref"):
+        t = O.Tracker(W.w, W.h, levels, *W.K, kind=kind)
+        t.set_ref(cu, cv, cid, hdi, flat(ref_pyr[0]), a0, b0, 1.0)
+        out.append(t)
+    return W, syn, levels, frames, out[0], out[1], (a0, b0)
+
+
+def test_make_coarse_depth_and_K_bit_exact(trackers):
+    W, syn, levels, frames, to, tr, _ = trackers
+    for l in range(levels):
+        co, cr = to.get_cloud(l), tr.get_cloud(l)
+        assert len(co[0]) == len(cr[0]) > 0
+        for a, b in zip(co, cr):
+            assert np.array_equal(bits(a), bits(b))
+        (ko, Kio), (kr, Kir) = to.get_K(l), tr.get_K(l)
+        assert ko == kr and np.array_equal(bits(Kio), bits(Kir))
+
+
+def test_calc_res_and_gs_bit_exact(trackers):
+    W, syn, levels, frames, to, tr, (a0, b0) = trackers
+    rng = np.random.default_rng(3)
+    for k, (img, rel, aff) in enumerate(frames):
+        pyr = O.make_images(img, levels)
+        to.set_new_frame(flat(pyr[0]), 1.0)
+        tr.set_new_frame(flat(pyr[0]), 1.0)
+        for pose in ((np.eye(3), np.zeros(3)), rel, syn.se3_mul(syn.se3_exp(rng.normal(0, 3e-3, 6)), rel)):
+            for lvl in range(levels):
+                for cutoff in (20.0, 80.0):
+                    p = syn.pose12(pose)
+                    ro = to.calc_res(lvl, p, aff[0], aff[1], cutoff)
+                    rr = tr.calc_res(lvl, p, aff[0], aff[1], cutoff)
+                    assert np.array_equal(bits(ro), bits(rr)), (k, lvl, ro, rr)
+                    no, bo = to.get_warped()
+                    nr, br = tr.get_warped()
+                    assert no == nr
+                    for x, y in zip(bo, br):
+                        assert np.array_equal(bits(x), bits(y))
+                    Ho, go = to.calc_gs(lvl, aff[0], aff[1])
+                    Hr, gr = tr.calc_gs(lvl, aff[0], aff[1])
+                    assert np.array_equal(bits(Ho), bits(Hr)) and np.array_equal(bits(go), bits(gr))   # Accumulator9 tiers and lanes included
+
+
+def test_track_newest_coarse_agrees(trackers):
+    """the LM loop goes through the stand-in LDLT / SE3::exp in both builds (same algorithms) -> tight tolerance"""
+    W, syn, levels, frames, to, tr, (a0, b0) = trackers
+    ident = syn.pose12((np.eye(3), np.zeros(3)))
+    for k, (img, rel, aff) in enumerate(frames):
+        pyr = O.make_images(img, levels)
+        to.set_new_frame(flat(pyr[0]), 1.0)
+        tr.set_new_frame(flat(pyr[0]), 1.0)
+        ro = to.track(ident, a0, b0, levels - 1)
+        rr = tr.track(ident, a0, b0, levels - 1)
+        assert ro.ok == rr.ok == 1
+        assert np.abs(np.array(ro.pose) - np.array(rr.pose)).max() < 1e-9
+        assert abs(ro.aff_a - rr.aff_a) < 1e-9 and abs(ro.aff_b - rr.aff_b) < 1e-6
+        assert np.allclose(list(ro.lastResiduals)[:levels], list(rr.lastResiduals)[:levels], rtol=1e-6)
+        assert np.allclose(list(ro.lastFlowIndicators), list(rr.lastFlowIndicators), rtol=1e-6)
+        thr = np.array(ro.lastResiduals) * 0.3
+        assert to.track(ident, a0, b0, levels - 1, thr).ok == tr.track(ident, a0, b0, levels - 1, thr).ok == 0
+
+
+def test_ba_linearize_accumulate(pkg, window_small):
+    W = window_small
+    pyr = [O.make_images(img, 1)[0][0] for img in W.images]
+    Bo, Br = O.BA(W, pyr), O.BA(W, pyr, kind="ref")
+    go, gr = Bo.glue(), Br.glue()
+    for key in ("precalc", "adHost", "adTarget", "cDeltaF"):
+        assert np.array_equal(bits(go[key]), bits(gr[key])), key          # FrameFramePrecalc::set, setAdjointsF
+    lo, lr = Bo.linearize(), Br.linearize()
+    assert np.array_equal(lo["newState"], lr["newState"])
+    ok = lo["newState"] != 1
+    for key in ("newEnergy", "newEnergyWithOutlier"):
+        assert np.array_equal(bits(lo[key]), bits(lr[key])), key
+    assert np.array_equal(bits(lo["J"][ok]), bits(lr["J"][ok]))
+    assert np.array_equal(bits(lo["projectedTo"][ok]), bits(lr["projectedTo"][ok]))
+    assert lo["total"] == lr["total"]
+    ao, jo = Bo.apply_res()
+    ar, jr = Br.apply_res()
+    assert np.array_equal(ao, ar) and np.array_equal(bits(jo[ao == 1]), bits(jr[ar == 1]))
+    Ao, Ar = Bo.accumulate_A(False), Br.accumulate_A(False)
+    assert Ao["resInA"] == Ar["resInA"]
+    for key in ("Hdd", "bd", "Hcd"):
+        assert np.array_equal(bits(Ao[key]), bits(Ar[key])), key
+    sc = np.abs(Ar["H"]).max()
+    assert np.abs(Ao["H"] - Ar["H"]).max() <= 1e-12 * sc and np.abs(Ao["b"] - Ar["b"]).max() <= 1e-12 * np.abs(Ar["b"]).max()
+    So, Sr = Bo.accumulate_SC(False), Br.accumulate_SC(False)
+    for key in ("HdiF", "bdSumF", "idepth_hessian"):
+        assert np.array_equal(bits(So[key]), bits(Sr[key])), key
+    sc = np.abs(Sr["H"]).max()
+    assert np.abs(So["H"] - Sr["H"]).max() <= 1e-12 * sc and np.abs(So["b"] - Sr["b"]).max() <= 1e-12 * np.abs(Sr["b"]).max()
+    # the reference's thread-pool branch (6 workers, chunks of 50) agrees with its single-thread branch to float noise
+    Am = Br.accumulate_A(True)
+    assert np.abs(Am["H"] - Ar["H"]).max() <= 1e-5 * np.abs(Ar["H"]).max()
