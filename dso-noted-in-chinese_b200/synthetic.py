@@ -248,14 +248,14 @@ def make_window(seed=0, w=640, h=480, nF=7, n_points=2000, kf_step_t=0.06, kf_st
         gy[1:-1, :] = 0.5 * (img[2:, :] - img[:-2, :])
         g2 = gx * gx + gy * gy
         border = 8
-        cell = int(np.sqrt((w - 2 * border) * (h - 2 * border) / per_frame))
+        cell = max(2, int(np.sqrt((w - 2 * border) * (h - 2 * border) / (1.5 * per_frame))))   # 1.5x candidates, cut to per_frame below
         cands = []
         for y0 in range(border, h - border - cell + 1, cell):
             for x0 in range(border, w - border - cell + 1, cell):
                 blk = g2[y0:y0 + cell, x0:x0 + cell]
                 k = int(np.argmax(blk))
                 yy, xx = y0 + k // cell, x0 + k % cell
-                if g2[yy, xx] > grad_th:
+                if g2[yy, xx] > grad_th * (640.0 / w) ** 2:      # the texture's pixel gradients shrink with resolution
                     cands.append((xx, yy))
         rng.shuffle(cands)
         cands = cands[:per_frame]
