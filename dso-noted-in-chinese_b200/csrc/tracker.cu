@@ -505,6 +505,28 @@ __device__ __forceinline__ void exp_coeffs(double th2, double& A, double& B, dou
 	}
 }
 
+// exp(x) for the relative affine gain: |x| is ~1e-2 in tracking, where a degree-11 Taylor series is accurate to
+// < 1e-19 and much shorter than the general routine; anything larger goes through exp().
+__device__ __forceinline__ double exp_small(double x)
+{
+	if (fabs(x) < 0.125)
+	{
+		double p = 1.0 / 39916800.0;
+		p = fma(p, x, 1.0 / 3628800.0); p = fma(p, x, 1.0 / 362880.0); p = fma(p, x, 1.0 / 40320.0); p = fma(p, x, 1.0 / 5040.0);
+		p = fma(p, x, 1.0 / 720.0); p = fma(p, x, 1.0 / 120.0); p = fma(p, x, 1.0 / 24.0); p = fma(p, x, 1.0 / 6.0);
+		p = fma(p, x, 0.5); p = fma(p, x, 1.0); p = fma(p, x, 1.0);
+		return p;
+	}
+	return exp(x);
+}
+// AffLight::fromToVecExposure (NumType.h:176-189) for the tracker's (reference, new frame) pair
+__device__ __forceinline__ void aff_ref_to_new(const TrackLevels& TL, double a_req, double b_req, double& a, double& b)
+{
+	if (TL.ref_exposure == 1.f && TL.new_exposure == 1.f) a = exp_small(a_req - TL.ref_a);    // e*1/1 == e exactly
+	else { double bb; aff_from_to(TL.ref_exposure, TL.new_exposure, TL.ref_a, TL.ref_b, a_req, b_req, a, bb); }
+	b = b_req - a * TL.ref_b;
+}
+
 // One step of the trackNewestCoarse state machine (CoarseTracker.cpp:584-722), executed by warp 0 of
 // every CTA of the cluster on identical inputs (so all CTAs take identical decisions, no broadcast).
 // Consumes the sums of the evaluation just finished, leaves either S.done or the next EvalParams in P.
@@ -531,9 +553,11 @@ __device__ __forceinline__ void lm_step_warp(LMS& S, const float* s_tot, const T
 	const double newFlowT = (double)s_tot[S_FLOW_T], newFlowRT = (double)s_tot[S_FLOW_RT];
 	const double newFlowN = (double)s_tot[S_FLOW_N];
 
+	if (lmt) { long long q = clock64(); lmt[4] += q - q0; q0 = q; }
 	// uniform copies of the scalar state
 	int lvl = S.lvl, phase = S.phase, iteration = S.iteration;
 	float lambda = S.lambda, rep = S.levelCutoffRepeat;
+	const float rep_in = rep;
 	double a_cur = S.a_cur, b_cur = S.b_cur;
 	bool take = false, use_new = false, level_done = false, propose = false;
 
@@ -565,6 +589,7 @@ __device__ __forceinline__ void lm_step_warp(LMS& S, const float* s_tot, const T
 			out->n_iterations++;
 		}
 	}
+	if (lmt) { long long q = clock64(); lmt[5] += q - q0; q0 = q; }
 	double resOldE = S.resOldE, resOldN = S.resOldN, resOldFlowT = S.resOldFlowT, resOldFlowRT = S.resOldFlowRT, resOldFlowN = S.resOldFlowN;
 	if (take)
 	{
@@ -615,15 +640,19 @@ __device__ __forceinline__ void lm_step_warp(LMS& S, const float* s_tot, const T
 	}
 
 	if (lmt) { long long q = clock64(); lmt[0] += q - q0; q0 = q; }
-	double a_req = a_cur, b_req = b_cur;
+	double a_req = a_cur, b_req = b_cur, affA = 1.0, affB = 0.0;
 	double pe = (lane < 12) ? S.cur[lane] : 0.0;       // this lane's pose entry of the state to evaluate next
 	double incnorm = S.incnorm;
 	if (propose)
 	{
-		// ---- :613-665: damped solve, one lane per row; H + lambda*diag(H) is SPD, so plain elimination
-		// (Eigen's pivoted LDLT gives the same solution up to rounding) ----
+		// ---- :613-665: damped solve, one lane per row.  H + lambda*diag(H) is SPD, so no pivoting is needed
+		// (Eigen's pivoted LDLT gives the same solution up to rounding).  Division-free Gauss-Jordan: every step
+		// is row_i <- g*row_i - f*row_k for all i != k with (g, f) = (piv, row_i[k]) * 2^-exponent(piv): a power-of-
+		// two rescale (exact) replaces the reciprocal chain on the critical path and bounds the growth to 2x per
+		// step; the eight reciprocals are taken once at the end, in parallel.  Row scaling does not change the
+		// solution. ----
 		const double damp = (double)(1.f + lambda);
-		double row[8], rp[8], x[8];
+		double row[8], x[8];
 #pragma unroll
 		for (int j = 0; j < 8; j++) row[j] = take ? hn[j] : S.H[i * 8 + j];
 		double rhs = -(take ? bn : S.b[i]);
@@ -633,20 +662,30 @@ __device__ __forceinline__ void lm_step_warp(LMS& S, const float* s_tot, const T
 		for (int k = 0; k < 8; k++)
 		{
 			const double piv = shfl_d(row[k], k);
-			rp[k] = fast_rcp(piv);
-			const double f = (i > k) ? row[k] * rp[k] : 0.0;
 			const double prhs = shfl_d(rhs, k);
+			const bool self = (i == k);
+			const double sc = __hiloint2double((2046 - ((__double2hiint(piv) >> 20) & 0x7ff)) << 20, 0);   // 2^-exponent(piv)
+			const double f = self ? 0.0 : row[k] * sc;
+			const double g = self ? 1.0 : piv * sc;
 #pragma unroll
-			for (int j = k + 1; j < 8; j++) row[j] = fma(-f, shfl_d(row[j], k), row[j]);
-			rhs = fma(-f, prhs, rhs);
-		}
+			for (int j = 0; j < 8; j++)
+			{
+				if (j <= k) continue;                       // columns <= k of the other rows become 0 / are never read again
+				const double pj = shfl_d(row[j], k);
+				row[j] = fma(-f, pj, g * row[j]);
+			}
+			rhs = fma(-f, prhs, g * rhs);
 #pragma unroll
-		for (int k = 7; k >= 0; k--)
-		{
-			const double xk = shfl_d(rhs, k) * rp[k];
-			x[k] = xk;
-			rhs = fma((i < k) ? -row[k] : 0.0, xk, rhs);
+			for (int j = 0; j < 8; j++) if (j < k) row[j] = g * row[j];   // keep the already-diagonalised part consistent (only row[i], j == i, matters)
+			if (!self) row[k] = 0.0;
 		}
+		// row i is now (0,..,d_i,..,0 | rhs_i): x_i = rhs_i / d_i
+		double di = 0.0;
+#pragma unroll
+		for (int j = 0; j < 8; j++) if (j == i) di = row[j];
+		const double xi = rhs * fast_rcp(di);
+#pragma unroll
+		for (int k = 0; k < 8; k++) x[k] = shfl_d(xi, k);
 		if (lmt) { long long q = clock64(); lmt[1] += q - q0; q0 = q; }
 		float extrapFac = 1.f;
 		if (lambda < 0.001f) extrapFac = sqrtf(sqrtf(0.001f / lambda));       // :650
@@ -660,6 +699,7 @@ __device__ __forceinline__ void lm_step_warp(LMS& S, const float* s_tot, const T
 		}
 		incnorm = nrm;
 		a_req = a_cur + is[6]; b_req = b_cur + is[7];
+		aff_ref_to_new(TL, a_req, b_req, affA, affB);   // independent of the pose chain below: overlaps with it
 		// exp(inc) (Sophus SE3::exp): R = I + A W + B W^2, t = (I + B W + C W^2) u
 		const double wx = is[3], wy = is[4], wz = is[5];
 		const double th2 = wx * wx + wy * wy + wz * wz;
@@ -698,24 +738,25 @@ __device__ __forceinline__ void lm_step_warp(LMS& S, const float* s_tot, const T
 		const int r = (lane < 9) ? lane / 3 : 0, c = (lane < 9) ? lane - 3 * r : 0;
 		const float R0 = (float)shfl_d(pe, 3 * r), R1 = (float)shfl_d(pe, 3 * r + 1), R2 = (float)shfl_d(pe, 3 * r + 2);
 		const float rk = dot3e(R0, TL.Ki[lvl][c], R1, TL.Ki[lvl][3 + c], R2, TL.Ki[lvl][6 + c]);
-		double a, b;
-		if (TL.ref_exposure == 1.f && TL.new_exposure == 1.f) { a = exp(a_req - TL.ref_a); b = b_req - a * TL.ref_b; }   // e*1/1 == e exactly
-		else aff_from_to(TL.ref_exposure, TL.new_exposure, TL.ref_a, TL.ref_b, a_req, b_req, a, b);
-		if (lane < 9) { P.RKi[lane] = rk; P.Ki[lane] = TL.Ki[lvl][lane]; }
+		if (!use_new) aff_ref_to_new(TL, a_req, b_req, affA, affB);
+		const double a = affA, b = affB;
+		if (lane < 9) { P.RKi[lane] = rk; if (level_done) P.Ki[lane] = TL.Ki[lvl][lane]; }
 		else if (lane < 12) P.t[lane - 9] = (float)pe;
-		if (lane == 12)
+		if (lane == 12) { P.affLL0 = (float)a; P.affLL1 = (float)b; }
+		if (lane == 13 && (level_done || rep != rep_in))
 		{
+			// level- and cut-off-dependent parameters only change at a level switch / cut-off doubling
 			const float cutoff = opt.coarseCutoffTH * rep;
-			P.affLL0 = (float)a; P.affLL1 = (float)b;
-			P.fx = TL.fx[lvl]; P.fy = TL.fy[lvl]; P.cx = TL.cx[lvl]; P.cy = TL.cy[lvl];
-			P.wl = TL.w[lvl];
-			P.wl_m3 = (float)(TL.w[lvl] - 3); P.hl_m3 = (float)(TL.h[lvl] - 3);
-			P.n = TL.pc_n[lvl];
-			P.lvl0 = (lvl == 0);
 			P.cutoffTH = cutoff;
-			P.huberTH = opt.huberTH;
 			P.maxEnergy = fsub(fmul(fmul(2.0f, opt.huberTH), cutoff), fmul(opt.huberTH, opt.huberTH));
-			P.b0 = (float)TL.ref_b;
+			if (level_done)
+			{
+				P.fx = TL.fx[lvl]; P.fy = TL.fy[lvl]; P.cx = TL.cx[lvl]; P.cy = TL.cy[lvl];
+				P.wl = TL.w[lvl];
+				P.wl_m3 = (float)(TL.w[lvl] - 3); P.hl_m3 = (float)(TL.h[lvl] - 3);
+				P.n = TL.pc_n[lvl];
+				P.lvl0 = (lvl == 0);
+			}
 		}
 	}
 	if (lane == 0)
@@ -763,7 +804,7 @@ track_persistent_kernel(TrackLevels TL, dso_b200_track_opts opt, const TrackIn* 
 	const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 	long long tph[5] = { 0, 0, 0, 0, 0 };
 	long long tc0 = 0, tk0 = 0, tg0 = 0;
-	long long lmt[4] = { 0, 0, 0, 0 };   // LM step split: sums+control, solve, exp+pose, params+stores
+	long long lmt[6] = { 0, 0, 0, 0, 0, 0 };   // LM step split: sums+control, solve, exp+pose, params+stores
 	if (phase_cycles) { tk0 = clock64(); asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tg0)); }
 
 	__shared__ EvalParams sP;
@@ -866,7 +907,7 @@ track_persistent_kernel(TrackLevels TL, dso_b200_track_opts opt, const TrackIn* 
 		long long tg1; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tg1));
 		phase_cycles[5] = clock64() - tk0;
 		phase_cycles[6] = tg1 - tg0;
-		for (int k = 0; k < 4; k++) phase_cycles[8 + k] = lmt[k];
+		for (int k = 0; k < 6; k++) phase_cycles[8 + k] = lmt[k];
 	}
 }
 
@@ -1143,10 +1184,10 @@ static int enqueue_track(dso_b200_ctx* ctx, int trk, int frame_slot, int nHyp, c
 	cap = (int)std::min<size_t>((size_t)per, smem_cap_bytes / sizeof(float4));
 	dyn = (size_t)cap * sizeof(float4);
 	void (*kern)(TrackLevels, dso_b200_track_opts, const TrackIn*, dso_b200_track_result*, int, int, long long*) =
-		nt == 128 ? track_persistent_kernel<128> : (nt == 512 ? track_persistent_kernel<512> : track_persistent_kernel<256>);
-	if (nt != 128 && nt != 512) nt = 256;
-	static bool attr_set[64][3] = { { false } };
-	const int ki = nt == 128 ? 0 : (nt == 256 ? 1 : 2);
+		nt == 128 ? track_persistent_kernel<128> : (nt == 512 ? track_persistent_kernel<512> : (nt == 384 ? track_persistent_kernel<384> : track_persistent_kernel<256>));
+	if (nt != 128 && nt != 512 && nt != 384) nt = 256;
+	static bool attr_set[64][4] = { { false } };
+	const int ki = nt == 128 ? 0 : (nt == 256 ? 1 : (nt == 512 ? 2 : 3));
 	if (!attr_set[ctx->device & 63][ki])
 	{
 		CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_cap_bytes));
@@ -1185,7 +1226,7 @@ extern "C" int dso_b200_track_phase_cycles(dso_b200_ctx* ctx, int enable, long l
 	if (cycles7 && ctx->d_phase_cycles)
 	{
 		CK(cudaStreamSynchronize(ctx->stream));
-		CK(cudaMemcpy(cycles7, ctx->d_phase_cycles, 96, cudaMemcpyDeviceToHost));
+		CK(cudaMemcpy(cycles7, ctx->d_phase_cycles, 112, cudaMemcpyDeviceToHost));
 	}
 	if (!enable && ctx->d_phase_cycles) { cudaFree(ctx->d_phase_cycles); ctx->d_phase_cycles = nullptr; }
 	return 0;

@@ -20,7 +20,7 @@ for k in range(6):
     c = ctx.phase_cycles(True, read=True)
     n = max(c[4], 1)
     print("frame", k, "evals", r.n_evals, "cycles/eval: eval %.0f reduce %.0f xchg %.0f lm %.0f total %.0f" %
-          (c[0] / n, c[1] / n, c[2] / n, c[3] / n, c[:4].sum() / n), "| kernel cycles", c[5], "ns", c[6], "| lm split: sums+ctl %.0f solve %.0f exp+pose %.0f params %.0f" % tuple(c[8:12] / n))
+          (c[0] / n, c[1] / n, c[2] / n, c[3] / n, c[:4].sum() / n), "| kernel cycles", c[5], "ns", c[6], "| lm split: take/store+level %.0f solve %.0f exp+pose %.0f params %.0f | sums->H %.0f control %.0f" % tuple(c[8:14] / n))
 hy = np.stack([wl["inits"][2]] * 31)
 ctx.track_batched(0, 3, hy, *wl["affs"][2], levels - 1)
 c = ctx.phase_cycles(True, read=True)
