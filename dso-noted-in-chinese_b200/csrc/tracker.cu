@@ -772,6 +772,37 @@ __device__ __forceinline__ void lm_step_warp(LMS& S, const float* s_tot, const T
 	if (lmt) { long long q = clock64(); lmt[3] += q - q0; }
 }
 
+// ---- cluster exchange through remote shared memory + mbarrier (no cluster-wide barrier, no L1 invalidation) ----
+__device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(void* bar, unsigned count)
+{
+	asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(void* bar, unsigned bytes)
+{
+	asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(void* bar, unsigned parity)
+{
+	asm volatile(
+		"{\n"
+		".reg .pred p;\n"
+		"WAIT_LOOP:\n"
+		"mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+		"@p bra WAIT_DONE;\n"
+		"bra WAIT_LOOP;\n"
+		"WAIT_DONE:\n"
+		"}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+// store one float into CTA `rank`'s copy of `local_addr` and count 4 bytes on that CTA's mbarrier
+__device__ __forceinline__ void st_async_remote(const void* local_addr, const void* local_bar, unsigned rank, float v)
+{
+	unsigned raddr, rbar;
+	asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(raddr) : "r"(smem_u32(local_addr)), "r"(rank));
+	asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(rbar) : "r"(smem_u32(local_bar)), "r"(rank));
+	asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.b32 [%0], %1, [%2];" ::"r"(raddr), "r"(__float_as_uint(v)), "r"(rbar) : "memory");
+}
+
 // Fixed-tree warp reduction of S_COUNT (<= 64) values with recursive halving: 62 shuffles instead of
 // 5 per value.  On return lane l holds the warp sums of entries 2l and 2l+1 in v[0], v[1].
 __device__ __forceinline__ void warp_reduce_halving(float* v, int lane)
@@ -811,6 +842,7 @@ track_persistent_kernel(TrackLevels TL, dso_b200_track_opts opt, const TrackIn* 
 	__shared__ LMS S;
 	__shared__ float s_w[NT / 32][64];
 	__shared__ float xchg[2][MAX_CLUSTER][S_COUNT];
+	__shared__ __align__(8) unsigned long long xbar[2];   // one mbarrier per exchange buffer
 	__shared__ float s_tot[S_COUNT];
 	__shared__ dso_b200_track_result s_res;
 	extern __shared__ float4 s_pts[];
@@ -838,8 +870,11 @@ track_persistent_kernel(TrackLevels TL, dso_b200_track_opts opt, const TrackIn* 
 		}
 		__syncwarp();
 	}
+	if (tid == 0) { mbar_init(&xbar[0], 1); mbar_init(&xbar[1], 1); asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
 	__syncthreads();
+	cluster.sync();            // every CTA's barriers exist before anybody signals them
 	int buf = 0;
+	unsigned xphase[2] = { 0u, 0u };
 	int staged_lvl = -1;
 	while (true)
 	{
@@ -876,14 +911,21 @@ track_persistent_kernel(TrackLevels TL, dso_b200_track_opts opt, const TrackIn* 
 			float s = 0.f;
 #pragma unroll
 			for (int w = 0; w < NT / 32; w++) s += s_w[w][tid];
-			for (unsigned r = 0; r < CS; r++) *cluster.map_shared_rank(&xchg[buf][rank][tid], r) = s;
+			for (unsigned r = 0; r < CS; r++) st_async_remote(&xchg[buf][rank][tid], &xbar[buf], r, s);
 		}
+		if (tid == 0) mbar_arrive_expect_tx(&xbar[buf], CS * S_COUNT * 4);   // this CTA expects CS partials of S_COUNT floats
 		if (phase_cycles) { long long t = clock64(); tph[1] += t - tc0; tc0 = t; }
-		cluster.sync();
+		mbar_wait(&xbar[buf], xphase[buf]);
+		xphase[buf] ^= 1u;
 		if (tid < S_COUNT)
 		{
+			// ranks in index order; loads issued together (fixed trip count), adds in order
+			float v[MAX_CLUSTER];
+#pragma unroll
+			for (int r = 0; r < MAX_CLUSTER; r++) v[r] = (r < (int)CS) ? xchg[buf][r][tid] : 0.f;
 			float s = 0.f;
-			for (unsigned r = 0; r < CS; r++) s += xchg[buf][r][tid];
+#pragma unroll
+			for (int r = 0; r < MAX_CLUSTER; r++) s += v[r];
 			s_tot[tid] = s;
 		}
 		__syncthreads();
@@ -894,6 +936,7 @@ track_persistent_kernel(TrackLevels TL, dso_b200_track_opts opt, const TrackIn* 
 		if (S.done) break;
 		buf ^= 1;
 	}
+	cluster.sync();                // nobody leaves while a peer may still be writing into it
 	if (rank == 0)
 	{
 		const int nwords = sizeof(dso_b200_track_result) / 4;
