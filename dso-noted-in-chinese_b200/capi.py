@@ -74,6 +74,7 @@ SIGNATURES = {
     "dso_b200_track_replay_abort": (C.c_int, [C.POINTER(TrackResult), f64p, f64p]),
     "dso_b200_track_hostloop": (C.c_int, [vp, C.c_int, C.c_int, f64p, C.c_double, C.c_double, C.c_float, C.c_int, vp,
                                           C.POINTER(TrackOpts), C.POINTER(TrackResult)]),
+    "dso_b200_ba_set_affine_modes": (C.c_int, [vp, C.c_float, C.c_float]),
     "dso_b200_ba_set_window": (C.c_int, [vp, C.c_int, i32p, C.c_int, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float, f32p]),
     "dso_b200_ba_set_glue": (C.c_int, [vp, vp, f64p, f64p, f32p, f32p]),
     "dso_b200_ba_set_frames": (C.c_int, [vp, f64p, f64p, f64p, f32p, vp, vp, vp]),
@@ -285,6 +286,9 @@ class Context:
         return ok, lr
 
     # ---- K3-K5 ----
+    def ba_set_affine_modes(self, mode_a=1e12, mode_b=1e8):
+        self._check(self.L.dso_b200_ba_set_affine_modes(self.h, mode_a, mode_b))
+
     def ba_set_window(self, slots, w, h, K, frameEnergyTH):
         fx, fy, cx, cy = K
         slots = np.ascontiguousarray(slots, dtype=np.int32)

@@ -61,6 +61,7 @@ struct BAParams
 	float fx, fy, cx, cy, fxi, fyi, wM3G, hM3G;
 	float frameEnergyTH[MAXF];
 	const float4* img[MAXF];
+	int fixA, fixB;            // setting_affineOptModeA/B < 0 (Residuals.cpp:257-258)
 };
 
 struct BAWorkspace
@@ -269,7 +270,7 @@ __global__ void __launch_bounds__(256) ba_linearize_kernel(BAParams B, const flo
 			const float eLeft = outlier ? th : energy;
 			proj[16 * (size_t)r + 2 * idx] = Ku; proj[16 * (size_t)r + 2 * idx + 1] = Kv;
 			float* s = sJ[g];
-			s[J_RESF + idx] = resF; s[J_IDX0 + idx] = g1; s[J_IDX1 + idx] = g2; s[J_AB0 + idx] = ja; s[J_AB1 + idx] = hw;
+			s[J_RESF + idx] = resF; s[J_IDX0 + idx] = g1; s[J_IDX1 + idx] = g2; s[J_AB0 + idx] = B.fixA ? 0.f : ja; s[J_AB1 + idx] = B.fixB ? 0.f : hw;   // :257-258
 			if (idx == 0)
 			{
 				newState[r] = outlier ? ST_OUTLIER : ST_IN;
@@ -854,6 +855,14 @@ extern "C" int dso_b200_ba_set_window(dso_b200_ctx* ctx, int nF, const int* fram
 	P.fxi = 1.0f / fx; P.fyi = 1.0f / fy;
 	P.wM3G = (float)(w - 3); P.hM3G = (float)(h - 3);
 	W->window_set = true; W->glue_set = false; W->res_set = false; W->lin_done = false; W->top_done = false;
+	return 0;
+}
+
+extern "C" int dso_b200_ba_set_affine_modes(dso_b200_ctx* ctx, float modeA, float modeB)
+{
+	ARG_CHECK(ctx && ctx->ba, "null argument");
+	ctx->ba->P.fixA = modeA < 0; ctx->ba->P.fixB = modeB < 0;
+	ctx->ba->lin_done = false; ctx->ba->top_done = false;
 	return 0;
 }
 

@@ -633,6 +633,11 @@ __device__ __forceinline__ void lm_step_warp(LMS& S, const float* s_tot, const T
 					if ((opt.affineOptModeA == 0 && (fabsf(logf((float)ra)) > 1.5f)) || (opt.affineOptModeB == 0 && (fabsf((float)rb) > 200.f))) ok = 0;
 				}
 				out->ok = ok;
+				if (ok)                                                            // :743-744
+				{
+					if (opt.affineOptModeA < 0) out->aff_a = 0;
+					if (opt.affineOptModeB < 0) out->aff_b = 0;
+				}
 			}
 		}
 		done = abort || next < 0;
@@ -658,6 +663,18 @@ __device__ __forceinline__ void lm_step_warp(LMS& S, const float* s_tot, const T
 		double rhs = -(take ? bn : S.b[i]);
 #pragma unroll
 		for (int j = 0; j < 8; j++) if (j == i) row[j] *= damp;
+		// :621-643 fixed-affine variants: the reference solves the 6x6 / 7x7 system without the fixed parameter's
+		// row and column; replacing that row and column by the identity's (and its right-hand side by 0) yields
+		// the same increments for the free parameters and exactly 0 for the fixed one.
+		const bool fixA = opt.affineOptModeA < 0, fixB = opt.affineOptModeB < 0;
+		if (fixA || fixB)
+		{
+			const bool fi = (i == 6 && fixA) || (i == 7 && fixB);
+#pragma unroll
+			for (int j = 0; j < 8; j++)
+				if (fi || (j == 6 && fixA) || (j == 7 && fixB)) row[j] = (i == j) ? 1.0 : 0.0;
+			if (fi) rhs = 0.0;
+		}
 #pragma unroll
 		for (int k = 0; k < 8; k++)
 		{
@@ -1185,8 +1202,6 @@ static int enqueue_track(dso_b200_ctx* ctx, int trk, int frame_slot, int nHyp, c
 	TrackerSlot& T = ctx->trk[trk];
 	dso_b200_track_opts o;
 	if (opts) o = *opts; else dso_b200_track_opts_default(&o);
-	ARG_CHECK(!(o.affineOptModeA < 0) && !(o.affineOptModeB < 0),
-	          "fixed-affine modes (CoarseTracker.cpp:621-643) are only implemented in dso_b200_track_hostloop");
 	// pageable staging: cudaMemcpyAsync returns once the source has been copied to the driver's staging
 	// area, so back-to-back asynchronous calls may reuse it
 	TrackIn hin[DSO_B200_MAX_HYP];

@@ -211,6 +211,10 @@ typedef struct
  * CalibHessian::fxl..cyl (HessianBlocks.h:361-368), per-frame frameEnergyTH (HessianBlocks.h:136). */
 int dso_b200_ba_set_window(dso_b200_ctx* ctx, int nF, const int* frame_slots, int w, int h,
                            float fx, float fy, float cx, float cy, const float* frameEnergyTH);
+/* setting_affineOptModeA/B (util/settings.cpp:119-120, read at Residuals.cpp:257-258): a negative mode fixes that
+ * affine parameter, i.e. the stored JabF row is zero.  Defaults (1e12, 1e8) optimise both.  The tracker takes the
+ * same two settings through dso_b200_track_opts. */
+int dso_b200_ba_set_affine_modes(dso_b200_ctx* ctx, float modeA, float modeB);
 /* Per-iteration glue computed on the host exactly as the reference does (FrameFramePrecalc::set,
  * HessianBlocks.cpp:213-250; EnergyFunctional::setAdjointsF / setDeltaF, EnergyFunctional.cpp:47-114,
  * 178-205).  precalc[h*nF+t]; adHost/adTarget[(h+t*nF)*64] doubles; adHTdeltaF[(h+t*nF)*8]; cDeltaF[4]. */

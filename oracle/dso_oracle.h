@@ -23,6 +23,10 @@ extern "C" {
 void dso_oracle_make_images(const float* color, int w, int h, int levels, const float* B,
                             float* const* dIp, float* const* absgrad);
 
+/* setting_affineOptModeA/B (util/settings.cpp:119-120): run-time globals of the reference; < 0 fixes the parameter
+ * (CoarseTracker.cpp:621-643, :743-744; Residuals.cpp:257-258).  Process-wide, like the reference's. */
+void dso_oracle_set_affine_modes(float modeA, float modeB);
+
 /* ---- tracker (a2..a6) ------------------------------------------------------------------------ */
 typedef struct dso_oracle_tracker dso_oracle_tracker;
 /* CoarseTracker ctor + makeK, CoarseTracker.cpp:59-131 */

@@ -30,8 +30,9 @@ static const int patternP[8][2] = { {0,-2}, {-1,-1}, {1,-1}, {-2,0}, {0,0}, {2,0
 // settings.cpp:103,110,124-125
 static const float setting_outlierTHSumComponent = 50 * 50;
 static const float setting_huberTH = 9;
-static const float setting_affineOptModeA = 1e12f;
-static const float setting_affineOptModeB = 1e8f;
+extern float dso_oracle_setting_affineOptModeA, dso_oracle_setting_affineOptModeB;   // oracle_tracker.cpp (settings.cpp:119-120)
+#define setting_affineOptModeA dso_oracle_setting_affineOptModeA
+#define setting_affineOptModeB dso_oracle_setting_affineOptModeB
 
 enum { ST_IN = 0, ST_OOB = 1, ST_OUTLIER = 2 };
 

@@ -74,6 +74,7 @@ def lib(kind="oracle"):
         if restype is not None:
             f.restype = restype
 
+    sig("dso_oracle_set_affine_modes", [C.c_float, C.c_float])
     sig("dso_oracle_make_images", [f32p, C.c_int, C.c_int, C.c_int, vp, C.POINTER(vp), C.POINTER(vp)])
     sig("dso_oracle_tracker_create", [C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float], vp)
     sig("dso_oracle_tracker_destroy", [vp])
@@ -103,6 +104,11 @@ def lib(kind="oracle"):
     sig("dso_oracle_ba_accumulate_SC", [vp, C.c_int, C.c_int, f64p, f64p, f32p, f32p, f32p])
     _LIBS[kind] = L
     return L
+
+
+def set_affine_modes(mode_a=1e12, mode_b=1e8, kind="oracle"):
+    """setting_affineOptModeA/B (settings.cpp:119-120); process-wide: restore the defaults after use."""
+    lib(kind).dso_oracle_set_affine_modes(mode_a, mode_b)
 
 
 def _ptr_array(arrs):

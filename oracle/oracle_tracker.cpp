@@ -13,8 +13,15 @@ using namespace orc;
 // settings.cpp:110,125,138 (defaults)
 static const float setting_huberTH = 9;
 static const float setting_coarseCutoffTH = 20;
-static const float setting_affineOptModeA = 1e12f;
-static const float setting_affineOptModeB = 1e8f;
+// settings.cpp:119-120 are run-time globals in the reference (-1: fixed, >= 0: optimised); same here
+float dso_oracle_setting_affineOptModeA = 1e12f;
+float dso_oracle_setting_affineOptModeB = 1e8f;
+#define setting_affineOptModeA dso_oracle_setting_affineOptModeA
+#define setting_affineOptModeB dso_oracle_setting_affineOptModeB
+extern "C" void dso_oracle_set_affine_modes(float modeA, float modeB)
+{
+	dso_oracle_setting_affineOptModeA = modeA; dso_oracle_setting_affineOptModeB = modeB;
+}
 // HessianBlocks.h:54-61
 #define SCALE_XI_ROT 1.0f
 #define SCALE_XI_TRANS 0.5f

@@ -96,6 +96,8 @@ struct dso_oracle_tracker
 	void calib() { set_calib(w, h, levels, fx, fy, cx, cy); }
 };
 
+extern "C" void dso_ref_set_affine_modes(float modeA, float modeB) { setting_affineOptModeA = modeA; setting_affineOptModeB = modeB; }
+
 extern "C" dso_oracle_tracker* dso_ref_tracker_create(int w, int h, int levels, float fx, float fy, float cx, float cy)
 {
 	dso_oracle_tracker* T = new dso_oracle_tracker();

@@ -121,3 +121,25 @@ def test_ba_set_frames_matches_oracle_glue(pkg, oracle, window_small):
     Ao = B.accumulate_A(False)
     assert rel_err_matrix(st["H_A"], Ao["H"]).max() <= 1e-3     # precalc floats may differ in the last bit -> a few state ties
     ctx.close()
+
+
+@pytest.mark.parametrize("modes", [(-1.0, -1.0), (1e12, -1.0), (-1.0, 1e8)])
+def test_ba_fixed_affine_modes(pkg, oracle, window_small, modes):
+    """Residuals.cpp:257-258: the stored JabF rows are zero for a fixed parameter; everything downstream follows"""
+    W = window_small
+    B, ctx = _setup(pkg, oracle, W)
+    try:
+        oracle.set_affine_modes(*modes)
+        ctx.ba_set_affine_modes(*modes)
+        lo, lg = B.linearize(), ctx.ba_linearize()
+        ok = lo["newState"] != 1
+        assert np.array_equal(lo["newState"], lg["newState"])
+        assert np.array_equal(lo["J"][ok].view(np.uint32), lg["J"][ok].view(np.uint32))
+        B.apply_res(); ctx.ba_apply_res()
+        Ao, Ag = B.accumulate_A(False), ctx.ba_accumulate_A()
+        _check_system(Ag["H"], Ag["b"], Ao["H"], Ao["b"])
+        So, Sg = B.accumulate_SC(False), ctx.ba_accumulate_SC()
+        _check_system(Sg["H"], Sg["b"], So["H"], So["b"])
+    finally:
+        oracle.set_affine_modes()
+        ctx.close()

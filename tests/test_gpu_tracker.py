@@ -165,3 +165,29 @@ def test_track_replay_abort_matches_oracle(ctx_vga, scen_vga):
     full = ctx_vga.track_batched(0, 3, ident, scen_vga.a0, scen_vga.b0, scen_vga.levels - 1)[0]
     ok, lr = ctx_vga.replay_abort(full, thr)
     assert ok == 0 and np.isnan(lr[0])
+
+
+@pytest.mark.parametrize("modes", [(-1.0, -1.0), (1e12, -1.0), (-1.0, 1e8)])
+def test_track_fixed_affine_modes(ctx_vga, scen_vga, oracle, modes):
+    """setting_affineOptModeA/B < 0: 6x6 / 7x7 solves (CoarseTracker.cpp:621-643) and the zeroed outputs (:743-744)"""
+    syn = scen_vga.syn
+    ident = syn.pose12((np.eye(3), np.zeros(3)))
+    a, b = scen_vga.a0, scen_vga.b0
+    opts = ctx_vga.default_opts()
+    opts.affineOptModeA, opts.affineOptModeB = modes
+    scen_vga.oracle_set_frame(0)
+    try:
+        oracle.set_affine_modes(*modes)
+        ro = scen_vga.trk.track(ident, a, b, scen_vga.levels - 1)
+    finally:
+        oracle.set_affine_modes()
+    for rg in (ctx_vga.track_batched(0, 1, ident, a, b, scen_vga.levels - 1, opts=opts)[0],
+               ctx_vga.track_hostloop(0, 1, ident, a, b, scen_vga.levels - 1, opts=opts)):
+        assert rg.ok == ro.ok
+        if modes[0] < 0:
+            assert rg.aff_a == 0 == ro.aff_a
+        if modes[1] < 0:
+            assert rg.aff_b == 0 == ro.aff_b
+        same = list(ro.trace[:ro.trace_len]) == list(rg.trace[:rg.trace_len])
+        assert _pose_err(syn, rg.pose, ro.pose) <= (TOL_POSE if same else 2e-3)
+        assert abs(rg.aff_a - ro.aff_a) <= 1e-5 and abs(rg.aff_b - ro.aff_b) <= (1e-3 if same else 0.2)

@@ -132,3 +132,41 @@ def test_ba_linearize_accumulate(pkg, window_small):
     # the reference's thread-pool branch (6 workers, chunks of 50) agrees with its single-thread branch to float noise
     Am = Br.accumulate_A(True)
     assert np.abs(Am["H"] - Ar["H"]).max() <= 1e-5 * np.abs(Ar["H"]).max()
+
+
+@pytest.mark.parametrize("modes", [(-1.0, -1.0), (1e12, -1.0), (-1.0, 1e8)])
+def test_fixed_affine_modes_agree(trackers, pkg, window_small, modes):
+    """setting_affineOptModeA/B < 0 (CoarseTracker.cpp:621-643, :743-744; Residuals.cpp:257-258)"""
+    W, syn, levels, frames, to, tr, (a0, b0) = trackers
+    ident = syn.pose12((np.eye(3), np.zeros(3)))
+    img = frames[0][0]
+    pyr = O.make_images(img, levels)
+    to.set_new_frame(flat(pyr[0]), 1.0)
+    tr.set_new_frame(flat(pyr[0]), 1.0)
+    try:
+        O.set_affine_modes(*modes)
+        O.set_affine_modes(*modes, kind="ref")
+        ro = to.track(ident, a0, b0, levels - 1)
+        rr = tr.track(ident, a0, b0, levels - 1)
+        assert ro.ok == rr.ok
+        assert np.abs(np.array(ro.pose) - np.array(rr.pose)).max() < 1e-9
+        assert abs(ro.aff_a - rr.aff_a) < 1e-9 and abs(ro.aff_b - rr.aff_b) < 1e-6
+        if modes[0] < 0:
+            assert ro.aff_a == rr.aff_a == 0
+        if modes[1] < 0:
+            assert ro.aff_b == rr.aff_b == 0
+        p0 = [O.make_images(im, 1)[0][0] for im in window_small.images]
+        lo, lr = O.BA(window_small, p0).linearize(), O.BA(window_small, p0, kind="ref").linearize()
+        ok = lo["newState"] != 1
+        assert np.array_equal(bits(lo["J"][ok]), bits(lr["J"][ok]))
+        J = lo["J"][lo["newState"] == 0]
+        assert len(J) > 0
+        if modes[0] < 0:
+            assert not J[:, 46:54].any()
+        else:
+            assert J[:, 46:54].any()
+        if modes[1] < 0:
+            assert not J[:, 54:62].any()
+    finally:
+        O.set_affine_modes()
+        O.set_affine_modes(kind="ref")
