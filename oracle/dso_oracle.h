@@ -121,6 +121,27 @@ void dso_oracle_ba_accumulate_SC(dso_oracle_ba*, int MT, int nthreads, double* H
 /* same, multi-threaded linearizeAll (static split ceil(n/nthreads), FullSystemOptimize.cpp:164) for timing */
 double dso_oracle_ba_linearize_mt(dso_oracle_ba*, int nthreads);
 
+/* ---- N1/N2 rows: solveSystemF tail, resubstituteF_MT, linearised residuals --------------------- */
+/* accumulateLF_MT (EnergyFunctional.cpp:233-254): addPoint<1> over linearised active residuals, priors added in the
+ * stitch (AccumulatedTopHessian.cpp:314-324). per-point outputs are Hdd_accLF, bd_accLF, Hcd_accLF. */
+void dso_oracle_ba_accumulate_L(dso_oracle_ba*, int MT, int nthreads, double* H, double* b, int* resInL,
+                                float* Hdd, float* bd, float* Hcd4);
+/* EnergyFunctional::cPrior (4), frames[i]->prior / delta_prior / delta (8 per frame, EnergyFunctionalStructs.cpp:55-63),
+ * HM (N*N row-major), bM (N), N = 8nF+4.  NULL = zeros. */
+void dso_oracle_ba_set_priors(dso_oracle_ba*, const double* cPrior4, const double* framePrior, const double* frameDeltaPrior,
+                              const double* frameDelta, const double* HM, const double* bM);
+/* lastNullspaces_pose followed by lastNullspaces_scale: n vectors of N doubles (EnergyFunctional.cpp:745-747) */
+void dso_oracle_ba_set_nullspaces(dso_oracle_ba*, const double* ns, int n);
+/* EFResidual::fixLinearizationF (EnergyFunctionalStructs.cpp:89-115) on the active residuals flagged in `which`
+ * (NULL = all active); res_toZeroF_out: nR*8 (may be NULL) */
+void dso_oracle_ba_fix_linearization(dso_oracle_ba*, const unsigned char* which, float* res_toZeroF_out);
+/* EnergyFunctional::solveSystemF (EnergyFunctional.cpp:802-924) including its three accumulate calls and
+ * resubstituteF_MT (:276-330).  solverMode: setting_solverMode bits (settings.h:35-46; default 128|2048); the SVD and
+ * ORTHOGONALIZE_SYSTEM branches are not restated (returns -1).  x_out: N (= lastX), pointStep_out: nP (PointHessian::step),
+ * HFinal_out/bFinal_out: the damped Schur system that is solved (debug; may be NULL). */
+int dso_oracle_ba_solve(dso_oracle_ba*, int iteration, double lambda, int solverMode, double solverModeDelta, int MT, int nthreads,
+                        double* x_out, float* pointStep_out, double* HFinal_out, double* bFinal_out);
+
 #ifdef __cplusplus
 }
 #endif

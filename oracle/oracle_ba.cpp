@@ -303,8 +303,13 @@ struct dso_oracle_ba
 	float cDeltaF[4];
 	std::vector<Pt> points;
 	std::vector<Res> res;
+	// priors and marginalisation state (EnergyFunctional members cPrior, frames[i]->prior/delta_prior/delta, HM, bM)
+	double cPrior[4];
+	std::vector<double> framePrior, frameDeltaPrior, frameDelta, HM, bM;
+	std::vector<double> nullspaces; int nNullspaces;     // lastNullspaces_pose then _scale, each 8nF+4 long
+	std::vector<float> pointStep;
 	Pool* pool; int poolN;
-	dso_oracle_ba() : pool(0), poolN(0) {}
+	dso_oracle_ba() : nNullspaces(0), pool(0), poolN(0) { for (int i = 0; i < 4; i++) cPrior[i] = 0; }
 	Pool* getPool(int n) { if (!pool || poolN != n) { delete pool; pool = new Pool(n); poolN = n; } return pool; }
 };
 
@@ -406,20 +411,21 @@ extern "C" void dso_oracle_ba_prepare(dso_oracle_ba* B)
 			}
 			for (int i = 0; i < 64; i++) { B->adHostF[(h + t * nF) * 64 + i] = (float)AH[i]; B->adTargetF[(h + t * nF) * 64 + i] = (float)AT[i]; }
 		}
-	// setDeltaF, EnergyFunctional.cpp:178-193 (row vector times 8x8, float; only consumed by the
-	// linearised-residual mode, which is outside this oracle's scope, so plain left-to-right sums)
+	// setDeltaF, EnergyFunctional.cpp:178-193 (row vector times 8x8, float; each coefficient an unrolled 8-term redux)
 	for (int h = 0; h < nF; h++)
 		for (int t = 0; t < nF; t++)
 		{
 			int idx = h + t * nF;
 			for (int c = 0; c < 8; c++)
 			{
-				float s0 = 0, s1 = 0;
+				float p0[8], p1[8];
 				for (int r = 0; r < 8; r++)
 				{
-					s0 += (float)(B->frames[h].state[r] - B->frames[h].state_zero[r]) * B->adHostF[idx * 64 + r * 8 + c];
-					s1 += (float)(B->frames[t].state[r] - B->frames[t].state_zero[r]) * B->adTargetF[idx * 64 + r * 8 + c];
+					p0[r] = (float)(B->frames[h].state[r] - B->frames[h].state_zero[r]) * B->adHostF[idx * 64 + r * 8 + c];
+					p1[r] = (float)(B->frames[t].state[r] - B->frames[t].state_zero[r]) * B->adTargetF[idx * 64 + r * 8 + c];
 				}
+				const float s0 = ((p0[0] + p0[1]) + (p0[2] + p0[3])) + ((p0[4] + p0[5]) + (p0[6] + p0[7]));
+				const float s1 = ((p1[0] + p1[1]) + (p1[2] + p1[3])) + ((p1[4] + p1[5]) + (p1[6] + p1[7]));
 				B->adHTdeltaF[idx * 8 + c] = s0 + s1;
 			}
 		}
@@ -733,18 +739,54 @@ extern "C" void dso_oracle_ba_apply_res(dso_oracle_ba* B, unsigned char* isActiv
 	}
 }
 
-// AccumulatedTopHessianSSE::addPoint<0>, AccumulatedTopHessian.cpp:39-177
-static void addPointA(dso_oracle_ba* B, Pt& p, AccApprox* acc, int* nres)
+// Eigen's unrolled fixed-size redux (halves, then halves again): 6 terms (p0+(p1+p2))+(p3+(p4+p5)), 4 terms (p0+p1)+(p2+p3)
+static inline float dot6_tree(const float* a, const float* b)
+{
+	return (a[0] * b[0] + (a[1] * b[1] + a[2] * b[2])) + (a[3] * b[3] + (a[4] * b[4] + a[5] * b[5]));
+}
+static inline float sum8_tree(const float* p) { return ((p[0] + p[1]) + (p[2] + p[3])) + ((p[4] + p[5]) + (p[6] + p[7])); }
+static inline float dot4_tree(const float* a, const float* b) { return (a[0] * b[0] + a[1] * b[1]) + (a[2] * b[2] + a[3] * b[3]); }
+
+// Jp*delta of fixLinearizationF / addPoint<1> (EnergyFunctionalStructs.cpp:92-100, AccumulatedTopHessian.cpp:82-87)
+static inline void jp_delta(const dso_oracle_ba* B, const Res& r, const RawJ* J, float dd, float* out4)
+{
+	const float* dp = &B->adHTdeltaF[(r.host + B->nF * r.target) * 8];
+	out4[0] = dot6_tree(J->Jpdxi[0], dp) + dot4_tree(J->Jpdc[0], B->cDeltaF) + J->Jpdd[0] * dd;
+	out4[1] = dot6_tree(J->Jpdxi[1], dp) + dot4_tree(J->Jpdc[1], B->cDeltaF) + J->Jpdd[1] * dd;
+	out4[2] = dp[6]; out4[3] = dp[7];
+}
+
+// AccumulatedTopHessianSSE::addPoint<mode>, AccumulatedTopHessian.cpp:39-177 (0 = active, 1 = linearised, 2 = marginalise)
+static void addPointA(dso_oracle_ba* B, Pt& p, AccApprox* acc, int* nres, int mode = 0)
 {
 	int nF = B->nF;
 	float bd_acc = 0, Hdd_acc = 0, Hcd_acc[4] = { 0, 0, 0, 0 };
 	for (int ri : p.residualsAll)
 	{
 		Res& r = B->res[ri];
-		if (r.isLinearized || !r.isActive) continue;
+		if (mode == 0 && (r.isLinearized || !r.isActive)) continue;
+		if (mode == 1 && (!r.isLinearized || !r.isActive)) continue;
+		if (mode == 2 && !r.isActive) continue;
 		const RawJ* rJ = &r.efJ;
 		int htIDX = r.host + r.target * nF;
+		float resLin[8];
 		const float* resApprox = rJ->resF;
+		if (mode == 2) resApprox = r.res_toZeroF;
+		if (mode == 1)
+		{
+			float d[4];
+			jp_delta(B, r, rJ, p.deltaF, d);
+			for (int i = 0; i < patternNum; i++)
+			{
+				float rtz = r.res_toZeroF[i];              // :93-99, one mul + one add per term
+				rtz = rtz + rJ->JIdx[0][i] * d[0];
+				rtz = rtz + rJ->JIdx[1][i] * d[1];
+				rtz = rtz + rJ->JabF[0][i] * d[2];
+				rtz = rtz + rJ->JabF[1][i] * d[3];
+				resLin[i] = rtz;
+			}
+			resApprox = resLin;
+		}
 		float JI_r[2] = { 0, 0 }, Jab_r[2] = { 0, 0 }, rr = 0;
 		for (int i = 0; i < patternNum; i++)
 		{
@@ -766,8 +808,21 @@ static void addPointA(dso_oracle_ba* B, Pt& p, AccApprox* acc, int* nres)
 		for (int k = 0; k < 4; k++) Hcd_acc[k] += rJ->Jpdc[0][k] * Ji2_Jpdd[0] + rJ->Jpdc[1][k] * Ji2_Jpdd[1];
 		(*nres)++;
 	}
-	p.Hdd_accAF = Hdd_acc; p.bd_accAF = bd_acc;
-	for (int k = 0; k < 4; k++) p.Hcd_accAF[k] = Hcd_acc[k];
+	if (mode == 0)
+	{
+		p.Hdd_accAF = Hdd_acc; p.bd_accAF = bd_acc;
+		for (int k = 0; k < 4; k++) p.Hcd_accAF[k] = Hcd_acc[k];
+	}
+	else
+	{
+		p.Hdd_accLF = Hdd_acc; p.bd_accLF = bd_acc;
+		for (int k = 0; k < 4; k++) p.Hcd_accLF[k] = Hcd_acc[k];
+	}
+	if (mode == 2)
+	{
+		p.Hdd_accAF = 0; p.bd_accAF = 0;
+		for (int k = 0; k < 4; k++) p.Hcd_accAF[k] = 0;
+	}
 }
 
 static inline void mm8(const double* A, const double* Bm, double* C, bool transB)
@@ -828,8 +883,8 @@ static void stitchA(dso_oracle_ba* B, std::vector<std::vector<AccApprox>>& accs,
 }
 
 // accumulateAF_MT, EnergyFunctional.cpp:209-232 + stitchDoubleMT, AccumulatedTopHessian.h:91-139
-extern "C" void dso_oracle_ba_accumulate_A(dso_oracle_ba* B, int MT, int nthreads, double* H, double* b, int* resInA,
-                                           float* Hdd, float* bd, float* Hcd4)
+static void accumulate_top(dso_oracle_ba* B, int mode, bool usePrior, int MT, int nthreads, double* H, double* b, int* resInA,
+                           float* Hdd, float* bd, float* Hcd4)
 {
 	int nF = B->nF, N = 8 * nF + CPARS, nP = (int)B->points.size();
 	int T = MT ? nthreads : 1;
@@ -840,7 +895,7 @@ extern "C" void dso_oracle_ba_accumulate_A(dso_oracle_ba* B, int MT, int nthread
 	if (MT)
 	{
 		Pool* pool = B->getPool(nthreads);
-		pool->reduce([&](int lo, int hi, int tid) { for (int i = lo; i < hi; i++) addPointA(B, B->points[i], accs[tid].data(), &nres[tid]); }, 0, nP, 50);
+		pool->reduce([&](int lo, int hi, int tid) { for (int i = lo; i < hi; i++) addPointA(B, B->points[i], accs[tid].data(), &nres[tid], mode); }, 0, nP, 50);
 		std::vector<std::vector<double>> Hs(T, std::vector<double>(N * N, 0.0)), bs(T, std::vector<double>(N, 0.0));
 		pool->reduce([&](int lo, int hi, int tid) { stitchA(B, accs, T, Hs[tid].data(), bs[tid].data(), lo, hi); }, 0, nF * nF, 0);
 		for (int i = 0; i < T; i++)
@@ -852,8 +907,21 @@ extern "C" void dso_oracle_ba_accumulate_A(dso_oracle_ba* B, int MT, int nthread
 	}
 	else
 	{
-		for (int i = 0; i < nP; i++) addPointA(B, B->points[i], accs[0].data(), &nres[0]);
+		for (int i = 0; i < nP; i++) addPointA(B, B->points[i], accs[0].data(), &nres[0], mode);
 		stitchA(B, accs, 1, H, b, 0, nF * nF);
+	}
+	if (usePrior)
+	{
+		// AccumulatedTopHessian.cpp:314-324 ("only do this on one thread")
+		for (int i = 0; i < CPARS; i++) { H[i * N + i] += B->cPrior[i]; b[i] += B->cPrior[i] * (double)B->cDeltaF[i]; }
+		if ((int)B->framePrior.size() == 8 * nF)
+			for (int h = 0; h < nF; h++)
+				for (int i = 0; i < 8; i++)
+				{
+					const int k = CPARS + h * 8 + i;
+					H[k * N + k] += B->framePrior[h * 8 + i];
+					b[k] += B->framePrior[h * 8 + i] * B->frameDeltaPrior[h * 8 + i];
+				}
 	}
 	// "make diagonal by copying over parts", AccumulatedTopHessian.h:126-138
 	for (int h = 0; h < nF; h++)
@@ -870,10 +938,23 @@ extern "C" void dso_oracle_ba_accumulate_A(dso_oracle_ba* B, int MT, int nthread
 	if (resInA) *resInA = nres[0];
 	for (int i = 0; i < nP; i++)
 	{
-		if (Hdd) Hdd[i] = B->points[i].Hdd_accAF;
-		if (bd) bd[i] = B->points[i].bd_accAF;
-		if (Hcd4) memcpy(Hcd4 + 4 * i, B->points[i].Hcd_accAF, 16);
+		const Pt& p = B->points[i];
+		if (Hdd) Hdd[i] = mode == 0 ? p.Hdd_accAF : p.Hdd_accLF;
+		if (bd) bd[i] = mode == 0 ? p.bd_accAF : p.bd_accLF;
+		if (Hcd4) memcpy(Hcd4 + 4 * i, mode == 0 ? p.Hcd_accAF : p.Hcd_accLF, 16);
 	}
+}
+
+extern "C" void dso_oracle_ba_accumulate_A(dso_oracle_ba* B, int MT, int nthreads, double* H, double* b, int* resInA,
+                                           float* Hdd, float* bd, float* Hcd4)
+{
+	accumulate_top(B, 0, false, MT, nthreads, H, b, resInA, Hdd, bd, Hcd4);
+}
+// accumulateLF_MT, EnergyFunctional.cpp:233-254: addPoint<1> over the linearised residuals, stitch with usePrior = true
+extern "C" void dso_oracle_ba_accumulate_L(dso_oracle_ba* B, int MT, int nthreads, double* H, double* b, int* resInL,
+                                           float* Hdd, float* bd, float* Hcd4)
+{
+	accumulate_top(B, 1, true, MT, nthreads, H, b, resInL, Hdd, bd, Hcd4);
 }
 
 struct SCAcc
@@ -1038,4 +1119,193 @@ extern "C" void dso_oracle_ba_accumulate_SC(dso_oracle_ba* B, int MT, int nthrea
 		if (bdSumF) bdSumF[i] = B->points[i].bdSumF;
 		if (idepth_hessian) idepth_hessian[i] = B->points[i].idepth_hessian;
 	}
+}
+
+// =================================================================================================
+// N1: solveSystemF tail + resubstituteF_MT (EnergyFunctional.cpp:802-924, 276-330) and the pieces of
+// N2 it reads (fixLinearizationF, EnergyFunctionalStructs.cpp:89-115)
+// =================================================================================================
+extern "C" void dso_oracle_ba_set_priors(dso_oracle_ba* B, const double* cPrior4, const double* framePrior, const double* frameDeltaPrior,
+                                         const double* frameDelta, const double* HM, const double* bM)
+{
+	const int nF = B->nF, N = 8 * nF + CPARS;
+	for (int i = 0; i < 4; i++) B->cPrior[i] = cPrior4 ? cPrior4[i] : 0.0;
+	B->framePrior.assign(8 * nF, 0.0); B->frameDeltaPrior.assign(8 * nF, 0.0); B->frameDelta.assign(8 * nF, 0.0);
+	if (framePrior) B->framePrior.assign(framePrior, framePrior + 8 * nF);
+	if (frameDeltaPrior) B->frameDeltaPrior.assign(frameDeltaPrior, frameDeltaPrior + 8 * nF);
+	if (frameDelta) B->frameDelta.assign(frameDelta, frameDelta + 8 * nF);
+	B->HM.assign((size_t)N * N, 0.0); B->bM.assign(N, 0.0);
+	if (HM) B->HM.assign(HM, HM + (size_t)N * N);
+	if (bM) B->bM.assign(bM, bM + N);
+}
+extern "C" void dso_oracle_ba_set_nullspaces(dso_oracle_ba* B, const double* ns, int n)
+{
+	const int N = 8 * B->nF + CPARS;
+	B->nNullspaces = n;
+	B->nullspaces.assign(ns, ns + (size_t)n * N);
+}
+
+// EFResidual::fixLinearizationF for the flagged residuals (which == NULL: every active one)
+extern "C" void dso_oracle_ba_fix_linearization(dso_oracle_ba* B, const unsigned char* which, float* res_toZeroF_out)
+{
+	for (size_t i = 0; i < B->res.size(); i++)
+	{
+		Res& r = B->res[i];
+		if (r.isActive && (!which || which[i]))
+		{
+			const RawJ* J = &r.efJ;
+			float d[4];
+			jp_delta(B, r, J, B->points[r.point].deltaF, d);
+			for (int k = 0; k < patternNum; k++)
+			{
+				float rtz = J->resF[k];
+				rtz = rtz - J->JIdx[0][k] * d[0];
+				rtz = rtz - J->JIdx[1][k] * d[1];
+				rtz = rtz - J->JabF[0][k] * d[2];
+				rtz = rtz - J->JabF[1][k] * d[3];
+				r.res_toZeroF[k] = rtz;
+			}
+			r.isLinearized = true;
+		}
+		if (res_toZeroF_out) memcpy(res_toZeroF_out + 8 * i, r.res_toZeroF, 32);
+	}
+}
+
+// EnergyFunctional::orthogonalize(VecX* b, 0), :741-792: x -= 0.5 (N Npi^T + Npi N^T) x
+static void orthogonalize_vec(const dso_oracle_ba* B, double solverModeDelta, std::vector<double>& x)
+{
+	const int N = (int)x.size(), k = B->nNullspaces;
+	if (k == 0) return;
+	std::vector<double> Nn((size_t)N * k), U((size_t)N * k), S(k), V((size_t)k * k);
+	for (int j = 0; j < k; j++)
+	{
+		double n2 = 0;
+		for (int i = 0; i < N; i++) n2 += B->nullspaces[(size_t)j * N + i] * B->nullspaces[(size_t)j * N + i];
+		const double nrm = std::sqrt(n2);
+		for (int i = 0; i < N; i++) Nn[(size_t)i * k + j] = B->nullspaces[(size_t)j * N + i] / nrm;
+	}
+	orc::jacobi_svd_thin(Nn.data(), N, k, U.data(), S.data(), V.data());
+	double maxSv = 0;
+	for (int i = 0; i < k; i++) if (S[i] > maxSv) maxSv = S[i];
+	for (int i = 0; i < k; i++) S[i] = (S[i] > solverModeDelta * maxSv) ? 1.0 / S[i] : 0.0;
+	// Npi = U diag(S) V^T  (N x k);  NNpiT = Nn Npi^T (N x N);  NNpiTS = 0.5 (NNpiT + NNpiT^T)
+	std::vector<double> Npi((size_t)N * k, 0.0), P((size_t)N * N, 0.0);
+	for (int i = 0; i < N; i++)
+		for (int j = 0; j < k; j++)
+		{
+			double s = 0;
+			for (int q = 0; q < k; q++) s += U[(size_t)i * k + q] * S[q] * V[(size_t)j * k + q];
+			Npi[(size_t)i * k + j] = s;
+		}
+	for (int i = 0; i < N; i++)
+		for (int j = 0; j < N; j++)
+		{
+			double s = 0;
+			for (int q = 0; q < k; q++) s += Nn[(size_t)i * k + q] * Npi[(size_t)j * k + q];
+			P[(size_t)i * N + j] = s;
+		}
+	std::vector<double> y(N);
+	for (int i = 0; i < N; i++)
+	{
+		double s = 0;
+		for (int j = 0; j < N; j++) s += 0.5 * (P[(size_t)i * N + j] + P[(size_t)j * N + i]) * x[j];
+		y[i] = s;
+	}
+	for (int i = 0; i < N; i++) x[i] -= y[i];
+}
+
+#define SOLVER_SVD 1
+#define SOLVER_ORTHOGONALIZE_SYSTEM 2
+#define SOLVER_USE_GN 64
+#define SOLVER_FIX_LAMBDA 128
+#define SOLVER_ORTHOGONALIZE_X 256
+#define SOLVER_ORTHOGONALIZE_X_LATER 2048
+
+// EnergyFunctional::resubstituteF_MT + resubstituteFPt, EnergyFunctional.cpp:276-330
+static void resubstitute(dso_oracle_ba* B, const std::vector<double>& x)
+{
+	const int nF = B->nF, N = 8 * nF + CPARS, nP = (int)B->points.size();
+	std::vector<float> xF(N), xAd((size_t)nF * nF * 8);
+	for (int i = 0; i < N; i++) xF[i] = (float)x[i];
+	for (int h = 0; h < nF; h++)
+		for (int t = 0; t < nF; t++)
+		{
+			const float* AH = &B->adHostF[(h + nF * t) * 64];
+			const float* AT = &B->adTargetF[(h + nF * t) * 64];
+			for (int j = 0; j < 8; j++)
+			{
+				// (1x8)*(8x8) coefficient products, each an unrolled 8-term redux, then the two rows added (:291-292)
+				float ph[8], pt[8];
+				for (int i = 0; i < 8; i++) { ph[i] = xF[CPARS + 8 * h + i] * AH[i * 8 + j]; pt[i] = xF[CPARS + 8 * t + i] * AT[i * 8 + j]; }
+				xAd[(size_t)(nF * h + t) * 8 + j] = sum8_tree(ph) + sum8_tree(pt);
+			}
+		}
+	B->pointStep.assign(nP, 0.f);
+	for (int k = 0; k < nP; k++)
+	{
+		Pt& p = B->points[k];
+		int ngoodres = 0;
+		for (int ri : p.residualsAll) if (B->res[ri].isActive) ngoodres++;
+		if (ngoodres == 0) { B->pointStep[k] = 0; continue; }
+		float b = p.bdSumF;
+		float hc[4];
+		for (int i = 0; i < 4; i++) hc[i] = p.Hcd_accAF[i] + p.Hcd_accLF[i];
+		b -= dot4_tree(&xF[0], hc);
+		for (int ri : p.residualsAll)
+		{
+			const Res& r = B->res[ri];
+			if (!r.isActive) continue;
+			const float* xa = &xAd[(size_t)(r.host * nF + r.target) * 8];
+			float pr[8];
+			for (int i = 0; i < 8; i++) pr[i] = xa[i] * r.JpJdF[i];
+			b -= sum8_tree(pr);
+		}
+		B->pointStep[k] = -b * p.HdiF;
+	}
+}
+
+// EnergyFunctional::solveSystemF, :802-924.  Restated: the default solver (LDLT on the diagonally scaled system) with
+// SOLVER_USE_GN / SOLVER_FIX_LAMBDA / SOLVER_ORTHOGONALIZE_X(_LATER); the SVD and ORTHOGONALIZE_SYSTEM branches return -1.
+// x_out: 8nF+4 (= lastX; frame steps are -x segments, the calibration step -x.head<4>), pointStep_out: nP (PointHessian::step).
+extern "C" int dso_oracle_ba_solve(dso_oracle_ba* B, int iteration, double lambda, int solverMode, double solverModeDelta, int MT, int nthreads,
+                                   double* x_out, float* pointStep_out, double* HFinal_out, double* bFinal_out)
+{
+	if (solverMode & SOLVER_USE_GN) lambda = 0;
+	if (solverMode & SOLVER_FIX_LAMBDA) lambda = 1e-5;
+	if (solverMode & (SOLVER_SVD | SOLVER_ORTHOGONALIZE_SYSTEM)) return -1;
+	const int nF = B->nF, N = 8 * nF + CPARS;
+	if ((int)B->bM.size() != N) dso_oracle_ba_set_priors(B, B->cPrior, 0, 0, 0, 0, 0);
+	std::vector<double> HA((size_t)N * N), bA(N), HL((size_t)N * N), bL(N), HS((size_t)N * N), bS(N);
+	accumulate_top(B, 0, false, MT, nthreads, HA.data(), bA.data(), 0, 0, 0, 0);     // :816
+	accumulate_top(B, 1, true, MT, nthreads, HL.data(), bL.data(), 0, 0, 0, 0);      // :817
+	dso_oracle_ba_accumulate_SC(B, MT, nthreads, HS.data(), bS.data(), 0, 0, 0);      // :820
+	std::vector<double> d(N), bMtop(N), HF((size_t)N * N), bF(N);
+	for (int i = 0; i < CPARS; i++) d[i] = (double)B->cDeltaF[i];
+	for (int i = 0; i < 8 * nF; i++) d[CPARS + i] = B->frameDelta[i];
+	for (int i = 0; i < N; i++)
+	{
+		double s = 0;
+		for (int j = 0; j < N; j++) s += B->HM[(size_t)i * N + j] * d[j];
+		bMtop[i] = B->bM[i] + s;                                                       // :824
+	}
+	for (size_t i = 0; i < (size_t)N * N; i++) HF[i] = (HL[i] + B->HM[i]) + HA[i];     // :857
+	for (int i = 0; i < N; i++) bF[i] = ((bL[i] + bMtop[i]) + bA[i]) - bS[i];          // :859
+	for (int i = 0; i < N; i++) HF[(size_t)i * N + i] *= (1 + lambda);                  // :865
+	const double isc = 1.0f / (1 + lambda);                                             // :866
+	for (size_t i = 0; i < (size_t)N * N; i++) HF[i] -= HS[i] * isc;
+	if (HFinal_out) memcpy(HFinal_out, HF.data(), sizeof(double) * N * N);
+	if (bFinal_out) memcpy(bFinal_out, bF.data(), sizeof(double) * N);
+	// :905-908
+	std::vector<double> sv(N), Hs((size_t)N * N), bs(N), y(N), x(N);
+	for (int i = 0; i < N; i++) sv[i] = 1.0 / std::sqrt(HF[(size_t)i * N + i] + 10);
+	for (int i = 0; i < N; i++) for (int j = 0; j < N; j++) Hs[(size_t)i * N + j] = (sv[i] * HF[(size_t)i * N + j]) * sv[j];
+	for (int i = 0; i < N; i++) bs[i] = sv[i] * bF[i];
+	orc::ldlt_solve_n(Hs.data(), bs.data(), y.data(), N);
+	for (int i = 0; i < N; i++) x[i] = sv[i] * y[i];
+	if ((solverMode & SOLVER_ORTHOGONALIZE_X) || (iteration >= 2 && (solverMode & SOLVER_ORTHOGONALIZE_X_LATER)))
+		orthogonalize_vec(B, solverModeDelta, x);                                       // :913-917
+	resubstitute(B, x);                                                                 // :925
+	if (x_out) memcpy(x_out, x.data(), sizeof(double) * N);
+	if (pointStep_out) memcpy(pointStep_out, B->pointStep.data(), sizeof(float) * B->pointStep.size());
+	return 0;
 }

@@ -12,6 +12,7 @@
 #include <cmath>
 #include <cstring>
 #include <algorithm>
+#include <vector>
 
 namespace orc {
 
@@ -236,6 +237,87 @@ static inline void ldlt_solve(const double* Ain, const double* rhs, double* x, i
 	for (int k = n - 1; k >= 0; k--) std::swap(y[k], y[transp[k]]);
 	for (int i = 0; i < n; i++) x[i] = y[i];
 	(void)perm;
+}
+
+// ---- dynamic-size pieces for the solveSystemF tail (EnergyFunctional.cpp:802-924) ----
+// Eigen::LDLT<MatrixXd> (diagonal pivoting), same algorithm as ldlt_solve above for any n; A row-major n x n.
+static inline void ldlt_solve_n(const double* Ain, const double* rhs, double* x, int n)
+{
+	std::vector<double> A(Ain, Ain + (size_t)n * n), y(rhs, rhs + n);
+	std::vector<int> transp(n);
+	for (int k = 0; k < n; k++)
+	{
+		int p = k; double best = std::fabs(A[k * n + k]);
+		for (int i = k + 1; i < n; i++) { double v = std::fabs(A[i * n + i]); if (v > best) { best = v; p = i; } }
+		transp[k] = p;
+		if (p != k)
+		{
+			for (int j = 0; j < n; j++) std::swap(A[k * n + j], A[p * n + j]);
+			for (int i = 0; i < n; i++) std::swap(A[i * n + k], A[i * n + p]);
+		}
+		for (int j = 0; j < k; j++) A[k * n + k] -= A[k * n + j] * A[k * n + j] * A[j * n + j];
+		const double d = A[k * n + k];
+		for (int i = k + 1; i < n; i++)
+		{
+			double s = A[i * n + k];
+			for (int j = 0; j < k; j++) s -= A[i * n + j] * A[k * n + j] * A[j * n + j];
+			s = (std::fabs(d) > 0) ? s / d : 0.0;
+			A[i * n + k] = s; A[k * n + i] = s;
+		}
+	}
+	for (int k = 0; k < n; k++) std::swap(y[k], y[transp[k]]);
+	for (int i = 0; i < n; i++) for (int j = 0; j < i; j++) y[i] -= A[i * n + j] * y[j];
+	for (int i = 0; i < n; i++)
+	{
+		const double d = A[i * n + i];
+		y[i] = (std::fabs(d) > 2.2250738585072014e-308) ? y[i] / d : 0.0;
+	}
+	for (int i = n - 1; i >= 0; i--) for (int j = i + 1; j < n; j++) y[i] -= A[j * n + i] * y[j];
+	for (int k = n - 1; k >= 0; k--) std::swap(y[k], y[transp[k]]);
+	for (int i = 0; i < n; i++) x[i] = y[i];
+}
+
+// Thin SVD of an m x k matrix (k <= m) by one-sided Jacobi rotations (Hestenes): N = U diag(S) V^T.
+// Stands in for Eigen::JacobiSVD in EnergyFunctional::orthogonalize (:767); the projector built from it does not
+// depend on the SVD algorithm beyond rounding.  N, U: m x k row-major; V: k x k row-major.
+static inline void jacobi_svd_thin(const double* N, int m, int k, double* U, double* S, double* V)
+{
+	std::vector<double> A(N, N + (size_t)m * k);
+	for (int i = 0; i < k; i++) for (int j = 0; j < k; j++) V[i * k + j] = (i == j) ? 1.0 : 0.0;
+	for (int sweep = 0; sweep < 60; sweep++)
+	{
+		double off = 0;
+		for (int p = 0; p < k - 1; p++)
+			for (int q = p + 1; q < k; q++)
+			{
+				double alpha = 0, beta = 0, gamma = 0;
+				for (int i = 0; i < m; i++) { alpha += A[i * k + p] * A[i * k + p]; beta += A[i * k + q] * A[i * k + q]; gamma += A[i * k + p] * A[i * k + q]; }
+				if (gamma == 0 || std::fabs(gamma) <= 1e-300) continue;
+				off = std::max(off, std::fabs(gamma) / std::sqrt(alpha * beta));
+				if (std::fabs(gamma) <= 1e-17 * std::sqrt(alpha * beta)) continue;
+				const double zeta = (beta - alpha) / (2.0 * gamma);
+				const double t = (zeta >= 0 ? 1.0 : -1.0) / (std::fabs(zeta) + std::sqrt(1.0 + zeta * zeta));
+				const double c = 1.0 / std::sqrt(1.0 + t * t), s = c * t;
+				for (int i = 0; i < m; i++)
+				{
+					const double ap = A[i * k + p], aq = A[i * k + q];
+					A[i * k + p] = c * ap - s * aq; A[i * k + q] = s * ap + c * aq;
+				}
+				for (int i = 0; i < k; i++)
+				{
+					const double vp = V[i * k + p], vq = V[i * k + q];
+					V[i * k + p] = c * vp - s * vq; V[i * k + q] = s * vp + c * vq;
+				}
+			}
+		if (off < 1e-15) break;
+	}
+	for (int j = 0; j < k; j++)
+	{
+		double n2 = 0;
+		for (int i = 0; i < m; i++) n2 += A[i * k + j] * A[i * k + j];
+		S[j] = std::sqrt(n2);
+		for (int i = 0; i < m; i++) U[i * k + j] = S[j] > 0 ? A[i * k + j] / S[j] : 0.0;
+	}
 }
 
 } // namespace orc

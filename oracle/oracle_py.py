@@ -102,6 +102,11 @@ def lib(kind="oracle"):
     sig("dso_oracle_ba_apply_res", [vp, vp, vp])
     sig("dso_oracle_ba_accumulate_A", [vp, C.c_int, C.c_int, f64p, f64p, C.POINTER(C.c_int), f32p, f32p, f32p])
     sig("dso_oracle_ba_accumulate_SC", [vp, C.c_int, C.c_int, f64p, f64p, f32p, f32p, f32p])
+    sig("dso_oracle_ba_accumulate_L", [vp, C.c_int, C.c_int, f64p, f64p, C.POINTER(C.c_int), f32p, f32p, f32p])
+    sig("dso_oracle_ba_set_priors", [vp, vp, vp, vp, vp, vp, vp])
+    sig("dso_oracle_ba_set_nullspaces", [vp, f64p, C.c_int])
+    sig("dso_oracle_ba_fix_linearization", [vp, vp, vp])
+    sig("dso_oracle_ba_solve", [vp, C.c_int, C.c_double, C.c_int, C.c_double, C.c_int, C.c_int, vp, vp, vp, vp], C.c_int)
     _LIBS[kind] = L
     return L
 
@@ -284,3 +289,41 @@ class BA:
         ih = np.zeros(self.nP, dtype=np.float32)
         self.L.dso_oracle_ba_accumulate_SC(self.p, int(MT), nthreads, H, b, HdiF, bdSumF, ih)
         return dict(H=H.reshape(N, N), b=b, HdiF=HdiF, bdSumF=bdSumF, idepth_hessian=ih)
+
+    def accumulate_L(self, MT=False, nthreads=6):
+        N = 8 * self.nF + 4
+        H = np.zeros(N * N)
+        b = np.zeros(N)
+        n = C.c_int(0)
+        Hdd = np.zeros(self.nP, dtype=np.float32)
+        bd = np.zeros(self.nP, dtype=np.float32)
+        Hcd = np.zeros(self.nP * 4, dtype=np.float32)
+        self.L.dso_oracle_ba_accumulate_L(self.p, int(MT), nthreads, H, b, C.byref(n), Hdd, bd, Hcd)
+        return dict(H=H.reshape(N, N), b=b, resInL=n.value, Hdd=Hdd, bd=bd, Hcd=Hcd.reshape(self.nP, 4))
+
+    def set_priors(self, cPrior, framePrior, frameDeltaPrior, frameDelta, HM, bM):
+        self._pri = [None if x is None else np.ascontiguousarray(x, dtype=np.float64) for x in
+                     (cPrior, framePrior, frameDeltaPrior, frameDelta, HM, bM)]
+        self.L.dso_oracle_ba_set_priors(self.p, *[None if x is None else x.ctypes.data for x in self._pri])
+
+    def set_nullspaces(self, ns):
+        ns = np.ascontiguousarray(ns, dtype=np.float64).reshape(-1, 8 * self.nF + 4)
+        self.L.dso_oracle_ba_set_nullspaces(self.p, ns.reshape(-1), ns.shape[0])
+
+    def fix_linearization(self, which=None):
+        out = np.zeros(self.nR * 8, dtype=np.float32)
+        w = None if which is None else np.ascontiguousarray(which, dtype=np.uint8)
+        self.L.dso_oracle_ba_fix_linearization(self.p, None if w is None else w.ctypes.data, out.ctypes.data)
+        return out.reshape(self.nR, 8)
+
+    def solve(self, iteration, lam, solver_mode=128 | 2048, delta=1e-5, MT=False, nthreads=6):
+        N = 8 * self.nF + 4
+        x = np.zeros(N)
+        step = np.zeros(self.nP, dtype=np.float32)
+        HF = np.zeros(N * N)
+        bF = np.zeros(N)
+        rc = self.L.dso_oracle_ba_solve(self.p, iteration, lam, solver_mode, delta, int(MT), nthreads, x.ctypes.data,
+                                        step.ctypes.data, HF.ctypes.data, bF.ctypes.data)
+        if rc != 0:
+            raise RuntimeError("solver mode not restated")
+        return dict(x=x, step=step, HFinal=HF.reshape(N, N), bFinal=bF)

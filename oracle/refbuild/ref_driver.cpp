@@ -438,3 +438,74 @@ extern "C" void dso_ref_ba_accumulate_SC(dso_oracle_ba* B, int MT, int nthreads,
 		if (idepth_hessian) idepth_hessian[i] = B->pts[i]->idepth_hessian;
 	}
 }
+
+// ---- N1/N2: accumulateLF_MT, fixLinearizationF, solveSystemF + resubstituteF_MT (the reference's own code) ----
+extern "C" void dso_ref_ba_accumulate_L(dso_oracle_ba* B, int MT, int nthreads, double* H, double* b, int* resInL, float* Hdd, float* bd, float* Hcd4)
+{
+	(void)nthreads;
+	B->calib();
+	MatXX HL; VecX bL;
+	B->ef->accumulateLF_MT(HL, bL, MT != 0);                   // EnergyFunctional.cpp:233
+	export_sys(HL, bL, H, b);
+	if (resInL) *resInL = B->ef->resInL;
+	for (size_t i = 0; i < B->pts.size(); i++)
+	{
+		EFPoint* p = B->pts[i]->efPoint;
+		if (Hdd) Hdd[i] = p->Hdd_accLF;
+		if (bd) bd[i] = p->bd_accLF;
+		if (Hcd4) for (int k = 0; k < 4; k++) Hcd4[4 * i + k] = p->Hcd_accLF[k];
+	}
+}
+extern "C" void dso_ref_ba_set_priors(dso_oracle_ba* B, const double* cPrior4, const double* framePrior, const double* frameDeltaPrior,
+                                      const double* frameDelta, const double* HM, const double* bM)
+{
+	const int nF = B->nF, N = 8 * nF + CPARS;
+	EnergyFunctional* ef = B->ef;
+	for (int i = 0; i < 4; i++) ef->cPrior[i] = cPrior4 ? cPrior4[i] : 0.0;
+	ef->cPriorF = ef->cPrior.cast<float>();
+	for (int h = 0; h < nF; h++)
+		for (int i = 0; i < 8; i++)
+		{
+			ef->frames[h]->prior[i] = framePrior ? framePrior[8 * h + i] : 0.0;
+			ef->frames[h]->delta_prior[i] = frameDeltaPrior ? frameDeltaPrior[8 * h + i] : 0.0;
+			ef->frames[h]->delta[i] = frameDelta ? frameDelta[8 * h + i] : 0.0;
+		}
+	ef->HM = MatXX::Zero(N, N); ef->bM = VecX::Zero(N);
+	if (HM) for (int r = 0; r < N; r++) for (int c = 0; c < N; c++) ef->HM(r, c) = HM[r * N + c];
+	if (bM) for (int r = 0; r < N; r++) ef->bM[r] = bM[r];
+}
+extern "C" void dso_ref_ba_set_nullspaces(dso_oracle_ba* B, const double* ns, int n)
+{
+	const int N = 8 * B->nF + CPARS;
+	B->ef->lastNullspaces_pose.clear(); B->ef->lastNullspaces_scale.clear();
+	for (int k = 0; k < n; k++)
+	{
+		VecX v(N);
+		for (int i = 0; i < N; i++) v[i] = ns[(size_t)k * N + i];
+		B->ef->lastNullspaces_pose.push_back(v);               // orthogonalize concatenates pose and scale vectors (:745-747)
+	}
+}
+extern "C" void dso_ref_ba_fix_linearization(dso_oracle_ba* B, const unsigned char* which, float* res_toZeroF_out)
+{
+	for (size_t i = 0; i < B->res.size(); i++)
+	{
+		EFResidual* r = B->res[i]->efResidual;
+		if (r->isActive() && (!which || which[i])) r->fixLinearizationF(B->ef);    // EnergyFunctionalStructs.cpp:89
+		if (res_toZeroF_out) for (int k = 0; k < 8; k++) res_toZeroF_out[8 * i + k] = r->res_toZeroF[k];
+	}
+}
+extern "C" int dso_ref_ba_solve(dso_oracle_ba* B, int iteration, double lambda, int solverMode, double solverModeDelta, int MT, int nthreads,
+                                double* x_out, float* pointStep_out, double* HFinal_out, double* bFinal_out)
+{
+	(void)nthreads; (void)HFinal_out; (void)bFinal_out;
+	B->calib();
+	const int N = 8 * B->nF + CPARS;
+	if ((int)B->ef->bM.size() != N) dso_ref_ba_set_priors(B, 0, 0, 0, 0, 0, 0);
+	const bool mtOld = multiThreading; const int smOld = setting_solverMode; const double sdOld = setting_solverModeDelta;
+	multiThreading = MT != 0; setting_solverMode = solverMode; setting_solverModeDelta = solverModeDelta;
+	B->ef->solveSystemF(iteration, lambda, B->HCalib);         // EnergyFunctional.cpp:802
+	multiThreading = mtOld; setting_solverMode = smOld; setting_solverModeDelta = sdOld;
+	if (x_out) for (int i = 0; i < N; i++) x_out[i] = B->ef->lastX[i];
+	if (pointStep_out) for (size_t i = 0; i < B->pts.size(); i++) pointStep_out[i] = B->pts[i]->step;
+	return 0;
+}

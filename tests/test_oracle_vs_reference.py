@@ -105,7 +105,7 @@ def test_ba_linearize_accumulate(pkg, window_small):
     pyr = [O.make_images(img, 1)[0][0] for img in W.images]
     Bo, Br = O.BA(W, pyr), O.BA(W, pyr, kind="ref")
     go, gr = Bo.glue(), Br.glue()
-    for key in ("precalc", "adHost", "adTarget", "cDeltaF"):
+    for key in ("precalc", "adHost", "adTarget", "adHTdeltaF", "cDeltaF"):
         assert np.array_equal(bits(go[key]), bits(gr[key])), key          # FrameFramePrecalc::set, setAdjointsF
     lo, lr = Bo.linearize(), Br.linearize()
     assert np.array_equal(lo["newState"], lr["newState"])
@@ -170,3 +170,54 @@ def test_fixed_affine_modes_agree(trackers, pkg, window_small, modes):
     finally:
         O.set_affine_modes()
         O.set_affine_modes(kind="ref")
+
+
+def _solve_inputs(W, seed=0):
+    """priors as FrameHessian::getPrior gives them for frameID 0 (HessianBlocks.h:285-313), a synthetic marginalisation
+    prior HM/bM, frame deltas and seven null-space vectors"""
+    rng = np.random.default_rng(seed)
+    nF, N = W.nF, 8 * W.nF + 4
+    cP = np.full(4, 5e9)
+    fP = np.zeros((nF, 8))
+    fP[0] = [1e10] * 3 + [1e11] * 3 + [1e14, 1e14]
+    dP = rng.normal(0, 1e-4, (nF, 8))
+    dl = rng.normal(0, 1e-3, (nF, 8))
+    A = rng.normal(0, 30.0, (N, 12))
+    HM = A @ A.T
+    HM[:4, :] *= 10
+    HM[:, :4] *= 10
+    bM = rng.normal(0, 50.0, N)
+    ns = rng.normal(0, 1.0, (7, N))
+    return cP, fP.reshape(-1), dP.reshape(-1), dl.reshape(-1), HM, bM, ns
+
+
+@pytest.mark.parametrize("iteration,with_lin", [(0, False), (3, False), (3, True)])
+def test_solve_system_and_resubstitute(pkg, window_small, iteration, with_lin):
+    """EnergyFunctional::solveSystemF + resubstituteF_MT (EnergyFunctional.cpp:802-924, 276-330), default solver mode;
+    with_lin also runs fixLinearizationF on a third of the residuals so that accumulateLF_MT (addPoint<1>) has work"""
+    W = window_small
+    pyr = [O.make_images(img, 1)[0][0] for img in W.images]
+    Bo, Br = O.BA(W, pyr), O.BA(W, pyr, kind="ref")
+    inp = _solve_inputs(W)
+    outs = []
+    for B in (Bo, Br):
+        B.linearize()
+        act, _ = B.apply_res()
+        if with_lin:
+            which = (np.arange(W.nR) % 3 == 0).astype(np.uint8)
+            outs.append(B.fix_linearization(which)[(which == 1) & (act == 1)])      # the rest is uninitialised in the reference
+        B.set_priors(*inp[:6])
+        B.set_nullspaces(inp[6])
+    if with_lin:
+        assert np.array_equal(bits(outs[0]), bits(outs[1])) and np.abs(outs[0]).max() > 0
+        Lo, Lr = Bo.accumulate_L(False), Br.accumulate_L(False)
+        assert Lo["resInL"] == Lr["resInL"] > 0
+        for key in ("Hdd", "bd", "Hcd"):
+            assert np.array_equal(bits(Lo[key]), bits(Lr[key])), key
+        assert np.abs(Lo["H"] - Lr["H"]).max() <= 1e-12 * np.abs(Lr["H"]).max()
+        assert np.abs(Lo["b"] - Lr["b"]).max() <= 1e-12 * np.abs(Lr["b"]).max()
+    so, sr = Bo.solve(iteration, 1e-1), Br.solve(iteration, 1e-1)
+    assert np.abs(so["x"]).max() > 0
+    assert np.abs(so["x"] - sr["x"]).max() <= 1e-9 * np.abs(sr["x"]).max()
+    assert np.abs(so["step"] - sr["step"]).max() <= 1e-5 * np.abs(sr["step"]).max()
+    assert np.isfinite(so["step"]).all() and np.abs(so["step"]).max() > 0
