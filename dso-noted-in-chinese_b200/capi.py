@@ -75,6 +75,16 @@ SIGNATURES = {
     "dso_b200_track_hostloop": (C.c_int, [vp, C.c_int, C.c_int, f64p, C.c_double, C.c_double, C.c_float, C.c_int, vp,
                                           C.POINTER(TrackOpts), C.POINTER(TrackResult)]),
     "dso_b200_ba_set_affine_modes": (C.c_int, [vp, C.c_float, C.c_float]),
+    "dso_b200_ba_set_calib_delta": (C.c_int, [vp, f64p]),
+    "dso_b200_ba_set_priors": (C.c_int, [vp, vp, vp, vp, vp, vp, vp]),
+    "dso_b200_ba_set_nullspaces": (C.c_int, [vp, vp, C.c_int, C.c_double]),
+    "dso_b200_ba_fix_linearization": (C.c_int, [vp, vp, vp]),
+    "dso_b200_ba_accumulate_L": (C.c_int, [vp, f64p, f64p, C.POINTER(C.c_int), vp, vp, vp]),
+    "dso_b200_ba_solve": (C.c_int, [vp, C.c_int, C.c_double, C.c_int, vp, vp, vp, vp]),
+    "dso_b200_ba_points_backup": (C.c_int, [vp]),
+    "dso_b200_ba_points_step": (C.c_int, [vp, C.c_float, vp, vp]),
+    "dso_b200_ba_points_restore": (C.c_int, [vp]),
+    "dso_b200_ba_iteration": (C.c_int, [vp, C.c_int, C.c_double, C.c_int, C.c_float, vp, vp, vp]),
     "dso_b200_ba_set_window": (C.c_int, [vp, C.c_int, i32p, C.c_int, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float, f32p]),
     "dso_b200_ba_set_glue": (C.c_int, [vp, vp, f64p, f64p, f32p, f32p]),
     "dso_b200_ba_set_frames": (C.c_int, [vp, f64p, f64p, f64p, f32p, vp, vp, vp]),
@@ -371,6 +381,69 @@ class Context:
         ih = np.zeros(self.nP, dtype=np.float32)
         self._check(self.L.dso_b200_ba_accumulate_SC(self.h, H, b, HdiF.ctypes.data, bdSumF.ctypes.data, ih.ctypes.data))
         return dict(H=H.reshape(N, N), b=b, HdiF=HdiF, bdSumF=bdSumF, idepth_hessian=ih)
+
+    # ---- next rows: solveSystemF tail, resubstituteF_MT, linearised residuals ----
+    def ba_set_calib_delta(self, d4):
+        self._check(self.L.dso_b200_ba_set_calib_delta(self.h, np.ascontiguousarray(d4, dtype=np.float64)))
+
+    def ba_set_priors(self, cPrior=None, framePrior=None, frameDeltaPrior=None, frameDelta=None, HM=None, bM=None):
+        arrs = [None if x is None else np.ascontiguousarray(x, dtype=np.float64) for x in
+                (cPrior, framePrior, frameDeltaPrior, frameDelta, HM, bM)]
+        self._check(self.L.dso_b200_ba_set_priors(self.h, *[None if x is None else x.ctypes.data for x in arrs]))
+
+    def ba_set_nullspaces(self, ns, delta=1e-5):
+        N = 8 * self.nF + 4
+        ns = np.ascontiguousarray(ns, dtype=np.float64).reshape(-1, N)
+        self._check(self.L.dso_b200_ba_set_nullspaces(self.h, ns.ctypes.data, ns.shape[0], delta))
+
+    def ba_fix_linearization(self, which=None):
+        out = np.zeros(self.nR * 8, dtype=np.float32)
+        w = None if which is None else np.ascontiguousarray(which, dtype=np.uint8)
+        self._check(self.L.dso_b200_ba_fix_linearization(self.h, None if w is None else w.ctypes.data, out.ctypes.data))
+        return out.reshape(self.nR, 8)
+
+    def ba_accumulate_L(self):
+        N = 8 * self.nF + 4
+        H, b = np.zeros(N * N), np.zeros(N)
+        n = C.c_int(0)
+        Hdd = np.zeros(self.nP, dtype=np.float32)
+        bd = np.zeros(self.nP, dtype=np.float32)
+        Hcd = np.zeros(self.nP * 4, dtype=np.float32)
+        self._check(self.L.dso_b200_ba_accumulate_L(self.h, H, b, C.byref(n), Hdd.ctypes.data, bd.ctypes.data, Hcd.ctypes.data))
+        return dict(H=H.reshape(N, N), b=b, resInL=n.value, Hdd=Hdd, bd=bd, Hcd=Hcd.reshape(self.nP, 4))
+
+    def ba_solve(self, iteration, lam, solver_mode=128 | 2048, debug=False):
+        N = 8 * self.nF + 4
+        x = np.zeros(N)
+        step = np.zeros(self.nP, dtype=np.float32)
+        HF = np.zeros(N * N) if debug else None
+        bF = np.zeros(N) if debug else None
+        self._check(self.L.dso_b200_ba_solve(self.h, iteration, lam, solver_mode, x.ctypes.data, step.ctypes.data,
+                                             None if HF is None else HF.ctypes.data, None if bF is None else bF.ctypes.data))
+        out = dict(x=x, step=step)
+        if debug:
+            out.update(HFinal=HF.reshape(N, N), bFinal=bF)
+        return out
+
+    def ba_points_backup(self):
+        self._check(self.L.dso_b200_ba_points_backup(self.h))
+
+    def ba_points_step(self, stepfacD=1.0, want_idepth=True):
+        sums = np.zeros(2, dtype=np.float32)
+        idp = np.zeros(self.nP, dtype=np.float32) if want_idepth else None
+        self._check(self.L.dso_b200_ba_points_step(self.h, stepfacD, sums.ctypes.data, None if idp is None else idp.ctypes.data))
+        return sums, idp
+
+    def ba_points_restore(self):
+        self._check(self.L.dso_b200_ba_points_restore(self.h))
+
+    def ba_iteration(self, iteration, lam, solver_mode=128 | 2048, stepfacD=1.0):
+        N = 8 * self.nF + 4
+        x = np.zeros(N)
+        e = C.c_double(0)
+        sums = np.zeros(2, dtype=np.float32)
+        self._check(self.L.dso_b200_ba_iteration(self.h, iteration, lam, solver_mode, stepfacD, x.ctypes.data, C.byref(e), sums.ctypes.data))
+        return dict(x=x, energy=e.value, step_sums=sums)
 
     def ba_step(self):
         N = 8 * self.nF + 4

@@ -23,74 +23,9 @@
 #include "lm_math.cuh"
 #include <algorithm>
 
-#define CPARS 4
-#define CHUNK_R 64
-#define CHUNK_P 16
-#define NTOP 91           // 55 + 30 + 6 unique entries of the 13x13 block
-#define NTOP_PAD 96
-#define JSZ 74
-#define ST_IN 0
-#define ST_OOB 1
-#define ST_OUTLIER 2
-#define SCALE_IDEPTH 1.0f
-#define SCALE_F 50.0f
-#define SCALE_C 50.0f
-#define OUTLIER_TH_SUM 2500.0f     // setting_outlierTHSumComponent = 50*50
-#define HUBER_TH 9.0f              // setting_huberTH
-
-// offsets into the flattened RawResidualJacobian (RawResidualJacobian.h:40-79)
-#define J_RESF 0
-#define J_PDXI0 8
-#define J_PDXI1 14
-#define J_PDC0 20
-#define J_PDC1 24
-#define J_PDD 28
-#define J_IDX0 30
-#define J_IDX1 38
-#define J_AB0 46
-#define J_AB1 54
-#define J_IDX2 62
-#define J_ABIDX 66
-#define J_AB2 70
+#include "ba_internal.cuh"
 
 __constant__ int c_pattern[8][2] = { {0,-2}, {-1,-1}, {1,-1}, {-2,0}, {0,0}, {2,0}, {-1,1}, {0,2} };   // settings.cpp:274
-
-struct BAParams
-{
-	int nF, w, h, nR, nP;
-	float fx, fy, cx, cy, fxi, fyi, wM3G, hM3G;
-	float frameEnergyTH[MAXF];
-	const float4* img[MAXF];
-	int fixA, fixB;            // setting_affineOptModeA/B < 0 (Residuals.cpp:257-258)
-};
-
-struct BAWorkspace
-{
-	BAParams P;
-	bool window_set, glue_set, points_set, res_set, lin_done, top_done;
-	float* d_precalc; double* d_adHost; double* d_adTarget;
-	// points
-	int capP;
-	float4* d_pt; float* d_color; float* d_weights; int* d_phost; float* d_priorF; float* d_deltaF; int* d_res_begin;
-	float* d_Hdd; float* d_bd; float* d_Hcd; float* d_HdiF; float* d_bdSumF; float* d_idh;
-	// residuals
-	int capR;
-	int* d_rpoint; int* d_rtarget; int* d_state; int* d_newState; double* d_energy; float* d_newEnergy; float* d_newEnergyWO;
-	unsigned char* d_isLin; unsigned char* d_isAct; unsigned char* d_efsel;
-	float* d_cpt; float* d_proj; float* d_J[2]; float* d_JpJdF; float* d_contrib; double* d_resEnergy;
-	int* d_perm;
-	// chunks (top): residuals sorted by pair; (schur): points by host
-	int nChunks, capChunks; int* d_chunk_start; int* d_chunk_cnt; int* d_pair_chunk_begin;   // [nF*nF+1]
-	float* d_topPartials; int* d_chunk_nres;
-	int nPC, capPC; int* d_pc_start; int* d_pc_cnt; int* d_pc_host; int* d_host_pc_begin;     // [nF+1]
-	float* d_scPartials; int scN;
-	double* d_scContrib;       // stage-1 contributions
-	double* d_scRed; double* d_topRed; double* d_topContrib;
-	// outputs
-	double* d_HA; double* d_bA; double* d_HS; double* d_bS; double* d_energy_blocks; double* d_scalars;   // [0] energy sum, [1] resInA
-	double* h_out;             // pinned: HA, bA, HS, bS, scalars
-	std::vector<int> h_rpoint, h_res_begin, h_phost;
-};
 
 
 int ba_create(dso_b200_ctx* ctx)
@@ -118,6 +53,20 @@ int ba_create(dso_b200_ctx* ctx)
 	CK(cudaMalloc(&W->d_topContrib, (size_t)MAXF * MAXF * 292 * sizeof(double)));
 	CK(cudaHostAlloc((void**)&W->h_out, (2 * (size_t)N * N + 2 * N + 8) * sizeof(double), cudaHostAllocDefault));
 	W->d_energy_blocks = nullptr;
+	CK(cudaMalloc(&W->d_adHTdeltaF, MAXF * MAXF * 8 * sizeof(float)));
+	CK(cudaMalloc(&W->d_cDeltaF, 4 * sizeof(float)));
+	CK(cudaMemset(W->d_adHTdeltaF, 0, MAXF * MAXF * 8 * sizeof(float)));
+	CK(cudaMemset(W->d_cDeltaF, 0, 4 * sizeof(float)));
+	for (int i = 0; i < 4; i++) W->h_cDeltaF[i] = 0.f;
+	CK(cudaMalloc(&W->d_HL, (size_t)N * N * sizeof(double)));
+	CK(cudaMalloc(&W->d_bL, N * sizeof(double)));
+	CK(cudaMalloc(&W->d_priorH, N * sizeof(double)));
+	CK(cudaMalloc(&W->d_priorD, N * sizeof(double)));
+	CK(cudaMalloc(&W->d_delta, N * sizeof(double)));
+	CK(cudaMemset(W->d_priorH, 0, N * sizeof(double)));
+	CK(cudaMemset(W->d_priorD, 0, N * sizeof(double)));
+	CK(cudaMemset(W->d_delta, 0, N * sizeof(double)));
+	W->nLin = 0; W->S = nullptr;
 	ctx->ba = W;
 	return 0;
 }
@@ -127,6 +76,7 @@ static void free_points(BAWorkspace* W)
 	if (!W->capP) return;
 	cudaFree(W->d_pt); cudaFree(W->d_color); cudaFree(W->d_weights); cudaFree(W->d_phost); cudaFree(W->d_priorF); cudaFree(W->d_deltaF);
 	cudaFree(W->d_res_begin); cudaFree(W->d_Hdd); cudaFree(W->d_bd); cudaFree(W->d_Hcd); cudaFree(W->d_HdiF); cudaFree(W->d_bdSumF); cudaFree(W->d_idh);
+	cudaFree(W->d_Hdd_L); cudaFree(W->d_bd_L); cudaFree(W->d_Hcd_L); cudaFree(W->d_HcdSum);
 	if (W->capPC) { cudaFree(W->d_pc_start); cudaFree(W->d_pc_cnt); cudaFree(W->d_pc_host); cudaFree(W->d_scPartials); }
 	W->capP = 0; W->capPC = 0;
 }
@@ -136,7 +86,7 @@ static void free_res(BAWorkspace* W)
 	cudaFree(W->d_rpoint); cudaFree(W->d_rtarget); cudaFree(W->d_state); cudaFree(W->d_newState); cudaFree(W->d_energy); cudaFree(W->d_newEnergy);
 	cudaFree(W->d_newEnergyWO); cudaFree(W->d_isLin); cudaFree(W->d_isAct); cudaFree(W->d_efsel); cudaFree(W->d_cpt); cudaFree(W->d_proj);
 	cudaFree(W->d_J[0]); cudaFree(W->d_J[1]); cudaFree(W->d_JpJdF); cudaFree(W->d_contrib); cudaFree(W->d_resEnergy); cudaFree(W->d_perm);
-	cudaFree(W->d_energy_blocks);
+	cudaFree(W->d_energy_blocks); cudaFree(W->d_resToZero);
 	if (W->capChunks) { cudaFree(W->d_chunk_start); cudaFree(W->d_chunk_cnt); cudaFree(W->d_topPartials); cudaFree(W->d_chunk_nres); }
 	W->capR = 0; W->capChunks = 0;
 }
@@ -145,7 +95,9 @@ void ba_destroy(dso_b200_ctx* ctx)
 {
 	BAWorkspace* W = ctx->ba;
 	if (!W) return;
+	ba_solve_destroy(W);
 	free_points(W); free_res(W);
+	cudaFree(W->d_adHTdeltaF); cudaFree(W->d_cDeltaF); cudaFree(W->d_HL); cudaFree(W->d_bL); cudaFree(W->d_priorH); cudaFree(W->d_priorD); cudaFree(W->d_delta);
 	cudaFree(W->d_precalc); cudaFree(W->d_adHost); cudaFree(W->d_adTarget); cudaFree(W->d_pair_chunk_begin); cudaFree(W->d_host_pc_begin);
 	cudaFree(W->d_HA); cudaFree(W->d_bA); cudaFree(W->d_HS); cudaFree(W->d_bS); cudaFree(W->d_scalars); cudaFree(W->d_scContrib); cudaFree(W->d_scRed); cudaFree(W->d_topRed); cudaFree(W->d_topContrib);
 	cudaFreeHost(W->h_out);
@@ -368,12 +320,32 @@ __global__ void ba_energy_final_kernel(int nb, const double* __restrict__ blocks
 	if (threadIdx.x == 0 && blockIdx.x == 0) { double s = 0; for (int i = 0; i < nb; i++) s += blocks[i]; out[0] = s; }
 }
 
-// AccumulatedTopHessianSSE::addPoint<0>, AccumulatedTopHessian.cpp:39-160, one chunk of one (host,target) pair
+// Jp*delta of EFResidual::fixLinearizationF / addPoint<1> (EnergyFunctionalStructs.cpp:92-100, AccumulatedTopHessian.cpp:82-87):
+// d[0..1] = Jpdxi[k].dot(dp.head<6>()) + Jpdc[k].dot(dc) + Jpdd[k]*dd (fixed-size reductions in Eigen's unrolled order:
+// 6 terms (p0+(p1+p2))+(p3+(p4+p5)), 4 terms (p0+p1)+(p2+p3)), d[2..3] = dp[6], dp[7]
+__device__ __forceinline__ void ba_jp_delta(const float* __restrict__ J, const float* __restrict__ dp, const float* __restrict__ dc, float dd, float* d)
+{
+#pragma unroll
+	for (int k = 0; k < 2; k++)
+	{
+		const float* xi = J + (k ? J_PDXI1 : J_PDXI0);
+		const float* c = J + (k ? J_PDC1 : J_PDC0);
+		const float s6 = fadd(fadd(fmul(xi[0], dp[0]), fadd(fmul(xi[1], dp[1]), fmul(xi[2], dp[2]))),
+		                      fadd(fmul(xi[3], dp[3]), fadd(fmul(xi[4], dp[4]), fmul(xi[5], dp[5]))));
+		const float s4 = fadd(fadd(fmul(c[0], dc[0]), fmul(c[1], dc[1])), fadd(fmul(c[2], dc[2]), fmul(c[3], dc[3])));
+		d[k] = fadd(fadd(s6, s4), fmul(J[J_PDD + k], dd));
+	}
+	d[2] = dp[6]; d[3] = dp[7];
+}
+
+// AccumulatedTopHessianSSE::addPoint<MODE>, AccumulatedTopHessian.cpp:39-160, one chunk of one (host,target) pair.
+// MODE 0: active, not linearised, r = resF.  MODE 1: active and linearised, r = res_toZeroF + J*delta (:73-101).
+template <int MODE>
 __global__ void __launch_bounds__(128) ba_accum_top_kernel(const int* __restrict__ perm, const int* __restrict__ chunk_start,
                                                            const int* __restrict__ chunk_cnt, const unsigned char* __restrict__ isAct,
                                                            const unsigned char* __restrict__ isLin, const unsigned char* __restrict__ efsel,
                                                            const float* __restrict__ J0, const float* __restrict__ J1, float* contrib,
-                                                           float* partials, int* chunk_nres)
+                                                           float* partials, int* chunk_nres, BALinArgs LA)
 {
 	__shared__ float sx[CHUNK_R][10], sy[CHUNK_R][10], sw[CHUNK_R][16];   // sw: a,b,c | TR00,TR10,TR01,TR11,TR02,TR12 | BR0..5
 	__shared__ int s_n;
@@ -384,7 +356,7 @@ __global__ void __launch_bounds__(128) ba_accum_top_kernel(const int* __restrict
 	if (tid < cnt)
 	{
 		const int r = perm[start + tid];
-		const bool act = isAct[r] && !isLin[r];                             // :57
+		const bool act = isAct[r] && (MODE == 0 ? !isLin[r] : isLin[r] != 0);   // :55-62
 		float x[10], y[10], w[15];
 		if (act)
 		{
@@ -393,11 +365,34 @@ __global__ void __launch_bounds__(128) ba_accum_top_kernel(const int* __restrict
 			for (int k = 0; k < 4; k++) { x[k] = J[J_PDC0 + k]; y[k] = J[J_PDC1 + k]; }
 #pragma unroll
 			for (int k = 0; k < 6; k++) { x[4 + k] = J[J_PDXI0 + k]; y[4 + k] = J[J_PDXI1 + k]; }
+			float res[8];
+			if (MODE == 0)
+			{
+#pragma unroll
+				for (int i = 0; i < 8; i++) res[i] = J[J_RESF + i];
+			}
+			else
+			{
+				const int p = LA.rpoint[r];
+				float d[4];
+				ba_jp_delta(J, LA.adHTdeltaF + 8 * (LA.phost[p] + LA.nF * LA.rtarget[r]), LA.cDeltaF, LA.deltaF[p], d);
+				const float* tz = LA.resToZero + 8 * (size_t)r;
+#pragma unroll
+				for (int i = 0; i < 8; i++)
+				{
+					float rtz = tz[i];                                              // :93-99
+					rtz = fadd(rtz, fmul(J[J_IDX0 + i], d[0]));
+					rtz = fadd(rtz, fmul(J[J_IDX1 + i], d[1]));
+					rtz = fadd(rtz, fmul(J[J_AB0 + i], d[2]));
+					rtz = fadd(rtz, fmul(J[J_AB1 + i], d[3]));
+					res[i] = rtz;
+				}
+			}
 			float JI_r0 = 0.f, JI_r1 = 0.f, Jab_r0 = 0.f, Jab_r1 = 0.f, rr = 0.f;   // :107-118
 #pragma unroll
 			for (int i = 0; i < 8; i++)
 			{
-				const float ri = J[J_RESF + i];
+				const float ri = res[i];
 				JI_r0 = fadd(JI_r0, fmul(ri, J[J_IDX0 + i]));
 				JI_r1 = fadd(JI_r1, fmul(ri, J[J_IDX1 + i]));
 				Jab_r0 = fadd(Jab_r0, fmul(ri, J[J_AB0 + i]));
@@ -470,14 +465,14 @@ __global__ void __launch_bounds__(128) ba_accum_top_kernel(const int* __restrict
 // per-point sums in EFPoint::residualsAll order, AccumulatedTopHessian.cpp:142-160
 __global__ void ba_point_sums_kernel(int nP, const int* __restrict__ res_begin, const unsigned char* __restrict__ isAct,
                                      const unsigned char* __restrict__ isLin, const float* __restrict__ contrib,
-                                     float* Hdd, float* bd, float* Hcd)
+                                     float* Hdd, float* bd, float* Hcd, int mode)
 {
 	const int p = blockIdx.x * blockDim.x + threadIdx.x;
 	if (p >= nP) return;
 	float bd_acc = 0.f, Hdd_acc = 0.f, h0 = 0.f, h1 = 0.f, h2 = 0.f, h3 = 0.f;
 	for (int r = res_begin[p]; r < res_begin[p + 1]; r++)
 	{
-		if (!isAct[r] || isLin[r]) continue;
+		if (!isAct[r] || (mode == 0 ? isLin[r] != 0 : !isLin[r])) continue;
 		const float* c = contrib + 6 * (size_t)r;
 		bd_acc = fadd(bd_acc, c[0]); Hdd_acc = fadd(Hdd_acc, c[1]);
 		h0 = fadd(h0, c[2]); h1 = fadd(h1, c[3]); h2 = fadd(h2, c[4]); h3 = fadd(h3, c[5]);
@@ -574,7 +569,9 @@ __global__ void __launch_bounds__(256) ba_top_pair_kernel(int nF, const double* 
 
 // gather per output block in a fixed order, including "make diagonal by copying over parts" (AccumulatedTopHessian.h:126-138)
 __global__ void __launch_bounds__(64) ba_top_gather_kernel(int nF, int nChunks, const int* __restrict__ chunk_nres,
-                                                           const double* __restrict__ contrib, double* Hout, double* bout, double* scalars)
+                                                           const double* __restrict__ contrib, double* Hout, double* bout, double* scalars,
+                                                           const double* __restrict__ priorH, const double* __restrict__ priorD,
+                                                           const float* __restrict__ cDeltaF)
 {
 	const int N = 8 * nF + CPARS, o = threadIdx.x, i = o >> 3, j = o & 7;
 	if ((int)blockIdx.x < nF * nF)
@@ -588,6 +585,7 @@ __global__ void __launch_bounds__(64) ba_top_gather_kernel(int nF, int nChunks, 
 				v += contrib[(size_t)(r + nF * q) * TC_STRIDE + TC_HH + o];
 				v += contrib[(size_t)(q + nF * r) * TC_STRIDE + TC_TT + o];
 			}
+			if (priorH && i == j) v += priorH[CPARS + r * 8 + i];     // usePrior, AccumulatedTopHessian.cpp:314-324
 		}
 		else
 			v = contrib[(size_t)(r + nF * c) * TC_STRIDE + TC_HT + o] + contrib[(size_t)(c + nF * r) * TC_STRIDE + TC_HT + j * 8 + i];
@@ -616,12 +614,15 @@ __global__ void __launch_bounds__(64) ba_top_gather_kernel(int nF, int nChunks, 
 				v += contrib[(size_t)(r + nF * m) * TC_STRIDE + TC_BH + q];
 				v += contrib[(size_t)(m + nF * r) * TC_STRIDE + TC_BT + q];
 			}
+			if (priorH) v += __dmul_rn(priorH[CPARS + e], priorD[CPARS + e]);   // prior.cwiseProduct(delta_prior)
 			bout[CPARS + e] = v;
 		}
 		if (o < 20)
 		{
 			double v = 0.0;
 			for (int k = 0; k < nF * nF; k++) v += contrib[(size_t)k * TC_STRIDE + TC_CC + o];
+			if (priorH && o < 16 && (o >> 2) == (o & 3)) v += priorH[o >> 2];
+			if (priorH && o >= 16) v += __dmul_rn(priorH[o - 16], (double)cDeltaF[o - 16]);   // cPrior.cwiseProduct(cDeltaF.cast<double>())
 			if (o < 16) Hout[(o >> 2) * N + (o & 3)] = v; else bout[o - 16] = v;
 		}
 		if (o == 32) { int n = 0; for (int c = 0; c < nChunks; c++) n += chunk_nres[c]; scalars[1] = (double)n; }
@@ -630,19 +631,23 @@ __global__ void __launch_bounds__(64) ba_top_gather_kernel(int nF, int nChunks, 
 
 // AccumulatedSCHessianSSE::addPoint (AccumulatedSCHessian.cpp:35-60): per-point inverse Hessian and b
 __global__ void ba_schur_prep_kernel(int nP, const int* __restrict__ res_begin, const unsigned char* __restrict__ isAct,
-                                     const float* __restrict__ Hdd, const float* __restrict__ bd, const float* __restrict__ priorF,
-                                     const float* __restrict__ deltaF, float* HdiF, float* bdSumF, float* idh)
+                                     const float* __restrict__ Hdd, const float* __restrict__ bd, const float* __restrict__ Hcd,
+                                     const float* __restrict__ Hdd_L, const float* __restrict__ bd_L, const float* __restrict__ Hcd_L,
+                                     const float* __restrict__ priorF, const float* __restrict__ deltaF,
+                                     float* HdiF, float* bdSumF, float* idh, float* HcdSum)
 {
 	const int p = blockIdx.x * blockDim.x + threadIdx.x;
 	if (p >= nP) return;
+#pragma unroll
+	for (int k = 0; k < 4; k++) HcdSum[4 * p + k] = fadd(Hcd[4 * p + k], Hcd_L[4 * p + k]);   // Hcd_accAF + Hcd_accLF (:62)
 	int ngood = 0;
 	for (int r = res_begin[p]; r < res_begin[p + 1]; r++) ngood += isAct[r] ? 1 : 0;
 	if (ngood == 0) { HdiF[p] = 0.f; bdSumF[p] = 0.f; idh[p] = 0.f; return; }
-	float H = fadd(fadd(Hdd[p], 0.f), priorF[p]);        // Hdd_accAF + Hdd_accLF + priorF
+	float H = fadd(fadd(Hdd[p], Hdd_L[p]), priorF[p]);   // Hdd_accAF + Hdd_accLF + priorF
 	if (H < 1e-10) H = 1e-10;
 	idh[p] = H;
 	HdiF[p] = (float)(1.0 / (double)H);
-	float bs = fadd(bd[p], 0.f);
+	float bs = fadd(bd[p], bd_L[p]);
 	bs = fadd(bs, fmul(priorF[p], deltaF[p]));            // shiftPriorToZero = true (EnergyFunctional.cpp:263, 271)
 	bdSumF[p] = bs;
 }
@@ -833,7 +838,6 @@ __global__ void __launch_bounds__(64) ba_schur_gather_kernel(int nF, int nPC, co
 }
 
 // ---- host side --------------------------------------------------------------------------------------------
-#define BA_CHECK(cond, msg) do { if (!(cond)) { dso_set_error("%s: %s", __func__, msg); return DSO_B200_E_STATE; } } while (0)
 
 extern "C" int dso_b200_ba_set_window(dso_b200_ctx* ctx, int nF, const int* frame_slots, int w, int h,
                                       float fx, float fy, float cx, float cy, const float* frameEnergyTH)
@@ -870,7 +874,6 @@ extern "C" int dso_b200_ba_set_glue(dso_b200_ctx* ctx, const dso_b200_precalc* p
                                     const double* adTarget, const float* adHTdeltaF, const float* cDeltaF4)
 {
 	ARG_CHECK(ctx && ctx->ba && precalc && adHost && adTarget, "null argument");
-	(void)adHTdeltaF; (void)cDeltaF4;   // only read by the linearised-residual mode (addPoint<1>), not implemented (N2)
 	BAWorkspace* W = ctx->ba;
 	BA_CHECK(W->window_set, "call dso_b200_ba_set_window first");
 	CK(cudaSetDevice(ctx->device));
@@ -878,6 +881,11 @@ extern "C" int dso_b200_ba_set_glue(dso_b200_ctx* ctx, const dso_b200_precalc* p
 	CK(cudaMemcpyAsync(W->d_precalc, precalc, (size_t)n2 * sizeof(dso_b200_precalc), cudaMemcpyHostToDevice, ctx->stream));
 	CK(cudaMemcpyAsync(W->d_adHost, adHost, (size_t)n2 * 64 * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
 	CK(cudaMemcpyAsync(W->d_adTarget, adTarget, (size_t)n2 * 64 * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+	// setDeltaF products, read by the linearised-residual mode (addPoint<1>, fixLinearizationF); NULL = zero deltas
+	if (adHTdeltaF) CK(cudaMemcpyAsync(W->d_adHTdeltaF, adHTdeltaF, (size_t)n2 * 8 * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+	else CK(cudaMemsetAsync(W->d_adHTdeltaF, 0, (size_t)n2 * 8 * sizeof(float), ctx->stream));
+	if (cDeltaF4) memcpy(W->h_cDeltaF, cDeltaF4, 4 * sizeof(float));
+	CK(cudaMemcpyAsync(W->d_cDeltaF, W->h_cDeltaF, 4 * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
 	CK(cudaStreamSynchronize(ctx->stream));
 	W->glue_set = true;
 	return 0;
@@ -907,8 +915,14 @@ extern "C" int dso_b200_ba_set_points(dso_b200_ctx* ctx, int nP, const float* u,
 		CK(cudaMalloc(&W->d_res_begin, (n + 1) * sizeof(int)));
 		CK(cudaMalloc(&W->d_Hdd, n * sizeof(float))); CK(cudaMalloc(&W->d_bd, n * sizeof(float))); CK(cudaMalloc(&W->d_Hcd, n * 4 * sizeof(float)));
 		CK(cudaMalloc(&W->d_HdiF, n * sizeof(float))); CK(cudaMalloc(&W->d_bdSumF, n * sizeof(float))); CK(cudaMalloc(&W->d_idh, n * sizeof(float)));
+		CK(cudaMalloc(&W->d_Hdd_L, n * sizeof(float))); CK(cudaMalloc(&W->d_bd_L, n * sizeof(float))); CK(cudaMalloc(&W->d_Hcd_L, n * 4 * sizeof(float)));
+		CK(cudaMalloc(&W->d_HcdSum, n * 4 * sizeof(float)));
 		W->capP = nP;
 	}
+	// *_accLF start at zero: accumulateLF_MT overwrites them when there are linearised residuals
+	CK(cudaMemsetAsync(W->d_Hdd_L, 0, (size_t)nP * sizeof(float), ctx->stream));
+	CK(cudaMemsetAsync(W->d_bd_L, 0, (size_t)nP * sizeof(float), ctx->stream));
+	CK(cudaMemsetAsync(W->d_Hcd_L, 0, (size_t)nP * 4 * sizeof(float), ctx->stream));
 	std::vector<float4> pt(nP);
 	for (int i = 0; i < nP; i++) pt[i] = make_float4(u[i], v[i], idepth_scaled[i], idepth_zero_scaled[i]);
 	CK(cudaMemcpyAsync(W->d_pt, pt.data(), (size_t)nP * sizeof(float4), cudaMemcpyHostToDevice, ctx->stream));
@@ -970,7 +984,7 @@ extern "C" int dso_b200_ba_set_residuals(dso_b200_ctx* ctx, int nR, const int* p
 		ARG_CHECK(target[i] != W->h_phost[point[i]], "residual target equals its host");
 		if (isLinearized && isLinearized[i] && isActive && isActive[i])
 		{
-			dso_set_error("dso_b200_ba_set_residuals: active linearised residuals (addPoint<1>, fixLinearizationF) are not implemented (SURVEY N2)");
+			dso_set_error("dso_b200_ba_set_residuals: active linearised residuals cannot be imported (their res_toZeroF and Jacobians live on the device): linearise them with dso_b200_ba_fix_linearization");
 			return DSO_B200_E_STATE;
 		}
 		rb[point[i] + 1]++;
@@ -988,6 +1002,7 @@ extern "C" int dso_b200_ba_set_residuals(dso_b200_ctx* ctx, int nR, const int* p
 		CK(cudaMalloc(&W->d_JpJdF, n * 8 * sizeof(float))); CK(cudaMalloc(&W->d_contrib, n * 6 * sizeof(float))); CK(cudaMalloc(&W->d_resEnergy, n * sizeof(double)));
 		CK(cudaMalloc(&W->d_perm, n * sizeof(int)));
 		CK(cudaMalloc(&W->d_energy_blocks, ((n + 255) / 256) * sizeof(double)));
+		CK(cudaMalloc(&W->d_resToZero, n * 8 * sizeof(float)));
 		W->capR = nR;
 	}
 	// pair-sorted permutation (stable: keeps point order inside a pair, the reference's accumulation order)
@@ -1041,6 +1056,8 @@ extern "C" int dso_b200_ba_set_residuals(dso_b200_ctx* ctx, int nR, const int* p
 	CK(cudaMemcpyAsync(W->d_chunk_cnt, cc.data(), cc.size() * sizeof(int), cudaMemcpyHostToDevice, s));
 	CK(cudaMemcpyAsync(W->d_pair_chunk_begin, pcb.data(), pcb.size() * sizeof(int), cudaMemcpyHostToDevice, s));
 	CK(cudaMemsetAsync(W->d_efsel, 0, nR, s));
+	CK(cudaMemsetAsync(W->d_resToZero, 0, (size_t)nR * 8 * sizeof(float), s));
+	W->nLin = 0;
 	{ std::vector<int> ns(nR, ST_OUTLIER); CK(cudaMemcpyAsync(W->d_newState, ns.data(), (size_t)nR * sizeof(int), cudaMemcpyHostToDevice, s)); CK(cudaStreamSynchronize(s)); }   // resetOOB, Residuals.h:97-105
 	CK(cudaMemsetAsync(W->d_newEnergyWO, 0, (size_t)nR * sizeof(float), s));
 	CK(cudaMemsetAsync(W->d_cpt, 0, (size_t)nR * 3 * sizeof(float), s));
@@ -1162,10 +1179,45 @@ extern "C" int dso_b200_ba_set_frames(dso_b200_ctx* ctx, const double* evalPT12,
 	if (precalc_out) memcpy(precalc_out, pre.data(), pre.size() * sizeof(dso_b200_precalc));
 	if (adHost_out) memcpy(adHost_out, adH.data(), adH.size() * sizeof(double));
 	if (adTarget_out) memcpy(adTarget_out, adT.data(), adT.size() * sizeof(double));
-	return dso_b200_ba_set_glue(ctx, pre.data(), adH.data(), adT.data(), nullptr, nullptr);
+	// setDeltaF, EnergyFunctional.cpp:178-193: adHTdeltaF[h+t*nF] = delta_h^T adHostF + delta_t^T adTargetF in float, every
+	// coefficient an unrolled 8-term reduction ((p0+p1)+(p2+p3))+((p4+p5)+(p6+p7))
+	std::vector<float> adHTd((size_t)nF * nF * 8);
+	for (int h = 0; h < nF; h++)
+		for (int t = 0; t < nF; t++)
+		{
+			const int idx = h + t * nF;
+			for (int c = 0; c < 8; c++)
+			{
+				volatile float p0[8], p1[8];
+				for (int r = 0; r < 8; r++)
+				{
+					p0[r] = (float)(state10[10 * h + r] - state_zero10[10 * h + r]) * (float)adH[(size_t)idx * 64 + r * 8 + c];
+					p1[r] = (float)(state10[10 * t + r] - state_zero10[10 * t + r]) * (float)adT[(size_t)idx * 64 + r * 8 + c];
+				}
+				const float s0 = ((p0[0] + p0[1]) + (p0[2] + p0[3])) + ((p0[4] + p0[5]) + (p0[6] + p0[7]));
+				const float s1 = ((p1[0] + p1[1]) + (p1[2] + p1[3])) + ((p1[4] + p1[5]) + (p1[6] + p1[7]));
+				adHTd[(size_t)idx * 8 + c] = s0 + s1;
+			}
+		}
+	// EFFrame::takeData (EnergyFunctionalStructs.cpp:55-63): delta = state - state_zero, delta_prior = state - getPriorZero() (= 0)
+	{
+		double dl[8 * MAXF + CPARS], dp[8 * MAXF + CPARS];
+		for (int i = 0; i < CPARS; i++) dl[i] = dp[i] = 0.0;
+		for (int f = 0; f < nF; f++)
+			for (int i = 0; i < 8; i++)
+			{
+				dl[CPARS + 8 * f + i] = state10[10 * f + i] - state_zero10[10 * f + i];
+				dp[CPARS + 8 * f + i] = state10[10 * f + i];
+			}
+		CK(cudaSetDevice(ctx->device));
+		CK(cudaMemcpyAsync(W->d_delta, dl, (8 * nF + CPARS) * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+		CK(cudaMemcpyAsync(W->d_priorD, dp, (8 * nF + CPARS) * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+		CK(cudaStreamSynchronize(ctx->stream));
+	}
+	return dso_b200_ba_set_glue(ctx, pre.data(), adH.data(), adT.data(), adHTd.data(), nullptr);
 }
 
-static int enqueue_linearize(dso_b200_ctx* ctx)
+int ba_enqueue_linearize(dso_b200_ctx* ctx)
 {
 	BAWorkspace* W = ctx->ba;
 	const int nR = W->P.nR;
@@ -1181,7 +1233,7 @@ static int enqueue_linearize(dso_b200_ctx* ctx)
 	return 0;
 }
 
-static int enqueue_apply(dso_b200_ctx* ctx)
+int ba_enqueue_apply(dso_b200_ctx* ctx)
 {
 	BAWorkspace* W = ctx->ba;
 	const int nR = W->P.nR;
@@ -1193,31 +1245,43 @@ static int enqueue_apply(dso_b200_ctx* ctx)
 	return 0;
 }
 
-static int enqueue_top(dso_b200_ctx* ctx)
+// mode 0: accumulateAF_MT -> d_HA, d_bA, per-point AF sums; mode 1: accumulateLF_MT -> d_HL, d_bL (+ priors), per-point LF sums
+int ba_enqueue_top(dso_b200_ctx* ctx, int mode)
 {
 	BAWorkspace* W = ctx->ba;
 	const int nF = W->P.nF;
 	cudaStream_t st = ctx->stream;
-	ba_accum_top_kernel<<<W->nChunks, 128, 0, st>>>(W->d_perm, W->d_chunk_start, W->d_chunk_cnt, W->d_isAct, W->d_isLin, W->d_efsel,
-	                                              W->d_J[0], W->d_J[1], W->d_contrib, W->d_topPartials, W->d_chunk_nres);
-	ba_point_sums_kernel<<<(W->P.nP + 127) / 128, 128, 0, st>>>(W->P.nP, W->d_res_begin, W->d_isAct, W->d_isLin, W->d_contrib, W->d_Hdd, W->d_bd, W->d_Hcd);
+	BALinArgs LA;
+	LA.rpoint = W->d_rpoint; LA.rtarget = W->d_rtarget; LA.phost = W->d_phost; LA.deltaF = W->d_deltaF;
+	LA.adHTdeltaF = W->d_adHTdeltaF; LA.cDeltaF = W->d_cDeltaF; LA.resToZero = W->d_resToZero; LA.nF = nF;
+	float* Hdd = mode ? W->d_Hdd_L : W->d_Hdd; float* bd = mode ? W->d_bd_L : W->d_bd; float* Hcd = mode ? W->d_Hcd_L : W->d_Hcd;
+	double* Hout = mode ? W->d_HL : W->d_HA; double* bout = mode ? W->d_bL : W->d_bA;
+	if (mode == 0)
+		ba_accum_top_kernel<0><<<W->nChunks, 128, 0, st>>>(W->d_perm, W->d_chunk_start, W->d_chunk_cnt, W->d_isAct, W->d_isLin, W->d_efsel,
+		                                                 W->d_J[0], W->d_J[1], W->d_contrib, W->d_topPartials, W->d_chunk_nres, LA);
+	else
+		ba_accum_top_kernel<1><<<W->nChunks, 128, 0, st>>>(W->d_perm, W->d_chunk_start, W->d_chunk_cnt, W->d_isAct, W->d_isLin, W->d_efsel,
+		                                                 W->d_J[0], W->d_J[1], W->d_contrib, W->d_topPartials, W->d_chunk_nres, LA);
+	ba_point_sums_kernel<<<(W->P.nP + 127) / 128, 128, 0, st>>>(W->P.nP, W->d_res_begin, W->d_isAct, W->d_isLin, W->d_contrib, Hdd, bd, Hcd, mode);
 	ba_reduce_partials_kernel<<<dim3(1, nF * nF), NTOP_PAD, 0, st>>>(W->d_topPartials, NTOP_PAD, NTOP_PAD, W->d_pair_chunk_begin, W->d_topRed);
 	ba_top_pair_kernel<<<nF * nF, 256, 0, st>>>(nF, W->d_topRed, W->d_adHost, W->d_adTarget, W->d_topContrib);
-	ba_top_gather_kernel<<<nF * nF + 1, 64, 0, st>>>(nF, W->nChunks, W->d_chunk_nres, W->d_topContrib, W->d_HA, W->d_bA, W->d_scalars);
+	ba_top_gather_kernel<<<nF * nF + 1, 64, 0, st>>>(nF, W->nChunks, W->d_chunk_nres, W->d_topContrib, Hout, bout, W->d_scalars + (mode ? 2 : 0),
+	                                               mode ? W->d_priorH : nullptr, W->d_priorD, W->d_cDeltaF);
 	ctx->launches += 5;
 	CK(cudaGetLastError());
-	W->top_done = true;
+	if (mode == 0) W->top_done = true;
 	return 0;
 }
 
-static int enqueue_schur(dso_b200_ctx* ctx)
+int ba_enqueue_schur(dso_b200_ctx* ctx)
 {
 	BAWorkspace* W = ctx->ba;
 	const int nF = W->P.nF, nP = W->P.nP;
-	ba_schur_prep_kernel<<<(nP + 127) / 128, 128, 0, ctx->stream>>>(nP, W->d_res_begin, W->d_isAct, W->d_Hdd, W->d_bd, W->d_priorF, W->d_deltaF,
-	                                                              W->d_HdiF, W->d_bdSumF, W->d_idh);
+	ba_schur_prep_kernel<<<(nP + 127) / 128, 128, 0, ctx->stream>>>(nP, W->d_res_begin, W->d_isAct, W->d_Hdd, W->d_bd, W->d_Hcd,
+	                                                              W->d_Hdd_L, W->d_bd_L, W->d_Hcd_L, W->d_priorF, W->d_deltaF,
+	                                                              W->d_HdiF, W->d_bdSumF, W->d_idh, W->d_HcdSum);
 	ba_schur_accum_kernel<<<W->nPC, 256, 0, ctx->stream>>>(nF, W->d_pc_start, W->d_pc_cnt, W->d_res_begin, W->d_rtarget, W->d_isAct, W->d_JpJdF,
-	                                                     W->d_HdiF, W->d_bdSumF, W->d_Hcd, W->d_scPartials, W->scN);
+	                                                     W->d_HdiF, W->d_bdSumF, W->d_HcdSum, W->d_scPartials, W->scN);
 	const int nRed = nF * nF * 64 + nF * 32 + nF * 8;
 	ba_reduce_partials_kernel<<<dim3((nRed + 255) / 256, nF), 256, 0, ctx->stream>>>(W->d_scPartials, W->scN, nRed, W->d_host_pc_begin, W->d_scRed);
 	ba_schur_stage1_kernel<<<nF * nF, 64, 0, ctx->stream>>>(nF, W->d_scRed, nRed, W->d_adHost, W->d_adTarget, W->d_scContrib);
@@ -1227,7 +1291,7 @@ static int enqueue_schur(dso_b200_ctx* ctx)
 	return 0;
 }
 
-static int check_ready(dso_b200_ctx* ctx, const char* fn)
+int ba_check_ready(dso_b200_ctx* ctx, const char* fn)
 {
 	if (!ctx || !ctx->ba) { dso_set_error("%s: null context", fn); return DSO_B200_E_ARG; }
 	BAWorkspace* W = ctx->ba;
@@ -1242,12 +1306,12 @@ static int check_ready(dso_b200_ctx* ctx, const char* fn)
 extern "C" int dso_b200_ba_linearize(dso_b200_ctx* ctx, int* newState, float* newEnergy, float* newEnergyWithOutlier,
                                      float* centerProjectedTo3, float* projectedTo16, float* J74, double* energy_sum)
 {
-	int rc = check_ready(ctx, __func__);
+	int rc = ba_check_ready(ctx, __func__);
 	if (rc) return rc;
 	CK(cudaSetDevice(ctx->device));
 	BAWorkspace* W = ctx->ba;
 	const size_t nR = W->P.nR;
-	rc = enqueue_linearize(ctx);
+	rc = ba_enqueue_linearize(ctx);
 	if (rc) return rc;
 	cudaStream_t s = ctx->stream;
 	if (newState) CK(cudaMemcpyAsync(newState, W->d_newState, nR * sizeof(int), cudaMemcpyDeviceToHost, s));
@@ -1272,12 +1336,12 @@ extern "C" int dso_b200_ba_linearize(dso_b200_ctx* ctx, int* newState, float* ne
 
 extern "C" int dso_b200_ba_apply_res(dso_b200_ctx* ctx, unsigned char* isActive_out, float* JpJdF8_out)
 {
-	int rc = check_ready(ctx, __func__);
+	int rc = ba_check_ready(ctx, __func__);
 	if (rc) return rc;
 	BAWorkspace* W = ctx->ba;
 	BA_CHECK(W->lin_done, "call dso_b200_ba_linearize first");
 	CK(cudaSetDevice(ctx->device));
-	rc = enqueue_apply(ctx);
+	rc = ba_enqueue_apply(ctx);
 	if (rc) return rc;
 	const size_t nR = W->P.nR;
 	if (isActive_out) CK(cudaMemcpyAsync(isActive_out, W->d_isAct, nR, cudaMemcpyDeviceToHost, ctx->stream));
@@ -1290,12 +1354,12 @@ extern "C" int dso_b200_ba_apply_res(dso_b200_ctx* ctx, unsigned char* isActive_
 extern "C" int dso_b200_ba_accumulate_A(dso_b200_ctx* ctx, double* H, double* b, int* resInA,
                                         float* Hdd_accAF, float* bd_accAF, float* Hcd_accAF4)
 {
-	int rc = check_ready(ctx, __func__);
+	int rc = ba_check_ready(ctx, __func__);
 	if (rc) return rc;
 	ARG_CHECK(H && b, "null output");
 	CK(cudaSetDevice(ctx->device));
 	BAWorkspace* W = ctx->ba;
-	rc = enqueue_top(ctx);
+	rc = ba_enqueue_top(ctx, 0);
 	if (rc) return rc;
 	const int N = 8 * W->P.nF + CPARS;
 	const size_t nP = W->P.nP;
@@ -1316,13 +1380,13 @@ extern "C" int dso_b200_ba_accumulate_A(dso_b200_ctx* ctx, double* H, double* b,
 extern "C" int dso_b200_ba_accumulate_SC(dso_b200_ctx* ctx, double* H_sc, double* b_sc,
                                          float* HdiF, float* bdSumF, float* idepth_hessian)
 {
-	int rc = check_ready(ctx, __func__);
+	int rc = ba_check_ready(ctx, __func__);
 	if (rc) return rc;
 	ARG_CHECK(H_sc && b_sc, "null output");
 	BAWorkspace* W = ctx->ba;
 	BA_CHECK(W->top_done, "call dso_b200_ba_accumulate_A first (it produces Hdd/bd/Hcd, as in EnergyFunctional::solveSystemF)");
 	CK(cudaSetDevice(ctx->device));
-	rc = enqueue_schur(ctx);
+	rc = ba_enqueue_schur(ctx);
 	if (rc) return rc;
 	const int N = 8 * W->P.nF + CPARS;
 	const size_t nP = W->P.nP;
@@ -1341,15 +1405,15 @@ extern "C" int dso_b200_ba_accumulate_SC(dso_b200_ctx* ctx, double* H_sc, double
 extern "C" int dso_b200_ba_step(dso_b200_ctx* ctx, double* H_A, double* b_A, double* H_sc, double* b_sc,
                                 double* energy_sum, int* resInA)
 {
-	int rc = check_ready(ctx, __func__);
+	int rc = ba_check_ready(ctx, __func__);
 	if (rc) return rc;
 	ARG_CHECK(H_A && b_A && H_sc && b_sc, "null output");
 	CK(cudaSetDevice(ctx->device));
 	BAWorkspace* W = ctx->ba;
-	if ((rc = enqueue_linearize(ctx))) return rc;
-	if ((rc = enqueue_apply(ctx))) return rc;
-	if ((rc = enqueue_top(ctx))) return rc;
-	if ((rc = enqueue_schur(ctx))) return rc;
+	if ((rc = ba_enqueue_linearize(ctx))) return rc;
+	if ((rc = ba_enqueue_apply(ctx))) return rc;
+	if ((rc = ba_enqueue_top(ctx, 0))) return rc;
+	if ((rc = ba_enqueue_schur(ctx))) return rc;
 	const int N = 8 * W->P.nF + CPARS;
 	const size_t NN = (size_t)N * N;
 	cudaStream_t s = ctx->stream;

@@ -1,0 +1,99 @@
+// Shared definitions of the windowed-BA kernels (ba.cu: linearize / accumulate; ba_solve.cu: solve / resubstitute).
+#pragma once
+#include "common.cuh"
+#include <vector>
+
+#define CPARS 4
+#define CHUNK_R 64
+#define CHUNK_P 16
+#define NTOP 91           // 55 + 30 + 6 unique entries of the 13x13 block
+#define NTOP_PAD 96
+#define JSZ 74
+#define ST_IN 0
+#define ST_OOB 1
+#define ST_OUTLIER 2
+#define SCALE_IDEPTH 1.0f
+#define SCALE_F 50.0f
+#define SCALE_C 50.0f
+#define OUTLIER_TH_SUM 2500.0f     // setting_outlierTHSumComponent = 50*50
+#define HUBER_TH 9.0f              // setting_huberTH
+
+// offsets into the flattened RawResidualJacobian (RawResidualJacobian.h:40-79)
+#define J_RESF 0
+#define J_PDXI0 8
+#define J_PDXI1 14
+#define J_PDC0 20
+#define J_PDC1 24
+#define J_PDD 28
+#define J_IDX0 30
+#define J_IDX1 38
+#define J_AB0 46
+#define J_AB1 54
+#define J_IDX2 62
+#define J_ABIDX 66
+#define J_AB2 70
+
+
+struct BAParams
+{
+	int nF, w, h, nR, nP;
+	float fx, fy, cx, cy, fxi, fyi, wM3G, hM3G;
+	float frameEnergyTH[MAXF];
+	const float4* img[MAXF];
+	int fixA, fixB;            // setting_affineOptModeA/B < 0 (Residuals.cpp:257-258)
+};
+
+// inputs of the linearised-residual mode (addPoint<1>, fixLinearizationF)
+struct BALinArgs
+{
+	const int* rpoint; const int* rtarget; const int* phost; const float* deltaF;
+	const float* adHTdeltaF; const float* cDeltaF; const float* resToZero;
+	int nF;
+};
+
+struct BASolve;    // ba_solve.cu
+
+struct BAWorkspace
+{
+	BAParams P;
+	bool window_set, glue_set, points_set, res_set, lin_done, top_done;
+	float* d_precalc; double* d_adHost; double* d_adTarget;
+	// points
+	int capP;
+	float4* d_pt; float* d_color; float* d_weights; int* d_phost; float* d_priorF; float* d_deltaF; int* d_res_begin;
+	float* d_Hdd; float* d_bd; float* d_Hcd; float* d_HdiF; float* d_bdSumF; float* d_idh;
+	// residuals
+	int capR;
+	int* d_rpoint; int* d_rtarget; int* d_state; int* d_newState; double* d_energy; float* d_newEnergy; float* d_newEnergyWO;
+	unsigned char* d_isLin; unsigned char* d_isAct; unsigned char* d_efsel;
+	float* d_cpt; float* d_proj; float* d_J[2]; float* d_JpJdF; float* d_contrib; double* d_resEnergy;
+	int* d_perm;
+	// chunks (top): residuals sorted by pair; (schur): points by host
+	int nChunks, capChunks; int* d_chunk_start; int* d_chunk_cnt; int* d_pair_chunk_begin;   // [nF*nF+1]
+	float* d_topPartials; int* d_chunk_nres;
+	int nPC, capPC; int* d_pc_start; int* d_pc_cnt; int* d_pc_host; int* d_host_pc_begin;     // [nF+1]
+	float* d_scPartials; int scN;
+	double* d_scContrib;       // stage-1 contributions
+	double* d_scRed; double* d_topRed; double* d_topContrib;
+	// outputs
+	double* d_HA; double* d_bA; double* d_HS; double* d_bS; double* d_energy_blocks; double* d_scalars;   // [0] energy sum, [1] resInA
+	double* h_out;             // pinned: HA, bA, HS, bS, scalars
+	std::vector<int> h_rpoint, h_res_begin, h_phost;
+	// linearised residuals (accumulateLF_MT) and priors
+	float* d_adHTdeltaF; float* d_cDeltaF; float h_cDeltaF[4];                   // EnergyFunctional::setDeltaF
+	float* d_resToZero;                                                          // EFResidual::res_toZeroF [nR*8]
+	float* d_Hdd_L; float* d_bd_L; float* d_Hcd_L; float* d_HcdSum;              // per point: *_accLF, Hcd_accAF + Hcd_accLF
+	double* d_HL; double* d_bL;                                                  // d_scalars[3] = resInL
+	double* d_priorH; double* d_priorD; double* d_delta;                         // [8nF+4]: prior, delta_prior, delta (entries 0..3 of the deltas: cDeltaF)
+	int nLin;                                                                    // linearised residuals (-1: unknown)
+	BASolve* S;
+};
+
+int ba_check_ready(dso_b200_ctx* ctx, const char* fn);
+int ba_enqueue_linearize(dso_b200_ctx* ctx);
+int ba_enqueue_apply(dso_b200_ctx* ctx);
+int ba_enqueue_top(dso_b200_ctx* ctx, int mode);
+int ba_enqueue_schur(dso_b200_ctx* ctx);
+void ba_solve_destroy(BAWorkspace* W);
+
+#define BA_CHECK(cond, msg) do { if (!(cond)) { dso_set_error("%s: %s", __func__, msg); return DSO_B200_E_STATE; } } while (0)

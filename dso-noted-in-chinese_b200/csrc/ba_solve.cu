@@ -1,0 +1,691 @@
+// Next rows of the windowed-BA path (SURVEY.md section 8f, N1 and the accumulate half of N2): everything between the
+// Schur accumulation and the next linearisation stays on the device.
+//
+//   ba_fix_lin_kernel        EFResidual::fixLinearizationF (EnergyFunctionalStructs.cpp:89-115)
+//   ba_accum_top_kernel<1>   accumulateLF_MT = addPoint<1> + stitch with priors (ba.cu, shared with the active mode)
+//   ba_solve_kernel          EnergyFunctional::solveSystemF tail (EnergyFunctional.cpp:822-918): bM_top, HFinal_top /
+//                            bFinal_top, damping, the diagonally scaled LDL^T solve (Eigen::LDLT pivot rule: largest
+//                            remaining ORIGINAL diagonal entry), orthogonalize(&x, 0), and resubstituteF_MT's xAd (:276-293)
+//   ba_resubstitute_kernel   resubstituteFPt (:304-330): per-point inverse-depth step
+//   ba_points_step_kernel    the per-point half of FullSystem::doStepFromBackup (FullSystemOptimize.cpp:272-286)
+//
+// One CTA solves the (8nF+4)^2 <= 68^2 FP64 system out of shared memory: a latency-bound chain of 68 pivots, not a
+// bandwidth problem; the point kernels are a few kB of coalesced FP32 traffic.
+#include "ba_internal.cuh"
+#include <cmath>
+#include <cstring>
+
+#define NMAX (8 * MAXF + CPARS)
+#define LDH (NMAX + 1)
+
+#define SOLVER_SVD 1
+#define SOLVER_ORTHOGONALIZE_SYSTEM 2
+#define SOLVER_USE_GN 64
+#define SOLVER_FIX_LAMBDA 128
+#define SOLVER_ORTHOGONALIZE_X 256
+#define SOLVER_ORTHOGONALIZE_X_LATER 2048
+
+struct BASolve
+{
+	double* d_HM; double* d_bM;                      // marginalisation prior
+	double* d_P; bool haveP;                         // 0.5 (N Npi^T + Npi N^T) of EnergyFunctional::orthogonalize
+	double* d_x; float* d_xAd; double* d_HF; double* d_bF;
+	int capP, capR;
+	float* d_step; float* d_idepth_backup; double* d_stepBlocks; unsigned char* d_which;
+	double* h_x;                                     // pinned: x (NMAX), step sums (4)
+	bool priors_set;
+};
+
+static int solve_state(dso_b200_ctx* ctx, BASolve** out)
+{
+	BAWorkspace* W = ctx->ba;
+	if (!W->S)
+	{
+		BASolve* S = new BASolve();
+		memset(S, 0, sizeof(*S));
+		CK(cudaMalloc(&S->d_HM, (size_t)NMAX * NMAX * sizeof(double)));
+		CK(cudaMalloc(&S->d_bM, NMAX * sizeof(double)));
+		CK(cudaMalloc(&S->d_P, (size_t)NMAX * NMAX * sizeof(double)));
+		CK(cudaMalloc(&S->d_x, NMAX * sizeof(double)));
+		CK(cudaMalloc(&S->d_xAd, MAXF * MAXF * 8 * sizeof(float)));
+		CK(cudaMalloc(&S->d_HF, (size_t)NMAX * NMAX * sizeof(double)));
+		CK(cudaMalloc(&S->d_bF, NMAX * sizeof(double)));
+		CK(cudaMemset(S->d_HM, 0, (size_t)NMAX * NMAX * sizeof(double)));
+		CK(cudaMemset(S->d_bM, 0, NMAX * sizeof(double)));
+		CK(cudaHostAlloc((void**)&S->h_x, (NMAX + 8) * sizeof(double), cudaHostAllocDefault));
+		W->S = S;
+	}
+	*out = W->S;
+	return 0;
+}
+
+static int ensure_point_buffers(dso_b200_ctx* ctx, BASolve* S)
+{
+	BAWorkspace* W = ctx->ba;
+	if (W->P.nP > S->capP)
+	{
+		if (S->capP) { cudaFree(S->d_step); cudaFree(S->d_idepth_backup); cudaFree(S->d_stepBlocks); }
+		const size_t n = (size_t)W->P.nP;
+		CK(cudaMalloc(&S->d_step, n * sizeof(float)));
+		CK(cudaMalloc(&S->d_idepth_backup, n * sizeof(float)));
+		CK(cudaMalloc(&S->d_stepBlocks, ((n + 255) / 256) * 2 * sizeof(double)));
+		CK(cudaMemset(S->d_step, 0, n * sizeof(float)));
+		S->capP = W->P.nP;
+	}
+	return 0;
+}
+
+void ba_solve_destroy(BAWorkspace* W)
+{
+	BASolve* S = W->S;
+	if (!S) return;
+	cudaFree(S->d_HM); cudaFree(S->d_bM); cudaFree(S->d_P); cudaFree(S->d_x);
+	cudaFree(S->d_xAd); cudaFree(S->d_HF); cudaFree(S->d_bF);
+	if (S->capP) { cudaFree(S->d_step); cudaFree(S->d_idepth_backup); cudaFree(S->d_stepBlocks); }
+	if (S->capR) cudaFree(S->d_which);
+	cudaFreeHost(S->h_x);
+	delete S;
+	W->S = nullptr;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// EFResidual::fixLinearizationF, EnergyFunctionalStructs.cpp:89-115: res_toZeroF = resF - J * delta for the flagged
+// active residuals, which become linearised
+__device__ __forceinline__ void jp_delta(const float* __restrict__ J, const float* __restrict__ dp, const float* __restrict__ dc, float dd, float* d)
+{
+#pragma unroll
+	for (int k = 0; k < 2; k++)
+	{
+		const float* xi = J + (k ? J_PDXI1 : J_PDXI0);
+		const float* c = J + (k ? J_PDC1 : J_PDC0);
+		const float s6 = fadd(fadd(fmul(xi[0], dp[0]), fadd(fmul(xi[1], dp[1]), fmul(xi[2], dp[2]))),
+		                      fadd(fmul(xi[3], dp[3]), fadd(fmul(xi[4], dp[4]), fmul(xi[5], dp[5]))));
+		const float s4 = fadd(fadd(fmul(c[0], dc[0]), fmul(c[1], dc[1])), fadd(fmul(c[2], dc[2]), fmul(c[3], dc[3])));
+		d[k] = fadd(fadd(s6, s4), fmul(J[J_PDD + k], dd));
+	}
+	d[2] = dp[6]; d[3] = dp[7];
+}
+
+__global__ void ba_fix_lin_kernel(int nR, int nF, const unsigned char* __restrict__ which, const unsigned char* __restrict__ isAct,
+                                  unsigned char* isLin, const unsigned char* __restrict__ efsel, const float* __restrict__ J0,
+                                  const float* __restrict__ J1, const int* __restrict__ rpoint, const int* __restrict__ rtarget,
+                                  const int* __restrict__ phost, const float* __restrict__ deltaF, const float* __restrict__ adHTdeltaF,
+                                  const float* __restrict__ cDeltaF, float* resToZero)
+{
+	const int r = blockIdx.x * blockDim.x + threadIdx.x;
+	if (r >= nR) return;
+	if (!isAct[r] || (which && !which[r])) return;
+	const float* J = (efsel[r] ? J1 : J0) + (size_t)r * JSZ;
+	const int p = rpoint[r];
+	float d[4];
+	jp_delta(J, adHTdeltaF + 8 * (phost[p] + nF * rtarget[r]), cDeltaF, deltaF[p], d);
+#pragma unroll
+	for (int i = 0; i < 8; i++)
+	{
+		float rtz = J[J_RESF + i];
+		rtz = fsub(rtz, fmul(J[J_IDX0 + i], d[0]));
+		rtz = fsub(rtz, fmul(J[J_IDX1 + i], d[1]));
+		rtz = fsub(rtz, fmul(J[J_AB0 + i], d[2]));
+		rtz = fsub(rtz, fmul(J[J_AB1 + i], d[3]));
+		resToZero[8 * (size_t)r + i] = rtz;
+	}
+	isLin[r] = 1;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+struct SolveArgs
+{
+	int nF, orth, haveL;
+	double lambda;
+	const double* HA; const double* bA; const double* HL; const double* bL; const double* HS; const double* bS;
+	const double* HM; const double* bM; const double* delta; const double* priorH; const double* priorD; const float* cDeltaF;
+	const double* P; const double* adHost; const double* adTarget;
+	double* x; float* xAd; double* HF; double* bF;
+};
+
+// solveSystemF tail (EnergyFunctional.cpp:822-918, default solver branch) + xAd of resubstituteF_MT (:283-293).
+// All products and sums are separate IEEE operations in the reference's order (no contraction), so the only
+// differences to the CPU path are the summation order of the back substitution and of Eigen's GEMV.
+__global__ void __launch_bounds__(256) ba_solve_kernel(SolveArgs a)
+{
+	__shared__ double A[NMAX * LDH];
+	__shared__ double sv[NMAX], rhs[NMAX], yv[NMAX], xv[NMAX], dg[NMAX], Lk[NMAX], dl[NMAX];
+	__shared__ int ord[NMAX];
+	const int tid = threadIdx.x, N = 8 * a.nF + CPARS;
+	// getStitchedDeltaF (:952-958)
+	if (tid < N) dl[tid] = tid < CPARS ? (double)a.cDeltaF[tid] : a.delta[tid];
+	__syncthreads();
+	if (tid < N)
+	{
+		// bM_top = bM + HM * delta (:824); bFinal_top = bL_top + bM_top + bA_top - b_sc (:859)
+		double s = 0.0;
+		for (int j = 0; j < N; j++) s = __dadd_rn(s, __dmul_rn(a.HM[(size_t)tid * N + j], dl[j]));
+		const double bMtop = __dadd_rn(a.bM[tid], s);
+		const double bl = a.haveL ? a.bL[tid] : __dmul_rn(a.priorH[tid], tid < CPARS ? (double)a.cDeltaF[tid] : a.priorD[tid]);
+		rhs[tid] = __dsub_rn(__dadd_rn(__dadd_rn(bl, bMtop), a.bA[tid]), a.bS[tid]);
+	}
+	// HFinal_top = HL_top + HM + HA_top; diagonal *= (1+lambda); -= H_sc * (1.0f/(1+lambda))  (:857-866)
+	const double damp = __dadd_rn(1.0, a.lambda), isc = __ddiv_rn(1.0, __dadd_rn(1.0, a.lambda));
+	for (int e = tid; e < N * N; e += 256)
+	{
+		const int i = e / N, j = e - i * N;
+		const double hl = a.haveL ? a.HL[e] : (i == j ? a.priorH[i] : 0.0);
+		double v = __dadd_rn(__dadd_rn(hl, a.HM[e]), a.HA[e]);
+		if (i == j) v = __dmul_rn(v, damp);
+		v = __dsub_rn(v, __dmul_rn(a.HS[e], isc));
+		A[i * LDH + j] = v;
+		if (a.HF) a.HF[e] = v;
+	}
+	__syncthreads();
+	if (tid < N)
+	{
+		if (a.bF) a.bF[tid] = rhs[tid];
+		sv[tid] = __ddiv_rn(1.0, sqrt(__dadd_rn(A[tid * LDH + tid], 10.0)));    // :905
+	}
+	__syncthreads();
+	for (int e = tid; e < N * N; e += 256)
+	{
+		const int i = e / N, j = e - i * N;
+		A[i * LDH + j] = __dmul_rn(__dmul_rn(sv[i], A[i * LDH + j]), sv[j]);     // SVecI.asDiagonal() * H * SVecI.asDiagonal()
+	}
+	if (tid < N) { rhs[tid] = __dmul_rn(sv[tid], rhs[tid]); ord[tid] = tid; }
+	__syncthreads();
+	if (tid < N) dg[tid] = fabs(A[tid * LDH + tid]);
+	__syncthreads();
+	// Eigen::LDLT pivot order: at step k the largest |diagonal| among positions k..N-1 (first one on ties) is swapped to
+	// position k; the diagonal entries it looks at are the not-yet-updated ones, so the whole order follows from the
+	// initial diagonal.  Warp 0 runs the N selection steps on (dg, ord).
+	if (tid < 32)
+	{
+		for (int k = 0; k < N; k++)
+		{
+			double best = -1.0; int bi = N;
+			for (int i = k + tid; i < N; i += 32) { const double v = dg[i]; if (v > best) { best = v; bi = i; } }
+#pragma unroll
+			for (int o = 16; o > 0; o >>= 1)
+			{
+				const double ob = __shfl_xor_sync(0xffffffffu, best, o);
+				const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+				if (ob > best || (ob == best && oi < bi)) { best = ob; bi = oi; }
+			}
+			if (tid == 0 && bi != k && bi < N)
+			{
+				const double t = dg[k]; dg[k] = dg[bi]; dg[bi] = t;
+				const int u = ord[k]; ord[k] = ord[bi]; ord[bi] = u;
+			}
+			__syncwarp();
+		}
+	}
+	__syncthreads();
+#define AT(i, j) A[ord[i] * LDH + ord[j]]
+	// right-looking LDL^T on the permuted matrix, lower triangle: same operations, in the same order per entry, as the
+	// bordered form Eigen uses: A(i,j) -= (L(i,k) * L(j,k)) * D(k) for k ascending, then L(i,j) = A(i,j) / D(j)
+	for (int k = 0; k < N; k++)
+	{
+		const double d = AT(k, k);
+		if (tid > k && tid < N)
+		{
+			const double s = AT(tid, k);
+			const double l = (fabs(d) > 0.0) ? __ddiv_rn(s, d) : 0.0;
+			Lk[tid] = l;
+		}
+		__syncthreads();
+		const int m = N - k - 1;
+		for (int e = tid; e < m * m; e += 256)
+		{
+			const int ii = e / m, jj = e - ii * m;
+			if (jj > ii) continue;
+			const int i = k + 1 + ii, j = k + 1 + jj;
+			AT(i, j) = __dsub_rn(AT(i, j), __dmul_rn(__dmul_rn(Lk[i], Lk[j]), d));
+		}
+		if (tid > k && tid < N) AT(tid, k) = Lk[tid];
+		__syncthreads();
+	}
+	// solve: permute, L y = b, D, L^T, permute back (:908)
+	if (tid < N) yv[tid] = rhs[ord[tid]];
+	__syncthreads();
+	for (int k = 0; k < N; k++)
+	{
+		if (tid > k && tid < N) yv[tid] = __dsub_rn(yv[tid], __dmul_rn(AT(tid, k), yv[k]));
+		__syncthreads();
+	}
+	if (tid < N)
+	{
+		const double d = AT(tid, tid);
+		yv[tid] = (fabs(d) > 2.2250738585072014e-308) ? __ddiv_rn(yv[tid], d) : 0.0;
+	}
+	__syncthreads();
+	for (int k = N - 1; k > 0; k--)
+	{
+		if (tid < k) yv[tid] = __dsub_rn(yv[tid], __dmul_rn(AT(k, tid), yv[k]));
+		__syncthreads();
+	}
+#undef AT
+	if (tid < N) xv[ord[tid]] = __dmul_rn(sv[ord[tid]], yv[tid]);
+	__syncthreads();
+	if (a.orth)
+	{
+		// orthogonalize(&x, 0) (:741-792): x -= NNpiTS * x with the projector prepared by dso_b200_ba_set_nullspaces
+		double s = 0.0;
+		if (tid < N) for (int j = 0; j < N; j++) s = __dadd_rn(s, __dmul_rn(a.P[(size_t)tid * N + j], xv[j]));
+		__syncthreads();
+		if (tid < N) xv[tid] = __dsub_rn(xv[tid], s);
+		__syncthreads();
+	}
+	if (tid < N) a.x[tid] = xv[tid];
+	// xAd[nF*h + t] = xF_h^T adHostF[h + nF*t] + xF_t^T adTargetF[h + nF*t]  (:289-292), 8-term unrolled reductions
+	for (int e = tid; e < a.nF * a.nF * 8; e += 256)
+	{
+		const int j = e & 7, ht = e >> 3, h = ht / a.nF, t = ht - h * a.nF;
+		const double* AH = a.adHost + (size_t)(h + a.nF * t) * 64;
+		const double* AT_ = a.adTarget + (size_t)(h + a.nF * t) * 64;
+		float ph[8], pt[8];
+#pragma unroll
+		for (int i = 0; i < 8; i++)
+		{
+			ph[i] = fmul((float)xv[CPARS + 8 * h + i], (float)AH[i * 8 + j]);
+			pt[i] = fmul((float)xv[CPARS + 8 * t + i], (float)AT_[i * 8 + j]);
+		}
+		const float sh = fadd(fadd(fadd(ph[0], ph[1]), fadd(ph[2], ph[3])), fadd(fadd(ph[4], ph[5]), fadd(ph[6], ph[7])));
+		const float st = fadd(fadd(fadd(pt[0], pt[1]), fadd(pt[2], pt[3])), fadd(fadd(pt[4], pt[5]), fadd(pt[6], pt[7])));
+		a.xAd[e] = fadd(sh, st);
+	}
+}
+
+// resubstituteFPt, EnergyFunctional.cpp:304-330
+__global__ void ba_resubstitute_kernel(int nP, int nF, const int* __restrict__ res_begin, const int* __restrict__ rtarget,
+                                       const int* __restrict__ phost, const unsigned char* __restrict__ isAct,
+                                       const float* __restrict__ JpJdF, const float* __restrict__ HcdSum, const float* __restrict__ bdSumF,
+                                       const float* __restrict__ HdiF, const double* __restrict__ x, const float* __restrict__ xAd, float* step)
+{
+	const int p = blockIdx.x * blockDim.x + threadIdx.x;
+	if (p >= nP) return;
+	int ngood = 0;
+	for (int r = res_begin[p]; r < res_begin[p + 1]; r++) ngood += isAct[r] ? 1 : 0;
+	if (ngood == 0) { step[p] = 0.f; return; }
+	float b = bdSumF[p];
+	const float* hc = HcdSum + 4 * (size_t)p;
+	const float x0 = (float)x[0], x1 = (float)x[1], x2 = (float)x[2], x3 = (float)x[3];
+	b = fsub(b, fadd(fadd(fmul(x0, hc[0]), fmul(x1, hc[1])), fadd(fmul(x2, hc[2]), fmul(x3, hc[3]))));
+	const int h = phost[p];
+	for (int r = res_begin[p]; r < res_begin[p + 1]; r++)
+	{
+		if (!isAct[r]) continue;
+		const float* xa = xAd + 8 * (h * nF + rtarget[r]);
+		const float* jp = JpJdF + 8 * (size_t)r;
+		float q[8];
+#pragma unroll
+		for (int i = 0; i < 8; i++) q[i] = fmul(xa[i], jp[i]);
+		b = fsub(b, fadd(fadd(fadd(q[0], q[1]), fadd(q[2], q[3])), fadd(fadd(q[4], q[5]), fadd(q[6], q[7]))));
+	}
+	step[p] = fmul(-b, HdiF[p]);
+}
+
+// per-point half of FullSystem::doStepFromBackup (FullSystemOptimize.cpp:272-286): idepth = idepth_backup + stepfacD * step,
+// setIdepthZero of the same value (HessianBlocks.h:470-490; SCALE_IDEPTH = 1), EFPoint::deltaF = idepth - idepth_zero = 0;
+// block sums of step^2 and |idepth_backup| in FP64 (fixed tree)
+__global__ void __launch_bounds__(256) ba_points_step_kernel(int nP, float stepfacD, const float* __restrict__ step,
+                                                             const float* __restrict__ backup, float4* pt, float* deltaF, double* blocks)
+{
+	__shared__ double s0[256], s1[256];
+	const int p = blockIdx.x * 256 + threadIdx.x;
+	double a = 0.0, b = 0.0;
+	if (p < nP)
+	{
+		const float st = step[p], bk = backup[p];
+		const float v = fadd(bk, fmul(stepfacD, st));
+		float4 q = pt[p];
+		q.z = v; q.w = v;
+		pt[p] = q;
+		deltaF[p] = 0.f;
+		a = (double)fmul(st, st); b = (double)fabsf(bk);
+	}
+	s0[threadIdx.x] = a; s1[threadIdx.x] = b;
+	__syncthreads();
+	for (int o = 128; o > 0; o >>= 1)
+	{
+		if (threadIdx.x < o) { s0[threadIdx.x] += s0[threadIdx.x + o]; s1[threadIdx.x] += s1[threadIdx.x + o]; }
+		__syncthreads();
+	}
+	if (threadIdx.x == 0) { blocks[2 * blockIdx.x] = s0[0]; blocks[2 * blockIdx.x + 1] = s1[0]; }
+}
+__global__ void ba_points_step_final_kernel(int nb, const double* __restrict__ blocks, double* out)
+{
+	if (threadIdx.x == 0 && blockIdx.x == 0)
+	{
+		double a = 0, b = 0;
+		for (int i = 0; i < nb; i++) { a += blocks[2 * i]; b += blocks[2 * i + 1]; }
+		out[0] = a; out[1] = b;
+	}
+}
+__global__ void ba_points_backup_kernel(int nP, const float4* __restrict__ pt, float* backup, int restore, float4* pt_rw, float* deltaF)
+{
+	const int p = blockIdx.x * blockDim.x + threadIdx.x;
+	if (p >= nP) return;
+	if (!restore) backup[p] = pt[p].z;                      // FullSystem::backupState: ph->idepth_backup = ph->idepth
+	else { float4 q = pt_rw[p]; q.z = backup[p]; q.w = backup[p]; pt_rw[p] = q; deltaF[p] = 0.f; }   // loadSateBackup
+}
+
+// =========================================================================================================
+// host API
+// =========================================================================================================
+extern "C" int dso_b200_ba_set_calib_delta(dso_b200_ctx* ctx, const double* value_minus_value_zero4)
+{
+	ARG_CHECK(ctx && ctx->ba && value_minus_value_zero4, "null argument");
+	BAWorkspace* W = ctx->ba;
+	CK(cudaSetDevice(ctx->device));
+	for (int i = 0; i < 4; i++) W->h_cDeltaF[i] = (float)value_minus_value_zero4[i];   // cDeltaF = value_minus_value_zero.cast<float>() (:193)
+	CK(cudaMemcpyAsync(W->d_cDeltaF, W->h_cDeltaF, 4 * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+	CK(cudaStreamSynchronize(ctx->stream));
+	return 0;
+}
+
+extern "C" int dso_b200_ba_set_priors(dso_b200_ctx* ctx, const double* cPrior4, const double* framePrior, const double* frameDeltaPrior,
+                                      const double* frameDelta, const double* HM, const double* bM)
+{
+	ARG_CHECK(ctx && ctx->ba, "null argument");
+	BAWorkspace* W = ctx->ba;
+	BA_CHECK(W->window_set, "call dso_b200_ba_set_window first");
+	CK(cudaSetDevice(ctx->device));
+	BASolve* S;
+	int rc = solve_state(ctx, &S);
+	if (rc) return rc;
+	const int nF = W->P.nF, N = 8 * nF + CPARS;
+	double ph[NMAX];
+	for (int i = 0; i < N; i++) ph[i] = 0.0;
+	if (cPrior4) for (int i = 0; i < 4; i++) ph[i] = cPrior4[i];
+	if (framePrior) for (int i = 0; i < 8 * nF; i++) ph[CPARS + i] = framePrior[i];
+	cudaStream_t s = ctx->stream;
+	CK(cudaMemcpyAsync(W->d_priorH, ph, N * sizeof(double), cudaMemcpyHostToDevice, s));
+	// delta_prior / delta are also derived by dso_b200_ba_set_frames from the frame states; explicit arrays override them
+	if (frameDeltaPrior) CK(cudaMemcpyAsync(W->d_priorD + CPARS, frameDeltaPrior, 8 * nF * sizeof(double), cudaMemcpyHostToDevice, s));
+	if (frameDelta) CK(cudaMemcpyAsync(W->d_delta + CPARS, frameDelta, 8 * nF * sizeof(double), cudaMemcpyHostToDevice, s));
+	if (HM) CK(cudaMemcpyAsync(S->d_HM, HM, (size_t)N * N * sizeof(double), cudaMemcpyHostToDevice, s));
+	else CK(cudaMemsetAsync(S->d_HM, 0, (size_t)N * N * sizeof(double), s));
+	if (bM) CK(cudaMemcpyAsync(S->d_bM, bM, N * sizeof(double), cudaMemcpyHostToDevice, s));
+	else CK(cudaMemsetAsync(S->d_bM, 0, N * sizeof(double), s));
+	CK(cudaStreamSynchronize(s));
+	S->priors_set = true;
+	return 0;
+}
+
+// thin SVD by one-sided Jacobi rotations: A (m x k, row-major) is overwritten by U*diag(S); V (k x k) accumulates the rotations
+static void svd_hestenes(std::vector<double>& A, int m, int k, std::vector<double>& S, std::vector<double>& V)
+{
+	V.assign((size_t)k * k, 0.0);
+	for (int i = 0; i < k; i++) V[i * k + i] = 1.0;
+	for (int sweep = 0; sweep < 60; sweep++)
+	{
+		double off = 0.0;
+		for (int p = 0; p < k - 1; p++)
+			for (int q = p + 1; q < k; q++)
+			{
+				double al = 0, be = 0, ga = 0;
+				for (int i = 0; i < m; i++) { const double x = A[i * k + p], y = A[i * k + q]; al += x * x; be += y * y; ga += x * y; }
+				if (ga == 0.0 || al == 0.0 || be == 0.0) continue;
+				const double rel = std::fabs(ga) / std::sqrt(al * be);
+				if (rel > off) off = rel;
+				if (rel <= 1e-17) continue;
+				const double zeta = (be - al) / (2.0 * ga);
+				const double t = (zeta >= 0 ? 1.0 : -1.0) / (std::fabs(zeta) + std::sqrt(1.0 + zeta * zeta));
+				const double c = 1.0 / std::sqrt(1.0 + t * t), sn = c * t;
+				for (int i = 0; i < m; i++) { const double x = A[i * k + p], y = A[i * k + q]; A[i * k + p] = c * x - sn * y; A[i * k + q] = sn * x + c * y; }
+				for (int i = 0; i < k; i++) { const double x = V[i * k + p], y = V[i * k + q]; V[i * k + p] = c * x - sn * y; V[i * k + q] = sn * x + c * y; }
+			}
+		if (off < 1e-15) break;
+	}
+	S.assign(k, 0.0);
+	for (int j = 0; j < k; j++)
+	{
+		double n2 = 0;
+		for (int i = 0; i < m; i++) n2 += A[i * k + j] * A[i * k + j];
+		S[j] = std::sqrt(n2);
+	}
+}
+
+extern "C" int dso_b200_ba_set_nullspaces(dso_b200_ctx* ctx, const double* ns, int n, double solverModeDelta)
+{
+	ARG_CHECK(ctx && ctx->ba && (ns || n == 0) && n >= 0 && n <= 16, "bad argument");
+	BAWorkspace* W = ctx->ba;
+	BA_CHECK(W->window_set, "call dso_b200_ba_set_window first");
+	CK(cudaSetDevice(ctx->device));
+	BASolve* S;
+	int rc = solve_state(ctx, &S);
+	if (rc) return rc;
+	if (n == 0) { S->haveP = false; return 0; }
+	// EnergyFunctional::orthogonalize, EnergyFunctional.cpp:745-785: N = normalised columns, Npi = U diag(1/s) V^T (singular
+	// values below solverModeDelta * max dropped), NNpiTS = 0.5 (N Npi^T + Npi N^T).  Host FP64, once per optimisation.
+	const int N = 8 * W->P.nF + CPARS, k = n;
+	std::vector<double> Nn((size_t)N * k), US, Sv, V;
+	for (int j = 0; j < k; j++)
+	{
+		double n2 = 0;
+		for (int i = 0; i < N; i++) n2 += ns[(size_t)j * N + i] * ns[(size_t)j * N + i];
+		const double nrm = std::sqrt(n2);
+		for (int i = 0; i < N; i++) Nn[(size_t)i * k + j] = ns[(size_t)j * N + i] / nrm;
+	}
+	US = Nn;
+	svd_hestenes(US, N, k, Sv, V);
+	double maxSv = 0;
+	for (int j = 0; j < k; j++) if (Sv[j] > maxSv) maxSv = Sv[j];
+	std::vector<double> Npi((size_t)N * k, 0.0), P((size_t)N * N), PS((size_t)N * N);
+	for (int i = 0; i < N; i++)
+		for (int j = 0; j < k; j++)
+		{
+			double s = 0;
+			for (int q = 0; q < k; q++)
+				if (Sv[q] > solverModeDelta * maxSv) s += (US[(size_t)i * k + q] / Sv[q]) * (1.0 / Sv[q]) * V[(size_t)j * k + q];   // U = US / s, then * (1/s)
+			Npi[(size_t)i * k + j] = s;
+		}
+	for (int i = 0; i < N; i++)
+		for (int j = 0; j < N; j++)
+		{
+			double s = 0;
+			for (int q = 0; q < k; q++) s += Nn[(size_t)i * k + q] * Npi[(size_t)j * k + q];
+			P[(size_t)i * N + j] = s;
+		}
+	for (int i = 0; i < N; i++) for (int j = 0; j < N; j++) PS[(size_t)i * N + j] = 0.5 * (P[(size_t)i * N + j] + P[(size_t)j * N + i]);
+	CK(cudaMemcpyAsync(S->d_P, PS.data(), (size_t)N * N * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+	CK(cudaStreamSynchronize(ctx->stream));
+	S->haveP = true;
+	return 0;
+}
+
+extern "C" int dso_b200_ba_fix_linearization(dso_b200_ctx* ctx, const unsigned char* which, float* res_toZeroF_out)
+{
+	int rc = ba_check_ready(ctx, __func__);
+	if (rc) return rc;
+	CK(cudaSetDevice(ctx->device));
+	BAWorkspace* W = ctx->ba;
+	BASolve* S;
+	if ((rc = solve_state(ctx, &S))) return rc;
+	const int nR = W->P.nR;
+	cudaStream_t s = ctx->stream;
+	if (which)
+	{
+		if (nR > S->capR)
+		{
+			if (S->capR) cudaFree(S->d_which);
+			CK(cudaMalloc(&S->d_which, (size_t)nR));
+			S->capR = nR;
+		}
+		CK(cudaMemcpyAsync(S->d_which, which, (size_t)nR, cudaMemcpyHostToDevice, s));
+	}
+	ba_fix_lin_kernel<<<(nR + 255) / 256, 256, 0, s>>>(nR, W->P.nF, which ? S->d_which : nullptr, W->d_isAct, W->d_isLin, W->d_efsel, W->d_J[0], W->d_J[1],
+	                                                 W->d_rpoint, W->d_rtarget, W->d_phost, W->d_deltaF, W->d_adHTdeltaF, W->d_cDeltaF, W->d_resToZero);
+	ctx->launches++;
+	CK(cudaGetLastError());
+	if (res_toZeroF_out) CK(cudaMemcpyAsync(res_toZeroF_out, W->d_resToZero, (size_t)nR * 8 * sizeof(float), cudaMemcpyDeviceToHost, s));
+	CK(cudaStreamSynchronize(s));
+	W->nLin = -1;                  // some residuals may now be linearised: accumulateLF has work
+	W->top_done = false;
+	return 0;
+}
+
+extern "C" int dso_b200_ba_accumulate_L(dso_b200_ctx* ctx, double* H, double* b, int* resInL,
+                                        float* Hdd_accLF, float* bd_accLF, float* Hcd_accLF4)
+{
+	int rc = ba_check_ready(ctx, __func__);
+	if (rc) return rc;
+	ARG_CHECK(H && b, "null output");
+	CK(cudaSetDevice(ctx->device));
+	BAWorkspace* W = ctx->ba;
+	if ((rc = ba_enqueue_top(ctx, 1))) return rc;
+	const int N = 8 * W->P.nF + CPARS;
+	const size_t nP = W->P.nP;
+	cudaStream_t s = ctx->stream;
+	CK(cudaMemcpyAsync(W->h_out, W->d_HL, (size_t)N * N * sizeof(double), cudaMemcpyDeviceToHost, s));
+	CK(cudaMemcpyAsync(W->h_out + N * N, W->d_bL, N * sizeof(double), cudaMemcpyDeviceToHost, s));
+	CK(cudaMemcpyAsync(W->h_out + N * N + N, W->d_scalars + 2, 2 * sizeof(double), cudaMemcpyDeviceToHost, s));
+	if (Hdd_accLF) CK(cudaMemcpyAsync(Hdd_accLF, W->d_Hdd_L, nP * sizeof(float), cudaMemcpyDeviceToHost, s));
+	if (bd_accLF) CK(cudaMemcpyAsync(bd_accLF, W->d_bd_L, nP * sizeof(float), cudaMemcpyDeviceToHost, s));
+	if (Hcd_accLF4) CK(cudaMemcpyAsync(Hcd_accLF4, W->d_Hcd_L, nP * 4 * sizeof(float), cudaMemcpyDeviceToHost, s));
+	CK(cudaStreamSynchronize(s));
+	memcpy(H, W->h_out, (size_t)N * N * sizeof(double));
+	memcpy(b, W->h_out + N * N, N * sizeof(double));
+	if (resInL) *resInL = (int)W->h_out[N * N + N + 1];
+	return 0;
+}
+
+// EnergyFunctional::solveSystemF (EnergyFunctional.cpp:802-924): accumulateAF_MT, accumulateLF_MT, accumulateSCF_MT, the
+// solve and resubstituteF_MT, all enqueued on the context stream; one synchronisation at the end.
+static int enqueue_solve(dso_b200_ctx* ctx, BASolve* S, int iteration, double lambda, int solverMode, bool debug)
+{
+	BAWorkspace* W = ctx->ba;
+	int rc;
+	if (solverMode & SOLVER_USE_GN) lambda = 0;                      // :804
+	if (solverMode & SOLVER_FIX_LAMBDA) lambda = 1e-5;              // :805
+	if ((rc = ba_enqueue_top(ctx, 0))) return rc;                   // :816
+	const bool haveL = W->nLin != 0;
+	if (haveL && (rc = ba_enqueue_top(ctx, 1))) return rc;          // :817 (without linearised residuals H_L, b_L are the priors alone)
+	if ((rc = ba_enqueue_schur(ctx))) return rc;                    // :820
+	if ((rc = ensure_point_buffers(ctx, S))) return rc;
+	SolveArgs a;
+	a.nF = W->P.nF; a.lambda = lambda; a.haveL = haveL ? 1 : 0;
+	a.orth = ((solverMode & SOLVER_ORTHOGONALIZE_X) || (iteration >= 2 && (solverMode & SOLVER_ORTHOGONALIZE_X_LATER))) && S->haveP;   // :913
+	a.HA = W->d_HA; a.bA = W->d_bA; a.HL = W->d_HL; a.bL = W->d_bL; a.HS = W->d_HS; a.bS = W->d_bS;
+	a.HM = S->d_HM; a.bM = S->d_bM; a.delta = W->d_delta; a.priorH = W->d_priorH; a.priorD = W->d_priorD; a.cDeltaF = W->d_cDeltaF;
+	a.P = S->d_P; a.adHost = W->d_adHost; a.adTarget = W->d_adTarget;
+	a.x = S->d_x; a.xAd = S->d_xAd; a.HF = debug ? S->d_HF : nullptr; a.bF = debug ? S->d_bF : nullptr;
+	ba_solve_kernel<<<1, 256, 0, ctx->stream>>>(a);
+	ba_resubstitute_kernel<<<(W->P.nP + 127) / 128, 128, 0, ctx->stream>>>(W->P.nP, W->P.nF, W->d_res_begin, W->d_rtarget, W->d_phost, W->d_isAct,
+	                                                                    W->d_JpJdF, W->d_HcdSum, W->d_bdSumF, W->d_HdiF, S->d_x, S->d_xAd, S->d_step);
+	ctx->launches += 2;
+	CK(cudaGetLastError());
+	return 0;
+}
+
+extern "C" int dso_b200_ba_solve(dso_b200_ctx* ctx, int iteration, double lambda, int solverMode, double* x_out, float* pointStep_out,
+                                 double* HFinal_out, double* bFinal_out)
+{
+	int rc = ba_check_ready(ctx, __func__);
+	if (rc) return rc;
+	ARG_CHECK(!(solverMode & (SOLVER_SVD | SOLVER_ORTHOGONALIZE_SYSTEM)),
+	          "the SOLVER_SVD and SOLVER_ORTHOGONALIZE_SYSTEM branches of solveSystemF are not implemented (default mode is 128|2048)");
+	CK(cudaSetDevice(ctx->device));
+	BAWorkspace* W = ctx->ba;
+	BASolve* S;
+	if ((rc = solve_state(ctx, &S))) return rc;
+	const bool debug = HFinal_out || bFinal_out;
+	if ((rc = enqueue_solve(ctx, S, iteration, lambda, solverMode, debug))) return rc;
+	const int N = 8 * W->P.nF + CPARS;
+	cudaStream_t s = ctx->stream;
+	CK(cudaMemcpyAsync(S->h_x, S->d_x, N * sizeof(double), cudaMemcpyDeviceToHost, s));
+	if (pointStep_out) CK(cudaMemcpyAsync(pointStep_out, S->d_step, (size_t)W->P.nP * sizeof(float), cudaMemcpyDeviceToHost, s));
+	if (HFinal_out) CK(cudaMemcpyAsync(HFinal_out, S->d_HF, (size_t)N * N * sizeof(double), cudaMemcpyDeviceToHost, s));
+	if (bFinal_out) CK(cudaMemcpyAsync(bFinal_out, S->d_bF, N * sizeof(double), cudaMemcpyDeviceToHost, s));
+	CK(cudaStreamSynchronize(s));
+	if (x_out) memcpy(x_out, S->h_x, N * sizeof(double));
+	return 0;
+}
+
+// One Gauss-Newton iteration of FullSystem::optimize as far as it lives on the device: linearizeAll(false) + applyRes
+// (the caller decided to accept the previous step), solveSystemF, and the point half of doStepFromBackup.
+extern "C" int dso_b200_ba_iteration(dso_b200_ctx* ctx, int iteration, double lambda, int solverMode, float stepfacD,
+                                     double* x_out, double* energy_sum, float* step_sums2)
+{
+	int rc = ba_check_ready(ctx, __func__);
+	if (rc) return rc;
+	ARG_CHECK(!(solverMode & (SOLVER_SVD | SOLVER_ORTHOGONALIZE_SYSTEM)), "solver mode not implemented");
+	CK(cudaSetDevice(ctx->device));
+	BAWorkspace* W = ctx->ba;
+	BASolve* S;
+	if ((rc = solve_state(ctx, &S))) return rc;
+	if ((rc = ensure_point_buffers(ctx, S))) return rc;
+	cudaStream_t s = ctx->stream;
+	const int nP = W->P.nP, nb = (nP + 255) / 256, N = 8 * W->P.nF + CPARS;
+	if ((rc = ba_enqueue_linearize(ctx))) return rc;
+	if ((rc = ba_enqueue_apply(ctx))) return rc;
+	if ((rc = enqueue_solve(ctx, S, iteration, lambda, solverMode, false))) return rc;
+	ba_points_backup_kernel<<<(nP + 255) / 256, 256, 0, s>>>(nP, W->d_pt, S->d_idepth_backup, 0, nullptr, nullptr);
+	ba_points_step_kernel<<<nb, 256, 0, s>>>(nP, stepfacD, S->d_step, S->d_idepth_backup, W->d_pt, W->d_deltaF, S->d_stepBlocks);
+	ba_points_step_final_kernel<<<1, 32, 0, s>>>(nb, S->d_stepBlocks, W->d_scalars + 4);
+	ctx->launches += 3;
+	CK(cudaGetLastError());
+	CK(cudaMemcpyAsync(S->h_x, S->d_x, N * sizeof(double), cudaMemcpyDeviceToHost, s));
+	CK(cudaMemcpyAsync(S->h_x + NMAX, W->d_scalars, 6 * sizeof(double), cudaMemcpyDeviceToHost, s));
+	CK(cudaStreamSynchronize(s));
+	if (x_out) memcpy(x_out, S->h_x, N * sizeof(double));
+	if (energy_sum) *energy_sum = S->h_x[NMAX];
+	if (step_sums2) { step_sums2[0] = (float)S->h_x[NMAX + 4]; step_sums2[1] = (float)S->h_x[NMAX + 5]; }
+	W->lin_done = false;
+	return 0;
+}
+
+extern "C" int dso_b200_ba_points_backup(dso_b200_ctx* ctx)
+{
+	int rc = ba_check_ready(ctx, __func__);
+	if (rc) return rc;
+	CK(cudaSetDevice(ctx->device));
+	BAWorkspace* W = ctx->ba;
+	BASolve* S;
+	if ((rc = solve_state(ctx, &S))) return rc;
+	if ((rc = ensure_point_buffers(ctx, S))) return rc;
+	ba_points_backup_kernel<<<(W->P.nP + 255) / 256, 256, 0, ctx->stream>>>(W->P.nP, W->d_pt, S->d_idepth_backup, 0, nullptr, nullptr);
+	ctx->launches++;
+	CK(cudaGetLastError());
+	return 0;
+}
+
+extern "C" int dso_b200_ba_points_step(dso_b200_ctx* ctx, float stepfacD, float* sums2_out, float* idepth_out)
+{
+	int rc = ba_check_ready(ctx, __func__);
+	if (rc) return rc;
+	CK(cudaSetDevice(ctx->device));
+	BAWorkspace* W = ctx->ba;
+	BASolve* S;
+	if ((rc = solve_state(ctx, &S))) return rc;
+	BA_CHECK(S->capP >= W->P.nP, "call dso_b200_ba_points_backup and dso_b200_ba_solve first");
+	cudaStream_t s = ctx->stream;
+	const int nP = W->P.nP, nb = (nP + 255) / 256;
+	ba_points_step_kernel<<<nb, 256, 0, s>>>(nP, stepfacD, S->d_step, S->d_idepth_backup, W->d_pt, W->d_deltaF, S->d_stepBlocks);
+	ba_points_step_final_kernel<<<1, 32, 0, s>>>(nb, S->d_stepBlocks, W->d_scalars + 4);
+	ctx->launches += 2;
+	CK(cudaGetLastError());
+	CK(cudaMemcpyAsync(S->h_x + NMAX, W->d_scalars + 4, 2 * sizeof(double), cudaMemcpyDeviceToHost, s));
+	if (idepth_out)
+	{
+		// idepth is component z of the packed point record
+		CK(cudaMemcpy2DAsync(idepth_out, sizeof(float), (const char*)W->d_pt + 8, sizeof(float4), sizeof(float), nP, cudaMemcpyDeviceToHost, s));
+	}
+	CK(cudaStreamSynchronize(s));
+	if (sums2_out) { sums2_out[0] = (float)S->h_x[NMAX]; sums2_out[1] = (float)S->h_x[NMAX + 1]; }
+	W->lin_done = false; W->top_done = false;
+	return 0;
+}
+
+extern "C" int dso_b200_ba_points_restore(dso_b200_ctx* ctx)
+{
+	int rc = ba_check_ready(ctx, __func__);
+	if (rc) return rc;
+	CK(cudaSetDevice(ctx->device));
+	BAWorkspace* W = ctx->ba;
+	BASolve* S;
+	if ((rc = solve_state(ctx, &S))) return rc;
+	BA_CHECK(S->capP >= W->P.nP, "call dso_b200_ba_points_backup first");
+	ba_points_backup_kernel<<<(W->P.nP + 255) / 256, 256, 0, ctx->stream>>>(W->P.nP, W->d_pt, S->d_idepth_backup, 1, W->d_pt, W->d_deltaF);
+	ctx->launches++;
+	CK(cudaGetLastError());
+	W->lin_done = false; W->top_done = false;
+	return 0;
+}

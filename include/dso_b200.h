@@ -263,6 +263,52 @@ int dso_b200_ba_accumulate_SC(dso_b200_ctx* ctx, double* H_sc, double* b_sc,
 int dso_b200_ba_step(dso_b200_ctx* ctx, double* H_A, double* b_A, double* H_sc, double* b_sc,
                      double* energy_sum, int* resInA);
 
+/* ---- next rows: solveSystemF tail, resubstituteF_MT, linearised residuals ---------------
+ * The state these calls add lives next to the window's: priors, the marginalisation prior HM/bM, the null-space
+ * projector, res_toZeroF, the per-point *_accLF sums, the solution x and the per-point steps. */
+
+/* CalibHessian::value_minus_value_zero -> EnergyFunctional::cDeltaF (EnergyFunctional.cpp:193). Default zeros. */
+int dso_b200_ba_set_calib_delta(dso_b200_ctx* ctx, const double* value_minus_value_zero4);
+/* EnergyFunctional::cPrior (4), EFFrame::prior / delta_prior / delta (8 per frame; EnergyFunctionalStructs.cpp:55-63),
+ * HM (N*N row-major) and bM (N), N = 8nF+4.  NULL: zeros for cPrior/framePrior/HM/bM; for the two delta arrays NULL keeps
+ * what dso_b200_ba_set_frames derived from the frame states (delta = state - state_zero, delta_prior = state). */
+int dso_b200_ba_set_priors(dso_b200_ctx* ctx, const double* cPrior4, const double* framePrior, const double* frameDeltaPrior,
+                           const double* frameDelta, const double* HM, const double* bM);
+/* lastNullspaces_pose followed by lastNullspaces_scale (n vectors of N doubles).  Builds the projector of
+ * EnergyFunctional::orthogonalize (EnergyFunctional.cpp:741-785; solverModeDelta = setting_solverModeDelta) once, on the
+ * host, and keeps it on the device.  n = 0 removes it. */
+int dso_b200_ba_set_nullspaces(dso_b200_ctx* ctx, const double* nullspaces, int n, double solverModeDelta);
+/* EFResidual::fixLinearizationF (EnergyFunctionalStructs.cpp:89-115) on the active residuals flagged in `which`
+ * (nR bytes, NULL = every active residual): res_toZeroF = resF - J*delta, isLinearized = true.
+ * res_toZeroF_out: nR*8 floats or NULL. */
+int dso_b200_ba_fix_linearization(dso_b200_ctx* ctx, const unsigned char* which, float* res_toZeroF_out);
+/* EnergyFunctional::accumulateLF_MT (EnergyFunctional.cpp:233-254): AccumulatedTopHessianSSE::addPoint<1>
+ * (AccumulatedTopHessian.cpp:39-177) over the linearised active residuals + stitchDoubleMT with usePrior = true
+ * (AccumulatedTopHessian.cpp:314-324). */
+int dso_b200_ba_accumulate_L(dso_b200_ctx* ctx, double* H_L, double* b_L, int* resInL,
+                             float* Hdd_accLF, float* bd_accLF, float* Hcd_accLF4);
+/* EnergyFunctional::solveSystemF (EnergyFunctional.cpp:802-924) after linearize + applyRes: the three accumulate calls,
+ * HFinal_top / bFinal_top, damping, the diagonally scaled LDL^T solve, orthogonalize(&x) when solverMode asks for it
+ * (and null spaces were set), and resubstituteF_MT (EnergyFunctional.cpp:276-330).  solverMode = setting_solverMode
+ * (util/settings.h:35-46; the reference default is 128|2048); the SOLVER_SVD and SOLVER_ORTHOGONALIZE_SYSTEM branches
+ * return DSO_B200_E_ARG.  x_out: N doubles (= lastX; frame steps are -x segments, HCalib->step = -x.head<4>()),
+ * pointStep_out: nP floats (PointHessian::step), both may be NULL (results stay on the device);
+ * HFinal_out/bFinal_out: the system that was solved, for inspection (may be NULL). */
+int dso_b200_ba_solve(dso_b200_ctx* ctx, int iteration, double lambda, int solverMode, double* x_out, float* pointStep_out,
+                      double* HFinal_out, double* bFinal_out);
+/* FullSystem::backupState / doStepFromBackup / loadSateBackup, point half (FullSystemOptimize.cpp:225-345):
+ * backup keeps idepth; step sets idepth = idepth_zero = idepth_backup + stepfacD*step for every point and returns
+ * sums2_out = { sum step^2, sum |idepth_backup| } (FP64 tree sums; the reference adds floats in point order) and,
+ * if idepth_out != NULL, the nP new inverse depths; restore puts the backup back. */
+int dso_b200_ba_points_backup(dso_b200_ctx* ctx);
+int dso_b200_ba_points_step(dso_b200_ctx* ctx, float stepfacD, float* sums2_out, float* idepth_out);
+int dso_b200_ba_points_restore(dso_b200_ctx* ctx);
+/* linearize -> applyRes(true) -> solveSystemF -> backup + step of the points, one synchronisation: the device side of one
+ * iteration of FullSystem::optimize (FullSystemOptimize.cpp:455-520).  The caller applies -x to the frame states and
+ * calls dso_b200_ba_set_frames before the next one. */
+int dso_b200_ba_iteration(dso_b200_ctx* ctx, int iteration, double lambda, int solverMode, float stepfacD,
+                          double* x_out, double* energy_sum, float* step_sums2);
+
 #ifdef __cplusplus
 }
 #endif

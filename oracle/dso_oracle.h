@@ -139,6 +139,8 @@ void dso_oracle_ba_fix_linearization(dso_oracle_ba*, const unsigned char* which,
  * resubstituteF_MT (:276-330).  solverMode: setting_solverMode bits (settings.h:35-46; default 128|2048); the SVD and
  * ORTHOGONALIZE_SYSTEM branches are not restated (returns -1).  x_out: N (= lastX), pointStep_out: nP (PointHessian::step),
  * HFinal_out/bFinal_out: the damped Schur system that is solved (debug; may be NULL). */
+/* the solve step alone (EnergyFunctional.cpp:905-908) on a given N x N system: diagonal scaling + Eigen-style LDL^T */
+void dso_oracle_scaled_ldlt_solve(const double* HFinal, const double* bFinal, int N, double* x);
 int dso_oracle_ba_solve(dso_oracle_ba*, int iteration, double lambda, int solverMode, double solverModeDelta, int MT, int nthreads,
                         double* x_out, float* pointStep_out, double* HFinal_out, double* bFinal_out);
 

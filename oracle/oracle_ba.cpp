@@ -1264,6 +1264,17 @@ static void resubstitute(dso_oracle_ba* B, const std::vector<double>& x)
 	}
 }
 
+// x = SVecI * (SVecI H SVecI).ldlt().solve(SVecI b), SVecI = 1/sqrt(diag(H) + 10), EnergyFunctional.cpp:905-908
+extern "C" void dso_oracle_scaled_ldlt_solve(const double* HF, const double* bF, int N, double* x)
+{
+	std::vector<double> sv(N), Hs((size_t)N * N), bs(N), y(N);
+	for (int i = 0; i < N; i++) sv[i] = 1.0 / std::sqrt(HF[(size_t)i * N + i] + 10);
+	for (int i = 0; i < N; i++) for (int j = 0; j < N; j++) Hs[(size_t)i * N + j] = (sv[i] * HF[(size_t)i * N + j]) * sv[j];
+	for (int i = 0; i < N; i++) bs[i] = sv[i] * bF[i];
+	orc::ldlt_solve_n(Hs.data(), bs.data(), y.data(), N);
+	for (int i = 0; i < N; i++) x[i] = sv[i] * y[i];
+}
+
 // EnergyFunctional::solveSystemF, :802-924.  Restated: the default solver (LDLT on the diagonally scaled system) with
 // SOLVER_USE_GN / SOLVER_FIX_LAMBDA / SOLVER_ORTHOGONALIZE_X(_LATER); the SVD and ORTHOGONALIZE_SYSTEM branches return -1.
 // x_out: 8nF+4 (= lastX; frame steps are -x segments, the calibration step -x.head<4>), pointStep_out: nP (PointHessian::step).
@@ -1295,13 +1306,8 @@ extern "C" int dso_oracle_ba_solve(dso_oracle_ba* B, int iteration, double lambd
 	for (size_t i = 0; i < (size_t)N * N; i++) HF[i] -= HS[i] * isc;
 	if (HFinal_out) memcpy(HFinal_out, HF.data(), sizeof(double) * N * N);
 	if (bFinal_out) memcpy(bFinal_out, bF.data(), sizeof(double) * N);
-	// :905-908
-	std::vector<double> sv(N), Hs((size_t)N * N), bs(N), y(N), x(N);
-	for (int i = 0; i < N; i++) sv[i] = 1.0 / std::sqrt(HF[(size_t)i * N + i] + 10);
-	for (int i = 0; i < N; i++) for (int j = 0; j < N; j++) Hs[(size_t)i * N + j] = (sv[i] * HF[(size_t)i * N + j]) * sv[j];
-	for (int i = 0; i < N; i++) bs[i] = sv[i] * bF[i];
-	orc::ldlt_solve_n(Hs.data(), bs.data(), y.data(), N);
-	for (int i = 0; i < N; i++) x[i] = sv[i] * y[i];
+	std::vector<double> x(N);
+	dso_oracle_scaled_ldlt_solve(HF.data(), bF.data(), N, x.data());                    // :905-908
 	if ((solverMode & SOLVER_ORTHOGONALIZE_X) || (iteration >= 2 && (solverMode & SOLVER_ORTHOGONALIZE_X_LATER)))
 		orthogonalize_vec(B, solverModeDelta, x);                                       // :913-917
 	resubstitute(B, x);                                                                 // :925

@@ -106,6 +106,7 @@ def lib(kind="oracle"):
     sig("dso_oracle_ba_set_priors", [vp, vp, vp, vp, vp, vp, vp])
     sig("dso_oracle_ba_set_nullspaces", [vp, f64p, C.c_int])
     sig("dso_oracle_ba_fix_linearization", [vp, vp, vp])
+    sig("dso_oracle_scaled_ldlt_solve", [f64p, f64p, C.c_int, f64p])
     sig("dso_oracle_ba_solve", [vp, C.c_int, C.c_double, C.c_int, C.c_double, C.c_int, C.c_int, vp, vp, vp, vp], C.c_int)
     _LIBS[kind] = L
     return L
@@ -114,6 +115,15 @@ def lib(kind="oracle"):
 def set_affine_modes(mode_a=1e12, mode_b=1e8, kind="oracle"):
     """setting_affineOptModeA/B (settings.cpp:119-120); process-wide: restore the defaults after use."""
     lib(kind).dso_oracle_set_affine_modes(mode_a, mode_b)
+
+
+def scaled_ldlt_solve(HF, bF):
+    """EnergyFunctional.cpp:905-908 on a given system (oracle build only)"""
+    HF = np.ascontiguousarray(HF, dtype=np.float64)
+    bF = np.ascontiguousarray(bF, dtype=np.float64)
+    x = np.zeros(len(bF))
+    lib("oracle").dso_oracle_scaled_ldlt_solve(HF.reshape(-1), bF, len(bF), x)
+    return x
 
 
 def _ptr_array(arrs):
