@@ -259,12 +259,36 @@ def ba_gpu_bench(pkg, W, dev, steps, warmup, flush_l2, torch, device):
         dev_ms += e0.elapsed_time(e1)
     launches = ctx.launch_count() - l0
     N = 8 * W.nF + 4
+    # next row N1: the whole Gauss-Newton iteration of FullSystem::optimize on the device (linearize, applyRes, the three
+    # accumulates, solve, resubstitute, point step; stepfacD = 0 keeps the synthetic state fixed between repetitions)
+    fP = np.zeros((W.nF, 8))
+    fP[0] = [1e10] * 3 + [1e11] * 3 + [1e14, 1e14]
+    ctx.ba_set_priors(np.full(4, 5e9), fP.reshape(-1))
+    for _ in range(warmup):
+        ctx.ba_iteration(0, 1e-5, stepfacD=0.0)
+    l1 = ctx.launch_count()
+    it_wall, it_ms = 0.0, 0.0
+    for _ in range(steps):
+        flush_l2(stream)
+        ctx.sync()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0 = time.perf_counter()
+        e0.record(stream)
+        ctx.ba_iteration(0, 1e-5, stepfacD=0.0)
+        e1.record(stream)
+        it_wall += time.perf_counter() - t0
+        e1.synchronize()
+        it_ms += e0.elapsed_time(e1)
+    it_launches = ctx.launch_count() - l1
     out = {"metric": "window BA linearize+Schur ms", "unit": "ms", "higher_is_better": False,
            "value": dev_ms / steps, "e2e_ms": wall / steps * 1e3, "steps": steps,
            "workload": "configs[1]: %d key frames, %d active points, %d residuals (%d active), %dx%d system; "
                        "linearizeAll + applyRes + accumulateAF + accumulateSCF per step" % (W.nF, W.nP, W.nR, st["resInA"], N, N),
            "gpu_launches_per_step": launches / steps, "d2h_bytes_per_step": 2 * (N * N + N) * 8 + 16,
-           "algorithmic_bytes_per_step": int(W.nR * 850)}
+           "algorithmic_bytes_per_step": int(W.nR * 850),
+           "gn_iteration": {"what": "linearizeAll + applyRes + solveSystemF (accumulate A/L/SC, 60x60 LDLT, resubstitute) + point step, "
+                                    "dso_b200_ba_iteration", "ms": it_ms / steps, "e2e_ms": it_wall / steps * 1e3,
+                            "gpu_launches_per_step": it_launches / steps, "d2h_bytes_per_step": N * 8 + 48}}
     ctx.close()
     return out
 
@@ -292,6 +316,25 @@ def ba_cpu_bench(W, seconds=4.0):
             step()
             n += 1
         res[name] = {"ms": (time.perf_counter() - t0) / n * 1e3, "threads": nt, "steps": n}
+        if cpu_kind()[0] == "oracle":
+            fP = np.zeros((W.nF, 8))
+            fP[0] = [1e10] * 3 + [1e11] * 3 + [1e14, 1e14]
+            B.set_priors(np.full(4, 5e9), fP.reshape(-1), None, None, None, None)
+
+            def iteration():
+                if mt:
+                    B.linearize_mt(nt)
+                else:
+                    B.L.dso_oracle_ba_linearize(B.p, None, None, None, None, None, None, None)
+                B.L.dso_oracle_ba_apply_res(B.p, None, None)
+                B.solve(0, 1e-5, MT=mt, nthreads=nt)
+            iteration()
+            t0 = time.perf_counter()
+            n = 0
+            while time.perf_counter() - t0 < seconds / 6:
+                iteration()
+                n += 1
+            res[name]["gn_iteration_ms"] = (time.perf_counter() - t0) / n * 1e3
     return res
 
 

@@ -14,6 +14,8 @@
 #include "ba_internal.cuh"
 #include <cmath>
 #include <cstring>
+#include <cstdio>
+#include <cstdlib>
 
 #define NMAX (8 * MAXF + CPARS)
 #define LDH (NMAX + 1)
@@ -33,6 +35,7 @@ struct BASolve
 	int capP, capR;
 	float* d_step; float* d_idepth_backup; double* d_stepBlocks; unsigned char* d_which;
 	double* h_x;                                     // pinned: x (NMAX), step sums (4)
+	long long* d_dbg;                                // DSO_B200_SOLVE_TIMING=1: clock64 stamps of ba_solve_kernel's phases
 	bool priors_set;
 };
 
@@ -53,6 +56,7 @@ static int solve_state(dso_b200_ctx* ctx, BASolve** out)
 		CK(cudaMemset(S->d_HM, 0, (size_t)NMAX * NMAX * sizeof(double)));
 		CK(cudaMemset(S->d_bM, 0, NMAX * sizeof(double)));
 		CK(cudaHostAlloc((void**)&S->h_x, (NMAX + 8) * sizeof(double), cudaHostAllocDefault));
+		if (getenv("DSO_B200_SOLVE_TIMING")) { CK(cudaMalloc(&S->d_dbg, 16 * sizeof(long long))); CK(cudaMemset(S->d_dbg, 0, 16 * sizeof(long long))); }
 		W->S = S;
 	}
 	*out = W->S;
@@ -84,6 +88,7 @@ void ba_solve_destroy(BAWorkspace* W)
 	if (S->capP) { cudaFree(S->d_step); cudaFree(S->d_idepth_backup); cudaFree(S->d_stepBlocks); }
 	if (S->capR) cudaFree(S->d_which);
 	cudaFreeHost(S->h_x);
+	if (S->d_dbg) cudaFree(S->d_dbg);
 	delete S;
 	W->S = nullptr;
 }
@@ -141,140 +146,227 @@ struct SolveArgs
 	const double* HM; const double* bM; const double* delta; const double* priorH; const double* priorD; const float* cDeltaF;
 	const double* P; const double* adHost; const double* adTarget;
 	double* x; float* xAd; double* HF; double* bF;
+	long long* dbg;
 };
 
 // solveSystemF tail (EnergyFunctional.cpp:822-918, default solver branch) + xAd of resubstituteF_MT (:283-293).
 // All products and sums are separate IEEE operations in the reference's order (no contraction), so the only
 // differences to the CPU path are the summation order of the back substitution and of Eigen's GEMV.
-__global__ void __launch_bounds__(256) ba_solve_kernel(SolveArgs a)
+#define SOLVE_NT 1024
+__global__ void __launch_bounds__(SOLVE_NT) ba_solve_kernel(SolveArgs a)
 {
 	__shared__ double A[NMAX * LDH];
 	__shared__ double sv[NMAX], rhs[NMAX], yv[NMAX], xv[NMAX], dg[NMAX], Lk[NMAX], dl[NMAX];
 	__shared__ int ord[NMAX];
 	const int tid = threadIdx.x, N = 8 * a.nF + CPARS;
+#define STAMP(i) do { if (a.dbg && tid == 0) a.dbg[i] = clock64(); } while (0)
+	STAMP(0);
 	// getStitchedDeltaF (:952-958)
 	if (tid < N) dl[tid] = tid < CPARS ? (double)a.cDeltaF[tid] : a.delta[tid];
 	__syncthreads();
+	// HM through shared memory first (coalesced, loads batched): bM_top = bM + HM * delta (:824) sums each row in order
+	constexpr int NQ = (NMAX * NMAX + SOLVE_NT - 1) / SOLVE_NT;
+	const float invN = 1.0f / (float)N;
+#pragma unroll
+	for (int q = 0; q < NQ; q++)
+	{
+		const int e = tid + SOLVE_NT * q;
+		if (e < N * N)
+		{
+			int i = (int)((float)e * invN);
+			i += ((i + 1) * N <= e) ? 1 : 0; i -= (i * N > e) ? 1 : 0;
+			A[i * LDH + (e - i * N)] = a.HM[e];
+		}
+	}
+	__syncthreads();
 	if (tid < N)
 	{
-		// bM_top = bM + HM * delta (:824); bFinal_top = bL_top + bM_top + bA_top - b_sc (:859)
+		// bFinal_top = bL_top + bM_top + bA_top - b_sc (:859)
 		double s = 0.0;
-		for (int j = 0; j < N; j++) s = __dadd_rn(s, __dmul_rn(a.HM[(size_t)tid * N + j], dl[j]));
+		for (int j = 0; j < N; j++) s = __dadd_rn(s, __dmul_rn(A[tid * LDH + j], dl[j]));
 		const double bMtop = __dadd_rn(a.bM[tid], s);
 		const double bl = a.haveL ? a.bL[tid] : __dmul_rn(a.priorH[tid], tid < CPARS ? (double)a.cDeltaF[tid] : a.priorD[tid]);
 		rhs[tid] = __dsub_rn(__dadd_rn(__dadd_rn(bl, bMtop), a.bA[tid]), a.bS[tid]);
 	}
-	// HFinal_top = HL_top + HM + HA_top; diagonal *= (1+lambda); -= H_sc * (1.0f/(1+lambda))  (:857-866)
+	STAMP(1);
+	// HFinal_top = HL_top + HM + HA_top; diagonal *= (1+lambda); -= H_sc * (1.0f/(1+lambda))  (:857-866); every thread
+	// rewrites the entries it staged itself
 	const double damp = __dadd_rn(1.0, a.lambda), isc = __ddiv_rn(1.0, __dadd_rn(1.0, a.lambda));
-	for (int e = tid; e < N * N; e += 256)
+	__syncthreads();
+#pragma unroll
+	for (int q = 0; q < NQ; q++)
 	{
-		const int i = e / N, j = e - i * N;
-		const double hl = a.haveL ? a.HL[e] : (i == j ? a.priorH[i] : 0.0);
-		double v = __dadd_rn(__dadd_rn(hl, a.HM[e]), a.HA[e]);
-		if (i == j) v = __dmul_rn(v, damp);
-		v = __dsub_rn(v, __dmul_rn(a.HS[e], isc));
-		A[i * LDH + j] = v;
-		if (a.HF) a.HF[e] = v;
+		const int e = tid + SOLVE_NT * q;
+		if (e < N * N)
+		{
+			int i = (int)((float)e * invN);
+			i += ((i + 1) * N <= e) ? 1 : 0; i -= (i * N > e) ? 1 : 0;
+			const int j = e - i * N;
+			const double hl = a.haveL ? a.HL[e] : (i == j ? a.priorH[i] : 0.0);
+			double v = __dadd_rn(__dadd_rn(hl, A[i * LDH + j]), a.HA[e]);
+			if (i == j) v = __dmul_rn(v, damp);
+			v = __dsub_rn(v, __dmul_rn(a.HS[e], isc));
+			A[i * LDH + j] = v;
+			if (a.HF) a.HF[e] = v;
+		}
 	}
 	__syncthreads();
+	STAMP(2);
 	if (tid < N)
 	{
 		if (a.bF) a.bF[tid] = rhs[tid];
 		sv[tid] = __ddiv_rn(1.0, sqrt(__dadd_rn(A[tid * LDH + tid], 10.0)));    // :905
 	}
 	__syncthreads();
-	for (int e = tid; e < N * N; e += 256)
+	for (int e = tid; e < N * N; e += SOLVE_NT)
 	{
-		const int i = e / N, j = e - i * N;
+		int i = (int)((float)e * invN);
+		i += ((i + 1) * N <= e) ? 1 : 0; i -= (i * N > e) ? 1 : 0;
+		const int j = e - i * N;
 		A[i * LDH + j] = __dmul_rn(__dmul_rn(sv[i], A[i * LDH + j]), sv[j]);     // SVecI.asDiagonal() * H * SVecI.asDiagonal()
 	}
 	if (tid < N) { rhs[tid] = __dmul_rn(sv[tid], rhs[tid]); ord[tid] = tid; }
 	__syncthreads();
+	STAMP(3);
 	if (tid < N) dg[tid] = fabs(A[tid * LDH + tid]);
 	__syncthreads();
 	// Eigen::LDLT pivot order: at step k the largest |diagonal| among positions k..N-1 (first one on ties) is swapped to
 	// position k; the diagonal entries it looks at are the not-yet-updated ones, so the whole order follows from the
-	// initial diagonal.  Warp 0 runs the N selection steps on (dg, ord).
-	if (tid < 32)
+	// initial diagonal.  Without exact ties that is a descending sort (rank = number of larger entries); with ties the
+	// swaps decide, and warp 0 replays the N selection steps.
+	int tie = 0;
+	if (tid < N)
 	{
-		for (int k = 0; k < N; k++)
+		const double v = dg[tid];
+		int rank = 0;
+		for (int j = 0; j < N; j++) { const double o = dg[j]; rank += (o > v) ? 1 : 0; tie |= (o == v && j != tid) ? 1 : 0; }
+		if (!tie) ord[rank] = tid;
+	}
+	if (__syncthreads_or(tie))
+	{
+		if (tid < N) ord[tid] = tid;
+		__syncthreads();
+		if (tid < 32)
 		{
-			double best = -1.0; int bi = N;
-			for (int i = k + tid; i < N; i += 32) { const double v = dg[i]; if (v > best) { best = v; bi = i; } }
+			for (int k = 0; k < N; k++)
+			{
+				double best = -1.0; int bi = N;
+				for (int i = k + tid; i < N; i += 32) { const double v = dg[i]; if (v > best) { best = v; bi = i; } }
 #pragma unroll
-			for (int o = 16; o > 0; o >>= 1)
-			{
-				const double ob = __shfl_xor_sync(0xffffffffu, best, o);
-				const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
-				if (ob > best || (ob == best && oi < bi)) { best = ob; bi = oi; }
+				for (int o = 16; o > 0; o >>= 1)
+				{
+					const double ob = __shfl_xor_sync(0xffffffffu, best, o);
+					const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+					if (ob > best || (ob == best && oi < bi)) { best = ob; bi = oi; }
+				}
+				if (tid == 0 && bi != k && bi < N)
+				{
+					const double t = dg[k]; dg[k] = dg[bi]; dg[bi] = t;
+					const int u = ord[k]; ord[k] = ord[bi]; ord[bi] = u;
+				}
+				__syncwarp();
 			}
-			if (tid == 0 && bi != k && bi < N)
-			{
-				const double t = dg[k]; dg[k] = dg[bi]; dg[bi] = t;
-				const int u = ord[k]; ord[k] = ord[bi]; ord[bi] = u;
-			}
-			__syncwarp();
 		}
+		__syncthreads();
+	}
+	// LDL^T of the permuted matrix, lower triangle, right-looking: A(i,j) -= (L(i,k) * L(j,k)) * D(k) for k ascending, then
+	// L(i,j) = A(i,j) / D(j) -- the same operations in the same order per entry as the bordered form Eigen uses.  Every
+	// thread keeps its entries (e = tid + SOLVE_NT q of the packed lower triangle) in registers for the whole factorisation;
+	// per pivot only the current column and the next pivot go through shared memory.
+	STAMP(4);
+	constexpr int MAXQ = (NMAX * (NMAX + 1) / 2 + SOLVE_NT - 1) / SOLVE_NT;
+	const int T = N * (N + 1) / 2;
+	double av[MAXQ];
+	int ei[MAXQ], ej[MAXQ];
+#pragma unroll
+	for (int q = 0; q < MAXQ; q++)
+	{
+		const int e = tid + SOLVE_NT * q;
+		int i = (int)((sqrtf(8.f * (float)e + 1.f) - 1.f) * 0.5f);
+		while (i * (i + 1) / 2 > e) i--;
+		while ((i + 1) * (i + 2) / 2 <= e) i++;
+		const int j = e - i * (i + 1) / 2;
+		const bool ok = e < T;
+		ei[q] = ok ? i : -1; ej[q] = ok ? j : -1;
+		av[q] = ok ? A[ord[i] * LDH + ord[j]] : 0.0;
+		if (ok && i == 0) dl[0] = av[q];                 // dl is free again: pivot values D(k)
+		if (ok && j == 0 && i > 0) Lk[i] = av[q];        // column 0, still undivided
 	}
 	__syncthreads();
-#define AT(i, j) A[ord[i] * LDH + ord[j]]
-	// right-looking LDL^T on the permuted matrix, lower triangle: same operations, in the same order per entry, as the
-	// bordered form Eigen uses: A(i,j) -= (L(i,k) * L(j,k)) * D(k) for k ascending, then L(i,j) = A(i,j) / D(j)
+	// per pivot: (1) rows k+1.. divide the staged column by D(k) -- one division per thread, on one code path;
+	// (2) the owners update their entries and stage column k+1 (undivided) and D(k+1) for the next pivot.
+	STAMP(5);
+	double* Lc = Lk; double* Ln = dg;                    // dg (pivot search) is free again
 	for (int k = 0; k < N; k++)
 	{
-		const double d = AT(k, k);
-		if (tid > k && tid < N)
+		const long long c0 = a.dbg ? clock64() : 0;
+		const double d = dl[k];
+		if (tid > k && tid < N) Lc[tid] = (fabs(d) > 0.0) ? __ddiv_rn(Lc[tid], d) : 0.0;
+		__syncthreads();
+		if (a.dbg && tid == 0) a.dbg[10] += clock64() - c0;
+		// a slot is skipped once its row is above the pivot (nearly warp-uniform: consecutive entries share a row)
+#pragma unroll
+		for (int q = 0; q < MAXQ; q++)
 		{
-			const double s = AT(tid, k);
-			const double l = (fabs(d) > 0.0) ? __ddiv_rn(s, d) : 0.0;
-			Lk[tid] = l;
+			if (ei[q] <= k) continue;
+			const double li = Lc[ei[q]];
+			if (ej[q] == k) av[q] = li;
+			else if (ej[q] > k)
+			{
+				const double v = __dsub_rn(av[q], __dmul_rn(__dmul_rn(li, Lc[ej[q]]), d));
+				av[q] = v;
+				if (ej[q] == k + 1) { if (ei[q] == k + 1) dl[k + 1] = v; else Ln[ei[q]] = v; }
+			}
 		}
 		__syncthreads();
-		const int m = N - k - 1;
-		for (int e = tid; e < m * m; e += 256)
-		{
-			const int ii = e / m, jj = e - ii * m;
-			if (jj > ii) continue;
-			const int i = k + 1 + ii, j = k + 1 + jj;
-			AT(i, j) = __dsub_rn(AT(i, j), __dmul_rn(__dmul_rn(Lk[i], Lk[j]), d));
-		}
-		if (tid > k && tid < N) AT(tid, k) = Lk[tid];
-		__syncthreads();
+		double* t = Lc; Lc = Ln; Ln = t;
 	}
+	STAMP(6);
+	// factors back to shared memory in permuted coordinates (the scaled matrix is not needed any more)
+#pragma unroll
+	for (int q = 0; q < MAXQ; q++) if (ei[q] >= 0) A[ei[q] * LDH + ej[q]] = av[q];
 	// solve: permute, L y = b, D, L^T, permute back (:908)
 	if (tid < N) yv[tid] = rhs[ord[tid]];
 	__syncthreads();
 	for (int k = 0; k < N; k++)
 	{
-		if (tid > k && tid < N) yv[tid] = __dsub_rn(yv[tid], __dmul_rn(AT(tid, k), yv[k]));
+		if (tid > k && tid < N) yv[tid] = __dsub_rn(yv[tid], __dmul_rn(A[tid * LDH + k], yv[k]));
 		__syncthreads();
 	}
 	if (tid < N)
 	{
-		const double d = AT(tid, tid);
+		const double d = A[tid * LDH + tid];
 		yv[tid] = (fabs(d) > 2.2250738585072014e-308) ? __ddiv_rn(yv[tid], d) : 0.0;
 	}
 	__syncthreads();
 	for (int k = N - 1; k > 0; k--)
 	{
-		if (tid < k) yv[tid] = __dsub_rn(yv[tid], __dmul_rn(AT(k, tid), yv[k]));
+		if (tid < k) yv[tid] = __dsub_rn(yv[tid], __dmul_rn(A[k * LDH + tid], yv[k]));
 		__syncthreads();
 	}
-#undef AT
+	STAMP(7);
 	if (tid < N) xv[ord[tid]] = __dmul_rn(sv[ord[tid]], yv[tid]);
 	__syncthreads();
 	if (a.orth)
 	{
 		// orthogonalize(&x, 0) (:741-792): x -= NNpiTS * x with the projector prepared by dso_b200_ba_set_nullspaces
+		for (int e = tid; e < N * N; e += SOLVE_NT)               // the factors in A are no longer needed
+		{
+			int i = (int)((float)e * invN);
+			i += ((i + 1) * N <= e) ? 1 : 0; i -= (i * N > e) ? 1 : 0;
+			A[i * LDH + (e - i * N)] = a.P[e];
+		}
+		__syncthreads();
 		double s = 0.0;
-		if (tid < N) for (int j = 0; j < N; j++) s = __dadd_rn(s, __dmul_rn(a.P[(size_t)tid * N + j], xv[j]));
+		if (tid < N) for (int j = 0; j < N; j++) s = __dadd_rn(s, __dmul_rn(A[tid * LDH + j], xv[j]));
 		__syncthreads();
 		if (tid < N) xv[tid] = __dsub_rn(xv[tid], s);
 		__syncthreads();
 	}
+	STAMP(8);
 	if (tid < N) a.x[tid] = xv[tid];
 	// xAd[nF*h + t] = xF_h^T adHostF[h + nF*t] + xF_t^T adTargetF[h + nF*t]  (:289-292), 8-term unrolled reductions
-	for (int e = tid; e < a.nF * a.nF * 8; e += 256)
+	for (int e = tid; e < a.nF * a.nF * 8; e += SOLVE_NT)
 	{
 		const int j = e & 7, ht = e >> 3, h = ht / a.nF, t = ht - h * a.nF;
 		const double* AH = a.adHost + (size_t)(h + a.nF * t) * 64;
@@ -290,6 +382,8 @@ __global__ void __launch_bounds__(256) ba_solve_kernel(SolveArgs a)
 		const float st = fadd(fadd(fadd(pt[0], pt[1]), fadd(pt[2], pt[3])), fadd(fadd(pt[4], pt[5]), fadd(pt[6], pt[7])));
 		a.xAd[e] = fadd(sh, st);
 	}
+	STAMP(9);
+#undef STAMP
 }
 
 // resubstituteFPt, EnergyFunctional.cpp:304-330
@@ -567,7 +661,9 @@ static int enqueue_solve(dso_b200_ctx* ctx, BASolve* S, int iteration, double la
 	a.HM = S->d_HM; a.bM = S->d_bM; a.delta = W->d_delta; a.priorH = W->d_priorH; a.priorD = W->d_priorD; a.cDeltaF = W->d_cDeltaF;
 	a.P = S->d_P; a.adHost = W->d_adHost; a.adTarget = W->d_adTarget;
 	a.x = S->d_x; a.xAd = S->d_xAd; a.HF = debug ? S->d_HF : nullptr; a.bF = debug ? S->d_bF : nullptr;
-	ba_solve_kernel<<<1, 256, 0, ctx->stream>>>(a);
+	a.dbg = S->d_dbg;
+	if (S->d_dbg) CK(cudaMemsetAsync(S->d_dbg, 0, 16 * sizeof(long long), ctx->stream));
+	ba_solve_kernel<<<1, SOLVE_NT, 0, ctx->stream>>>(a);
 	ba_resubstitute_kernel<<<(W->P.nP + 127) / 128, 128, 0, ctx->stream>>>(W->P.nP, W->P.nF, W->d_res_begin, W->d_rtarget, W->d_phost, W->d_isAct,
 	                                                                    W->d_JpJdF, W->d_HcdSum, W->d_bdSumF, W->d_HdiF, S->d_x, S->d_xAd, S->d_step);
 	ctx->launches += 2;
@@ -596,6 +692,13 @@ extern "C" int dso_b200_ba_solve(dso_b200_ctx* ctx, int iteration, double lambda
 	if (bFinal_out) CK(cudaMemcpyAsync(bFinal_out, S->d_bF, N * sizeof(double), cudaMemcpyDeviceToHost, s));
 	CK(cudaStreamSynchronize(s));
 	if (x_out) memcpy(x_out, S->h_x, N * sizeof(double));
+	if (S->d_dbg)
+	{
+		long long t[11];
+		CK(cudaMemcpy(t, S->d_dbg, sizeof(t), cudaMemcpyDeviceToHost));
+		fprintf(stderr, "ba_solve_kernel cycles: stageHM %lld rhs %lld assemble %lld scale %lld pivots %lld load %lld ldlt %lld subst %lld orth %lld xAd %lld | total %lld | ldlt div phase %lld\n",
+		        t[1] - t[0], 0LL, t[2] - t[1], t[3] - t[2], t[4] - t[3], t[5] - t[4], t[6] - t[5], t[7] - t[6], t[8] - t[7], t[9] - t[8], t[9] - t[0], t[10]);
+	}
 	return 0;
 }
 

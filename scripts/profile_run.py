@@ -1,4 +1,4 @@
-"""Short driver for ncu: a few frames of makeImages + trackNewestCoarse and a few BA steps (run on the GPU box)."""
+"""Short driver for ncu: a few frames of makeImages + trackNewestCoarse, a few BA steps and a few full GN iterations (run on the GPU box)."""
 import os
 import sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
@@ -24,5 +24,10 @@ ctx.ba_set_points(W)
 ctx.ba_set_residuals(W)
 for rep in range(4):
     st = ctx.ba_step()
-print("profile_run ok: launches", ctx.launch_count(), "resInA", st["resInA"])
+fP = np.zeros((W.nF, 8))
+fP[0] = [1e10] * 3 + [1e11] * 3 + [1e14, 1e14]
+ctx.ba_set_priors(np.full(4, 5e9), fP.reshape(-1))
+for rep in range(4):
+    it = ctx.ba_iteration(rep, 1e-5, stepfacD=0.0)
+print("profile_run ok: launches", ctx.launch_count(), "resInA", st["resInA"], "energy", it["energy"])
 ctx.close()
