@@ -1,8 +1,8 @@
 """Generates tests/golden/golden_small.npz from the CPU oracle (run from the repo root: python tests/golden/make_golden.py).
 
-The reference ships no fixtures and cannot be built in this image, so these vectors are produced by the
-oracle restatement ("parity unpinned"); they freeze its outputs so that neither the oracle nor the CUDA path can drift
-unnoticed.  Inputs are regenerated from the seed; a checksum of the rendered images guards against generator drift.
+The reference ships no fixtures, so these vectors are produced by the oracle restatement, which
+tests/test_oracle_vs_reference.py pins bit for bit against the reference's own sources (oracle/refbuild); they freeze
+its outputs so that neither the oracle nor the CUDA path can drift unnoticed, also where /root/reference is absent.  Inputs are regenerated from the seed; a checksum of the rendered images guards against generator drift.
 """
 import os
 import sys
