@@ -149,4 +149,85 @@ private:
 	float fx0, fy0, cx0, cy0;
 };
 
+// ---- windowed BA: EnergyFunctional's accumulate / solve members (OptimizationBackend/EnergyFunctional.h:60-160) ----
+struct VecX { std::vector<double> v; int size() const { return (int)v.size(); } double& operator[](int i) { return v[i]; } const double& operator[](int i) const { return v[i]; } };
+struct MatXX { int n; std::vector<double> m; MatXX() : n(0) {} double& operator()(int r, int c) { return m[(size_t)r * n + c]; } int rows() const { return n; } int cols() const { return n; } };
+
+// Flat description of the optimisation window, gathered by the caller from frameHessians / pointHessians / residuals
+// in EnergyFunctional::makeIDX order (EnergyFunctional.cpp:928-948): frames by idx, points by host frame, residuals by point.
+struct WindowArrays
+{
+	int nF, nP, nR;
+	const int* frame_slots; const float* frameEnergyTH;                           // per frame
+	const double* evalPT12; const double* state10; const double* state_zero10; const float* ab_exposure;
+	const float *u, *v, *idepth_scaled, *idepth_zero_scaled, *color8, *weights8, *priorF, *deltaF; const int* host;   // per point
+	const int *res_point, *res_target, *res_state; const double* res_energy; const unsigned char *res_isLinearized, *res_isActive;   // per residual
+};
+
+class EnergyFunctional
+{
+public:
+	explicit EnergyFunctional(DeviceContext* d) : nFrames(0), nPoints(0), nResiduals(0), resInA(0), resInL(0), currentLambda(0), dev(d) {}
+
+	// insertFrame / insertPoint / insertResidual / makeIDX (EnergyFunctional.cpp:432-520, 928-948) collapse into one upload
+	void setWindow(const WindowArrays& W, CalibHessian* HCalib)
+	{
+		nFrames = W.nF; nPoints = W.nP; nResiduals = W.nR;
+		DSO_B200_CHECK(dso_b200_ba_set_window(dev->ctx, W.nF, W.frame_slots, dev->w, dev->h, HCalib->fxl(), HCalib->fyl(), HCalib->cxl(), HCalib->cyl(), W.frameEnergyTH));
+		setPrecalcValues(W);
+		DSO_B200_CHECK(dso_b200_ba_set_points(dev->ctx, W.nP, W.u, W.v, W.idepth_scaled, W.idepth_zero_scaled, W.color8, W.weights8, W.host, W.priorF, W.deltaF));
+		DSO_B200_CHECK(dso_b200_ba_set_residuals(dev->ctx, W.nR, W.res_point, W.res_target, W.res_state, W.res_energy, W.res_isLinearized, W.res_isActive));
+	}
+	// FullSystem::setPrecalcValues (FullSystemOptimize.cpp:413-422): FrameFramePrecalc::set for all pairs + ef->setDeltaF
+	void setPrecalcValues(const WindowArrays& W)
+	{
+		DSO_B200_CHECK(dso_b200_ba_set_frames(dev->ctx, W.evalPT12, W.state10, W.state_zero10, W.ab_exposure, 0, 0, 0));
+	}
+	// FullSystem::linearizeAll(fixLinearization) (FullSystemOptimize.cpp:146-220): energy of the new linearisation;
+	// fixLinearization = true also applies it (applyRes_Reductor(true, ...))
+	double linearizeAll(bool fixLinearization)
+	{
+		double e = 0;
+		DSO_B200_CHECK(dso_b200_ba_linearize(dev->ctx, 0, 0, 0, 0, 0, 0, &e));
+		if (fixLinearization) applyRes();
+		return e;
+	}
+	void applyRes() { DSO_B200_CHECK(dso_b200_ba_apply_res(dev->ctx, 0, 0)); }   // FullSystem::applyRes_Reductor(true, ...)
+
+	// void accumulateAF_MT(MatXX &H, VecX &b, bool MT)   EnergyFunctional.cpp:209 (MT has no meaning on the device)
+	void accumulateAF_MT(MatXX& H, VecX& b, bool MT) { (void)MT; size(H, b); DSO_B200_CHECK(dso_b200_ba_accumulate_A(dev->ctx, H.m.data(), b.v.data(), &resInA, 0, 0, 0)); }
+	// void accumulateLF_MT(MatXX &H, VecX &b, bool MT)   EnergyFunctional.cpp:233
+	void accumulateLF_MT(MatXX& H, VecX& b, bool MT) { (void)MT; size(H, b); DSO_B200_CHECK(dso_b200_ba_accumulate_L(dev->ctx, H.m.data(), b.v.data(), &resInL, 0, 0, 0)); }
+	// void accumulateSCF_MT(MatXX &H, VecX &b, bool MT)  EnergyFunctional.cpp:257
+	void accumulateSCF_MT(MatXX& H, VecX& b, bool MT) { (void)MT; size(H, b); DSO_B200_CHECK(dso_b200_ba_accumulate_SC(dev->ctx, H.m.data(), b.v.data(), 0, 0, 0)); }
+
+	// priors / marginalisation prior / null spaces, set when they change (insertFrame, marginalizeFrame, FullSystem::optimize)
+	void setPriors(const double* cPrior4, const double* framePrior8, const MatXX& HM, const VecX& bM)
+	{ DSO_B200_CHECK(dso_b200_ba_set_priors(dev->ctx, cPrior4, framePrior8, 0, 0, HM.m.data(), bM.v.data())); }
+	void setNullspaces(const double* ns, int n, double setting_solverModeDelta) { DSO_B200_CHECK(dso_b200_ba_set_nullspaces(dev->ctx, ns, n, setting_solverModeDelta)); }
+
+	// void solveSystemF(int iteration, double lambda, CalibHessian* HCalib)   EnergyFunctional.cpp:802; lastX as in :921,
+	// frame / calibration steps are -x segments (:281-288); point steps stay on the device (doStepFromBackupPoints)
+	void solveSystemF(int iteration, double lambda, int setting_solverMode, const double* value_minus_value_zero4)
+	{
+		DSO_B200_CHECK(dso_b200_ba_set_calib_delta(dev->ctx, value_minus_value_zero4));
+		lastX.v.assign(8 * nFrames + 4, 0.0);
+		currentLambda = lambda;
+		DSO_B200_CHECK(dso_b200_ba_solve(dev->ctx, iteration, lambda, setting_solverMode, lastX.v.data(), 0, 0, 0));
+		currentLambda = 0;
+	}
+	// point loops of FullSystem::backupState / doStepFromBackup / loadSateBackup (FullSystemOptimize.cpp:225-345)
+	void backupStatePoints() { DSO_B200_CHECK(dso_b200_ba_points_backup(dev->ctx)); }
+	void doStepFromBackupPoints(float stepfacD, float& sumID, float& sumNID) { float s[2]; DSO_B200_CHECK(dso_b200_ba_points_step(dev->ctx, stepfacD, s, 0)); sumID = s[0]; sumNID = s[1]; }
+	void loadStateBackupPoints() { DSO_B200_CHECK(dso_b200_ba_points_restore(dev->ctx)); }
+
+	int nFrames, nPoints, nResiduals;
+	int resInA, resInL;
+	VecX lastX;
+	double currentLambda;
+private:
+	void size(MatXX& H, VecX& b) const { const int N = 8 * nFrames + 4; H.n = N; H.m.assign((size_t)N * N, 0.0); b.v.assign(N, 0.0); }
+	DeviceContext* dev;
+};
+
 }   // namespace dso
