@@ -52,6 +52,7 @@ SIGNATURES = {
     "dso_b200_host_free": (None, [vp]),
     "dso_b200_launch_count": (C.c_longlong, [vp]),
     "dso_b200_make_images": (C.c_int, [vp, C.c_int, vp, C.c_int, C.c_int, C.c_int, vp, C.POINTER(vp), C.POINTER(vp)]),
+    "dso_b200_make_images_async": (C.c_int, [vp, C.c_int, vp, C.c_int, C.c_int, C.c_int]),
     "dso_b200_make_images_dev": (C.c_int, [vp, C.c_int, vp, C.c_int, C.c_int, C.c_int, vp]),
     "dso_b200_tracker_set_ref": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float,
                                            i32p, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), C.POINTER(vp),
@@ -246,6 +247,12 @@ class Context:
                                                    new_exposure, coarsest, _opt(mr), None if opts is None else C.byref(opts),
                                                    C.byref(res)))
         return res
+
+    def make_images_async(self, slot, color_ptr, w, h, levels):
+        """color_ptr: host address (pinned) or numpy array that the caller keeps alive until the slot is consumed"""
+        if isinstance(color_ptr, np.ndarray):
+            color_ptr = color_ptr.ctypes.data
+        self._check(self.L.dso_b200_make_images_async(self.h, slot, color_ptr, w, h, levels))
 
     def track_batched(self, trk, slot, poses12, a, b, coarsest, new_exposure=1.0, opts=None):
         poses12 = np.ascontiguousarray(poses12, dtype=np.float64).reshape(-1, 12)

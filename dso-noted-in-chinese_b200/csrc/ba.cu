@@ -67,6 +67,8 @@ int ba_create(dso_b200_ctx* ctx)
 	CK(cudaMemset(W->d_priorD, 0, N * sizeof(double)));
 	CK(cudaMemset(W->d_delta, 0, N * sizeof(double)));
 	W->nLin = 0; W->S = nullptr;
+	memset(&W->g_step, 0, sizeof(W->g_step)); memset(W->g_iter, 0, sizeof(W->g_iter));
+	W->use_graphs = !getenv("DSO_B200_NO_GRAPH");
 	ctx->ba = W;
 	return 0;
 }
@@ -91,11 +93,22 @@ static void free_res(BAWorkspace* W)
 	W->capR = 0; W->capChunks = 0;
 }
 
+void ba_graphs_invalidate(BAWorkspace* W)
+{
+	BAGraph* gs[3] = { &W->g_step, &W->g_iter[0], &W->g_iter[1] };
+	for (BAGraph* g : gs)
+	{
+		if (g->exec) cudaGraphExecDestroy(g->exec);
+		g->exec = nullptr; g->valid = false;
+	}
+}
+
 void ba_destroy(dso_b200_ctx* ctx)
 {
 	BAWorkspace* W = ctx->ba;
 	if (!W) return;
 	ba_solve_destroy(W);
+	ba_graphs_invalidate(W);
 	free_points(W); free_res(W);
 	cudaFree(W->d_adHTdeltaF); cudaFree(W->d_cDeltaF); cudaFree(W->d_HL); cudaFree(W->d_bL); cudaFree(W->d_priorH); cudaFree(W->d_priorD); cudaFree(W->d_delta);
 	cudaFree(W->d_precalc); cudaFree(W->d_adHost); cudaFree(W->d_adTarget); cudaFree(W->d_pair_chunk_begin); cudaFree(W->d_host_pc_begin);
@@ -851,6 +864,7 @@ extern "C" int dso_b200_ba_set_window(dso_b200_ctx* ctx, int nF, const int* fram
 		ARG_CHECK(frame_slots[i] >= 0 && frame_slots[i] < ctx->n_slots && ctx->slots[frame_slots[i]].valid, "frame slot empty");
 		ARG_CHECK(ctx->slots[frame_slots[i]].w == w && ctx->slots[frame_slots[i]].h == h, "frame size mismatch");
 		P.img[i] = ctx->slots[frame_slots[i]].pyr[0];
+		if (frame_slot_wait(ctx, frame_slots[i])) return DSO_B200_E_CUDA;
 		P.frameEnergyTH[i] = frameEnergyTH[i];
 	}
 	P.nF = nF; P.w = w; P.h = h;
@@ -859,6 +873,7 @@ extern "C" int dso_b200_ba_set_window(dso_b200_ctx* ctx, int nF, const int* fram
 	P.fxi = 1.0f / fx; P.fyi = 1.0f / fy;
 	P.wM3G = (float)(w - 3); P.hM3G = (float)(h - 3);
 	W->window_set = true; W->glue_set = false; W->res_set = false; W->lin_done = false; W->top_done = false;
+	ba_graphs_invalidate(W);
 	return 0;
 }
 
@@ -867,6 +882,7 @@ extern "C" int dso_b200_ba_set_affine_modes(dso_b200_ctx* ctx, float modeA, floa
 	ARG_CHECK(ctx && ctx->ba, "null argument");
 	ctx->ba->P.fixA = modeA < 0; ctx->ba->P.fixB = modeB < 0;
 	ctx->ba->lin_done = false; ctx->ba->top_done = false;
+	ba_graphs_invalidate(ctx->ba);
 	return 0;
 }
 
@@ -964,6 +980,7 @@ extern "C" int dso_b200_ba_set_points(dso_b200_ctx* ctx, int nP, const float* u,
 	W->h_phost.assign(host, host + nP);
 	W->P.nP = nP;
 	W->points_set = true; W->res_set = false; W->lin_done = false; W->top_done = false;
+	ba_graphs_invalidate(W);
 	return 0;
 }
 
@@ -1069,6 +1086,7 @@ extern "C" int dso_b200_ba_set_residuals(dso_b200_ctx* ctx, int nR, const int* p
 	CK(cudaStreamSynchronize(s));
 	W->P.nR = nR;
 	W->res_set = true; W->lin_done = false; W->top_done = false;
+	ba_graphs_invalidate(W);
 	return 0;
 }
 
@@ -1410,18 +1428,24 @@ extern "C" int dso_b200_ba_step(dso_b200_ctx* ctx, double* H_A, double* b_A, dou
 	ARG_CHECK(H_A && b_A && H_sc && b_sc, "null output");
 	CK(cudaSetDevice(ctx->device));
 	BAWorkspace* W = ctx->ba;
-	if ((rc = ba_enqueue_linearize(ctx))) return rc;
-	if ((rc = ba_enqueue_apply(ctx))) return rc;
-	if ((rc = ba_enqueue_top(ctx, 0))) return rc;
-	if ((rc = ba_enqueue_schur(ctx))) return rc;
 	const int N = 8 * W->P.nF + CPARS;
 	const size_t NN = (size_t)N * N;
 	cudaStream_t s = ctx->stream;
-	CK(cudaMemcpyAsync(W->h_out, W->d_HA, NN * sizeof(double), cudaMemcpyDeviceToHost, s));
-	CK(cudaMemcpyAsync(W->h_out + NN, W->d_bA, N * sizeof(double), cudaMemcpyDeviceToHost, s));
-	CK(cudaMemcpyAsync(W->h_out + NN + N, W->d_HS, NN * sizeof(double), cudaMemcpyDeviceToHost, s));
-	CK(cudaMemcpyAsync(W->h_out + 2 * NN + N, W->d_bS, N * sizeof(double), cudaMemcpyDeviceToHost, s));
-	CK(cudaMemcpyAsync(W->h_out + 2 * NN + 2 * N, W->d_scalars, 2 * sizeof(double), cudaMemcpyDeviceToHost, s));
+	rc = ba_run_graphed(ctx, W->g_step, 0ull, [&]() -> int {
+		int r;
+		if ((r = ba_enqueue_linearize(ctx))) return r;
+		if ((r = ba_enqueue_apply(ctx))) return r;
+		if ((r = ba_enqueue_top(ctx, 0))) return r;
+		if ((r = ba_enqueue_schur(ctx))) return r;
+		CK(cudaMemcpyAsync(W->h_out, W->d_HA, NN * sizeof(double), cudaMemcpyDeviceToHost, s));
+		CK(cudaMemcpyAsync(W->h_out + NN, W->d_bA, N * sizeof(double), cudaMemcpyDeviceToHost, s));
+		CK(cudaMemcpyAsync(W->h_out + NN + N, W->d_HS, NN * sizeof(double), cudaMemcpyDeviceToHost, s));
+		CK(cudaMemcpyAsync(W->h_out + 2 * NN + N, W->d_bS, N * sizeof(double), cudaMemcpyDeviceToHost, s));
+		CK(cudaMemcpyAsync(W->h_out + 2 * NN + 2 * N, W->d_scalars, 2 * sizeof(double), cudaMemcpyDeviceToHost, s));
+		return 0;
+	});
+	if (rc) return rc;
+	W->top_done = true;
 	CK(cudaStreamSynchronize(s));
 	memcpy(H_A, W->h_out, NN * sizeof(double));
 	memcpy(b_A, W->h_out + NN, N * sizeof(double));

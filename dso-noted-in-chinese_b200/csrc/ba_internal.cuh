@@ -53,6 +53,14 @@ struct BALinArgs
 
 struct BASolve;    // ba_solve.cu
 
+// A fixed launch sequence captured once as a CUDA graph and replayed (dso_b200_ba_step, dso_b200_ba_iteration): the
+// kernels are 3-15 us each, so launch gaps would otherwise be ~40 % of the step.  Invalidated by every call that
+// changes a kernel argument (window, points, residuals, affine modes); `key` carries the by-value scalars.
+struct BAGraph
+{
+	cudaGraphExec_t exec; bool valid; unsigned long long key; long long nlaunch;
+};
+
 struct BAWorkspace
 {
 	BAParams P;
@@ -87,7 +95,39 @@ struct BAWorkspace
 	double* d_priorH; double* d_priorD; double* d_delta;                         // [8nF+4]: prior, delta_prior, delta (entries 0..3 of the deltas: cDeltaF)
 	int nLin;                                                                    // linearised residuals (-1: unknown)
 	BASolve* S;
+	BAGraph g_step, g_iter[2];
+	bool use_graphs;                                                             // DSO_B200_NO_GRAPH=1 turns them off
 };
+
+void ba_graphs_invalidate(BAWorkspace* W);
+
+// Runs `enqueue` (kernel launches and async copies on ctx->stream only) through graph slot g.
+template <class F>
+static int ba_run_graphed(dso_b200_ctx* ctx, BAGraph& g, unsigned long long key, F enqueue)
+{
+	BAWorkspace* W = ctx->ba;
+	if (!W->use_graphs) return enqueue();
+	if (!g.valid || g.key != key)
+	{
+		if (g.exec) { cudaGraphExecDestroy(g.exec); g.exec = nullptr; }
+		g.valid = false;
+		const long long l0 = ctx->launches;
+		CK(cudaStreamBeginCapture(ctx->stream, cudaStreamCaptureModeThreadLocal));
+		const int rc = enqueue();
+		cudaGraph_t graph = nullptr;
+		const cudaError_t e = cudaStreamEndCapture(ctx->stream, &graph);
+		g.nlaunch = ctx->launches - l0;
+		ctx->launches = l0;
+		if (rc) { if (graph) cudaGraphDestroy(graph); return rc; }
+		CK(e);
+		CK(cudaGraphInstantiate(&g.exec, graph, 0));
+		CK(cudaGraphDestroy(graph));
+		g.valid = true; g.key = key;
+	}
+	CK(cudaGraphLaunch(g.exec, ctx->stream));
+	ctx->launches += g.nlaunch;
+	return 0;
+}
 
 int ba_check_ready(dso_b200_ctx* ctx, const char* fn);
 int ba_enqueue_linearize(dso_b200_ctx* ctx);

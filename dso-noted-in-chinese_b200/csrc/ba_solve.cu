@@ -612,6 +612,7 @@ extern "C" int dso_b200_ba_fix_linearization(dso_b200_ctx* ctx, const unsigned c
 	if (res_toZeroF_out) CK(cudaMemcpyAsync(res_toZeroF_out, W->d_resToZero, (size_t)nR * 8 * sizeof(float), cudaMemcpyDeviceToHost, s));
 	CK(cudaStreamSynchronize(s));
 	W->nLin = -1;                  // some residuals may now be linearised: accumulateLF has work
+	ba_graphs_invalidate(W);
 	W->top_done = false;
 	return 0;
 }
@@ -717,16 +718,29 @@ extern "C" int dso_b200_ba_iteration(dso_b200_ctx* ctx, int iteration, double la
 	if ((rc = ensure_point_buffers(ctx, S))) return rc;
 	cudaStream_t s = ctx->stream;
 	const int nP = W->P.nP, nb = (nP + 255) / 256, N = 8 * W->P.nF + CPARS;
-	if ((rc = ba_enqueue_linearize(ctx))) return rc;
-	if ((rc = ba_enqueue_apply(ctx))) return rc;
-	if ((rc = enqueue_solve(ctx, S, iteration, lambda, solverMode, false))) return rc;
-	ba_points_backup_kernel<<<(nP + 255) / 256, 256, 0, s>>>(nP, W->d_pt, S->d_idepth_backup, 0, nullptr, nullptr);
-	ba_points_step_kernel<<<nb, 256, 0, s>>>(nP, stepfacD, S->d_step, S->d_idepth_backup, W->d_pt, W->d_deltaF, S->d_stepBlocks);
-	ba_points_step_final_kernel<<<1, 32, 0, s>>>(nb, S->d_stepBlocks, W->d_scalars + 4);
-	ctx->launches += 3;
-	CK(cudaGetLastError());
-	CK(cudaMemcpyAsync(S->h_x, S->d_x, N * sizeof(double), cudaMemcpyDeviceToHost, s));
-	CK(cudaMemcpyAsync(S->h_x + NMAX, W->d_scalars, 6 * sizeof(double), cudaMemcpyDeviceToHost, s));
+	// by-value kernel arguments of the captured sequence: orthogonalisation on/off, lambda, stepfacD, solver mode, L path
+	const int orth = ((solverMode & SOLVER_ORTHOGONALIZE_X) || (iteration >= 2 && (solverMode & SOLVER_ORTHOGONALIZE_X_LATER))) ? 1 : 0;
+	float lf = (float)lambda;
+	unsigned int lbits, sbits;
+	memcpy(&lbits, &lf, 4); memcpy(&sbits, &stepfacD, 4);
+	const unsigned long long key = ((unsigned long long)lbits << 32) ^ ((unsigned long long)sbits << 1) ^ ((unsigned long long)(solverMode & 0xfff) << 20)
+	                               ^ (unsigned long long)(W->nLin != 0) ^ ((unsigned long long)(S->haveP ? 1 : 0) << 19) ^ ((unsigned long long)(S->d_dbg ? 1 : 0) << 18);
+	rc = ba_run_graphed(ctx, W->g_iter[orth], key, [&]() -> int {
+		int r;
+		if ((r = ba_enqueue_linearize(ctx))) return r;
+		if ((r = ba_enqueue_apply(ctx))) return r;
+		if ((r = enqueue_solve(ctx, S, orth ? 2 : 0, lambda, solverMode, false))) return r;
+		ba_points_backup_kernel<<<(nP + 255) / 256, 256, 0, s>>>(nP, W->d_pt, S->d_idepth_backup, 0, nullptr, nullptr);
+		ba_points_step_kernel<<<nb, 256, 0, s>>>(nP, stepfacD, S->d_step, S->d_idepth_backup, W->d_pt, W->d_deltaF, S->d_stepBlocks);
+		ba_points_step_final_kernel<<<1, 32, 0, s>>>(nb, S->d_stepBlocks, W->d_scalars + 4);
+		ctx->launches += 3;
+		CK(cudaGetLastError());
+		CK(cudaMemcpyAsync(S->h_x, S->d_x, N * sizeof(double), cudaMemcpyDeviceToHost, s));
+		CK(cudaMemcpyAsync(S->h_x + NMAX, W->d_scalars, 6 * sizeof(double), cudaMemcpyDeviceToHost, s));
+		return 0;
+	});
+	if (rc) return rc;
+	W->top_done = true;
 	CK(cudaStreamSynchronize(s));
 	if (x_out) memcpy(x_out, S->h_x, N * sizeof(double));
 	if (energy_sum) *energy_sum = S->h_x[NMAX];

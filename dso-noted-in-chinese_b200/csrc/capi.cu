@@ -47,6 +47,7 @@ extern "C" int dso_b200_create(int device, int max_w, int max_h, int n_frame_slo
 	ctx->sm_count = prop.multiProcessorCount;
 	ctx->max_w = max_w; ctx->max_h = max_h; ctx->n_slots = n_frame_slots;
 	CK(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+	CK(cudaStreamCreateWithFlags(&ctx->upload_stream, cudaStreamNonBlocking));
 
 	// frame slots: per level a float4 image and (for l >= 1) a float intensity plane
 	ctx->slots = new FrameSlot[n_frame_slots];
@@ -62,6 +63,7 @@ extern "C" int dso_b200_create(int device, int max_w, int max_h, int n_frame_slo
 			if (l >= 1) bytes += align_up(n * sizeof(float), 256);
 		}
 		CK(cudaMalloc(&F.base, bytes));
+		CK(cudaEventCreateWithFlags(&F.ready, cudaEventDisableTiming));
 		char* p = (char*)F.base;
 		for (int l = 0; l < MAXL; l++)
 		{
@@ -73,6 +75,7 @@ extern "C" int dso_b200_create(int device, int max_w, int max_h, int n_frame_slo
 	// staging: input image, host-layout outputs, LUT
 	size_t npx0 = (size_t)max_w * max_h;
 	CK(cudaMalloc(&ctx->d_color, align_up(npx0 * sizeof(float), 256)));
+	CK(cudaMalloc(&ctx->d_color_up, align_up(npx0 * sizeof(float), 256)));
 	for (int l = 0; l < MAXL; l++)
 	{
 		size_t n = (size_t)(max_w >> l) * (max_h >> l);
@@ -98,8 +101,12 @@ extern "C" int dso_b200_create(int device, int max_w, int max_h, int n_frame_slo
 		CK(cudaHostAlloc((void**)&T.h_sums, S_COUNT * sizeof(float), cudaHostAllocDefault));
 		CK(cudaMalloc(&T.d_track_in, 4096 * 2));
 		CK(cudaMalloc(&T.d_track_out, sizeof(dso_b200_track_result) * DSO_B200_MAX_HYP));
-		CK(cudaHostAlloc(&T.h_track_in, 4096 * 2, cudaHostAllocDefault));
-		CK(cudaHostAlloc(&T.h_track_out, sizeof(dso_b200_track_result) * DSO_B200_MAX_HYP, cudaHostAllocDefault));
+		CK(cudaHostAlloc(&T.h_track_in, TRACK_IN_RING * TRACK_IN_BLOCK, cudaHostAllocMapped));
+		CK(cudaHostAlloc(&T.h_track_out, sizeof(dso_b200_track_result) * DSO_B200_MAX_HYP, cudaHostAllocMapped));
+		CK(cudaHostAlloc((void**)&T.h_flags, sizeof(unsigned int) * DSO_B200_MAX_HYP, cudaHostAllocMapped));
+		memset(T.h_flags, 0, sizeof(unsigned int) * DSO_B200_MAX_HYP);
+		T.seq = 0; T.last_in = T.d_track_in;
+		CK(cudaMemset(T.d_track_in, 0, 4096 * 2));
 		T.last_lvl = -1;
 	}
 	int rc = ba_create(ctx);
@@ -112,11 +119,13 @@ extern "C" void dso_b200_destroy(dso_b200_ctx* ctx)
 {
 	if (!ctx) return;
 	cudaSetDevice(ctx->device);
+	cudaStreamSynchronize(ctx->upload_stream);
 	cudaStreamSynchronize(ctx->stream);
 	ba_destroy(ctx);
-	for (int s = 0; s < ctx->n_slots; s++) cudaFree(ctx->slots[s].base);
+	for (int s = 0; s < ctx->n_slots; s++) { cudaFree(ctx->slots[s].base); cudaEventDestroy(ctx->slots[s].ready); }
 	delete[] ctx->slots;
-	cudaFree(ctx->d_color);
+	cudaFree(ctx->d_color); cudaFree(ctx->d_color_up);
+	cudaStreamDestroy(ctx->upload_stream);
 	for (int l = 0; l < MAXL; l++) { cudaFree(ctx->d_aos[l]); cudaFree(ctx->d_abs[l]); }
 	cudaFree(ctx->d_Blut);
 	if (ctx->d_phase_cycles) cudaFree(ctx->d_phase_cycles);
@@ -125,7 +134,7 @@ extern "C" void dso_b200_destroy(dso_b200_ctx* ctx)
 		TrackerSlot& T = ctx->trk[t];
 		cudaFree(T.base); cudaFree(T.d_sums); cudaFree(T.d_partials); cudaFree(T.d_ticket);
 		cudaFreeHost(T.h_sums); cudaFree(T.d_track_in); cudaFree(T.d_track_out);
-		cudaFreeHost(T.h_track_in); cudaFreeHost(T.h_track_out);
+		cudaFreeHost(T.h_track_in); cudaFreeHost(T.h_track_out); cudaFreeHost(T.h_flags);
 	}
 	cudaStreamDestroy(ctx->stream);
 	delete ctx;
@@ -135,6 +144,7 @@ extern "C" void* dso_b200_stream(dso_b200_ctx* ctx) { return ctx ? (void*)ctx->s
 extern "C" int dso_b200_sync(dso_b200_ctx* ctx)
 {
 	ARG_CHECK(ctx, "null context");
+	CK(cudaStreamSynchronize(ctx->upload_stream));
 	CK(cudaStreamSynchronize(ctx->stream));
 	return 0;
 }
@@ -178,6 +188,31 @@ extern "C" int dso_b200_make_images_dev(dso_b200_ctx* ctx, int frame_slot, const
 	rc = upload_lut(ctx, B_lut_host, &d_lut);
 	if (rc) return rc;
 	return pyramid_build(ctx, ctx->slots[frame_slot], color_dev, w, h, levels, d_lut, false);
+}
+
+int frame_slot_wait(dso_b200_ctx* ctx, int frame_slot)
+{
+	FrameSlot& F = ctx->slots[frame_slot];
+	if (F.pending)
+	{
+		CK(cudaStreamWaitEvent(ctx->stream, F.ready, 0));
+		F.pending = false;
+	}
+	return 0;
+}
+
+extern "C" int dso_b200_make_images_async(dso_b200_ctx* ctx, int frame_slot, const float* color_host, int w, int h, int levels)
+{
+	int rc = check_image_args(ctx, frame_slot, color_host, w, h, levels);
+	if (rc) return rc;
+	CK(cudaSetDevice(ctx->device));
+	FrameSlot& F = ctx->slots[frame_slot];
+	CK(cudaMemcpyAsync(ctx->d_color_up, color_host, (size_t)w * h * sizeof(float), cudaMemcpyHostToDevice, ctx->upload_stream));
+	rc = pyramid_build_on(ctx, ctx->upload_stream, F, ctx->d_color_up, w, h, levels, nullptr, false);
+	if (rc) return rc;
+	CK(cudaEventRecord(F.ready, ctx->upload_stream));
+	F.pending = true;
+	return 0;
 }
 
 extern "C" int dso_b200_make_images(dso_b200_ctx* ctx, int frame_slot, const float* color_host, int w, int h, int levels,

@@ -46,6 +46,8 @@ struct FrameSlot
 {
 	int w, h, levels;
 	bool valid;
+	bool pending;              // written by the upload stream, not yet waited for by the compute stream
+	cudaEvent_t ready;
 	void* base;
 	float4* pyr[MAXL];
 	float* inten[MAXL];
@@ -74,9 +76,14 @@ struct TrackerSlot
 	// batched tracker workspace
 	void* d_track_in;
 	void* d_track_out;
-	void* h_track_in;
-	void* h_track_out;
+	void* h_track_in;           // mapped pinned ring of TRACK_IN_RING input blocks, read by the kernel over PCIe (no H2D copy node)
+	void* h_track_out;          // mapped pinned: the kernel writes its results here, then h_flags[hyp] = seq
+	unsigned int* h_flags;      // mapped pinned, one word per hypothesis
+	unsigned int seq;           // sequence number of the last enqueued tracking call with host-visible results (0: none pending)
+	const void* last_in;        // input block of the last call (dso_b200_track_batched_async with pose NULL re-runs it)
 };
+#define TRACK_IN_RING 4
+#define TRACK_IN_BLOCK 8192
 
 struct BAWorkspace;
 
@@ -93,6 +100,8 @@ struct dso_b200_ctx
 	float* d_abs[MAXL];
 	float* d_Blut;
 	float* d_color;            // landing zone of the uploaded input image
+	cudaStream_t upload_stream;   // dso_b200_make_images_async: H2D + pyramid of the next frame while the current one is tracked
+	float* d_color_up;            // its own landing zone
 	TrackerSlot trk[2];
 	BAWorkspace* ba;
 	long long launches;
@@ -113,6 +122,9 @@ enum
 	S_COUNT = 52
 };
 
+int pyramid_build_on(dso_b200_ctx* ctx, cudaStream_t stream, FrameSlot& fs, const float* color_dev, int w, int h, int levels,
+                     const float* d_Blut, bool host_layout);
+int frame_slot_wait(dso_b200_ctx* ctx, int frame_slot);   // makes ctx->stream wait for a pending asynchronous upload of the slot
 int pyramid_build(dso_b200_ctx* ctx, FrameSlot& fs, const float* color_dev, int w, int h, int levels,
                   const float* d_Blut, bool host_layout);
 int ba_create(dso_b200_ctx* ctx);

@@ -186,6 +186,12 @@ __global__ void __launch_bounds__(256) pyr_gradient_kernel(GradArgs a)
 int pyramid_build(dso_b200_ctx* ctx, FrameSlot& fs, const float* color_dev, int w, int h, int levels,
                   const float* d_Blut, bool host_layout)
 {
+	return pyramid_build_on(ctx, ctx->stream, fs, color_dev, w, h, levels, d_Blut, host_layout);
+}
+
+int pyramid_build_on(dso_b200_ctx* ctx, cudaStream_t stream, FrameSlot& fs, const float* color_dev, int w, int h, int levels,
+                     const float* d_Blut, bool host_layout)
+{
 	fs.w = w; fs.h = h; fs.levels = levels;
 	IntensityArgs ia;
 	ia.src = color_dev; ia.w = w; ia.h = h; ia.levels = levels;
@@ -193,7 +199,7 @@ int pyramid_build(dso_b200_ctx* ctx, FrameSlot& fs, const float* color_dev, int 
 	if (levels > 1)
 	{
 		dim3 grid((w + TILE - 1) / TILE, (h + TILE - 1) / TILE);
-		pyr_intensity_kernel<<<grid, 256, 0, ctx->stream>>>(ia);
+		pyr_intensity_kernel<<<grid, 256, 0, stream>>>(ia);
 		ctx->launches++;
 	}
 	GradArgs ga;
@@ -215,7 +221,7 @@ int pyramid_build(dso_b200_ctx* ctx, FrameSlot& fs, const float* color_dev, int 
 		int n = wl * hl;
 		blocks += (n + 1023) / 1024;   // 256 threads x 4 pixels
 	}
-	pyr_gradient_kernel<<<blocks, 256, 0, ctx->stream>>>(ga);
+	pyr_gradient_kernel<<<blocks, 256, 0, stream>>>(ga);
 	ctx->launches++;
 	CK(cudaGetLastError());
 	fs.valid = true;

@@ -20,6 +20,7 @@
 // Roofline: gather-bound (L2 at VGA, HBM for the large sweeps): per point 16 B of cloud + 4 x 16 B
 // texels, ~170 flop.
 #include "common.cuh"
+#include <atomic>
 #include "lm_math.cuh"
 #include <cooperative_groups.h>
 namespace cg = cooperative_groups;
@@ -843,7 +844,8 @@ __device__ __forceinline__ void warp_reduce_halving(float* v, int lane)
 template <int NT>
 __global__ void __launch_bounds__(NT, 1)
 track_persistent_kernel(TrackLevels TL, dso_b200_track_opts opt, const TrackIn* __restrict__ in,
-                        dso_b200_track_result* out, int coarsestLvl, int smem_pts_cap, long long* phase_cycles)
+                        dso_b200_track_result* out, int coarsestLvl, int smem_pts_cap, long long* phase_cycles,
+                        dso_b200_track_result* host_out, unsigned int* host_flags, unsigned int seq)
 {
 	cg::cluster_group cluster = cg::this_cluster();
 	const unsigned CS = cluster.num_blocks();
@@ -866,9 +868,14 @@ track_persistent_kernel(TrackLevels TL, dso_b200_track_opts opt, const TrackIn* 
 
 	if (warp == 0)
 	{
+		// the input block may live in mapped host memory: one coalesced read by 19 lanes, then shared memory
+		__shared__ TrackIn s_in;
+		static_assert(sizeof(TrackIn) == 19 * sizeof(double), "TrackIn layout");
+		if (lane < 19) reinterpret_cast<double*>(&s_in)[lane] = reinterpret_cast<const double*>(in + hyp)[lane];
+		__syncwarp();
 		if (lane == 0)
 		{
-			const TrackIn& I = in[hyp];
+			const TrackIn& I = s_in;
 			for (int i = 0; i < 12; i++) S.cur[i] = I.pose[i];
 			S.a_cur = I.aff_a; S.b_cur = I.aff_b; S.a_new = I.aff_a; S.b_new = I.aff_b;
 			for (int i = 0; i < 5; i++) S.minRes[i] = I.minRes[i];
@@ -960,6 +967,16 @@ track_persistent_kernel(TrackLevels TL, dso_b200_track_opts opt, const TrackIn* 
 		const unsigned int* src = reinterpret_cast<const unsigned int*>(&s_res);
 		unsigned int* dst = reinterpret_cast<unsigned int*>(out + hyp);
 		for (int i = tid; i < nwords; i += NT) dst[i] = src[i];
+		if (host_out)
+		{
+			// results straight into mapped host memory, then the per-hypothesis flag: the host polls it instead of waiting
+			// for a copy node and a stream synchronisation
+			unsigned int* hdst = reinterpret_cast<unsigned int*>(host_out + hyp);
+			for (int i = tid; i < nwords; i += NT) hdst[i] = src[i];
+			__threadfence_system();
+			__syncthreads();
+			if (tid == 0) { *reinterpret_cast<volatile unsigned int*>(host_flags + hyp) = seq; __threadfence_system(); }
+		}
 	}
 	if (phase_cycles && blockIdx.x == 0 && tid == 0)
 	{
@@ -1064,7 +1081,7 @@ static int check_eval_args(dso_b200_ctx* ctx, int trk, int frame_slot, int lvl)
 	const FrameSlot& F = ctx->slots[frame_slot];
 	ARG_CHECK(lvl >= 0 && lvl < T.levels && lvl < F.levels, "bad level");
 	ARG_CHECK(F.w == T.w[0] && F.h == T.h[0], "frame / tracker size mismatch");
-	return 0;
+	return frame_slot_wait(ctx, frame_slot);   // a pending dso_b200_make_images_async of this slot
 }
 
 static int grid_for(const dso_b200_ctx* ctx, int n)
@@ -1204,16 +1221,24 @@ static int enqueue_track(dso_b200_ctx* ctx, int trk, int frame_slot, int nHyp, c
 	if (opts) o = *opts; else dso_b200_track_opts_default(&o);
 	// pageable staging: cudaMemcpyAsync returns once the source has been copied to the driver's staging
 	// area, so back-to-back asynchronous calls may reuse it
-	TrackIn hin[DSO_B200_MAX_HYP];
+	static_assert(sizeof(TrackIn) * DSO_B200_MAX_HYP <= TRACK_IN_BLOCK, "input block too small");
+	const TrackIn* kin = (const TrackIn*)T.last_in;
+	unsigned int seq = 0;
 	if (pose12_init)
 	{
+		// the kernel reads its inputs from a ring of mapped pinned blocks (one PCIe read by one warp) and writes its
+		// results back the same way: no copy nodes in front of or behind the kernel
+		seq = ++T.seq;
+		if (seq == 0) seq = ++T.seq;
+		TrackIn* hin = (TrackIn*)((char*)T.h_track_in + (size_t)(seq % TRACK_IN_RING) * TRACK_IN_BLOCK);
 		for (int i = 0; i < nHyp; i++)
 		{
 			memcpy(hin[i].pose, pose12_init + 12 * i, 96);
 			hin[i].aff_a = aff_a_init; hin[i].aff_b = aff_b_init;
 			for (int k = 0; k < 5; k++) hin[i].minRes[k] = NAN;
 		}
-		CK(cudaMemcpyAsync(T.d_track_in, hin, sizeof(TrackIn) * nHyp, cudaMemcpyHostToDevice, ctx->stream));
+		kin = hin;
+		T.last_in = hin;
 	}
 	TrackLevels TL;
 	fill_levels(ctx, T, &ctx->slots[frame_slot], new_ab_exposure, TL);
@@ -1241,7 +1266,8 @@ static int enqueue_track(dso_b200_ctx* ctx, int trk, int frame_slot, int nHyp, c
 	per = (max_n + cs - 1) / cs;
 	cap = (int)std::min<size_t>((size_t)per, smem_cap_bytes / sizeof(float4));
 	dyn = (size_t)cap * sizeof(float4);
-	void (*kern)(TrackLevels, dso_b200_track_opts, const TrackIn*, dso_b200_track_result*, int, int, long long*) =
+	void (*kern)(TrackLevels, dso_b200_track_opts, const TrackIn*, dso_b200_track_result*, int, int, long long*,
+	             dso_b200_track_result*, unsigned int*, unsigned int) =
 		nt == 128 ? track_persistent_kernel<128> : (nt == 512 ? track_persistent_kernel<512> : (nt == 384 ? track_persistent_kernel<384> : track_persistent_kernel<256>));
 	if (nt != 128 && nt != 512 && nt != 384) nt = 256;
 	static bool attr_set[64][4] = { { false } };
@@ -1261,11 +1287,9 @@ static int enqueue_track(dso_b200_ctx* ctx, int trk, int frame_slot, int nHyp, c
 	at[0].id = cudaLaunchAttributeClusterDimension;
 	at[0].val.clusterDim.x = cs; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
 	cfg.attrs = at; cfg.numAttrs = 1;
-	CK(cudaLaunchKernelEx(&cfg, kern, TL, o, (const TrackIn*)T.d_track_in,
-	                      (dso_b200_track_result*)T.d_track_out, coarsestLvl, cap, (long long*)ctx->d_phase_cycles));
+	CK(cudaLaunchKernelEx(&cfg, kern, TL, o, kin, (dso_b200_track_result*)T.d_track_out, coarsestLvl, cap, (long long*)ctx->d_phase_cycles,
+	                      seq ? (dso_b200_track_result*)T.h_track_out : (dso_b200_track_result*)nullptr, T.h_flags, seq));
 	ctx->launches++;
-	if (pose12_init)
-		CK(cudaMemcpyAsync(T.h_track_out, T.d_track_out, sizeof(dso_b200_track_result) * nHyp, cudaMemcpyDeviceToHost, ctx->stream));
 	return 0;
 }
 
@@ -1293,8 +1317,29 @@ extern "C" int dso_b200_track_phase_cycles(dso_b200_ctx* ctx, int enable, long l
 extern "C" int dso_b200_track_fetch(dso_b200_ctx* ctx, int trk, int nHyp, dso_b200_track_result* out)
 {
 	ARG_CHECK(ctx && (trk == 0 || trk == 1) && out && nHyp >= 1 && nHyp <= DSO_B200_MAX_HYP, "bad arguments");
-	CK(cudaStreamSynchronize(ctx->stream));
-	memcpy(out, ctx->trk[trk].h_track_out, sizeof(dso_b200_track_result) * nHyp);
+	TrackerSlot& T = ctx->trk[trk];
+	if (T.seq)
+	{
+		// poll the flags the kernel writes after its results (mapped pinned memory); look at the stream now and then so
+		// that a failed launch or a device fault surfaces as an error instead of a hang
+		volatile unsigned int* f = T.h_flags;
+		const unsigned int want = T.seq;
+		unsigned long long spins = 0;
+		for (int i = 0; i < nHyp; i++)
+			while (f[i] != want)
+			{
+				if ((++spins & 0x3fff) == 0)
+				{
+					cudaError_t e = cudaStreamQuery(ctx->stream);
+					if (e != cudaSuccess && e != cudaErrorNotReady) CK(e);
+					if (e == cudaSuccess && f[i] != want) { dso_set_error("dso_b200_track_fetch: stream idle but results missing"); return DSO_B200_E_STATE; }
+				}
+			}
+		std::atomic_thread_fence(std::memory_order_acquire);
+	}
+	else
+		CK(cudaStreamSynchronize(ctx->stream));
+	memcpy(out, T.h_track_out, sizeof(dso_b200_track_result) * nHyp);
 	return 0;
 }
 

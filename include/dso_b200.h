@@ -59,6 +59,13 @@ long long dso_b200_launch_count(dso_b200_ctx* ctx);
  * absSquaredGrad, which the reference leaves uninitialised, are written as 0. */
 int dso_b200_make_images(dso_b200_ctx* ctx, int frame_slot, const float* color_host, int w, int h, int levels,
                          const float* B_lut, float* const* dIp_out, float* const* absgrad_out);
+/* Asynchronous variant for pipelined front ends (the image of frame k+1 is usually in host memory while frame k is still
+ * being tracked): enqueues the H2D copy and the pyramid kernels of FrameHessian::makeImages (HessianBlocks.cpp:137-211,
+ * device pyramid only, no gamma LUT) on the context's second stream and returns.  The next tracker / BA call that reads
+ * `frame_slot` waits for it on the device.  `color_host` must stay valid until then and should be pinned
+ * (dso_b200_host_alloc); the slot must not be one a running tracking call still reads.  No counterpart in the reference,
+ * whose makeImages is synchronous. */
+int dso_b200_make_images_async(dso_b200_ctx* ctx, int frame_slot, const float* color_host, int w, int h, int levels);
 /* same, input already in device memory, nothing copied back, no synchronisation */
 int dso_b200_make_images_dev(dso_b200_ctx* ctx, int frame_slot, const float* color_dev, int w, int h, int levels,
                              const float* B_lut_host);
