@@ -52,6 +52,9 @@ SIGNATURES = {
     "dso_b200_host_free": (None, [vp]),
     "dso_b200_launch_count": (C.c_longlong, [vp]),
     "dso_b200_make_images": (C.c_int, [vp, C.c_int, vp, C.c_int, C.c_int, C.c_int, vp, C.POINTER(vp), C.POINTER(vp)]),
+    "dso_b200_tracker_set_ref_points": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float, C.c_int,
+                                                  f32p, f32p, f32p, f32p, C.c_double, C.c_double, C.c_float, vp]),
+    "dso_b200_tracker_get_cloud": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, vp, C.POINTER(C.c_int)]),
     "dso_b200_make_images_async": (C.c_int, [vp, C.c_int, vp, C.c_int, C.c_int, C.c_int]),
     "dso_b200_make_images_dev": (C.c_int, [vp, C.c_int, vp, C.c_int, C.c_int, C.c_int, vp]),
     "dso_b200_tracker_set_ref": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float,
@@ -247,6 +250,23 @@ class Context:
                                                    new_exposure, coarsest, _opt(mr), None if opts is None else C.byref(opts),
                                                    C.byref(res)))
         return res
+
+    def tracker_set_ref_points(self, trk, ref_slot, levels, K, cu, cv, cid, hdi, ref_a, ref_b, ref_exposure=1.0):
+        """makeCoarseDepthL0 on the device; returns pc_n per level"""
+        fx, fy, cx, cy = K
+        arrs = [np.ascontiguousarray(x, dtype=np.float32) for x in (cu, cv, cid, hdi)]
+        pc_n = np.zeros(8, dtype=np.int32)
+        self._check(self.L.dso_b200_tracker_set_ref_points(self.h, trk, ref_slot, levels, fx, fy, cx, cy, len(arrs[0]), *arrs,
+                                                           ref_a, ref_b, ref_exposure, pc_n.ctypes.data))
+        return pc_n[:levels].copy()
+
+    def tracker_get_cloud(self, trk, lvl):
+        n = C.c_int(0)
+        self._check(self.L.dso_b200_tracker_get_cloud(self.h, trk, lvl, 0, None, C.byref(n)))
+        out = np.zeros((n.value, 4), dtype=np.float32)
+        if n.value:
+            self._check(self.L.dso_b200_tracker_get_cloud(self.h, trk, lvl, n.value, out.ctypes.data, C.byref(n)))
+        return out
 
     def make_images_async(self, slot, color_ptr, w, h, levels):
         """color_ptr: host address (pinned) or numpy array that the caller keeps alive until the slot is consumed"""

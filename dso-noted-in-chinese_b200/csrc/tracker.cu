@@ -1030,17 +1030,9 @@ extern "C" void dso_b200_track_opts_default(dso_b200_track_opts* o)
 	for (int i = 0; i < 5; i++) o->maxIterations[i] = mi[i];
 }
 
-extern "C" int dso_b200_tracker_set_ref(dso_b200_ctx* ctx, int trk, int w, int h, int levels,
-                                        float fx, float fy, float cx, float cy,
-                                        const int* pc_n, const float* const* pc_u, const float* const* pc_v,
-                                        const float* const* pc_idepth, const float* const* pc_color,
-                                        double ref_aff_a, double ref_aff_b, float ref_ab_exposure)
+// CoarseTracker::makeK, CoarseTracker.cpp:102-131
+void tracker_make_K(TrackerSlot& T, int w, int h, int levels, float fx, float fy, float cx, float cy)
 {
-	ARG_CHECK(ctx && (trk == 0 || trk == 1), "bad tracker slot");
-	ARG_CHECK(levels >= 1 && levels <= MAXL && w <= ctx->max_w && h <= ctx->max_h, "bad size / levels");
-	CK(cudaSetDevice(ctx->device));
-	TrackerSlot& T = ctx->trk[trk];
-	// makeK, CoarseTracker.cpp:102-131
 	T.levels = levels;
 	T.w[0] = w; T.h[0] = h; T.fx[0] = fx; T.fy[0] = fy; T.cx[0] = cx; T.cy[0] = cy;
 	for (int l = 1; l < levels; l++)
@@ -1056,6 +1048,19 @@ extern "C" int dso_b200_tracker_set_ref(dso_b200_ctx* ctx, int trk, int w, int h
 		float K[9] = { T.fx[l], 0, T.cx[l], 0, T.fy[l], T.cy[l], 0, 0, 1 };
 		mat33f_inverse(K, T.Ki[l]);
 	}
+}
+
+extern "C" int dso_b200_tracker_set_ref(dso_b200_ctx* ctx, int trk, int w, int h, int levels,
+                                        float fx, float fy, float cx, float cy,
+                                        const int* pc_n, const float* const* pc_u, const float* const* pc_v,
+                                        const float* const* pc_idepth, const float* const* pc_color,
+                                        double ref_aff_a, double ref_aff_b, float ref_ab_exposure)
+{
+	ARG_CHECK(ctx && (trk == 0 || trk == 1), "bad tracker slot");
+	ARG_CHECK(levels >= 1 && levels <= MAXL && w <= ctx->max_w && h <= ctx->max_h, "bad size / levels");
+	CK(cudaSetDevice(ctx->device));
+	TrackerSlot& T = ctx->trk[trk];
+	tracker_make_K(T, w, h, levels, fx, fy, cx, cy);
 	// clouds: SoA host arrays -> one float4 per point, packed on the host, one copy per level
 	std::vector<float4> tmp;
 	for (int l = 0; l < levels; l++)

@@ -79,6 +79,20 @@ int dso_b200_tracker_set_ref(dso_b200_ctx* ctx, int trk, int w, int h, int level
                              const int* pc_n, const float* const* pc_u, const float* const* pc_v,
                              const float* const* pc_idepth, const float* const* pc_color,
                              double ref_aff_a, double ref_aff_b, float ref_ab_exposure);
+/* The same with CoarseTracker::makeCoarseDepthL0 (CoarseTracker.cpp:135-292) done on the device (next row N3): the
+ * caller passes, for every active point with lastResiduals[0] IN (:147), the projection into the newest key frame
+ * r->centerProjectedTo[0..2] (cpt_u, cpt_v, cpt_idepth) and ph->efPoint->HdiF; the key frame's pyramid must already be in
+ * `ref_frame_slot` (its level-l intensities are the cloud's colours, :270).  Splat, 2x2 sum pyramid, dilation,
+ * normalisation and raster-order compaction run on the context stream; pc_n_out (may be NULL) receives pc_n[lvl].
+ * Points projecting outside the image are skipped (the reference does not check).  Results are bit-identical to the
+ * reference's sequential loops, also where several points fall on one pixel. */
+int dso_b200_tracker_set_ref_points(dso_b200_ctx* ctx, int trk, int ref_frame_slot, int levels,
+                                    float fx, float fy, float cx, float cy, int n_points,
+                                    const float* cpt_u, const float* cpt_v, const float* cpt_idepth, const float* HdiF,
+                                    double ref_aff_a, double ref_aff_b, float ref_ab_exposure, int* pc_n_out);
+/* Reads back a tracker slot's cloud of one level as (u, v, idepth, color) records (tests, debugPlot). */
+int dso_b200_tracker_get_cloud(dso_b200_ctx* ctx, int trk, int lvl, int max_points, float* out4, int* n_out);
+
 
 /* CoarseTracker::calcRes (CoarseTracker.cpp:359-520, decl CoarseTracker.h:100), fused with the
  * accumulation of calcGSSSE so that no warped buffers are materialised.
