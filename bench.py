@@ -130,19 +130,23 @@ class quiet_stdout:
         os.close(self.saved)
 
 
-def build_workload(seed, n_frames, tracker_points):
-    """Window (configs[1]) + reference cloud + a ring of follow-up frames with constant-velocity priors."""
+def build_workload(seed, n_frames, tracker_points, with_oracle=True):
+    """Window (configs[1]) + the inputs of setCoarseTrackingRef + a ring of follow-up frames with constant-velocity priors.
+    with_oracle: also build the CPU tracker and its reference cloud (cpu_baseline / reference arm / debug scripts); the GPU
+    arm builds its own cloud on the device (dso_b200_tracker_set_ref_points) and never needs it."""
     pkg = entry.load_package()
-    O = entry.load_oracle()     # the oracle's makeCoarseDepthL0 produces the reference cloud (input data)
     syn = pkg.synthetic
     W = syn.make_window(seed=seed, n_points=tracker_points)
     levels = syn.pyr_levels_for(W.w, W.h)
-    ref_pyr = O.make_images(W.images[-1], levels)
-    trk = O.Tracker(W.w, W.h, levels, *W.K, kind=cpu_kind()[0])
     cu, cv, cid, hdi = syn.tracker_reference_inputs(W)
     a0, b0 = W.aff_true[-1]
-    trk.set_ref(cu, cv, cid, hdi, [x.reshape(-1) for x in ref_pyr[0]], a0, b0, 1.0)
-    clouds = [trk.get_cloud(l) for l in range(levels)]
+    trk, clouds = None, None
+    if with_oracle:
+        O = entry.load_oracle()
+        ref_pyr = O.make_images(W.images[-1], levels)
+        trk = O.Tracker(W.w, W.h, levels, *W.K, kind=cpu_kind()[0])
+        trk.set_ref(cu, cv, cid, hdi, [x.reshape(-1) for x in ref_pyr[0]], a0, b0, 1.0)
+        clouds = [trk.get_cloud(l) for l in range(levels)]
     frames = syn.tracking_sequence(W, n_frames)
     # constant-motion prior (FullSystem.cpp:311): lastF_2_fh ~ (slast_2_sprelast)^-1 ... built from the true poses
     rel = [(np.eye(3), np.zeros(3))] + [f[1] for f in frames]
@@ -156,7 +160,7 @@ def build_workload(seed, n_frames, tracker_points):
         inits.append(syn.pose12(init))
         affs.append(frames[k - 2][2] if k >= 2 else (a0, b0))
     return dict(W=W, levels=levels, clouds=clouds, frames=frames, inits=inits, affs=affs, a0=a0, b0=b0,
-                oracle_tracker=trk, ref_points=len(cu))
+                oracle_tracker=trk, ref_points=len(cu), ref_inputs=(cu, cv, cid, hdi))
 
 
 def dist_setup(n):
@@ -345,6 +349,7 @@ def run_reference(args):
     O = entry.load_oracle()
     with quiet_stdout():
         wl = build_workload(0, args.frames, args.tracker_points)
+        wl["pc_n"] = [len(c[0]) for c in wl["clouds"]]
         nfr = len(wl["frames"])
         for k in range(args.warmup):
             cpu_track_once(wl, k % nfr, O, True)
@@ -373,7 +378,7 @@ def workload_config(wl, args):
     return {"workload": "configs[0]/[2]: 640x480 synthetic pinhole sequence, trackNewestCoarse vs the newest of 7 key frames, "
                         "1 pose hypothesis, %d-level pyramid (reference default at VGA, SURVEY F4), default settings" % wl["levels"],
             "width": W.w, "height": W.h, "levels": wl["levels"], "key_frames": W.nF, "active_points": int(W.nP),
-            "reference_points": int(wl["ref_points"]), "pc_n": [int(len(c[0])) for c in wl["clouds"]],
+            "reference_points": int(wl["ref_points"]), "pc_n": [int(x) for x in wl["pc_n"]],
             "ring_frames": len(wl["frames"]), "l2": "NOT flushed (diagnostic run)" if args.no_flush else "flushed between timed steps (256 MiB memset)",
             "step": "one trackNewestCoarse call on a new frame", "parallelism": "replicas x%d" % args.gpus}
 
@@ -388,12 +393,16 @@ def run_ours(args):
     device = torch.device("cuda", dev)
     pkg = entry.load_package()
     with quiet_stdout():
-        wl = build_workload(rank, args.frames, args.tracker_points)
+        wl = build_workload(rank, args.frames, args.tracker_points, with_oracle=(rank == 0 and not args.no_cpu and int(os.environ.get("WORLD_SIZE", "1")) == 1))
     W, levels = wl["W"], wl["levels"]
     nfr = len(wl["frames"])
     RING = 26            # e2e frame slots: 26 x 6.9 MB of pyramid = 180 MB > 126 MB L2
     ctx = pkg.Context(dev, W.w, W.h, nfr + 2 + RING)
-    ctx.tracker_set_ref(0, W.w, W.h, levels, W.K, wl["clouds"], wl["a0"], wl["b0"], 1.0)
+    # setCoarseTrackingRef on the device: key-frame pyramid in slot 0, makeCoarseDepthL0 from the active points' projections
+    ctx.make_images(0, W.images[-1], levels, want_host=False)
+    t0 = time.perf_counter()
+    wl["pc_n"] = ctx.tracker_set_ref_points(0, 0, levels, W.K, *wl["ref_inputs"], wl["a0"], wl["b0"], 1.0)
+    set_ref_ms = (time.perf_counter() - t0) * 1e3
     stream = torch.cuda.ExternalStream(ctx.stream, device=device)
 
     # pinned host copies of the frames (e2e input) and resident pyramids (value input)
@@ -552,6 +561,7 @@ def run_ours(args):
                                    "tracked_ok": conv / total_steps}},
                 "gpu_launches": int(launches), "ba": ba, "roofline": roofline, "cpu_baseline": cpu, "clocks": clocks,
                 "wall_s_timed_region": t_wall1 - t_wall0,
+                "set_coarse_tracking_ref_ms": set_ref_ms,     # makeCoarseDepthL0 on the device incl. upload of the points and 1 sync (first call)
                 "lm": {"evals_per_frame": float(np.mean([r.n_evals for r in results])),
                        "iterations_per_frame": float(np.mean([r.n_iterations for r in results])),
                        "point_evals_per_frame": float(np.mean([r.point_evals for r in results]))}}
