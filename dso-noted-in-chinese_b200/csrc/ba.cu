@@ -48,7 +48,7 @@ int ba_create(dso_b200_ctx* ctx)
 	CK(cudaMalloc(&W->d_scalars, 8 * sizeof(double)));
 	// stage-1 contributions: per (i,j): C1,C2 (64 each), C3,C4 (MAXF*64 each), CEh,CEt (32 each), Cbh,Cbt (8 each)
 	CK(cudaMalloc(&W->d_scContrib, (size_t)MAXF * MAXF * (128 + 2 * MAXF * 64 + 64 + 16) * sizeof(double)));
-	CK(cudaMalloc(&W->d_scRed, (size_t)MAXF * (MAXF * MAXF * 64 + MAXF * 40) * sizeof(double)));
+	CK(cudaMalloc(&W->d_scRed, (size_t)MAXF * (MAXF * MAXF * 64 + MAXF * 40 + 24) * sizeof(double)));
 	CK(cudaMalloc(&W->d_topRed, (size_t)MAXF * MAXF * NTOP_PAD * sizeof(double)));
 	CK(cudaMalloc(&W->d_topContrib, (size_t)MAXF * MAXF * 292 * sizeof(double)));
 	CK(cudaHostAlloc((void**)&W->h_out, (2 * (size_t)N * N + 2 * N + 8) * sizeof(double), cudaHostAllocDefault));
@@ -505,6 +505,11 @@ __device__ __forceinline__ int top_index(int i, int j)
 	return 85 + (a == 0 ? b : (a == 1 ? 2 + b : 5));
 }
 
+// v += sum_{k < n} EXPR(k) for n <= MAXF: every load is issued before the first add, the adds stay in index order
+// (a plain loop over a run-time n makes each add wait for its own load: n dependent DRAM/L2 round trips)
+#define ORDERED_SUM_MAXF(v, n, k, EXPR) do { double t_[MAXF]; _Pragma("unroll") for (int k = 0; k < MAXF; k++) t_[k] = (k < (n)) ? (EXPR) : 0.0; \
+	_Pragma("unroll") for (int k = 0; k < MAXF; k++) if (k < (n)) v += t_[k]; } while (0)
+
 // sum of the per-chunk partials of every group (pair or host) in chunk order, FP64: one thread per entry
 __global__ void ba_reduce_partials_kernel(const float* __restrict__ partials, int stride, int nEntries,
                                           const int* __restrict__ group_begin, double* out)
@@ -512,7 +517,15 @@ __global__ void ba_reduce_partials_kernel(const float* __restrict__ partials, in
 	const int e = blockIdx.x * blockDim.x + threadIdx.x, g = blockIdx.y;
 	if (e >= nEntries) return;
 	double s = 0.0;
-	for (int c = group_begin[g]; c < group_begin[g + 1]; c++) s += (double)partials[(size_t)c * stride + e];
+	const int c1 = group_begin[g + 1];
+	for (int c0 = group_begin[g]; c0 < c1; c0 += 8)              // eight loads in flight, adds in chunk order
+	{
+		float t[8];
+#pragma unroll
+		for (int u = 0; u < 8; u++) t[u] = (c0 + u < c1) ? partials[(size_t)(c0 + u) * stride + e] : 0.f;
+#pragma unroll
+		for (int u = 0; u < 8; u++) if (c0 + u < c1) s += (double)t[u];
+	}
 	out[(size_t)g * nEntries + e] = s;
 }
 
@@ -593,11 +606,16 @@ __global__ void __launch_bounds__(64) ba_top_gather_kernel(int nF, int nChunks, 
 		double v = 0.0;
 		if (r == c)
 		{
-			for (int q = 0; q < nF; q++)           // pairs with host r, then pairs with target r (fixed order)
+			// pairs with host r, then pairs with target r, alternating (fixed order)
+			double th[MAXF], tt[MAXF];
+#pragma unroll
+			for (int q = 0; q < MAXF; q++)
 			{
-				v += contrib[(size_t)(r + nF * q) * TC_STRIDE + TC_HH + o];
-				v += contrib[(size_t)(q + nF * r) * TC_STRIDE + TC_TT + o];
+				th[q] = (q < nF) ? contrib[(size_t)(r + nF * q) * TC_STRIDE + TC_HH + o] : 0.0;
+				tt[q] = (q < nF) ? contrib[(size_t)(q + nF * r) * TC_STRIDE + TC_TT + o] : 0.0;
 			}
+#pragma unroll
+			for (int q = 0; q < MAXF; q++) if (q < nF) { v += th[q]; v += tt[q]; }
 			if (priorH && i == j) v += priorH[CPARS + r * 8 + i];     // usePrior, AccumulatedTopHessian.cpp:314-324
 		}
 		else
@@ -610,10 +628,16 @@ __global__ void __launch_bounds__(64) ba_top_gather_kernel(int nF, int nChunks, 
 		{
 			const int r = e / 32, q = e % 32;
 			double v = 0.0;
-			for (int m = 0; m < nF; m++)
 			{
-				v += contrib[(size_t)(r + nF * m) * TC_STRIDE + TC_CH + q];
-				v += contrib[(size_t)(m + nF * r) * TC_STRIDE + TC_CT + q];
+				double th[MAXF], tt[MAXF];
+#pragma unroll
+				for (int m = 0; m < MAXF; m++)
+				{
+					th[m] = (m < nF) ? contrib[(size_t)(r + nF * m) * TC_STRIDE + TC_CH + q] : 0.0;
+					tt[m] = (m < nF) ? contrib[(size_t)(m + nF * r) * TC_STRIDE + TC_CT + q] : 0.0;
+				}
+#pragma unroll
+				for (int m = 0; m < MAXF; m++) if (m < nF) { v += th[m]; v += tt[m]; }
 			}
 			const int row = CPARS + r * 8 + (q >> 2), col = q & 3;
 			Hout[row * N + col] = v; Hout[col * N + row] = v;
@@ -622,23 +646,55 @@ __global__ void __launch_bounds__(64) ba_top_gather_kernel(int nF, int nChunks, 
 		{
 			const int r = e / 8, q = e % 8;
 			double v = 0.0;
-			for (int m = 0; m < nF; m++)
 			{
-				v += contrib[(size_t)(r + nF * m) * TC_STRIDE + TC_BH + q];
-				v += contrib[(size_t)(m + nF * r) * TC_STRIDE + TC_BT + q];
+				double th[MAXF], tt[MAXF];
+#pragma unroll
+				for (int m = 0; m < MAXF; m++)
+				{
+					th[m] = (m < nF) ? contrib[(size_t)(r + nF * m) * TC_STRIDE + TC_BH + q] : 0.0;
+					tt[m] = (m < nF) ? contrib[(size_t)(m + nF * r) * TC_STRIDE + TC_BT + q] : 0.0;
+				}
+#pragma unroll
+				for (int m = 0; m < MAXF; m++) if (m < nF) { v += th[m]; v += tt[m]; }
 			}
 			if (priorH) v += __dmul_rn(priorH[CPARS + e], priorD[CPARS + e]);   // prior.cwiseProduct(delta_prior)
 			bout[CPARS + e] = v;
 		}
+		// calibration block / vector: sum over all pairs, three threads per entry (each a third of the pairs, in order), then
+		// the three parts in order
+		__shared__ double s_cc[3][20];
+		if (o < 60)
+		{
+			const int e = o % 20, part = o / 20, np = nF * nF, per = (np + 2) / 3;
+			const int k1 = min(np, (part + 1) * per);
+			double v = 0.0;
+			for (int k0 = part * per; k0 < k1; k0 += 8)
+			{
+				double t[8];
+#pragma unroll
+				for (int u = 0; u < 8; u++) t[u] = (k0 + u < k1) ? contrib[(size_t)(k0 + u) * TC_STRIDE + TC_CC + e] : 0.0;
+#pragma unroll
+				for (int u = 0; u < 8; u++) if (k0 + u < k1) v += t[u];
+			}
+			s_cc[part][e] = v;
+		}
+		__syncthreads();
 		if (o < 20)
 		{
-			double v = 0.0;
-			for (int k = 0; k < nF * nF; k++) v += contrib[(size_t)k * TC_STRIDE + TC_CC + o];
+			double v = (s_cc[0][o] + s_cc[1][o]) + s_cc[2][o];
 			if (priorH && o < 16 && (o >> 2) == (o & 3)) v += priorH[o >> 2];
 			if (priorH && o >= 16) v += __dmul_rn(priorH[o - 16], (double)cDeltaF[o - 16]);   // cPrior.cwiseProduct(cDeltaF.cast<double>())
 			if (o < 16) Hout[(o >> 2) * N + (o & 3)] = v; else bout[o - 16] = v;
 		}
-		if (o == 32) { int n = 0; for (int c = 0; c < nChunks; c++) n += chunk_nres[c]; scalars[1] = (double)n; }
+		if (o >= 32)
+		{
+			// resInA: integer sum over the chunks, one warp
+			int n = 0;
+			for (int c = o - 32; c < nChunks; c += 32) n += chunk_nres[c];
+#pragma unroll
+			for (int d = 16; d > 0; d >>= 1) n += __shfl_xor_sync(0xffffffffu, n, d);
+			if (o == 32) scalars[1] = (double)n;
+		}
 	}
 }
 
@@ -755,7 +811,8 @@ __global__ void __launch_bounds__(64) ba_schur_stage1_kernel(int nF, const doubl
                                                              const double* __restrict__ adHost, const double* __restrict__ adTarget,
                                                              double* contrib)
 {
-	__shared__ double D[64], S1[64], Q[64], AHij[64], ATij[64], AHik[64], ATik[64], E[32], EB[8];
+	__shared__ double Dk[MAXF][64], AHk[MAXF][64], ATk[MAXF][64];   // all k-dependent operands, loaded in one go
+	__shared__ double S1[64], Q[64], AHij[64], ATij[64], E[32], EB[8];
 	const int i = blockIdx.x % nF, j = blockIdx.x / nF, o = threadIdx.x;
 	const int ij = i + nF * j;
 	const int nD = nF * nF * 64, nE = nF * 32;
@@ -765,13 +822,18 @@ __global__ void __launch_bounds__(64) ba_schur_stage1_kernel(int nF, const doubl
 	S1[o] = 0.0;
 	if (o < 32) E[o] = red[nD + j * 32 + o];
 	if (o < 8) EB[o] = red[nD + nE + j * 8 + o];
+#pragma unroll
+	for (int k = 0; k < MAXF; k++)
+		if (k < nF)
+		{
+			const int ik = i + nF * k;
+			Dk[k][o] = red[(j * nF + k) * 64 + o];
+			AHk[k][o] = adHost[(size_t)ik * 64 + o]; ATk[k][o] = adTarget[(size_t)ik * 64 + o];
+		}
 	__syncthreads();
 	for (int k = 0; k < nF; k++)
 	{
-		const int ik = i + nF * k;
-		D[o] = red[(j * nF + k) * 64 + o];
-		AHik[o] = adHost[(size_t)ik * 64 + o]; ATik[o] = adTarget[(size_t)ik * 64 + o];
-		__syncthreads();
+		const double* D = Dk[k]; const double* AHik = AHk[k]; const double* ATik = ATk[k];
 		{
 			const int r = o >> 3, c = o & 7;
 			double v = 0.0, q = 0.0;
@@ -805,7 +867,7 @@ __global__ void __launch_bounds__(64) ba_schur_stage1_kernel(int nF, const doubl
 }
 
 // stage 2: gather the contributions of every output block in a fixed order
-__global__ void __launch_bounds__(64) ba_schur_gather_kernel(int nF, int nPC, const float* __restrict__ partials, int scN,
+__global__ void __launch_bounds__(64) ba_schur_gather_kernel(int nF, const double* __restrict__ scRed,
                                                              const double* __restrict__ contrib, double* Hout, double* bout)
 {
 	const int N = 8 * nF + CPARS, o = threadIdx.x;
@@ -813,10 +875,11 @@ __global__ void __launch_bounds__(64) ba_schur_gather_kernel(int nF, int nPC, co
 	{
 		const int r = blockIdx.x / nF, c = blockIdx.x % nF;
 		double v = 0.0;
-		if (r == c) for (int j = 0; j < nF; j++) v += contrib[(size_t)(r + nF * j) * SCC_STRIDE + SCC_C1 + o];
-		v += contrib[(size_t)(c + nF * r) * SCC_STRIDE + SCC_C2 + o];                                     // i = c, j = r
-		for (int i = 0; i < nF; i++) v += contrib[(size_t)(i + nF * r) * SCC_STRIDE + SCC_C3 + c * 64 + o];   // j = r, k = c
-		for (int j = 0; j < nF; j++) v += contrib[(size_t)(r + nF * j) * SCC_STRIDE + SCC_C4 + c * 64 + o];   // i = r, k = c
+		const double c2 = contrib[(size_t)(c + nF * r) * SCC_STRIDE + SCC_C2 + o];                         // i = c, j = r
+		if (r == c) ORDERED_SUM_MAXF(v, nF, j, contrib[(size_t)(r + nF * j) * SCC_STRIDE + SCC_C1 + o]);
+		v += c2;
+		ORDERED_SUM_MAXF(v, nF, i, contrib[(size_t)(i + nF * r) * SCC_STRIDE + SCC_C3 + c * 64 + o]);      // j = r, k = c
+		ORDERED_SUM_MAXF(v, nF, j, contrib[(size_t)(r + nF * j) * SCC_STRIDE + SCC_C4 + c * 64 + o]);      // i = r, k = c
 		Hout[(CPARS + r * 8 + (o >> 3)) * N + CPARS + c * 8 + (o & 7)] = v;
 	}
 	else
@@ -827,8 +890,8 @@ __global__ void __launch_bounds__(64) ba_schur_gather_kernel(int nF, int nPC, co
 		{
 			const int r = e / 32, q = e % 32;
 			double v = 0.0;
-			for (int j = 0; j < nF; j++) v += contrib[(size_t)(r + nF * j) * SCC_STRIDE + SCC_CEH + q];
-			for (int i = 0; i < nF; i++) v += contrib[(size_t)(i + nF * r) * SCC_STRIDE + SCC_CET + q];
+			ORDERED_SUM_MAXF(v, nF, j, contrib[(size_t)(r + nF * j) * SCC_STRIDE + SCC_CEH + q]);
+			ORDERED_SUM_MAXF(v, nF, i, contrib[(size_t)(i + nF * r) * SCC_STRIDE + SCC_CET + q]);
 			const int row = CPARS + r * 8 + (q >> 2), col = q & 3;
 			Hout[row * N + col] = v;
 			Hout[col * N + row] = v;                                  // AccumulatedSCHessian.h:130-134
@@ -837,14 +900,15 @@ __global__ void __launch_bounds__(64) ba_schur_gather_kernel(int nF, int nPC, co
 		{
 			const int r = e / 8, q = e % 8;
 			double v = 0.0;
-			for (int j = 0; j < nF; j++) v += contrib[(size_t)(r + nF * j) * SCC_STRIDE + SCC_CBH + q];
-			for (int i = 0; i < nF; i++) v += contrib[(size_t)(i + nF * r) * SCC_STRIDE + SCC_CBT + q];
+			ORDERED_SUM_MAXF(v, nF, j, contrib[(size_t)(r + nF * j) * SCC_STRIDE + SCC_CBH + q]);
+			ORDERED_SUM_MAXF(v, nF, i, contrib[(size_t)(i + nF * r) * SCC_STRIDE + SCC_CBT + q]);
 			bout[CPARS + e] = v;
 		}
 		if (o < 20)
 		{
 			double v = 0.0;
-			for (int c = 0; c < nPC; c++) v += (double)partials[(size_t)c * scN + nD + nE + nEB + o];
+			// accHcc / accbc: chunk partials already summed per host by ba_reduce_partials_kernel, hosts in order here
+			ORDERED_SUM_MAXF(v, nF, i, scRed[(size_t)i * (nD + nE + nEB + 20) + nD + nE + nEB + o]);
 			if (o < 16) Hout[(o >> 2) * N + (o & 3)] = v; else bout[o - 16] = v;
 		}
 	}
@@ -1300,10 +1364,10 @@ int ba_enqueue_schur(dso_b200_ctx* ctx)
 	                                                              W->d_HdiF, W->d_bdSumF, W->d_idh, W->d_HcdSum);
 	ba_schur_accum_kernel<<<W->nPC, 256, 0, ctx->stream>>>(nF, W->d_pc_start, W->d_pc_cnt, W->d_res_begin, W->d_rtarget, W->d_isAct, W->d_JpJdF,
 	                                                     W->d_HdiF, W->d_bdSumF, W->d_HcdSum, W->d_scPartials, W->scN);
-	const int nRed = nF * nF * 64 + nF * 32 + nF * 8;
+	const int nRed = nF * nF * 64 + nF * 32 + nF * 8 + 20;          // accD, accE, accEB, accHcc + accbc per host
 	ba_reduce_partials_kernel<<<dim3((nRed + 255) / 256, nF), 256, 0, ctx->stream>>>(W->d_scPartials, W->scN, nRed, W->d_host_pc_begin, W->d_scRed);
 	ba_schur_stage1_kernel<<<nF * nF, 64, 0, ctx->stream>>>(nF, W->d_scRed, nRed, W->d_adHost, W->d_adTarget, W->d_scContrib);
-	ba_schur_gather_kernel<<<nF * nF + 1, 64, 0, ctx->stream>>>(nF, W->nPC, W->d_scPartials, W->scN, W->d_scContrib, W->d_HS, W->d_bS);
+	ba_schur_gather_kernel<<<nF * nF + 1, 64, 0, ctx->stream>>>(nF, W->d_scRed, W->d_scContrib, W->d_HS, W->d_bS);
 	ctx->launches += 5;
 	CK(cudaGetLastError());
 	return 0;
