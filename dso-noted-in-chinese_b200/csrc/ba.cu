@@ -330,7 +330,19 @@ __global__ void ba_energy_blocks_kernel(int n, const double* __restrict__ e, dou
 }
 __global__ void ba_energy_final_kernel(int nb, const double* __restrict__ blocks, double* out)
 {
-	if (threadIdx.x == 0 && blockIdx.x == 0) { double s = 0; for (int i = 0; i < nb; i++) s += blocks[i]; out[0] = s; }
+	if (threadIdx.x == 0 && blockIdx.x == 0)
+	{
+		double s = 0;
+		for (int i0 = 0; i0 < nb; i0 += 16)                   // sixteen loads in flight, adds in block order
+		{
+			double t[16];
+#pragma unroll
+			for (int u = 0; u < 16; u++) t[u] = (i0 + u < nb) ? blocks[i0 + u] : 0.0;
+#pragma unroll
+			for (int u = 0; u < 16; u++) if (i0 + u < nb) s += t[u];
+		}
+		out[0] = s;
+	}
 }
 
 // Jp*delta of EFResidual::fixLinearizationF / addPoint<1> (EnergyFunctionalStructs.cpp:92-100, AccumulatedTopHessian.cpp:82-87):
@@ -483,12 +495,25 @@ __global__ void ba_point_sums_kernel(int nP, const int* __restrict__ res_begin, 
 	const int p = blockIdx.x * blockDim.x + threadIdx.x;
 	if (p >= nP) return;
 	float bd_acc = 0.f, Hdd_acc = 0.f, h0 = 0.f, h1 = 0.f, h2 = 0.f, h3 = 0.f;
-	for (int r = res_begin[p]; r < res_begin[p + 1]; r++)
+	const int r1 = res_begin[p + 1];
+	for (int r0 = res_begin[p]; r0 < r1; r0 += 4)              // four residuals' loads in flight, sums in residualsAll order
 	{
-		if (!isAct[r] || (mode == 0 ? isLin[r] != 0 : !isLin[r])) continue;
-		const float* c = contrib + 6 * (size_t)r;
-		bd_acc = fadd(bd_acc, c[0]); Hdd_acc = fadd(Hdd_acc, c[1]);
-		h0 = fadd(h0, c[2]); h1 = fadd(h1, c[3]); h2 = fadd(h2, c[4]); h3 = fadd(h3, c[5]);
+		float c[4][6]; bool use[4];
+#pragma unroll
+		for (int u = 0; u < 4; u++)
+		{
+			const int r = r0 + u;
+			use[u] = r < r1 && isAct[r] && (mode == 0 ? !isLin[r] : isLin[r] != 0);
+#pragma unroll
+			for (int k = 0; k < 6; k++) c[u][k] = use[u] ? contrib[6 * (size_t)r + k] : 0.f;
+		}
+#pragma unroll
+		for (int u = 0; u < 4; u++)
+			if (use[u])
+			{
+				bd_acc = fadd(bd_acc, c[u][0]); Hdd_acc = fadd(Hdd_acc, c[u][1]);
+				h0 = fadd(h0, c[u][2]); h1 = fadd(h1, c[u][3]); h2 = fadd(h2, c[u][4]); h3 = fadd(h3, c[u][5]);
+			}
 	}
 	Hdd[p] = Hdd_acc; bd[p] = bd_acc;
 	Hcd[4 * p] = h0; Hcd[4 * p + 1] = h1; Hcd[4 * p + 2] = h2; Hcd[4 * p + 3] = h3;

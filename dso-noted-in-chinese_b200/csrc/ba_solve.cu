@@ -402,15 +402,27 @@ __global__ void ba_resubstitute_kernel(int nP, int nF, const int* __restrict__ r
 	const float x0 = (float)x[0], x1 = (float)x[1], x2 = (float)x[2], x3 = (float)x[3];
 	b = fsub(b, fadd(fadd(fmul(x0, hc[0]), fmul(x1, hc[1])), fadd(fmul(x2, hc[2]), fmul(x3, hc[3]))));
 	const int h = phost[p];
-	for (int r = res_begin[p]; r < res_begin[p + 1]; r++)
+	const int r1 = res_begin[p + 1];
+	for (int r0 = res_begin[p]; r0 < r1; r0 += 4)              // four residuals' loads in flight, subtractions in residualsAll order
 	{
-		if (!isAct[r]) continue;
-		const float* xa = xAd + 8 * (h * nF + rtarget[r]);
-		const float* jp = JpJdF + 8 * (size_t)r;
-		float q[8];
+		float d[4]; bool use[4];
 #pragma unroll
-		for (int i = 0; i < 8; i++) q[i] = fmul(xa[i], jp[i]);
-		b = fsub(b, fadd(fadd(fadd(q[0], q[1]), fadd(q[2], q[3])), fadd(fadd(q[4], q[5]), fadd(q[6], q[7]))));
+		for (int u = 0; u < 4; u++)
+		{
+			const int r = r0 + u;
+			use[u] = r < r1 && isAct[r];
+			d[u] = 0.f;
+			if (use[u])
+			{
+				const float4* xa = reinterpret_cast<const float4*>(xAd + 8 * (h * nF + rtarget[r]));
+				const float4* jp = reinterpret_cast<const float4*>(JpJdF + 8 * (size_t)r);
+				const float4 x0 = xa[0], x1 = xa[1], j0 = jp[0], j1 = jp[1];
+				d[u] = fadd(fadd(fadd(fmul(x0.x, j0.x), fmul(x0.y, j0.y)), fadd(fmul(x0.z, j0.z), fmul(x0.w, j0.w))),
+				            fadd(fadd(fmul(x1.x, j1.x), fmul(x1.y, j1.y)), fadd(fmul(x1.z, j1.z), fmul(x1.w, j1.w))));
+			}
+		}
+#pragma unroll
+		for (int u = 0; u < 4; u++) if (use[u]) b = fsub(b, d[u]);
 	}
 	step[p] = fmul(-b, HdiF[p]);
 }
@@ -448,7 +460,14 @@ __global__ void ba_points_step_final_kernel(int nb, const double* __restrict__ b
 	if (threadIdx.x == 0 && blockIdx.x == 0)
 	{
 		double a = 0, b = 0;
-		for (int i = 0; i < nb; i++) { a += blocks[2 * i]; b += blocks[2 * i + 1]; }
+		for (int i0 = 0; i0 < nb; i0 += 8)
+		{
+			double ta[8], tb[8];
+#pragma unroll
+			for (int u = 0; u < 8; u++) { ta[u] = (i0 + u < nb) ? blocks[2 * (i0 + u)] : 0.0; tb[u] = (i0 + u < nb) ? blocks[2 * (i0 + u) + 1] : 0.0; }
+#pragma unroll
+			for (int u = 0; u < 8; u++) if (i0 + u < nb) { a += ta[u]; b += tb[u]; }
+		}
 		out[0] = a; out[1] = b;
 	}
 }

@@ -134,7 +134,7 @@ def test_track_batched_31_hypotheses(ctx_vga, scen_vga):
     single = ctx_vga.track_batched(0, 2, P[7], scen_vga.a0, scen_vga.b0, scen_vga.levels - 1)[0]
     # a different cluster size changes the summation tree, nothing else
     if list(res[7].trace[:res[7].trace_len]) == list(single.trace[:single.trace_len]):
-        assert np.abs(np.array(res[7].pose) - np.array(single.pose)).max() < 1e-7 and res[7].n_evals == single.n_evals
+        assert np.abs(np.array(res[7].pose) - np.array(single.pose)).max() < 1e-6 and res[7].n_evals == single.n_evals   # FP32 sums, two trees
     scen_vga.oracle_set_frame(1)
     good = 0
     for i in (0, 3, 12):
