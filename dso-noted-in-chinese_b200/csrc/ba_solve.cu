@@ -138,6 +138,8 @@ __global__ void ba_fix_lin_kernel(int nR, int nF, const unsigned char* __restric
 }
 
 // ---------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ double shfl_dd(double v, int src) { return __shfl_sync(0xffffffffu, v, src); }
+
 struct SolveArgs
 {
 	int nF, orth, haveL;
@@ -269,81 +271,151 @@ __global__ void __launch_bounds__(SOLVE_NT) ba_solve_kernel(SolveArgs a)
 		}
 		__syncthreads();
 	}
-	// LDL^T of the permuted matrix, lower triangle, right-looking: A(i,j) -= (L(i,k) * L(j,k)) * D(k) for k ascending, then
-	// L(i,j) = A(i,j) / D(j) -- the same operations in the same order per entry as the bordered form Eigen uses.  Every
-	// thread keeps its entries (e = tid + SOLVE_NT q of the packed lower triangle) in registers for the whole factorisation;
-	// per pivot only the current column and the next pivot go through shared memory.
+	// LDL^T of the permuted matrix, lower triangle, right-looking and blocked by panels of PANEL columns:
+	// A(i,j) -= (L(i,k) * L(j,k)) * D(k) for k ascending, L(i,j) = A(i,j) / D(j) -- the same operations in the same order
+	// per entry as the bordered form Eigen uses.  The matrix is first permuted physically (through registers), then per
+	// panel warp 0 factors the PANEL columns in registers (three rows per lane, pivots and pivot rows by shuffle) and all
+	// threads apply the rank-PANEL update to their entries of the trailing matrix: 2 block barriers per PANEL pivots.
 	STAMP(4);
+	constexpr int PANEL = 4;                             // 8 nF + 4 is a multiple of 4
 	constexpr int MAXQ = (NMAX * (NMAX + 1) / 2 + SOLVE_NT - 1) / SOLVE_NT;
 	const int T = N * (N + 1) / 2;
-	double av[MAXQ];
 	int ei[MAXQ], ej[MAXQ];
-#pragma unroll
-	for (int q = 0; q < MAXQ; q++)
 	{
-		const int e = tid + SOLVE_NT * q;
-		int i = (int)((sqrtf(8.f * (float)e + 1.f) - 1.f) * 0.5f);
-		while (i * (i + 1) / 2 > e) i--;
-		while ((i + 1) * (i + 2) / 2 <= e) i++;
-		const int j = e - i * (i + 1) / 2;
-		const bool ok = e < T;
-		ei[q] = ok ? i : -1; ej[q] = ok ? j : -1;
-		av[q] = ok ? A[ord[i] * LDH + ord[j]] : 0.0;
-		if (ok && i == 0) dl[0] = av[q];                 // dl is free again: pivot values D(k)
-		if (ok && j == 0 && i > 0) Lk[i] = av[q];        // column 0, still undivided
-	}
-	__syncthreads();
-	// per pivot: (1) rows k+1.. divide the staged column by D(k) -- one division per thread, on one code path;
-	// (2) the owners update their entries and stage column k+1 (undivided) and D(k+1) for the next pivot.
-	STAMP(5);
-	double* Lc = Lk; double* Ln = dg;                    // dg (pivot search) is free again
-	for (int k = 0; k < N; k++)
-	{
-		const long long c0 = a.dbg ? clock64() : 0;
-		const double d = dl[k];
-		if (tid > k && tid < N) Lc[tid] = (fabs(d) > 0.0) ? __ddiv_rn(Lc[tid], d) : 0.0;
-		__syncthreads();
-		if (a.dbg && tid == 0) a.dbg[10] += clock64() - c0;
-		// a slot is skipped once its row is above the pivot (nearly warp-uniform: consecutive entries share a row)
+		double av[MAXQ];
 #pragma unroll
 		for (int q = 0; q < MAXQ; q++)
 		{
-			if (ei[q] <= k) continue;
-			const double li = Lc[ei[q]];
-			if (ej[q] == k) av[q] = li;
-			else if (ej[q] > k)
+			const int e = tid + SOLVE_NT * q;
+			int i = (int)((sqrtf(8.f * (float)e + 1.f) - 1.f) * 0.5f);
+			while (i * (i + 1) / 2 > e) i--;
+			while ((i + 1) * (i + 2) / 2 <= e) i++;
+			const int j = e - i * (i + 1) / 2;
+			const bool ok = e < T;
+			ei[q] = ok ? i : -1; ej[q] = ok ? j : -1;
+			av[q] = ok ? A[ord[i] * LDH + ord[j]] : 0.0;
+		}
+		__syncthreads();
+#pragma unroll
+		for (int q = 0; q < MAXQ; q++) if (ei[q] >= 0) A[ei[q] * LDH + ej[q]] = av[q];
+		if (tid < N) yv[tid] = rhs[ord[tid]];
+	}
+	__syncthreads();
+	STAMP(5);
+	const int lane = tid & 31;
+	for (int k0 = 0; k0 < N; k0 += PANEL)
+	{
+		if (tid < 32)
+		{
+			double p[3][PANEL];
+#pragma unroll
+			for (int c = 0; c < 3; c++)
 			{
-				const double v = __dsub_rn(av[q], __dmul_rn(__dmul_rn(li, Lc[ej[q]]), d));
-				av[q] = v;
-				if (ej[q] == k + 1) { if (ei[q] == k + 1) dl[k + 1] = v; else Ln[ei[q]] = v; }
+				const int r = k0 + lane + 32 * c;
+#pragma unroll
+				for (int b = 0; b < PANEL; b++) p[c][b] = (r < N && k0 + b <= r) ? A[r * LDH + k0 + b] : 0.0;
+			}
+#pragma unroll
+			for (int b = 0; b < PANEL; b++)
+			{
+				const double d = shfl_dd(p[0][b], b);                      // D(k0+b): row k0+b is lane b, c = 0
+				// column / D: one IEEE reciprocal per pivot, then q0 = p*rd, e = p - q0*d (exact, FMA), q = q0 + e*rd,
+				// which is the correctly rounded quotient (Markstein) -- three FMAs per row instead of a division each
+				const double rd = (fabs(d) > 0.0) ? __ddiv_rn(1.0, d) : 0.0;
+#pragma unroll
+				for (int c = 0; c < 3; c++)
+				{
+					const int r = k0 + lane + 32 * c;
+					if (r > k0 + b && r < N)
+					{
+						const double q0 = __dmul_rn(p[c][b], rd);
+						const double e = __fma_rn(-q0, d, p[c][b]);
+						p[c][b] = (fabs(d) > 0.0) ? __fma_rn(e, rd, q0) : 0.0;
+					}
+				}
+#pragma unroll
+				for (int b2 = b + 1; b2 < PANEL; b2++)
+				{
+					const double lrow = shfl_dd(p[0][b], b2);              // L(k0+b2, k0+b)
+#pragma unroll
+					for (int c = 0; c < 3; c++)
+					{
+						const int r = k0 + lane + 32 * c;
+						if (r >= k0 + b2 && r < N) p[c][b2] = __dsub_rn(p[c][b2], __dmul_rn(__dmul_rn(p[c][b], lrow), d));
+					}
+				}
+			}
+#pragma unroll
+			for (int c = 0; c < 3; c++)
+			{
+				const int r = k0 + lane + 32 * c;
+#pragma unroll
+				for (int b = 0; b < PANEL; b++) if (r < N && k0 + b <= r) A[r * LDH + k0 + b] = p[c][b];
 			}
 		}
 		__syncthreads();
-		double* t = Lc; Lc = Ln; Ln = t;
+		double dk[PANEL];
+#pragma unroll
+		for (int b = 0; b < PANEL; b++) dk[b] = A[(k0 + b) * LDH + k0 + b];
+#pragma unroll
+		for (int q = 0; q < MAXQ; q++)
+		{
+			if (ej[q] < k0 + PANEL) continue;                            // also skips the unused slots (ej = -1)
+			const int i = ei[q], j = ej[q];
+			double li[PANEL], lj[PANEL];
+#pragma unroll
+			for (int b = 0; b < PANEL; b++) { li[b] = A[i * LDH + k0 + b]; lj[b] = A[j * LDH + k0 + b]; }
+			double v = A[i * LDH + j];
+#pragma unroll
+			for (int b = 0; b < PANEL; b++) v = __dsub_rn(v, __dmul_rn(__dmul_rn(li[b], lj[b]), dk[b]));
+			A[i * LDH + j] = v;
+		}
+		__syncthreads();
 	}
 	STAMP(6);
-	// factors back to shared memory in permuted coordinates (the scaled matrix is not needed any more)
+	// solve: permute (done above), L y = b, D, L^T, permute back (:908) -- warp 0 alone, three rows per lane in registers,
+	// pivot entries broadcast by shuffle: no block barrier per column
+	if (tid < 32)
+	{
+		double y[3];
 #pragma unroll
-	for (int q = 0; q < MAXQ; q++) if (ei[q] >= 0) A[ei[q] * LDH + ej[q]] = av[q];
-	// solve: permute, L y = b, D, L^T, permute back (:908)
-	if (tid < N) yv[tid] = rhs[ord[tid]];
+		for (int c = 0; c < 3; c++) y[c] = (lane + 32 * c < N) ? yv[lane + 32 * c] : 0.0;
+		for (int k = 0; k < N; k++)
+		{
+			const double cand = k < 32 ? y[0] : (k < 64 ? y[1] : y[2]);
+			const double yk = shfl_dd(cand, k & 31);
+#pragma unroll
+			for (int c = 0; c < 3; c++)
+			{
+				const int r = lane + 32 * c;
+				if (r > k && r < N) y[c] = __dsub_rn(y[c], __dmul_rn(A[r * LDH + k], yk));
+			}
+		}
+#pragma unroll
+		for (int c = 0; c < 3; c++)
+		{
+			const int r = lane + 32 * c;
+			if (r < N)
+			{
+				const double d = A[r * LDH + r];
+				y[c] = (fabs(d) > 2.2250738585072014e-308) ? __ddiv_rn(y[c], d) : 0.0;
+			}
+		}
+		for (int k = N - 1; k > 0; k--)
+		{
+			const double cand = k < 32 ? y[0] : (k < 64 ? y[1] : y[2]);
+			const double yk = shfl_dd(cand, k & 31);
+#pragma unroll
+			for (int c = 0; c < 3; c++)
+			{
+				const int r = lane + 32 * c;
+				if (r < k) y[c] = __dsub_rn(y[c], __dmul_rn(A[k * LDH + r], yk));
+			}
+		}
+#pragma unroll
+		for (int c = 0; c < 3; c++) if (lane + 32 * c < N) yv[lane + 32 * c] = y[c];
+	}
 	__syncthreads();
-	for (int k = 0; k < N; k++)
-	{
-		if (tid > k && tid < N) yv[tid] = __dsub_rn(yv[tid], __dmul_rn(A[tid * LDH + k], yv[k]));
-		__syncthreads();
-	}
-	if (tid < N)
-	{
-		const double d = A[tid * LDH + tid];
-		yv[tid] = (fabs(d) > 2.2250738585072014e-308) ? __ddiv_rn(yv[tid], d) : 0.0;
-	}
-	__syncthreads();
-	for (int k = N - 1; k > 0; k--)
-	{
-		if (tid < k) yv[tid] = __dsub_rn(yv[tid], __dmul_rn(A[k * LDH + tid], yv[k]));
-		__syncthreads();
-	}
 	STAMP(7);
 	if (tid < N) xv[ord[tid]] = __dmul_rn(sv[ord[tid]], yv[tid]);
 	__syncthreads();
@@ -716,7 +788,7 @@ extern "C" int dso_b200_ba_solve(dso_b200_ctx* ctx, int iteration, double lambda
 	{
 		long long t[11];
 		CK(cudaMemcpy(t, S->d_dbg, sizeof(t), cudaMemcpyDeviceToHost));
-		fprintf(stderr, "ba_solve_kernel cycles: stageHM %lld rhs %lld assemble %lld scale %lld pivots %lld load %lld ldlt %lld subst %lld orth %lld xAd %lld | total %lld | ldlt div phase %lld\n",
+		fprintf(stderr, "ba_solve_kernel cycles: stageHM %lld rhs %lld assemble %lld scale %lld pivots %lld load %lld ldlt %lld subst %lld orth %lld xAd %lld | total %lld | %lld\n",
 		        t[1] - t[0], 0LL, t[2] - t[1], t[3] - t[2], t[4] - t[3], t[5] - t[4], t[6] - t[5], t[7] - t[6], t[8] - t[7], t[9] - t[8], t[9] - t[0], t[10]);
 	}
 	return 0;
