@@ -144,6 +144,18 @@ void dso_oracle_scaled_ldlt_solve(const double* HFinal, const double* bFinal, in
 int dso_oracle_ba_solve(dso_oracle_ba*, int iteration, double lambda, int solverMode, double solverModeDelta, int MT, int nthreads,
                         double* x_out, float* pointStep_out, double* HFinal_out, double* bFinal_out);
 
+/* EnergyFunctional::calcLEnergyF_MT (EnergyFunctional.cpp:411-428 + calcLEnergyPt :346-408, Accumulator11 with its 1k / 1M
+ * tiers) and calcMEnergyF (:334-343).  nthreads <= 1: one accumulator over all points; otherwise one per chunk of 50. */
+double dso_oracle_ba_calc_L_energy(dso_oracle_ba*, int nthreads);
+double dso_oracle_ba_calc_M_energy(dso_oracle_ba*);
+/* EnergyFunctional::marginalizePointsF (EnergyFunctional.cpp:642-703) for the flagged points, without the structural part
+ * (removePoint / makeIDX): priorF *= priorMargFac, addPoint<2> + AccumulatedSCHessianSSE::addPoint(p, false), stitch,
+ * HM += margWeightFac * (M - Msc), bM likewise.  H_out / b_out: M - Msc, Mb - Mbsc.  The residuals of flagged points must
+ * have been linearised (dso_oracle_ba_fix_linearization).  The reference-build variant is destructive (call it last). */
+void dso_oracle_ba_marginalize_points(dso_oracle_ba*, const unsigned char* flags, float priorMargFac, double margWeightFac,
+                                      double* H_out, double* b_out, int* resInM, float* idepth_hessian_out);
+void dso_oracle_ba_get_marg_prior(dso_oracle_ba*, double* HM, double* bM);
+
 #ifdef __cplusplus
 }
 #endif

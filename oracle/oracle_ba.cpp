@@ -884,7 +884,7 @@ static void stitchA(dso_oracle_ba* B, std::vector<std::vector<AccApprox>>& accs,
 
 // accumulateAF_MT, EnergyFunctional.cpp:209-232 + stitchDoubleMT, AccumulatedTopHessian.h:91-139
 static void accumulate_top(dso_oracle_ba* B, int mode, bool usePrior, int MT, int nthreads, double* H, double* b, int* resInA,
-                           float* Hdd, float* bd, float* Hcd4)
+                           float* Hdd, float* bd, float* Hcd4, const unsigned char* pointMask = nullptr)
 {
 	int nF = B->nF, N = 8 * nF + CPARS, nP = (int)B->points.size();
 	int T = MT ? nthreads : 1;
@@ -907,7 +907,7 @@ static void accumulate_top(dso_oracle_ba* B, int mode, bool usePrior, int MT, in
 	}
 	else
 	{
-		for (int i = 0; i < nP; i++) addPointA(B, B->points[i], accs[0].data(), &nres[0], mode);
+		for (int i = 0; i < nP; i++) if (!pointMask || pointMask[i]) addPointA(B, B->points[i], accs[0].data(), &nres[0], mode);
 		stitchA(B, accs, 1, H, b, 0, nF * nF);
 	}
 	if (usePrior)
@@ -1314,4 +1314,144 @@ extern "C" int dso_oracle_ba_solve(dso_oracle_ba* B, int iteration, double lambd
 	if (x_out) memcpy(x_out, x.data(), sizeof(double) * N);
 	if (pointStep_out) memcpy(pointStep_out, B->pointStep.data(), sizeof(float) * B->pointStep.size());
 	return 0;
+}
+
+// =================================================================================================
+// rest of N2: marginalizePointsF (EnergyFunctional.cpp:642-703), calcLEnergyF_MT / calcLEnergyPt (:346-428),
+// calcMEnergyF (:334-343)
+// =================================================================================================
+// Accumulator11, MatrixAccumulators.h:89-170
+struct Acc11
+{
+	float A; float d[4], d1k[4], d1m[4]; float n1, n1k, n1m;
+	void initialize() { A = 0; for (int i = 0; i < 4; i++) d[i] = d1k[i] = d1m[i] = 0; n1 = n1k = n1m = 0; }
+	void shiftUp(bool force)
+	{
+		if (n1 > 1000 || force) { for (int i = 0; i < 4; i++) { d1k[i] = d[i] + d1k[i]; d[i] = 0; } n1k += n1; n1 = 0; }
+		if (n1k > 1000 || force) { for (int i = 0; i < 4; i++) { d1m[i] = d1k[i] + d1m[i]; d1k[i] = 0; } n1m += n1k; n1k = 0; }
+	}
+	void updateSingle(float v) { d[0] += v; n1++; shiftUp(false); }
+	void updateSSENoShift(const float* v4) { for (int i = 0; i < 4; i++) d[i] = d[i] + v4[i]; n1++; }
+	void finish() { shiftUp(true); A = d1m[0] + d1m[1] + d1m[2] + d1m[3]; }
+};
+
+static float lenergy_range(dso_oracle_ba* B, int lo, int hi)
+{
+	Acc11 E; E.initialize();
+	for (int i = lo; i < hi; i++)
+	{
+		Pt& p = B->points[i];
+		for (int ri : p.residualsAll)
+		{
+			Res& r = B->res[ri];
+			if (!r.isLinearized || !r.isActive) continue;
+			const RawJ* rJ = &r.efJ;
+			float d[4];
+			jp_delta(B, r, rJ, p.deltaF, d);
+			for (int k = 0; k + 3 < patternNum; k += 4)
+			{
+				float v[4];
+				for (int q = 0; q < 4; q++)
+				{
+					float Jdelta = rJ->JIdx[0][k + q] * d[0];
+					Jdelta = Jdelta + rJ->JIdx[1][k + q] * d[1];
+					Jdelta = Jdelta + rJ->JabF[0][k + q] * d[2];
+					Jdelta = Jdelta + rJ->JabF[1][k + q] * d[3];
+					float r0 = r.res_toZeroF[k + q];
+					r0 = r0 + r0;
+					r0 = r0 + Jdelta;
+					v[q] = Jdelta * r0;
+				}
+				E.updateSSENoShift(v);
+			}
+		}
+		E.updateSingle(p.deltaF * p.deltaF * p.priorF);
+	}
+	E.finish();
+	return E.A;
+}
+
+// calcLEnergyF_MT: nthreads <= 1 sums all points with one accumulator (what the reference's reduce does for one worker);
+// otherwise chunks of 50 points per accumulator, chunk results added in double in chunk order
+extern "C" double dso_oracle_ba_calc_L_energy(dso_oracle_ba* B, int nthreads)
+{
+	const int nF = B->nF, nP = (int)B->points.size();
+	double E = 0;
+	if ((int)B->framePrior.size() == 8 * nF)
+		for (int h = 0; h < nF; h++)
+		{
+			double e = 0;            // f->delta_prior.cwiseProduct(f->prior).dot(f->delta_prior), dynamic-free Vec8: unrolled redux
+			double t[8];
+			for (int i = 0; i < 8; i++) t[i] = (B->frameDeltaPrior[8 * h + i] * B->framePrior[8 * h + i]) * B->frameDeltaPrior[8 * h + i];
+			e = ((t[0] + t[1]) + (t[2] + t[3])) + ((t[4] + t[5]) + (t[6] + t[7]));
+			E += e;
+		}
+	{
+		float t[4];
+		for (int i = 0; i < 4; i++) t[i] = (B->cDeltaF[i] * (float)B->cPrior[i]) * B->cDeltaF[i];     // cDeltaF.cwiseProduct(cPriorF).dot(cDeltaF)
+		E += (t[0] + t[1]) + (t[2] + t[3]);
+	}
+	double pts = 0;
+	if (nthreads <= 1) pts = lenergy_range(B, 0, nP);
+	else for (int lo = 0; lo < nP; lo += 50) pts += lenergy_range(B, lo, std::min(nP, lo + 50));
+	return E + pts;
+}
+
+// calcMEnergyF: delta.dot(2*bM + HM*delta)
+extern "C" double dso_oracle_ba_calc_M_energy(dso_oracle_ba* B)
+{
+	const int nF = B->nF, N = 8 * nF + CPARS;
+	if ((int)B->bM.size() != N) return 0.0;
+	std::vector<double> d(N);
+	for (int i = 0; i < CPARS; i++) d[i] = (double)B->cDeltaF[i];
+	for (int i = 0; i < 8 * nF; i++) d[CPARS + i] = B->frameDelta[i];
+	double e = 0;
+	for (int i = 0; i < N; i++)
+	{
+		double s = 0;
+		for (int j = 0; j < N; j++) s += B->HM[(size_t)i * N + j] * d[j];
+		e += d[i] * (2 * B->bM[i] + s);
+	}
+	return e;
+}
+
+// marginalizePointsF for the points flagged PS_MARGINALIZE: priorF *= setting_idepthFixPriorMargFac, addPoint<2> +
+// AccumulatedSCHessianSSE::addPoint(p, false), H = M - Msc, HM += setting_margWeightFac * H (likewise b).  The structural
+// part (removePoint, makeIDX) is the caller's.  H_out / b_out: the contribution M - Msc, Mb - Mbsc.
+extern "C" void dso_oracle_ba_marginalize_points(dso_oracle_ba* B, const unsigned char* flags, float priorMargFac, double margWeightFac,
+                                                 double* H_out, double* b_out, int* resInM, float* idepth_hessian_out)
+{
+	const int nF = B->nF, N = 8 * nF + CPARS, nP = (int)B->points.size();
+	if ((int)B->bM.size() != N) dso_oracle_ba_set_priors(B, B->cPrior, 0, 0, 0, 0, 0);
+	for (int i = 0; i < nP; i++) if (flags[i]) B->points[i].priorF *= priorMargFac;
+	std::vector<double> M((size_t)N * N), Mb(N), Msc((size_t)N * N, 0.0), Mbsc(N, 0.0);
+	accumulate_top(B, 2, false, 0, 1, M.data(), Mb.data(), resInM, 0, 0, 0, flags);
+	std::vector<SCAcc> S(1);
+	S[0].setZero(nF);
+	for (int i = 0; i < nP; i++) if (flags[i]) addPointSC(B, B->points[i], false, S[0]);
+	stitchSC(B, S, 1, Msc.data(), Mbsc.data(), 0, nF * nF);
+	for (int h = 0; h < nF; h++)
+	{
+		int hIdx = CPARS + h * 8;
+		for (int i = 0; i < CPARS; i++) for (int j = 0; j < 8; j++) Msc[i * N + hIdx + j] = Msc[(hIdx + j) * N + i];
+	}
+	for (size_t i = 0; i < (size_t)N * N; i++)
+	{
+		const double h = M[i] - Msc[i];
+		if (H_out) H_out[i] = h;
+		B->HM[i] += margWeightFac * h;
+	}
+	for (int i = 0; i < N; i++)
+	{
+		const double v = Mb[i] - Mbsc[i];
+		if (b_out) b_out[i] = v;
+		B->bM[i] += margWeightFac * v;
+	}
+	if (idepth_hessian_out) for (int i = 0; i < nP; i++) idepth_hessian_out[i] = B->points[i].idepth_hessian;
+}
+extern "C" void dso_oracle_ba_get_marg_prior(dso_oracle_ba* B, double* HM, double* bM)
+{
+	const int N = 8 * B->nF + CPARS;
+	if ((int)B->bM.size() != N) dso_oracle_ba_set_priors(B, B->cPrior, 0, 0, 0, 0, 0);
+	memcpy(HM, B->HM.data(), sizeof(double) * N * N); memcpy(bM, B->bM.data(), sizeof(double) * N);
 }

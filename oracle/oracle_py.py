@@ -106,6 +106,10 @@ def lib(kind="oracle"):
     sig("dso_oracle_ba_set_priors", [vp, vp, vp, vp, vp, vp, vp])
     sig("dso_oracle_ba_set_nullspaces", [vp, f64p, C.c_int])
     sig("dso_oracle_ba_fix_linearization", [vp, vp, vp])
+    sig("dso_oracle_ba_calc_L_energy", [vp, C.c_int], C.c_double)
+    sig("dso_oracle_ba_calc_M_energy", [vp], C.c_double)
+    sig("dso_oracle_ba_marginalize_points", [vp, vp, C.c_float, C.c_double, vp, vp, vp, vp])
+    sig("dso_oracle_ba_get_marg_prior", [vp, f64p, f64p])
     sig("dso_oracle_scaled_ldlt_solve", [f64p, f64p, C.c_int, f64p])
     sig("dso_oracle_ba_solve", [vp, C.c_int, C.c_double, C.c_int, C.c_double, C.c_int, C.c_int, vp, vp, vp, vp], C.c_int)
     _LIBS[kind] = L
@@ -337,3 +341,21 @@ class BA:
         if rc != 0:
             raise RuntimeError("solver mode not restated")
         return dict(x=x, step=step, HFinal=HF.reshape(N, N), bFinal=bF)
+
+    def calc_L_energy(self, nthreads=1):
+        return self.L.dso_oracle_ba_calc_L_energy(self.p, nthreads)
+
+    def calc_M_energy(self):
+        return self.L.dso_oracle_ba_calc_M_energy(self.p)
+
+    def marginalize_points(self, flags, prior_marg_fac=600.0 * 600.0, marg_weight_fac=0.25):
+        N = 8 * self.nF + 4
+        flags = np.ascontiguousarray(flags, dtype=np.uint8)
+        H, b = np.zeros(N * N), np.zeros(N)
+        n = C.c_int(0)
+        ih = np.zeros(self.nP, dtype=np.float32)
+        self.L.dso_oracle_ba_marginalize_points(self.p, flags.ctypes.data, prior_marg_fac, marg_weight_fac, H.ctypes.data, b.ctypes.data,
+                                                C.addressof(n), ih.ctypes.data)
+        HM, bM = np.zeros(N * N), np.zeros(N)
+        self.L.dso_oracle_ba_get_marg_prior(self.p, HM, bM)
+        return dict(H=H.reshape(N, N), b=b, resInM=n.value, idepth_hessian=ih, HM=HM.reshape(N, N), bM=bM)

@@ -509,3 +509,46 @@ extern "C" int dso_ref_ba_solve(dso_oracle_ba* B, int iteration, double lambda, 
 	if (pointStep_out) for (size_t i = 0; i < B->pts.size(); i++) pointStep_out[i] = B->pts[i]->step;
 	return 0;
 }
+
+// ---- rest of N2: marginalizePointsF, calcLEnergyF_MT, calcMEnergyF (the reference's own code) ----
+extern "C" double dso_ref_ba_calc_L_energy(dso_oracle_ba* B, int nthreads)
+{
+	(void)nthreads;      // the reference always goes through its 6-worker pool (chunks of 50 points)
+	B->calib();
+	return B->ef->calcLEnergyF_MT();                           // EnergyFunctional.cpp:411
+}
+extern "C" double dso_ref_ba_calc_M_energy(dso_oracle_ba* B)
+{
+	const int N = 8 * B->nF + CPARS;
+	if ((int)B->ef->bM.size() != N) return 0.0;
+	return B->ef->calcMEnergyF();                              // EnergyFunctional.cpp:334
+}
+extern "C" void dso_ref_ba_get_marg_prior(dso_oracle_ba* B, double* HM, double* bM)
+{
+	const int N = 8 * B->nF + CPARS;
+	if ((int)B->ef->bM.size() != N) dso_ref_ba_set_priors(B, 0, 0, 0, 0, 0, 0);
+	for (int r = 0; r < N; r++) { for (int c = 0; c < N; c++) HM[r * N + c] = B->ef->HM(r, c); bM[r] = B->ef->bM[r]; }
+}
+// destructive: marginalizePointsF removes the flagged points from the EnergyFunctional (call it last)
+extern "C" void dso_ref_ba_marginalize_points(dso_oracle_ba* B, const unsigned char* flags, float priorMargFac, double margWeightFac,
+                                              double* H_out, double* b_out, int* resInM, float* idepth_hessian_out)
+{
+	B->calib();
+	const int N = 8 * B->nF + CPARS;
+	if ((int)B->ef->bM.size() != N) dso_ref_ba_set_priors(B, 0, 0, 0, 0, 0, 0);
+	MatXX HM0 = B->ef->HM; VecX bM0 = B->ef->bM;
+	const float f0 = setting_idepthFixPriorMargFac, w0 = setting_margWeightFac;
+	setting_idepthFixPriorMargFac = priorMargFac; setting_margWeightFac = (float)margWeightFac;
+	for (size_t i = 0; i < B->pts.size(); i++)
+		if (flags[i]) B->pts[i]->efPoint->stateFlag = EFPointStatus::PS_MARGINALIZE;
+	const int res0 = B->ef->resInM;
+	B->ef->marginalizePointsF();                               // EnergyFunctional.cpp:642
+	setting_idepthFixPriorMargFac = f0; setting_margWeightFac = w0;
+	if (resInM) *resInM = B->ef->resInM - res0;
+	for (int r = 0; r < N; r++)
+	{
+		for (int c = 0; c < N; c++) if (H_out) H_out[r * N + c] = (B->ef->HM(r, c) - HM0(r, c)) / margWeightFac;
+		if (b_out) b_out[r] = (B->ef->bM[r] - bM0[r]) / margWeightFac;
+	}
+	if (idepth_hessian_out) for (size_t i = 0; i < B->pts.size(); i++) idepth_hessian_out[i] = B->pts[i]->idepth_hessian;
+}

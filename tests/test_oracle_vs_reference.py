@@ -221,3 +221,33 @@ def test_solve_system_and_resubstitute(pkg, window_small, iteration, with_lin):
     assert np.abs(so["x"] - sr["x"]).max() <= 1e-9 * np.abs(sr["x"]).max()
     assert np.abs(so["step"] - sr["step"]).max() <= 1e-5 * np.abs(sr["step"]).max()
     assert np.isfinite(so["step"]).all() and np.abs(so["step"]).max() > 0
+
+
+def test_marginalize_points_and_energies(pkg, window_small):
+    """rest of N2: calcLEnergyF_MT, calcMEnergyF and marginalizePointsF (EnergyFunctional.cpp:334-428, 642-703).  A third of
+    the points are flagged; their residuals are linearised first (FullSystem::flagPointsForRemoval does the same)."""
+    W = window_small
+    pyr = [O.make_images(img, 1)[0][0] for img in W.images]
+    Bo, Br = O.BA(W, pyr), O.BA(W, pyr, kind="ref")
+    inp = _solve_inputs(W)
+    pflags = (np.arange(W.nP) % 3 == 1).astype(np.uint8)
+    rflags = pflags[W.res_point]
+    res = []
+    for B in (Bo, Br):
+        B.linearize()
+        B.apply_res()
+        B.fix_linearization(rflags)
+        B.set_priors(*inp[:6])
+        res.append((B.calc_L_energy(6), B.calc_M_energy()))
+    (Lo, Mo), (Lr, Mr) = res
+    assert abs(Mo - Mr) <= 1e-12 * abs(Mr) and Mr != 0
+    assert abs(Lo - Lr) <= 1e-5 * abs(Lr) and Lr != 0          # float tiers; the reference's chunk -> worker assignment is dynamic
+    mo, mr = Bo.marginalize_points(pflags), Br.marginalize_points(pflags)
+    assert mo["resInM"] == mr["resInM"] > 100
+    sel = pflags == 1
+    assert np.array_equal(bits(mo["idepth_hessian"][sel]), bits(mr["idepth_hessian"][sel]))
+    sc = np.abs(mr["H"]).max()
+    assert np.abs(mo["H"] - mr["H"]).max() <= 1e-9 * sc and sc > 0      # recovered from HM differences in the reference build
+    assert np.abs(mo["b"] - mr["b"]).max() <= 1e-9 * np.abs(mr["b"]).max()
+    assert np.abs(mo["HM"] - mr["HM"]).max() <= 1e-12 * np.abs(mr["HM"]).max()
+    assert np.abs(mo["bM"] - mr["bM"]).max() <= 1e-12 * np.abs(mr["bM"]).max()
