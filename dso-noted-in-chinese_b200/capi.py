@@ -88,6 +88,9 @@ SIGNATURES = {
     "dso_b200_ba_points_backup": (C.c_int, [vp]),
     "dso_b200_ba_points_step": (C.c_int, [vp, C.c_float, vp, vp]),
     "dso_b200_ba_points_restore": (C.c_int, [vp]),
+    "dso_b200_ba_marginalize_points": (C.c_int, [vp, vp, C.c_float, C.c_double, vp, vp, vp, vp]),
+    "dso_b200_ba_get_marg_prior": (C.c_int, [vp, f64p, f64p]),
+    "dso_b200_ba_calc_energies": (C.c_int, [vp, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     "dso_b200_ba_iteration": (C.c_int, [vp, C.c_int, C.c_double, C.c_int, C.c_float, vp, vp, vp]),
     "dso_b200_ba_set_window": (C.c_int, [vp, C.c_int, i32p, C.c_int, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float, f32p]),
     "dso_b200_ba_set_glue": (C.c_int, [vp, vp, f64p, f64p, f32p, f32p]),
@@ -471,6 +474,23 @@ class Context:
         sums = np.zeros(2, dtype=np.float32)
         self._check(self.L.dso_b200_ba_iteration(self.h, iteration, lam, solver_mode, stepfacD, x.ctypes.data, C.byref(e), sums.ctypes.data))
         return dict(x=x, energy=e.value, step_sums=sums)
+
+    def ba_marginalize_points(self, flags, prior_marg_fac=600.0 * 600.0, marg_weight_fac=0.25):
+        N = 8 * self.nF + 4
+        flags = np.ascontiguousarray(flags, dtype=np.uint8)
+        H, b = np.zeros(N * N), np.zeros(N)
+        n = C.c_int(0)
+        ih = np.zeros(self.nP, dtype=np.float32)
+        self._check(self.L.dso_b200_ba_marginalize_points(self.h, flags.ctypes.data, prior_marg_fac, marg_weight_fac, H.ctypes.data,
+                                                          b.ctypes.data, C.addressof(n), ih.ctypes.data))
+        HM, bM = np.zeros(N * N), np.zeros(N)
+        self._check(self.L.dso_b200_ba_get_marg_prior(self.h, HM, bM))
+        return dict(H=H.reshape(N, N), b=b, resInM=n.value, idepth_hessian=ih, HM=HM.reshape(N, N), bM=bM)
+
+    def ba_calc_energies(self):
+        l, m = C.c_double(0), C.c_double(0)
+        self._check(self.L.dso_b200_ba_calc_energies(self.h, C.byref(l), C.byref(m)))
+        return l.value, m.value
 
     def ba_step(self):
         N = 8 * self.nF + 4

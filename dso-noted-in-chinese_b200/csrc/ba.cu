@@ -78,7 +78,7 @@ static void free_points(BAWorkspace* W)
 	if (!W->capP) return;
 	cudaFree(W->d_pt); cudaFree(W->d_color); cudaFree(W->d_weights); cudaFree(W->d_phost); cudaFree(W->d_priorF); cudaFree(W->d_deltaF);
 	cudaFree(W->d_res_begin); cudaFree(W->d_Hdd); cudaFree(W->d_bd); cudaFree(W->d_Hcd); cudaFree(W->d_HdiF); cudaFree(W->d_bdSumF); cudaFree(W->d_idh);
-	cudaFree(W->d_Hdd_L); cudaFree(W->d_bd_L); cudaFree(W->d_Hcd_L); cudaFree(W->d_HcdSum);
+	cudaFree(W->d_Hdd_L); cudaFree(W->d_bd_L); cudaFree(W->d_Hcd_L); cudaFree(W->d_HcdSum); cudaFree(W->d_HdiF_m); cudaFree(W->d_bdSumF_m);
 	if (W->capPC) { cudaFree(W->d_pc_start); cudaFree(W->d_pc_cnt); cudaFree(W->d_pc_host); cudaFree(W->d_scPartials); }
 	W->capP = 0; W->capPC = 0;
 }
@@ -381,7 +381,7 @@ __global__ void __launch_bounds__(128) ba_accum_top_kernel(const int* __restrict
 	if (tid < cnt)
 	{
 		const int r = perm[start + tid];
-		const bool act = isAct[r] && (MODE == 0 ? !isLin[r] : isLin[r] != 0);   // :55-62
+		const bool act = isAct[r] && (MODE == 0 ? !isLin[r] : (MODE == 1 ? isLin[r] != 0 : LA.pmask[LA.rpoint[r]] != 0));   // :55-67
 		float x[10], y[10], w[15];
 		if (act)
 		{
@@ -395,6 +395,12 @@ __global__ void __launch_bounds__(128) ba_accum_top_kernel(const int* __restrict
 			{
 #pragma unroll
 				for (int i = 0; i < 8; i++) res[i] = J[J_RESF + i];
+			}
+			else if (MODE == 2)
+			{
+				const float* tz = LA.resToZero + 8 * (size_t)r;           // marginalise: resApprox = res_toZeroF (:71-72)
+#pragma unroll
+				for (int i = 0; i < 8; i++) res[i] = tz[i];
 			}
 			else
 			{
@@ -490,10 +496,12 @@ __global__ void __launch_bounds__(128) ba_accum_top_kernel(const int* __restrict
 // per-point sums in EFPoint::residualsAll order, AccumulatedTopHessian.cpp:142-160
 __global__ void ba_point_sums_kernel(int nP, const int* __restrict__ res_begin, const unsigned char* __restrict__ isAct,
                                      const unsigned char* __restrict__ isLin, const float* __restrict__ contrib,
-                                     float* Hdd, float* bd, float* Hcd, int mode)
+                                     float* Hdd, float* bd, float* Hcd, int mode, const unsigned char* __restrict__ pmask,
+                                     float* Hdd_A, float* bd_A, float* Hcd_A)
 {
 	const int p = blockIdx.x * blockDim.x + threadIdx.x;
 	if (p >= nP) return;
+	if (mode == 2 && !pmask[p]) return;                        // addPoint<2> only visits the points being marginalised
 	float bd_acc = 0.f, Hdd_acc = 0.f, h0 = 0.f, h1 = 0.f, h2 = 0.f, h3 = 0.f;
 	const int r1 = res_begin[p + 1];
 	for (int r0 = res_begin[p]; r0 < r1; r0 += 4)              // four residuals' loads in flight, sums in residualsAll order
@@ -503,7 +511,7 @@ __global__ void ba_point_sums_kernel(int nP, const int* __restrict__ res_begin, 
 		for (int u = 0; u < 4; u++)
 		{
 			const int r = r0 + u;
-			use[u] = r < r1 && isAct[r] && (mode == 0 ? !isLin[r] : isLin[r] != 0);
+			use[u] = r < r1 && isAct[r] && (mode == 0 ? !isLin[r] : (mode == 1 ? isLin[r] != 0 : true));
 #pragma unroll
 			for (int k = 0; k < 6; k++) c[u][k] = use[u] ? contrib[6 * (size_t)r + k] : 0.f;
 		}
@@ -517,6 +525,11 @@ __global__ void ba_point_sums_kernel(int nP, const int* __restrict__ res_begin, 
 	}
 	Hdd[p] = Hdd_acc; bd[p] = bd_acc;
 	Hcd[4 * p] = h0; Hcd[4 * p + 1] = h1; Hcd[4 * p + 2] = h2; Hcd[4 * p + 3] = h3;
+	if (mode == 2)                                              // :168-175: the AF sums of a marginalised point are zero
+	{
+		Hdd_A[p] = 0.f; bd_A[p] = 0.f;
+		Hcd_A[4 * p] = 0.f; Hcd_A[4 * p + 1] = 0.f; Hcd_A[4 * p + 2] = 0.f; Hcd_A[4 * p + 3] = 0.f;
+	}
 }
 
 // index of entry (i,j) of the symmetric 13x13 block in the 91-vector written by ba_accum_top_kernel
@@ -728,10 +741,19 @@ __global__ void ba_schur_prep_kernel(int nP, const int* __restrict__ res_begin, 
                                      const float* __restrict__ Hdd, const float* __restrict__ bd, const float* __restrict__ Hcd,
                                      const float* __restrict__ Hdd_L, const float* __restrict__ bd_L, const float* __restrict__ Hcd_L,
                                      const float* __restrict__ priorF, const float* __restrict__ deltaF,
-                                     float* HdiF, float* bdSumF, float* idh, float* HcdSum)
+                                     float* HdiF, float* bdSumF, float* idh, float* HcdSum, const unsigned char* __restrict__ pmask)
 {
 	const int p = blockIdx.x * blockDim.x + threadIdx.x;
 	if (p >= nP) return;
+	// marginalisation pass (pmask != NULL): only the flagged points contribute (weight HdiF = 0 for the others, their
+	// idepth_hessian is left alone) and the prior is not shifted (addPoint(p, false), EnergyFunctional.cpp:670)
+	if (pmask && !pmask[p])
+	{
+#pragma unroll
+		for (int k = 0; k < 4; k++) HcdSum[4 * p + k] = 0.f;
+		HdiF[p] = 0.f; bdSumF[p] = 0.f;
+		return;
+	}
 #pragma unroll
 	for (int k = 0; k < 4; k++) HcdSum[4 * p + k] = fadd(Hcd[4 * p + k], Hcd_L[4 * p + k]);   // Hcd_accAF + Hcd_accLF (:62)
 	int ngood = 0;
@@ -742,7 +764,7 @@ __global__ void ba_schur_prep_kernel(int nP, const int* __restrict__ res_begin, 
 	idh[p] = H;
 	HdiF[p] = (float)(1.0 / (double)H);
 	float bs = fadd(bd[p], bd_L[p]);
-	bs = fadd(bs, fmul(priorF[p], deltaF[p]));            // shiftPriorToZero = true (EnergyFunctional.cpp:263, 271)
+	if (!pmask) bs = fadd(bs, fmul(priorF[p], deltaF[p]));   // shiftPriorToZero = true (EnergyFunctional.cpp:263, 271)
 	bdSumF[p] = bs;
 }
 
@@ -1022,6 +1044,7 @@ extern "C" int dso_b200_ba_set_points(dso_b200_ctx* ctx, int nP, const float* u,
 		CK(cudaMalloc(&W->d_HdiF, n * sizeof(float))); CK(cudaMalloc(&W->d_bdSumF, n * sizeof(float))); CK(cudaMalloc(&W->d_idh, n * sizeof(float)));
 		CK(cudaMalloc(&W->d_Hdd_L, n * sizeof(float))); CK(cudaMalloc(&W->d_bd_L, n * sizeof(float))); CK(cudaMalloc(&W->d_Hcd_L, n * 4 * sizeof(float)));
 		CK(cudaMalloc(&W->d_HcdSum, n * 4 * sizeof(float)));
+		CK(cudaMalloc(&W->d_HdiF_m, n * sizeof(float))); CK(cudaMalloc(&W->d_bdSumF_m, n * sizeof(float)));
 		W->capP = nP;
 	}
 	// *_accLF start at zero: accumulateLF_MT overwrites them when there are linearised residuals
@@ -1353,42 +1376,46 @@ int ba_enqueue_apply(dso_b200_ctx* ctx)
 }
 
 // mode 0: accumulateAF_MT -> d_HA, d_bA, per-point AF sums; mode 1: accumulateLF_MT -> d_HL, d_bL (+ priors), per-point LF sums
-int ba_enqueue_top(dso_b200_ctx* ctx, int mode)
+int ba_enqueue_top(dso_b200_ctx* ctx, int mode, const unsigned char* d_pmask)
 {
 	BAWorkspace* W = ctx->ba;
 	const int nF = W->P.nF;
 	cudaStream_t st = ctx->stream;
 	BALinArgs LA;
 	LA.rpoint = W->d_rpoint; LA.rtarget = W->d_rtarget; LA.phost = W->d_phost; LA.deltaF = W->d_deltaF;
-	LA.adHTdeltaF = W->d_adHTdeltaF; LA.cDeltaF = W->d_cDeltaF; LA.resToZero = W->d_resToZero; LA.nF = nF;
+	LA.adHTdeltaF = W->d_adHTdeltaF; LA.cDeltaF = W->d_cDeltaF; LA.resToZero = W->d_resToZero; LA.nF = nF; LA.pmask = d_pmask;
 	float* Hdd = mode ? W->d_Hdd_L : W->d_Hdd; float* bd = mode ? W->d_bd_L : W->d_bd; float* Hcd = mode ? W->d_Hcd_L : W->d_Hcd;
 	double* Hout = mode ? W->d_HL : W->d_HA; double* bout = mode ? W->d_bL : W->d_bA;
-	if (mode == 0)
+	if (mode == 2)
+		ba_accum_top_kernel<2><<<W->nChunks, 128, 0, st>>>(W->d_perm, W->d_chunk_start, W->d_chunk_cnt, W->d_isAct, W->d_isLin, W->d_efsel,
+		                                                 W->d_J[0], W->d_J[1], W->d_contrib, W->d_topPartials, W->d_chunk_nres, LA);
+	else if (mode == 0)
 		ba_accum_top_kernel<0><<<W->nChunks, 128, 0, st>>>(W->d_perm, W->d_chunk_start, W->d_chunk_cnt, W->d_isAct, W->d_isLin, W->d_efsel,
 		                                                 W->d_J[0], W->d_J[1], W->d_contrib, W->d_topPartials, W->d_chunk_nres, LA);
 	else
 		ba_accum_top_kernel<1><<<W->nChunks, 128, 0, st>>>(W->d_perm, W->d_chunk_start, W->d_chunk_cnt, W->d_isAct, W->d_isLin, W->d_efsel,
 		                                                 W->d_J[0], W->d_J[1], W->d_contrib, W->d_topPartials, W->d_chunk_nres, LA);
-	ba_point_sums_kernel<<<(W->P.nP + 127) / 128, 128, 0, st>>>(W->P.nP, W->d_res_begin, W->d_isAct, W->d_isLin, W->d_contrib, Hdd, bd, Hcd, mode);
+	ba_point_sums_kernel<<<(W->P.nP + 127) / 128, 128, 0, st>>>(W->P.nP, W->d_res_begin, W->d_isAct, W->d_isLin, W->d_contrib, Hdd, bd, Hcd, mode, d_pmask, W->d_Hdd, W->d_bd, W->d_Hcd);
 	ba_reduce_partials_kernel<<<dim3(1, nF * nF), NTOP_PAD, 0, st>>>(W->d_topPartials, NTOP_PAD, NTOP_PAD, W->d_pair_chunk_begin, W->d_topRed);
 	ba_top_pair_kernel<<<nF * nF, 256, 0, st>>>(nF, W->d_topRed, W->d_adHost, W->d_adTarget, W->d_topContrib);
 	ba_top_gather_kernel<<<nF * nF + 1, 64, 0, st>>>(nF, W->nChunks, W->d_chunk_nres, W->d_topContrib, Hout, bout, W->d_scalars + (mode ? 2 : 0),
-	                                               mode ? W->d_priorH : nullptr, W->d_priorD, W->d_cDeltaF);
+	                                               mode == 1 ? W->d_priorH : nullptr, W->d_priorD, W->d_cDeltaF);
 	ctx->launches += 5;
 	CK(cudaGetLastError());
 	if (mode == 0) W->top_done = true;
 	return 0;
 }
 
-int ba_enqueue_schur(dso_b200_ctx* ctx)
+int ba_enqueue_schur(dso_b200_ctx* ctx, const unsigned char* d_pmask)
 {
 	BAWorkspace* W = ctx->ba;
 	const int nF = W->P.nF, nP = W->P.nP;
+	float* HdiF = d_pmask ? W->d_HdiF_m : W->d_HdiF; float* bdSumF = d_pmask ? W->d_bdSumF_m : W->d_bdSumF;
 	ba_schur_prep_kernel<<<(nP + 127) / 128, 128, 0, ctx->stream>>>(nP, W->d_res_begin, W->d_isAct, W->d_Hdd, W->d_bd, W->d_Hcd,
 	                                                              W->d_Hdd_L, W->d_bd_L, W->d_Hcd_L, W->d_priorF, W->d_deltaF,
-	                                                              W->d_HdiF, W->d_bdSumF, W->d_idh, W->d_HcdSum);
+	                                                              HdiF, bdSumF, W->d_idh, W->d_HcdSum, d_pmask);
 	ba_schur_accum_kernel<<<W->nPC, 256, 0, ctx->stream>>>(nF, W->d_pc_start, W->d_pc_cnt, W->d_res_begin, W->d_rtarget, W->d_isAct, W->d_JpJdF,
-	                                                     W->d_HdiF, W->d_bdSumF, W->d_HcdSum, W->d_scPartials, W->scN);
+	                                                     HdiF, bdSumF, W->d_HcdSum, W->d_scPartials, W->scN);
 	const int nRed = nF * nF * 64 + nF * 32 + nF * 8 + 20;          // accD, accE, accEB, accHcc + accbc per host
 	ba_reduce_partials_kernel<<<dim3((nRed + 255) / 256, nF), 256, 0, ctx->stream>>>(W->d_scPartials, W->scN, nRed, W->d_host_pc_begin, W->d_scRed);
 	ba_schur_stage1_kernel<<<nF * nF, 64, 0, ctx->stream>>>(nF, W->d_scRed, nRed, W->d_adHost, W->d_adTarget, W->d_scContrib);

@@ -48,6 +48,7 @@ struct BALinArgs
 {
 	const int* rpoint; const int* rtarget; const int* phost; const float* deltaF;
 	const float* adHTdeltaF; const float* cDeltaF; const float* resToZero;
+	const unsigned char* pmask;        // mode 2: points flagged PS_MARGINALIZE
 	int nF;
 };
 
@@ -90,7 +91,8 @@ struct BAWorkspace
 	// linearised residuals (accumulateLF_MT) and priors
 	float* d_adHTdeltaF; float* d_cDeltaF; float h_cDeltaF[4];                   // EnergyFunctional::setDeltaF
 	float* d_resToZero;                                                          // EFResidual::res_toZeroF [nR*8]
-	float* d_Hdd_L; float* d_bd_L; float* d_Hcd_L; float* d_HcdSum;              // per point: *_accLF, Hcd_accAF + Hcd_accLF
+	float* d_Hdd_L; float* d_bd_L; float* d_Hcd_L; float* d_HcdSum;
+	float* d_HdiF_m; float* d_bdSumF_m;                                          // scratch of the marginalisation pass (per point)              // per point: *_accLF, Hcd_accAF + Hcd_accLF
 	double* d_HL; double* d_bL;                                                  // d_scalars[3] = resInL
 	double* d_priorH; double* d_priorD; double* d_delta;                         // [8nF+4]: prior, delta_prior, delta (entries 0..3 of the deltas: cDeltaF)
 	int nLin;                                                                    // linearised residuals (-1: unknown)
@@ -132,8 +134,8 @@ static int ba_run_graphed(dso_b200_ctx* ctx, BAGraph& g, unsigned long long key,
 int ba_check_ready(dso_b200_ctx* ctx, const char* fn);
 int ba_enqueue_linearize(dso_b200_ctx* ctx);
 int ba_enqueue_apply(dso_b200_ctx* ctx);
-int ba_enqueue_top(dso_b200_ctx* ctx, int mode);
-int ba_enqueue_schur(dso_b200_ctx* ctx);
+int ba_enqueue_top(dso_b200_ctx* ctx, int mode, const unsigned char* d_pmask = nullptr);
+int ba_enqueue_schur(dso_b200_ctx* ctx, const unsigned char* d_pmask = nullptr);
 void ba_solve_destroy(BAWorkspace* W);
 
 #define BA_CHECK(cond, msg) do { if (!(cond)) { dso_set_error("%s: %s", __func__, msg); return DSO_B200_E_STATE; } } while (0)

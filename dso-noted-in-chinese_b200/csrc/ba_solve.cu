@@ -35,6 +35,7 @@ struct BASolve
 	int capP, capR;
 	float* d_step; float* d_idepth_backup; double* d_stepBlocks; unsigned char* d_which;
 	double* h_x;                                     // pinned: x (NMAX), step sums (4)
+	unsigned char* d_pmask; int capPm; double* d_margH; double* d_eblocks;   // marginalisation / energy scratch
 	long long* d_dbg;                                // DSO_B200_SOLVE_TIMING=1: clock64 stamps of ba_solve_kernel's phases
 	bool priors_set;
 };
@@ -89,6 +90,8 @@ void ba_solve_destroy(BAWorkspace* W)
 	if (S->capR) cudaFree(S->d_which);
 	cudaFreeHost(S->h_x);
 	if (S->d_dbg) cudaFree(S->d_dbg);
+	if (S->capPm) { cudaFree(S->d_pmask); cudaFree(S->d_eblocks); }
+	if (S->d_margH) cudaFree(S->d_margH);
 	delete S;
 	W->S = nullptr;
 }
@@ -895,5 +898,207 @@ extern "C" int dso_b200_ba_points_restore(dso_b200_ctx* ctx)
 	ctx->launches++;
 	CK(cudaGetLastError());
 	W->lin_done = false; W->top_done = false;
+	return 0;
+}
+
+// =========================================================================================================
+// rest of N2: marginalizePointsF (EnergyFunctional.cpp:642-703), calcLEnergyF_MT (:346-428), calcMEnergyF (:334-343)
+// =========================================================================================================
+__global__ void ba_marg_prior_kernel(int nP, const unsigned char* __restrict__ pmask, float fac, float* priorF)
+{
+	const int p = blockIdx.x * blockDim.x + threadIdx.x;
+	if (p < nP && pmask[p]) priorF[p] = fmul(priorF[p], fac);          // :656 p->priorF *= setting_idepthFixPriorMargFac
+}
+
+// H = M - Msc, b = Mb - Mbsc (:681-682); HM += w H, bM += w b (:694-695)
+__global__ void ba_marg_combine_kernel(int N, double w, const double* __restrict__ M, const double* __restrict__ Mb,
+                                       const double* __restrict__ Msc, const double* __restrict__ Mbsc,
+                                       double* H, double* b, double* HM, double* bM)
+{
+	const int e = blockIdx.x * blockDim.x + threadIdx.x;
+	if (e < N * N)
+	{
+		const double h = __dsub_rn(M[e], Msc[e]);
+		H[e] = h;
+		HM[e] = __dadd_rn(HM[e], __dmul_rn(w, h));
+	}
+	if (e < N)
+	{
+		const double v = __dsub_rn(Mb[e], Mbsc[e]);
+		b[e] = v;
+		bM[e] = __dadd_rn(bM[e], __dmul_rn(w, v));
+	}
+}
+
+// calcLEnergyPt (:346-408) per point: the float terms of the reference (Jdelta * (2 res_toZero + Jdelta) per pattern pixel of
+// every linearised active residual, deltaF^2 priorF), summed in FP64 by a fixed tree instead of the Accumulator11 float tiers
+__global__ void __launch_bounds__(256) ba_lenergy_kernel(int nP, int nF, const int* __restrict__ res_begin, const int* __restrict__ rtarget,
+                                                         const int* __restrict__ phost, const unsigned char* __restrict__ isAct,
+                                                         const unsigned char* __restrict__ isLin, const unsigned char* __restrict__ efsel,
+                                                         const float* __restrict__ J0, const float* __restrict__ J1,
+                                                         const float* __restrict__ resToZero, const float* __restrict__ adHTdeltaF,
+                                                         const float* __restrict__ cDeltaF, const float* __restrict__ deltaF,
+                                                         const float* __restrict__ priorF, double* blocks)
+{
+	__shared__ double s[256];
+	const int p = blockIdx.x * 256 + threadIdx.x;
+	double e = 0.0;
+	if (p < nP)
+	{
+		const float dd = deltaF[p];
+		const int h = phost[p];
+		for (int r = res_begin[p]; r < res_begin[p + 1]; r++)
+		{
+			if (!isLin[r] || !isAct[r]) continue;
+			const float* J = (efsel[r] ? J1 : J0) + (size_t)r * JSZ;
+			float d[4];
+			jp_delta(J, adHTdeltaF + 8 * (h + nF * rtarget[r]), cDeltaF, dd, d);
+#pragma unroll
+			for (int i = 0; i < 8; i++)
+			{
+				float Jd = fmul(J[J_IDX0 + i], d[0]);
+				Jd = fadd(Jd, fmul(J[J_IDX1 + i], d[1]));
+				Jd = fadd(Jd, fmul(J[J_AB0 + i], d[2]));
+				Jd = fadd(Jd, fmul(J[J_AB1 + i], d[3]));
+				float r0 = resToZero[8 * (size_t)r + i];
+				r0 = fadd(r0, r0);
+				r0 = fadd(r0, Jd);
+				e += (double)fmul(Jd, r0);
+			}
+		}
+		e += (double)fmul(fmul(dd, dd), priorF[p]);
+	}
+	s[threadIdx.x] = e;
+	__syncthreads();
+	for (int o = 128; o > 0; o >>= 1)
+	{
+		if (threadIdx.x < o) s[threadIdx.x] += s[threadIdx.x + o];
+		__syncthreads();
+	}
+	if (threadIdx.x == 0) blocks[blockIdx.x] = s[0];
+}
+
+// out[0] = calcLEnergyF_MT: frame and calibration prior terms (:416-420) + the point blocks; out[1] = calcMEnergyF
+__global__ void __launch_bounds__(128) ba_energy_final_kernel2(int nF, int nb, const double* __restrict__ blocks, const double* __restrict__ priorH,
+                                                               const double* __restrict__ priorD, const double* __restrict__ delta,
+                                                               const float* __restrict__ cDeltaF, const double* __restrict__ HM,
+                                                               const double* __restrict__ bM, double* out)
+{
+	__shared__ double s[128];
+	const int tid = threadIdx.x, N = 8 * nF + CPARS;
+	double m = 0.0;                                            // delta . (2 bM + HM delta)
+	if (tid < N)
+	{
+		double acc = 0.0;
+		for (int j = 0; j < N; j++) acc = __dadd_rn(acc, __dmul_rn(HM[(size_t)tid * N + j], j < CPARS ? (double)cDeltaF[j] : delta[j]));
+		const double di = tid < CPARS ? (double)cDeltaF[tid] : delta[tid];
+		m = di * (2.0 * bM[tid] + acc);
+	}
+	s[tid] = m;
+	__syncthreads();
+	if (tid == 0)
+	{
+		double t = 0;
+		for (int i = 0; i < N; i++) t += s[i];
+		out[1] = t;
+		double E = 0.0;
+		for (int h = 0; h < nF; h++)
+		{
+			double q[8];
+			for (int i = 0; i < 8; i++) { const int k = CPARS + 8 * h + i; q[i] = (priorD[k] * priorH[k]) * priorD[k]; }
+			E += ((q[0] + q[1]) + (q[2] + q[3])) + ((q[4] + q[5]) + (q[6] + q[7]));
+		}
+		float c[4];
+		for (int i = 0; i < 4; i++) c[i] = fmul(fmul(cDeltaF[i], (float)priorH[i]), cDeltaF[i]);
+		E += (double)fadd(fadd(c[0], c[1]), fadd(c[2], c[3]));
+		double pts = 0.0;
+		for (int i = 0; i < nb; i++) pts += blocks[i];
+		out[0] = E + pts;
+	}
+}
+
+static int marg_buffers(dso_b200_ctx* ctx, BASolve* S)
+{
+	BAWorkspace* W = ctx->ba;
+	if (!S->d_margH) CK(cudaMalloc(&S->d_margH, ((size_t)NMAX * NMAX + NMAX) * sizeof(double)));
+	if (W->P.nP > S->capPm)
+	{
+		if (S->capPm) { cudaFree(S->d_pmask); cudaFree(S->d_eblocks); }
+		CK(cudaMalloc(&S->d_pmask, (size_t)W->P.nP));
+		CK(cudaMalloc(&S->d_eblocks, ((size_t)W->P.nP / 256 + 1) * sizeof(double)));
+		S->capPm = W->P.nP;
+	}
+	return 0;
+}
+
+extern "C" int dso_b200_ba_marginalize_points(dso_b200_ctx* ctx, const unsigned char* point_flags, float idepthFixPriorMargFac,
+                                              double margWeightFac, double* H_out, double* b_out, int* resInM, float* idepth_hessian_out)
+{
+	int rc = ba_check_ready(ctx, __func__);
+	if (rc) return rc;
+	ARG_CHECK(point_flags, "null flags");
+	CK(cudaSetDevice(ctx->device));
+	BAWorkspace* W = ctx->ba;
+	BASolve* S;
+	if ((rc = solve_state(ctx, &S))) return rc;
+	if ((rc = marg_buffers(ctx, S))) return rc;
+	const int nP = W->P.nP, N = 8 * W->P.nF + CPARS;
+	cudaStream_t s = ctx->stream;
+	CK(cudaMemcpyAsync(S->d_pmask, point_flags, (size_t)nP, cudaMemcpyHostToDevice, s));
+	ba_marg_prior_kernel<<<(nP + 255) / 256, 256, 0, s>>>(nP, S->d_pmask, idepthFixPriorMargFac, W->d_priorF);
+	ctx->launches++;
+	if ((rc = ba_enqueue_top(ctx, 2, S->d_pmask))) return rc;      // accSSE_top_A->addPoint<2> + stitchDouble -> d_HL, d_bL
+	if ((rc = ba_enqueue_schur(ctx, S->d_pmask))) return rc;       // accSSE_bot->addPoint(p, false) + stitchDouble -> d_HS, d_bS
+	double* dH = S->d_margH; double* db = S->d_margH + (size_t)NMAX * NMAX;
+	ba_marg_combine_kernel<<<(N * N + 255) / 256, 256, 0, s>>>(N, margWeightFac, W->d_HL, W->d_bL, W->d_HS, W->d_bS, dH, db, S->d_HM, S->d_bM);
+	ctx->launches++;
+	CK(cudaGetLastError());
+	if (H_out) CK(cudaMemcpyAsync(H_out, dH, (size_t)N * N * sizeof(double), cudaMemcpyDeviceToHost, s));
+	if (b_out) CK(cudaMemcpyAsync(b_out, db, N * sizeof(double), cudaMemcpyDeviceToHost, s));
+	if (idepth_hessian_out) CK(cudaMemcpyAsync(idepth_hessian_out, W->d_idh, (size_t)nP * sizeof(float), cudaMemcpyDeviceToHost, s));
+	CK(cudaMemcpyAsync(S->h_x + NMAX, W->d_scalars + 2, 2 * sizeof(double), cudaMemcpyDeviceToHost, s));
+	CK(cudaStreamSynchronize(s));
+	if (resInM) *resInM = (int)S->h_x[NMAX + 1];
+	W->top_done = false; W->lin_done = false;
+	ba_graphs_invalidate(W);
+	return 0;
+}
+
+extern "C" int dso_b200_ba_get_marg_prior(dso_b200_ctx* ctx, double* HM_out, double* bM_out)
+{
+	ARG_CHECK(ctx && ctx->ba && HM_out && bM_out, "null argument");
+	BAWorkspace* W = ctx->ba;
+	BA_CHECK(W->window_set, "call dso_b200_ba_set_window first");
+	CK(cudaSetDevice(ctx->device));
+	BASolve* S;
+	int rc = solve_state(ctx, &S);
+	if (rc) return rc;
+	const int N = 8 * W->P.nF + CPARS;
+	CK(cudaMemcpyAsync(HM_out, S->d_HM, (size_t)N * N * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+	CK(cudaMemcpyAsync(bM_out, S->d_bM, N * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+	CK(cudaStreamSynchronize(ctx->stream));
+	return 0;
+}
+
+extern "C" int dso_b200_ba_calc_energies(dso_b200_ctx* ctx, double* L_energy, double* M_energy)
+{
+	int rc = ba_check_ready(ctx, __func__);
+	if (rc) return rc;
+	CK(cudaSetDevice(ctx->device));
+	BAWorkspace* W = ctx->ba;
+	BASolve* S;
+	if ((rc = solve_state(ctx, &S))) return rc;
+	if ((rc = marg_buffers(ctx, S))) return rc;
+	const int nP = W->P.nP, nb = (nP + 255) / 256;
+	cudaStream_t s = ctx->stream;
+	ba_lenergy_kernel<<<nb, 256, 0, s>>>(nP, W->P.nF, W->d_res_begin, W->d_rtarget, W->d_phost, W->d_isAct, W->d_isLin, W->d_efsel, W->d_J[0], W->d_J[1],
+	                                     W->d_resToZero, W->d_adHTdeltaF, W->d_cDeltaF, W->d_deltaF, W->d_priorF, S->d_eblocks);
+	ba_energy_final_kernel2<<<1, 128, 0, s>>>(W->P.nF, nb, S->d_eblocks, W->d_priorH, W->d_priorD, W->d_delta, W->d_cDeltaF, S->d_HM, S->d_bM, W->d_scalars + 6);
+	ctx->launches += 2;
+	CK(cudaGetLastError());
+	CK(cudaMemcpyAsync(S->h_x + NMAX, W->d_scalars + 6, 2 * sizeof(double), cudaMemcpyDeviceToHost, s));
+	CK(cudaStreamSynchronize(s));
+	if (L_energy) *L_energy = S->h_x[NMAX];
+	if (M_energy) *M_energy = S->h_x[NMAX + 1];
 	return 0;
 }

@@ -216,13 +216,19 @@ public:
 		DSO_B200_CHECK(dso_b200_ba_solve(dev->ctx, iteration, lambda, setting_solverMode, lastX.v.data(), 0, 0, 0));
 		currentLambda = 0;
 	}
+	// void marginalizePointsF()   EnergyFunctional.cpp:642 (accumulation + HM/bM update; removePoint/makeIDX stay with the caller)
+	void marginalizePointsF(const unsigned char* isMarginalizeFlag, float setting_idepthFixPriorMargFac, double setting_margWeightFac)
+	{ DSO_B200_CHECK(dso_b200_ba_marginalize_points(dev->ctx, isMarginalizeFlag, setting_idepthFixPriorMargFac, setting_margWeightFac, 0, 0, &resInM, 0)); }
+	// double calcLEnergyF_MT() / double calcMEnergyF()   EnergyFunctional.cpp:411, :334
+	double calcLEnergyF_MT() { double l = 0, m = 0; DSO_B200_CHECK(dso_b200_ba_calc_energies(dev->ctx, &l, &m)); return l; }
+	double calcMEnergyF() { double l = 0, m = 0; DSO_B200_CHECK(dso_b200_ba_calc_energies(dev->ctx, &l, &m)); return m; }
 	// point loops of FullSystem::backupState / doStepFromBackup / loadSateBackup (FullSystemOptimize.cpp:225-345)
 	void backupStatePoints() { DSO_B200_CHECK(dso_b200_ba_points_backup(dev->ctx)); }
 	void doStepFromBackupPoints(float stepfacD, float& sumID, float& sumNID) { float s[2]; DSO_B200_CHECK(dso_b200_ba_points_step(dev->ctx, stepfacD, s, 0)); sumID = s[0]; sumNID = s[1]; }
 	void loadStateBackupPoints() { DSO_B200_CHECK(dso_b200_ba_points_restore(dev->ctx)); }
 
 	int nFrames, nPoints, nResiduals;
-	int resInA, resInL;
+	int resInA, resInL, resInM = 0;
 	VecX lastX;
 	double currentLambda;
 private:

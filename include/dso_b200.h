@@ -329,6 +329,21 @@ int dso_b200_ba_points_restore(dso_b200_ctx* ctx);
  * calls dso_b200_ba_set_frames before the next one. */
 int dso_b200_ba_iteration(dso_b200_ctx* ctx, int iteration, double lambda, int solverMode, float stepfacD,
                           double* x_out, double* energy_sum, float* step_sums2);
+/* EnergyFunctional::marginalizePointsF (EnergyFunctional.cpp:642-703) for the points flagged PS_MARGINALIZE (point_flags, nP
+ * bytes), whose active residuals have been linearised (dso_b200_ba_fix_linearization, as FullSystem::flagPointsForRemoval
+ * does): priorF *= idepthFixPriorMargFac, AccumulatedTopHessianSSE::addPoint<2> + AccumulatedSCHessianSSE::addPoint(p, false),
+ * both stitched, H = M - Msc, b = Mb - Mbsc, and on the device HM += margWeightFac * H, bM += margWeightFac * b.  H_out, b_out
+ * (may be NULL) return H and b, resInM the residual count, idepth_hessian_out (nP, may be NULL) PointHessian::idepth_hessian.
+ * The structural part (removePoint, makeIDX, connectivityMap) stays with the caller, who re-uploads the window afterwards.
+ * The SOLVER_ORTHOGONALIZE_POINTMARG / _FULL variants (not the default solver mode) are not implemented. */
+int dso_b200_ba_marginalize_points(dso_b200_ctx* ctx, const unsigned char* point_flags, float idepthFixPriorMargFac,
+                                   double margWeightFac, double* H_out, double* b_out, int* resInM, float* idepth_hessian_out);
+/* The marginalisation prior as it stands on the device (after dso_b200_ba_set_priors and any marginalisation). */
+int dso_b200_ba_get_marg_prior(dso_b200_ctx* ctx, double* HM_out, double* bM_out);
+/* EnergyFunctional::calcLEnergyF_MT (EnergyFunctional.cpp:411-428, calcLEnergyPt :346-408) and calcMEnergyF (:334-343), the
+ * two terms FullSystem::optimize adds to the linearisation energy in its accept test.  The point terms are the reference's
+ * float values summed in FP64 by a fixed tree (the reference uses float tiers and a dynamic thread split). */
+int dso_b200_ba_calc_energies(dso_b200_ctx* ctx, double* L_energy, double* M_energy);
 
 #ifdef __cplusplus
 }

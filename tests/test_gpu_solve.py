@@ -114,3 +114,29 @@ def test_gauss_newton_iterations_reduce_energy(pkg, oracle, window_small):
     assert energies[-1] < 0.8 * energies[0], energies
     assert all(b <= a * 1.02 for a, b in zip(energies, energies[1:])), energies
     ctx.close()
+
+
+def test_marginalize_points_and_energies(pkg, oracle, window_small):
+    """rest of N2 on the device: calcLEnergyF_MT, calcMEnergyF, marginalizePointsF vs the oracle (pinned against the reference
+    build in test_oracle_vs_reference.py::test_marginalize_points_and_energies)"""
+    W = window_small
+    B, ctx = _setup(pkg, oracle, W)
+    inp = _solve_inputs(W)
+    pflags = (np.arange(W.nP) % 3 == 1).astype(np.uint8)
+    rflags = pflags[W.res_point]
+    B.linearize(); ctx.ba_linearize()
+    B.apply_res(); ctx.ba_apply_res()
+    B.fix_linearization(rflags); ctx.ba_fix_linearization(rflags)
+    B.set_priors(*inp[:6]); ctx.ba_set_priors(*inp[:6])
+    Lo, Mo = B.calc_L_energy(1), B.calc_M_energy()
+    Lg, Mg = ctx.ba_calc_energies()
+    assert abs(Mg - Mo) <= 1e-12 * abs(Mo) and Mo != 0
+    assert abs(Lg - Lo) <= 1e-5 * abs(Lo) and Lo != 0           # FP64 tree vs the reference's float tiers
+    mo, mg = B.marginalize_points(pflags), ctx.ba_marginalize_points(pflags)
+    assert mo["resInM"] == mg["resInM"] > 100
+    sel = pflags == 1
+    assert np.array_equal(mo["idepth_hessian"][sel].view(np.uint32), mg["idepth_hessian"][sel].view(np.uint32))
+    _check_system(mg["H"], mg["b"], mo["H"], mo["b"])
+    _check_system(mg["HM"], mg["bM"], mo["HM"], mo["bM"])
+    assert np.allclose(mg["HM"], inp[4] + 0.25 * mg["H"], rtol=0, atol=1e-9 * np.abs(mg["HM"]).max())
+    ctx.close()
