@@ -365,3 +365,37 @@ def motion_hypotheses(fh_2_slast, lastF_2_slast):
     for q in quats:
         tries.append(se3_mul(base, quat_pose(1.0, *q)))
     return tries
+
+
+def immature_scenario(W, host_idx=2, n_points=1500, n_frames=3, seed=0, step_t=0.03, step_deg=0.7):
+    """Inputs of FullSystem::traceNewCoarse (FullSystem.cpp:486-530) for one host key frame: candidate pixels (integer,
+    textured, away from the border), their true inverse depths, and for each of n_frames new frames the image and
+    hostToFrame_KRKi / hostToFrame_Kt / hostToFrame_affine as float32 (true poses, true affine parameters)."""
+    rng = np.random.default_rng(seed + 7000)
+    sc = W.scene
+    fx, fy, cx, cy = W.K
+    K = np.array([[fx, 0, cx], [0, fy, cy], [0, 0, 1]], dtype=np.float64)
+    img = W.images[host_idx]
+    gx = np.zeros_like(img); gy = np.zeros_like(img)
+    gx[:, 1:-1] = 0.5 * (img[:, 2:] - img[:, :-2]); gy[1:-1, :] = 0.5 * (img[2:, :] - img[:-2, :])
+    g2 = gx * gx + gy * gy
+    m = 12
+    ys, xs = np.nonzero(g2[m:-m, m:-m] > np.percentile(g2, 70))
+    sel = rng.choice(len(xs), size=min(n_points, len(xs)), replace=False)
+    u = (xs[sel] + m).astype(np.int32); v = (ys[sel] + m).astype(np.int32)
+    idepth_true = (1.0 / W.depths[host_idx][v, u]).astype(np.float32)
+    T_host = W.poses_true[host_idx]
+    a_h, b_h = W.aff_true[host_idx]
+    poses = sc.trajectory(n_frames + 1, step_t=step_t, step_deg=step_deg, start=W.poses_true[-1])[1:]
+    frames = []
+    for T in poses:
+        aff = (float(rng.uniform(-0.05, 0.05)), float(rng.uniform(-3, 3)))
+        im, _ = sc.render(T, aff)
+        R, t = se3_mul(T, se3_inv(T_host))
+        KRKi = (K @ R @ np.linalg.inv(K)).astype(np.float32)
+        Kt = (K @ t).astype(np.float32)
+        # AffLight::fromToVecExposure with unit exposures (NumType.h:176-189)
+        a = np.exp(aff[0] - a_h)
+        frames.append(dict(image=im, KRKi=np.ascontiguousarray(KRKi), Kt=np.ascontiguousarray(Kt),
+                           aff=np.array([a, aff[1] - a * b_h], dtype=np.float32)))
+    return dict(host_image=img, u=u, v=v, idepth_true=idepth_true, frames=frames)

@@ -156,6 +156,20 @@ void dso_oracle_ba_marginalize_points(dso_oracle_ba*, const unsigned char* flags
                                       double* H_out, double* b_out, int* resInM, float* idepth_hessian_out);
 void dso_oracle_ba_get_marg_prior(dso_oracle_ba*, double* HM, double* bM);
 
+/* ---- N3: immature points ------------------------------------------------------------------------ */
+/* ImmaturePoint::ImmaturePoint (FullSystem/ImmaturePoint.cpp:25-57): pattern colours, gradient weights, gradH, energyTH of
+ * n points at integer pixels (u, v) of the host frame's level-0 AoS image. */
+void dso_oracle_immature_init(int w, int h, const float* host_dI, int n, const int* u, const int* v,
+                              float* color8, float* weights8, float* gradH4, float* energyTH);
+/* ImmaturePoint::traceOn (FullSystem/ImmaturePoint.cpp:77-438) for n points of one host frame on one new frame (level-0
+ * AoS image): KRKi, Kt, affine = hostToFrame_* of FullSystem::traceNewCoarse (FullSystem.cpp:497-508).
+ * In/out: idepth_min, idepth_max, quality, status (ImmaturePointStatus), lastTraceUV (2n), lastTracePixelInterval. */
+void dso_oracle_trace_on(int w, int h, const float* frame_dI, int n, const float* u, const float* v,
+                         const float* color8, const float* weights8, const float* gradH4, const float* energyTH,
+                         float* idepth_min, float* idepth_max, float* quality, int* status,
+                         const float* KRKi9, const float* Kt3, const float* aff2,
+                         float* lastTraceUV2, float* lastTracePixelInterval);
+
 #ifdef __cplusplus
 }
 #endif

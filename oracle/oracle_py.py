@@ -110,6 +110,9 @@ def lib(kind="oracle"):
     sig("dso_oracle_ba_calc_M_energy", [vp], C.c_double)
     sig("dso_oracle_ba_marginalize_points", [vp, vp, C.c_float, C.c_double, vp, vp, vp, vp])
     sig("dso_oracle_ba_get_marg_prior", [vp, f64p, f64p])
+    sig("dso_oracle_immature_init", [C.c_int, C.c_int, f32p, C.c_int, i32p, i32p, f32p, f32p, f32p, f32p])
+    sig("dso_oracle_trace_on", [C.c_int, C.c_int, f32p, C.c_int, f32p, f32p, f32p, f32p, f32p, f32p, f32p, f32p, f32p, i32p,
+                                f32p, f32p, f32p, f32p, f32p])
     sig("dso_oracle_scaled_ldlt_solve", [f64p, f64p, C.c_int, f64p])
     sig("dso_oracle_ba_solve", [vp, C.c_int, C.c_double, C.c_int, C.c_double, C.c_int, C.c_int, vp, vp, vp, vp], C.c_int)
     _LIBS[kind] = L
@@ -128,6 +131,37 @@ def scaled_ldlt_solve(HF, bF):
     x = np.zeros(len(bF))
     lib("oracle").dso_oracle_scaled_ldlt_solve(HF.reshape(-1), bF, len(bF), x)
     return x
+
+
+def immature_init(dI, u, v, kind="oracle"):
+    """ImmaturePoint constructor fields for integer pixels (u, v) of the AoS level-0 image dI [h, w, 3]"""
+    h, w = dI.shape[:2]
+    n = len(u)
+    out = dict(color=np.zeros((n, 8), dtype=np.float32), weights=np.zeros((n, 8), dtype=np.float32),
+               gradH=np.zeros((n, 4), dtype=np.float32), energyTH=np.zeros(n, dtype=np.float32))
+    lib(kind).dso_oracle_immature_init(w, h, np.ascontiguousarray(dI, dtype=np.float32).reshape(-1), n,
+                                       np.ascontiguousarray(u, dtype=np.int32), np.ascontiguousarray(v, dtype=np.int32),
+                                       out["color"].reshape(-1), out["weights"].reshape(-1), out["gradH"].reshape(-1), out["energyTH"])
+    return out
+
+
+def trace_on(dI, u, v, fields, state, KRKi, Kt, aff, kind="oracle"):
+    """ImmaturePoint::traceOn on all points; state: dict(idepth_min, idepth_max, quality, status, uv, interval), updated in place"""
+    h, w = dI.shape[:2]
+    lib(kind).dso_oracle_trace_on(w, h, np.ascontiguousarray(dI, dtype=np.float32).reshape(-1), len(u),
+                                  np.ascontiguousarray(u, dtype=np.float32), np.ascontiguousarray(v, dtype=np.float32),
+                                  fields["color"].reshape(-1), fields["weights"].reshape(-1), fields["gradH"].reshape(-1), fields["energyTH"],
+                                  state["idepth_min"], state["idepth_max"], state["quality"], state["status"],
+                                  np.ascontiguousarray(KRKi, dtype=np.float32).reshape(-1), np.ascontiguousarray(Kt, dtype=np.float32),
+                                  np.ascontiguousarray(aff, dtype=np.float32), state["uv"].reshape(-1), state["interval"])
+    return state
+
+
+def trace_state(n):
+    """a fresh immature point: idepth_min = 0, idepth_max = NaN, quality = 10000, IPS_UNINITIALIZED (ImmaturePoint.cpp:25-57, .h)"""
+    return dict(idepth_min=np.zeros(n, dtype=np.float32), idepth_max=np.full(n, np.nan, dtype=np.float32),
+                quality=np.full(n, 10000.0, dtype=np.float32), status=np.full(n, 5, dtype=np.int32),
+                uv=np.full((n, 2), -1.0, dtype=np.float32), interval=np.zeros(n, dtype=np.float32))
 
 
 def _ptr_array(arrs):

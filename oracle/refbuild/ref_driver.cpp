@@ -25,11 +25,10 @@
 
 namespace dso
 {
-// statics that live in translation units we do not compile (FullSystem.cpp:61-63, ImmaturePoint.cpp)
+// statics that live in translation units we do not compile (FullSystem.cpp:61-63)
 int FrameHessian::instanceCounter = 0;
 int PointHessian::instanceCounter = 0;
 int CalibHessian::instanceCounter = 0;
-ImmaturePoint::~ImmaturePoint() {}
 }
 using namespace dso;
 
@@ -551,4 +550,61 @@ extern "C" void dso_ref_ba_marginalize_points(dso_oracle_ba* B, const unsigned c
 		if (b_out) b_out[r] = (B->ef->bM[r] - bM0[r]) / margWeightFac;
 	}
 	if (idepth_hessian_out) for (size_t i = 0; i < B->pts.size(); i++) idepth_hessian_out[i] = B->pts[i]->idepth_hessian;
+}
+
+// ---- N3: ImmaturePoint constructor and traceOn (FullSystem/ImmaturePoint.cpp, compiled unmodified) ----
+static FrameHessian* frame_with_dI(int w, int h, const float* dI)
+{
+	FrameHessian* fh = new FrameHessian();
+	fh->shell = new FrameShell(); fh->shell->id = 0;
+	fh->dIp[0] = (Eigen::Vector3f*)const_cast<float*>(dI);     // borrowed for the duration of the call
+	fh->dI = fh->dIp[0];
+	(void)w; (void)h;
+	return fh;
+}
+static void release_frame(FrameHessian* fh) { fh->dIp[0] = 0; fh->dI = 0; }   // the shell object leaks on purpose (test process; ~FrameHessian frees image arrays it never allocated here)
+
+extern "C" void dso_ref_immature_init(int w, int h, const float* host_dI, int n, const int* u, const int* v,
+                                      float* color8, float* weights8, float* gradH4, float* energyTH)
+{
+	set_calib(w, h, 1, 500, 500, w * 0.5f, h * 0.5f);
+	CalibHessian HCalib;
+	FrameHessian* host = frame_with_dI(w, h, host_dI);
+	for (int k = 0; k < n; k++)
+	{
+		ImmaturePoint ip(u[k], v[k], host, 1, &HCalib);           // ImmaturePoint.cpp:25
+		for (int i = 0; i < 8; i++) { color8[8 * k + i] = ip.color[i]; weights8[8 * k + i] = ip.weights[i]; }
+		gradH4[4 * k] = ip.gradH(0, 0); gradH4[4 * k + 1] = ip.gradH(0, 1); gradH4[4 * k + 2] = ip.gradH(1, 0); gradH4[4 * k + 3] = ip.gradH(1, 1);
+		energyTH[k] = ip.energyTH;
+	}
+	release_frame(host);
+}
+extern "C" void dso_ref_trace_on(int w, int h, const float* frame_dI, int n, const float* u, const float* v,
+                                 const float* color8, const float* weights8, const float* gradH4, const float* energyTH,
+                                 float* idepth_min, float* idepth_max, float* quality, int* status,
+                                 const float* KRKi9, const float* Kt3, const float* aff2,
+                                 float* lastTraceUV2, float* lastTracePixelInterval)
+{
+	set_calib(w, h, 1, 500, 500, w * 0.5f, h * 0.5f);
+	CalibHessian HCalib;
+	FrameHessian* frame = frame_with_dI(w, h, frame_dI);
+	FrameHessian* host = frame_with_dI(w, h, frame_dI);
+	host->shell->id = 1;
+	Mat33f KRKi; Vec3f Kt; Vec2f aff;
+	for (int r = 0; r < 3; r++) { for (int c = 0; c < 3; c++) KRKi(r, c) = KRKi9[r * 3 + c]; Kt[r] = Kt3[r]; }
+	aff[0] = aff2[0]; aff[1] = aff2[1];
+	for (int k = 0; k < n; k++)
+	{
+		ImmaturePoint* ip = raw_immature(host, u[k], v[k], 1, color8 + 8 * k, weights8 + 8 * k);
+		ip->gradH(0, 0) = gradH4[4 * k]; ip->gradH(0, 1) = gradH4[4 * k + 1]; ip->gradH(1, 0) = gradH4[4 * k + 2]; ip->gradH(1, 1) = gradH4[4 * k + 3];
+		ip->energyTH = energyTH[k]; ip->idepth_min = idepth_min[k]; ip->idepth_max = idepth_max[k]; ip->quality = quality[k];
+		ip->lastTraceStatus = (ImmaturePointStatus)status[k];
+		ip->lastTraceUV = Vec2f(lastTraceUV2[2 * k], lastTraceUV2[2 * k + 1]); ip->lastTracePixelInterval = lastTracePixelInterval[k];
+		ip->traceOn(frame, KRKi, Kt, aff, &HCalib, false);        // ImmaturePoint.cpp:77
+		idepth_min[k] = ip->idepth_min; idepth_max[k] = ip->idepth_max; quality[k] = ip->quality; status[k] = (int)ip->lastTraceStatus;
+		lastTraceUV2[2 * k] = ip->lastTraceUV[0]; lastTraceUV2[2 * k + 1] = ip->lastTraceUV[1];
+		lastTracePixelInterval[k] = ip->lastTracePixelInterval;
+		free(ip);
+	}
+	release_frame(frame); release_frame(host);
 }

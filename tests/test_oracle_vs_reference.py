@@ -251,3 +251,29 @@ def test_marginalize_points_and_energies(pkg, window_small):
     assert np.abs(mo["b"] - mr["b"]).max() <= 1e-9 * np.abs(mr["b"]).max()
     assert np.abs(mo["HM"] - mr["HM"]).max() <= 1e-12 * np.abs(mr["HM"]).max()
     assert np.abs(mo["bM"] - mr["bM"]).max() <= 1e-12 * np.abs(mr["bM"]).max()
+
+
+def test_immature_point_init_and_trace_on_bit_exact(pkg, window_small):
+    """next row N3: ImmaturePoint's constructor and traceOn (FullSystem/ImmaturePoint.cpp:25-57, 77-438) over three
+    successive frames (interval (0, NaN) first, then the refined intervals), every output bit for bit"""
+    W = window_small
+    sc = pkg.synthetic.immature_scenario(W, host_idx=1, n_points=600, n_frames=3)
+    hostI = O.make_images(sc["host_image"], 1)[0][0]
+    fo, fr = O.immature_init(hostI, sc["u"], sc["v"]), O.immature_init(hostI, sc["u"], sc["v"], kind="ref")
+    for k in fo:
+        assert np.array_equal(bits(fo[k]), bits(fr[k])), k
+    so, sr = O.trace_state(len(sc["u"])), O.trace_state(len(sc["u"]))
+    seen = set()
+    for fr_ in sc["frames"]:
+        dI = O.make_images(fr_["image"], 1)[0][0]
+        O.trace_on(dI, sc["u"], sc["v"], fo, so, fr_["KRKi"], fr_["Kt"], fr_["aff"])
+        O.trace_on(dI, sc["u"], sc["v"], fo, sr, fr_["KRKi"], fr_["Kt"], fr_["aff"], kind="ref")
+        assert np.array_equal(so["status"], sr["status"])
+        for k in ("idepth_min", "idepth_max", "quality", "uv", "interval"):
+            assert np.array_equal(bits(so[k]), bits(sr[k])), k
+        seen |= set(so["status"].tolist())
+    assert {0, 1}.issubset(seen) and len(seen) >= 3, seen          # GOOD, OOB and at least one of SKIPPED / BADCONDITION / OUTLIER
+    good = so["status"] == 0
+    assert good.sum() > 100
+    mid = 0.5 * (so["idepth_min"][good] + so["idepth_max"][good])
+    assert np.median(np.abs(mid - sc["idepth_true"][good]) / sc["idepth_true"][good]) < 0.05     # the search finds the true depth
