@@ -55,6 +55,8 @@ SIGNATURES = {
     "dso_b200_tracker_set_ref_points": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float, C.c_int,
                                                   f32p, f32p, f32p, f32p, C.c_double, C.c_double, C.c_float, vp]),
     "dso_b200_tracker_get_cloud": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, vp, C.POINTER(C.c_int)]),
+    "dso_b200_trace_set_points": (C.c_int, [vp, C.c_int, f32p, f32p, f32p, f32p, f32p, f32p, i32p, f32p, f32p, f32p, i32p, vp, vp]),
+    "dso_b200_trace_new_coarse": (C.c_int, [vp, C.c_int, C.c_int, f32p, f32p, f32p, vp, vp, vp, vp, vp, vp]),
     "dso_b200_make_images_async": (C.c_int, [vp, C.c_int, vp, C.c_int, C.c_int, C.c_int]),
     "dso_b200_make_images_dev": (C.c_int, [vp, C.c_int, vp, C.c_int, C.c_int, C.c_int, vp]),
     "dso_b200_tracker_set_ref": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float,
@@ -269,6 +271,25 @@ class Context:
         out = np.zeros((n.value, 4), dtype=np.float32)
         if n.value:
             self._check(self.L.dso_b200_tracker_get_cloud(self.h, trk, lvl, n.value, out.ctypes.data, C.byref(n)))
+        return out
+
+    def trace_set_points(self, u, v, fields, host_idx, state):
+        f = lambda a: np.ascontiguousarray(a, dtype=np.float32)
+        self._trace_n = len(u)
+        self._check(self.L.dso_b200_trace_set_points(self.h, len(u), f(u), f(v), f(fields["color"]).reshape(-1), f(fields["weights"]).reshape(-1),
+                                                     f(fields["gradH"]).reshape(-1), f(fields["energyTH"]),
+                                                     np.ascontiguousarray(host_idx, dtype=np.int32), f(state["idepth_min"]), f(state["idepth_max"]),
+                                                     f(state["quality"]), np.ascontiguousarray(state["status"], dtype=np.int32),
+                                                     f(state["uv"]).ctypes.data, f(state["interval"]).ctypes.data))
+
+    def trace_new_coarse(self, slot, KRKi, Kt, aff, fetch=True):
+        KRKi = np.ascontiguousarray(KRKi, dtype=np.float32).reshape(-1, 9)
+        n = self._trace_n
+        out = dict(idepth_min=np.zeros(n, dtype=np.float32), idepth_max=np.zeros(n, dtype=np.float32), quality=np.zeros(n, dtype=np.float32),
+                   status=np.zeros(n, dtype=np.int32), uv=np.zeros((n, 2), dtype=np.float32), interval=np.zeros(n, dtype=np.float32))
+        ptrs = [out[k].ctypes.data if fetch else None for k in ("idepth_min", "idepth_max", "quality", "status", "uv", "interval")]
+        self._check(self.L.dso_b200_trace_new_coarse(self.h, slot, KRKi.shape[0], KRKi.reshape(-1), np.ascontiguousarray(Kt, dtype=np.float32).reshape(-1),
+                                                     np.ascontiguousarray(aff, dtype=np.float32).reshape(-1), *ptrs))
         return out
 
     def make_images_async(self, slot, color_ptr, w, h, levels):

@@ -123,6 +123,7 @@ extern "C" void dso_b200_destroy(dso_b200_ctx* ctx)
 	cudaStreamSynchronize(ctx->stream);
 	ba_destroy(ctx);
 	coarse_depth_destroy(ctx);
+	trace_destroy(ctx);
 	for (int s = 0; s < ctx->n_slots; s++) { cudaFree(ctx->slots[s].base); cudaEventDestroy(ctx->slots[s].ready); }
 	delete[] ctx->slots;
 	cudaFree(ctx->d_color); cudaFree(ctx->d_color_up);

@@ -105,6 +105,7 @@ struct dso_b200_ctx
 	TrackerSlot trk[2];
 	BAWorkspace* ba;
 	void* coarse_depth;        // CoarseDepthWS (coarse_depth.cu), allocated at the first dso_b200_tracker_set_ref_points
+	void* trace;               // TraceWS (trace.cu): the immature points of the window
 	long long launches;
 	void* d_phase_cycles;      // optional: per-phase cycle counters of the persistent tracker (debug)
 };
@@ -127,7 +128,8 @@ int pyramid_build_on(dso_b200_ctx* ctx, cudaStream_t stream, FrameSlot& fs, cons
                      const float* d_Blut, bool host_layout);
 int frame_slot_wait(dso_b200_ctx* ctx, int frame_slot);
 void tracker_make_K(TrackerSlot& T, int w, int h, int levels, float fx, float fy, float cx, float cy);   // CoarseTracker::makeK
-void coarse_depth_destroy(dso_b200_ctx* ctx);   // makes ctx->stream wait for a pending asynchronous upload of the slot
+void coarse_depth_destroy(dso_b200_ctx* ctx);
+void trace_destroy(dso_b200_ctx* ctx);   // makes ctx->stream wait for a pending asynchronous upload of the slot
 int pyramid_build(dso_b200_ctx* ctx, FrameSlot& fs, const float* color_dev, int w, int h, int levels,
                   const float* d_Blut, bool host_layout);
 int ba_create(dso_b200_ctx* ctx);

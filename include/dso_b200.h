@@ -345,6 +345,24 @@ int dso_b200_ba_get_marg_prior(dso_b200_ctx* ctx, double* HM_out, double* bM_out
  * float values summed in FP64 by a fixed tree (the reference uses float tiers and a dynamic thread split). */
 int dso_b200_ba_calc_energies(dso_b200_ctx* ctx, double* L_energy, double* M_energy);
 
+/* ---- next row N3, second half: immature points (FullSystem/ImmaturePoint.{h,cpp}) ----------------------------------
+ * The immature points of the window live on the device between frames.  dso_b200_trace_set_points uploads them when the
+ * set changes (points created by makeNewTraces, activated or dropped): per point u, v, color[8], weights[8], gradH (2x2,
+ * row-major), energyTH (ImmaturePoint.h:60-75, filled by the constructor, ImmaturePoint.cpp:25-57), the index of its host
+ * frame among the n_hosts key frames, and the trace state idepth_min, idepth_max, quality, lastTraceStatus
+ * (ImmaturePointStatus as int), lastTraceUV, lastTracePixelInterval (the last two may be NULL). */
+int dso_b200_trace_set_points(dso_b200_ctx* ctx, int n, const float* u, const float* v, const float* color8, const float* weights8,
+                              const float* gradH4, const float* energyTH, const int* host_idx,
+                              const float* idepth_min, const float* idepth_max, const float* quality, const int* status,
+                              const float* lastTraceUV2, const float* lastTracePixelInterval);
+/* FullSystem::traceNewCoarse (FullSystem.cpp:486-530): ImmaturePoint::traceOn (ImmaturePoint.cpp:77-438) for every uploaded
+ * point on the new frame in `frame_slot` (device pyramid from dso_b200_make_images*).  Per host frame h < n_hosts:
+ * hostToFrame_KRKi (9, row-major), hostToFrame_Kt (3), hostToFrame_affine (2) as computed at FullSystem.cpp:497-508.
+ * The trace state is updated in place on the device; any non-NULL output array receives a copy (n entries, UV: 2n). */
+int dso_b200_trace_new_coarse(dso_b200_ctx* ctx, int frame_slot, int n_hosts, const float* KRKi9, const float* Kt3, const float* aff2,
+                              float* idepth_min_out, float* idepth_max_out, float* quality_out, int* status_out,
+                              float* lastTraceUV2_out, float* lastTracePixelInterval_out);
+
 #ifdef __cplusplus
 }
 #endif
