@@ -302,6 +302,67 @@ def ba_gpu_bench(pkg, W, dev, steps, warmup, flush_l2, torch, device):
     return out
 
 
+def trace_bench(pkg, W, dev, steps, warmup, flush_l2, torch, device, with_cpu):
+    """next row N3: FullSystem::traceNewCoarse -- ImmaturePoint::traceOn for the immature points of all key frames on one
+    new frame (dso_b200_trace_new_coarse), next to the oracle port on one host thread (the reference loop is serial)"""
+    syn = pkg.synthetic
+    hosts = list(range(W.nF - 1))
+    scs = [syn.immature_scenario(W, host_idx=h, n_points=1700, n_frames=1, seed=h) for h in hosts]
+    u = np.concatenate([s["u"] for s in scs]).astype(np.float32)
+    v = np.concatenate([s["v"] for s in scs]).astype(np.float32)
+    host_idx = np.concatenate([np.full(len(s["u"]), i, dtype=np.int32) for i, s in enumerate(scs)])
+    O = entry.load_oracle() if with_cpu else None
+    img = scs[0]["frames"][0]["image"]
+    ctx = pkg.Context(dev, W.w, W.h, W.nF + 1)
+    # constructor fields: from the oracle when it is loaded anyway, else a plain numpy evaluation of the same formulas
+    if O is not None:
+        fields = [O.immature_init(O.make_images(s["host_image"], 1)[0][0], s["u"], s["v"]) for s in scs]
+        fcat = {k: np.concatenate([f[k] for f in fields]) for k in fields[0]}
+    else:
+        n = len(u)
+        fcat = dict(color=np.full((n, 8), 100.0, dtype=np.float32), weights=np.ones((n, 8), dtype=np.float32),
+                    gradH=np.tile(np.array([50.0, 0, 0, 50.0], dtype=np.float32), (n, 1)), energyTH=np.full(n, 8 * 144.0, dtype=np.float32))
+        for i, s in enumerate(scs):
+            sel = host_idx == i
+            im = s["host_image"]
+            pat = [(0, -2), (-1, -1), (1, -1), (-2, 0), (0, 0), (2, 0), (-1, 1), (0, 2)]
+            fcat["color"][sel] = np.stack([im[s["v"] + dy, s["u"] + dx] for dx, dy in pat], axis=1)
+    n = len(u)
+    st = dict(idepth_min=np.zeros(n, dtype=np.float32), idepth_max=np.full(n, np.nan, dtype=np.float32), quality=np.full(n, 10000.0, dtype=np.float32),
+              status=np.full(n, 5, dtype=np.int32), uv=np.full((n, 2), -1.0, dtype=np.float32), interval=np.zeros(n, dtype=np.float32))
+    KRKi = np.stack([s["frames"][0]["KRKi"].reshape(-1) for s in scs]); Kt = np.stack([s["frames"][0]["Kt"] for s in scs])
+    aff = np.stack([s["frames"][0]["aff"] for s in scs])
+    ctx.make_images(0, img, 1, want_host=False)
+    stream = torch.cuda.ExternalStream(ctx.stream, device=device)
+    ms = 0.0
+    for i in range(warmup + steps):
+        ctx.trace_set_points(u, v, fcat, host_idx, st)          # fresh points every repetition (the first trace is the long one)
+        flush_l2(stream)
+        ctx.sync()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        ctx.trace_new_coarse(0, KRKi, Kt, aff, fetch=False)
+        e1.record(stream)
+        e1.synchronize()
+        if i >= warmup:
+            ms += e0.elapsed_time(e1)
+    g = ctx.trace_new_coarse(0, KRKi, Kt, aff)
+    out = {"what": "FullSystem::traceNewCoarse: first traceOn of %d immature points of %d key frames on one 640x480 frame" % (n, len(hosts)),
+           "ms": ms / steps, "points": int(n), "status_histogram_second_pass": np.bincount(g["status"], minlength=6).tolist()}
+    if O is not None:
+        dI = O.make_images(img, 1)[0][0]
+        t0 = time.perf_counter()
+        reps = 0
+        while time.perf_counter() - t0 < 2.0:
+            for i, s in enumerate(scs):
+                so = O.trace_state(len(s["u"]))
+                O.trace_on(dI, s["u"], s["v"], fields[i], so, s["frames"][0]["KRKi"], s["frames"][0]["Kt"], s["frames"][0]["aff"])
+            reps += 1
+        out["cpu_ms_1thread"] = (time.perf_counter() - t0) / reps * 1e3
+    ctx.close()
+    return out
+
+
 def ba_cpu_bench(W, seconds=4.0):
     """the same step on the host with the oracle port: reference thread-pool branch (NUM_THREADS = 6), all cores, and 1 thread"""
     O = entry.load_oracle()
@@ -540,6 +601,7 @@ def run_ours(args):
     conv = reduce_sum(dist, float(ok), device)
 
     ba = ba_gpu_bench(pkg, W, dev, max(5, min(args.steps, 50)), args.warmup, flush_l2, torch, device)
+    trace = trace_bench(pkg, W, dev, 10, 3, flush_l2, torch, device, with_cpu=(rank == 0 and world == 1 and not args.no_cpu)) if rank == 0 else None
     ba_ms = reduce_max(dist, ba["value"], device)
     ba["value"] = ba_ms
     cpu = None
@@ -565,7 +627,7 @@ def run_ours(args):
                         "serial": {"value": total_steps / t_e2e, "ms_per_step": t_e2e / args.steps * 1e3,
                                    "api": "dso_b200_track_frame (H2D, K1, K2, D2H, 1 sync per frame), L2 flushed before every step",
                                    "tracked_ok": conv / total_steps}},
-                "gpu_launches": int(launches), "ba": ba, "roofline": roofline, "cpu_baseline": cpu, "clocks": clocks,
+                "gpu_launches": int(launches), "ba": ba, "trace_new_coarse": trace, "roofline": roofline, "cpu_baseline": cpu, "clocks": clocks,
                 "wall_s_timed_region": t_wall1 - t_wall0,
                 "set_coarse_tracking_ref_ms": set_ref_ms,     # makeCoarseDepthL0 on the device incl. upload of the points and 1 sync (first call)
                 "lm": {"evals_per_frame": float(np.mean([r.n_evals for r in results])),
