@@ -399,3 +399,30 @@ def immature_scenario(W, host_idx=2, n_points=1500, n_frames=3, seed=0, step_t=0
         frames.append(dict(image=im, KRKi=np.ascontiguousarray(KRKi), Kt=np.ascontiguousarray(Kt),
                            aff=np.array([a, aff[1] - a * b_h], dtype=np.float32)))
     return dict(host_image=img, u=u, v=v, idepth_true=idepth_true, frames=frames)
+
+
+def activation_scenario(W, host_idx=2, n_points=800, seed=0, interval=0.05):
+    """Inputs of FullSystem::optimizeImmaturePoint (FullSystemOptPoint.cpp:51-209) for the immature points of one host key
+    frame: all other key frames of the window as targets with the host's FrameFramePrecalc entries (PRE_RTll, PRE_tTll,
+    PRE_aff_mode; true poses and affine parameters, float32) and inverse-depth intervals around the truth; a tenth of the
+    points get a wrong interval so that the failure exits are exercised too."""
+    rng = np.random.default_rng(seed + 9000)
+    sc = immature_scenario(W, host_idx=host_idx, n_points=n_points, n_frames=1, seed=seed)
+    T_host = W.poses_true[host_idx]
+    a_h, b_h = W.aff_true[host_idx]
+    targets = [t for t in range(W.nF) if t != host_idx]
+    RT, tT, aff = [], [], []
+    for t in targets:
+        R, tr = se3_mul(W.poses_true[t], se3_inv(T_host))
+        a = np.exp(W.aff_true[t][0] - a_h)
+        RT.append(R.astype(np.float32).reshape(-1)); tT.append(tr.astype(np.float32))
+        aff.append(np.array([a, W.aff_true[t][1] - a * b_h], dtype=np.float32))
+    idt = sc["idepth_true"]
+    noise = rng.uniform(-0.3, 0.3, len(idt)).astype(np.float32) * interval
+    centre = idt * (1 + noise)
+    wrong = rng.random(len(idt)) < 0.1
+    centre[wrong] *= rng.uniform(1.5, 3.0, wrong.sum()).astype(np.float32)
+    return dict(u=sc["u"], v=sc["v"], host_image=sc["host_image"], targets=targets, images=[W.images[t] for t in targets],
+                RTll=np.ascontiguousarray(np.stack(RT)), tTll=np.ascontiguousarray(np.stack(tT)), aff=np.ascontiguousarray(np.stack(aff)),
+                idepth_min=(centre * (1 - interval)).astype(np.float32), idepth_max=(centre * (1 + interval)).astype(np.float32),
+                idepth_true=idt, wrong=wrong)

@@ -170,6 +170,16 @@ void dso_oracle_trace_on(int w, int h, const float* frame_dI, int n, const float
                          const float* KRKi9, const float* Kt3, const float* aff2,
                          float* lastTraceUV2, float* lastTracePixelInterval);
 
+/* FullSystem::optimizeImmaturePoint (FullSystemOptPoint.cpp:51-209) for n immature points of one host frame against nT
+ * target frames (level-0 AoS images; per target PRE_RTll (9), PRE_tTll (3), PRE_aff_mode (2) of the host's FrameFramePrecalc).
+ * result: 0 = null, -1 = the "delete me" marker, 1 = activated with idepth_out; res_state_out[k*nT+t]: final ResState of the
+ * temporary residual to target t (meaningful when result != 0). */
+void dso_oracle_optimize_immature(int w, int h, float fx, float fy, float cx, float cy, int nT, const float* const* target_dI,
+                                  const float* RTll9, const float* tTll3, const float* aff2,
+                                  int n, const float* u, const float* v, const float* color8, const float* weights8,
+                                  const float* energyTH, const float* idepth_min, const float* idepth_max, int minObs,
+                                  int* result, float* idepth_out, int* res_state_out);
+
 #ifdef __cplusplus
 }
 #endif

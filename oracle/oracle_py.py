@@ -113,6 +113,8 @@ def lib(kind="oracle"):
     sig("dso_oracle_immature_init", [C.c_int, C.c_int, f32p, C.c_int, i32p, i32p, f32p, f32p, f32p, f32p])
     sig("dso_oracle_trace_on", [C.c_int, C.c_int, f32p, C.c_int, f32p, f32p, f32p, f32p, f32p, f32p, f32p, f32p, f32p, i32p,
                                 f32p, f32p, f32p, f32p, f32p])
+    sig("dso_oracle_optimize_immature", [C.c_int, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float, C.c_int, C.POINTER(vp), f32p, f32p, f32p,
+                                         C.c_int, f32p, f32p, f32p, f32p, f32p, f32p, f32p, C.c_int, i32p, f32p, i32p])
     sig("dso_oracle_scaled_ldlt_solve", [f64p, f64p, C.c_int, f64p])
     sig("dso_oracle_ba_solve", [vp, C.c_int, C.c_double, C.c_int, C.c_double, C.c_int, C.c_int, vp, vp, vp, vp], C.c_int)
     _LIBS[kind] = L
@@ -162,6 +164,20 @@ def trace_state(n):
     return dict(idepth_min=np.zeros(n, dtype=np.float32), idepth_max=np.full(n, np.nan, dtype=np.float32),
                 quality=np.full(n, 10000.0, dtype=np.float32), status=np.full(n, 5, dtype=np.int32),
                 uv=np.full((n, 2), -1.0, dtype=np.float32), interval=np.zeros(n, dtype=np.float32))
+
+
+def optimize_immature(K, target_dIs, RTll, tTll, aff, u, v, fields, idepth_min, idepth_max, min_obs=1, kind="oracle"):
+    """FullSystem::optimizeImmaturePoint on every point; returns (result, idepth, res_state [n, nT])"""
+    h, w = target_dIs[0].shape[:2]
+    fx, fy, cx, cy = K
+    dI = [np.ascontiguousarray(x, dtype=np.float32) for x in target_dIs]
+    n, nT = len(u), len(dI)
+    result = np.zeros(n, dtype=np.int32); idp = np.zeros(n, dtype=np.float32); rs = np.zeros(n * nT, dtype=np.int32)
+    f = lambda a: np.ascontiguousarray(a, dtype=np.float32).reshape(-1)
+    lib(kind).dso_oracle_optimize_immature(w, h, fx, fy, cx, cy, nT, _ptr_array(dI), f(RTll), f(tTll), f(aff), n, f(u), f(v),
+                                           f(fields["color"]), f(fields["weights"]), f(fields["energyTH"]), f(idepth_min), f(idepth_max),
+                                           min_obs, result, idp, rs)
+    return result, idp, rs.reshape(n, nT)
 
 
 def _ptr_array(arrs):

@@ -297,3 +297,128 @@ extern "C" void dso_oracle_trace_on(int w, int h, const float* frame_dI, int n, 
 		lastTracePixelInterval[k] = p.lastTracePixelInterval;
 	}
 }
+
+// ---------------------------------------------------------------------------------------------------------
+// FullSystem::optimizeImmaturePoint (FullSystemOptPoint.cpp:51-209) with ImmaturePoint::linearizeResidual
+// (ImmaturePoint.cpp:499-570), projectPoint (ResidualProjections.h:69-101) and derive_idepth (:39-47)
+// ---------------------------------------------------------------------------------------------------------
+namespace {
+const float setting_minIdepthH_act = 100;        // settings.cpp:67
+const int setting_GNItsOnPointActivation = 3;    // settings.cpp:159
+enum { RS_IN = 0, RS_OOB = 1, RS_OUTLIER = 2 };
+
+struct Calib { float fxl, fyl, cxl, cyl, fxli, fyli, wM3G, hM3G; int w; };
+struct Target { const float* dI; const float* RTll; const float* tTll; const float* aff; };
+struct TmpRes { int state_state, state_NewState; float state_energy, state_NewEnergy; };   // the energies are doubles holding floats
+
+// ImmaturePoint::linearizeResidual: adds to Hdd / bd as it goes (also when it leaves early), returns the energy
+double linearize_residual(const Calib& C, const Target& T, float pu, float pv, const float* color, const float* weights, float energyTH,
+                          float outlierTHSlack, TmpRes& tr, float& Hdd, float& bd, float idepth)
+{
+	if (tr.state_state == RS_OOB) { tr.state_NewState = RS_OOB; return tr.state_energy; }       // :505-506
+	float energyLeft = 0;
+	for (int idx = 0; idx < patternNum; idx++)
+	{
+		int dx = patternP[idx][0], dy = patternP[idx][1];
+		// projectPoint, ResidualProjections.h:69-101
+		float KliP[3] = { (pu + dx - C.cxl) * C.fxli, (pv + dy - C.cyl) * C.fyli, 1 };
+		float Rk[3];
+		orc::mat33f_vec(T.RTll, KliP, Rk);
+		float ptp[3];
+		for (int i = 0; i < 3; i++) ptp[i] = Rk[i] + T.tTll[i] * idepth;
+		float drescale = 1.0f / ptp[2];
+		bool ok = drescale > 0;
+		float u = 0, v = 0, Ku = 0, Kv = 0;
+		if (ok)
+		{
+			u = ptp[0] * drescale;
+			v = ptp[1] * drescale;
+			Ku = u * C.fxl + C.cxl;
+			Kv = v * C.fyl + C.cyl;
+			ok = Ku > 1.1f && Kv > 1.1f && Ku < C.wM3G && Kv < C.hM3G;
+		}
+		if (!ok) { tr.state_NewState = RS_OOB; return tr.state_energy; }                        // :524-526
+		float hit[3];
+		interp33(T.dI, Ku, Kv, C.w, hit);
+		if (!std::isfinite((float)hit[0])) { tr.state_NewState = RS_OOB; return tr.state_energy; }   // :531
+		float residual = hit[0] - (T.aff[0] * color[idx] + T.aff[1]);
+		float hw = fabsf(residual) < setting_huberTH ? 1 : setting_huberTH / fabsf(residual);
+		energyLeft += weights[idx] * weights[idx] * hw * residual * residual * (2 - hw);
+		float dxInterp = hit[1] * C.fxl;
+		float dyInterp = hit[2] * C.fyl;
+		float d_idepth = (dxInterp * drescale * (T.tTll[0] - T.tTll[2] * u) + dyInterp * drescale * (T.tTll[1] - T.tTll[2] * v)) * 1.0f;   // SCALE_IDEPTH
+		hw *= weights[idx] * weights[idx];
+		Hdd += (hw * d_idepth) * d_idepth;
+		bd += (hw * residual) * d_idepth;
+	}
+	if (energyLeft > energyTH * outlierTHSlack) { energyLeft = energyTH * outlierTHSlack; tr.state_NewState = RS_OUTLIER; }   // :555-563
+	else tr.state_NewState = RS_IN;
+	tr.state_NewEnergy = energyLeft;
+	return energyLeft;
+}
+}   // namespace
+
+// result per point: 0 = returned null (:90-97 / :117-124), -1 = "(PointHessian*)-1" (:160-176), 1 = a PointHessian would be
+// created with idepth_out; res_state_out[k*nT + t] = final state_state of the residual to target t (ResState)
+extern "C" void dso_oracle_optimize_immature(int w, int h, float fx, float fy, float cx, float cy, int nT, const float* const* target_dI,
+                                             const float* RTll9, const float* tTll3, const float* aff2,
+                                             int n, const float* u, const float* v, const float* color8, const float* weights8,
+                                             const float* energyTH, const float* idepth_min, const float* idepth_max, int minObs,
+                                             int* result, float* idepth_out, int* res_state_out)
+{
+	Calib C;
+	C.fxl = fx; C.fyl = fy; C.cxl = cx; C.cyl = cy; C.fxli = 1.0f / fx; C.fyli = 1.0f / fy;     // CalibHessian::setValueScaled
+	C.wM3G = (float)(w - 3); C.hM3G = (float)(h - 3); C.w = w;                                   // globalCalib.cpp:70-71
+	for (int k = 0; k < n; k++)
+	{
+		const float* color = color8 + 8 * k; const float* weights = weights8 + 8 * k;
+		TmpRes res[16];
+		Target T[16];
+		const int nres = nT;
+		for (int t = 0; t < nres; t++)
+		{
+			res[t].state_NewEnergy = res[t].state_energy = 0; res[t].state_NewState = RS_OUTLIER; res[t].state_state = RS_IN;   // :57-66
+			T[t].dI = target_dI[t]; T[t].RTll = RTll9 + 9 * t; T[t].tTll = tTll3 + 3 * t; T[t].aff = aff2 + 2 * t;
+		}
+		float lastEnergy = 0, lastHdd = 0, lastbd = 0;
+		float currentIdepth = (idepth_max[k] + idepth_min[k]) * 0.5f;                            // :76
+		for (int i = 0; i < nres; i++)
+		{
+			lastEnergy += linearize_residual(C, T[i], u[k], v[k], color, weights, energyTH[k], 1000, res[i], lastHdd, lastbd, currentIdepth);
+			res[i].state_state = res[i].state_NewState;
+			res[i].state_energy = res[i].state_NewEnergy;
+		}
+		result[k] = 1; idepth_out[k] = NAN;
+		for (int t = 0; t < nres; t++) res_state_out[k * nT + t] = res[t].state_state;
+		if (!std::isfinite(lastEnergy) || lastHdd < setting_minIdepthH_act) { result[k] = 0; continue; }    // :90-97
+		float lambda = 0.1;
+		bool null_ret = false;
+		for (int iteration = 0; iteration < setting_GNItsOnPointActivation; iteration++)
+		{
+			float H = lastHdd;
+			H *= 1 + lambda;
+			float step = (1.0 / H) * lastbd;                                                     // :106 (double reciprocal, double product)
+			float newIdepth = currentIdepth - step;
+			float newHdd = 0, newbd = 0, newEnergy = 0;
+			for (int i = 0; i < nres; i++)
+				newEnergy += linearize_residual(C, T[i], u[k], v[k], color, weights, energyTH[k], 1, res[i], newHdd, newbd, newIdepth);
+			if (!std::isfinite(lastEnergy) || newHdd < setting_minIdepthH_act) { null_ret = true; break; }   // :117-124
+			if (newEnergy < lastEnergy)
+			{
+				currentIdepth = newIdepth; lastHdd = newHdd; lastbd = newbd; lastEnergy = newEnergy;
+				for (int i = 0; i < nres; i++) { res[i].state_state = res[i].state_NewState; res[i].state_energy = res[i].state_NewEnergy; }
+				lambda *= 0.5;
+			}
+			else lambda *= 5;
+			if (fabsf(step) < 0.0001 * currentIdepth) break;                                     // :151
+		}
+		for (int t = 0; t < nres; t++) res_state_out[k * nT + t] = res[t].state_state;
+		if (null_ret) { result[k] = 0; continue; }
+		if (!std::isfinite(currentIdepth)) { result[k] = -1; continue; }                        // :155-159
+		int numGoodRes = 0;
+		for (int i = 0; i < nres; i++) if (res[i].state_state == RS_IN) numGoodRes++;
+		if (numGoodRes < minObs) { result[k] = -1; continue; }                                   // :162-170
+		if (!std::isfinite(energyTH[k])) { result[k] = -1; continue; }                           // :174 (PointHessian copies energyTH)
+		idepth_out[k] = currentIdepth;                                                           // :181-182
+	}
+}

@@ -608,3 +608,41 @@ extern "C" void dso_ref_trace_on(int w, int h, const float* frame_dI, int n, con
 	}
 	release_frame(frame); release_frame(host);
 }
+
+// FullSystem::optimizeImmaturePoint (FullSystemOptPoint.cpp:51, compiled unmodified).  The FullSystem object is raw zeroed
+// memory with only the members that function touches brought to life (its constructor starts threads and opens log files).
+extern "C" void dso_ref_optimize_immature(int w, int h, float fx, float fy, float cx, float cy, int nT, const float* const* target_dI,
+                                          const float* RTll9, const float* tTll3, const float* aff2,
+                                          int n, const float* u, const float* v, const float* color8, const float* weights8,
+                                          const float* energyTH, const float* idepth_min, const float* idepth_max, int minObs,
+                                          int* result, float* idepth_out, int* res_state_out)
+{
+	set_calib(w, h, 1, fx, fy, cx, cy);
+	FullSystem* fs = (FullSystem*)calloc(1, sizeof(FullSystem));
+	new (&fs->Hcalib) CalibHessian();
+	new (&fs->frameHessians) std::vector<FrameHessian*>();
+	FrameHessian* host = frame_with_dI(w, h, target_dI[0]);
+	host->idx = 0; host->frameID = 0;
+	fs->frameHessians.push_back(host);
+	host->targetPrecalc.resize(nT + 1);
+	for (int t = 0; t < nT; t++)
+	{
+		FrameHessian* fh = frame_with_dI(w, h, target_dI[t]);
+		fh->idx = t + 1; fh->frameID = t + 1; fh->shell->id = t + 1;
+		fs->frameHessians.push_back(fh);
+		FrameFramePrecalc& P = host->targetPrecalc[t + 1];
+		for (int r = 0; r < 3; r++) { for (int c = 0; c < 3; c++) P.PRE_RTll(r, c) = RTll9[9 * t + r * 3 + c]; P.PRE_tTll[r] = tTll3[3 * t + r]; }
+		P.PRE_aff_mode[0] = aff2[2 * t]; P.PRE_aff_mode[1] = aff2[2 * t + 1];
+	}
+	std::vector<ImmaturePointTemporaryResidual> tmp(nT + 1);
+	for (int k = 0; k < n; k++)
+	{
+		ImmaturePoint* ip = raw_immature(host, u[k], v[k], 1, color8 + 8 * k, weights8 + 8 * k);
+		ip->energyTH = energyTH[k]; ip->idepth_min = idepth_min[k]; ip->idepth_max = idepth_max[k];
+		PointHessian* ph = fs->optimizeImmaturePoint(ip, minObs, tmp.data());
+		result[k] = ph == 0 ? 0 : (ph == (PointHessian*)((long)(-1)) ? -1 : 1);
+		idepth_out[k] = result[k] == 1 ? ph->idepth : NAN;
+		for (int t = 0; t < nT; t++) res_state_out[k * nT + t] = (int)tmp[t].state_state;
+	}
+	for (FrameHessian* fh : fs->frameHessians) release_frame(fh);
+}

@@ -277,3 +277,22 @@ def test_immature_point_init_and_trace_on_bit_exact(pkg, window_small):
     assert good.sum() > 100
     mid = 0.5 * (so["idepth_min"][good] + so["idepth_max"][good])
     assert np.median(np.abs(mid - sc["idepth_true"][good]) / sc["idepth_true"][good]) < 0.05     # the search finds the true depth
+
+
+def test_optimize_immature_point_bit_exact(pkg, window_small):
+    """next row N3: FullSystem::optimizeImmaturePoint + ImmaturePoint::linearizeResidual (FullSystemOptPoint.cpp:51-209,
+    ImmaturePoint.cpp:499-570): result code, activated inverse depth and residual states, bit for bit"""
+    W = window_small
+    sc = pkg.synthetic.activation_scenario(W, host_idx=1, n_points=600)
+    fields = O.immature_init(O.make_images(sc["host_image"], 1)[0][0], sc["u"], sc["v"])
+    dIs = [O.make_images(im, 1)[0][0] for im in sc["images"]]
+    args = (W.K, dIs, sc["RTll"], sc["tTll"], sc["aff"], sc["u"], sc["v"], fields, sc["idepth_min"], sc["idepth_max"])
+    ro, io, so = O.optimize_immature(*args, min_obs=1)
+    rr, ir, sr = O.optimize_immature(*args, min_obs=1, kind="ref")
+    assert np.array_equal(ro, rr)
+    ok = ro == 1
+    assert ok.sum() > 200 and (ro == 0).sum() + (ro == -1).sum() > 10, np.bincount(ro + 1)
+    assert np.array_equal(bits(io[ok]), bits(ir[ok]))
+    assert np.array_equal(so[ro != 0], sr[rr != 0])
+    good = ok & ~sc["wrong"]
+    assert np.median(np.abs(io[good] - sc["idepth_true"][good]) / sc["idepth_true"][good]) < 0.01      # converges to the true depth
