@@ -57,6 +57,8 @@ SIGNATURES = {
     "dso_b200_tracker_get_cloud": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, vp, C.POINTER(C.c_int)]),
     "dso_b200_trace_set_points": (C.c_int, [vp, C.c_int, f32p, f32p, f32p, f32p, f32p, f32p, i32p, f32p, f32p, f32p, i32p, vp, vp]),
     "dso_b200_trace_new_coarse": (C.c_int, [vp, C.c_int, C.c_int, f32p, f32p, f32p, vp, vp, vp, vp, vp, vp]),
+    "dso_b200_optimize_immature": (C.c_int, [vp, C.c_int, i32p, C.c_float, C.c_float, C.c_float, C.c_float, f32p, f32p, f32p, C.c_int,
+                                             f32p, f32p, f32p, f32p, f32p, f32p, f32p, C.c_int, i32p, f32p, i32p]),
     "dso_b200_make_images_async": (C.c_int, [vp, C.c_int, vp, C.c_int, C.c_int, C.c_int]),
     "dso_b200_make_images_dev": (C.c_int, [vp, C.c_int, vp, C.c_int, C.c_int, C.c_int, vp]),
     "dso_b200_tracker_set_ref": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float,
@@ -291,6 +293,16 @@ class Context:
         self._check(self.L.dso_b200_trace_new_coarse(self.h, slot, KRKi.shape[0], KRKi.reshape(-1), np.ascontiguousarray(Kt, dtype=np.float32).reshape(-1),
                                                      np.ascontiguousarray(aff, dtype=np.float32).reshape(-1), *ptrs))
         return out
+
+    def optimize_immature(self, target_slots, K, RTll, tTll, aff, u, v, fields, idepth_min, idepth_max, min_obs=1):
+        f = lambda a: np.ascontiguousarray(a, dtype=np.float32).reshape(-1)
+        fx, fy, cx, cy = K
+        n, nT = len(u), len(target_slots)
+        result = np.zeros(n, dtype=np.int32); idp = np.zeros(n, dtype=np.float32); rs = np.zeros(n * nT, dtype=np.int32)
+        self._check(self.L.dso_b200_optimize_immature(self.h, nT, np.ascontiguousarray(target_slots, dtype=np.int32), fx, fy, cx, cy,
+                                                      f(RTll), f(tTll), f(aff), n, f(u), f(v), f(fields["color"]), f(fields["weights"]),
+                                                      f(fields["energyTH"]), f(idepth_min), f(idepth_max), min_obs, result, idp, rs))
+        return result, idp, rs.reshape(n, nT)
 
     def make_images_async(self, slot, color_ptr, w, h, levels):
         """color_ptr: host address (pinned) or numpy array that the caller keeps alive until the slot is consumed"""

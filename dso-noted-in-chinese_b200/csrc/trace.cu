@@ -387,3 +387,209 @@ extern "C" int dso_b200_trace_new_coarse(dso_b200_ctx* ctx, int frame_slot, int 
 	if (idepth_min_out || idepth_max_out || quality_out || status_out || lastTraceUV2_out || lastTracePixelInterval_out) CK(cudaStreamSynchronize(s));
 	return 0;
 }
+
+// =========================================================================================================
+// FullSystem::optimizeImmaturePoint (FullSystemOptPoint.cpp:51-209) + ImmaturePoint::linearizeResidual
+// (ImmaturePoint.cpp:499-570): the per-point Gauss-Newton on the inverse depth that decides about activation.
+// Eight lanes per point again; the residuals to the <= 7 target frames are visited one after the other (the reference's
+// running sums Hdd, bd, energy cross residual boundaries and keep the partial contribution of a residual that leaves
+// early), the eight pattern samples of a residual in parallel with the sums taken in pattern order.
+// =========================================================================================================
+#define RS_IN 0
+#define RS_OOB 1
+#define RS_OUTLIER 2
+#define ACT_MAXT (MAXF - 1)
+
+struct ActTargets
+{
+	int nT, w;
+	float fxl, fyl, cxl, cyl, fxli, fyli, wM3G, hM3G;
+	const float4* img[ACT_MAXT];
+	float RTll[ACT_MAXT][9], tTll[ACT_MAXT][3], aff[ACT_MAXT][2];
+};
+
+struct ActRes { int state, newState; float energy, newEnergy; };
+
+// linearizeResidual for target t; returns the value the reference returns (as double), updates Hdd / bd
+__device__ __forceinline__ double act_linearize(const ActTargets& A, int t, float pu, float pv, float color, float weight, float energyTH,
+                                                float slack, ActRes& r, float& Hdd, float& bd, float idepth, int idx, int base, unsigned gmask)
+{
+	if (r.state == RS_OOB) { r.newState = RS_OOB; return (double)r.energy; }            // :505-506
+	const float dxp = (float)c_trace_pattern[idx][0], dyp = (float)c_trace_pattern[idx][1];
+	// projectPoint, ResidualProjections.h:69-101
+	const float k0 = fmul(fsub(fadd(pu, dxp), A.cxl), A.fxli), k1 = fmul(fsub(fadd(pv, dyp), A.cyl), A.fyli);
+	const float* R = A.RTll[t]; const float* tt = A.tTll[t];
+	float ptp[3];
+#pragma unroll
+	for (int i = 0; i < 3; i++) ptp[i] = fadd(dot3e(R[3 * i], k0, R[3 * i + 1], k1, R[3 * i + 2], 1.f), fmul(tt[i], idepth));
+	const float drescale = fdiv(1.0f, ptp[2]);
+	bool ok = drescale > 0.f;
+	float u = 0.f, v = 0.f, Ku = 0.f, Kv = 0.f;
+	if (ok)
+	{
+		u = fmul(ptp[0], drescale); v = fmul(ptp[1], drescale);
+		Ku = fadd(fmul(u, A.fxl), A.cxl); Kv = fadd(fmul(v, A.fyl), A.cyl);
+		ok = Ku > 1.1f && Kv > 1.1f && Ku < A.wM3G && Kv < A.hM3G;
+	}
+	float tE = 0.f, tH = 0.f, tb = 0.f;
+	if (ok)
+	{
+		float h0, h1, h2;
+		tr_interp(A.img[t], Ku, Kv, A.w, h0, h1, h2, true);
+		if (!isfinite(h0)) ok = false;                                                    // :531
+		else
+		{
+			const float residual = fsub(h0, fadd(fmul(A.aff[t][0], color), A.aff[t][1]));
+			const float ar = fabsf(residual);
+			float hw = ar < 9.f ? 1.f : fdiv(9.f, ar);
+			tE = fmul(fmul(fmul(fmul(fmul(weight, weight), hw), residual), residual), fsub(2.f, hw));
+			const float dxI = fmul(h1, A.fxl), dyI = fmul(h2, A.fyl);
+			const float d_id = fmul(fadd(fmul(fmul(dxI, drescale), fsub(tt[0], fmul(tt[2], u))), fmul(fmul(dyI, drescale), fsub(tt[1], fmul(tt[2], v)))), 1.0f);
+			hw = fmul(hw, fmul(weight, weight));
+			tH = fmul(fmul(hw, d_id), d_id);
+			tb = fmul(fmul(hw, residual), d_id);
+		}
+	}
+	// the first failing pattern pixel ends the residual; the pixels before it have already been added (:524-531)
+	const unsigned failmask = (__ballot_sync(gmask, !ok) >> base) & 0xffu;
+	const int firstFail = failmask ? (__ffs(failmask) - 1) : 8;
+	float energyLeft = 0.f;
+#pragma unroll
+	for (int k = 0; k < 8; k++)
+	{
+		const float ek = __shfl_sync(gmask, tE, base + k), hk = __shfl_sync(gmask, tH, base + k), bk = __shfl_sync(gmask, tb, base + k);
+		if (k < firstFail) { energyLeft = fadd(energyLeft, ek); Hdd = fadd(Hdd, hk); bd = fadd(bd, bk); }
+	}
+	if (firstFail < 8) { r.newState = RS_OOB; return (double)r.energy; }
+	const float th = fmul(energyTH, slack);
+	if (energyLeft > th) { energyLeft = th; r.newState = RS_OUTLIER; }                   // :555-563
+	else r.newState = RS_IN;
+	r.newEnergy = energyLeft;
+	return (double)energyLeft;
+}
+
+__global__ void __launch_bounds__(256) optimize_immature_kernel(int n, ActTargets A, int minObs, const float* __restrict__ pu, const float* __restrict__ pv,
+                                                                const float* __restrict__ color8, const float* __restrict__ weights8,
+                                                                const float* __restrict__ energyTH, const float* __restrict__ idmin,
+                                                                const float* __restrict__ idmax, int* result, float* idepth_out, int* res_state)
+{
+	const int tid = threadIdx.x, lane = tid & 31, g = tid >> 3, idx = tid & 7, base = lane & ~7;
+	const int k = blockIdx.x * TR_PTS_PER_BLOCK + g;
+	if (k >= n) return;
+	const unsigned gmask = 0xffu << base;
+	const float u = pu[k], v = pv[k], color = color8[8 * (size_t)k + idx], weight = weights8[8 * (size_t)k + idx], eTH = energyTH[k];
+	const int nres = A.nT;
+	ActRes res[ACT_MAXT];
+#pragma unroll
+	for (int t = 0; t < ACT_MAXT; t++) { res[t].state = RS_IN; res[t].newState = RS_OUTLIER; res[t].energy = 0.f; res[t].newEnergy = 0.f; }   // :57-66
+	float lastEnergy = 0.f, lastHdd = 0.f, lastbd = 0.f;
+	float currentIdepth = fmul(fadd(idmax[k], idmin[k]), 0.5f);                           // :76
+#pragma unroll
+	for (int t = 0; t < ACT_MAXT; t++)
+		if (t < nres)
+		{
+			lastEnergy = (float)((double)lastEnergy + act_linearize(A, t, u, v, color, weight, eTH, 1000.f, res[t], lastHdd, lastbd, currentIdepth, idx, base, gmask));
+			res[t].state = res[t].newState; res[t].energy = res[t].newEnergy;
+		}
+	int out = 1;
+	if (!isfinite(lastEnergy) || lastHdd < 100.f) out = 0;                                // :90-97 setting_minIdepthH_act
+	if (out)
+	{
+		float lambda = 0.1f;
+		for (int iteration = 0; iteration < 3; iteration++)                               // setting_GNItsOnPointActivation
+		{
+			float H = lastHdd;
+			H = fmul(H, fadd(1.f, lambda));
+			const float step = (float)((1.0 / (double)H) * (double)lastbd);                 // :106
+			const float newIdepth = fsub(currentIdepth, step);
+			float newHdd = 0.f, newbd = 0.f, newEnergy = 0.f;
+#pragma unroll
+			for (int t = 0; t < ACT_MAXT; t++)
+				if (t < nres)
+					newEnergy = (float)((double)newEnergy + act_linearize(A, t, u, v, color, weight, eTH, 1.f, res[t], newHdd, newbd, newIdepth, idx, base, gmask));
+			if (!isfinite(lastEnergy) || newHdd < 100.f) { out = 0; break; }                // :117-124
+			if (newEnergy < lastEnergy)
+			{
+				currentIdepth = newIdepth; lastHdd = newHdd; lastbd = newbd; lastEnergy = newEnergy;
+#pragma unroll
+				for (int t = 0; t < ACT_MAXT; t++) { res[t].state = res[t].newState; res[t].energy = res[t].newEnergy; }
+				lambda = fmul(lambda, 0.5f);
+			}
+			else lambda = fmul(lambda, 5.f);
+			if ((double)fabsf(step) < 0.0001 * (double)currentIdepth) break;                // :151
+		}
+	}
+	if (out)
+	{
+		if (!isfinite(currentIdepth)) out = -1;                                           // :155-159
+		else
+		{
+			int good = 0;
+#pragma unroll
+			for (int t = 0; t < ACT_MAXT; t++) if (t < nres && res[t].state == RS_IN) good++;
+			if (good < minObs || !isfinite(eTH)) out = -1;                                  // :162-174
+		}
+	}
+	if (idx == 0)
+	{
+		result[k] = out;
+		idepth_out[k] = out == 1 ? currentIdepth : __int_as_float(0x7fc00000);
+#pragma unroll
+		for (int t = 0; t < ACT_MAXT; t++) if (t < nres) res_state[(size_t)k * nres + t] = res[t].state;
+	}
+}
+
+extern "C" int dso_b200_optimize_immature(dso_b200_ctx* ctx, int n_targets, const int* target_slots, float fx, float fy, float cx, float cy,
+                                          const float* RTll9, const float* tTll3, const float* aff2,
+                                          int n, const float* u, const float* v, const float* color8, const float* weights8, const float* energyTH,
+                                          const float* idepth_min, const float* idepth_max, int minObs,
+                                          int* result, float* idepth_out, int* res_state_out)
+{
+	ARG_CHECK(ctx && target_slots && RTll9 && tTll3 && aff2 && u && v && color8 && weights8 && energyTH && idepth_min && idepth_max && result && idepth_out,
+	          "null argument");
+	ARG_CHECK(n_targets >= 1 && n_targets <= ACT_MAXT && n >= 1, "1..7 targets, n >= 1");
+	CK(cudaSetDevice(ctx->device));
+	ActTargets A;
+	memset(&A, 0, sizeof(A));
+	A.nT = n_targets;
+	for (int t = 0; t < n_targets; t++)
+	{
+		const int sl = target_slots[t];
+		ARG_CHECK(sl >= 0 && sl < ctx->n_slots && ctx->slots[sl].valid, "target frame slot empty");
+		ARG_CHECK(t == 0 || (ctx->slots[sl].w == A.w), "target frames differ in size");
+		int rc = frame_slot_wait(ctx, sl);
+		if (rc) return rc;
+		A.w = ctx->slots[sl].w;
+		A.img[t] = ctx->slots[sl].pyr[0];
+		memcpy(A.RTll[t], RTll9 + 9 * t, 36); memcpy(A.tTll[t], tTll3 + 3 * t, 12); memcpy(A.aff[t], aff2 + 2 * t, 8);
+	}
+	const int h = ctx->slots[target_slots[0]].h;
+	// CalibHessian::setValueScaled (HessianBlocks.h:383-397) and wM3G / hM3G (globalCalib.cpp:70-71)
+	A.fxl = fx; A.fyl = fy; A.cxl = cx; A.cyl = cy; A.fxli = 1.0f / fx; A.fyli = 1.0f / fy;
+	A.wM3G = (float)(A.w - 3); A.hM3G = (float)(h - 3);
+	// scratch: reuse the trace workspace's arrays of the same shape (separate point set: allocate a private block)
+	const size_t m = (size_t)n;
+	float* d = nullptr;
+	CK(cudaMalloc(&d, m * (4 + 4 + 32 + 32 + 4 + 4 + 4 + 4 + 4) + m * n_targets * 4));
+	float* d_u = d; float* d_v = d_u + m; float* d_c = d_v + m; float* d_w = d_c + 8 * m; float* d_e = d_w + 8 * m;
+	float* d_lo = d_e + m; float* d_hi = d_lo + m; float* d_id = d_hi + m; int* d_res = (int*)(d_id + m); int* d_rs = d_res + m;
+	cudaStream_t s = ctx->stream;
+	cudaError_t e = cudaSuccess;
+#define UP(dst, src, bytes) if (e == cudaSuccess) e = cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, s)
+	UP(d_u, u, m * 4); UP(d_v, v, m * 4); UP(d_c, color8, m * 32); UP(d_w, weights8, m * 32); UP(d_e, energyTH, m * 4);
+	UP(d_lo, idepth_min, m * 4); UP(d_hi, idepth_max, m * 4);
+#undef UP
+	if (e == cudaSuccess)
+	{
+		optimize_immature_kernel<<<(n + TR_PTS_PER_BLOCK - 1) / TR_PTS_PER_BLOCK, 256, 0, s>>>(n, A, minObs, d_u, d_v, d_c, d_w, d_e, d_lo, d_hi, d_res, d_id, d_rs);
+		ctx->launches++;
+		e = cudaGetLastError();
+	}
+	if (e == cudaSuccess) e = cudaMemcpyAsync(result, d_res, m * 4, cudaMemcpyDeviceToHost, s);
+	if (e == cudaSuccess) e = cudaMemcpyAsync(idepth_out, d_id, m * 4, cudaMemcpyDeviceToHost, s);
+	if (e == cudaSuccess && res_state_out) e = cudaMemcpyAsync(res_state_out, d_rs, m * n_targets * 4, cudaMemcpyDeviceToHost, s);
+	if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+	cudaFree(d);
+	CK(e);
+	return 0;
+}

@@ -363,6 +363,19 @@ int dso_b200_trace_new_coarse(dso_b200_ctx* ctx, int frame_slot, int n_hosts, co
                               float* idepth_min_out, float* idepth_max_out, float* quality_out, int* status_out,
                               float* lastTraceUV2_out, float* lastTracePixelInterval_out);
 
+/* FullSystem::optimizeImmaturePoint (FullSystemOptPoint.cpp:51-209, with ImmaturePoint::linearizeResidual,
+ * ImmaturePoint.cpp:499-570) for n immature points of ONE host key frame: the other key frames are the targets
+ * (target_slots: their device pyramids; per target PRE_RTll (9, row-major), PRE_tTll (3), PRE_aff_mode (2) of
+ * host->targetPrecalc[target], HessianBlocks.h:73-99), fx..cy = HCalib->fxl() ... cyl().
+ * result[k]: 0 = the reference returns null, -1 = its "(PointHessian*)-1" marker, 1 = the point is activated with
+ * idepth_out[k] (NaN otherwise); res_state_out[k*n_targets + t] (may be NULL): final ResState of the temporary residual to
+ * target t, i.e. which PointFrameResiduals to create (:185-205).  Called from FullSystem::activatePointsMT_Reductor. */
+int dso_b200_optimize_immature(dso_b200_ctx* ctx, int n_targets, const int* target_slots, float fx, float fy, float cx, float cy,
+                               const float* RTll9, const float* tTll3, const float* aff2,
+                               int n, const float* u, const float* v, const float* color8, const float* weights8, const float* energyTH,
+                               const float* idepth_min, const float* idepth_max, int minObs,
+                               int* result, float* idepth_out, int* res_state_out);
+
 #ifdef __cplusplus
 }
 #endif

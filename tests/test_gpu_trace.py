@@ -44,3 +44,26 @@ def test_trace_new_coarse_bit_exact(pkg, oracle, window_small, window_vga, which
         seen |= set(so["status"].tolist())
     assert {0, 1}.issubset(seen) and len(seen) >= 3, seen
     ctx.close()
+
+
+@pytest.mark.parametrize("which,min_obs", [("small", 1), ("vga", 2)])
+def test_optimize_immature_bit_exact(pkg, oracle, window_small, window_vga, which, min_obs):
+    """FullSystem::optimizeImmaturePoint on the device vs the pinned oracle: result codes, activated inverse depths and
+    residual states bit for bit (null / delete / activate exits all present)"""
+    W = window_small if which == "small" else window_vga
+    sc = pkg.synthetic.activation_scenario(W, host_idx=1, n_points=900)
+    fields = oracle.immature_init(oracle.make_images(sc["host_image"], 1)[0][0], sc["u"], sc["v"])
+    dIs = [oracle.make_images(im, 1)[0][0] for im in sc["images"]]
+    ro, io, so = oracle.optimize_immature(W.K, dIs, sc["RTll"], sc["tTll"], sc["aff"], sc["u"], sc["v"], fields,
+                                          sc["idepth_min"], sc["idepth_max"], min_obs=min_obs)
+    ctx = pkg.Context(0, W.w, W.h, len(dIs) + 1)
+    for i, im in enumerate(sc["images"]):
+        ctx.make_images(i, im, 1, want_host=False)
+    rg, ig, sg = ctx.optimize_immature(np.arange(len(dIs)), W.K, sc["RTll"], sc["tTll"], sc["aff"], sc["u"], sc["v"], fields,
+                                       sc["idepth_min"], sc["idepth_max"], min_obs=min_obs)
+    assert np.array_equal(rg, ro), np.nonzero(rg != ro)[0][:10]
+    ok = ro == 1
+    assert ok.sum() > 200 and (ro != 1).sum() > 10
+    assert np.array_equal(_bits(ig[ok]), _bits(io[ok]))
+    assert np.array_equal(sg[ro != 0], so[ro != 0])
+    ctx.close()
