@@ -101,6 +101,9 @@ extern "C" int dso_b200_create(int device, int max_w, int max_h, int n_frame_slo
 		CK(cudaHostAlloc((void**)&T.h_sums, S_COUNT * sizeof(float), cudaHostAllocDefault));
 		CK(cudaMalloc(&T.d_track_in, 4096 * 2));
 		CK(cudaMalloc(&T.d_track_out, sizeof(dso_b200_track_result) * DSO_B200_MAX_HYP));
+		CK(cudaMalloc(&T.d_mc_part, (size_t)DSO_B200_MAX_HYP * 2 * 16 * S_COUNT * sizeof(float)));
+		CK(cudaMalloc(&T.d_mc_count, DSO_B200_MAX_HYP * sizeof(unsigned int)));
+		CK(cudaMemset(T.d_mc_count, 0, DSO_B200_MAX_HYP * sizeof(unsigned int)));
 		CK(cudaHostAlloc(&T.h_track_in, TRACK_IN_RING * TRACK_IN_BLOCK, cudaHostAllocMapped));
 		CK(cudaHostAlloc(&T.h_track_out, sizeof(dso_b200_track_result) * DSO_B200_MAX_HYP, cudaHostAllocMapped));
 		CK(cudaHostAlloc((void**)&T.h_flags, sizeof(unsigned int) * DSO_B200_MAX_HYP, cudaHostAllocMapped));
@@ -135,7 +138,7 @@ extern "C" void dso_b200_destroy(dso_b200_ctx* ctx)
 	{
 		TrackerSlot& T = ctx->trk[t];
 		cudaFree(T.base); cudaFree(T.d_sums); cudaFree(T.d_partials); cudaFree(T.d_ticket);
-		cudaFreeHost(T.h_sums); cudaFree(T.d_track_in); cudaFree(T.d_track_out);
+		cudaFreeHost(T.h_sums); cudaFree(T.d_track_in); cudaFree(T.d_track_out); cudaFree(T.d_mc_part); cudaFree(T.d_mc_count);
 		cudaFreeHost(T.h_track_in); cudaFreeHost(T.h_track_out); cudaFreeHost(T.h_flags);
 	}
 	cudaStreamDestroy(ctx->stream);

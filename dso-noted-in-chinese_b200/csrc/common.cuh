@@ -76,6 +76,8 @@ struct TrackerSlot
 	// batched tracker workspace
 	void* d_track_in;
 	void* d_track_out;
+	float* d_mc_part;           // multi-cluster tracking: cluster totals [hyp][2][16][S_COUNT]
+	unsigned int* d_mc_count;   // and the arrival counter per hypothesis
 	void* h_track_in;           // mapped pinned ring of TRACK_IN_RING input blocks, read by the kernel over PCIe (no H2D copy node)
 	void* h_track_out;          // mapped pinned: the kernel writes its results here, then h_flags[hyp] = seq
 	unsigned int* h_flags;      // mapped pinned, one word per hypothesis

@@ -33,6 +33,7 @@ namespace cg = cooperative_groups;
 #define EVAL_THREADS 256
 #define PERS_THREADS 256
 #define MAX_CLUSTER 16
+#define DSO_B200_TRACK_MAX_NC 16      // clusters one hypothesis may be spread over
 
 struct EvalParams
 {
@@ -845,12 +846,17 @@ template <int NT>
 __global__ void __launch_bounds__(NT, 1)
 track_persistent_kernel(TrackLevels TL, dso_b200_track_opts opt, const TrackIn* __restrict__ in,
                         dso_b200_track_result* out, int coarsestLvl, int smem_pts_cap, long long* phase_cycles,
-                        dso_b200_track_result* host_out, unsigned int* host_flags, unsigned int seq)
+                        dso_b200_track_result* host_out, unsigned int* host_flags, unsigned int seq,
+                        int NC, float* mc_part, unsigned int* mc_count)
 {
+	// NC > 1: one hypothesis is spread over NC clusters (large clouds): cluster totals go through global memory and a
+	// monotonic arrival counter; every CTA of the grid must be resident (the host caps NC by cudaOccupancyMaxActiveClusters)
 	cg::cluster_group cluster = cg::this_cluster();
 	const unsigned CS = cluster.num_blocks();
 	const unsigned rank = cluster.block_rank();
-	const int hyp = blockIdx.x / CS;
+	const int hyp = blockIdx.x / (CS * NC);
+	const int cidx = (blockIdx.x / CS) % NC;
+	unsigned int mc_round = 0;
 	const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 	long long tph[5] = { 0, 0, 0, 0, 0 };
 	long long tc0 = 0, tk0 = 0, tg0 = 0;
@@ -904,8 +910,8 @@ track_persistent_kernel(TrackLevels TL, dso_b200_track_opts opt, const TrackIn* 
 	{
 		const int lvl = S.lvl;
 		const int n = TL.pc_n[lvl];
-		const int per = (n + CS - 1) / CS;
-		const int beg = min((int)rank * per, n), end = min(beg + per, n);
+		const int per = (n + CS * NC - 1) / (CS * NC);
+		const int beg = min((int)(cidx * CS + rank) * per, n), end = min(beg + per, n);
 		const float4* __restrict__ gp = TL.pc[lvl];
 		const bool use_smem = (end - beg) <= smem_pts_cap;
 		if (use_smem && staged_lvl != lvl)
@@ -951,8 +957,36 @@ track_persistent_kernel(TrackLevels TL, dso_b200_track_opts opt, const TrackIn* 
 #pragma unroll
 			for (int r = 0; r < MAX_CLUSTER; r++) s += v[r];
 			s_tot[tid] = s;
+			if (NC > 1 && rank == 0) __stcg(mc_part + ((size_t)(hyp * 2 + (mc_round & 1)) * NC + cidx) * S_COUNT + tid, s);
 		}
 		__syncthreads();
+		if (NC > 1)
+		{
+			mc_round++;
+			if (tid == 0)
+			{
+				if (rank == 0) { __threadfence(); atomicAdd(mc_count + hyp, 1u); }
+				const unsigned int want = mc_round * (unsigned)NC;
+				while (*((volatile unsigned int*)(mc_count + hyp)) < want) { }
+				__threadfence();
+			}
+			__syncthreads();
+			if (tid < S_COUNT)
+			{
+				const float* src = mc_part + (size_t)(hyp * 2 + ((mc_round - 1) & 1)) * NC * S_COUNT + tid;
+				float sum = 0.f;
+				for (int c0 = 0; c0 < NC; c0 += 8)                // clusters in index order, eight loads in flight
+				{
+					float t[8];
+#pragma unroll
+					for (int q = 0; q < 8; q++) t[q] = (c0 + q < NC) ? __ldcg(src + (size_t)(c0 + q) * S_COUNT) : 0.f;
+#pragma unroll
+					for (int q = 0; q < 8; q++) if (c0 + q < NC) sum += t[q];
+				}
+				s_tot[tid] = sum;
+			}
+			__syncthreads();
+		}
 		if (phase_cycles) { long long t = clock64(); tph[2] += t - tc0; tc0 = t; }
 		if (warp == 0) lm_step_warp(S, s_tot, TL, opt, &s_res, sP, n, lane, phase_cycles ? lmt : nullptr);
 		__syncthreads();
@@ -961,7 +995,7 @@ track_persistent_kernel(TrackLevels TL, dso_b200_track_opts opt, const TrackIn* 
 		buf ^= 1;
 	}
 	cluster.sync();                // nobody leaves while a peer may still be writing into it
-	if (rank == 0)
+	if (rank == 0 && cidx == 0)
 	{
 		const int nwords = sizeof(dso_b200_track_result) / 4;
 		const unsigned int* src = reinterpret_cast<const unsigned int*>(&s_res);
@@ -1272,7 +1306,7 @@ static int enqueue_track(dso_b200_ctx* ctx, int trk, int frame_slot, int nHyp, c
 	cap = (int)std::min<size_t>((size_t)per, smem_cap_bytes / sizeof(float4));
 	dyn = (size_t)cap * sizeof(float4);
 	void (*kern)(TrackLevels, dso_b200_track_opts, const TrackIn*, dso_b200_track_result*, int, int, long long*,
-	             dso_b200_track_result*, unsigned int*, unsigned int) =
+	             dso_b200_track_result*, unsigned int*, unsigned int, int, float*, unsigned int*) =
 		nt == 128 ? track_persistent_kernel<128> : (nt == 512 ? track_persistent_kernel<512> : (nt == 384 ? track_persistent_kernel<384> : track_persistent_kernel<256>));
 	if (nt != 128 && nt != 512 && nt != 384) nt = 256;
 	static bool attr_set[64][4] = { { false } };
@@ -1283,8 +1317,39 @@ static int enqueue_track(dso_b200_ctx* ctx, int trk, int frame_slot, int nHyp, c
 		CK(cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
 		attr_set[ctx->device & 63][ki] = true;
 	}
+	// large clouds, one hypothesis: spread it over several clusters (DSO_B200_TRACK_NCLUSTERS overrides; 1 = off).  All
+	// CTAs exchange through a spin barrier, so the count is capped by what can be resident at once.
+	int nc = 1;
+	static int env_nc = -1;
+	if (env_nc < 0) { const char* e = getenv("DSO_B200_TRACK_NCLUSTERS"); env_nc = e ? atoi(e) : 0; }
+	if (nHyp == 1 && (env_nc > 1 || (env_nc == 0 && max_n >= 32768)))
+	{
+		cudaLaunchConfig_t q = {};
+		q.gridDim = dim3(cs, 1, 1); q.blockDim = dim3(nt, 1, 1);
+		cudaLaunchAttribute qa[1];
+		qa[0].id = cudaLaunchAttributeClusterDimension; qa[0].val.clusterDim.x = cs; qa[0].val.clusterDim.y = 1; qa[0].val.clusterDim.z = 1;
+		q.attrs = qa; q.numAttrs = 1;
+		q.dynamicSmemBytes = 0;
+		int maxc = 0;
+		nc = env_nc > 1 ? env_nc : (max_n + 16383) / 16384;
+		// the per-CTA slice shrinks with nc, and so does the dynamic shared memory the query must assume
+		for (int it = 0; it < 4; it++)
+		{
+			q.dynamicSmemBytes = std::min<size_t>((size_t)((max_n + cs * nc - 1) / (cs * nc)), smem_cap_bytes / sizeof(float4)) * sizeof(float4);
+			CK(cudaOccupancyMaxActiveClusters(&maxc, kern, &q));
+			if (maxc < 1) maxc = 1;
+			if (nc <= maxc) break;
+			nc = maxc;
+		}
+		if (nc > DSO_B200_TRACK_MAX_NC) nc = DSO_B200_TRACK_MAX_NC;
+		if (nc < 1) nc = 1;
+		per = (max_n + cs * nc - 1) / (cs * nc);
+		cap = (int)std::min<size_t>((size_t)per, smem_cap_bytes / sizeof(float4));
+		dyn = (size_t)cap * sizeof(float4);
+		if (nc > 1) CK(cudaMemsetAsync(T.d_mc_count, 0, sizeof(unsigned int) * DSO_B200_MAX_HYP, ctx->stream));
+	}
 	cudaLaunchConfig_t cfg = {};
-	cfg.gridDim = dim3(nHyp * cs, 1, 1);
+	cfg.gridDim = dim3(nHyp * cs * nc, 1, 1);
 	cfg.blockDim = dim3(nt, 1, 1);
 	cfg.dynamicSmemBytes = dyn;
 	cfg.stream = ctx->stream;
@@ -1293,7 +1358,8 @@ static int enqueue_track(dso_b200_ctx* ctx, int trk, int frame_slot, int nHyp, c
 	at[0].val.clusterDim.x = cs; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
 	cfg.attrs = at; cfg.numAttrs = 1;
 	CK(cudaLaunchKernelEx(&cfg, kern, TL, o, kin, (dso_b200_track_result*)T.d_track_out, coarsestLvl, cap, (long long*)ctx->d_phase_cycles,
-	                      seq ? (dso_b200_track_result*)T.h_track_out : (dso_b200_track_result*)nullptr, T.h_flags, seq));
+	                      seq ? (dso_b200_track_result*)T.h_track_out : (dso_b200_track_result*)nullptr, T.h_flags, seq,
+	                      nc, T.d_mc_part, T.d_mc_count));
 	ctx->launches++;
 	return 0;
 }
