@@ -122,64 +122,32 @@ __global__ void __launch_bounds__(256) pyr_gradient_kernel(GradArgs a)
 	const int n = L.w * L.h;
 	const int wl = L.w;
 	const int lo = wl, hi = wl * (L.h - 1);   // :188 gradient range
-	const int t = (blockIdx.x - L.block_start) * 256 + threadIdx.x;
 	const float* I = L.inten;
-	if (L.vec)
+	// 1024 consecutive pixels per CTA; thread t takes pixels t, t+256, t+512, t+768 of them, so every load and every
+	// 16-byte store instruction of a warp covers 32 consecutive pixels (128 B read, 512 B written, full sectors)
+	const int start = (blockIdx.x - L.block_start) * 1024 + threadIdx.x;
+	float c[4], lf[4], rt[4], u[4], d[4];
+	bool interior[4], valid[4];
+#pragma unroll
+	for (int k = 0; k < 4; k++)
 	{
-		const int base = t * 4;
-		if (base >= n) return;
-		float4 c = __ldg(reinterpret_cast<const float4*>(I + base));
-		float4 u = c, d = c;
-		float lf = 0.f, rt = 0.f;
-		// w % 4 == 0: the four pixels of a thread share a row, so "interior" is uniform over them
-		const bool interior = (base >= lo) && (base < hi);
-		if (interior)
-		{
-			u = __ldg(reinterpret_cast<const float4*>(I + base - wl));
-			d = __ldg(reinterpret_cast<const float4*>(I + base + wl));
-			lf = __ldg(I + base - 1);
-			rt = __ldg(I + base + 4);
-		}
-		float cc[4] = { c.x, c.y, c.z, c.w };
-		float uu[4] = { u.x, u.y, u.z, u.w };
-		float dd[4] = { d.x, d.y, d.z, d.w };
-		float ll[4] = { lf, c.x, c.y, c.z };
-		float rr[4] = { c.y, c.z, c.w, rt };
-		float dx[4], dy[4], ab[4];
-#pragma unroll
-		for (int k = 0; k < 4; k++)
-		{
-			grad_px(cc[k], ll[k], rr[k], uu[k], dd[k], a.Blut, interior, dx[k], dy[k], ab[k]);
-		}
-		float4* o = L.out + base;
-#pragma unroll
-		for (int k = 0; k < 4; k++) o[k] = make_float4(cc[k], dx[k], dy[k], ab[k]);
-		if (L.aos)
-		{
-			float4* s = reinterpret_cast<float4*>(L.aos + 3 * (size_t)base);
-			s[0] = make_float4(cc[0], dx[0], dy[0], cc[1]);
-			s[1] = make_float4(dx[1], dy[1], cc[2], dx[2]);
-			s[2] = make_float4(dy[2], cc[3], dx[3], dy[3]);
-		}
-		if (L.absg) *reinterpret_cast<float4*>(L.absg + base) = make_float4(ab[0], ab[1], ab[2], ab[3]);
+		const int idx = start + 256 * k;
+		valid[k] = idx < n;
+		interior[k] = valid[k] && idx >= lo && idx < hi;
+		c[k] = valid[k] ? __ldg(I + idx) : 0.f;
+		lf[k] = rt[k] = u[k] = d[k] = 0.f;
+		if (interior[k]) { lf[k] = __ldg(I + idx - 1); rt[k] = __ldg(I + idx + 1); u[k] = __ldg(I + idx - wl); d[k] = __ldg(I + idx + wl); }
 	}
-	else
+#pragma unroll
+	for (int k = 0; k < 4; k++)
 	{
-		// scalar path for widths that are not a multiple of 4 (1024 pixels per CTA, like the vector path)
-		const int per_block = 1024;
-		int start = (blockIdx.x - L.block_start) * per_block;
-		for (int idx = start + threadIdx.x; idx < start + per_block && idx < n; idx += 256)
-		{
-			float c = __ldg(I + idx);
-			bool interior = idx >= lo && idx < hi;
-			float lf = 0.f, rt = 0.f, u = 0.f, d = 0.f;
-			if (interior) { lf = __ldg(I + idx - 1); rt = __ldg(I + idx + 1); u = __ldg(I + idx - wl); d = __ldg(I + idx + wl); }
-			float dx, dy, ab;
-			grad_px(c, lf, rt, u, d, a.Blut, interior, dx, dy, ab);
-			L.out[idx] = make_float4(c, dx, dy, ab);
-			if (L.aos) { L.aos[3 * (size_t)idx] = c; L.aos[3 * (size_t)idx + 1] = dx; L.aos[3 * (size_t)idx + 2] = dy; }
-			if (L.absg) L.absg[idx] = ab;
-		}
+		if (!valid[k]) continue;
+		const int idx = start + 256 * k;
+		float dx, dy, ab;
+		grad_px(c[k], lf[k], rt[k], u[k], d[k], a.Blut, interior[k], dx, dy, ab);
+		L.out[idx] = make_float4(c[k], dx, dy, ab);
+		if (L.aos) { L.aos[3 * (size_t)idx] = c[k]; L.aos[3 * (size_t)idx + 1] = dx; L.aos[3 * (size_t)idx + 2] = dy; }
+		if (L.absg) L.absg[idx] = ab;
 	}
 }
 
