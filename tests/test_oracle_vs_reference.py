@@ -29,9 +29,16 @@ def test_make_images_bit_exact(w, h, levels):
             assert np.array_equal(bits(d0[l]), bits(d1[l])) and np.array_equal(bits(a0[l]), bits(a1[l]))
 
 
+@pytest.fixture(scope="module", params=["small", "vga"])
+def win(request):
+    """every pin runs on the small window (320x240, 4 key frames, 500 points) AND on the BASELINE window
+    (640x480, 7 key frames, 2002 points, 12012 residuals) the GPU parity tests and bench.py use"""
+    return request.getfixturevalue("window_" + request.param)
+
+
 @pytest.fixture(scope="module")
-def trackers(pkg, window_small):
-    W = window_small
+def trackers(pkg, win):
+    W = win
     syn = pkg.synthetic
     levels = syn.pyr_levels_for(W.w, W.h)
     ref_pyr = O.make_images(W.images[-1], levels)
@@ -100,8 +107,8 @@ def test_track_newest_coarse_agrees(trackers):
         assert to.track(ident, a0, b0, levels - 1, thr).ok == tr.track(ident, a0, b0, levels - 1, thr).ok == 0
 
 
-def test_ba_linearize_accumulate(pkg, window_small):
-    W = window_small
+def test_ba_linearize_accumulate(pkg, win):
+    W = win
     pyr = [O.make_images(img, 1)[0][0] for img in W.images]
     Bo, Br = O.BA(W, pyr), O.BA(W, pyr, kind="ref")
     go, gr = Bo.glue(), Br.glue()
@@ -135,7 +142,7 @@ def test_ba_linearize_accumulate(pkg, window_small):
 
 
 @pytest.mark.parametrize("modes", [(-1.0, -1.0), (1e12, -1.0), (-1.0, 1e8)])
-def test_fixed_affine_modes_agree(trackers, pkg, window_small, modes):
+def test_fixed_affine_modes_agree(trackers, pkg, win, modes):
     """setting_affineOptModeA/B < 0 (CoarseTracker.cpp:621-643, :743-744; Residuals.cpp:257-258)"""
     W, syn, levels, frames, to, tr, (a0, b0) = trackers
     ident = syn.pose12((np.eye(3), np.zeros(3)))
@@ -155,8 +162,8 @@ def test_fixed_affine_modes_agree(trackers, pkg, window_small, modes):
             assert ro.aff_a == rr.aff_a == 0
         if modes[1] < 0:
             assert ro.aff_b == rr.aff_b == 0
-        p0 = [O.make_images(im, 1)[0][0] for im in window_small.images]
-        lo, lr = O.BA(window_small, p0).linearize(), O.BA(window_small, p0, kind="ref").linearize()
+        p0 = [O.make_images(im, 1)[0][0] for im in win.images]
+        lo, lr = O.BA(win, p0).linearize(), O.BA(win, p0, kind="ref").linearize()
         ok = lo["newState"] != 1
         assert np.array_equal(bits(lo["J"][ok]), bits(lr["J"][ok]))
         J = lo["J"][lo["newState"] == 0]
@@ -192,10 +199,10 @@ def _solve_inputs(W, seed=0):
 
 
 @pytest.mark.parametrize("iteration,with_lin", [(0, False), (3, False), (3, True)])
-def test_solve_system_and_resubstitute(pkg, window_small, iteration, with_lin):
+def test_solve_system_and_resubstitute(pkg, win, iteration, with_lin):
     """EnergyFunctional::solveSystemF + resubstituteF_MT (EnergyFunctional.cpp:802-924, 276-330), default solver mode;
     with_lin also runs fixLinearizationF on a third of the residuals so that accumulateLF_MT (addPoint<1>) has work"""
-    W = window_small
+    W = win
     pyr = [O.make_images(img, 1)[0][0] for img in W.images]
     Bo, Br = O.BA(W, pyr), O.BA(W, pyr, kind="ref")
     inp = _solve_inputs(W)
@@ -223,10 +230,10 @@ def test_solve_system_and_resubstitute(pkg, window_small, iteration, with_lin):
     assert np.isfinite(so["step"]).all() and np.abs(so["step"]).max() > 0
 
 
-def test_marginalize_points_and_energies(pkg, window_small):
+def test_marginalize_points_and_energies(pkg, win):
     """rest of N2: calcLEnergyF_MT, calcMEnergyF and marginalizePointsF (EnergyFunctional.cpp:334-428, 642-703).  A third of
     the points are flagged; their residuals are linearised first (FullSystem::flagPointsForRemoval does the same)."""
-    W = window_small
+    W = win
     pyr = [O.make_images(img, 1)[0][0] for img in W.images]
     Bo, Br = O.BA(W, pyr), O.BA(W, pyr, kind="ref")
     inp = _solve_inputs(W)
@@ -253,10 +260,10 @@ def test_marginalize_points_and_energies(pkg, window_small):
     assert np.abs(mo["bM"] - mr["bM"]).max() <= 1e-12 * np.abs(mr["bM"]).max()
 
 
-def test_immature_point_init_and_trace_on_bit_exact(pkg, window_small):
+def test_immature_point_init_and_trace_on_bit_exact(pkg, win):
     """next row N3: ImmaturePoint's constructor and traceOn (FullSystem/ImmaturePoint.cpp:25-57, 77-438) over three
     successive frames (interval (0, NaN) first, then the refined intervals), every output bit for bit"""
-    W = window_small
+    W = win
     sc = pkg.synthetic.immature_scenario(W, host_idx=1, n_points=600, n_frames=3)
     hostI = O.make_images(sc["host_image"], 1)[0][0]
     fo, fr = O.immature_init(hostI, sc["u"], sc["v"]), O.immature_init(hostI, sc["u"], sc["v"], kind="ref")
@@ -274,15 +281,16 @@ def test_immature_point_init_and_trace_on_bit_exact(pkg, window_small):
         seen |= set(so["status"].tolist())
     assert {0, 1}.issubset(seen) and len(seen) >= 3, seen          # GOOD, OOB and at least one of SKIPPED / BADCONDITION / OUTLIER
     good = so["status"] == 0
-    assert good.sum() > 100
+    assert good.sum() > (100 if W.w == 320 else 10)      # the VGA scenario's longer baseline leaves mostly OOB / OUTLIER / SKIPPED exits
     mid = 0.5 * (so["idepth_min"][good] + so["idepth_max"][good])
-    assert np.median(np.abs(mid - sc["idepth_true"][good]) / sc["idepth_true"][good]) < 0.05     # the search finds the true depth
+    if W.w == 320:          # scenario sanity (not parity): on the small window the search finds the true depth
+        assert np.median(np.abs(mid - sc["idepth_true"][good]) / sc["idepth_true"][good]) < 0.05
 
 
-def test_optimize_immature_point_bit_exact(pkg, window_small):
+def test_optimize_immature_point_bit_exact(pkg, win):
     """next row N3: FullSystem::optimizeImmaturePoint + ImmaturePoint::linearizeResidual (FullSystemOptPoint.cpp:51-209,
     ImmaturePoint.cpp:499-570): result code, activated inverse depth and residual states, bit for bit"""
-    W = window_small
+    W = win
     sc = pkg.synthetic.activation_scenario(W, host_idx=1, n_points=600)
     fields = O.immature_init(O.make_images(sc["host_image"], 1)[0][0], sc["u"], sc["v"])
     dIs = [O.make_images(im, 1)[0][0] for im in sc["images"]]
