@@ -33,7 +33,7 @@ class TrackResult(C.Structure):
                 ("aff_b", C.c_double), ("lastResiduals", C.c_double * 5), ("lastFlowIndicators", C.c_double * 3),
                 ("n_passes", C.c_int), ("pass_level", C.c_int * MAX_PASSES), ("pass_rmse", C.c_double * MAX_PASSES),
                 ("n_iterations", C.c_int), ("n_evals", C.c_int), ("trace_len", C.c_int), ("trace", C.c_ubyte * 256),
-                ("point_evals", C.c_double)]
+                ("point_evals", C.c_double), ("trace_dE", C.c_float * 64), ("trace_E", C.c_float * 64)]
 
 
 class Precalc(C.Structure):
@@ -47,6 +47,7 @@ SIGNATURES = {
     "dso_b200_destroy": (None, [vp]),
     "dso_b200_last_error": (C.c_char_p, []),
     "dso_b200_stream": (vp, [vp]),
+    "dso_b200_stream_for": (vp, [vp, C.c_int]),
     "dso_b200_sync": (C.c_int, [vp]),
     "dso_b200_host_alloc": (vp, [C.c_size_t]),
     "dso_b200_host_free": (None, [vp]),
@@ -79,6 +80,8 @@ SIGNATURES = {
     "dso_b200_track_frame": (C.c_int, [vp, C.c_int, C.c_int, vp, C.c_int, C.c_int, C.c_int, C.c_int, f64p, C.c_double, C.c_double,
                                        C.c_float, C.c_int, C.POINTER(TrackOpts), C.POINTER(TrackResult)]),
     "dso_b200_track_phase_cycles": (C.c_int, [vp, C.c_int, vp]),
+    "dso_b200_track_set_tuning": (C.c_int, [vp, C.c_int, C.c_int, C.c_int]),
+    "dso_b200_track_last_shape": (C.c_int, [vp, i32p]),
     "dso_b200_track_replay_abort": (C.c_int, [C.POINTER(TrackResult), f64p, f64p]),
     "dso_b200_track_hostloop": (C.c_int, [vp, C.c_int, C.c_int, f64p, C.c_double, C.c_double, C.c_float, C.c_int, vp,
                                           C.POINTER(TrackOpts), C.POINTER(TrackResult)]),
@@ -178,6 +181,17 @@ class Context:
     @property
     def stream(self):
         return self.L.dso_b200_stream(self.h)
+
+    def stream_for(self, which):
+        """0 main (makeImages), 1 / 2 tracker slot 0 / 1, 3 mapping (BA, immature points), 4 upload"""
+        return self.L.dso_b200_stream_for(self.h, which)
+
+    def tracker_stream(self, trk=0):
+        return self.stream_for(1 + trk)
+
+    @property
+    def ba_stream(self):
+        return self.stream_for(3)
 
     def sync(self):
         self._check(self.L.dso_b200_sync(self.h))
@@ -352,6 +366,14 @@ class Context:
         out = np.zeros(14, dtype=np.int64)
         self._check(self.L.dso_b200_track_phase_cycles(self.h, int(enable), out.ctypes.data if read else None))
         return out
+
+    def track_set_tuning(self, threads=0, cluster=0, nclusters=0):
+        self._check(self.L.dso_b200_track_set_tuning(self.h, threads, cluster, nclusters))
+
+    def track_last_shape(self):
+        out = np.zeros(3, dtype=np.int32)
+        self._check(self.L.dso_b200_track_last_shape(self.h, out))
+        return tuple(int(x) for x in out)
 
     def replay_abort(self, res, min_res):
         lr = np.zeros(5)

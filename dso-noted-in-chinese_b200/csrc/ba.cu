@@ -975,7 +975,7 @@ extern "C" int dso_b200_ba_set_window(dso_b200_ctx* ctx, int nF, const int* fram
 		ARG_CHECK(frame_slots[i] >= 0 && frame_slots[i] < ctx->n_slots && ctx->slots[frame_slots[i]].valid, "frame slot empty");
 		ARG_CHECK(ctx->slots[frame_slots[i]].w == w && ctx->slots[frame_slots[i]].h == h, "frame size mismatch");
 		P.img[i] = ctx->slots[frame_slots[i]].pyr[0];
-		if (frame_slot_wait(ctx, frame_slots[i])) return DSO_B200_E_CUDA;
+		if (frame_slot_wait(ctx, frame_slots[i], ctx->ba_stream, DSO_B200_STREAM_MAPPING)) return DSO_B200_E_CUDA;
 		P.frameEnergyTH[i] = frameEnergyTH[i];
 	}
 	P.nF = nF; P.w = w; P.h = h;
@@ -1005,15 +1005,15 @@ extern "C" int dso_b200_ba_set_glue(dso_b200_ctx* ctx, const dso_b200_precalc* p
 	BA_CHECK(W->window_set, "call dso_b200_ba_set_window first");
 	CK(cudaSetDevice(ctx->device));
 	const int n2 = W->P.nF * W->P.nF;
-	CK(cudaMemcpyAsync(W->d_precalc, precalc, (size_t)n2 * sizeof(dso_b200_precalc), cudaMemcpyHostToDevice, ctx->stream));
-	CK(cudaMemcpyAsync(W->d_adHost, adHost, (size_t)n2 * 64 * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
-	CK(cudaMemcpyAsync(W->d_adTarget, adTarget, (size_t)n2 * 64 * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+	CK(cudaMemcpyAsync(W->d_precalc, precalc, (size_t)n2 * sizeof(dso_b200_precalc), cudaMemcpyHostToDevice, ctx->ba_stream));
+	CK(cudaMemcpyAsync(W->d_adHost, adHost, (size_t)n2 * 64 * sizeof(double), cudaMemcpyHostToDevice, ctx->ba_stream));
+	CK(cudaMemcpyAsync(W->d_adTarget, adTarget, (size_t)n2 * 64 * sizeof(double), cudaMemcpyHostToDevice, ctx->ba_stream));
 	// setDeltaF products, read by the linearised-residual mode (addPoint<1>, fixLinearizationF); NULL = zero deltas
-	if (adHTdeltaF) CK(cudaMemcpyAsync(W->d_adHTdeltaF, adHTdeltaF, (size_t)n2 * 8 * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
-	else CK(cudaMemsetAsync(W->d_adHTdeltaF, 0, (size_t)n2 * 8 * sizeof(float), ctx->stream));
+	if (adHTdeltaF) CK(cudaMemcpyAsync(W->d_adHTdeltaF, adHTdeltaF, (size_t)n2 * 8 * sizeof(float), cudaMemcpyHostToDevice, ctx->ba_stream));
+	else CK(cudaMemsetAsync(W->d_adHTdeltaF, 0, (size_t)n2 * 8 * sizeof(float), ctx->ba_stream));
 	if (cDeltaF4) memcpy(W->h_cDeltaF, cDeltaF4, 4 * sizeof(float));
-	CK(cudaMemcpyAsync(W->d_cDeltaF, W->h_cDeltaF, 4 * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
-	CK(cudaStreamSynchronize(ctx->stream));
+	CK(cudaMemcpyAsync(W->d_cDeltaF, W->h_cDeltaF, 4 * sizeof(float), cudaMemcpyHostToDevice, ctx->ba_stream));
+	CK(cudaStreamSynchronize(ctx->ba_stream));
 	W->glue_set = true;
 	return 0;
 }
@@ -1048,17 +1048,17 @@ extern "C" int dso_b200_ba_set_points(dso_b200_ctx* ctx, int nP, const float* u,
 		W->capP = nP;
 	}
 	// *_accLF start at zero: accumulateLF_MT overwrites them when there are linearised residuals
-	CK(cudaMemsetAsync(W->d_Hdd_L, 0, (size_t)nP * sizeof(float), ctx->stream));
-	CK(cudaMemsetAsync(W->d_bd_L, 0, (size_t)nP * sizeof(float), ctx->stream));
-	CK(cudaMemsetAsync(W->d_Hcd_L, 0, (size_t)nP * 4 * sizeof(float), ctx->stream));
+	CK(cudaMemsetAsync(W->d_Hdd_L, 0, (size_t)nP * sizeof(float), ctx->ba_stream));
+	CK(cudaMemsetAsync(W->d_bd_L, 0, (size_t)nP * sizeof(float), ctx->ba_stream));
+	CK(cudaMemsetAsync(W->d_Hcd_L, 0, (size_t)nP * 4 * sizeof(float), ctx->ba_stream));
 	std::vector<float4> pt(nP);
 	for (int i = 0; i < nP; i++) pt[i] = make_float4(u[i], v[i], idepth_scaled[i], idepth_zero_scaled[i]);
-	CK(cudaMemcpyAsync(W->d_pt, pt.data(), (size_t)nP * sizeof(float4), cudaMemcpyHostToDevice, ctx->stream));
-	CK(cudaMemcpyAsync(W->d_color, color8, (size_t)nP * 8 * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
-	CK(cudaMemcpyAsync(W->d_weights, weights8, (size_t)nP * 8 * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
-	CK(cudaMemcpyAsync(W->d_phost, host, (size_t)nP * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
-	CK(cudaMemcpyAsync(W->d_priorF, priorF, (size_t)nP * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
-	CK(cudaMemcpyAsync(W->d_deltaF, deltaF, (size_t)nP * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+	CK(cudaMemcpyAsync(W->d_pt, pt.data(), (size_t)nP * sizeof(float4), cudaMemcpyHostToDevice, ctx->ba_stream));
+	CK(cudaMemcpyAsync(W->d_color, color8, (size_t)nP * 8 * sizeof(float), cudaMemcpyHostToDevice, ctx->ba_stream));
+	CK(cudaMemcpyAsync(W->d_weights, weights8, (size_t)nP * 8 * sizeof(float), cudaMemcpyHostToDevice, ctx->ba_stream));
+	CK(cudaMemcpyAsync(W->d_phost, host, (size_t)nP * sizeof(int), cudaMemcpyHostToDevice, ctx->ba_stream));
+	CK(cudaMemcpyAsync(W->d_priorF, priorF, (size_t)nP * sizeof(float), cudaMemcpyHostToDevice, ctx->ba_stream));
+	CK(cudaMemcpyAsync(W->d_deltaF, deltaF, (size_t)nP * sizeof(float), cudaMemcpyHostToDevice, ctx->ba_stream));
 	// Schur chunks: CHUNK_P consecutive points of one host
 	std::vector<int> pcs, pcc, pch, hb(nF + 1, 0);
 	int i = 0;
@@ -1084,11 +1084,11 @@ extern "C" int dso_b200_ba_set_points(dso_b200_ctx* ctx, int nP, const float* u,
 		CK(cudaMalloc(&W->d_scPartials, (size_t)W->nPC * (MAXF * MAXF * 64 + MAXF * 40 + 24) * sizeof(float)));
 		W->capPC = W->nPC;
 	}
-	CK(cudaMemcpyAsync(W->d_pc_start, pcs.data(), pcs.size() * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
-	CK(cudaMemcpyAsync(W->d_pc_cnt, pcc.data(), pcc.size() * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
-	CK(cudaMemcpyAsync(W->d_pc_host, pch.data(), pch.size() * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
-	CK(cudaMemcpyAsync(W->d_host_pc_begin, hb.data(), (nF + 1) * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
-	CK(cudaStreamSynchronize(ctx->stream));
+	CK(cudaMemcpyAsync(W->d_pc_start, pcs.data(), pcs.size() * sizeof(int), cudaMemcpyHostToDevice, ctx->ba_stream));
+	CK(cudaMemcpyAsync(W->d_pc_cnt, pcc.data(), pcc.size() * sizeof(int), cudaMemcpyHostToDevice, ctx->ba_stream));
+	CK(cudaMemcpyAsync(W->d_pc_host, pch.data(), pch.size() * sizeof(int), cudaMemcpyHostToDevice, ctx->ba_stream));
+	CK(cudaMemcpyAsync(W->d_host_pc_begin, hb.data(), (nF + 1) * sizeof(int), cudaMemcpyHostToDevice, ctx->ba_stream));
+	CK(cudaStreamSynchronize(ctx->ba_stream));
 	W->h_phost.assign(host, host + nP);
 	W->P.nP = nP;
 	W->points_set = true; W->res_set = false; W->lin_done = false; W->top_done = false;
@@ -1171,7 +1171,7 @@ extern "C" int dso_b200_ba_set_residuals(dso_b200_ctx* ctx, int nR, const int* p
 		if (isLinearized) lin[k] = isLinearized[k];
 		if (isActive) act[k] = isActive[k];
 	}
-	cudaStream_t s = ctx->stream;
+	cudaStream_t s = ctx->ba_stream;
 	CK(cudaMemcpyAsync(W->d_rpoint, point, (size_t)nR * sizeof(int), cudaMemcpyHostToDevice, s));
 	CK(cudaMemcpyAsync(W->d_rtarget, target, (size_t)nR * sizeof(int), cudaMemcpyHostToDevice, s));
 	CK(cudaMemcpyAsync(W->d_state, state_state, (size_t)nR * sizeof(int), cudaMemcpyHostToDevice, s));
@@ -1204,11 +1204,6 @@ extern "C" int dso_b200_ba_set_residuals(dso_b200_ctx* ctx, int nR, const int* p
 
 
 // ---- host-side glue: FrameFramePrecalc::set + EnergyFunctional::setAdjointsF ------------------
-static void pose_inverse(const Pose& a, Pose& o)
-{
-	for (int r = 0; r < 3; r++) for (int c = 0; c < 3; c++) o.R[r * 3 + c] = a.R[c * 3 + r];
-	for (int r = 0; r < 3; r++) o.t[r] = -(o.R[r * 3] * a.t[0] + o.R[r * 3 + 1] * a.t[1] + o.R[r * 3 + 2] * a.t[2]);
-}
 // Eigen's compute_inverse<Matrix3f> (cofactors of column 0, determinant by expansion along it)
 static float cof33h(const float* m, int i, int j)
 {
@@ -1280,18 +1275,8 @@ extern "C" int dso_b200_ba_set_frames(dso_b200_ctx* ctx, const double* evalPT12,
 			double* AH = &adH[(size_t)(h + t * nF) * 64];
 			double* AT = &adT[(size_t)(h + t * nF) * 64];
 			for (int i = 0; i < 64; i++) { AH[i] = (i % 9 == 0) ? 1.0 : 0.0; AT[i] = (i % 9 == 0) ? 1.0 : 0.0; }
-			// Sophus Adj = [[R, hat(t) R], [0, R]]
 			double Ad[36];
-			const double* R = l0.R; const double* tt = l0.t;
-			const double Th[9] = { 0, -tt[2], tt[1], tt[2], 0, -tt[0], -tt[1], tt[0], 0 };
-			for (int i = 0; i < 36; i++) Ad[i] = 0;
-			for (int r = 0; r < 3; r++)
-				for (int c = 0; c < 3; c++)
-				{
-					Ad[r * 6 + c] = R[r * 3 + c];
-					Ad[(r + 3) * 6 + 3 + c] = R[r * 3 + c];
-					Ad[r * 6 + 3 + c] = Th[r * 3] * R[c] + Th[r * 3 + 1] * R[3 + c] + Th[r * 3 + 2] * R[6 + c];
-				}
+			pose_adjoint(l0, Ad);
 			for (int r = 0; r < 6; r++) for (int c = 0; c < 6; c++) AH[r * 8 + c] = -Ad[c * 6 + r];
 			double a0, b0;
 			aff_from_to(ab_exposure[h], ab_exposure[t], state_zero10[10 * h + 6] * SA, state_zero10[10 * h + 7] * SB,
@@ -1340,9 +1325,9 @@ extern "C" int dso_b200_ba_set_frames(dso_b200_ctx* ctx, const double* evalPT12,
 				dp[CPARS + 8 * f + i] = state10[10 * f + i];
 			}
 		CK(cudaSetDevice(ctx->device));
-		CK(cudaMemcpyAsync(W->d_delta, dl, (8 * nF + CPARS) * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
-		CK(cudaMemcpyAsync(W->d_priorD, dp, (8 * nF + CPARS) * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
-		CK(cudaStreamSynchronize(ctx->stream));
+		CK(cudaMemcpyAsync(W->d_delta, dl, (8 * nF + CPARS) * sizeof(double), cudaMemcpyHostToDevice, ctx->ba_stream));
+		CK(cudaMemcpyAsync(W->d_priorD, dp, (8 * nF + CPARS) * sizeof(double), cudaMemcpyHostToDevice, ctx->ba_stream));
+		CK(cudaStreamSynchronize(ctx->ba_stream));
 	}
 	return dso_b200_ba_set_glue(ctx, pre.data(), adH.data(), adT.data(), adHTd.data(), nullptr);
 }
@@ -1351,13 +1336,13 @@ int ba_enqueue_linearize(dso_b200_ctx* ctx)
 {
 	BAWorkspace* W = ctx->ba;
 	const int nR = W->P.nR;
-	ba_linearize_kernel<<<(nR + 31) / 32, 256, 0, ctx->stream>>>(W->P, W->d_precalc, W->d_pt, W->d_color, W->d_weights, W->d_phost, W->d_rpoint,
+	ba_linearize_kernel<<<(nR + 31) / 32, 256, 0, ctx->ba_stream>>>(W->P, W->d_precalc, W->d_pt, W->d_color, W->d_weights, W->d_phost, W->d_rpoint,
 	                                                           W->d_rtarget, W->d_state, W->d_energy, W->d_efsel, W->d_J[0], W->d_J[1],
 	                                                           W->d_newState, W->d_newEnergy, W->d_newEnergyWO, W->d_cpt, W->d_proj, W->d_resEnergy);
 	const int nb = (nR + 255) / 256;
-	ba_energy_blocks_kernel<<<nb, 256, 0, ctx->stream>>>(nR, W->d_resEnergy, W->d_energy_blocks);
-	ba_energy_final_kernel<<<1, 32, 0, ctx->stream>>>(nb, W->d_energy_blocks, W->d_scalars);
-	ctx->launches += 3;
+	ba_energy_blocks_kernel<<<nb, 256, 0, ctx->ba_stream>>>(nR, W->d_resEnergy, W->d_energy_blocks);
+	ba_energy_final_kernel<<<1, 32, 0, ctx->ba_stream>>>(nb, W->d_energy_blocks, W->d_scalars);
+	LAUNCHED(ctx, 3);
 	CK(cudaGetLastError());
 	W->lin_done = true;
 	return 0;
@@ -1367,9 +1352,9 @@ int ba_enqueue_apply(dso_b200_ctx* ctx)
 {
 	BAWorkspace* W = ctx->ba;
 	const int nR = W->P.nR;
-	ba_apply_res_kernel<<<(nR + 255) / 256, 256, 0, ctx->stream>>>(nR, W->d_state, W->d_newState, W->d_energy, W->d_newEnergy, W->d_isAct, W->d_efsel,
+	ba_apply_res_kernel<<<(nR + 255) / 256, 256, 0, ctx->ba_stream>>>(nR, W->d_state, W->d_newState, W->d_energy, W->d_newEnergy, W->d_isAct, W->d_efsel,
 	                                                             W->d_J[0], W->d_J[1], W->d_JpJdF);
-	ctx->launches++;
+	LAUNCHED(ctx, 1);
 	CK(cudaGetLastError());
 	W->top_done = false;
 	return 0;
@@ -1380,7 +1365,7 @@ int ba_enqueue_top(dso_b200_ctx* ctx, int mode, const unsigned char* d_pmask)
 {
 	BAWorkspace* W = ctx->ba;
 	const int nF = W->P.nF;
-	cudaStream_t st = ctx->stream;
+	cudaStream_t st = ctx->ba_stream;
 	BALinArgs LA;
 	LA.rpoint = W->d_rpoint; LA.rtarget = W->d_rtarget; LA.phost = W->d_phost; LA.deltaF = W->d_deltaF;
 	LA.adHTdeltaF = W->d_adHTdeltaF; LA.cDeltaF = W->d_cDeltaF; LA.resToZero = W->d_resToZero; LA.nF = nF; LA.pmask = d_pmask;
@@ -1400,7 +1385,7 @@ int ba_enqueue_top(dso_b200_ctx* ctx, int mode, const unsigned char* d_pmask)
 	ba_top_pair_kernel<<<nF * nF, 256, 0, st>>>(nF, W->d_topRed, W->d_adHost, W->d_adTarget, W->d_topContrib);
 	ba_top_gather_kernel<<<nF * nF + 1, 64, 0, st>>>(nF, W->nChunks, W->d_chunk_nres, W->d_topContrib, Hout, bout, W->d_scalars + (mode ? 2 : 0),
 	                                               mode == 1 ? W->d_priorH : nullptr, W->d_priorD, W->d_cDeltaF);
-	ctx->launches += 5;
+	LAUNCHED(ctx, 5);
 	CK(cudaGetLastError());
 	if (mode == 0) W->top_done = true;
 	return 0;
@@ -1411,16 +1396,16 @@ int ba_enqueue_schur(dso_b200_ctx* ctx, const unsigned char* d_pmask)
 	BAWorkspace* W = ctx->ba;
 	const int nF = W->P.nF, nP = W->P.nP;
 	float* HdiF = d_pmask ? W->d_HdiF_m : W->d_HdiF; float* bdSumF = d_pmask ? W->d_bdSumF_m : W->d_bdSumF;
-	ba_schur_prep_kernel<<<(nP + 127) / 128, 128, 0, ctx->stream>>>(nP, W->d_res_begin, W->d_isAct, W->d_Hdd, W->d_bd, W->d_Hcd,
+	ba_schur_prep_kernel<<<(nP + 127) / 128, 128, 0, ctx->ba_stream>>>(nP, W->d_res_begin, W->d_isAct, W->d_Hdd, W->d_bd, W->d_Hcd,
 	                                                              W->d_Hdd_L, W->d_bd_L, W->d_Hcd_L, W->d_priorF, W->d_deltaF,
 	                                                              HdiF, bdSumF, W->d_idh, W->d_HcdSum, d_pmask);
-	ba_schur_accum_kernel<<<W->nPC, 256, 0, ctx->stream>>>(nF, W->d_pc_start, W->d_pc_cnt, W->d_res_begin, W->d_rtarget, W->d_isAct, W->d_JpJdF,
+	ba_schur_accum_kernel<<<W->nPC, 256, 0, ctx->ba_stream>>>(nF, W->d_pc_start, W->d_pc_cnt, W->d_res_begin, W->d_rtarget, W->d_isAct, W->d_JpJdF,
 	                                                     HdiF, bdSumF, W->d_HcdSum, W->d_scPartials, W->scN);
 	const int nRed = nF * nF * 64 + nF * 32 + nF * 8 + 20;          // accD, accE, accEB, accHcc + accbc per host
-	ba_reduce_partials_kernel<<<dim3((nRed + 255) / 256, nF), 256, 0, ctx->stream>>>(W->d_scPartials, W->scN, nRed, W->d_host_pc_begin, W->d_scRed);
-	ba_schur_stage1_kernel<<<nF * nF, 64, 0, ctx->stream>>>(nF, W->d_scRed, nRed, W->d_adHost, W->d_adTarget, W->d_scContrib);
-	ba_schur_gather_kernel<<<nF * nF + 1, 64, 0, ctx->stream>>>(nF, W->d_scRed, W->d_scContrib, W->d_HS, W->d_bS);
-	ctx->launches += 5;
+	ba_reduce_partials_kernel<<<dim3((nRed + 255) / 256, nF), 256, 0, ctx->ba_stream>>>(W->d_scPartials, W->scN, nRed, W->d_host_pc_begin, W->d_scRed);
+	ba_schur_stage1_kernel<<<nF * nF, 64, 0, ctx->ba_stream>>>(nF, W->d_scRed, nRed, W->d_adHost, W->d_adTarget, W->d_scContrib);
+	ba_schur_gather_kernel<<<nF * nF + 1, 64, 0, ctx->ba_stream>>>(nF, W->d_scRed, W->d_scContrib, W->d_HS, W->d_bS);
+	LAUNCHED(ctx, 5);
 	CK(cudaGetLastError());
 	return 0;
 }
@@ -1447,7 +1432,7 @@ extern "C" int dso_b200_ba_linearize(dso_b200_ctx* ctx, int* newState, float* ne
 	const size_t nR = W->P.nR;
 	rc = ba_enqueue_linearize(ctx);
 	if (rc) return rc;
-	cudaStream_t s = ctx->stream;
+	cudaStream_t s = ctx->ba_stream;
 	if (newState) CK(cudaMemcpyAsync(newState, W->d_newState, nR * sizeof(int), cudaMemcpyDeviceToHost, s));
 	if (newEnergy) CK(cudaMemcpyAsync(newEnergy, W->d_newEnergy, nR * sizeof(float), cudaMemcpyDeviceToHost, s));
 	if (newEnergyWithOutlier) CK(cudaMemcpyAsync(newEnergyWithOutlier, W->d_newEnergyWO, nR * sizeof(float), cudaMemcpyDeviceToHost, s));
@@ -1478,9 +1463,9 @@ extern "C" int dso_b200_ba_apply_res(dso_b200_ctx* ctx, unsigned char* isActive_
 	rc = ba_enqueue_apply(ctx);
 	if (rc) return rc;
 	const size_t nR = W->P.nR;
-	if (isActive_out) CK(cudaMemcpyAsync(isActive_out, W->d_isAct, nR, cudaMemcpyDeviceToHost, ctx->stream));
-	if (JpJdF8_out) CK(cudaMemcpyAsync(JpJdF8_out, W->d_JpJdF, nR * 8 * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
-	CK(cudaStreamSynchronize(ctx->stream));
+	if (isActive_out) CK(cudaMemcpyAsync(isActive_out, W->d_isAct, nR, cudaMemcpyDeviceToHost, ctx->ba_stream));
+	if (JpJdF8_out) CK(cudaMemcpyAsync(JpJdF8_out, W->d_JpJdF, nR * 8 * sizeof(float), cudaMemcpyDeviceToHost, ctx->ba_stream));
+	CK(cudaStreamSynchronize(ctx->ba_stream));
 	W->lin_done = false;
 	return 0;
 }
@@ -1497,7 +1482,7 @@ extern "C" int dso_b200_ba_accumulate_A(dso_b200_ctx* ctx, double* H, double* b,
 	if (rc) return rc;
 	const int N = 8 * W->P.nF + CPARS;
 	const size_t nP = W->P.nP;
-	cudaStream_t s = ctx->stream;
+	cudaStream_t s = ctx->ba_stream;
 	CK(cudaMemcpyAsync(W->h_out, W->d_HA, (size_t)N * N * sizeof(double), cudaMemcpyDeviceToHost, s));
 	CK(cudaMemcpyAsync(W->h_out + N * N, W->d_bA, N * sizeof(double), cudaMemcpyDeviceToHost, s));
 	CK(cudaMemcpyAsync(W->h_out + N * N + N, W->d_scalars, 2 * sizeof(double), cudaMemcpyDeviceToHost, s));
@@ -1524,7 +1509,7 @@ extern "C" int dso_b200_ba_accumulate_SC(dso_b200_ctx* ctx, double* H_sc, double
 	if (rc) return rc;
 	const int N = 8 * W->P.nF + CPARS;
 	const size_t nP = W->P.nP;
-	cudaStream_t s = ctx->stream;
+	cudaStream_t s = ctx->ba_stream;
 	CK(cudaMemcpyAsync(W->h_out, W->d_HS, (size_t)N * N * sizeof(double), cudaMemcpyDeviceToHost, s));
 	CK(cudaMemcpyAsync(W->h_out + N * N, W->d_bS, N * sizeof(double), cudaMemcpyDeviceToHost, s));
 	if (HdiF) CK(cudaMemcpyAsync(HdiF, W->d_HdiF, nP * sizeof(float), cudaMemcpyDeviceToHost, s));
@@ -1546,8 +1531,8 @@ extern "C" int dso_b200_ba_step(dso_b200_ctx* ctx, double* H_A, double* b_A, dou
 	BAWorkspace* W = ctx->ba;
 	const int N = 8 * W->P.nF + CPARS;
 	const size_t NN = (size_t)N * N;
-	cudaStream_t s = ctx->stream;
-	rc = ba_run_graphed(ctx, W->g_step, 0ull, [&]() -> int {
+	cudaStream_t s = ctx->ba_stream;
+	rc = ba_run_graphed(ctx, W->g_step, BAGraphKey{ 0.0, 0.f, 0, 0, 0, 0 }, [&]() -> int {
 		int r;
 		if ((r = ba_enqueue_linearize(ctx))) return r;
 		if ((r = ba_enqueue_apply(ctx))) return r;

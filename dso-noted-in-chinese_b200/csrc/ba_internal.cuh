@@ -57,9 +57,18 @@ struct BASolve;    // ba_solve.cu
 // A fixed launch sequence captured once as a CUDA graph and replayed (dso_b200_ba_step, dso_b200_ba_iteration): the
 // kernels are 3-15 us each, so launch gaps would otherwise be ~40 % of the step.  Invalidated by every call that
 // changes a kernel argument (window, points, residuals, affine modes); `key` carries the by-value scalars.
+struct BAGraphKey       // every by-value argument baked into the captured launches, compared field by field
+{
+	double lambda; float stepfacD; int solverMode, nLin, haveP, dbg;
+	bool operator==(const BAGraphKey& o) const
+	{
+		return memcmp(&lambda, &o.lambda, sizeof(double)) == 0 && memcmp(&stepfacD, &o.stepfacD, sizeof(float)) == 0 &&
+		       solverMode == o.solverMode && nLin == o.nLin && haveP == o.haveP && dbg == o.dbg;
+	}
+};
 struct BAGraph
 {
-	cudaGraphExec_t exec; bool valid; unsigned long long key; long long nlaunch;
+	cudaGraphExec_t exec; bool valid; BAGraphKey key; long long nlaunch;
 };
 
 struct BAWorkspace
@@ -103,31 +112,33 @@ struct BAWorkspace
 
 void ba_graphs_invalidate(BAWorkspace* W);
 
-// Runs `enqueue` (kernel launches and async copies on ctx->stream only) through graph slot g.
+// Runs `enqueue` (kernel launches and async copies on ctx->ba_stream only) through graph slot g.
 template <class F>
-static int ba_run_graphed(dso_b200_ctx* ctx, BAGraph& g, unsigned long long key, F enqueue)
+static int ba_run_graphed(dso_b200_ctx* ctx, BAGraph& g, const BAGraphKey& key, F enqueue)
 {
 	BAWorkspace* W = ctx->ba;
 	if (!W->use_graphs) return enqueue();
-	if (!g.valid || g.key != key)
+	if (!g.valid || !(g.key == key))
 	{
 		if (g.exec) { cudaGraphExecDestroy(g.exec); g.exec = nullptr; }
 		g.valid = false;
-		const long long l0 = ctx->launches;
-		CK(cudaStreamBeginCapture(ctx->stream, cudaStreamCaptureModeThreadLocal));
+		// launches issued while capturing are counted per thread (another host thread may be launching tracker work)
+		t_capture_launches = 0; t_capturing = true;
+		cudaError_t eb = cudaStreamBeginCapture(ctx->ba_stream, cudaStreamCaptureModeThreadLocal);
+		if (eb != cudaSuccess) { t_capturing = false; CK(eb); }
 		const int rc = enqueue();
 		cudaGraph_t graph = nullptr;
-		const cudaError_t e = cudaStreamEndCapture(ctx->stream, &graph);
-		g.nlaunch = ctx->launches - l0;
-		ctx->launches = l0;
+		const cudaError_t e = cudaStreamEndCapture(ctx->ba_stream, &graph);
+		t_capturing = false;
+		g.nlaunch = t_capture_launches;
 		if (rc) { if (graph) cudaGraphDestroy(graph); return rc; }
 		CK(e);
 		CK(cudaGraphInstantiate(&g.exec, graph, 0));
 		CK(cudaGraphDestroy(graph));
 		g.valid = true; g.key = key;
 	}
-	CK(cudaGraphLaunch(g.exec, ctx->stream));
-	ctx->launches += g.nlaunch;
+	CK(cudaGraphLaunch(g.exec, ctx->ba_stream));
+	LAUNCHED(ctx, g.nlaunch);
 	return 0;
 }
 

@@ -563,8 +563,8 @@ extern "C" int dso_b200_ba_set_calib_delta(dso_b200_ctx* ctx, const double* valu
 	BAWorkspace* W = ctx->ba;
 	CK(cudaSetDevice(ctx->device));
 	for (int i = 0; i < 4; i++) W->h_cDeltaF[i] = (float)value_minus_value_zero4[i];   // cDeltaF = value_minus_value_zero.cast<float>() (:193)
-	CK(cudaMemcpyAsync(W->d_cDeltaF, W->h_cDeltaF, 4 * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
-	CK(cudaStreamSynchronize(ctx->stream));
+	CK(cudaMemcpyAsync(W->d_cDeltaF, W->h_cDeltaF, 4 * sizeof(float), cudaMemcpyHostToDevice, ctx->ba_stream));
+	CK(cudaStreamSynchronize(ctx->ba_stream));
 	return 0;
 }
 
@@ -583,7 +583,7 @@ extern "C" int dso_b200_ba_set_priors(dso_b200_ctx* ctx, const double* cPrior4, 
 	for (int i = 0; i < N; i++) ph[i] = 0.0;
 	if (cPrior4) for (int i = 0; i < 4; i++) ph[i] = cPrior4[i];
 	if (framePrior) for (int i = 0; i < 8 * nF; i++) ph[CPARS + i] = framePrior[i];
-	cudaStream_t s = ctx->stream;
+	cudaStream_t s = ctx->ba_stream;
 	CK(cudaMemcpyAsync(W->d_priorH, ph, N * sizeof(double), cudaMemcpyHostToDevice, s));
 	// delta_prior / delta are also derived by dso_b200_ba_set_frames from the frame states; explicit arrays override them
 	if (frameDeltaPrior) CK(cudaMemcpyAsync(W->d_priorD + CPARS, frameDeltaPrior, 8 * nF * sizeof(double), cudaMemcpyHostToDevice, s));
@@ -673,8 +673,8 @@ extern "C" int dso_b200_ba_set_nullspaces(dso_b200_ctx* ctx, const double* ns, i
 			P[(size_t)i * N + j] = s;
 		}
 	for (int i = 0; i < N; i++) for (int j = 0; j < N; j++) PS[(size_t)i * N + j] = 0.5 * (P[(size_t)i * N + j] + P[(size_t)j * N + i]);
-	CK(cudaMemcpyAsync(S->d_P, PS.data(), (size_t)N * N * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
-	CK(cudaStreamSynchronize(ctx->stream));
+	CK(cudaMemcpyAsync(S->d_P, PS.data(), (size_t)N * N * sizeof(double), cudaMemcpyHostToDevice, ctx->ba_stream));
+	CK(cudaStreamSynchronize(ctx->ba_stream));
 	S->haveP = true;
 	return 0;
 }
@@ -688,7 +688,7 @@ extern "C" int dso_b200_ba_fix_linearization(dso_b200_ctx* ctx, const unsigned c
 	BASolve* S;
 	if ((rc = solve_state(ctx, &S))) return rc;
 	const int nR = W->P.nR;
-	cudaStream_t s = ctx->stream;
+	cudaStream_t s = ctx->ba_stream;
 	if (which)
 	{
 		if (nR > S->capR)
@@ -701,7 +701,7 @@ extern "C" int dso_b200_ba_fix_linearization(dso_b200_ctx* ctx, const unsigned c
 	}
 	ba_fix_lin_kernel<<<(nR + 255) / 256, 256, 0, s>>>(nR, W->P.nF, which ? S->d_which : nullptr, W->d_isAct, W->d_isLin, W->d_efsel, W->d_J[0], W->d_J[1],
 	                                                 W->d_rpoint, W->d_rtarget, W->d_phost, W->d_deltaF, W->d_adHTdeltaF, W->d_cDeltaF, W->d_resToZero);
-	ctx->launches++;
+	LAUNCHED(ctx, 1);
 	CK(cudaGetLastError());
 	if (res_toZeroF_out) CK(cudaMemcpyAsync(res_toZeroF_out, W->d_resToZero, (size_t)nR * 8 * sizeof(float), cudaMemcpyDeviceToHost, s));
 	CK(cudaStreamSynchronize(s));
@@ -722,7 +722,7 @@ extern "C" int dso_b200_ba_accumulate_L(dso_b200_ctx* ctx, double* H, double* b,
 	if ((rc = ba_enqueue_top(ctx, 1))) return rc;
 	const int N = 8 * W->P.nF + CPARS;
 	const size_t nP = W->P.nP;
-	cudaStream_t s = ctx->stream;
+	cudaStream_t s = ctx->ba_stream;
 	CK(cudaMemcpyAsync(W->h_out, W->d_HL, (size_t)N * N * sizeof(double), cudaMemcpyDeviceToHost, s));
 	CK(cudaMemcpyAsync(W->h_out + N * N, W->d_bL, N * sizeof(double), cudaMemcpyDeviceToHost, s));
 	CK(cudaMemcpyAsync(W->h_out + N * N + N, W->d_scalars + 2, 2 * sizeof(double), cudaMemcpyDeviceToHost, s));
@@ -757,11 +757,11 @@ static int enqueue_solve(dso_b200_ctx* ctx, BASolve* S, int iteration, double la
 	a.P = S->d_P; a.adHost = W->d_adHost; a.adTarget = W->d_adTarget;
 	a.x = S->d_x; a.xAd = S->d_xAd; a.HF = debug ? S->d_HF : nullptr; a.bF = debug ? S->d_bF : nullptr;
 	a.dbg = S->d_dbg;
-	if (S->d_dbg) CK(cudaMemsetAsync(S->d_dbg, 0, 16 * sizeof(long long), ctx->stream));
-	ba_solve_kernel<<<1, SOLVE_NT, 0, ctx->stream>>>(a);
-	ba_resubstitute_kernel<<<(W->P.nP + 127) / 128, 128, 0, ctx->stream>>>(W->P.nP, W->P.nF, W->d_res_begin, W->d_rtarget, W->d_phost, W->d_isAct,
+	if (S->d_dbg) CK(cudaMemsetAsync(S->d_dbg, 0, 16 * sizeof(long long), ctx->ba_stream));
+	ba_solve_kernel<<<1, SOLVE_NT, 0, ctx->ba_stream>>>(a);
+	ba_resubstitute_kernel<<<(W->P.nP + 127) / 128, 128, 0, ctx->ba_stream>>>(W->P.nP, W->P.nF, W->d_res_begin, W->d_rtarget, W->d_phost, W->d_isAct,
 	                                                                    W->d_JpJdF, W->d_HcdSum, W->d_bdSumF, W->d_HdiF, S->d_x, S->d_xAd, S->d_step);
-	ctx->launches += 2;
+	LAUNCHED(ctx, 2);
 	CK(cudaGetLastError());
 	return 0;
 }
@@ -780,7 +780,7 @@ extern "C" int dso_b200_ba_solve(dso_b200_ctx* ctx, int iteration, double lambda
 	const bool debug = HFinal_out || bFinal_out;
 	if ((rc = enqueue_solve(ctx, S, iteration, lambda, solverMode, debug))) return rc;
 	const int N = 8 * W->P.nF + CPARS;
-	cudaStream_t s = ctx->stream;
+	cudaStream_t s = ctx->ba_stream;
 	CK(cudaMemcpyAsync(S->h_x, S->d_x, N * sizeof(double), cudaMemcpyDeviceToHost, s));
 	if (pointStep_out) CK(cudaMemcpyAsync(pointStep_out, S->d_step, (size_t)W->P.nP * sizeof(float), cudaMemcpyDeviceToHost, s));
 	if (HFinal_out) CK(cudaMemcpyAsync(HFinal_out, S->d_HF, (size_t)N * N * sizeof(double), cudaMemcpyDeviceToHost, s));
@@ -810,15 +810,11 @@ extern "C" int dso_b200_ba_iteration(dso_b200_ctx* ctx, int iteration, double la
 	BASolve* S;
 	if ((rc = solve_state(ctx, &S))) return rc;
 	if ((rc = ensure_point_buffers(ctx, S))) return rc;
-	cudaStream_t s = ctx->stream;
+	cudaStream_t s = ctx->ba_stream;
 	const int nP = W->P.nP, nb = (nP + 255) / 256, N = 8 * W->P.nF + CPARS;
 	// by-value kernel arguments of the captured sequence: orthogonalisation on/off, lambda, stepfacD, solver mode, L path
 	const int orth = ((solverMode & SOLVER_ORTHOGONALIZE_X) || (iteration >= 2 && (solverMode & SOLVER_ORTHOGONALIZE_X_LATER))) ? 1 : 0;
-	float lf = (float)lambda;
-	unsigned int lbits, sbits;
-	memcpy(&lbits, &lf, 4); memcpy(&sbits, &stepfacD, 4);
-	const unsigned long long key = ((unsigned long long)lbits << 32) ^ ((unsigned long long)sbits << 1) ^ ((unsigned long long)(solverMode & 0xfff) << 20)
-	                               ^ (unsigned long long)(W->nLin != 0) ^ ((unsigned long long)(S->haveP ? 1 : 0) << 19) ^ ((unsigned long long)(S->d_dbg ? 1 : 0) << 18);
+	const BAGraphKey key = { lambda, stepfacD, solverMode, W->nLin != 0 ? 1 : 0, S->haveP ? 1 : 0, S->d_dbg ? 1 : 0 };
 	rc = ba_run_graphed(ctx, W->g_iter[orth], key, [&]() -> int {
 		int r;
 		if ((r = ba_enqueue_linearize(ctx))) return r;
@@ -827,7 +823,7 @@ extern "C" int dso_b200_ba_iteration(dso_b200_ctx* ctx, int iteration, double la
 		ba_points_backup_kernel<<<(nP + 255) / 256, 256, 0, s>>>(nP, W->d_pt, S->d_idepth_backup, 0, nullptr, nullptr);
 		ba_points_step_kernel<<<nb, 256, 0, s>>>(nP, stepfacD, S->d_step, S->d_idepth_backup, W->d_pt, W->d_deltaF, S->d_stepBlocks);
 		ba_points_step_final_kernel<<<1, 32, 0, s>>>(nb, S->d_stepBlocks, W->d_scalars + 4);
-		ctx->launches += 3;
+		LAUNCHED(ctx, 3);
 		CK(cudaGetLastError());
 		CK(cudaMemcpyAsync(S->h_x, S->d_x, N * sizeof(double), cudaMemcpyDeviceToHost, s));
 		CK(cudaMemcpyAsync(S->h_x + NMAX, W->d_scalars, 6 * sizeof(double), cudaMemcpyDeviceToHost, s));
@@ -852,8 +848,8 @@ extern "C" int dso_b200_ba_points_backup(dso_b200_ctx* ctx)
 	BASolve* S;
 	if ((rc = solve_state(ctx, &S))) return rc;
 	if ((rc = ensure_point_buffers(ctx, S))) return rc;
-	ba_points_backup_kernel<<<(W->P.nP + 255) / 256, 256, 0, ctx->stream>>>(W->P.nP, W->d_pt, S->d_idepth_backup, 0, nullptr, nullptr);
-	ctx->launches++;
+	ba_points_backup_kernel<<<(W->P.nP + 255) / 256, 256, 0, ctx->ba_stream>>>(W->P.nP, W->d_pt, S->d_idepth_backup, 0, nullptr, nullptr);
+	LAUNCHED(ctx, 1);
 	CK(cudaGetLastError());
 	return 0;
 }
@@ -867,11 +863,11 @@ extern "C" int dso_b200_ba_points_step(dso_b200_ctx* ctx, float stepfacD, float*
 	BASolve* S;
 	if ((rc = solve_state(ctx, &S))) return rc;
 	BA_CHECK(S->capP >= W->P.nP, "call dso_b200_ba_points_backup and dso_b200_ba_solve first");
-	cudaStream_t s = ctx->stream;
+	cudaStream_t s = ctx->ba_stream;
 	const int nP = W->P.nP, nb = (nP + 255) / 256;
 	ba_points_step_kernel<<<nb, 256, 0, s>>>(nP, stepfacD, S->d_step, S->d_idepth_backup, W->d_pt, W->d_deltaF, S->d_stepBlocks);
 	ba_points_step_final_kernel<<<1, 32, 0, s>>>(nb, S->d_stepBlocks, W->d_scalars + 4);
-	ctx->launches += 2;
+	LAUNCHED(ctx, 2);
 	CK(cudaGetLastError());
 	CK(cudaMemcpyAsync(S->h_x + NMAX, W->d_scalars + 4, 2 * sizeof(double), cudaMemcpyDeviceToHost, s));
 	if (idepth_out)
@@ -894,8 +890,8 @@ extern "C" int dso_b200_ba_points_restore(dso_b200_ctx* ctx)
 	BASolve* S;
 	if ((rc = solve_state(ctx, &S))) return rc;
 	BA_CHECK(S->capP >= W->P.nP, "call dso_b200_ba_points_backup first");
-	ba_points_backup_kernel<<<(W->P.nP + 255) / 256, 256, 0, ctx->stream>>>(W->P.nP, W->d_pt, S->d_idepth_backup, 1, W->d_pt, W->d_deltaF);
-	ctx->launches++;
+	ba_points_backup_kernel<<<(W->P.nP + 255) / 256, 256, 0, ctx->ba_stream>>>(W->P.nP, W->d_pt, S->d_idepth_backup, 1, W->d_pt, W->d_deltaF);
+	LAUNCHED(ctx, 1);
 	CK(cudaGetLastError());
 	W->lin_done = false; W->top_done = false;
 	return 0;
@@ -1043,15 +1039,15 @@ extern "C" int dso_b200_ba_marginalize_points(dso_b200_ctx* ctx, const unsigned 
 	if ((rc = solve_state(ctx, &S))) return rc;
 	if ((rc = marg_buffers(ctx, S))) return rc;
 	const int nP = W->P.nP, N = 8 * W->P.nF + CPARS;
-	cudaStream_t s = ctx->stream;
+	cudaStream_t s = ctx->ba_stream;
 	CK(cudaMemcpyAsync(S->d_pmask, point_flags, (size_t)nP, cudaMemcpyHostToDevice, s));
 	ba_marg_prior_kernel<<<(nP + 255) / 256, 256, 0, s>>>(nP, S->d_pmask, idepthFixPriorMargFac, W->d_priorF);
-	ctx->launches++;
+	LAUNCHED(ctx, 1);
 	if ((rc = ba_enqueue_top(ctx, 2, S->d_pmask))) return rc;      // accSSE_top_A->addPoint<2> + stitchDouble -> d_HL, d_bL
 	if ((rc = ba_enqueue_schur(ctx, S->d_pmask))) return rc;       // accSSE_bot->addPoint(p, false) + stitchDouble -> d_HS, d_bS
 	double* dH = S->d_margH; double* db = S->d_margH + (size_t)NMAX * NMAX;
 	ba_marg_combine_kernel<<<(N * N + 255) / 256, 256, 0, s>>>(N, margWeightFac, W->d_HL, W->d_bL, W->d_HS, W->d_bS, dH, db, S->d_HM, S->d_bM);
-	ctx->launches++;
+	LAUNCHED(ctx, 1);
 	CK(cudaGetLastError());
 	if (H_out) CK(cudaMemcpyAsync(H_out, dH, (size_t)N * N * sizeof(double), cudaMemcpyDeviceToHost, s));
 	if (b_out) CK(cudaMemcpyAsync(b_out, db, N * sizeof(double), cudaMemcpyDeviceToHost, s));
@@ -1074,9 +1070,9 @@ extern "C" int dso_b200_ba_get_marg_prior(dso_b200_ctx* ctx, double* HM_out, dou
 	int rc = solve_state(ctx, &S);
 	if (rc) return rc;
 	const int N = 8 * W->P.nF + CPARS;
-	CK(cudaMemcpyAsync(HM_out, S->d_HM, (size_t)N * N * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
-	CK(cudaMemcpyAsync(bM_out, S->d_bM, N * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
-	CK(cudaStreamSynchronize(ctx->stream));
+	CK(cudaMemcpyAsync(HM_out, S->d_HM, (size_t)N * N * sizeof(double), cudaMemcpyDeviceToHost, ctx->ba_stream));
+	CK(cudaMemcpyAsync(bM_out, S->d_bM, N * sizeof(double), cudaMemcpyDeviceToHost, ctx->ba_stream));
+	CK(cudaStreamSynchronize(ctx->ba_stream));
 	return 0;
 }
 
@@ -1090,11 +1086,11 @@ extern "C" int dso_b200_ba_calc_energies(dso_b200_ctx* ctx, double* L_energy, do
 	if ((rc = solve_state(ctx, &S))) return rc;
 	if ((rc = marg_buffers(ctx, S))) return rc;
 	const int nP = W->P.nP, nb = (nP + 255) / 256;
-	cudaStream_t s = ctx->stream;
+	cudaStream_t s = ctx->ba_stream;
 	ba_lenergy_kernel<<<nb, 256, 0, s>>>(nP, W->P.nF, W->d_res_begin, W->d_rtarget, W->d_phost, W->d_isAct, W->d_isLin, W->d_efsel, W->d_J[0], W->d_J[1],
 	                                     W->d_resToZero, W->d_adHTdeltaF, W->d_cDeltaF, W->d_deltaF, W->d_priorF, S->d_eblocks);
 	ba_energy_final_kernel2<<<1, 128, 0, s>>>(W->P.nF, nb, S->d_eblocks, W->d_priorH, W->d_priorD, W->d_delta, W->d_cDeltaF, S->d_HM, S->d_bM, W->d_scalars + 6);
-	ctx->launches += 2;
+	LAUNCHED(ctx, 2);
 	CK(cudaGetLastError());
 	CK(cudaMemcpyAsync(S->h_x + NMAX, W->d_scalars + 6, 2 * sizeof(double), cudaMemcpyDeviceToHost, s));
 	CK(cudaStreamSynchronize(s));

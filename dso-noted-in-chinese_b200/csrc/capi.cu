@@ -3,6 +3,8 @@
 #include <cstdarg>
 
 static thread_local char g_err[512] = "";
+thread_local bool t_capturing = false;
+thread_local long long t_capture_launches = 0;
 
 void dso_set_error(const char* fmt, ...)
 {
@@ -21,6 +23,8 @@ static size_t pyr_pixels(int w, int h, int levels)
 	return s;
 }
 static size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+static int create_impl(dso_b200_ctx* ctx, int device, int max_w, int max_h, int n_frame_slots);
 
 extern "C" int dso_b200_create(int device, int max_w, int max_h, int n_frame_slots, dso_b200_ctx** out)
 {
@@ -46,15 +50,32 @@ extern "C" int dso_b200_create(int device, int max_w, int max_h, int n_frame_slo
 	ctx->device = device;
 	ctx->sm_count = prop.multiProcessorCount;
 	ctx->max_w = max_w; ctx->max_h = max_h; ctx->n_slots = n_frame_slots;
+	int rc = create_impl(ctx, device, max_w, max_h, n_frame_slots);
+	if (rc)
+	{
+		// a half-built context is torn down again (dso_b200_destroy copes with missing pieces); the error text survives
+		char keep[512];
+		strncpy(keep, g_err, sizeof(keep)); keep[sizeof(keep) - 1] = 0;
+		dso_b200_destroy(ctx);
+		dso_set_error("%s", keep);
+		return rc;
+	}
+	*out = ctx;
+	return 0;
+}
+
+static int create_impl(dso_b200_ctx* ctx, int device, int max_w, int max_h, int n_frame_slots)
+{
 	CK(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
 	CK(cudaStreamCreateWithFlags(&ctx->upload_stream, cudaStreamNonBlocking));
+	CK(cudaStreamCreateWithFlags(&ctx->ba_stream, cudaStreamNonBlocking));
 
 	// frame slots: per level a float4 image and (for l >= 1) a float intensity plane
 	ctx->slots = new FrameSlot[n_frame_slots];
+	memset(ctx->slots, 0, sizeof(FrameSlot) * n_frame_slots);
 	for (int s = 0; s < n_frame_slots; s++)
 	{
 		FrameSlot& F = ctx->slots[s];
-		memset(&F, 0, sizeof(F));
 		size_t bytes = 0;
 		for (int l = 0; l < MAXL; l++)
 		{
@@ -89,6 +110,8 @@ extern "C" int dso_b200_create(int device, int max_w, int max_h, int n_frame_slo
 	{
 		TrackerSlot& T = ctx->trk[t];
 		T.cap_points = npx0;
+		T.consumer = DSO_B200_STREAM_TRACKER0 + t;
+		CK(cudaStreamCreateWithFlags(&T.stream, cudaStreamNonBlocking));
 		size_t bytes = 0;
 		for (int l = 0; l < MAXL; l++) bytes += align_up((size_t)(max_w >> l) * (max_h >> l) * sizeof(float4), 256);
 		CK(cudaMalloc(&T.base, bytes));
@@ -105,52 +128,75 @@ extern "C" int dso_b200_create(int device, int max_w, int max_h, int n_frame_slo
 		CK(cudaMalloc(&T.d_mc_count, DSO_B200_MAX_HYP * sizeof(unsigned int)));
 		CK(cudaMemset(T.d_mc_count, 0, DSO_B200_MAX_HYP * sizeof(unsigned int)));
 		CK(cudaHostAlloc(&T.h_track_in, TRACK_IN_RING * TRACK_IN_BLOCK, cudaHostAllocMapped));
-		CK(cudaHostAlloc(&T.h_track_out, sizeof(dso_b200_track_result) * DSO_B200_MAX_HYP, cudaHostAllocMapped));
-		CK(cudaHostAlloc((void**)&T.h_flags, sizeof(unsigned int) * DSO_B200_MAX_HYP, cudaHostAllocMapped));
-		memset(T.h_flags, 0, sizeof(unsigned int) * DSO_B200_MAX_HYP);
-		T.seq = 0; T.last_in = T.d_track_in;
+		CK(cudaHostAlloc(&T.h_track_out, sizeof(dso_b200_track_result) * DSO_B200_MAX_HYP * TRACK_IN_RING, cudaHostAllocMapped));
+		CK(cudaHostAlloc((void**)&T.h_flags, sizeof(unsigned int) * DSO_B200_MAX_HYP * TRACK_IN_RING, cudaHostAllocMapped));
+		memset(T.h_flags, 0, sizeof(unsigned int) * DSO_B200_MAX_HYP * TRACK_IN_RING);
+		T.seq = 0; T.fetched = 0; T.last_in = T.d_track_in;
 		CK(cudaMemset(T.d_track_in, 0, 4096 * 2));
 		T.last_lvl = -1;
 	}
-	int rc = ba_create(ctx);
-	if (rc) return rc;
-	*out = ctx;
-	return 0;
+	return ba_create(ctx);
 }
 
 extern "C" void dso_b200_destroy(dso_b200_ctx* ctx)
 {
 	if (!ctx) return;
 	cudaSetDevice(ctx->device);
-	cudaStreamSynchronize(ctx->upload_stream);
-	cudaStreamSynchronize(ctx->stream);
-	ba_destroy(ctx);
+	cudaStream_t all[5] = { ctx->upload_stream, ctx->stream, ctx->ba_stream, ctx->trk[0].stream, ctx->trk[1].stream };
+	for (int i = 0; i < 5; i++) if (all[i]) cudaStreamSynchronize(all[i]);
+	if (ctx->ba) ba_destroy(ctx);
 	coarse_depth_destroy(ctx);
 	trace_destroy(ctx);
-	for (int s = 0; s < ctx->n_slots; s++) { cudaFree(ctx->slots[s].base); cudaEventDestroy(ctx->slots[s].ready); }
-	delete[] ctx->slots;
-	cudaFree(ctx->d_color); cudaFree(ctx->d_color_up);
-	cudaStreamDestroy(ctx->upload_stream);
+	if (ctx->slots)
+	{
+		for (int s = 0; s < ctx->n_slots; s++)
+		{
+			if (ctx->slots[s].base) cudaFree(ctx->slots[s].base);
+			if (ctx->slots[s].ready) cudaEventDestroy(ctx->slots[s].ready);
+		}
+		delete[] ctx->slots;
+	}
+	cudaFree(ctx->d_color); cudaFree(ctx->d_color_up);      // cudaFree(NULL) is a no-op
 	for (int l = 0; l < MAXL; l++) { cudaFree(ctx->d_aos[l]); cudaFree(ctx->d_abs[l]); }
 	cudaFree(ctx->d_Blut);
 	if (ctx->d_phase_cycles) cudaFree(ctx->d_phase_cycles);
+	cudaFree(ctx->act_scratch);
 	for (int t = 0; t < 2; t++)
 	{
 		TrackerSlot& T = ctx->trk[t];
 		cudaFree(T.base); cudaFree(T.d_sums); cudaFree(T.d_partials); cudaFree(T.d_ticket);
-		cudaFreeHost(T.h_sums); cudaFree(T.d_track_in); cudaFree(T.d_track_out); cudaFree(T.d_mc_part); cudaFree(T.d_mc_count);
-		cudaFreeHost(T.h_track_in); cudaFreeHost(T.h_track_out); cudaFreeHost(T.h_flags);
+		cudaFree(T.d_track_in); cudaFree(T.d_track_out); cudaFree(T.d_mc_part); cudaFree(T.d_mc_count);
+		if (T.h_sums) cudaFreeHost(T.h_sums);
+		if (T.h_track_in) cudaFreeHost(T.h_track_in);
+		if (T.h_track_out) cudaFreeHost(T.h_track_out);
+		if (T.h_flags) cudaFreeHost(T.h_flags);
 	}
-	cudaStreamDestroy(ctx->stream);
+	for (int i = 0; i < 5; i++) if (all[i]) cudaStreamDestroy(all[i]);
 	delete ctx;
 }
 
 extern "C" void* dso_b200_stream(dso_b200_ctx* ctx) { return ctx ? (void*)ctx->stream : nullptr; }
+extern "C" void* dso_b200_stream_for(dso_b200_ctx* ctx, int which)
+{
+	if (!ctx) return nullptr;
+	switch (which)
+	{
+	case DSO_B200_STREAM_MAIN: return (void*)ctx->stream;
+	case DSO_B200_STREAM_TRACKER0: return (void*)ctx->trk[0].stream;
+	case DSO_B200_STREAM_TRACKER1: return (void*)ctx->trk[1].stream;
+	case DSO_B200_STREAM_MAPPING: return (void*)ctx->ba_stream;
+	case DSO_B200_STREAM_UPLOAD: return (void*)ctx->upload_stream;
+	}
+	return nullptr;
+}
 extern "C" int dso_b200_sync(dso_b200_ctx* ctx)
 {
 	ARG_CHECK(ctx, "null context");
 	CK(cudaStreamSynchronize(ctx->upload_stream));
 	CK(cudaStreamSynchronize(ctx->stream));
+	CK(cudaStreamSynchronize(ctx->trk[0].stream));
+	CK(cudaStreamSynchronize(ctx->trk[1].stream));
+	CK(cudaStreamSynchronize(ctx->ba_stream));
 	return 0;
 }
 extern "C" void* dso_b200_host_alloc(size_t bytes)
@@ -160,7 +206,7 @@ extern "C" void* dso_b200_host_alloc(size_t bytes)
 	return p;
 }
 extern "C" void dso_b200_host_free(void* p) { if (p) cudaFreeHost(p); }
-extern "C" long long dso_b200_launch_count(dso_b200_ctx* ctx) { return ctx ? ctx->launches : -1; }
+extern "C" long long dso_b200_launch_count(dso_b200_ctx* ctx) { return ctx ? __atomic_load_n(&ctx->launches, __ATOMIC_RELAXED) : -1; }
 
 static int check_image_args(dso_b200_ctx* ctx, int frame_slot, const float* color, int w, int h, int levels)
 {
@@ -192,16 +238,26 @@ extern "C" int dso_b200_make_images_dev(dso_b200_ctx* ctx, int frame_slot, const
 	const float* d_lut;
 	rc = upload_lut(ctx, B_lut_host, &d_lut);
 	if (rc) return rc;
-	return pyramid_build(ctx, ctx->slots[frame_slot], color_dev, w, h, levels, d_lut, false);
+	rc = pyramid_build(ctx, ctx->slots[frame_slot], color_dev, w, h, levels, d_lut, false);
+	if (rc) return rc;
+	return frame_slot_produced(ctx, ctx->slots[frame_slot], ctx->stream);
 }
 
-int frame_slot_wait(dso_b200_ctx* ctx, int frame_slot)
+int frame_slot_produced(dso_b200_ctx* ctx, FrameSlot& F, cudaStream_t stream)
+{
+	CK(cudaEventRecord(F.ready, stream));
+	F.producer = stream;
+	F.version++;
+	return 0;
+}
+
+int frame_slot_wait(dso_b200_ctx* ctx, int frame_slot, cudaStream_t stream, int consumer)
 {
 	FrameSlot& F = ctx->slots[frame_slot];
-	if (F.pending)
+	if (F.seen[consumer] != F.version)
 	{
-		CK(cudaStreamWaitEvent(ctx->stream, F.ready, 0));
-		F.pending = false;
+		if (F.producer != stream) CK(cudaStreamWaitEvent(stream, F.ready, 0));
+		F.seen[consumer] = F.version;
 	}
 	return 0;
 }
@@ -215,9 +271,7 @@ extern "C" int dso_b200_make_images_async(dso_b200_ctx* ctx, int frame_slot, con
 	CK(cudaMemcpyAsync(ctx->d_color_up, color_host, (size_t)w * h * sizeof(float), cudaMemcpyHostToDevice, ctx->upload_stream));
 	rc = pyramid_build_on(ctx, ctx->upload_stream, F, ctx->d_color_up, w, h, levels, nullptr, false);
 	if (rc) return rc;
-	CK(cudaEventRecord(F.ready, ctx->upload_stream));
-	F.pending = true;
-	return 0;
+	return frame_slot_produced(ctx, F, ctx->upload_stream);
 }
 
 extern "C" int dso_b200_make_images(dso_b200_ctx* ctx, int frame_slot, const float* color_host, int w, int h, int levels,

@@ -281,14 +281,14 @@ extern "C" int dso_b200_tracker_set_ref_points(dso_b200_ctx* ctx, int trk, int r
 	CK(cudaSetDevice(ctx->device));
 	FrameSlot& F = ctx->slots[ref_frame_slot];
 	ARG_CHECK(levels >= 1 && levels <= MAXL && levels <= F.levels, "levels exceed the reference frame's pyramid");
-	int rc = frame_slot_wait(ctx, ref_frame_slot);
-	if (rc) return rc;
 	TrackerSlot& T = ctx->trk[trk];
+	int rc = frame_slot_wait(ctx, ref_frame_slot, T.stream, T.consumer);
+	if (rc) return rc;
 	const int w = F.w, h = F.h;
 	tracker_make_K(T, w, h, levels, fx, fy, cx, cy);                                   // makeK, CoarseTracker.cpp:102-131
 	CoarseDepthWS* ws;
 	if ((rc = cd_workspace(ctx, &ws, (size_t)(n_points > 0 ? n_points : 1)))) return rc;
-	cudaStream_t s = ctx->stream;
+	cudaStream_t s = T.stream;      // the tracker slot being prepared (coarseTracker_forNewKF), not the one tracking
 	CDLevels L;
 	memset(&L, 0, sizeof(L));
 	L.levels = levels;
@@ -320,24 +320,24 @@ extern "C" int dso_b200_tracker_set_ref_points(dso_b200_ctx* ctx, int trk, int r
 		cd_hits_kernel<<<(n_points + 255) / 256, 256, 0, s>>>(n_points, du, dv, w, h, hits);
 		cd_splat_kernel<<<(n_points + 255) / 256, 256, 0, s>>>(n_points, du, dv, di, dh, w, h, hits, L.idepth[0], L.wsum[0]);
 		cd_splat_serial_kernel<<<1, 1024, 0, s>>>(n_points, du, dv, di, dh, w, h, hits, L.idepth[0], L.wsum[0]);
-		ctx->launches += 3;
+		LAUNCHED(ctx, 3);
 	}
 	for (int l = 1; l < levels; l++)
 	{
 		const int n = L.w[l] * L.h[l];
 		cd_down_kernel<<<(n + 255) / 256, 256, 0, s>>>(L.w[l], L.h[l], L.w[l - 1], L.idepth[l - 1], L.wsum[l - 1], L.idepth[l], L.wsum[l]);
-		ctx->launches++;
+		LAUNCHED(ctx, 1);
 	}
 	for (int l = 0; l < levels; l++)
 	{
 		const int n = L.w[l] * L.h[l];
 		cd_dilate_kernel<<<(n + 255) / 256, 256, 0, s>>>(L.w[l], L.h[l], l < 2 ? 1 : 0, L.idepth[l], L.wsum[l], L.wsum2[l]);
-		ctx->launches++;
+		LAUNCHED(ctx, 1);
 	}
 	cd_count_kernel<<<blocks, 256, 0, s>>>(L, ws->d_block_count);
 	cd_scan_kernel<<<levels, 1024, 0, s>>>(L, ws->d_block_count, ws->d_block_off, ws->d_pc_n);
 	cd_write_kernel<<<blocks, 256, 0, s>>>(L, ws->d_block_off);
-	ctx->launches += 3;
+	LAUNCHED(ctx, 3);
 	CK(cudaGetLastError());
 	CK(cudaMemcpyAsync(ws->h_pc_n, ws->d_pc_n, levels * sizeof(int), cudaMemcpyDeviceToHost, s));
 	CK(cudaStreamSynchronize(s));
@@ -362,8 +362,8 @@ extern "C" int dso_b200_tracker_get_cloud(dso_b200_ctx* ctx, int trk, int lvl, i
 	if (out4)
 	{
 		const int n = T.pc_n[lvl] < max_points ? T.pc_n[lvl] : max_points;
-		CK(cudaMemcpyAsync(out4, T.pc[lvl], (size_t)n * sizeof(float4), cudaMemcpyDeviceToHost, ctx->stream));
-		CK(cudaStreamSynchronize(ctx->stream));
+		CK(cudaMemcpyAsync(out4, T.pc[lvl], (size_t)n * sizeof(float4), cudaMemcpyDeviceToHost, T.stream));
+		CK(cudaStreamSynchronize(T.stream));
 	}
 	return 0;
 }

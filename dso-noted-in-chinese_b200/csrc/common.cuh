@@ -46,8 +46,12 @@ struct FrameSlot
 {
 	int w, h, levels;
 	bool valid;
-	bool pending;              // written by the upload stream, not yet waited for by the compute stream
+	// cross-stream ordering: every asynchronous build of this slot records `ready` on its stream and bumps `version`;
+	// each consumer stream (DSO_B200_STREAM_MAIN / _TRACKER0 / _TRACKER1 / _MAPPING) waits for the event once per version
 	cudaEvent_t ready;
+	unsigned int version;
+	unsigned int seen[4];
+	cudaStream_t producer;
 	void* base;
 	float4* pyr[MAXL];
 	float* inten[MAXL];
@@ -81,9 +85,14 @@ struct TrackerSlot
 	void* h_track_in;           // mapped pinned ring of TRACK_IN_RING input blocks, read by the kernel over PCIe (no H2D copy node)
 	void* h_track_out;          // mapped pinned: the kernel writes its results here, then h_flags[hyp] = seq
 	unsigned int* h_flags;      // mapped pinned, one word per hypothesis
-	unsigned int seq;           // sequence number of the last enqueued tracking call with host-visible results (0: none pending)
+	unsigned int seq;           // sequence number of the last enqueued tracking call with host-visible results (0: none yet)
+	unsigned int fetched;       // sequence number of the last call whose results dso_b200_track_fetch handed out
 	const void* last_in;        // input block of the last call (dso_b200_track_batched_async with pose NULL re-runs it)
+	cudaStream_t stream;        // all work of this tracker slot (CoarseTracker object) runs here
+	int consumer;               // DSO_B200_STREAM_TRACKER0 / _TRACKER1
 };
+// h_track_in / h_track_out / h_flags are rings of TRACK_IN_RING blocks indexed by seq % TRACK_IN_RING, so that up to that
+// many tracking calls may be in flight before their results are fetched
 #define TRACK_IN_RING 4
 #define TRACK_IN_BLOCK 8192
 
@@ -93,7 +102,8 @@ struct dso_b200_ctx
 {
 	int device;
 	int sm_count;
-	cudaStream_t stream;
+	cudaStream_t stream;       // DSO_B200_STREAM_MAIN: makeImages (synchronous and _dev variants)
+	cudaStream_t ba_stream;    // DSO_B200_STREAM_MAPPING: windowed BA, immature points (the reference's mapping thread)
 	int max_w, max_h;
 	int n_slots;
 	FrameSlot* slots;
@@ -108,9 +118,18 @@ struct dso_b200_ctx
 	BAWorkspace* ba;
 	void* coarse_depth;        // CoarseDepthWS (coarse_depth.cu), allocated at the first dso_b200_tracker_set_ref_points
 	void* trace;               // TraceWS (trace.cu): the immature points of the window
-	long long launches;
+	void* act_scratch; size_t act_scratch_bytes;      // dso_b200_optimize_immature: grow-only device scratch
+	int tune_threads, tune_cluster, tune_nclusters;   // dso_b200_track_set_tuning (0 = automatic)
+	int last_shape[3];                                // threads, cluster size, clusters per hypothesis of the last tracker launch
+	long long launches;                               // incremented with __atomic_fetch_add (two host threads may launch)
 	void* d_phase_cycles;      // optional: per-phase cycle counters of the persistent tracker (debug)
 };
+
+// kernel-launch accounting: while a thread captures a CUDA graph its launches are only recorded, they count when the
+// graph is replayed
+extern thread_local bool t_capturing;
+extern thread_local long long t_capture_launches;
+#define LAUNCHED(ctx, n) do { if (t_capturing) t_capture_launches += (long long)(n); else __atomic_fetch_add(&(ctx)->launches, (long long)(n), __ATOMIC_RELAXED); } while (0)
 
 // sums layout of one tracker evaluation
 enum
@@ -128,10 +147,13 @@ enum
 
 int pyramid_build_on(dso_b200_ctx* ctx, cudaStream_t stream, FrameSlot& fs, const float* color_dev, int w, int h, int levels,
                      const float* d_Blut, bool host_layout);
-int frame_slot_wait(dso_b200_ctx* ctx, int frame_slot);
+// makes `stream` (consumer id DSO_B200_STREAM_*) wait for the last asynchronous build of the slot, once per build
+int frame_slot_wait(dso_b200_ctx* ctx, int frame_slot, cudaStream_t stream, int consumer);
+// records that the slot's pyramid has just been enqueued on `stream`
+int frame_slot_produced(dso_b200_ctx* ctx, FrameSlot& F, cudaStream_t stream);
 void tracker_make_K(TrackerSlot& T, int w, int h, int levels, float fx, float fy, float cx, float cy);   // CoarseTracker::makeK
 void coarse_depth_destroy(dso_b200_ctx* ctx);
-void trace_destroy(dso_b200_ctx* ctx);   // makes ctx->stream wait for a pending asynchronous upload of the slot
+void trace_destroy(dso_b200_ctx* ctx);
 int pyramid_build(dso_b200_ctx* ctx, FrameSlot& fs, const float* color_dev, int w, int h, int levels,
                   const float* d_Blut, bool host_layout);
 int ba_create(dso_b200_ctx* ctx);

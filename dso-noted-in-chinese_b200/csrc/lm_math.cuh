@@ -29,31 +29,74 @@ HD void pose_to12(const Pose& p, double* v)
 	for (int i = 0; i < 9; i++) v[i] = p.R[i];
 	for (int i = 0; i < 3; i++) v[9 + i] = p.t[i];
 }
-// c = a * b
+// Three-term double products in the order Eigen's fixed-size redux takes them, c0 + (c1 + c2), every operation
+// rounded separately
+HD double dot3dd(double a0, double b0, double a1, double b1, double a2, double b2)
+{
+#ifdef __CUDA_ARCH__
+	return __dadd_rn(__dmul_rn(a0, b0), __dadd_rn(__dmul_rn(a1, b1), __dmul_rn(a2, b2)));
+#else
+	volatile double p0 = a0 * b0, p1 = a1 * b1, p2 = a2 * b2;
+	volatile double s12 = p1 + p2;
+	return p0 + s12;
+#endif
+}
+HD double dadd_r(double a, double b)
+{
+#ifdef __CUDA_ARCH__
+	return __dadd_rn(a, b);
+#else
+	volatile double s = a + b;
+	return s;
+#endif
+}
+HD double dmul_r(double a, double b)
+{
+#ifdef __CUDA_ARCH__
+	return __dmul_rn(a, b);
+#else
+	volatile double s = a * b;
+	return s;
+#endif
+}
+HD void mat33d_mul(const double* A, const double* B, double* C)
+{
+	double T[9];
+	for (int r = 0; r < 3; r++)
+		for (int c = 0; c < 3; c++)
+			T[r * 3 + c] = dot3dd(A[r * 3 + 0], B[c], A[r * 3 + 1], B[3 + c], A[r * 3 + 2], B[6 + c]);
+	for (int i = 0; i < 9; i++) C[i] = T[i];
+}
+// c = a * b  (Sophus SE3 operator*: R = Ra Rb, t = Ra tb + ta)
 HD void pose_mul(const Pose& a, const Pose& b, Pose& c)
 {
 	Pose o;
+	mat33d_mul(a.R, b.R, o.R);
 	for (int r = 0; r < 3; r++)
-	{
-		for (int k = 0; k < 3; k++)
-			o.R[r * 3 + k] = a.R[r * 3 + 0] * b.R[k] + a.R[r * 3 + 1] * b.R[3 + k] + a.R[r * 3 + 2] * b.R[6 + k];
-		o.t[r] = a.R[r * 3 + 0] * b.t[0] + a.R[r * 3 + 1] * b.t[1] + a.R[r * 3 + 2] * b.t[2] + a.t[r];
-	}
+		o.t[r] = dadd_r(dot3dd(a.R[r * 3 + 0], b.t[0], a.R[r * 3 + 1], b.t[1], a.R[r * 3 + 2], b.t[2]), a.t[r]);
 	c = o;
+}
+// Sophus SE3::inverse: R^T, -R^T t
+HD void pose_inverse(const Pose& a, Pose& o)
+{
+	Pose q;
+	for (int r = 0; r < 3; r++) for (int c = 0; c < 3; c++) q.R[r * 3 + c] = a.R[c * 3 + r];
+	for (int r = 0; r < 3; r++)
+		q.t[r] = -dot3dd(q.R[r * 3 + 0], a.t[0], q.R[r * 3 + 1], a.t[1], q.R[r * 3 + 2], a.t[2]);
+	o = q;
 }
 // xi = (translation part u[3], rotation part w[3]);  R = I + A W + B W^2,  t = (I + B W + C W^2) u
 HD void se3_exp(const double* xi, Pose& o)
 {
-	const double ux = xi[0], uy = xi[1], uz = xi[2];
-	const double wx = xi[3], wy = xi[4], wz = xi[5];
-	const double th2 = wx * wx + wy * wy + wz * wz;
+	const double* u = xi; const double* w = xi + 3;
+	const double th2 = dadd_r(dadd_r(dmul_r(w[0], w[0]), dmul_r(w[1], w[1])), dmul_r(w[2], w[2]));
 	const double th = sqrt(th2);
 	double A, B, C;
 	if (th < 1e-5)
 	{
-		A = 1.0 - th2 / 6.0 + th2 * th2 / 120.0;
-		B = 0.5 - th2 / 24.0 + th2 * th2 / 720.0;
-		C = 1.0 / 6.0 - th2 / 120.0 + th2 * th2 / 5040.0;
+		A = dadd_r(1.0 - th2 / 6.0, dmul_r(th2, th2) / 120.0);
+		B = dadd_r(0.5 - th2 / 24.0, dmul_r(th2, th2) / 720.0);
+		C = dadd_r(1.0 / 6.0 - th2 / 120.0, dmul_r(th2, th2) / 5040.0);
 	}
 	else
 	{
@@ -65,19 +108,33 @@ HD void se3_exp(const double* xi, Pose& o)
 #endif
 		A = s / th;
 		B = (1.0 - c) / th2;
-		C = (th - s) / (th2 * th);
+		C = (th - s) / dmul_r(th2, th);
 	}
-	// W = hat(w), W2 = W*W = w w^T - th2 I
-	const double W[9] = { 0, -wz, wy, wz, 0, -wx, -wy, wx, 0 };
-	const double W2[9] = { wx * wx - th2, wx * wy, wx * wz, wx * wy, wy * wy - th2, wy * wz, wx * wz, wy * wz, wz * wz - th2 };
-	const double u[3] = { ux, uy, uz };
-	for (int i = 0; i < 9; i++) o.R[i] = ((i % 4 == 0) ? 1.0 : 0.0) + A * W[i] + B * W2[i];
+	const double W[9] = { 0, -w[2], w[1], w[2], 0, -w[0], -w[1], w[0], 0 };
+	double W2[9];
+	mat33d_mul(W, W, W2);
+	for (int i = 0; i < 9; i++) o.R[i] = dadd_r(dadd_r((i % 4 == 0) ? 1.0 : 0.0, dmul_r(A, W[i])), dmul_r(B, W2[i]));
 	for (int r = 0; r < 3; r++)
 	{
-		double s = 0;
-		for (int c = 0; c < 3; c++) s += (((r == c) ? 1.0 : 0.0) + B * W[r * 3 + c] + C * W2[r * 3 + c]) * u[c];
-		o.t[r] = s;
+		double V[3];
+		for (int c = 0; c < 3; c++) V[c] = dadd_r(dadd_r((r == c) ? 1.0 : 0.0, dmul_r(B, W[r * 3 + c])), dmul_r(C, W2[r * 3 + c]));
+		o.t[r] = dot3dd(V[0], u[0], V[1], u[1], V[2], u[2]);
 	}
+}
+// Sophus SE3::Adj, 6x6 row-major: [[R, hat(t) R], [0, R]]
+HD void pose_adjoint(const Pose& T, double* Ad)
+{
+	const double Th[9] = { 0, -T.t[2], T.t[1], T.t[2], 0, -T.t[0], -T.t[1], T.t[0], 0 };
+	double ThR[9];
+	mat33d_mul(Th, T.R, ThR);
+	for (int i = 0; i < 36; i++) Ad[i] = 0;
+	for (int r = 0; r < 3; r++)
+		for (int c = 0; c < 3; c++)
+		{
+			Ad[r * 6 + c] = T.R[r * 3 + c];
+			Ad[r * 6 + 3 + c] = ThR[r * 3 + c];
+			Ad[(r + 3) * 6 + 3 + c] = T.R[r * 3 + c];
+		}
 }
 
 // AffLight::fromToVecExposure (NumType.h:176-189)

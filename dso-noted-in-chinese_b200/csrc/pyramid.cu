@@ -168,7 +168,7 @@ int pyramid_build_on(dso_b200_ctx* ctx, cudaStream_t stream, FrameSlot& fs, cons
 	{
 		dim3 grid((w + TILE - 1) / TILE, (h + TILE - 1) / TILE);
 		pyr_intensity_kernel<<<grid, 256, 0, stream>>>(ia);
-		ctx->launches++;
+		LAUNCHED(ctx, 1);
 	}
 	GradArgs ga;
 	memset(&ga, 0, sizeof(ga));
@@ -190,7 +190,7 @@ int pyramid_build_on(dso_b200_ctx* ctx, cudaStream_t stream, FrameSlot& fs, cons
 		blocks += (n + 1023) / 1024;   // 256 threads x 4 pixels
 	}
 	pyr_gradient_kernel<<<blocks, 256, 0, stream>>>(ga);
-	ctx->launches++;
+	LAUNCHED(ctx, 1);
 	CK(cudaGetLastError());
 	fs.valid = true;
 	return 0;

@@ -337,7 +337,7 @@ extern "C" int dso_b200_trace_set_points(dso_b200_ctx* ctx, int n, const float* 
 	TraceWS* T;
 	int rc = trace_ws(ctx, &T, n);
 	if (rc) return rc;
-	cudaStream_t s = ctx->stream;
+	cudaStream_t s = ctx->ba_stream;
 	const size_t m = (size_t)n;
 	CK(cudaMemcpyAsync(T->d_u, u, m * 4, cudaMemcpyHostToDevice, s)); CK(cudaMemcpyAsync(T->d_v, v, m * 4, cudaMemcpyHostToDevice, s));
 	CK(cudaMemcpyAsync(T->d_color, color8, m * 32, cudaMemcpyHostToDevice, s)); CK(cudaMemcpyAsync(T->d_weights, weights8, m * 32, cudaMemcpyHostToDevice, s));
@@ -360,7 +360,7 @@ extern "C" int dso_b200_trace_new_coarse(dso_b200_ctx* ctx, int frame_slot, int 
 	ARG_CHECK(frame_slot >= 0 && frame_slot < ctx->n_slots && ctx->slots[frame_slot].valid, "frame slot empty");
 	ARG_CHECK(n_hosts >= 1 && n_hosts <= MAXF && KRKi9 && Kt3 && aff2, "bad host arguments");
 	CK(cudaSetDevice(ctx->device));
-	int rc = frame_slot_wait(ctx, frame_slot);
+	int rc = frame_slot_wait(ctx, frame_slot, ctx->ba_stream, DSO_B200_STREAM_MAPPING);
 	if (rc) return rc;
 	TraceWS* T = (TraceWS*)ctx->trace;
 	const FrameSlot& F = ctx->slots[frame_slot];
@@ -370,12 +370,12 @@ extern "C" int dso_b200_trace_new_coarse(dso_b200_ctx* ctx, int frame_slot, int 
 	{
 		memcpy(H.KRKi[i], KRKi9 + 9 * i, 36); memcpy(H.Kt[i], Kt3 + 3 * i, 12); memcpy(H.aff[i], aff2 + 2 * i, 8);
 	}
-	cudaStream_t s = ctx->stream;
+	cudaStream_t s = ctx->ba_stream;
 	const int n = T->n;
 	trace_on_kernel<<<(n + TR_PTS_PER_BLOCK - 1) / TR_PTS_PER_BLOCK, 256, 0, s>>>(n, F.pyr[0], F.w, F.h, H, T->d_u, T->d_v, T->d_color, T->d_weights, T->d_gradH,
 	                                                                             T->d_energyTH, T->d_host, T->d_idmin, T->d_idmax, T->d_quality, T->d_status,
 	                                                                             T->d_uv, T->d_interval);
-	ctx->launches++;
+	LAUNCHED(ctx, 1);
 	CK(cudaGetLastError());
 	const size_t m = (size_t)n;
 	if (idepth_min_out) CK(cudaMemcpyAsync(idepth_min_out, T->d_idmin, m * 4, cudaMemcpyDeviceToHost, s));
@@ -557,7 +557,7 @@ extern "C" int dso_b200_optimize_immature(dso_b200_ctx* ctx, int n_targets, cons
 		const int sl = target_slots[t];
 		ARG_CHECK(sl >= 0 && sl < ctx->n_slots && ctx->slots[sl].valid, "target frame slot empty");
 		ARG_CHECK(t == 0 || (ctx->slots[sl].w == A.w), "target frames differ in size");
-		int rc = frame_slot_wait(ctx, sl);
+		int rc = frame_slot_wait(ctx, sl, ctx->ba_stream, DSO_B200_STREAM_MAPPING);
 		if (rc) return rc;
 		A.w = ctx->slots[sl].w;
 		A.img[t] = ctx->slots[sl].pyr[0];
@@ -569,11 +569,22 @@ extern "C" int dso_b200_optimize_immature(dso_b200_ctx* ctx, int n_targets, cons
 	A.wM3G = (float)(A.w - 3); A.hM3G = (float)(h - 3);
 	// scratch: reuse the trace workspace's arrays of the same shape (separate point set: allocate a private block)
 	const size_t m = (size_t)n;
-	float* d = nullptr;
-	CK(cudaMalloc(&d, m * (4 + 4 + 32 + 32 + 4 + 4 + 4 + 4 + 4) + m * n_targets * 4));
+	// grow-only scratch kept in the context (cudaMalloc / cudaFree per call would stall the whole device, including the
+	// tracking thread's stream)
+	const size_t need = m * (4 + 4 + 32 + 32 + 4 + 4 + 4 + 4 + 4) + m * n_targets * 4;
+	if (need > ctx->act_scratch_bytes)
+	{
+		CK(cudaStreamSynchronize(ctx->ba_stream));
+		if (ctx->act_scratch) CK(cudaFree(ctx->act_scratch));
+		ctx->act_scratch = nullptr; ctx->act_scratch_bytes = 0;
+		const size_t cap = need + need / 2;
+		CK(cudaMalloc(&ctx->act_scratch, cap));
+		ctx->act_scratch_bytes = cap;
+	}
+	float* d = (float*)ctx->act_scratch;
 	float* d_u = d; float* d_v = d_u + m; float* d_c = d_v + m; float* d_w = d_c + 8 * m; float* d_e = d_w + 8 * m;
 	float* d_lo = d_e + m; float* d_hi = d_lo + m; float* d_id = d_hi + m; int* d_res = (int*)(d_id + m); int* d_rs = d_res + m;
-	cudaStream_t s = ctx->stream;
+	cudaStream_t s = ctx->ba_stream;
 	cudaError_t e = cudaSuccess;
 #define UP(dst, src, bytes) if (e == cudaSuccess) e = cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, s)
 	UP(d_u, u, m * 4); UP(d_v, v, m * 4); UP(d_c, color8, m * 32); UP(d_w, weights8, m * 32); UP(d_e, energyTH, m * 4);
@@ -582,14 +593,13 @@ extern "C" int dso_b200_optimize_immature(dso_b200_ctx* ctx, int n_targets, cons
 	if (e == cudaSuccess)
 	{
 		optimize_immature_kernel<<<(n + TR_PTS_PER_BLOCK - 1) / TR_PTS_PER_BLOCK, 256, 0, s>>>(n, A, minObs, d_u, d_v, d_c, d_w, d_e, d_lo, d_hi, d_res, d_id, d_rs);
-		ctx->launches++;
+		LAUNCHED(ctx, 1);
 		e = cudaGetLastError();
 	}
 	if (e == cudaSuccess) e = cudaMemcpyAsync(result, d_res, m * 4, cudaMemcpyDeviceToHost, s);
 	if (e == cudaSuccess) e = cudaMemcpyAsync(idepth_out, d_id, m * 4, cudaMemcpyDeviceToHost, s);
 	if (e == cudaSuccess && res_state_out) e = cudaMemcpyAsync(res_state_out, d_rs, m * n_targets * 4, cudaMemcpyDeviceToHost, s);
 	if (e == cudaSuccess) e = cudaStreamSynchronize(s);
-	cudaFree(d);
 	CK(e);
 	return 0;
 }

@@ -429,6 +429,11 @@ struct LM
 			return;
 		}
 		const bool accept = (r.E / r.n) < (resOldE / resOldN);         // :669
+		if (out->trace_len < DSO_B200_TRACE_MARGINS)
+		{
+			out->trace_dE[out->trace_len] = (float)(r.E * resOldN - resOldE * r.n);
+			out->trace_E[out->trace_len] = (float)(resOldE * r.n);
+		}
 		if (out->trace_len < 256) out->trace[out->trace_len++] = accept ? 1 : 0;
 		out->n_iterations++;
 		if (accept)
@@ -573,7 +578,8 @@ __device__ __forceinline__ void lm_step_warp(LMS& S, const float* s_tot, const T
 	{
 		// :669  (E'/n' < E/n) evaluated as E'*n < E*n' (n, n' >= 0; equal up to a 1-ulp tie of the two quotients,
 		// and false like the reference's NaN comparison when a count is 0) -- keeps two FP64 divisions off the chain
-		const bool accept = (newE * S.resOldN) < (S.resOldE * newN);
+		const double acc_l = newE * S.resOldN, acc_r = S.resOldE * newN;
+		const bool accept = acc_l < acc_r;
 		if (accept)
 		{
 			take = true;
@@ -587,6 +593,7 @@ __device__ __forceinline__ void lm_step_warp(LMS& S, const float* s_tot, const T
 		propose = !level_done;
 		if (lane == 0)
 		{
+			if (out->trace_len < DSO_B200_TRACE_MARGINS) { out->trace_dE[out->trace_len] = (float)(acc_l - acc_r); out->trace_E[out->trace_len] = (float)acc_r; }
 			if (out->trace_len < 256) out->trace[out->trace_len++] = accept ? 1 : 0;
 			out->n_iterations++;
 		}
@@ -872,6 +879,8 @@ track_persistent_kernel(TrackLevels TL, dso_b200_track_opts opt, const TrackIn* 
 	__shared__ dso_b200_track_result s_res;
 	extern __shared__ float4 s_pts[];
 
+	for (int i = tid; i < (int)(sizeof(dso_b200_track_result) / 4); i += NT) reinterpret_cast<unsigned int*>(&s_res)[i] = 0u;
+	__syncthreads();
 	if (warp == 0)
 	{
 		// the input block may live in mapped host memory: one coalesced read by 19 lanes, then shared memory
@@ -967,7 +976,19 @@ track_persistent_kernel(TrackLevels TL, dso_b200_track_opts opt, const TrackIn* 
 			{
 				if (rank == 0) { __threadfence(); atomicAdd(mc_count + hyp, 1u); }
 				const unsigned int want = mc_round * (unsigned)NC;
-				while (*((volatile unsigned int*)(mc_count + hyp)) < want) { }
+				// the grid is launched cooperatively (all clusters co-resident or the launch is refused), so this wait
+				// always ends; the time limit only turns a violated assumption into a launch failure instead of a hang
+				unsigned long long t0 = 0, spins = 0;
+				while (*((volatile unsigned int*)(mc_count + hyp)) < want)
+				{
+					if ((++spins & 0xfffu) == 0)
+					{
+						unsigned long long now;
+						asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+						if (!t0) t0 = now;
+						else if (now - t0 > 4000000000ull) __trap();
+					}
+				}
 				__threadfence();
 			}
 			__syncthreads();
@@ -1104,9 +1125,13 @@ extern "C" int dso_b200_tracker_set_ref(dso_b200_ctx* ctx, int trk, int w, int h
 		T.pc_n[l] = n;
 		tmp.resize(n);
 		for (int i = 0; i < n; i++) tmp[i] = make_float4(pc_u[l][i], pc_v[l][i], pc_idepth[l][i], pc_color[l][i]);
-		if (n) CK(cudaMemcpyAsync(T.pc[l], tmp.data(), sizeof(float4) * n, cudaMemcpyHostToDevice, ctx->stream));
-		CK(cudaStreamSynchronize(ctx->stream));
+		if (n)
+		{
+			// pageable source: the call returns once the data sits in the driver's staging area, so tmp can be reused
+			CK(cudaMemcpyAsync(T.pc[l], tmp.data(), sizeof(float4) * n, cudaMemcpyHostToDevice, T.stream));
+		}
 	}
+	CK(cudaStreamSynchronize(T.stream));
 	T.ref_a = ref_aff_a; T.ref_b = ref_aff_b; T.ref_exposure = ref_ab_exposure;
 	T.valid = true; T.last_lvl = -1; T.last_warped_n = 0;
 	return 0;
@@ -1120,7 +1145,7 @@ static int check_eval_args(dso_b200_ctx* ctx, int trk, int frame_slot, int lvl)
 	const FrameSlot& F = ctx->slots[frame_slot];
 	ARG_CHECK(lvl >= 0 && lvl < T.levels && lvl < F.levels, "bad level");
 	ARG_CHECK(F.w == T.w[0] && F.h == T.h[0], "frame / tracker size mismatch");
-	return frame_slot_wait(ctx, frame_slot);   // a pending dso_b200_make_images_async of this slot
+	return frame_slot_wait(ctx, frame_slot, ctx->trk[trk].stream, ctx->trk[trk].consumer);   // an asynchronous build of this slot on another stream
 }
 
 static int grid_for(const dso_b200_ctx* ctx, int n)
@@ -1142,13 +1167,13 @@ static int run_eval(dso_b200_ctx* ctx, int trk, int frame_slot, int lvl, const P
 	make_eval_params(TL, lvl, pose, a, b, cutoffTH, huberTH, P);
 	int g = grid_for(ctx, P.n);
 	if (debug)
-		track_eval_kernel<true><<<g, EVAL_THREADS, 0, ctx->stream>>>(P, T.pc[lvl], TL.img[lvl], T.d_partials, T.d_ticket, T.d_sums, d_status, d_warped);
+		track_eval_kernel<true><<<g, EVAL_THREADS, 0, T.stream>>>(P, T.pc[lvl], TL.img[lvl], T.d_partials, T.d_ticket, T.d_sums, d_status, d_warped);
 	else
-		track_eval_kernel<false><<<g, EVAL_THREADS, 0, ctx->stream>>>(P, T.pc[lvl], TL.img[lvl], T.d_partials, T.d_ticket, T.d_sums, nullptr, nullptr);
-	ctx->launches++;
+		track_eval_kernel<false><<<g, EVAL_THREADS, 0, T.stream>>>(P, T.pc[lvl], TL.img[lvl], T.d_partials, T.d_ticket, T.d_sums, nullptr, nullptr);
+	LAUNCHED(ctx, 1);
 	CK(cudaGetLastError());
-	CK(cudaMemcpyAsync(T.h_sums, T.d_sums, sizeof(float) * S_COUNT, cudaMemcpyDeviceToHost, ctx->stream));
-	CK(cudaStreamSynchronize(ctx->stream));
+	CK(cudaMemcpyAsync(T.h_sums, T.d_sums, sizeof(float) * S_COUNT, cudaMemcpyDeviceToHost, T.stream));
+	CK(cudaStreamSynchronize(T.stream));
 	T.last_lvl = lvl;
 	return 0;
 }
@@ -1190,7 +1215,7 @@ extern "C" int dso_b200_calc_res_debug(dso_b200_ctx* ctx, int trk, int frame_slo
 	unsigned char* d_status = nullptr; float* d_warped = nullptr;
 	CK(cudaMalloc(&d_status, n + 16));
 	CK(cudaMalloc(&d_warped, sizeof(float) * 8 * (size_t)(n + 1)));
-	CK(cudaMemsetAsync(d_warped, 0, sizeof(float) * 8 * (size_t)(n + 1), ctx->stream));
+	CK(cudaMemsetAsync(d_warped, 0, sizeof(float) * 8 * (size_t)(n + 1), T.stream));
 	Pose p; pose_from12(p, refToNew12);
 	rc = run_eval(ctx, trk, frame_slot, lvl, p, aff_a, aff_b, new_ab_exposure, cutoffTH, 9.0f, true, d_status, d_warped);
 	if (!rc)
@@ -1244,8 +1269,17 @@ extern "C" int dso_b200_track_replay_abort(const dso_b200_track_result* r, const
 	return ok;
 }
 
-// Enqueue (no synchronisation): upload of the initial poses, the persistent kernel, download of the
-// results into the slot's pinned buffer.
+// sequence numbers of tracking calls: 1, 2, ..., 2^32-1, 1, ... (0 = "no host-visible results")
+static inline unsigned int next_seq(unsigned int s) { return s + 1u == 0u ? 1u : s + 1u; }
+static inline unsigned int seq_distance(unsigned int from, unsigned int to)
+{
+	unsigned int d = 0;
+	while (from != to && d <= TRACK_IN_RING) { from = next_seq(from); d++; }
+	return d;
+}
+
+// Enqueue (no synchronisation): the persistent kernel reads the initial poses from and writes its results to mapped
+// pinned memory.
 static int enqueue_track(dso_b200_ctx* ctx, int trk, int frame_slot, int nHyp, const double* pose12_init,
                          double aff_a_init, double aff_b_init, float new_ab_exposure, int coarsestLvl,
                          const dso_b200_track_opts* opts)
@@ -1266,9 +1300,14 @@ static int enqueue_track(dso_b200_ctx* ctx, int trk, int frame_slot, int nHyp, c
 	if (pose12_init)
 	{
 		// the kernel reads its inputs from a ring of mapped pinned blocks (one PCIe read by one warp) and writes its
-		// results back the same way: no copy nodes in front of or behind the kernel
-		seq = ++T.seq;
-		if (seq == 0) seq = ++T.seq;
+		// results into the matching block of the result ring: no copy nodes in front of or behind the kernel
+		if (seq_distance(T.fetched, T.seq) >= TRACK_IN_RING)
+		{
+			dso_set_error("dso_b200_track_batched_async: %d tracking calls on this slot are waiting for dso_b200_track_fetch; "
+			              "fetch before enqueueing more", TRACK_IN_RING);
+			return DSO_B200_E_STATE;
+		}
+		seq = T.seq = next_seq(T.seq);
 		TrackIn* hin = (TrackIn*)((char*)T.h_track_in + (size_t)(seq % TRACK_IN_RING) * TRACK_IN_BLOCK);
 		for (int i = 0; i < nHyp; i++)
 		{
@@ -1292,15 +1331,18 @@ static int enqueue_track(dso_b200_ctx* ctx, int trk, int frame_slot, int nHyp, c
 	size_t smem_cap_bytes = 160 * 1024;
 	int cap = (int)std::min<size_t>((size_t)per, smem_cap_bytes / sizeof(float4));
 	size_t dyn = (size_t)cap * sizeof(float4);
-	// tuning knobs (debug): threads per CTA and cluster size
+	// tuning knobs (dso_b200_track_set_tuning; the DSO_B200_TRACK_* environment variables give the defaults): threads per
+	// CTA and cluster size
 	static int env_threads = -1, env_cluster = -1;
 	if (env_threads < 0)
 	{
 		const char* e = getenv("DSO_B200_TRACK_THREADS"); env_threads = e ? atoi(e) : 0;
 		e = getenv("DSO_B200_TRACK_CLUSTER"); env_cluster = e ? atoi(e) : 0;
 	}
-	int nt = env_threads ? env_threads : PERS_THREADS;
-	if (env_cluster) cs = env_cluster;
+	const int want_threads = ctx->tune_threads ? ctx->tune_threads : env_threads;
+	const int want_cluster = ctx->tune_cluster ? ctx->tune_cluster : env_cluster;
+	int nt = want_threads ? want_threads : PERS_THREADS;
+	if (want_cluster) cs = want_cluster;
 	while (cs > 1 && nHyp * cs > ctx->sm_count) cs >>= 1;
 	per = (max_n + cs - 1) / cs;
 	cap = (int)std::min<size_t>((size_t)per, smem_cap_bytes / sizeof(float4));
@@ -1320,8 +1362,9 @@ static int enqueue_track(dso_b200_ctx* ctx, int trk, int frame_slot, int nHyp, c
 	// large clouds, one hypothesis: spread it over several clusters (DSO_B200_TRACK_NCLUSTERS overrides; 1 = off).  All
 	// CTAs exchange through a spin barrier, so the count is capped by what can be resident at once.
 	int nc = 1;
-	static int env_nc = -1;
-	if (env_nc < 0) { const char* e = getenv("DSO_B200_TRACK_NCLUSTERS"); env_nc = e ? atoi(e) : 0; }
+	static int env_nc_s = -1;
+	if (env_nc_s < 0) { const char* e = getenv("DSO_B200_TRACK_NCLUSTERS"); env_nc_s = e ? atoi(e) : 0; }
+	const int env_nc = ctx->tune_nclusters ? ctx->tune_nclusters : env_nc_s;
 	if (nHyp == 1 && (env_nc > 1 || (env_nc == 0 && max_n >= 32768)))
 	{
 		cudaLaunchConfig_t q = {};
@@ -1346,21 +1389,42 @@ static int enqueue_track(dso_b200_ctx* ctx, int trk, int frame_slot, int nHyp, c
 		per = (max_n + cs * nc - 1) / (cs * nc);
 		cap = (int)std::min<size_t>((size_t)per, smem_cap_bytes / sizeof(float4));
 		dyn = (size_t)cap * sizeof(float4);
-		if (nc > 1) CK(cudaMemsetAsync(T.d_mc_count, 0, sizeof(unsigned int) * DSO_B200_MAX_HYP, ctx->stream));
+		if (nc > 1) CK(cudaMemsetAsync(T.d_mc_count, 0, sizeof(unsigned int) * DSO_B200_MAX_HYP, T.stream));
 	}
 	cudaLaunchConfig_t cfg = {};
-	cfg.gridDim = dim3(nHyp * cs * nc, 1, 1);
 	cfg.blockDim = dim3(nt, 1, 1);
-	cfg.dynamicSmemBytes = dyn;
-	cfg.stream = ctx->stream;
-	cudaLaunchAttribute at[1];
+	cfg.stream = T.stream;
+	cudaLaunchAttribute at[2];
 	at[0].id = cudaLaunchAttributeClusterDimension;
 	at[0].val.clusterDim.x = cs; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
-	cfg.attrs = at; cfg.numAttrs = 1;
-	CK(cudaLaunchKernelEx(&cfg, kern, TL, o, kin, (dso_b200_track_result*)T.d_track_out, coarsestLvl, cap, (long long*)ctx->d_phase_cycles,
-	                      seq ? (dso_b200_track_result*)T.h_track_out : (dso_b200_track_result*)nullptr, T.h_flags, seq,
-	                      nc, T.d_mc_part, T.d_mc_count));
-	ctx->launches++;
+	// nc > 1: the clusters of one hypothesis wait for each other in global memory, so they must all be resident at once.
+	// A cooperative launch makes the driver guarantee that (or refuse the launch, e.g. when another context holds SMs);
+	// a refused launch falls back to one cluster, which needs no co-residency.
+	at[1].id = cudaLaunchAttributeCooperative; at[1].val.cooperative = 1;
+	cfg.attrs = at;
+	for (int attempt = 0; attempt < 2; attempt++)
+	{
+		cfg.gridDim = dim3(nHyp * cs * nc, 1, 1);
+		cfg.dynamicSmemBytes = dyn;
+		cfg.numAttrs = nc > 1 ? 2 : 1;
+		cudaError_t le = cudaLaunchKernelEx(&cfg, kern, TL, o, kin, (dso_b200_track_result*)T.d_track_out, coarsestLvl, cap, (long long*)ctx->d_phase_cycles,
+		                                    seq ? (dso_b200_track_result*)T.h_track_out + (size_t)(seq % TRACK_IN_RING) * DSO_B200_MAX_HYP : (dso_b200_track_result*)nullptr,
+		                                    T.h_flags + (size_t)(seq % TRACK_IN_RING) * DSO_B200_MAX_HYP, seq,
+		                                    nc, T.d_mc_part, T.d_mc_count);
+		if (le == cudaSuccess) break;
+		if (nc > 1 && attempt == 0)
+		{
+			(void)cudaGetLastError();
+			nc = 1;
+			per = (max_n + cs - 1) / cs;
+			cap = (int)std::min<size_t>((size_t)per, smem_cap_bytes / sizeof(float4));
+			dyn = (size_t)cap * sizeof(float4);
+			continue;
+		}
+		CK(le);
+	}
+	ctx->last_shape[0] = nt; ctx->last_shape[1] = cs; ctx->last_shape[2] = nc;
+	LAUNCHED(ctx, 1);
 	return 0;
 }
 
@@ -1371,6 +1435,23 @@ extern "C" int dso_b200_track_batched_async(dso_b200_ctx* ctx, int trk, int fram
 	return enqueue_track(ctx, trk, frame_slot, nHyp, pose12_init, aff_a_init, aff_b_init, new_ab_exposure, coarsestLvl, opts);
 }
 
+extern "C" int dso_b200_track_set_tuning(dso_b200_ctx* ctx, int threads, int cluster_size, int n_clusters)
+{
+	ARG_CHECK(ctx, "null context");
+	ARG_CHECK(threads == 0 || threads == 128 || threads == 256 || threads == 384 || threads == 512, "threads must be 0, 128, 256, 384 or 512");
+	ARG_CHECK(cluster_size == 0 || cluster_size == 1 || cluster_size == 2 || cluster_size == 4 || cluster_size == 8 || cluster_size == 16, "cluster_size must be 0 or a power of two <= 16");
+	ARG_CHECK(n_clusters >= 0 && n_clusters <= DSO_B200_TRACK_MAX_NC, "n_clusters out of range");
+	ctx->tune_threads = threads; ctx->tune_cluster = cluster_size; ctx->tune_nclusters = n_clusters;
+	return 0;
+}
+
+extern "C" int dso_b200_track_last_shape(dso_b200_ctx* ctx, int* shape3)
+{
+	ARG_CHECK(ctx && shape3, "null argument");
+	for (int i = 0; i < 3; i++) shape3[i] = ctx->last_shape[i];
+	return 0;
+}
+
 extern "C" int dso_b200_track_phase_cycles(dso_b200_ctx* ctx, int enable, long long* cycles7)
 {
 	ARG_CHECK(ctx, "null context");
@@ -1378,7 +1459,8 @@ extern "C" int dso_b200_track_phase_cycles(dso_b200_ctx* ctx, int enable, long l
 	if (enable && !ctx->d_phase_cycles) { CK(cudaMalloc(&ctx->d_phase_cycles, 128)); CK(cudaMemset(ctx->d_phase_cycles, 0, 128)); }
 	if (cycles7 && ctx->d_phase_cycles)
 	{
-		CK(cudaStreamSynchronize(ctx->stream));
+		CK(cudaStreamSynchronize(ctx->trk[0].stream));
+		CK(cudaStreamSynchronize(ctx->trk[1].stream));
 		CK(cudaMemcpy(cycles7, ctx->d_phase_cycles, 112, cudaMemcpyDeviceToHost));
 	}
 	if (!enable && ctx->d_phase_cycles) { cudaFree(ctx->d_phase_cycles); ctx->d_phase_cycles = nullptr; }
@@ -1389,28 +1471,34 @@ extern "C" int dso_b200_track_fetch(dso_b200_ctx* ctx, int trk, int nHyp, dso_b2
 {
 	ARG_CHECK(ctx && (trk == 0 || trk == 1) && out && nHyp >= 1 && nHyp <= DSO_B200_MAX_HYP, "bad arguments");
 	TrackerSlot& T = ctx->trk[trk];
-	if (T.seq)
+	if (T.fetched != T.seq)
 	{
-		// poll the flags the kernel writes after its results (mapped pinned memory); look at the stream now and then so
-		// that a failed launch or a device fault surfaces as an error instead of a hang
-		volatile unsigned int* f = T.h_flags;
-		const unsigned int want = T.seq;
+		// oldest call whose results have not been handed out: poll the flags the kernel writes after its results (mapped
+		// pinned memory); look at the stream now and then so that a failed launch or a device fault surfaces as an error
+		// instead of a hang
+		const unsigned int want = next_seq(T.fetched);
+		const size_t blk = (size_t)(want % TRACK_IN_RING) * DSO_B200_MAX_HYP;
+		volatile unsigned int* f = T.h_flags + blk;
 		unsigned long long spins = 0;
 		for (int i = 0; i < nHyp; i++)
 			while (f[i] != want)
 			{
 				if ((++spins & 0x3fff) == 0)
 				{
-					cudaError_t e = cudaStreamQuery(ctx->stream);
+					cudaError_t e = cudaStreamQuery(T.stream);
 					if (e != cudaSuccess && e != cudaErrorNotReady) CK(e);
 					if (e == cudaSuccess && f[i] != want) { dso_set_error("dso_b200_track_fetch: stream idle but results missing"); return DSO_B200_E_STATE; }
 				}
 			}
 		std::atomic_thread_fence(std::memory_order_acquire);
+		memcpy(out, (const dso_b200_track_result*)T.h_track_out + blk, sizeof(dso_b200_track_result) * nHyp);
+		T.fetched = want;
+		return 0;
 	}
-	else
-		CK(cudaStreamSynchronize(ctx->stream));
-	memcpy(out, T.h_track_out, sizeof(dso_b200_track_result) * nHyp);
+	// nothing pending with host-visible results (kernel-only launches): the device-side results of the last launch
+	CK(cudaSetDevice(ctx->device));
+	CK(cudaStreamSynchronize(T.stream));
+	CK(cudaMemcpy(out, T.d_track_out, sizeof(dso_b200_track_result) * nHyp, cudaMemcpyDeviceToHost));
 	return 0;
 }
 
@@ -1431,8 +1519,13 @@ extern "C" int dso_b200_track_frame(dso_b200_ctx* ctx, int trk, int frame_slot, 
 	ARG_CHECK(ctx && color_host && frame_slot >= 0 && frame_slot < ctx->n_slots, "bad arguments");
 	ARG_CHECK(w >= 16 && h >= 16 && w <= ctx->max_w && h <= ctx->max_h && levels >= 1 && levels <= MAXL, "bad image size / levels");
 	CK(cudaSetDevice(ctx->device));
-	CK(cudaMemcpyAsync(ctx->d_color, color_host, (size_t)w * h * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
-	int rc = pyramid_build(ctx, ctx->slots[frame_slot], ctx->d_color, w, h, levels, nullptr, false);
+	// the whole frame on the tracker slot's stream: upload, pyramid, tracking (no cross-stream hand-over)
+	ARG_CHECK(trk == 0 || trk == 1, "bad tracker slot");
+	cudaStream_t st = ctx->trk[trk].stream;
+	CK(cudaMemcpyAsync(ctx->d_color, color_host, (size_t)w * h * sizeof(float), cudaMemcpyHostToDevice, st));
+	int rc = pyramid_build_on(ctx, st, ctx->slots[frame_slot], ctx->d_color, w, h, levels, nullptr, false);
+	if (rc) return rc;
+	rc = frame_slot_produced(ctx, ctx->slots[frame_slot], st);
 	if (rc) return rc;
 	rc = enqueue_track(ctx, trk, frame_slot, nHyp, pose12_init, aff_a_init, aff_b_init, new_ab_exposure, coarsestLvl, opts);
 	if (rc) return rc;

@@ -12,8 +12,13 @@
  *   - matrices are row-major; poses are 12 doubles: R (3x3 row-major) followed by t.
  *   - "host" pointers are ordinary (ideally pinned, see dso_b200_host_alloc) CPU memory; "dev"
  *     pointers are CUDA device memory owned by the caller.
- *   - all work of a context is issued on the context's stream; calls that return data to host
- *     memory synchronise that stream before returning, *_async/_dev variants do not.
+ *   - streams and threads.  The reference runs tracking (FullSystem::addActiveFrame, under trackMutex, FullSystem.cpp:838)
+ *     and mapping (FullSystem::makeKeyFrame, under mapMutex, :1098) on two threads at once and swaps its two CoarseTracker
+ *     objects between them (:898-902, :1180-1182).  A context therefore has one stream per tracker slot, one for the
+ *     mapping side (windowed BA, immature points) and one for makeImages; work of different groups never queues behind
+ *     each other, and device-side events order a frame slot's build before its readers.  One host thread per group may call
+ *     into the same context concurrently (tracker slot 0 / tracker slot 1 / mapping); calls within a group are not
+ *     re-entrant.  Calls that return data to host memory synchronise their own stream, *_async/_dev variants do not.
  */
 #ifndef DSO_B200_H
 #define DSO_B200_H
@@ -26,6 +31,7 @@ extern "C" {
 #define DSO_B200_MAX_FRAMES 8      /* window size at optimise time, FullSystem.cpp:1102-1152 */
 #define DSO_B200_MAX_HYP 32        /* FullSystem.cpp:311-354 builds 31 pose priors */
 #define DSO_B200_MAX_PASSES 8      /* level passes of one trackNewestCoarse (levels + one repeat) */
+#define DSO_B200_TRACE_MARGINS 64  /* accept tests whose margin is kept in dso_b200_track_result */
 
 #define DSO_B200_E_ARG (-1)
 #define DSO_B200_E_CUDA (-2)
@@ -41,8 +47,17 @@ typedef struct dso_b200_ctx dso_b200_ctx;
 int dso_b200_create(int device, int max_w, int max_h, int n_frame_slots, dso_b200_ctx** out);
 void dso_b200_destroy(dso_b200_ctx* ctx);
 const char* dso_b200_last_error(void);
-/* cudaStream_t of the context (so callers can order their own work / record events on it). */
+/* cudaStream_t of the context's main stream / of one of its groups (so callers can order their own work or record
+ * events on it): MAIN makeImages and its _dev variant; TRACKER0/1 everything taking that `trk` index (tracker_set_ref*,
+ * calc_res, track_*); MAPPING every dso_b200_ba_*, dso_b200_trace_* and dso_b200_optimize_immature call; UPLOAD
+ * dso_b200_make_images_async. */
+#define DSO_B200_STREAM_MAIN 0
+#define DSO_B200_STREAM_TRACKER0 1
+#define DSO_B200_STREAM_TRACKER1 2
+#define DSO_B200_STREAM_MAPPING 3
+#define DSO_B200_STREAM_UPLOAD 4
 void* dso_b200_stream(dso_b200_ctx* ctx);
+void* dso_b200_stream_for(dso_b200_ctx* ctx, int which);
 int dso_b200_sync(dso_b200_ctx* ctx);
 /* pinned host memory for image / result buffers (cudaHostAlloc / cudaFreeHost) */
 void* dso_b200_host_alloc(size_t bytes);
@@ -148,10 +163,10 @@ int dso_b200_calc_res_debug(dso_b200_ctx* ctx, int trk, int frame_slot, int lvl,
 
 typedef struct
 {
-	float huberTH;            /* setting_huberTH = 9 (util/settings.cpp:138) */
-	float coarseCutoffTH;     /* setting_coarseCutoffTH = 20 (:146) */
-	float affineOptModeA;     /* setting_affineOptModeA = 1e12 (:124) */
-	float affineOptModeB;     /* setting_affineOptModeB = 1e8 (:125) */
+	float huberTH;            /* setting_huberTH = 9 (util/settings.cpp:127) */
+	float coarseCutoffTH;     /* setting_coarseCutoffTH = 20 (:138) */
+	float affineOptModeA;     /* setting_affineOptModeA = 1e12 (:119) */
+	float affineOptModeB;     /* setting_affineOptModeB = 1e8 (:120) */
 	int maxIterations[5];     /* {10,20,50,50,50}, CoarseTracker.cpp:569 */
 } dso_b200_track_opts;
 void dso_b200_track_opts_default(dso_b200_track_opts* o);
@@ -172,6 +187,10 @@ typedef struct
 	int trace_len;
 	unsigned char trace[256];        /* accept(1) / reject(0) per LM iteration */
 	double point_evals;
+	/* how close the first DSO_B200_TRACE_MARGINS accept tests (CoarseTracker.cpp:669, E'/n' < E/n, cross-multiplied) were:
+	 * trace_dE[i] = E'n - En', trace_E[i] = En'.  The float energy sums are taken in a different order than the reference's
+	 * sequential loop, so a decision with |trace_dE / trace_E| of the order of float rounding may legitimately differ. */
+	float trace_dE[DSO_B200_TRACE_MARGINS], trace_E[DSO_B200_TRACE_MARGINS];
 } dso_b200_track_result;
 
 /* CoarseTracker::trackNewestCoarse (CoarseTracker.cpp:551-747, decl CoarseTracker.h:51-55) for nHyp
@@ -182,10 +201,12 @@ typedef struct
 int dso_b200_track_batched(dso_b200_ctx* ctx, int trk, int frame_slot, int nHyp, const double* pose12_init,
                            double aff_a_init, double aff_b_init, float new_ab_exposure, int coarsestLvl,
                            const dso_b200_track_opts* opts, dso_b200_track_result* out);
-/* Asynchronous form of dso_b200_track_batched: enqueues the work on the context's stream and returns;
- * dso_b200_track_fetch waits for the stream and copies out the results of the most recent call on trk.
- * With pose12_init == NULL only the kernel is enqueued: it re-uses the initial poses uploaded by the
- * previous call and leaves its results on the device (used to time the kernel alone). */
+/* Asynchronous form of dso_b200_track_batched: enqueues the work on the tracker slot's stream and returns.
+ * dso_b200_track_fetch hands out results in call order: each fetch waits for and returns the oldest call on trk whose
+ * results have not been fetched yet.  At most 4 such calls may be in flight; a fifth is refused with DSO_B200_E_STATE.
+ * With pose12_init == NULL only the kernel is enqueued: it re-uses the initial poses of the previous call and leaves its
+ * results on the device (used to time the kernel alone); a fetch with no un-fetched call pending waits for the slot's
+ * stream and returns those device-side results of the last launch. */
 int dso_b200_track_batched_async(dso_b200_ctx* ctx, int trk, int frame_slot, int nHyp, const double* pose12_init,
                                  double aff_a_init, double aff_b_init, float new_ab_exposure, int coarsestLvl,
                                  const dso_b200_track_opts* opts);
@@ -203,6 +224,15 @@ int dso_b200_track_frame(dso_b200_ctx* ctx, int trk, int frame_slot, const float
  * cycles7 (12 values, may be NULL) receives them; [8..11] split the LM step into sums+control, solve,
  * exponential+pose update, parameter build. */
 int dso_b200_track_phase_cycles(dso_b200_ctx* ctx, int enable, long long* cycles7);
+/* Launch shape of the persistent tracker (no counterpart in the reference; tests and tuning): threads per CTA (128, 256,
+ * 384, 512), CTAs per cluster (power of two <= 16) and, for single-hypothesis calls, the number of clusters the cloud is
+ * spread over (1 = never split; by default clouds of >= 32768 points per level are split).  0 = automatic.  Results
+ * change only through the order of the float sums. */
+int dso_b200_track_set_tuning(dso_b200_ctx* ctx, int threads, int cluster_size, int n_clusters);
+/* shape3 = { threads, cluster size, clusters per hypothesis } of the last persistent-tracker launch on this context.  With
+ * more than one cluster per hypothesis the launch is cooperative (all clusters co-resident, guaranteed by the driver); if the
+ * device cannot host them at once -- e.g. another context occupies SMs -- the call falls back to one cluster. */
+int dso_b200_track_last_shape(dso_b200_ctx* ctx, int* shape3);
 /* Applies CoarseTracker.cpp:713 to a finished result: returns 1 if trackNewestCoarse would have
  * returned true for this minResForAbort, 0 if it would have aborted (lastResiduals5_out then holds
  * what CoarseTracker::lastResiduals would contain at the abort). */

@@ -71,6 +71,9 @@ typedef struct
 	int trace_len;            /* accept(1)/reject(0) decisions, at most 256 kept */
 	unsigned char trace[256];
 	double point_evals;       /* sum over calcRes calls of pc_n[lvl] (work measure) */
+	/* margin of the first 64 accept tests (:669), E'/n' < E/n cross-multiplied: trace_dE = E'n - En', trace_E = En';
+	 * |trace_dE / trace_E| says how close a decision was (a flip is only legitimate when it is ~ float rounding) */
+	float trace_dE[64], trace_E[64];
 } dso_oracle_track_result;
 /* trackNewestCoarse, CoarseTracker.cpp:551-747. settings: huber 9, cutoff 20, affine modes 1e12/1e8 (settings.cpp) */
 void dso_oracle_track_newest_coarse(dso_oracle_tracker*, const double* pose12_in, double aff_a_in, double aff_b_in,

@@ -21,7 +21,8 @@ class TrackResult(C.Structure):
                 ("aff_a", C.c_double), ("aff_b", C.c_double), ("lastResiduals", C.c_double * 5),
                 ("lastFlowIndicators", C.c_double * 3), ("n_passes", C.c_int), ("pass_level", C.c_int * 8),
                 ("pass_rmse", C.c_double * 8), ("n_iterations", C.c_int), ("n_evals", C.c_int),
-                ("trace_len", C.c_int), ("trace", C.c_ubyte * 256), ("point_evals", C.c_double)]
+                ("trace_len", C.c_int), ("trace", C.c_ubyte * 256), ("point_evals", C.c_double),
+                ("trace_dE", C.c_float * 64), ("trace_E", C.c_float * 64)]
 
 
 def build(force=False):

@@ -635,6 +635,11 @@ extern "C" void dso_oracle_track_newest_coarse(dso_oracle_tracker* T, const doub
 			double resNew[6];
 			calcRes(T, lvl, refToNew_new, a_new, b_new, setting_coarseCutoffTH * levelCutoffRepeat, resNew);
 			bool accept = (resNew[0] / resNew[1]) < (resOld[0] / resOld[1]);   // :669
+			if (out->trace_len < 64)
+			{
+				out->trace_dE[out->trace_len] = (float)(resNew[0] * resOld[1] - resOld[0] * resNew[1]);
+				out->trace_E[out->trace_len] = (float)(resOld[0] * resNew[1]);
+			}
 			if (out->trace_len < 256) out->trace[out->trace_len++] = accept ? 1 : 0;
 			out->n_iterations++;
 

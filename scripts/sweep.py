@@ -70,7 +70,8 @@ def run(w, h, npts, nF, levels):
     ro = trk.track(ident, a0, b0, levels - 1)
     cpu_k2 = (time.perf_counter() - t1) * 1e3
     rg = ctx.track_batched(0, nF + 1, ident, a0, b0, levels - 1)[0]
-    ms = ev_time(stream, lambda: ctx.track_batched_async(0, nF + 1, ident, a0, b0, levels - 1), 10)
+    tstream = torch.cuda.ExternalStream(ctx.tracker_stream(0), device=dev)
+    ms = ev_time(tstream, lambda: ctx.track_kernel_only(0, nF + 1, 1, levels - 1), 10)     # poses of the call above
     same = list(ro.trace[:ro.trace_len]) == list(rg.trace[:rg.trace_len])
     perr = float(np.abs(np.array(ro.pose) - np.array(rg.pose)).max())
     gb = rg.point_evals * bench.POINT_BYTES
@@ -94,7 +95,8 @@ def run(w, h, npts, nF, levels):
     cpu_ba = (time.perf_counter() - t1) * 1e3
     errA = float(np.abs(st["H_A"] - Ao["H"]).max() / np.abs(Ao["H"]).max())
     errS = float(np.abs(st["H_sc"] - So["H"]).max() / np.abs(So["H"]).max())
-    ms = ev_time(stream, lambda: ctx.ba_step(), 5)
+    bstream = torch.cuda.ExternalStream(ctx.ba_stream, device=dev)
+    ms = ev_time(bstream, lambda: ctx.ba_step(), 5)
     out["BA"] = {"ms": ms, "residuals": int(W.nR), "active": int(st["resInA"]), "algorithmic_MB": W.nR * 850 / 1e6,
                  "GBps": W.nR * 850 / ms / 1e6, "cpu_mt6_ms": cpu_ba, "relerr_HA": errA, "relerr_Hsc": errS}
     ctx.close()
@@ -115,8 +117,11 @@ def batch31():
     P = np.stack([syn.pose12(x) for x in hyps])
     a, b = wl["affs"][3]
     res = ctx.track_batched(0, 4, P, a, b, levels - 1)
-    ms31 = ev_time(stream, lambda: ctx.track_batched_async(0, 4, P, a, b, levels - 1), 10)
-    ms1 = ev_time(stream, lambda: ctx.track_batched_async(0, 4, P[0], a, b, levels - 1), 10)
+    tstream = torch.cuda.ExternalStream(ctx.tracker_stream(0), device=dev)
+    ctx.track_batched(0, 4, P, a, b, levels - 1)
+    ms31 = ev_time(tstream, lambda: ctx.track_kernel_only(0, 4, 31, levels - 1), 10)
+    ctx.track_batched(0, 4, P[0], a, b, levels - 1)
+    ms1 = ev_time(tstream, lambda: ctx.track_kernel_only(0, 4, 1, levels - 1), 10)
     trk = wl["oracle_tracker"]
     pyr = O.make_images(wl["frames"][3][0], levels)
     trk.set_new_frame([x.reshape(-1) for x in pyr[0]], 1.0)

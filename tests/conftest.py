@@ -34,3 +34,10 @@ def window_small(pkg):
 @pytest.fixture(scope="session")
 def window_vga(pkg):
     return pkg.synthetic.make_window(seed=0)
+
+
+@pytest.fixture(scope="session")
+def window_large(pkg):
+    """one BASELINE configs[3] size under the driver-run tests: 1280x1024, ~18 k active points (level-0 cloud ~55 k points,
+    which selects the multi-cluster tracker path), 4 key frames, ~54 k residuals"""
+    return pkg.synthetic.make_window(seed=0, w=1280, h=1024, nF=4, n_points=18000, kf_step_t=0.04, kf_step_deg=1.0)

@@ -30,9 +30,11 @@ def _check_system(Hg, bg, Ho, bo, tol=1e-4):
     assert np.abs(bg - bo).max() <= tol * np.abs(bo).max()
 
 
-@pytest.mark.parametrize("which", ["small", "vga"])
-def test_ba_pipeline_parity(pkg, oracle, window_small, window_vga, which):
-    W = window_small if which == "small" else window_vga
+@pytest.mark.parametrize("which", ["small", "vga", "large"])
+def test_ba_pipeline_parity(pkg, oracle, request, which):
+    """small: 320x240 / 4 key frames / 500 points; vga: BASELINE configs[1]; large: one configs[3] size (1280x1024, ~18 k
+    points, ~54 k residuals)"""
+    W = request.getfixturevalue("window_" + which)
     B, ctx = _setup(pkg, oracle, W)
     lo = B.linearize()
     lg = ctx.ba_linearize()
@@ -106,20 +108,31 @@ def test_ba_input_validation(pkg, oracle, window_small):
     ctx.close()
 
 
-def test_ba_set_frames_matches_oracle_glue(pkg, oracle, window_small):
-    """host-side FrameFramePrecalc::set / setAdjointsF inside the library vs the oracle's restatement"""
-    W = window_small
+@pytest.mark.parametrize("which", ["small", "vga"])
+def test_ba_set_frames_matches_oracle_glue(pkg, oracle, window_small, window_vga, which):
+    """FrameHessian::setState + FrameFramePrecalc::set (HessianBlocks.h:183-199, HessianBlocks.cpp:213-250) +
+    EnergyFunctional::setAdjointsF / setDeltaF (EnergyFunctional.cpp:47-114, 178-205) inside the library vs the oracle
+    (itself bit-identical to the reference build, test_oracle_vs_reference.py::test_ba_linearize_accumulate): every
+    float / double of the glue bit for bit, and therefore the same linearisation and system as the set_glue path.
+    This is the path bench.py and host/dso_b200_host.h (setPrecalcValues) use."""
+    W = window_small if which == "small" else window_vga
     B, ctx = _setup(pkg, oracle, W)
     g = B.glue()
     out = ctx.ba_set_frames(W, want_out=True)
-    assert np.allclose(out["precalc"], g["precalc"], rtol=2e-6, atol=1e-7)
-    assert np.allclose(out["adHost"], g["adHost"], rtol=1e-12, atol=1e-12)
-    assert np.allclose(out["adTarget"], g["adTarget"], rtol=1e-12, atol=1e-12)
-    # and the pipeline driven by it gives the same system
+    assert np.array_equal(out["precalc"].view(np.uint32), np.ascontiguousarray(g["precalc"]).reshape(-1, 28).view(np.uint32))
+    assert np.array_equal(out["adHost"].reshape(-1).view(np.uint64), np.ascontiguousarray(g["adHost"]).reshape(-1).view(np.uint64))
+    assert np.array_equal(out["adTarget"].reshape(-1).view(np.uint64), np.ascontiguousarray(g["adTarget"]).reshape(-1).view(np.uint64))
+    # and the pipeline driven by it: states / energies / Jacobians bit-exact, the system within the H, b bar
+    lo, lg = B.linearize(), ctx.ba_linearize()
+    assert np.array_equal(lo["newState"], lg["newState"])
+    ok = lo["newState"] != 1
+    assert np.array_equal(lo["J"][ok].view(np.uint32), lg["J"][ok].view(np.uint32))
+    assert np.array_equal(lo["newEnergy"].view(np.uint32), lg["newEnergy"].view(np.uint32))
     st = ctx.ba_step()
     B.linearize(); B.apply_res()
-    Ao = B.accumulate_A(False)
-    assert rel_err_matrix(st["H_A"], Ao["H"]).max() <= 1e-3     # precalc floats may differ in the last bit -> a few state ties
+    Ao, So = B.accumulate_A(False), B.accumulate_SC(False)
+    _check_system(st["H_A"], st["b_A"], Ao["H"], Ao["b"])
+    _check_system(st["H_sc"], st["b_sc"], So["H"], So["b"])
     ctx.close()
 
 

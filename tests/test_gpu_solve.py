@@ -21,9 +21,10 @@ def _np_solve(HF, bF):
     return sv * np.linalg.solve(sv[:, None] * HF * sv[None, :], sv * bF)
 
 
-@pytest.mark.parametrize("iteration,with_lin", [(0, False), (3, False), (3, True)])
-def test_solve_parity(pkg, oracle, window_small, iteration, with_lin):
-    W = window_small
+@pytest.mark.parametrize("which,iteration,with_lin", [("small", 0, False), ("small", 3, False), ("small", 3, True),
+                                                      ("vga", 0, False), ("vga", 3, True)])
+def test_solve_parity(pkg, oracle, request, which, iteration, with_lin):
+    W = request.getfixturevalue("window_" + which)
     B, ctx = _setup(pkg, oracle, W)
     inp = _solve_inputs(W)
     B.linearize(); ctx.ba_linearize()
