@@ -81,6 +81,7 @@ SIGNATURES = {
                                        C.c_float, C.c_int, C.POINTER(TrackOpts), C.POINTER(TrackResult)]),
     "dso_b200_track_phase_cycles": (C.c_int, [vp, C.c_int, vp]),
     "dso_b200_track_set_tuning": (C.c_int, [vp, C.c_int, C.c_int, C.c_int]),
+    "dso_b200_debug_lm_bench": (C.c_int, [vp, C.c_int, vp]),
     "dso_b200_track_last_shape": (C.c_int, [vp, i32p]),
     "dso_b200_track_replay_abort": (C.c_int, [C.POINTER(TrackResult), f64p, f64p]),
     "dso_b200_track_hostloop": (C.c_int, [vp, C.c_int, C.c_int, f64p, C.c_double, C.c_double, C.c_float, C.c_int, vp,
@@ -366,6 +367,11 @@ class Context:
         out = np.zeros(14, dtype=np.int64)
         self._check(self.L.dso_b200_track_phase_cycles(self.h, int(enable), out.ctypes.data if read else None))
         return out
+
+    def debug_lm_bench(self, iters=1000):
+        out = np.zeros(7, dtype=np.int64)
+        self._check(self.L.dso_b200_debug_lm_bench(self.h, iters, out.ctypes.data))
+        return out / iters
 
     def track_set_tuning(self, threads=0, cluster=0, nclusters=0):
         self._check(self.L.dso_b200_track_set_tuning(self.h, threads, cluster, nclusters))

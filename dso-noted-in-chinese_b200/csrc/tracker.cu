@@ -97,11 +97,24 @@ __device__ __forceinline__ void proj3(const float* M, float x, float y, const fl
 	}
 }
 
-// One reference point of calcRes (CoarseTracker.cpp:402-486) + its calcGSSSE contribution (:313-334).
-template <bool DEBUG>
-__device__ __forceinline__ void eval_point(const float4 pc, int i, const EvalParams& P, const float4* __restrict__ img,
-                                           float* acc, unsigned char* status, float* warped)
+// One reference point of calcRes (CoarseTracker.cpp:402-486) + its calcGSSSE contribution (:313-334), in two stages so that
+// a thread can have the texel gathers of several points in flight before it consumes the first one:
+//   eval_issue   warp, flow indicators, bounds test, interpolation weights, the four 16-byte texel loads
+//   eval_finish  bilinear sample, residual, Huber weight, cut-off, Jacobian and the 44 weighted products
+struct PtIssue
 {
+	float4 p00, p10, p01, p11;
+	float w00, w01, w10, w11;
+	float u, v, new_idepth, refColor;
+	int i;
+	bool live;
+};
+
+template <bool DEBUG>
+__device__ __forceinline__ void eval_issue(const float4 pc, int i, const EvalParams& P, const float4* __restrict__ img,
+                                           float* acc, unsigned char* status, PtIssue& q)
+{
+	q.live = false; q.i = i;
 	const float id = pc.z, x = pc.x, y = pc.y;
 	float pt[3];
 	proj3(P.RKi, x, y, P.t, id, 1.f, pt);                // :408
@@ -113,13 +126,13 @@ __device__ __forceinline__ void eval_point(const float4 pc, int i, const EvalPar
 
 	if (P.lvl0 && (i & 31) == 0)                         // :416-447 flow indicators
 	{
-		float q[3];
-		proj3(P.Ki, x, y, P.t, id, 1.f, q);
-		float KuT = fadd(fmul(P.fx, fdiv(q[0], q[2])), P.cx), KvT = fadd(fmul(P.fy, fdiv(q[1], q[2])), P.cy);
-		proj3(P.Ki, x, y, P.t, id, -1.f, q);
-		float KuT2 = fadd(fmul(P.fx, fdiv(q[0], q[2])), P.cx), KvT2 = fadd(fmul(P.fy, fdiv(q[1], q[2])), P.cy);
-		proj3(P.RKi, x, y, P.t, id, -1.f, q);
-		float Ku3 = fadd(fmul(P.fx, fdiv(q[0], q[2])), P.cx), Kv3 = fadd(fmul(P.fy, fdiv(q[1], q[2])), P.cy);
+		float t[3];
+		proj3(P.Ki, x, y, P.t, id, 1.f, t);
+		float KuT = fadd(fmul(P.fx, fdiv(t[0], t[2])), P.cx), KvT = fadd(fmul(P.fy, fdiv(t[1], t[2])), P.cy);
+		proj3(P.Ki, x, y, P.t, id, -1.f, t);
+		float KuT2 = fadd(fmul(P.fx, fdiv(t[0], t[2])), P.cx), KvT2 = fadd(fmul(P.fy, fdiv(t[1], t[2])), P.cy);
+		proj3(P.RKi, x, y, P.t, id, -1.f, t);
+		float Ku3 = fadd(fmul(P.fx, fdiv(t[0], t[2])), P.cx), Kv3 = fadd(fmul(P.fy, fdiv(t[1], t[2])), P.cy);
 		float a0 = fsub(KuT, x), a1 = fsub(KvT, y), b0 = fsub(KuT2, x), b1 = fsub(KvT2, y);
 		float c0 = fsub(Ku, x), c1 = fsub(Kv, y), d0 = fsub(Ku3, x), d1 = fsub(Kv3, y);
 		acc[S_FLOW_T] += fadd(fmul(a0, a0), fmul(a1, a1));
@@ -136,15 +149,23 @@ __device__ __forceinline__ void eval_point(const float4 pc, int i, const EvalPar
 	const int ix = (int)Ku, iy = (int)Kv;
 	const float dx = fsub(Ku, (float)ix), dy = fsub(Kv, (float)iy);
 	const float dxdy = fmul(dx, dy);
-	const float w11 = dxdy, w01 = fsub(dy, dxdy), w10 = fsub(dx, dxdy);
-	const float w00 = fadd(fsub(fsub(1.f, dx), dy), dxdy);
+	q.w11 = dxdy; q.w01 = fsub(dy, dxdy); q.w10 = fsub(dx, dxdy);
+	q.w00 = fadd(fsub(fsub(1.f, dx), dy), dxdy);
 	const float4* bp = img + ix + iy * P.wl;
-	const float4 p00 = __ldg(bp), p10 = __ldg(bp + 1), p01 = __ldg(bp + P.wl), p11 = __ldg(bp + 1 + P.wl);
-	const float h0 = fadd(fadd(fadd(fmul(w11, p11.x), fmul(w01, p01.x)), fmul(w10, p10.x)), fmul(w00, p00.x));
-	const float h1 = fadd(fadd(fadd(fmul(w11, p11.y), fmul(w01, p01.y)), fmul(w10, p10.y)), fmul(w00, p00.y));
-	const float h2 = fadd(fadd(fadd(fmul(w11, p11.z), fmul(w01, p01.z)), fmul(w10, p10.z)), fmul(w00, p00.z));
+	q.p00 = __ldg(bp); q.p10 = __ldg(bp + 1); q.p01 = __ldg(bp + P.wl); q.p11 = __ldg(bp + 1 + P.wl);
+	q.u = u; q.v = v; q.new_idepth = new_idepth; q.refColor = pc.w;
+	q.live = true;
+}
+
+template <bool DEBUG>
+__device__ __forceinline__ void eval_finish(const PtIssue& q, const EvalParams& P, float* acc, unsigned char* status, float* warped)
+{
+	if (!q.live) return;
+	const float h0 = fadd(fadd(fadd(fmul(q.w11, q.p11.x), fmul(q.w01, q.p01.x)), fmul(q.w10, q.p10.x)), fmul(q.w00, q.p00.x));
+	const float h1 = fadd(fadd(fadd(fmul(q.w11, q.p11.y), fmul(q.w01, q.p01.y)), fmul(q.w10, q.p10.y)), fmul(q.w00, q.p00.y));
+	const float h2 = fadd(fadd(fadd(fmul(q.w11, q.p11.z), fmul(q.w01, q.p01.z)), fmul(q.w10, q.p10.z)), fmul(q.w00, q.p00.z));
 	if (!isfinite(h0)) return;                           // :456
-	const float refColor = pc.w;
+	const float u = q.u, v = q.v, new_idepth = q.new_idepth, refColor = q.refColor;
 	const float residual = fsub(h0, fadd(fmul(P.affLL0, refColor), P.affLL1));   // :458
 	const float ar = fabsf(residual);
 	const float hw = ar < P.huberTH ? 1.f : fdiv(P.huberTH, ar);                  // :459
@@ -154,7 +175,7 @@ __device__ __forceinline__ void eval_point(const float4 pc, int i, const EvalPar
 		acc[S_E] += P.maxEnergy;
 		acc[S_NTERMS] += 1.f;
 		acc[S_NSAT] += 1.f;
-		if (DEBUG) status[i] = 1;
+		if (DEBUG) status[q.i] = 1;
 		return;
 	}
 	acc[S_E] += fmul(fmul(fmul(hw, residual), residual), fsub(2.f, hw));   // :473
@@ -162,8 +183,8 @@ __device__ __forceinline__ void eval_point(const float4 pc, int i, const EvalPar
 	acc[S_NWARP] += 1.f;
 	if (DEBUG)
 	{
-		status[i] = 2;
-		float* wp = warped + 8 * (size_t)i;
+		status[q.i] = 2;
+		float* wp = warped + 8 * (size_t)q.i;
 		wp[0] = new_idepth; wp[1] = u; wp[2] = v; wp[3] = h1; wp[4] = h2; wp[5] = residual; wp[6] = hw; wp[7] = refColor;
 	}
 	// calcGSSSE :313-334
@@ -188,6 +209,15 @@ __device__ __forceinline__ void eval_point(const float4 pc, int i, const EvalPar
 	}
 #pragma unroll
 	for (int r = 0; r < 8; r++) { acc[k] = fmaf(fmul(J[r], hw), J[8], acc[k]); k++; }
+}
+
+template <bool DEBUG>
+__device__ __forceinline__ void eval_point(const float4 pc, int i, const EvalParams& P, const float4* __restrict__ img,
+                                           float* acc, unsigned char* status, float* warped)
+{
+	PtIssue q;
+	eval_issue<DEBUG>(pc, i, P, img, acc, status, q);
+	eval_finish<DEBUG>(q, P, acc, status, warped);
 }
 
 // Fixed-order CTA reduction of S_COUNT per-thread sums: xor-butterfly inside each warp, then the
@@ -463,337 +493,386 @@ struct TrackIn
 	double minRes[5];
 };
 
-// LM state of one hypothesis, in shared memory.  The serial dependency chain of trackNewestCoarse
-// (solve -> exp -> warp -> reduce -> accept?) is the latency floor of this kernel, so the step between
-// two evaluations is executed by one warp: per-lane rows / pose entries in registers, uniform scalar
-// work replicated in every lane (no divergent sections), shuffles instead of shared-memory round trips.
-struct LMS
+// LM state of one hypothesis.  The serial dependency chain of trackNewestCoarse (solve -> exp -> warp -> reduce ->
+// accept?) is the latency floor of this kernel, so the step between two evaluations is executed by one warp and its state
+// lives in that warp's registers across iterations.  One warp issues in order, so the instruction count matters as much as
+// the dependent chains: the 8x9 system [H | -b] is spread over 24 lanes -- lane i + 8g (row i = lane & 7, group g = 0..2)
+// holds the three entries of row i in columns g, g+3, g+6 (column 8 is the right-hand side) -- lanes 0..11 hold the
+// entries of the current and the proposed pose, every scalar is replicated in all lanes.  What the other warps need (the
+// next EvalParams, the level, the done flag) and the two small vectors every lane reads with its own indices (the
+// increment, the current pose) go through shared memory.
+struct LMR
 {
-	double H[64], b[8];
-	double cur[12], nw[12];                       // R (row-major 9) then t
+	double m[3];                                  // accepted system (scaled as CoarseTracker.cpp:338-353, without the common 1/n)
+	double pe_cur, pe_new;                        // pose entry `lane` (R row-major 0..8, t 9..11) of refToNew_current / _new
 	double a_cur, b_cur, a_new, b_new;
-	double resOldE, resOldN, resOldFlowT, resOldFlowRT, resOldFlowN;   // flow sums kept raw
-	double incnorm;                 // squared norm of the last increment
-	double minRes[5];
-	float lambda, levelCutoffRepeat;
+	double incnorm2;                              // squared norm of the last increment
+	float oldE, oldN, oldFT, oldFRT, oldFN;       // raw float sums of the accepted state (resOld)
+	float lambda, rep;                            // rep = levelCutoffRepeat
 	int lvl, iteration, phase, haveRepeated, done;
+	int n_evals, n_iter, trace_len, n_passes;
+	double point_evals;
+};
+// per-lane constants of the LM warp
+struct LMC
+{
+	int i, g;                                     // row, column group (lanes 24..31 mirror group 0)
+	double si;                                    // SCALE of parameter i
+	int off[3];                                   // offsets into the evaluation sums of this lane's three entries
+	double scl[3];                                // their scale factors: SCALE_i * SCALE_c, -SCALE_i for the right-hand side
+	bool diag[3];                                 // entry s is H_ii
+	bool fixable[3];                              // entry lies in row / column 6 or 7 (fixed-affine modes)
+	int xa, xb, xc;                               // pose lanes: rows r, r+1, r+2 (cyclic) -> indices into the increment's rotation part
+	int pa, pb, pc;                               // and into the current pose (column c of those rows)
+	bool tl;                                      // translation lane (9..11)
+};
+struct LMShared
+{
+	double x[8];                                  // scaled increment of the last solve
+	double cur[12];                               // refToNew_current
 };
 
+__device__ __forceinline__ void lm_constants(int lane, LMC& K)
+{
+	const float sc[8] = { SCALE_XI_ROT, SCALE_XI_ROT, SCALE_XI_ROT, SCALE_XI_TRANS, SCALE_XI_TRANS, SCALE_XI_TRANS, SCALE_A, SCALE_B };
+	K.i = lane & 7;
+	K.g = (lane >> 3) == 3 ? 0 : (lane >> 3);
+	float si = 0.f;
+#pragma unroll
+	for (int q = 0; q < 8; q++) if (q == K.i) si = sc[q];
+	K.si = (double)si;
+#pragma unroll
+	for (int t = 0; t < 3; t++)
+	{
+		const int c = K.g + 3 * t;
+		if (c < 8)
+		{
+			const int a = K.i < c ? K.i : c, b = K.i < c ? c : K.i;
+			K.off[t] = S_ACC + a * 8 - ((a * (a - 1)) >> 1) + (b - a);
+			float scc = 0.f;
+#pragma unroll
+			for (int q = 0; q < 8; q++) if (q == c) scc = sc[q];
+			K.scl[t] = (double)si * (double)scc;
+		}
+		else { K.off[t] = S_ACC + 36 + K.i; K.scl[t] = -(double)si; }
+		K.diag[t] = (c == K.i);
+		K.fixable[t] = (K.i >= 6) || (c == 6 || c == 7);
+	}
+	const int r = (lane < 9) ? lane / 3 : (lane < 12 ? lane - 9 : 0);
+	const int c = (lane < 9) ? lane - 3 * r : 3;
+	const int r1 = (r + 1) % 3, r2 = (r + 2) % 3;
+	K.xa = 3 + r; K.xb = 3 + r1; K.xc = 3 + r2;
+	K.pa = c < 3 ? 3 * r + c : 9 + r; K.pb = c < 3 ? 3 * r1 + c : 9 + r1; K.pc = c < 3 ? 3 * r2 + c : 9 + r2;
+	K.tl = (lane >= 9 && lane < 12);
+}
+
 __device__ __forceinline__ double shfl_d(double v, int src) { return __shfl_sync(0xffffffffu, v, src); }
-// reciprocal to ~1e-15 relative: float seed + two Newton steps (no IEEE division on the critical path)
+// reciprocal to ~1e-15 relative: hardware seed (MUFU.RCP64H, ~20 bits) + two Newton steps; the operand is a pivot of an
+// SPD system (normal range), non-finite results are caught by the isfinite test of the increment
 __device__ __forceinline__ double fast_rcp(double x)
 {
-	double r = (double)__frcp_rn((float)x);
-	r = r * fma(-x, r, 2.0);
-	r = r * fma(-x, r, 2.0);
+	double r;
+	asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
+	r = fma(fma(-x, r, 1.0), r, r);
+	r = fma(fma(-x, r, 1.0), r, r);
 	return r;
 }
 __device__ __forceinline__ float scale_of(int i)
 {
 	return i < 3 ? SCALE_XI_ROT : (i < 6 ? SCALE_XI_TRANS : (i == 6 ? SCALE_A : SCALE_B));
 }
-
-// SE3 exponential coefficients A = sin(t)/t, B = (1-cos t)/t^2, C = (t - sin t)/t^3 as series in t^2
-// (|t| < 0.5 for any LM increment; truncation error < 1e-16), falling back to sincos otherwise.
-__device__ __forceinline__ void exp_coeffs(double th2, double& A, double& B, double& C)
+// c0 + c1 t + ... + c7 t^7 by Estrin's scheme: dependent depth 3 FMAs after t^2, t^4 instead of 7
+__device__ __forceinline__ double estrin8(double t, double t2, double t4, double c0, double c1, double c2, double c3,
+                                          double c4, double c5, double c6, double c7)
 {
-	if (th2 < 0.25)
-	{
-		A = 1.0 + th2 * (-1.0 / 6 + th2 * (1.0 / 120 + th2 * (-1.0 / 5040 + th2 * (1.0 / 362880 + th2 * (-1.0 / 39916800 + th2 * (1.0 / 6227020800.0 + th2 * (-1.0 / 1307674368000.0)))))));
-		B = 0.5 + th2 * (-1.0 / 24 + th2 * (1.0 / 720 + th2 * (-1.0 / 40320 + th2 * (1.0 / 3628800 + th2 * (-1.0 / 479001600 + th2 * (1.0 / 87178291200.0 + th2 * (-1.0 / 20922789888000.0)))))));
-		C = 1.0 / 6 + th2 * (-1.0 / 120 + th2 * (1.0 / 5040 + th2 * (-1.0 / 362880 + th2 * (1.0 / 39916800 + th2 * (-1.0 / 6227020800.0 + th2 * (1.0 / 1307674368000.0 + th2 * (-1.0 / 355687428096000.0)))))));
-	}
-	else
-	{
-		const double th = sqrt(th2);
-		double s, c;
-		sincos(th, &s, &c);
-		A = s / th; B = (1.0 - c) / th2; C = (th - s) / (th2 * th);
-	}
+	const double p01 = fma(c1, t, c0), p23 = fma(c3, t, c2), p45 = fma(c5, t, c4), p67 = fma(c7, t, c6);
+	const double p03 = fma(p23, t2, p01), p47 = fma(p67, t2, p45);
+	return fma(p47, t4, p03);
 }
-
-// exp(x) for the relative affine gain: |x| is ~1e-2 in tracking, where a degree-11 Taylor series is accurate to
-// < 1e-19 and much shorter than the general routine; anything larger goes through exp().
-__device__ __forceinline__ double exp_small(double x)
+// SE3 exponential coefficients A = sin(t)/t, B = (1-cos t)/t^2, C = (t - sin t)/t^3 as series in t^2 = th2, valid for
+// th2 < 0.25 (truncation error < 1e-16; any LM increment is far below); branch-free so that the three chains interleave
+__device__ __forceinline__ void exp_coeffs_series(double th2, double& A, double& B, double& C)
 {
-	if (fabs(x) < 0.125)
-	{
-		double p = 1.0 / 39916800.0;
-		p = fma(p, x, 1.0 / 3628800.0); p = fma(p, x, 1.0 / 362880.0); p = fma(p, x, 1.0 / 40320.0); p = fma(p, x, 1.0 / 5040.0);
-		p = fma(p, x, 1.0 / 720.0); p = fma(p, x, 1.0 / 120.0); p = fma(p, x, 1.0 / 24.0); p = fma(p, x, 1.0 / 6.0);
-		p = fma(p, x, 0.5); p = fma(p, x, 1.0); p = fma(p, x, 1.0);
-		return p;
-	}
-	return exp(x);
+	const double t2 = th2 * th2, t4 = t2 * t2;
+	A = estrin8(th2, t2, t4, 1.0, -1.0 / 6, 1.0 / 120, -1.0 / 5040, 1.0 / 362880, -1.0 / 39916800, 1.0 / 6227020800.0, -1.0 / 1307674368000.0);
+	B = estrin8(th2, t2, t4, 0.5, -1.0 / 24, 1.0 / 720, -1.0 / 40320, 1.0 / 3628800, -1.0 / 479001600, 1.0 / 87178291200.0, -1.0 / 20922789888000.0);
+	C = estrin8(th2, t2, t4, 1.0 / 6, -1.0 / 120, 1.0 / 5040, -1.0 / 362880, 1.0 / 39916800, -1.0 / 6227020800.0, 1.0 / 1307674368000.0, -1.0 / 355687428096000.0);
 }
-// AffLight::fromToVecExposure (NumType.h:176-189) for the tracker's (reference, new frame) pair
+// exp(x) for the relative affine gain, |x| < 0.125 (it is ~1e-2 in tracking): degree-11 Taylor series (error < 1e-19)
+__device__ __forceinline__ double exp_series(double x)
+{
+	const double x2 = x * x, x4 = x2 * x2, x8 = x4 * x4;
+	const double lo = estrin8(x, x2, x4, 1.0, 1.0, 0.5, 1.0 / 6, 1.0 / 24, 1.0 / 120, 1.0 / 720, 1.0 / 5040);
+	const double p89 = fma(1.0 / 362880, x, 1.0 / 40320), p1011 = fma(1.0 / 39916800, x, 1.0 / 3628800);
+	return fma(fma(p1011, x2, p89), x8, lo);
+}
+// AffLight::fromToVecExposure (NumType.h:176-189) for the tracker's (reference, new frame) pair, general (slow) form
 __device__ __forceinline__ void aff_ref_to_new(const TrackLevels& TL, double a_req, double b_req, double& a, double& b)
 {
-	if (TL.ref_exposure == 1.f && TL.new_exposure == 1.f) a = exp_small(a_req - TL.ref_a);    // e*1/1 == e exactly
-	else { double bb; aff_from_to(TL.ref_exposure, TL.new_exposure, TL.ref_a, TL.ref_b, a_req, b_req, a, bb); }
+	double bb;
+	aff_from_to(TL.ref_exposure, TL.new_exposure, TL.ref_a, TL.ref_b, a_req, b_req, a, bb);
 	b = b_req - a * TL.ref_b;
 }
 
-// One step of the trackNewestCoarse state machine (CoarseTracker.cpp:584-722), executed by warp 0 of
-// every CTA of the cluster on identical inputs (so all CTAs take identical decisions, no broadcast).
-// Consumes the sums of the evaluation just finished, leaves either S.done or the next EvalParams in P.
-__device__ __forceinline__ void lm_step_warp(LMS& S, const float* s_tot, const TrackLevels& TL, const dso_b200_track_opts& opt,
-                                             dso_b200_track_result* out, EvalParams& P, int n_points, int lane, long long* lmt)
+// CoarseTracker.cpp:375-378 + :385 for the state to evaluate next, written into the shared EvalParams by warp 0 with one
+// store per lane: lanes 0..8 one entry of R*K^-1 each, lanes 9..11 the translation, lanes 12/13 the affine pair; the level-
+// and cut-off-dependent scalars only when they change.  pe = this lane's entry (R row-major 0..8, t 9..11) of the pose.
+__device__ __forceinline__ void lm_write_params(EvalParams& P, const TrackLevels& TL, const dso_b200_track_opts& opt, int lane, int lvl,
+                                                double pe, double affA, double affB, float rep, bool level_changed, bool cutoff_changed)
 {
-	long long q0 = lmt ? clock64() : 0;
-	const int i = lane & 7;
-	// ---- sums -> this lane's row of the scaled H, b (:338-353) and the Vec6 (:511-519) ----
-	const int nwarp = (int)s_tot[S_NWARP];
-	const float invn = fdiv(1.0f, (float)((nwarp + 3) & ~3));
-	const double si = (double)invn * (double)scale_of(i);
-	double hn[8];
-#pragma unroll
-	for (int j = 0; j < 8; j++)
+	static_assert(offsetof(EvalParams, t) == 9 * sizeof(float) && offsetof(EvalParams, affLL0) == 21 * sizeof(float) &&
+	              offsetof(EvalParams, affLL1) == 22 * sizeof(float), "EvalParams layout");
+	const float pef = (float)pe;
+	const int r = (lane < 9) ? lane / 3 : 0, c = (lane < 9) ? lane - 3 * r : 0;
+	const float k0 = TL.Ki[lvl][c], k1 = TL.Ki[lvl][3 + c], k2 = TL.Ki[lvl][6 + c];
+	const float R0 = __shfl_sync(0xffffffffu, pef, 3 * r), R1 = __shfl_sync(0xffffffffu, pef, 3 * r + 1), R2 = __shfl_sync(0xffffffffu, pef, 3 * r + 2);
+	const float rk = dot3e(R0, k0, R1, k1, R2, k2);
+	const float val = lane < 9 ? rk : (lane < 12 ? pef : (lane == 12 ? (float)affA : (float)affB));
+	if (lane < 14) reinterpret_cast<float*>(&P)[lane < 12 ? lane : lane + 9] = val;
+	if (level_changed || cutoff_changed)
 	{
-		const int a = i < j ? i : j, b = i < j ? j : i;
-		const int idx = a * 8 - ((a * (a - 1)) >> 1) + (b - a);
-		hn[j] = (double)s_tot[S_ACC + idx] * si * (double)scale_of(j);
-	}
-	const double bn = (double)s_tot[S_ACC + 36 + i] * si;
-	const double newE = (double)s_tot[S_E], newN = (double)s_tot[S_NTERMS];
-	// flow indicators are only read when a level finishes: keep the raw sums, divide there (:514-516)
-	const double newFlowT = (double)s_tot[S_FLOW_T], newFlowRT = (double)s_tot[S_FLOW_RT];
-	const double newFlowN = (double)s_tot[S_FLOW_N];
-
-	if (lmt) { long long q = clock64(); lmt[4] += q - q0; q0 = q; }
-	// uniform copies of the scalar state
-	int lvl = S.lvl, phase = S.phase, iteration = S.iteration;
-	float lambda = S.lambda, rep = S.levelCutoffRepeat;
-	const float rep_in = rep;
-	double a_cur = S.a_cur, b_cur = S.b_cur;
-	bool take = false, use_new = false, level_done = false, propose = false;
-
-	if (phase == 0)
-	{
-		const double newSat = (double)fdiv(s_tot[S_NSAT], s_tot[S_NTERMS]);     // :517
-		if (newSat > 0.6 && rep < 50) rep *= 2;                                // :586-593: same state, larger cut-off
-		else { take = true; lambda = 0.01f; iteration = 0; phase = 1; level_done = (0 >= opt.maxIterations[lvl]); propose = !level_done; }
-	}
-	else
-	{
-		// :669  (E'/n' < E/n) evaluated as E'*n < E*n' (n, n' >= 0; equal up to a 1-ulp tie of the two quotients,
-		// and false like the reference's NaN comparison when a count is 0) -- keeps two FP64 divisions off the chain
-		const double acc_l = newE * S.resOldN, acc_r = S.resOldE * newN;
-		const bool accept = acc_l < acc_r;
-		if (accept)
+		if (lane < 9 && level_changed) P.Ki[lane] = TL.Ki[lvl][lane];
+		if (lane == 13)
 		{
-			take = true;
-			a_cur = S.a_new; b_cur = S.b_new;
-			if (lane < 12) S.cur[lane] = S.nw[lane];
-			lambda *= 0.5f;
-		}
-		else { lambda *= 4; if (lambda < 0.001f) lambda = 0.001f; }
-		iteration++;
-		level_done = (!(S.incnorm > 1e-6) || iteration >= opt.maxIterations[lvl]);   // :700 (|inc| > 1e-3 on the squared norm), :613
-		propose = !level_done;
-		if (lane == 0)
-		{
-			if (out->trace_len < DSO_B200_TRACE_MARGINS) { out->trace_dE[out->trace_len] = (float)(acc_l - acc_r); out->trace_E[out->trace_len] = (float)acc_r; }
-			if (out->trace_len < 256) out->trace[out->trace_len++] = accept ? 1 : 0;
-			out->n_iterations++;
-		}
-	}
-	if (lmt) { long long q = clock64(); lmt[5] += q - q0; q0 = q; }
-	double resOldE = S.resOldE, resOldN = S.resOldN, resOldFlowT = S.resOldFlowT, resOldFlowRT = S.resOldFlowRT, resOldFlowN = S.resOldFlowN;
-	if (take)
-	{
-		resOldE = newE; resOldN = newN; resOldFlowT = newFlowT; resOldFlowRT = newFlowRT; resOldFlowN = newFlowN;
-		if (lane < 8)
-		{
-#pragma unroll
-			for (int j = 0; j < 8; j++) S.H[i * 8 + j] = hn[j];
-			S.b[i] = bn;
-		}
-	}
-	__syncwarp();
-
-	bool done = false;
-	if (level_done)
-	{
-		// :708-722 (+ :727-746 when the finest level is finished)
-		const float rmse = sqrtf((float)(resOldE / resOldN));
-		const bool abort = (double)rmse > 1.5 * S.minRes[lvl];
-		int next = lvl - 1;
-		int haveRepeated = S.haveRepeated;
-		if (rep > 1 && !haveRepeated) { next = lvl; haveRepeated = 1; }
-		if (lane == 0)
-		{
-			out->lastResiduals[lvl] = rmse;
-			out->lastFlowIndicators[0] = resOldFlowT / (resOldFlowN + 0.1); out->lastFlowIndicators[1] = 0;
-			out->lastFlowIndicators[2] = resOldFlowRT / (resOldFlowN + 0.1);
-			if (out->n_passes < DSO_B200_MAX_PASSES) { out->pass_level[out->n_passes] = lvl; out->pass_rmse[out->n_passes] = rmse; out->n_passes++; }
-			S.haveRepeated = haveRepeated;
-			if (abort) { out->ok = 0; out->reserved = lvl; }
-			else if (next < 0)
-			{
-				for (int k = 0; k < 12; k++) out->pose[k] = S.cur[k];
-				out->aff_a = a_cur; out->aff_b = b_cur;
-				int ok = 1;
-				if ((opt.affineOptModeA != 0 && (fabsf((float)a_cur) > 1.2f)) || (opt.affineOptModeB != 0 && (fabsf((float)b_cur) > 200.f))) ok = 0;
-				else
-				{
-					double ra, rb;
-					aff_from_to(TL.ref_exposure, TL.new_exposure, TL.ref_a, TL.ref_b, a_cur, b_cur, ra, rb);
-					if ((opt.affineOptModeA == 0 && (fabsf(logf((float)ra)) > 1.5f)) || (opt.affineOptModeB == 0 && (fabsf((float)rb) > 200.f))) ok = 0;
-				}
-				out->ok = ok;
-				if (ok)                                                            // :743-744
-				{
-					if (opt.affineOptModeA < 0) out->aff_a = 0;
-					if (opt.affineOptModeB < 0) out->aff_b = 0;
-				}
-			}
-		}
-		done = abort || next < 0;
-		lvl = next; phase = 0; rep = 1; iteration = 0;                         // :584 of the next level pass
-	}
-
-	if (lmt) { long long q = clock64(); lmt[0] += q - q0; q0 = q; }
-	double a_req = a_cur, b_req = b_cur, affA = 1.0, affB = 0.0;
-	double pe = (lane < 12) ? S.cur[lane] : 0.0;       // this lane's pose entry of the state to evaluate next
-	double incnorm = S.incnorm;
-	if (propose)
-	{
-		// ---- :613-665: damped solve, one lane per row.  H + lambda*diag(H) is SPD, so no pivoting is needed
-		// (Eigen's pivoted LDLT gives the same solution up to rounding).  Division-free Gauss-Jordan: every step
-		// is row_i <- g*row_i - f*row_k for all i != k with (g, f) = (piv, row_i[k]) * 2^-exponent(piv): a power-of-
-		// two rescale (exact) replaces the reciprocal chain on the critical path and bounds the growth to 2x per
-		// step; the eight reciprocals are taken once at the end, in parallel.  Row scaling does not change the
-		// solution. ----
-		const double damp = (double)(1.f + lambda);
-		double row[8], x[8];
-#pragma unroll
-		for (int j = 0; j < 8; j++) row[j] = take ? hn[j] : S.H[i * 8 + j];
-		double rhs = -(take ? bn : S.b[i]);
-#pragma unroll
-		for (int j = 0; j < 8; j++) if (j == i) row[j] *= damp;
-		// :621-643 fixed-affine variants: the reference solves the 6x6 / 7x7 system without the fixed parameter's
-		// row and column; replacing that row and column by the identity's (and its right-hand side by 0) yields
-		// the same increments for the free parameters and exactly 0 for the fixed one.
-		const bool fixA = opt.affineOptModeA < 0, fixB = opt.affineOptModeB < 0;
-		if (fixA || fixB)
-		{
-			const bool fi = (i == 6 && fixA) || (i == 7 && fixB);
-#pragma unroll
-			for (int j = 0; j < 8; j++)
-				if (fi || (j == 6 && fixA) || (j == 7 && fixB)) row[j] = (i == j) ? 1.0 : 0.0;
-			if (fi) rhs = 0.0;
-		}
-#pragma unroll
-		for (int k = 0; k < 8; k++)
-		{
-			const double piv = shfl_d(row[k], k);
-			const double prhs = shfl_d(rhs, k);
-			const bool self = (i == k);
-			const double sc = __hiloint2double((2046 - ((__double2hiint(piv) >> 20) & 0x7ff)) << 20, 0);   // 2^-exponent(piv)
-			const double f = self ? 0.0 : row[k] * sc;
-			const double g = self ? 1.0 : piv * sc;
-#pragma unroll
-			for (int j = 0; j < 8; j++)
-			{
-				if (j <= k) continue;                       // columns <= k of the other rows become 0 / are never read again
-				const double pj = shfl_d(row[j], k);
-				row[j] = fma(-f, pj, g * row[j]);
-			}
-			rhs = fma(-f, prhs, g * rhs);
-#pragma unroll
-			for (int j = 0; j < 8; j++) if (j < k) row[j] = g * row[j];   // keep the already-diagonalised part consistent (only row[i], j == i, matters)
-			if (!self) row[k] = 0.0;
-		}
-		// row i is now (0,..,d_i,..,0 | rhs_i): x_i = rhs_i / d_i
-		double di = 0.0;
-#pragma unroll
-		for (int j = 0; j < 8; j++) if (j == i) di = row[j];
-		const double xi = rhs * fast_rcp(di);
-#pragma unroll
-		for (int k = 0; k < 8; k++) x[k] = shfl_d(xi, k);
-		if (lmt) { long long q = clock64(); lmt[1] += q - q0; q0 = q; }
-		float extrapFac = 1.f;
-		if (lambda < 0.001f) extrapFac = sqrtf(sqrtf(0.001f / lambda));       // :650
-		double nrm = 0, sum = 0, is[8];
-#pragma unroll
-		for (int k = 0; k < 8; k++) { x[k] *= (double)extrapFac; nrm = fma(x[k], x[k], nrm); is[k] = x[k] * (double)scale_of(k); sum += is[k]; }
-		if (!isfinite(sum))                                                    // :659
-		{
-#pragma unroll
-			for (int k = 0; k < 8; k++) is[k] = 0;
-		}
-		incnorm = nrm;
-		a_req = a_cur + is[6]; b_req = b_cur + is[7];
-		aff_ref_to_new(TL, a_req, b_req, affA, affB);   // independent of the pose chain below: overlaps with it
-		// exp(inc) (Sophus SE3::exp): R = I + A W + B W^2, t = (I + B W + C W^2) u
-		const double wx = is[3], wy = is[4], wz = is[5];
-		const double th2 = wx * wx + wy * wy + wz * wz;
-		double A, B, C;
-		exp_coeffs(th2, A, B, C);
-		// this lane's row r of exp(inc) (R lanes: r = lane/3, t lanes: r = lane-9)
-		const int r = (lane < 9) ? lane / 3 : (lane < 12 ? lane - 9 : 0);
-		const int c = (lane < 9) ? lane - 3 * r : 0;
-		const double wr = r == 0 ? wx : (r == 1 ? wy : wz);
-		// W row r = (0,-wz,wy),(wz,0,-wx),(-wy,wx,0); W^2 row r = wr*w - th2*e_r
-		const double W0 = r == 0 ? 0.0 : (r == 1 ? wz : -wy);
-		const double W1 = r == 0 ? -wz : (r == 1 ? 0.0 : wx);
-		const double W2 = r == 0 ? wy : (r == 1 ? -wx : 0.0);
-		const double Q0 = wr * wx - (r == 0 ? th2 : 0.0), Q1 = wr * wy - (r == 1 ? th2 : 0.0), Q2 = wr * wz - (r == 2 ? th2 : 0.0);
-		const double e0 = (r == 0 ? 1.0 : 0.0) + A * W0 + B * Q0;
-		const double e1 = (r == 1 ? 1.0 : 0.0) + A * W1 + B * Q1;
-		const double e2 = (r == 2 ? 1.0 : 0.0) + A * W2 + B * Q2;
-		const double v0 = (r == 0 ? 1.0 : 0.0) + B * W0 + C * Q0;
-		const double v1 = (r == 1 ? 1.0 : 0.0) + B * W1 + C * Q1;
-		const double v2 = (r == 2 ? 1.0 : 0.0) + B * W2 + C * Q2;
-		const double et = v0 * is[0] + v1 * is[1] + v2 * is[2];
-		// refToNew_new = exp(inc) * refToNew_current (:661): entry (r,c) = sum_k e[r][k] cur[k][c]; t_r = sum_k e[r][k] t_k + et_r
-		const int src0 = (lane < 9) ? c : 9, src1 = (lane < 9) ? 3 + c : 10, src2 = (lane < 9) ? 6 + c : 11;
-		const double c0 = shfl_d(pe, src0), c1 = shfl_d(pe, src1), c2 = shfl_d(pe, src2);
-		double ne = e0 * c0 + e1 * c1 + e2 * c2;
-		if (lane >= 9) ne += et;
-		pe = ne;
-		if (lane < 12) S.nw[lane] = ne;
-		use_new = true;
-	}
-
-	if (lmt) { long long q = clock64(); lmt[2] += q - q0; q0 = q; }
-	// ---- CoarseTracker.cpp:375-378 + :385 for the state to evaluate next (skipped when done) ----
-	if (!done)
-	{
-		const int r = (lane < 9) ? lane / 3 : 0, c = (lane < 9) ? lane - 3 * r : 0;
-		const float R0 = (float)shfl_d(pe, 3 * r), R1 = (float)shfl_d(pe, 3 * r + 1), R2 = (float)shfl_d(pe, 3 * r + 2);
-		const float rk = dot3e(R0, TL.Ki[lvl][c], R1, TL.Ki[lvl][3 + c], R2, TL.Ki[lvl][6 + c]);
-		if (!use_new) aff_ref_to_new(TL, a_req, b_req, affA, affB);
-		const double a = affA, b = affB;
-		if (lane < 9) { P.RKi[lane] = rk; if (level_done) P.Ki[lane] = TL.Ki[lvl][lane]; }
-		else if (lane < 12) P.t[lane - 9] = (float)pe;
-		if (lane == 12) { P.affLL0 = (float)a; P.affLL1 = (float)b; }
-		if (lane == 13 && (level_done || rep != rep_in))
-		{
-			// level- and cut-off-dependent parameters only change at a level switch / cut-off doubling
 			const float cutoff = opt.coarseCutoffTH * rep;
 			P.cutoffTH = cutoff;
 			P.maxEnergy = fsub(fmul(fmul(2.0f, opt.huberTH), cutoff), fmul(opt.huberTH, opt.huberTH));
-			if (level_done)
+			if (level_changed)
 			{
 				P.fx = TL.fx[lvl]; P.fy = TL.fy[lvl]; P.cx = TL.cx[lvl]; P.cy = TL.cy[lvl];
 				P.wl = TL.w[lvl];
 				P.wl_m3 = (float)(TL.w[lvl] - 3); P.hl_m3 = (float)(TL.h[lvl] - 3);
 				P.n = TL.pc_n[lvl];
 				P.lvl0 = (lvl == 0);
+				P.huberTH = opt.huberTH;
+				P.b0 = (float)TL.ref_b;
 			}
 		}
 	}
-	if (lane == 0)
+}
+
+// Rare general cases of the LM step, redone with the plain formulas and kept out of line (the persistent kernel's
+// instruction footprint matters): rotation beyond the range of the series, exposure ratio != 1, affine gain far from 1.
+struct LMGeneral { double pe, affA, affB; };
+__device__ __noinline__ LMGeneral lm_general_case(const LMShared* SH, float ref_exposure, float new_exposure, double ref_a, double ref_b,
+                                                  bool propose, int lane, double a_req, double b_req, double pe_in)
+{
+	LMGeneral o;
+	o.pe = pe_in;
+	if (propose)
 	{
-		S.lvl = lvl; S.phase = phase; S.iteration = iteration; S.lambda = lambda; S.levelCutoffRepeat = rep;
-		S.a_cur = a_cur; S.b_cur = b_cur;
-		if (use_new) { S.a_new = a_req; S.b_new = b_req; S.incnorm = incnorm; }
-		S.resOldE = resOldE; S.resOldN = resOldN; S.resOldFlowT = resOldFlowT; S.resOldFlowRT = resOldFlowRT; S.resOldFlowN = resOldFlowN;
-		S.done = done ? 1 : 0;
-		out->n_evals++; out->point_evals += n_points;
+		double x[8];
+#pragma unroll
+		for (int k = 0; k < 8; k++) x[k] = SH->x[k];
+		Pose e, cur, nw;
+		se3_exp(x, e);
+#pragma unroll
+		for (int k = 0; k < 9; k++) cur.R[k] = SH->cur[k];
+#pragma unroll
+		for (int k = 0; k < 3; k++) cur.t[k] = SH->cur[9 + k];
+		pose_mul(e, cur, nw);
+#pragma unroll
+		for (int k = 0; k < 9; k++) if (lane == k) o.pe = nw.R[k];
+#pragma unroll
+		for (int k = 0; k < 3; k++) if (lane == 9 + k) o.pe = nw.t[k];
 	}
+	double bb;
+	aff_from_to(ref_exposure, new_exposure, ref_a, ref_b, a_req, b_req, o.affA, bb);
+	o.affB = b_req - o.affA * ref_b;
+	return o;
+}
+
+// One step of the trackNewestCoarse state machine (CoarseTracker.cpp:584-722), executed by warp 0 of every CTA of the
+// cluster on identical inputs (so all CTAs take identical decisions, no broadcast).  Consumes the sums of the evaluation
+// just finished (s_tot, shared memory), leaves either R.done or the next EvalParams in P.
+//
+// This is the serial section of the kernel (one warp, in-order issue), so it is written as straight-line code with few
+// instructions and short dependent chains: the new system entries are formed speculatively while the accept test is
+// evaluated; the elimination works on 24 lanes x 3 entries with the pivots rescaled by powers of two estimated beforehand
+// (nothing but shuffle -> multiply -> FMA per pivot on the chain); the series of the exponentials are evaluated by
+// Estrin's scheme; every lane picks "its" rows of the rotation by index instead of by selects; and the rare general cases
+// (large rotation, exposure ratio != 1, non-finite increment) are redone in a branch at the end.  Everything that is not
+// needed to start the next evaluation is either a fire-and-forget store (trace, margins) or postponed to the end of the
+// kernel (the per-pass RMSE with its FP64 division and square root, the flow indicators, the counters).
+template <int V = 0>
+__device__ __forceinline__ void lm_step_warp(LMR& R, const LMC& K, LMShared& SH, const float* s_tot, const TrackLevels& TL,
+                                             const dso_b200_track_opts& opt, dso_b200_track_result* out, float* s_passE, float* s_passN,
+                                             EvalParams& P, int* sCtl, int n_points, int lane, long long* lmt)
+{
+	long long q0 = lmt ? clock64() : 0;
+	const int i = K.i;
+	// ---- all loads of this step up front ----
+	const float newE = s_tot[S_E], newN = s_tot[S_NTERMS], newSatN = s_tot[S_NSAT];
+	const float nFT = s_tot[S_FLOW_T], nFRT = s_tot[S_FLOW_RT], nFN = s_tot[S_FLOW_N];
+	const float h0 = s_tot[K.off[0]], h1 = s_tot[K.off[1]], h2 = s_tot[K.off[2]];
+	R.n_evals++; R.point_evals += (double)n_points;
+	const float rep_in = R.rep;
+	const int lvl_in = R.lvl;
+	// speculative entries of the new system (:338-353).  The common factor 1/n of H and b is left out: the increment
+	// (H + lambda diag H)^-1 b does not depend on it and nothing else reads H or b.
+	const double n0 = (double)h0 * K.scl[0], n1 = (double)h1 * K.scl[1], n2 = (double)h2 * K.scl[2];
+
+	// ---- control ----
+	bool take, level_done, propose;
+	if (R.phase == 0)
+	{
+		const double newSat = (double)fdiv(newSatN, newN);                         // :517
+		const bool repeat = newSat > 0.6 && R.rep < 50;                           // :586-593: same state, larger cut-off
+		if (repeat) R.rep *= 2;
+		take = !repeat;
+		if (take) { R.lambda = 0.01f; R.iteration = 0; R.phase = 1; }
+		level_done = take && (0 >= opt.maxIterations[R.lvl]);
+		propose = take && !level_done;
+	}
+	else
+	{
+		// :669  (E'/n' < E/n) evaluated as E'*n < E*n' (n, n' >= 0; equal up to a 1-ulp tie of the two quotients,
+		// and false like the reference's NaN comparison when a count is 0) -- keeps two FP64 divisions off the chain
+		const double acc_l = (double)newE * (double)R.oldN, acc_r = (double)R.oldE * (double)newN;
+		const bool accept = acc_l < acc_r;
+		if (lane == 0)
+		{
+			if (R.trace_len < DSO_B200_TRACE_MARGINS) { out->trace_dE[R.trace_len] = (float)(acc_l - acc_r); out->trace_E[R.trace_len] = (float)acc_r; }
+			if (R.trace_len < 256) out->trace[R.trace_len] = accept ? 1 : 0;
+		}
+		if (R.trace_len < 256) R.trace_len++;
+		R.n_iter++;
+		take = accept;
+		if (accept)
+		{
+			R.a_cur = R.a_new; R.b_cur = R.b_new; R.pe_cur = R.pe_new;
+			if (lane < 12) SH.cur[lane] = R.pe_new;
+		}
+		const float l4 = fmaxf(R.lambda * 4, 0.001f);
+		R.lambda = accept ? R.lambda * 0.5f : l4;
+		R.iteration++;
+		level_done = (!(R.incnorm2 > 1e-6) || R.iteration >= opt.maxIterations[R.lvl]);   // :700 (|inc| > 1e-3 on the squared norm), :613
+		propose = !level_done;
+	}
+	if (lmt) { long long q = clock64(); lmt[5] += q - q0; q0 = q; }
+	R.m[0] = take ? n0 : R.m[0]; R.m[1] = take ? n1 : R.m[1]; R.m[2] = take ? n2 : R.m[2];
+	R.oldE = take ? newE : R.oldE; R.oldN = take ? newN : R.oldN;
+	R.oldFT = take ? nFT : R.oldFT; R.oldFRT = take ? nFRT : R.oldFRT; R.oldFN = take ? nFN : R.oldFN;   // divided when read (:514-516)
+	if (lmt) { long long q = clock64(); lmt[4] += q - q0; q0 = q; }
+
+	if (level_done)
+	{
+		// :708-722; the RMSE of this pass is computed from (E, n) at the end of the kernel
+		if (lane == 0 && R.n_passes < DSO_B200_MAX_PASSES) { out->pass_level[R.n_passes] = R.lvl; s_passE[R.n_passes] = R.oldE; s_passN[R.n_passes] = R.oldN; }
+		if (R.n_passes < DSO_B200_MAX_PASSES) R.n_passes++;
+		int next = R.lvl - 1;
+		if (R.rep > 1 && !R.haveRepeated) { next = R.lvl; R.haveRepeated = 1; }
+		R.done = next < 0 ? 1 : 0;
+		R.lvl = next; R.phase = 0; R.rep = 1; R.iteration = 0;                    // :584 of the next level pass
+	}
+	if (lmt) { long long q = clock64(); lmt[0] += q - q0; q0 = q; }
+
+	const bool unit_exposure = (TL.ref_exposure == 1.f && TL.new_exposure == 1.f);
+	double a_req = R.a_cur, b_req = R.b_cur;
+	double pe = R.pe_cur;                          // this lane's pose entry of the state to evaluate next
+	bool redo = !unit_exposure;                    // the general (slow) forms are needed
+	bool bad_inc = false;
+	if (propose)
+	{
+		// ---- :613-665: damped solve.  H + lambda*diag(H) is SPD, so no pivoting is needed (Eigen's pivoted LDLT gives the
+		// same solution up to rounding).  Division-free Gauss-Jordan on [H | -b]: step k is, for every row i != k and every
+		// column, M_i <- (piv*sc_k)*M_i - (M_ik*sc_k)*M_k, with sc_k a power of two (exact) close to 1/H_kk taken from
+		// the diagonal BEFORE the elimination (pivots of an SPD matrix only shrink, by less than the conditioning of the
+		// damped system), so that the magnitudes stay within a few hundred binades of where they started.  The pivot row
+		// itself takes the same code path with the multipliers (1/sc_k, 0), which leaves it unchanged exactly.  Row
+		// scaling does not change the solution; the reciprocal of the diagonal is taken once at the end. ----
+		const float extrapFac = (R.lambda < 0.001f) ? sqrtf(sqrtf(0.001f / R.lambda)) : 1.f;      // :650
+		const double damp = (double)(1.f + R.lambda);
+		double m0 = K.diag[0] ? R.m[0] * damp : R.m[0];
+		double m1 = K.diag[1] ? R.m[1] * damp : R.m[1];
+		double m2 = K.diag[2] ? R.m[2] * damp : R.m[2];
+		// :621-643 fixed-affine variants: the reference solves the 6x6 / 7x7 system without the fixed parameter's row and
+		// column; replacing that row and column by the identity's (and its right-hand side by 0) yields the same
+		// increments for the free parameters and exactly 0 for the fixed one.
+		const bool fixA = opt.affineOptModeA < 0, fixB = opt.affineOptModeB < 0;
+		if (fixA || fixB)
+		{
+			const bool fi = (i == 6 && fixA) || (i == 7 && fixB);
+			const int c0 = K.g, c1 = K.g + 3, c2 = K.g + 6;
+			if (fi || (c0 == 6 && fixA) || (c0 == 7 && fixB)) m0 = K.diag[0] ? 1.0 : 0.0;
+			if (fi || (c1 == 6 && fixA) || (c1 == 7 && fixB)) m1 = K.diag[1] ? 1.0 : 0.0;
+			if (fi || (c2 == 6 && fixA) || (c2 == 7 && fixB)) m2 = K.diag[2] ? 1.0 : 0.0;
+		}
+		// power-of-two scales from the diagonal: H_ii sits in lane i + 8*(i%3), entry i/3
+		const int i3 = i / 3, im3 = i - 3 * i3;
+		const double cand = i3 == 0 ? m0 : (i3 == 1 ? m1 : m2);
+		const int myexp = (__double2hiint(cand) >> 20) & 0x7ff;
+#pragma unroll
+		for (int k = 0; k < ((V & 32) ? 0 : 8); k++)
+		{
+			const int ek = __shfl_sync(0xffffffffu, myexp, k + 8 * (k % 3));
+			const double sc = __hiloint2double((2046 - ek) << 20, 0), isc = __hiloint2double(ek << 20, 0);
+			const bool self = (i == k);
+			// off the chain: everything that does not need the pivot row
+			const double mk = (k / 3 == 0) ? m0 : ((k / 3 == 1) ? m1 : m2);       // compile-time choice
+			const double fr = shfl_d(mk, i + 8 * (k % 3));                        // M_ik
+			const double f = self ? 0.0 : fr * sc;
+			const double t0 = m0 * sc, t1 = m1 * sc, t2 = m2 * sc;
+			// on the chain: the pivot row arrives, one multiply, one FMA
+			const double pivr = shfl_d(mk, k + 8 * (k % 3));
+			const double p0 = shfl_d(m0, k + 8 * K.g), p1 = shfl_d(m1, k + 8 * K.g), p2 = shfl_d(m2, k + 8 * K.g);
+			const double piv = self ? isc : pivr;
+			m0 = fma(-f, p0, piv * t0);
+			m1 = fma(-f, p1, piv * t1);
+			m2 = fma(-f, p2, piv * t2);
+		}
+		// row i is now (0,..,d_i,..,0 | rhs_i): x_i = rhs_i / d_i
+		const double dcand = i3 == 0 ? m0 : (i3 == 1 ? m1 : m2);
+		const double di = shfl_d(dcand, i + 8 * im3);
+		const double ri = shfl_d(m2, i + 16);
+		const double xi = ri * fast_rcp(di) * (double)extrapFac;             // entry i of the (extrapolated) increment, in every group
+		bad_inc = __any_sync(0xffffffffu, !isfinite(xi));                     // :659 (a non-finite entry makes the sum non-finite)
+		const double isi = bad_inc ? 0.0 : xi * K.si;                         // :652-659: scaled, zero if not finite
+		if (lane < 8) SH.x[lane] = isi;
+		double nn = xi * xi;                                                  // |inc|^2 for :700 (NaN ends the level, as there)
+		nn += shfl_d(nn, lane ^ 1); nn += shfl_d(nn, lane ^ 2); nn += shfl_d(nn, lane ^ 4);
+		R.incnorm2 = nn;
+		__syncwarp();
+		if (lmt) { long long q = clock64(); lmt[1] += q - q0; q0 = q; }
+		// every lane reads the entries it needs by index: the canonical rotation vector (for theta^2), "its" cyclic
+		// permutation of it and of the translation part, column c of the matching rows of the current pose
+		if (V & 16) { pe = xi; R.pe_new = xi; } else {
+		const double w3 = SH.x[3], w4 = SH.x[4], w5 = SH.x[5], x6 = SH.x[6], x7 = SH.x[7];
+		const double wa = SH.x[K.xa], wb = SH.x[K.xb], wc = SH.x[K.xc];
+		const double ua = SH.x[K.xa - 3], ub = SH.x[K.xb - 3], uc = SH.x[K.xc - 3];
+		const double pa = SH.cur[K.pa], pb = SH.cur[K.pb], pc = SH.cur[K.pc];
+		a_req = R.a_cur + x6; b_req = R.b_cur + x7;
+		// exp(inc) (Sophus SE3::exp): R = I + A W + B W^2, t = (I + B W + C W^2) u.  In the cyclic order (r, r+1, r+2) row r
+		// of W is (0, -w_{r+2}, w_{r+1}) and row r of W^2 is w_r w - theta^2 e_r
+		const double th2 = fma(w3, w3, fma(w4, w4, w5 * w5));
+		redo = redo || !(th2 < 0.25);
+		double A, B, C;
+		exp_coeffs_series(th2, A, B, C);
+		const double waa = fma(wa, wa, -th2), wab = wa * wb, wac = wa * wc;
+		const double ea = fma(B, waa, 1.0), eb = fma(B, wab, -(A * wc)), ec = fma(B, wac, A * wb);
+		const double va = fma(C, waa, 1.0), vb = fma(C, wab, -(B * wc)), vc = fma(C, wac, B * wb);
+		const double et = fma(va, ua, fma(vb, ub, vc * uc));
+		// refToNew_new = exp(inc) * refToNew_current (:661): entry (r,c) = sum_k e[r][k] cur[k][c]; t_r = sum_k e[r][k] t_k + et_r
+		const double ne = fma(ea, pa, fma(eb, pb, fma(ec, pc, K.tl ? et : 0.0)));
+		pe = ne;
+		R.pe_new = ne; R.a_new = a_req; R.b_new = b_req;
+		}
+	}
+	// affine pair of the state to evaluate (NumType.h:176-189 with unit exposures: a = exp(a_req - ref_a) exactly)
+	const double da = a_req - TL.ref_a;
+	redo = redo || !(fabs(da) < 0.125);
+	double affA = exp_series(da);
+	double affB = fma(-affA, TL.ref_b, b_req);
+	if (lmt) { long long q = clock64(); lmt[2] += q - q0; q0 = q; }
+	if (redo)
+	{
+		const LMGeneral gc = lm_general_case(&SH, TL.ref_exposure, TL.new_exposure, TL.ref_a, TL.ref_b, propose, lane, a_req, b_req, pe);
+		pe = gc.pe; affA = gc.affA; affB = gc.affB;
+		if (propose) R.pe_new = gc.pe;
+	}
+	if (V & 8) { if (lane < 12) reinterpret_cast<float*>(&P)[lane] = (float)(pe + affA + affB); }
+	else if (!R.done) lm_write_params(P, TL, opt, lane, R.lvl, pe, affA, affB, R.rep, level_done, R.rep != rep_in);
+	if (lane == 0) { sCtl[0] = R.done ? lvl_in : R.lvl; sCtl[1] = R.done; }
 	__syncwarp();
 	if (lmt) { long long q = clock64(); lmt[3] += q - q0; }
 }
@@ -847,17 +926,101 @@ __device__ __forceinline__ void warp_reduce_halving(float* v, int lane)
 	}
 }
 
-// phase_cycles (optional, debug): SM cycles spent by thread 0 of CTA 0 in [point evaluation, CTA
-// reduction, cluster exchange + barrier, LM step], number of evaluations, whole kernel cycles and ns.
-template <int NT>
+// Totals of one evaluation when a hypothesis is spread over NC clusters (large clouds): cluster totals go through global
+// memory and a monotonic arrival counter.  Executed by the LM warp of every CTA; kept out of line (rare path, and the
+// persistent kernel's instruction footprint matters).  s0 / s1: this lane's two cluster totals in, grid totals out.
+__device__ __noinline__ float2 mc_exchange(float s0, float s1, float* mc_part, unsigned int* mc_count, int hyp, int NC, int cidx,
+                                           unsigned rank, unsigned int mc_round, int lane)
+{
+	const bool second = lane < S_COUNT - 32;
+	float* mine = mc_part + ((size_t)(hyp * 2 + ((mc_round - 1) & 1)) * NC + cidx) * S_COUNT;
+	if (rank == 0) { __stcg(mine + lane, s0); if (second) __stcg(mine + 32 + lane, s1); }
+	__syncwarp();
+	if (lane == 0)
+	{
+		if (rank == 0) { __threadfence(); atomicAdd(mc_count + hyp, 1u); }
+		const unsigned int want = mc_round * (unsigned)NC;
+		// the grid is launched cooperatively (all clusters co-resident or the launch is refused), so this wait always
+		// ends; the time limit only turns a violated assumption into a launch failure instead of a hang
+		unsigned long long t0 = 0, spins = 0;
+		while (*((volatile unsigned int*)(mc_count + hyp)) < want)
+		{
+			if ((++spins & 0xfffu) == 0)
+			{
+				unsigned long long now;
+				asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+				if (!t0) t0 = now;
+				else if (now - t0 > 4000000000ull) __trap();
+			}
+		}
+		__threadfence();
+	}
+	__syncwarp();
+	const float* src = mc_part + (size_t)(hyp * 2 + ((mc_round - 1) & 1)) * NC * S_COUNT;
+	s0 = 0.f; s1 = 0.f;
+	for (int c0 = 0; c0 < NC; c0 += 8)                // clusters in index order, eight loads in flight
+	{
+		float t0v[8], t1v[8];
+#pragma unroll
+		for (int q = 0; q < 8; q++)
+		{
+			t0v[q] = (c0 + q < NC) ? __ldcg(src + (size_t)(c0 + q) * S_COUNT + lane) : 0.f;
+			t1v[q] = (second && c0 + q < NC) ? __ldcg(src + (size_t)(c0 + q) * S_COUNT + 32 + lane) : 0.f;
+		}
+#pragma unroll
+		for (int q = 0; q < 8; q++) if (c0 + q < NC) { s0 += t0v[q]; s1 += t1v[q]; }
+	}
+	return make_float2(s0, s1);
+}
+
+// What the LM loop postponed, at the end of the kernel: per-pass RMSE (:710), flow indicators (:711), :727-746
+__device__ __noinline__ void lm_finalize(dso_b200_track_result* res, const float* s_passE, const float* s_passN, int lane, int n_passes,
+                                         int n_iter, int n_evals, int trace_len, double point_evals, double pe_cur, double a_cur, double b_cur,
+                                         float oldFT, float oldFRT, float oldFN, float modeA, float modeB,
+                                         float ref_exposure, float new_exposure, double ref_a, double ref_b)
+{
+	if (lane < n_passes) res->pass_rmse[lane] = (double)sqrtf((float)((double)s_passE[lane] / (double)s_passN[lane]));
+	if (lane < 12) res->pose[lane] = pe_cur;
+	if (lane >= 16 && lane < 21) res->lastResiduals[lane - 16] = NAN;      // :563
+	__syncwarp();
+	if (lane == 0)
+	{
+		res->reserved = -1;
+		res->n_passes = n_passes; res->n_iterations = n_iter; res->n_evals = n_evals; res->trace_len = trace_len;
+		res->point_evals = point_evals;
+		for (int p = 0; p < n_passes; p++) res->lastResiduals[res->pass_level[p]] = res->pass_rmse[p];
+		res->lastFlowIndicators[0] = (double)oldFT / ((double)oldFN + 0.1); res->lastFlowIndicators[1] = 0;
+		res->lastFlowIndicators[2] = (double)oldFRT / ((double)oldFN + 0.1);
+		res->aff_a = a_cur; res->aff_b = b_cur;
+		int ok = 1;
+		if ((modeA != 0 && (fabsf((float)a_cur) > 1.2f)) || (modeB != 0 && (fabsf((float)b_cur) > 200.f))) ok = 0;
+		else
+		{
+			double ra, rb;
+			aff_from_to(ref_exposure, new_exposure, ref_a, ref_b, a_cur, b_cur, ra, rb);
+			if ((modeA == 0 && (fabsf(logf((float)ra)) > 1.5f)) || (modeB == 0 && (fabsf((float)rb) > 200.f))) ok = 0;
+		}
+		res->ok = ok;
+		if (ok)                                                            // :743-744
+		{
+			if (modeA < 0) res->aff_a = 0;
+			if (modeB < 0) res->aff_b = 0;
+		}
+	}
+}
+
+// K2b.  PROF = true compiles in the per-phase cycle counters (dso_b200_track_phase_cycles): SM cycles spent by thread 0 of
+// CTA 0 in [point evaluation, CTA reduction, cluster exchange + barrier, LM step], number of evaluations, whole kernel
+// cycles and ns, and the split of the LM step.  The production instantiation carries none of it.
+template <int NT, bool PROF>
 __global__ void __launch_bounds__(NT, 1)
 track_persistent_kernel(TrackLevels TL, dso_b200_track_opts opt, const TrackIn* __restrict__ in,
                         dso_b200_track_result* out, int coarsestLvl, int smem_pts_cap, long long* phase_cycles,
                         dso_b200_track_result* host_out, unsigned int* host_flags, unsigned int seq,
                         int NC, float* mc_part, unsigned int* mc_count)
 {
-	// NC > 1: one hypothesis is spread over NC clusters (large clouds): cluster totals go through global memory and a
-	// monotonic arrival counter; every CTA of the grid must be resident (the host caps NC by cudaOccupancyMaxActiveClusters)
+	// NC > 1: one hypothesis is spread over NC clusters (large clouds); every CTA of the grid must be resident
+	// (cooperative launch, see enqueue_track)
 	cg::cluster_group cluster = cg::this_cluster();
 	const unsigned CS = cluster.num_blocks();
 	const unsigned rank = cluster.block_rank();
@@ -867,47 +1030,45 @@ track_persistent_kernel(TrackLevels TL, dso_b200_track_opts opt, const TrackIn* 
 	const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 	long long tph[5] = { 0, 0, 0, 0, 0 };
 	long long tc0 = 0, tk0 = 0, tg0 = 0;
-	long long lmt[6] = { 0, 0, 0, 0, 0, 0 };   // LM step split: sums+control, solve, exp+pose, params+stores
-	if (phase_cycles) { tk0 = clock64(); asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tg0)); }
+	long long lmt[6] = { 0, 0, 0, 0, 0, 0 };   // LM step split: level, solve, exp+pose, params, sums->H, control
+	if (PROF) { tk0 = clock64(); asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tg0)); }
 
 	__shared__ EvalParams sP;
-	__shared__ LMS S;
+	__shared__ int sCtl[2];                               // level of the next evaluation, done flag
 	__shared__ float s_w[NT / 32][64];
 	__shared__ float xchg[2][MAX_CLUSTER][S_COUNT];
 	__shared__ __align__(8) unsigned long long xbar[2];   // one mbarrier per exchange buffer
-	__shared__ float s_tot[S_COUNT];
+	__shared__ float s_tot[64];
+	__shared__ float s_passE[DSO_B200_MAX_PASSES], s_passN[DSO_B200_MAX_PASSES];
+	__shared__ LMShared s_lm;
 	__shared__ dso_b200_track_result s_res;
 	extern __shared__ float4 s_pts[];
 
 	for (int i = tid; i < (int)(sizeof(dso_b200_track_result) / 4); i += NT) reinterpret_cast<unsigned int*>(&s_res)[i] = 0u;
-	__syncthreads();
+	LMR R;
+	LMC K;
 	if (warp == 0)
 	{
-		// the input block may live in mapped host memory: one coalesced read by 19 lanes, then shared memory
-		__shared__ TrackIn s_in;
+		lm_constants(lane, K);
+		// the input block may live in mapped host memory: one coalesced read by 19 lanes; the pose entries stay in the
+		// lanes that read them
 		static_assert(sizeof(TrackIn) == 19 * sizeof(double), "TrackIn layout");
-		if (lane < 19) reinterpret_cast<double*>(&s_in)[lane] = reinterpret_cast<const double*>(in + hyp)[lane];
-		__syncwarp();
-		if (lane == 0)
-		{
-			const TrackIn& I = s_in;
-			for (int i = 0; i < 12; i++) S.cur[i] = I.pose[i];
-			S.a_cur = I.aff_a; S.b_cur = I.aff_b; S.a_new = I.aff_a; S.b_new = I.aff_b;
-			for (int i = 0; i < 5; i++) S.minRes[i] = I.minRes[i];
-			S.haveRepeated = 0; S.done = 0; S.incnorm = 0; S.lambda = 0.01f;
-			S.lvl = coarsestLvl; S.phase = 0; S.levelCutoffRepeat = 1; S.iteration = 0;
-			S.resOldE = 0; S.resOldN = 1; S.resOldFlowT = 0; S.resOldFlowRT = 0; S.resOldFlowN = 0;
-			s_res.ok = 0; s_res.reserved = -1;
-			for (int i = 0; i < 12; i++) s_res.pose[i] = I.pose[i];
-			s_res.aff_a = I.aff_a; s_res.aff_b = I.aff_b;
-			for (int i = 0; i < 5; i++) s_res.lastResiduals[i] = NAN;        // :563
-			for (int i = 0; i < 3; i++) s_res.lastFlowIndicators[i] = 1000;  // :564
-			s_res.n_passes = 0; s_res.n_iterations = 0; s_res.n_evals = 0; s_res.trace_len = 0; s_res.point_evals = 0;
-			// CoarseTracker.cpp:375-385 for the very first evaluation (:584)
-			Pose p0; pose_from12(p0, I.pose);
-			make_eval_params(TL, coarsestLvl, p0, I.aff_a, I.aff_b, opt.coarseCutoffTH, opt.huberTH, sP);
-		}
-		__syncwarp();
+		const double vin = (lane < 19) ? reinterpret_cast<const double*>(in + hyp)[lane] : 0.0;
+		R.pe_cur = R.pe_new = vin;
+		if (lane < 12) s_lm.cur[lane] = vin;
+		if (lane < 8) s_lm.x[lane] = 0.0;
+		R.a_cur = R.a_new = shfl_d(vin, 12); R.b_cur = R.b_new = shfl_d(vin, 13);
+		R.m[0] = R.m[1] = R.m[2] = 0.0;
+		R.incnorm2 = 0.0;
+		R.oldE = 0.f; R.oldN = 1.f; R.oldFT = 0.f; R.oldFRT = 0.f; R.oldFN = 0.f;
+		R.lambda = 0.01f; R.rep = 1.f;
+		R.lvl = coarsestLvl; R.iteration = 0; R.phase = 0; R.haveRepeated = 0; R.done = 0;
+		R.n_evals = 0; R.n_iter = 0; R.trace_len = 0; R.n_passes = 0; R.point_evals = 0.0;
+		// CoarseTracker.cpp:375-385 for the very first evaluation (:584)
+		double affA, affB;
+		aff_ref_to_new(TL, R.a_cur, R.b_cur, affA, affB);
+		lm_write_params(sP, TL, opt, lane, coarsestLvl, R.pe_cur, affA, affB, 1.f, true, true);
+		if (lane == 0) { sCtl[0] = coarsestLvl; sCtl[1] = 0; }
 	}
 	if (tid == 0) { mbar_init(&xbar[0], 1); mbar_init(&xbar[1], 1); asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
 	__syncthreads();
@@ -917,7 +1078,7 @@ track_persistent_kernel(TrackLevels TL, dso_b200_track_opts opt, const TrackIn* 
 	int staged_lvl = -1;
 	while (true)
 	{
-		const int lvl = S.lvl;
+		const int lvl = sCtl[0];
 		const int n = TL.pc_n[lvl];
 		const int per = (n + CS * NC - 1) / (CS * NC);
 		const int beg = min((int)(cidx * CS + rank) * per, n), end = min(beg + per, n);
@@ -931,15 +1092,17 @@ track_persistent_kernel(TrackLevels TL, dso_b200_track_opts opt, const TrackIn* 
 		}
 		const EvalParams P = sP;
 		const float4* __restrict__ img = TL.img[lvl];
-		if (phase_cycles) { __syncthreads(); tc0 = clock64(); }
+		if (PROF) { __syncthreads(); tc0 = clock64(); }
 		float acc[64];
 #pragma unroll
 		for (int k = 0; k < 64; k++) acc[k] = 0.f;
-		if (use_smem)
-			for (int i = beg + tid; i < end; i += NT) eval_point<false>(s_pts[i - beg], i, P, img, acc, nullptr, nullptr);
-		else
-			for (int i = beg + tid; i < end; i += NT) eval_point<false>(__ldg(gp + i), i, P, img, acc, nullptr, nullptr);
-		if (phase_cycles) { __syncthreads(); long long t = clock64(); tph[0] += t - tc0; tc0 = t; }
+		for (int i = beg + tid; i < end; i += NT)      // one copy of the evaluation code (instruction footprint)
+		{
+			float4 pc;
+			if (use_smem) pc = s_pts[i - beg]; else pc = __ldg(gp + i);
+			eval_point<false>(pc, i, P, img, acc, nullptr, nullptr);
+		}
+		if (PROF) { __syncthreads(); long long t = clock64(); tph[0] += t - tc0; tc0 = t; }
 		warp_reduce_halving(acc, lane);
 		s_w[warp][2 * lane] = acc[0];
 		s_w[warp][2 * lane + 1] = acc[1];
@@ -953,71 +1116,50 @@ track_persistent_kernel(TrackLevels TL, dso_b200_track_opts opt, const TrackIn* 
 			for (unsigned r = 0; r < CS; r++) st_async_remote(&xchg[buf][rank][tid], &xbar[buf], r, s);
 		}
 		if (tid == 0) mbar_arrive_expect_tx(&xbar[buf], CS * S_COUNT * 4);   // this CTA expects CS partials of S_COUNT floats
-		if (phase_cycles) { long long t = clock64(); tph[1] += t - tc0; tc0 = t; }
-		mbar_wait(&xbar[buf], xphase[buf]);
-		xphase[buf] ^= 1u;
-		if (tid < S_COUNT)
+		if (PROF) { long long t = clock64(); tph[1] += t - tc0; tc0 = t; }
+		// only the LM warp needs the totals: the first 52 threads (two warps) add the ranks in index order and hand them
+		// over through a two-warp named barrier; everybody else goes straight to the barrier at the end of the iteration
+		if (warp < 2)
 		{
-			// ranks in index order; loads issued together (fixed trip count), adds in order
-			float v[MAX_CLUSTER];
-#pragma unroll
-			for (int r = 0; r < MAX_CLUSTER; r++) v[r] = (r < (int)CS) ? xchg[buf][r][tid] : 0.f;
-			float s = 0.f;
-#pragma unroll
-			for (int r = 0; r < MAX_CLUSTER; r++) s += v[r];
-			s_tot[tid] = s;
-			if (NC > 1 && rank == 0) __stcg(mc_part + ((size_t)(hyp * 2 + (mc_round & 1)) * NC + cidx) * S_COUNT + tid, s);
-		}
-		__syncthreads();
-		if (NC > 1)
-		{
-			mc_round++;
-			if (tid == 0)
-			{
-				if (rank == 0) { __threadfence(); atomicAdd(mc_count + hyp, 1u); }
-				const unsigned int want = mc_round * (unsigned)NC;
-				// the grid is launched cooperatively (all clusters co-resident or the launch is refused), so this wait
-				// always ends; the time limit only turns a violated assumption into a launch failure instead of a hang
-				unsigned long long t0 = 0, spins = 0;
-				while (*((volatile unsigned int*)(mc_count + hyp)) < want)
-				{
-					if ((++spins & 0xfffu) == 0)
-					{
-						unsigned long long now;
-						asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
-						if (!t0) t0 = now;
-						else if (now - t0 > 4000000000ull) __trap();
-					}
-				}
-				__threadfence();
-			}
-			__syncthreads();
+			mbar_wait(&xbar[buf], xphase[buf]);
 			if (tid < S_COUNT)
 			{
-				const float* src = mc_part + (size_t)(hyp * 2 + ((mc_round - 1) & 1)) * NC * S_COUNT + tid;
-				float sum = 0.f;
-				for (int c0 = 0; c0 < NC; c0 += 8)                // clusters in index order, eight loads in flight
-				{
-					float t[8];
+				float v[MAX_CLUSTER];                  // loads issued together (fixed trip count), adds in order
 #pragma unroll
-					for (int q = 0; q < 8; q++) t[q] = (c0 + q < NC) ? __ldcg(src + (size_t)(c0 + q) * S_COUNT) : 0.f;
+				for (int r = 0; r < MAX_CLUSTER; r++) v[r] = (r < (int)CS) ? xchg[buf][r][tid] : 0.f;
+				float sacc = 0.f;
 #pragma unroll
-					for (int q = 0; q < 8; q++) if (c0 + q < NC) sum += t[q];
-				}
-				s_tot[tid] = sum;
+				for (int r = 0; r < MAX_CLUSTER; r++) sacc += v[r];
+				s_tot[tid] = sacc;
 			}
-			__syncthreads();
+			asm volatile("bar.sync 1, 64;" ::: "memory");
 		}
-		if (phase_cycles) { long long t = clock64(); tph[2] += t - tc0; tc0 = t; }
-		if (warp == 0) lm_step_warp(S, s_tot, TL, opt, &s_res, sP, n, lane, phase_cycles ? lmt : nullptr);
-		__syncthreads();
-		if (phase_cycles) { long long t = clock64(); tph[3] += t - tc0; tph[4]++; }
-		if (S.done) break;
+		if (warp == 0)
+		{
+			if (NC > 1)
+			{
+				mc_round++;
+				const float2 g = mc_exchange(s_tot[lane], s_tot[32 + lane], mc_part, mc_count, hyp, NC, cidx, rank, mc_round, lane);
+				__syncwarp();
+				s_tot[lane] = g.x; s_tot[32 + lane] = g.y;
+				__syncwarp();
+			}
+			if (PROF) { long long t = clock64(); tph[2] += t - tc0; tc0 = t; }
+			lm_step_warp(R, K, s_lm, s_tot, TL, opt, &s_res, s_passE, s_passN, sP, sCtl, n, lane, PROF ? lmt : nullptr);
+			if (PROF) { long long t = clock64(); tph[3] += t - tc0; tph[4]++; }
+		}
+		xphase[buf] ^= 1u;
+		__syncthreads();           // the next EvalParams / level / done flag are in shared memory
+		if (sCtl[1]) break;
 		buf ^= 1;
 	}
 	cluster.sync();                // nobody leaves while a peer may still be writing into it
 	if (rank == 0 && cidx == 0)
 	{
+		if (warp == 0)
+			lm_finalize(&s_res, s_passE, s_passN, lane, R.n_passes, R.n_iter, R.n_evals, R.trace_len, R.point_evals, R.pe_cur, R.a_cur, R.b_cur,
+			            R.oldFT, R.oldFRT, R.oldFN, opt.affineOptModeA, opt.affineOptModeB, TL.ref_exposure, TL.new_exposure, TL.ref_a, TL.ref_b);
+		__syncthreads();
 		const int nwords = sizeof(dso_b200_track_result) / 4;
 		const unsigned int* src = reinterpret_cast<const unsigned int*>(&s_res);
 		unsigned int* dst = reinterpret_cast<unsigned int*>(out + hyp);
@@ -1033,7 +1175,7 @@ track_persistent_kernel(TrackLevels TL, dso_b200_track_opts opt, const TrackIn* 
 			if (tid == 0) { *reinterpret_cast<volatile unsigned int*>(host_flags + hyp) = seq; __threadfence_system(); }
 		}
 	}
-	if (phase_cycles && blockIdx.x == 0 && tid == 0)
+	if (PROF && blockIdx.x == 0 && tid == 0)
 	{
 		for (int k = 0; k < 5; k++) phase_cycles[k] = tph[k];
 		long long tg1; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tg1));
@@ -1041,6 +1183,85 @@ track_persistent_kernel(TrackLevels TL, dso_b200_track_opts opt, const TrackIn* 
 		phase_cycles[6] = tg1 - tg0;
 		for (int k = 0; k < 6; k++) phase_cycles[8 + k] = lmt[k];
 	}
+}
+
+static void mat33f_inverse(const float* m, float* out);
+// Timing harness for the LM step alone (debug): one warp runs lm_step_warp `iters` times on a fixed, well-conditioned
+// synthetic evaluation whose energy shrinks a little every time, so that every step is an accepted one with a new proposal.
+template <int V>
+__global__ void lm_step_bench_kernel(TrackLevels TL, dso_b200_track_opts opt, int iters, long long* cycles, double* sink)
+{
+	__shared__ EvalParams sP;
+	__shared__ int sCtl[2];
+	__shared__ float s_tot[64];
+	__shared__ float s_passE[DSO_B200_MAX_PASSES], s_passN[DSO_B200_MAX_PASSES];
+	__shared__ dso_b200_track_result s_res;
+	__shared__ LMShared s_lm;
+	const int lane = threadIdx.x;
+	LMC K;
+	lm_constants(lane, K);
+	for (int k = lane; k < 64; k += 32) s_tot[k] = 0.f;
+	__syncwarp();
+	if (lane == 0)
+	{
+		s_tot[S_E] = 5.0e5f; s_tot[S_NTERMS] = 4000.f; s_tot[S_NSAT] = 100.f; s_tot[S_NWARP] = 3900.f;
+		int k = S_ACC;
+		for (int r = 0; r < 8; r++) for (int c = r; c < 8; c++) s_tot[k++] = (r == c) ? 3.0e6f * (1 + r) : 1.0e4f * (r + c);
+		for (int r = 0; r < 8; r++) s_tot[k++] = 50.f * (r + 1);
+	}
+	__syncwarp();
+	LMR R;
+	R.pe_cur = R.pe_new = (lane == 0 || lane == 4 || lane == 8) ? 1.0 : 0.0;
+	if (lane < 12) s_lm.cur[lane] = R.pe_cur;
+	if (lane < 8) s_lm.x[lane] = 0.0;
+	R.a_cur = R.a_new = 0.0; R.b_cur = R.b_new = 0.0;
+	R.m[0] = R.m[1] = R.m[2] = 0.0;
+	R.incnorm2 = 1.0;
+	R.oldE = 6.0e5f; R.oldN = 4000.f; R.oldFT = 0.f; R.oldFRT = 0.f; R.oldFN = 0.f;
+	R.lambda = 0.01f; R.rep = 1.f;
+	R.lvl = 0; R.iteration = 0; R.phase = 1; R.haveRepeated = 0; R.done = 0;
+	R.n_evals = 0; R.n_iter = 0; R.trace_len = 0; R.n_passes = 0; R.point_evals = 0.0;
+	opt.maxIterations[0] = 1 << 30;
+	long long lmt[6] = { 0, 0, 0, 0, 0, 0 };
+	long long t0 = 0;
+	for (int it = 0; it < iters + 8; it++)
+	{
+		if (it == 8) { t0 = clock64(); for (int k = 0; k < 6; k++) lmt[k] = 0; }
+		lm_step_warp<V>(R, K, s_lm, s_tot, TL, opt, &s_res, s_passE, s_passN, sP, sCtl, 1000, lane, (V & 64) ? nullptr : lmt);
+		R.trace_len = 0; R.lambda = 0.01f; R.incnorm2 = 1.0; R.iteration = 0;
+		if (lane == 0) s_tot[S_E] *= 0.999f;
+		__syncwarp();
+	}
+	const long long t1 = clock64();
+	if (lane == 0) { cycles[0] = t1 - t0; for (int k = 0; k < 6; k++) cycles[1 + k] = lmt[k]; }
+	sink[lane] = R.pe_new + R.a_new + sP.RKi[lane % 9];
+}
+
+extern "C" int dso_b200_debug_lm_bench(dso_b200_ctx* ctx, int iters, long long* cycles7)
+{
+	ARG_CHECK(ctx && cycles7 && iters > 0, "bad arguments");
+	CK(cudaSetDevice(ctx->device));
+	TrackLevels TL;
+	memset(&TL, 0, sizeof(TL));
+	TL.levels = 1; TL.w[0] = 640; TL.h[0] = 480; TL.fx[0] = 500; TL.fy[0] = 500; TL.cx[0] = 320; TL.cy[0] = 240;
+	const float K[9] = { 500, 0, 320, 0, 500, 240, 0, 0, 1 };
+	mat33f_inverse(K, TL.Ki[0]);
+	TL.ref_exposure = 1.f; TL.new_exposure = 1.f;
+	dso_b200_track_opts o; dso_b200_track_opts_default(&o);
+	long long* d_c = nullptr; double* d_s = nullptr;
+	CK(cudaMalloc(&d_c, 64)); CK(cudaMalloc(&d_s, 32 * sizeof(double)));
+	const int variant = getenv("DSO_B200_LM_VARIANT") ? atoi(getenv("DSO_B200_LM_VARIANT")) : 0;
+	if (variant == 64) lm_step_bench_kernel<64><<<1, 32, 0, ctx->stream>>>(TL, o, iters, d_c, d_s);
+	else if (variant == 72) lm_step_bench_kernel<72><<<1, 32, 0, ctx->stream>>>(TL, o, iters, d_c, d_s);
+	else if (variant == 80) lm_step_bench_kernel<80><<<1, 32, 0, ctx->stream>>>(TL, o, iters, d_c, d_s);
+	else if (variant == 96) lm_step_bench_kernel<96><<<1, 32, 0, ctx->stream>>>(TL, o, iters, d_c, d_s);
+	else if (variant == 120) lm_step_bench_kernel<120><<<1, 32, 0, ctx->stream>>>(TL, o, iters, d_c, d_s);
+	else lm_step_bench_kernel<0><<<1, 32, 0, ctx->stream>>>(TL, o, iters, d_c, d_s);
+	CK(cudaGetLastError());
+	CK(cudaStreamSynchronize(ctx->stream));
+	CK(cudaMemcpy(cycles7, d_c, 56, cudaMemcpyDeviceToHost));
+	cudaFree(d_c); cudaFree(d_s);
+	return 0;
 }
 
 // ---- host side ------------------------------------------------------------------------------------
@@ -1347,12 +1568,14 @@ static int enqueue_track(dso_b200_ctx* ctx, int trk, int frame_slot, int nHyp, c
 	per = (max_n + cs - 1) / cs;
 	cap = (int)std::min<size_t>((size_t)per, smem_cap_bytes / sizeof(float4));
 	dyn = (size_t)cap * sizeof(float4);
-	void (*kern)(TrackLevels, dso_b200_track_opts, const TrackIn*, dso_b200_track_result*, int, int, long long*,
-	             dso_b200_track_result*, unsigned int*, unsigned int, int, float*, unsigned int*) =
-		nt == 128 ? track_persistent_kernel<128> : (nt == 512 ? track_persistent_kernel<512> : (nt == 384 ? track_persistent_kernel<384> : track_persistent_kernel<256>));
-	if (nt != 128 && nt != 512 && nt != 384) nt = 256;
+	if (nt != 128) nt = 256;
+	const bool prof = ctx->d_phase_cycles != nullptr;
+	typedef void (*kern_t)(TrackLevels, dso_b200_track_opts, const TrackIn*, dso_b200_track_result*, int, int, long long*,
+	                       dso_b200_track_result*, unsigned int*, unsigned int, int, float*, unsigned int*);
+	kern_t kern = nt == 128 ? (prof ? (kern_t)track_persistent_kernel<128, true> : (kern_t)track_persistent_kernel<128, false>)
+	                        : (prof ? (kern_t)track_persistent_kernel<256, true> : (kern_t)track_persistent_kernel<256, false>);
 	static bool attr_set[64][4] = { { false } };
-	const int ki = nt == 128 ? 0 : (nt == 256 ? 1 : (nt == 512 ? 2 : 3));
+	const int ki = (nt == 128 ? 0 : 2) + (prof ? 1 : 0);
 	if (!attr_set[ctx->device & 63][ki])
 	{
 		CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_cap_bytes));
@@ -1438,7 +1661,7 @@ extern "C" int dso_b200_track_batched_async(dso_b200_ctx* ctx, int trk, int fram
 extern "C" int dso_b200_track_set_tuning(dso_b200_ctx* ctx, int threads, int cluster_size, int n_clusters)
 {
 	ARG_CHECK(ctx, "null context");
-	ARG_CHECK(threads == 0 || threads == 128 || threads == 256 || threads == 384 || threads == 512, "threads must be 0, 128, 256, 384 or 512");
+	ARG_CHECK(threads == 0 || threads == 128 || threads == 256, "threads must be 0, 128 or 256");
 	ARG_CHECK(cluster_size == 0 || cluster_size == 1 || cluster_size == 2 || cluster_size == 4 || cluster_size == 8 || cluster_size == 16, "cluster_size must be 0 or a power of two <= 16");
 	ARG_CHECK(n_clusters >= 0 && n_clusters <= DSO_B200_TRACK_MAX_NC, "n_clusters out of range");
 	ctx->tune_threads = threads; ctx->tune_cluster = cluster_size; ctx->tune_nclusters = n_clusters;

@@ -224,8 +224,8 @@ int dso_b200_track_frame(dso_b200_ctx* ctx, int trk, int frame_slot, const float
  * cycles7 (12 values, may be NULL) receives them; [8..11] split the LM step into sums+control, solve,
  * exponential+pose update, parameter build. */
 int dso_b200_track_phase_cycles(dso_b200_ctx* ctx, int enable, long long* cycles7);
-/* Launch shape of the persistent tracker (no counterpart in the reference; tests and tuning): threads per CTA (128, 256,
- * 384, 512), CTAs per cluster (power of two <= 16) and, for single-hypothesis calls, the number of clusters the cloud is
+/* Launch shape of the persistent tracker (no counterpart in the reference; tests and tuning): threads per CTA (128, 256),
+ * CTAs per cluster (power of two <= 16) and, for single-hypothesis calls, the number of clusters the cloud is
  * spread over (1 = never split; by default clouds of >= 32768 points per level are split).  0 = automatic.  Results
  * change only through the order of the float sums. */
 int dso_b200_track_set_tuning(dso_b200_ctx* ctx, int threads, int cluster_size, int n_clusters);
@@ -233,6 +233,10 @@ int dso_b200_track_set_tuning(dso_b200_ctx* ctx, int threads, int cluster_size, 
  * more than one cluster per hypothesis the launch is cooperative (all clusters co-resident, guaranteed by the driver); if the
  * device cannot host them at once -- e.g. another context occupies SMs -- the call falls back to one cluster. */
 int dso_b200_track_last_shape(dso_b200_ctx* ctx, int* shape3);
+/* Profiling aid (no counterpart in the reference): runs the tracker's LM step (decision, damped 8x8 solve, SE3 update,
+ * next EvalParams) `iters` times in one warp on a synthetic accepted evaluation; cycles7 = { total SM cycles, then the split
+ * level, solve, exp+pose, params, sums->H, control }. */
+int dso_b200_debug_lm_bench(dso_b200_ctx* ctx, int iters, long long* cycles7);
 /* Applies CoarseTracker.cpp:713 to a finished result: returns 1 if trackNewestCoarse would have
  * returned true for this minResForAbort, 0 if it would have aborted (lastResiduals5_out then holds
  * what CoarseTracker::lastResiduals would contain at the abort). */
