@@ -130,9 +130,16 @@ class quiet_stdout:
         os.close(self.saved)
 
 
-# dram__bytes_read.sum + dram__bytes_write.sum of track_persistent_kernel per launch from the committed ncu --set full
-# capture (VGA, 1 hypothesis): well below the algorithmic gather bytes, i.e. L2/L1 serve the re-reads
-K2B_DRAM_BYTES_PER_LAUNCH = 1.30e6
+def k2b_traffic():
+    """dram__bytes_read.sum + dram__bytes_write.sum of track_persistent_kernel per launch, read from the committed summary of
+    the `ncu --set full` capture (profiles/r02_tracker_traffic.json, written by scripts/summarize_ncu.py); None if absent"""
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r02_tracker_traffic.json")
+    try:
+        with open(path) as f:
+            d = json.load(f)
+        return float(d["dram_bytes_per_launch"]), "profiles/r02_tracker_traffic.json (%s)" % d.get("source", "ncu --set full")
+    except (OSError, ValueError, KeyError):
+        return None, "no committed ncu capture found"
 
 
 def build_workload(seed, n_frames, tracker_points, with_oracle=True):
@@ -175,6 +182,15 @@ def dist_setup(n):
     local = int(os.environ.get("LOCAL_RANK", "0"))
     dist = None
     if world > 1:
+        # one disjoint slice of the host cores per rank: every rank hot-polls its result flags and launches from the host,
+        # so ranks sharing cores (the default affinity is "all cores" for every rank) lengthen each other's launch path
+        try:
+            avail = sorted(os.sched_getaffinity(0))
+            per = len(avail) // world
+            if per >= 1:
+                os.sched_setaffinity(0, set(avail[local * per:(local + 1) * per]))
+        except (AttributeError, OSError):
+            pass
         import torch.distributed as dist
         backend = "nccl" if torch.cuda.is_available() else "gloo"
         if backend == "nccl":
@@ -239,6 +255,58 @@ def cpu_baseline(wl, budget_s=12.0):
                       % (n, nfr, dt, dt_img * 1e3, os.cpu_count()),
             "ms_per_frame_track": dt / n * 1e3, "ms_per_frame_make_images": dt_img * 1e3}
 
+
+
+def tracker_row(pkg, wl, levels, dev, steps, warmup, flush_l2, torch, device, cpu_seconds):
+    """One more tracker configuration next to the headline one (rank 0, N = 1): device-timed trackNewestCoarse over the ring of
+    frames of workload `wl` with `levels` pyramid levels, and -- when cpu_seconds > 0 -- the CPU tracker on the same inputs.
+    Used for BASELINE configs[0] as worded (a forced fifth level) and for the survey-sized cloud."""
+    W = wl["W"]
+    nfr = len(wl["frames"])
+    ctx = pkg.Context(dev, W.w, W.h, nfr + 2)
+    ctx.make_images(0, W.images[-1], levels, want_host=False)
+    pc_n = ctx.tracker_set_ref_points(0, 0, levels, W.K, *wl["ref_inputs"], wl["a0"], wl["b0"], 1.0)
+    for k in range(nfr):
+        ctx.make_images(1 + k, wl["frames"][k][0], levels, want_host=False)
+    stream = torch.cuda.ExternalStream(ctx.tracker_stream(0), device=device)
+    res = []
+    ms = 0.0
+    for i in range(warmup + steps):
+        k = i % nfr
+        a, b = wl["affs"][k]
+        flush_l2(stream)
+        ctx.sync()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        ctx.track_batched_async(0, 1 + k, wl["inits"][k], a, b, levels - 1)
+        e1.record(stream)
+        r = ctx.track_fetch(0, 1)[0]
+        e1.synchronize()
+        if i >= warmup:
+            ms += e0.elapsed_time(e1)
+            res.append(r)
+    ctx.close()
+    out = {"levels": levels, "reference_points": int(wl["ref_points"]), "pc_n": [int(x) for x in pc_n],
+           "ms_per_frame": ms / steps, "value": steps / (ms * 1e-3), "unit": UNIT, "tracked_ok": float(np.mean([r.ok for r in res])),
+           "evals_per_frame": float(np.mean([r.n_evals for r in res])), "timing": "CUDA events on the tracker slot's stream, L2 flushed before every frame"}
+    if cpu_seconds > 0:
+        O = entry.load_oracle()
+        ref_pyr = O.make_images(W.images[-1], levels)
+        trk = O.Tracker(W.w, W.h, levels, *W.K, kind=cpu_kind()[0])
+        trk.set_ref(*wl["ref_inputs"], [x.reshape(-1) for x in ref_pyr[0]], wl["a0"], wl["b0"], 1.0)
+        pyrs = [O.make_images(f[0], levels) for f in wl["frames"]]
+        n, t0 = 0, time.perf_counter()
+        while time.perf_counter() - t0 < cpu_seconds:
+            k = n % nfr
+            trk.set_new_frame([x.reshape(-1) for x in pyrs[k][0]], 1.0)
+            a, b = wl["affs"][k]
+            trk.track(wl["inits"][k], a, b, levels - 1)
+            n += 1
+        dt = time.perf_counter() - t0
+        out["cpu"] = {"value": n / dt, "unit": UNIT, "ms_per_frame": dt / n * 1e3, "cores": 1, "kind": cpu_kind()[1],
+                      "sample": "%d trackNewestCoarse calls in %.1f s, pyramid precomputed" % (n, dt)}
+        out["speedup_vs_cpu_tracker"] = out["value"] / out["cpu"]["value"]
+    return out
 
 
 def ba_gpu_bench(pkg, W, dev, steps, warmup, flush_l2, torch, device):
@@ -558,8 +626,9 @@ def run_ours(args):
     bytes_per_launch = float(np.mean([r.point_evals for r in results])) * POINT_BYTES
     peak, peak_kind = peaks()
     achieved = bytes_per_launch / (np.mean(ms_k) * 1e-3) / 1e9
+    traffic, traffic_src = k2b_traffic()
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": K2B_DRAM_BYTES_PER_LAUNCH, "traffic_source": "profiles/r01_ncu_full_summary.txt (ncu --set full, dram__bytes_read + write, cold L2)",
+                "traffic": traffic, "traffic_source": traffic_src,
                 "kernel": "track_persistent_kernel", "kernel_ms": float(np.mean(ms_k)), "peak_source": peak_kind + " (MEASURED_PEAKS.json hbm_gbs)",
                 "algorithmic_bytes_per_launch": bytes_per_launch,
                 "note": "VGA working set (6.5 MB pyramid + 0.3 MB cloud) is L2-resident; the kernel is a chain of ~%d dependent "
@@ -605,6 +674,15 @@ def run_ours(args):
     trace = trace_bench(pkg, W, dev, 10, 3, flush_l2, torch, device, with_cpu=(rank == 0 and world == 1 and not args.no_cpu)) if rank == 0 else None
     ba_ms = reduce_max(dist, ba["value"], device)
     ba["value"] = ba_ms
+    rows = None
+    if rank == 0 and world == 1:
+        # BASELINE configs[0] as worded (5-level pyramid; the reference itself picks 4 at VGA) and the survey's
+        # cloud sizing (~2000 points with a residual into the newest key frame), each with its own CPU time
+        cs = 0.0 if args.no_cpu else 3.0
+        with quiet_stdout():
+            wl_big = build_workload(0, min(args.frames, 6), int(args.tracker_points * 1.3), with_oracle=False)
+        rows = {"levels5": tracker_row(pkg, wl, 5, dev, min(args.steps, 30), 3, flush_l2, torch, device, cs),
+                "survey_cloud": tracker_row(pkg, wl_big, wl_big["levels"], dev, min(args.steps, 30), 3, flush_l2, torch, device, cs)}
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
         with quiet_stdout():
@@ -629,6 +707,10 @@ def run_ours(args):
                                    "api": "dso_b200_track_frame (H2D, K1, K2, D2H, 1 sync per frame), L2 flushed before every step",
                                    "tracked_ok": conv / total_steps}},
                 "gpu_launches": int(launches), "ba": ba, "trace_new_coarse": trace, "roofline": roofline, "cpu_baseline": cpu, "clocks": clocks,
+                "more_tracker_rows": rows,
+                "launch_gap_ms": t_value / args.steps * 1e3 - roofline["kernel_ms"],
+                "value_without_launch_gap": total_steps / (roofline["kernel_ms"] * 1e-3 * args.steps),
+                "host_cores_of_rank0": sorted(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else None,
                 "wall_s_timed_region": t_wall1 - t_wall0,
                 "set_coarse_tracking_ref_ms": set_ref_ms,     # makeCoarseDepthL0 on the device incl. upload of the points and 1 sync (first call)
                 "lm": {"evals_per_frame": float(np.mean([r.n_evals for r in results])),
