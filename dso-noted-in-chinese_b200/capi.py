@@ -36,6 +36,13 @@ class TrackResult(C.Structure):
                 ("point_evals", C.c_double), ("trace_dE", C.c_float * 64), ("trace_E", C.c_float * 64)]
 
 
+class Settings(C.Structure):
+    _fields_ = [("huberTH", C.c_float), ("outlierTHSumComponent", C.c_float), ("maxPixSearch", C.c_float),
+                ("minTraceTestRadius", C.c_int), ("GNItsOnPointActivation", C.c_int), ("trace_stepsize", C.c_float),
+                ("trace_GNIterations", C.c_int), ("trace_GNThreshold", C.c_float), ("trace_extraSlackOnTH", C.c_float),
+                ("trace_slackInterval", C.c_float), ("trace_minImprovementFactor", C.c_float), ("minIdepthH_act", C.c_float)]
+
+
 class Precalc(C.Structure):
     _fields_ = [("PRE_RTll_0", C.c_float * 9), ("PRE_tTll_0", C.c_float * 3), ("PRE_KRKiTll", C.c_float * 9),
                 ("PRE_KtTll", C.c_float * 3), ("PRE_aff_mode", C.c_float * 2), ("PRE_b0_mode", C.c_float), ("pad", C.c_float)]
@@ -46,6 +53,8 @@ SIGNATURES = {
     "dso_b200_create": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(vp)]),
     "dso_b200_destroy": (None, [vp]),
     "dso_b200_last_error": (C.c_char_p, []),
+    "dso_b200_settings_default": (None, [C.POINTER(Settings)]),
+    "dso_b200_set_settings": (C.c_int, [vp, C.POINTER(Settings)]),
     "dso_b200_stream": (vp, [vp]),
     "dso_b200_stream_for": (vp, [vp, C.c_int]),
     "dso_b200_sync": (C.c_int, [vp]),
@@ -87,6 +96,7 @@ SIGNATURES = {
     "dso_b200_track_hostloop": (C.c_int, [vp, C.c_int, C.c_int, f64p, C.c_double, C.c_double, C.c_float, C.c_int, vp,
                                           C.POINTER(TrackOpts), C.POINTER(TrackResult)]),
     "dso_b200_ba_set_affine_modes": (C.c_int, [vp, C.c_float, C.c_float]),
+    "dso_b200_ba_linearize_residuals": (C.c_int, [vp, C.c_int, i32p, C.c_int, C.c_int, vp, vp, vp]),
     "dso_b200_ba_set_calib_delta": (C.c_int, [vp, f64p]),
     "dso_b200_ba_set_priors": (C.c_int, [vp, vp, vp, vp, vp, vp, vp]),
     "dso_b200_ba_set_nullspaces": (C.c_int, [vp, vp, C.c_int, C.c_double]),
@@ -182,6 +192,14 @@ class Context:
     @property
     def stream(self):
         return self.L.dso_b200_stream(self.h)
+
+    def default_settings(self):
+        s = Settings()
+        self.L.dso_b200_settings_default(C.byref(s))
+        return s
+
+    def set_settings(self, s):
+        self._check(self.L.dso_b200_set_settings(self.h, C.byref(s)))
 
     def stream_for(self, which):
         """0 main (makeImages), 1 / 2 tracker slot 0 / 1, 3 mapping (BA, immature points), 4 upload"""
@@ -535,6 +553,13 @@ class Context:
         sums = np.zeros(2, dtype=np.float32)
         self._check(self.L.dso_b200_ba_iteration(self.h, iteration, lam, solver_mode, stepfacD, x.ctypes.data, C.byref(e), sums.ctypes.data))
         return dict(x=x, energy=e.value, step_sums=sums)
+
+    def ba_linearize_residuals(self, idx, reset_oob=True, apply=True):
+        idx = np.ascontiguousarray(idx, dtype=np.int32)
+        k = len(idx)
+        ns, ne, ia = np.zeros(k, dtype=np.int32), np.zeros(k, dtype=np.float32), np.zeros(k, dtype=np.uint8)
+        self._check(self.L.dso_b200_ba_linearize_residuals(self.h, k, idx, int(reset_oob), int(apply), ns.ctypes.data, ne.ctypes.data, ia.ctypes.data))
+        return dict(newState=ns, newEnergy=ne, isActive=ia)
 
     def ba_marginalize_points(self, flags, prior_marg_fac=600.0 * 600.0, marg_weight_fac=0.25):
         N = 8 * self.nF + 4

@@ -28,6 +28,7 @@
 __constant__ int c_pattern[8][2] = { {0,-2}, {-1,-1}, {1,-1}, {-2,0}, {0,0}, {2,0}, {-1,1}, {0,2} };   // settings.cpp:274
 
 
+void ba_settings_changed(dso_b200_ctx* ctx);
 int ba_create(dso_b200_ctx* ctx)
 {
 	BAWorkspace* W = new BAWorkspace();
@@ -70,7 +71,19 @@ int ba_create(dso_b200_ctx* ctx)
 	memset(&W->g_step, 0, sizeof(W->g_step)); memset(W->g_iter, 0, sizeof(W->g_iter));
 	W->use_graphs = !getenv("DSO_B200_NO_GRAPH");
 	ctx->ba = W;
+	ba_settings_changed(ctx);
 	return 0;
+}
+
+// dso_b200_set_settings: the two thresholds PointFrameResidual::linearize reads travel in the kernel parameter block
+void ba_settings_changed(dso_b200_ctx* ctx)
+{
+	BAWorkspace* W = ctx->ba;
+	if (!W) return;
+	W->P.huberTH = ctx->settings.huberTH;
+	W->P.outlierTHSum = ctx->settings.outlierTHSumComponent;
+	W->lin_done = false; W->top_done = false;
+	ba_graphs_invalidate(W);
 }
 
 static void free_points(BAWorkspace* W)
@@ -87,7 +100,7 @@ static void free_res(BAWorkspace* W)
 	if (!W->capR) return;
 	cudaFree(W->d_rpoint); cudaFree(W->d_rtarget); cudaFree(W->d_state); cudaFree(W->d_newState); cudaFree(W->d_energy); cudaFree(W->d_newEnergy);
 	cudaFree(W->d_newEnergyWO); cudaFree(W->d_isLin); cudaFree(W->d_isAct); cudaFree(W->d_efsel); cudaFree(W->d_cpt); cudaFree(W->d_proj);
-	cudaFree(W->d_J[0]); cudaFree(W->d_J[1]); cudaFree(W->d_JpJdF); cudaFree(W->d_contrib); cudaFree(W->d_resEnergy); cudaFree(W->d_perm);
+	cudaFree(W->d_J[0]); cudaFree(W->d_J[1]); cudaFree(W->d_JpJdF); cudaFree(W->d_contrib); cudaFree(W->d_resEnergy); cudaFree(W->d_perm); cudaFree(W->d_subset);
 	cudaFree(W->d_energy_blocks); cudaFree(W->d_resToZero);
 	if (W->capChunks) { cudaFree(W->d_chunk_start); cudaFree(W->d_chunk_cnt); cudaFree(W->d_topPartials); cudaFree(W->d_chunk_nres); }
 	W->capR = 0; W->capChunks = 0;
@@ -95,6 +108,7 @@ static void free_res(BAWorkspace* W)
 
 void ba_graphs_invalidate(BAWorkspace* W)
 {
+	if (!W) return;
 	BAGraph* gs[3] = { &W->g_step, &W->g_iter[0], &W->g_iter[1] };
 	for (BAGraph* g : gs)
 	{
@@ -149,15 +163,19 @@ __global__ void __launch_bounds__(256) ba_linearize_kernel(BAParams B, const flo
                                                            const int* __restrict__ rtarget, const int* __restrict__ state,
                                                            const double* __restrict__ state_energy, const unsigned char* __restrict__ efsel,
                                                            float* J0, float* J1, int* newState, float* newEnergy, float* newEnergyWO,
-                                                           float* cpt, float* proj, double* resEnergy)
+                                                           float* cpt, float* proj, double* resEnergy,
+                                                           const int* __restrict__ subset, int nsub, int reset_oob)
 {
 	__shared__ float sJ[32][JSZ + 2];
 	const int tid = threadIdx.x, lane = tid & 31, g = tid >> 3, idx = tid & 7, base = lane & ~7;
-	const int r = blockIdx.x * 32 + g;
-	const bool valid = r < B.nR;
-	const int rr = valid ? r : 0;
+	// subset != NULL: the per-object form (a batch of k residuals, e.g. FullSystem::flagPointsForRemoval, FullSystem.cpp:781);
+	// reset_oob: PointFrameResidual::resetOOB first (Residuals.h:101-108: energies 0, state IN)
+	const int slot = blockIdx.x * 32 + g;
+	const bool valid = slot < (subset ? nsub : B.nR);
+	const int r = valid ? (subset ? subset[slot] : slot) : 0;
+	const int rr = r;
 	const int p = rpoint[rr], t = rtarget[rr], h = phost[p];
-	const int st = state[rr];
+	const int st = reset_oob ? ST_IN : state[rr];
 	const float4 P4 = __ldg(pt + p);            // u, v, idepth_scaled, idepth_zero_scaled
 	const float* pre = precalc + (size_t)(h * B.nF + t) * 28;
 	const float* R0 = pre;        // PRE_RTll_0
@@ -198,10 +216,10 @@ __global__ void __launch_bounds__(256) ba_linearize_kernel(BAParams B, const flo
 	const float col = __ldg(color + 8 * (size_t)p + idx), wgt = __ldg(weights + 8 * (size_t)p + idx);
 	const float residual = fsub(h0, fadd(fmul(affLL0, col), affLL1));
 	const float drdA = fsub(col, b0);
-	float wv = __fsqrt_rn(fdiv(OUTLIER_TH_SUM, fadd(OUTLIER_TH_SUM, fadd(fmul(h1, h1), fmul(h2, h2)))));
+	float wv = __fsqrt_rn(fdiv(B.outlierTHSum, fadd(B.outlierTHSum, fadd(fmul(h1, h1), fmul(h2, h2)))));
 	wv = fmul(0.5f, fadd(wv, wgt));
 	const float ar = fabsf(residual);
-	float hw = ar < HUBER_TH ? 1.f : fdiv(HUBER_TH, ar);
+	float hw = ar < B.huberTH ? 1.f : fdiv(B.huberTH, ar);
 	const float e_i = fmul(fmul(fmul(fmul(fmul(wv, wv), hw), residual), residual), fsub(2.f, hw));   // :219
 	if (hw < 1.f) hw = __fsqrt_rn(hw);
 	hw = fmul(hw, wv);
@@ -224,7 +242,7 @@ __global__ void __launch_bounds__(256) ba_linearize_kernel(BAParams B, const flo
 			{
 				newState[r] = ST_OOB;
 				newEnergyWO[r] = -1.f;
-				resEnergy[r] = state_energy[r];
+				resEnergy[r] = reset_oob ? 0.0 : state_energy[r];
 				if (st != ST_OOB && centre_ok) { cpt[3 * r] = Kuc; cpt[3 * r + 1] = Kvc; cpt[3 * r + 2] = new_idepth; }   // :124 precedes the pattern loop
 			}
 		}
@@ -291,10 +309,13 @@ __global__ void __launch_bounds__(256) ba_linearize_kernel(BAParams B, const flo
 
 // applyRes(true), Residuals.cpp:323-347 + EFResidual::takeDataF, EnergyFunctionalStructs.cpp:39-49
 __global__ void ba_apply_res_kernel(int nR, int* state, const int* __restrict__ newState, double* state_energy, const float* __restrict__ newEnergy,
-                                    unsigned char* isAct, unsigned char* efsel, const float* J0, const float* J1, float* JpJdF)
+                                    unsigned char* isAct, unsigned char* efsel, const float* J0, const float* J1, float* JpJdF,
+                                    const int* __restrict__ subset, int reset_oob)
 {
-	const int r = blockIdx.x * blockDim.x + threadIdx.x;
-	if (r >= nR) return;
+	const int slot = blockIdx.x * blockDim.x + threadIdx.x;
+	if (slot >= nR) return;
+	const int r = subset ? subset[slot] : slot;
+	if (reset_oob) { state[r] = ST_IN; state_energy[r] = 0.0; }   // PointFrameResidual::resetOOB preceded the linearisation
 	if (state[r] == ST_OOB) return;                       // can never go back from OOB
 	const int ns = newState[r];
 	if (ns == ST_IN)
@@ -1130,6 +1151,7 @@ extern "C" int dso_b200_ba_set_residuals(dso_b200_ctx* ctx, int nR, const int* p
 		CK(cudaMalloc(&W->d_J[0], n * JSZ * sizeof(float))); CK(cudaMalloc(&W->d_J[1], n * JSZ * sizeof(float)));
 		CK(cudaMalloc(&W->d_JpJdF, n * 8 * sizeof(float))); CK(cudaMalloc(&W->d_contrib, n * 6 * sizeof(float))); CK(cudaMalloc(&W->d_resEnergy, n * sizeof(double)));
 		CK(cudaMalloc(&W->d_perm, n * sizeof(int)));
+		CK(cudaMalloc(&W->d_subset, n * sizeof(int)));
 		CK(cudaMalloc(&W->d_energy_blocks, ((n + 255) / 256) * sizeof(double)));
 		CK(cudaMalloc(&W->d_resToZero, n * 8 * sizeof(float)));
 		W->capR = nR;
@@ -1338,7 +1360,8 @@ int ba_enqueue_linearize(dso_b200_ctx* ctx)
 	const int nR = W->P.nR;
 	ba_linearize_kernel<<<(nR + 31) / 32, 256, 0, ctx->ba_stream>>>(W->P, W->d_precalc, W->d_pt, W->d_color, W->d_weights, W->d_phost, W->d_rpoint,
 	                                                           W->d_rtarget, W->d_state, W->d_energy, W->d_efsel, W->d_J[0], W->d_J[1],
-	                                                           W->d_newState, W->d_newEnergy, W->d_newEnergyWO, W->d_cpt, W->d_proj, W->d_resEnergy);
+	                                                           W->d_newState, W->d_newEnergy, W->d_newEnergyWO, W->d_cpt, W->d_proj, W->d_resEnergy,
+	                                                           nullptr, 0, 0);
 	const int nb = (nR + 255) / 256;
 	ba_energy_blocks_kernel<<<nb, 256, 0, ctx->ba_stream>>>(nR, W->d_resEnergy, W->d_energy_blocks);
 	ba_energy_final_kernel<<<1, 32, 0, ctx->ba_stream>>>(nb, W->d_energy_blocks, W->d_scalars);
@@ -1353,7 +1376,7 @@ int ba_enqueue_apply(dso_b200_ctx* ctx)
 	BAWorkspace* W = ctx->ba;
 	const int nR = W->P.nR;
 	ba_apply_res_kernel<<<(nR + 255) / 256, 256, 0, ctx->ba_stream>>>(nR, W->d_state, W->d_newState, W->d_energy, W->d_newEnergy, W->d_isAct, W->d_efsel,
-	                                                             W->d_J[0], W->d_J[1], W->d_JpJdF);
+	                                                             W->d_J[0], W->d_J[1], W->d_JpJdF, nullptr, 0);
 	LAUNCHED(ctx, 1);
 	CK(cudaGetLastError());
 	W->top_done = false;
@@ -1450,6 +1473,57 @@ extern "C" int dso_b200_ba_linearize(dso_b200_ctx* ctx, int* newState, float* ne
 		CK(cudaMemcpy(j1.data(), W->d_J[1], nR * JSZ * sizeof(float), cudaMemcpyDeviceToHost));
 		for (size_t r = 0; r < nR; r++) memcpy(J74 + r * JSZ, (sel[r] ? j0.data() : j1.data()) + r * JSZ, JSZ * sizeof(float));
 	}
+	return 0;
+}
+
+// PointFrameResidual::linearize / applyRes per object, as a batch of k residuals: FullSystem::flagPointsForRemoval
+// (FullSystem.cpp:776-787) does r->resetOOB(); r->linearize(&Hcalib); r->applyRes(true) for the residuals of every point it
+// marginalises, one by one; the host mirror collects them and forwards one batch.
+extern "C" int dso_b200_ba_linearize_residuals(dso_b200_ctx* ctx, int k, const int* residual_idx, int reset_oob, int apply,
+                                               int* newState_out, float* newEnergy_out, unsigned char* isActive_out)
+{
+	int rc = ba_check_ready(ctx, __func__);
+	if (rc) return rc;
+	BAWorkspace* W = ctx->ba;
+	ARG_CHECK(k >= 0 && (k == 0 || residual_idx), "bad arguments");
+	if (k == 0) return 0;
+	const int nR = W->P.nR;
+	for (int q = 0; q < k; q++) ARG_CHECK(residual_idx[q] >= 0 && residual_idx[q] < nR, "residual index out of range");
+	CK(cudaSetDevice(ctx->device));
+	cudaStream_t s = ctx->ba_stream;
+	BA_CHECK(k <= nR, "more indices than residuals");
+	int* d_sub = W->d_subset;
+	CK(cudaMemcpyAsync(d_sub, residual_idx, (size_t)k * sizeof(int), cudaMemcpyHostToDevice, s));
+	ba_linearize_kernel<<<(k + 31) / 32, 256, 0, s>>>(W->P, W->d_precalc, W->d_pt, W->d_color, W->d_weights, W->d_phost, W->d_rpoint,
+	                                                  W->d_rtarget, W->d_state, W->d_energy, W->d_efsel, W->d_J[0], W->d_J[1],
+	                                                  W->d_newState, W->d_newEnergy, W->d_newEnergyWO, W->d_cpt, W->d_proj, W->d_resEnergy,
+	                                                  d_sub, k, reset_oob);
+	LAUNCHED(ctx, 1);
+	if (apply)
+	{
+		ba_apply_res_kernel<<<(k + 255) / 256, 256, 0, s>>>(k, W->d_state, W->d_newState, W->d_energy, W->d_newEnergy, W->d_isAct, W->d_efsel,
+		                                                    W->d_J[0], W->d_J[1], W->d_JpJdF, d_sub, reset_oob);
+		LAUNCHED(ctx, 1);
+		W->top_done = false;
+	}
+	CK(cudaGetLastError());
+	if (newState_out || newEnergy_out || isActive_out)
+	{
+		std::vector<int> ns(nR); std::vector<float> ne(nR); std::vector<unsigned char> ia(nR);
+		CK(cudaMemcpyAsync(ns.data(), W->d_newState, (size_t)nR * sizeof(int), cudaMemcpyDeviceToHost, s));
+		CK(cudaMemcpyAsync(ne.data(), W->d_newEnergy, (size_t)nR * sizeof(float), cudaMemcpyDeviceToHost, s));
+		CK(cudaMemcpyAsync(ia.data(), W->d_isAct, (size_t)nR, cudaMemcpyDeviceToHost, s));
+		CK(cudaStreamSynchronize(s));
+		for (int q = 0; q < k; q++)
+		{
+			if (newState_out) newState_out[q] = ns[residual_idx[q]];
+			if (newEnergy_out) newEnergy_out[q] = ne[residual_idx[q]];
+			if (isActive_out) isActive_out[q] = ia[residual_idx[q]];
+		}
+	}
+	else
+		CK(cudaStreamSynchronize(s));
+	ba_graphs_invalidate(W);      // nothing captured depends on it, but the residual states changed outside the captured sequence
 	return 0;
 }
 

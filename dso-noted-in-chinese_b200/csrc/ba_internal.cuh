@@ -15,8 +15,6 @@
 #define SCALE_IDEPTH 1.0f
 #define SCALE_F 50.0f
 #define SCALE_C 50.0f
-#define OUTLIER_TH_SUM 2500.0f     // setting_outlierTHSumComponent = 50*50
-#define HUBER_TH 9.0f              // setting_huberTH
 
 // offsets into the flattened RawResidualJacobian (RawResidualJacobian.h:40-79)
 #define J_RESF 0
@@ -41,6 +39,7 @@ struct BAParams
 	float frameEnergyTH[MAXF];
 	const float4* img[MAXF];
 	int fixA, fixB;            // setting_affineOptModeA/B < 0 (Residuals.cpp:257-258)
+	float huberTH, outlierTHSum;   // setting_huberTH, setting_outlierTHSumComponent (dso_b200_set_settings)
 };
 
 // inputs of the linearised-residual mode (addPoint<1>, fixLinearizationF)
@@ -85,7 +84,7 @@ struct BAWorkspace
 	int* d_rpoint; int* d_rtarget; int* d_state; int* d_newState; double* d_energy; float* d_newEnergy; float* d_newEnergyWO;
 	unsigned char* d_isLin; unsigned char* d_isAct; unsigned char* d_efsel;
 	float* d_cpt; float* d_proj; float* d_J[2]; float* d_JpJdF; float* d_contrib; double* d_resEnergy;
-	int* d_perm;
+	int* d_perm; int* d_subset;      // d_subset: index list of dso_b200_ba_linearize_residuals
 	// chunks (top): residuals sorted by pair; (schur): points by host
 	int nChunks, capChunks; int* d_chunk_start; int* d_chunk_cnt; int* d_pair_chunk_begin;   // [nF*nF+1]
 	float* d_topPartials; int* d_chunk_nres;

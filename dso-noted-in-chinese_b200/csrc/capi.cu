@@ -50,6 +50,7 @@ extern "C" int dso_b200_create(int device, int max_w, int max_h, int n_frame_slo
 	ctx->device = device;
 	ctx->sm_count = prop.multiProcessorCount;
 	ctx->max_w = max_w; ctx->max_h = max_h; ctx->n_slots = n_frame_slots;
+	dso_b200_settings_default(&ctx->settings);
 	int rc = create_impl(ctx, device, max_w, max_h, n_frame_slots);
 	if (rc)
 	{
@@ -173,6 +174,24 @@ extern "C" void dso_b200_destroy(dso_b200_ctx* ctx)
 	}
 	for (int i = 0; i < 5; i++) if (all[i]) cudaStreamDestroy(all[i]);
 	delete ctx;
+}
+
+extern "C" void dso_b200_settings_default(dso_b200_settings* s)
+{
+	s->huberTH = 9; s->outlierTHSumComponent = 50 * 50; s->maxPixSearch = 0.027f; s->minTraceTestRadius = 2;
+	s->GNItsOnPointActivation = 3; s->trace_stepsize = 1.0f; s->trace_GNIterations = 3; s->trace_GNThreshold = 0.1f;
+	s->trace_extraSlackOnTH = 1.2f; s->trace_slackInterval = 1.5f; s->trace_minImprovementFactor = 2; s->minIdepthH_act = 100;
+}
+void ba_settings_changed(dso_b200_ctx* ctx);
+extern "C" int dso_b200_set_settings(dso_b200_ctx* ctx, const dso_b200_settings* s)
+{
+	ARG_CHECK(ctx && s, "null argument");
+	ARG_CHECK(s->huberTH > 0 && s->outlierTHSumComponent > 0 && s->maxPixSearch > 0, "thresholds must be positive");
+	ARG_CHECK(s->minTraceTestRadius >= 0 && s->GNItsOnPointActivation >= 0 && s->GNItsOnPointActivation <= 16 &&
+	          s->trace_GNIterations >= 0 && s->trace_GNIterations <= 16, "iteration counts out of range");
+	ctx->settings = *s;
+	ba_settings_changed(ctx);
+	return 0;
 }
 
 extern "C" void* dso_b200_stream(dso_b200_ctx* ctx) { return ctx ? (void*)ctx->stream : nullptr; }

@@ -118,6 +118,7 @@ struct dso_b200_ctx
 	BAWorkspace* ba;
 	void* coarse_depth;        // CoarseDepthWS (coarse_depth.cu), allocated at the first dso_b200_tracker_set_ref_points
 	void* trace;               // TraceWS (trace.cu): the immature points of the window
+	dso_b200_settings settings;                       // dso_b200_set_settings
 	void* act_scratch; size_t act_scratch_bytes;      // dso_b200_optimize_immature: grow-only device scratch
 	int tune_threads, tune_cluster, tune_nclusters;   // dso_b200_track_set_tuning (0 = automatic)
 	int last_shape[3];                                // threads, cluster size, clusters per hypothesis of the last tracker launch

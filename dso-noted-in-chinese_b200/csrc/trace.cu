@@ -67,11 +67,11 @@ struct TracePoint
 __device__ __forceinline__ int tr_fail(TracePoint& p, int st) { p.uv0 = -1.f; p.uv1 = -1.f; p.interval = 0.f; return p.status = st; }
 
 // one point, executed by the 8 lanes of its group (idx = pattern pixel of this lane); control flow is uniform in the group
-__device__ int trace_on_group(TracePoint& p, float color, float weight, const float4* __restrict__ img, int wG0, int hG0,
+__device__ int trace_on_group(const dso_b200_settings& ST, TracePoint& p, float color, float weight, const float4* __restrict__ img, int wG0, int hG0,
                               const float* KRKi, const float* Kt, const float* aff, float* errors, int idx, int base, unsigned gmask)
 {
 	if (p.status == IPS_OOB) return p.status;                                          // :79
-	const float maxPixSearch = fmul((float)(wG0 + hG0), 0.027f);                       // :85 setting_maxPixSearch
+	const float maxPixSearch = fmul((float)(wG0 + hG0), ST.maxPixSearch);               // :85 setting_maxPixSearch
 	float pr[3];
 #pragma unroll
 	for (int r = 0; r < 3; r++) pr[r] = dot3e(KRKi[3 * r], p.u, KRKi[3 * r + 1], p.v, KRKi[3 * r + 2], 1.f);   // :96
@@ -92,7 +92,7 @@ __device__ int trace_on_group(TracePoint& p, float color, float weight, const fl
 		if (!(uMax > 4.f && vMax > 4.f && uMax < wlim && vMax < hlim)) return tr_fail(p, IPS_OOB);   // :124-130
 		const float du = fsub(uMin, uMax), dv = fsub(vMin, vMax);
 		dist = __fsqrt_rn(fadd(fmul(du, du), fmul(dv, dv)));                             // :135-136
-		if (dist < 1.5f)                                                                 // :138-145 setting_trace_slackInterval
+		if (dist < ST.trace_slackInterval)                                               // :138-145 setting_trace_slackInterval
 		{
 			p.uv0 = fmul(fadd(uMax, uMin), 0.5f); p.uv1 = fmul(fadd(vMax, vMin), 0.5f);
 			p.interval = dist;
@@ -113,8 +113,8 @@ __device__ int trace_on_group(TracePoint& p, float color, float weight, const fl
 		if (!(uMax > 4.f && vMax > 4.f && uMax < wlim && vMax < hlim)) return tr_fail(p, IPS_OOB);   // :166-172
 	}
 	if (!(p.idmin < 0.f || (ptpMin[2] > 0.75f && ptpMin[2] < 1.5f))) return tr_fail(p, IPS_OOB);     // :179-185
-	float dx = fmul(1.0f, fsub(uMax, uMin));                                            // :196 setting_trace_stepsize = 1
-	float dy = fmul(1.0f, fsub(vMax, vMin));
+	float dx = fmul(ST.trace_stepsize, fsub(uMax, uMin));                               // :196 setting_trace_stepsize
+	float dy = fmul(ST.trace_stepsize, fsub(vMax, vMin));
 	float a, b;
 	{
 		const float t0 = fadd(fmul(dx, p.G[0]), fmul(dy, p.G[2])), t1 = fadd(fmul(dx, p.G[1]), fmul(dy, p.G[3]));   // :199
@@ -123,7 +123,7 @@ __device__ int trace_on_group(TracePoint& p, float color, float weight, const fl
 		b = fadd(fmul(s0, dy), fmul(s1, -dx));
 	}
 	float errorInPixel = fadd(0.2f, fdiv(fmul(0.2f, fadd(a, b)), a));                   // :201
-	if (fmul(errorInPixel, 2.f) > dist && finiteMax)                                    // :203-209 setting_trace_minImprovementFactor
+	if (fmul(errorInPixel, ST.trace_minImprovementFactor) > dist && finiteMax)          // :203-209 setting_trace_minImprovementFactor
 	{
 		p.uv0 = fmul(fadd(uMax, uMin), 0.5f); p.uv1 = fmul(fadd(vMax, vMin), 0.5f);
 		p.interval = dist;
@@ -138,7 +138,7 @@ __device__ int trace_on_group(TracePoint& p, float color, float weight, const fl
 		vMax = fadd(vMin, fmul(maxPixSearch, dy));
 		dist = maxPixSearch;
 	}
-	int numSteps = (int)fadd(1.9999f, fdiv(dist, 1.0f));                                // :234
+	int numSteps = (int)fadd(1.9999f, fdiv(dist, ST.trace_stepsize));                   // :234
 	const float randShift = fsub(fmul(uMin, 1000.f), floorf(fmul(uMin, 1000.f)));       // :238
 	float ptx = fsub(uMin, fmul(randShift, dx));
 	float pty = fsub(vMin, fmul(randShift, dy));
@@ -159,7 +159,7 @@ __device__ int trace_on_group(TracePoint& p, float color, float weight, const fl
 		{
 			const float residual = fsub(hit, fadd(fmul(aff[0], color), aff[1]));
 			const float ar = fabsf(residual);
-			const float hw = ar < 9.f ? 1.f : fdiv(9.f, ar);                               // setting_huberTH
+			const float hw = ar < ST.huberTH ? 1.f : fdiv(ST.huberTH, ar);                 // setting_huberTH
 			term = fmul(fmul(fmul(hw, residual), residual), fsub(2.f, hw));
 		}
 		// energy += term in pattern order; the reference adds the double literal 1e5 for a non-finite sample (:277)
@@ -179,7 +179,7 @@ __device__ int trace_on_group(TracePoint& p, float color, float weight, const fl
 	__syncwarp(gmask);
 	float secondBest = 1e10f;                                                           // :303-309 (a minimum: order-free)
 	for (int i = idx; i < numSteps; i += 8)
-		if ((i < bestIdx - 2 || i > bestIdx + 2) && errors[i] < secondBest) secondBest = errors[i];   // setting_minTraceTestRadius
+		if ((i < bestIdx - ST.minTraceTestRadius || i > bestIdx + ST.minTraceTestRadius) && errors[i] < secondBest) secondBest = errors[i];   // setting_minTraceTestRadius
 #pragma unroll
 	for (int o = 4; o > 0; o >>= 1)
 	{
@@ -189,8 +189,8 @@ __device__ int trace_on_group(TracePoint& p, float color, float weight, const fl
 	const float newQuality = fdiv(secondBest, bestEnergy);
 	if (newQuality < p.quality || numSteps > 10) p.quality = newQuality;                // :311
 	float uBak = bestU, vBak = bestV, stepBack = 0.f;                                   // :315
-	bestEnergy = 1e5f;                                                                  // setting_trace_GNIterations = 3 > 0
-	for (int it = 0; it < 3; it++)                                                      // :318-375 Gauss-Newton along the line
+	if (ST.trace_GNIterations > 0) bestEnergy = 1e5f;                                   // :316
+	for (int it = 0; it < ST.trace_GNIterations; it++)                                  // :318-375 Gauss-Newton along the line
 	{
 		float h0, h1, h2;
 		tr_interp(img, fadd(bestU, rot0), fadd(bestV, rot1), wG0, h0, h1, h2, true);
@@ -201,7 +201,7 @@ __device__ int trace_on_group(TracePoint& p, float color, float weight, const fl
 			const float residual = fsub(h0, fadd(fmul(aff[0], color), aff[1]));
 			const float dRes = fadd(fmul(dx, h1), fmul(dy, h2));
 			const float ar = fabsf(residual);
-			const float hw = ar < 9.f ? 1.f : fdiv(9.f, ar);
+			const float hw = ar < ST.huberTH ? 1.f : fdiv(ST.huberTH, ar);
 			tH = fmul(fmul(hw, dRes), dRes);
 			tb = fmul(fmul(hw, residual), dRes);
 			tE = fmul(fmul(fmul(fmul(fmul(weight, weight), hw), residual), residual), fsub(2.f, hw));
@@ -233,9 +233,9 @@ __device__ int trace_on_group(TracePoint& p, float color, float weight, const fl
 			bestV = fadd(bestV, fmul(step, dy));
 			bestEnergy = energy;
 		}
-		if (fabsf(stepBack) < 0.1f) break;                                              // :374 setting_trace_GNThreshold
+		if (fabsf(stepBack) < ST.trace_GNThreshold) break;                              // :374 setting_trace_GNThreshold
 	}
-	if (!(bestEnergy < fmul(p.energyTH, 1.2f)))                                         // :380-391 setting_trace_extraSlackOnTH
+	if (!(bestEnergy < fmul(p.energyTH, ST.trace_extraSlackOnTH)))                      // :380-391 setting_trace_extraSlackOnTH
 	{
 		p.interval = 0.f; p.uv0 = -1.f; p.uv1 = -1.f;
 		if (p.status == IPS_OUTLIER) return p.status = IPS_OOB;
@@ -262,7 +262,7 @@ __device__ int trace_on_group(TracePoint& p, float color, float weight, const fl
 	return p.status = IPS_GOOD;
 }
 
-__global__ void __launch_bounds__(256) trace_on_kernel(int n, const float4* __restrict__ img, int w, int h, TraceHosts H,
+__global__ void __launch_bounds__(256) trace_on_kernel(dso_b200_settings ST, int n, const float4* __restrict__ img, int w, int h, TraceHosts H,
                                                        const float* __restrict__ pu, const float* __restrict__ pv,
                                                        const float* __restrict__ color8, const float* __restrict__ weights8,
                                                        const float* __restrict__ gradH4, const float* __restrict__ energyTH,
@@ -280,7 +280,7 @@ __global__ void __launch_bounds__(256) trace_on_kernel(int n, const float4* __re
 	for (int q = 0; q < 4; q++) p.G[q] = gradH4[4 * (size_t)k + q];
 	p.status = status[k]; p.uv0 = uv2[2 * (size_t)k]; p.uv1 = uv2[2 * (size_t)k + 1]; p.interval = interval[k];
 	const int hst = host[k];
-	trace_on_group(p, color8[8 * (size_t)k + idx], weights8[8 * (size_t)k + idx], img, w, h, H.KRKi[hst], H.Kt[hst], H.aff[hst],
+	trace_on_group(ST, p, color8[8 * (size_t)k + idx], weights8[8 * (size_t)k + idx], img, w, h, H.KRKi[hst], H.Kt[hst], H.aff[hst],
 	               s_err[g], idx, base, gmask);
 	if (idx == 0)
 	{
@@ -372,7 +372,7 @@ extern "C" int dso_b200_trace_new_coarse(dso_b200_ctx* ctx, int frame_slot, int 
 	}
 	cudaStream_t s = ctx->ba_stream;
 	const int n = T->n;
-	trace_on_kernel<<<(n + TR_PTS_PER_BLOCK - 1) / TR_PTS_PER_BLOCK, 256, 0, s>>>(n, F.pyr[0], F.w, F.h, H, T->d_u, T->d_v, T->d_color, T->d_weights, T->d_gradH,
+	trace_on_kernel<<<(n + TR_PTS_PER_BLOCK - 1) / TR_PTS_PER_BLOCK, 256, 0, s>>>(ctx->settings, n, F.pyr[0], F.w, F.h, H, T->d_u, T->d_v, T->d_color, T->d_weights, T->d_gradH,
 	                                                                             T->d_energyTH, T->d_host, T->d_idmin, T->d_idmax, T->d_quality, T->d_status,
 	                                                                             T->d_uv, T->d_interval);
 	LAUNCHED(ctx, 1);
@@ -411,7 +411,7 @@ struct ActTargets
 struct ActRes { int state, newState; float energy, newEnergy; };
 
 // linearizeResidual for target t; returns the value the reference returns (as double), updates Hdd / bd
-__device__ __forceinline__ double act_linearize(const ActTargets& A, int t, float pu, float pv, float color, float weight, float energyTH,
+__device__ __forceinline__ double act_linearize(const dso_b200_settings& ST, const ActTargets& A, int t, float pu, float pv, float color, float weight, float energyTH,
                                                 float slack, ActRes& r, float& Hdd, float& bd, float idepth, int idx, int base, unsigned gmask)
 {
 	if (r.state == RS_OOB) { r.newState = RS_OOB; return (double)r.energy; }            // :505-506
@@ -441,7 +441,7 @@ __device__ __forceinline__ double act_linearize(const ActTargets& A, int t, floa
 		{
 			const float residual = fsub(h0, fadd(fmul(A.aff[t][0], color), A.aff[t][1]));
 			const float ar = fabsf(residual);
-			float hw = ar < 9.f ? 1.f : fdiv(9.f, ar);
+			float hw = ar < ST.huberTH ? 1.f : fdiv(ST.huberTH, ar);
 			tE = fmul(fmul(fmul(fmul(fmul(weight, weight), hw), residual), residual), fsub(2.f, hw));
 			const float dxI = fmul(h1, A.fxl), dyI = fmul(h2, A.fyl);
 			const float d_id = fmul(fadd(fmul(fmul(dxI, drescale), fsub(tt[0], fmul(tt[2], u))), fmul(fmul(dyI, drescale), fsub(tt[1], fmul(tt[2], v)))), 1.0f);
@@ -468,7 +468,7 @@ __device__ __forceinline__ double act_linearize(const ActTargets& A, int t, floa
 	return (double)energyLeft;
 }
 
-__global__ void __launch_bounds__(256) optimize_immature_kernel(int n, ActTargets A, int minObs, const float* __restrict__ pu, const float* __restrict__ pv,
+__global__ void __launch_bounds__(256) optimize_immature_kernel(dso_b200_settings ST, int n, ActTargets A, int minObs, const float* __restrict__ pu, const float* __restrict__ pv,
                                                                 const float* __restrict__ color8, const float* __restrict__ weights8,
                                                                 const float* __restrict__ energyTH, const float* __restrict__ idmin,
                                                                 const float* __restrict__ idmax, int* result, float* idepth_out, int* res_state)
@@ -488,15 +488,15 @@ __global__ void __launch_bounds__(256) optimize_immature_kernel(int n, ActTarget
 	for (int t = 0; t < ACT_MAXT; t++)
 		if (t < nres)
 		{
-			lastEnergy = (float)((double)lastEnergy + act_linearize(A, t, u, v, color, weight, eTH, 1000.f, res[t], lastHdd, lastbd, currentIdepth, idx, base, gmask));
+			lastEnergy = (float)((double)lastEnergy + act_linearize(ST, A, t, u, v, color, weight, eTH, 1000.f, res[t], lastHdd, lastbd, currentIdepth, idx, base, gmask));
 			res[t].state = res[t].newState; res[t].energy = res[t].newEnergy;
 		}
 	int out = 1;
-	if (!isfinite(lastEnergy) || lastHdd < 100.f) out = 0;                                // :90-97 setting_minIdepthH_act
+	if (!isfinite(lastEnergy) || lastHdd < ST.minIdepthH_act) out = 0;                     // :90-97 setting_minIdepthH_act
 	if (out)
 	{
 		float lambda = 0.1f;
-		for (int iteration = 0; iteration < 3; iteration++)                               // setting_GNItsOnPointActivation
+		for (int iteration = 0; iteration < ST.GNItsOnPointActivation; iteration++)       // setting_GNItsOnPointActivation
 		{
 			float H = lastHdd;
 			H = fmul(H, fadd(1.f, lambda));
@@ -506,8 +506,8 @@ __global__ void __launch_bounds__(256) optimize_immature_kernel(int n, ActTarget
 #pragma unroll
 			for (int t = 0; t < ACT_MAXT; t++)
 				if (t < nres)
-					newEnergy = (float)((double)newEnergy + act_linearize(A, t, u, v, color, weight, eTH, 1.f, res[t], newHdd, newbd, newIdepth, idx, base, gmask));
-			if (!isfinite(lastEnergy) || newHdd < 100.f) { out = 0; break; }                // :117-124
+					newEnergy = (float)((double)newEnergy + act_linearize(ST, A, t, u, v, color, weight, eTH, 1.f, res[t], newHdd, newbd, newIdepth, idx, base, gmask));
+			if (!isfinite(lastEnergy) || newHdd < ST.minIdepthH_act) { out = 0; break; }                // :117-124
 			if (newEnergy < lastEnergy)
 			{
 				currentIdepth = newIdepth; lastHdd = newHdd; lastbd = newbd; lastEnergy = newEnergy;
@@ -592,7 +592,7 @@ extern "C" int dso_b200_optimize_immature(dso_b200_ctx* ctx, int n_targets, cons
 #undef UP
 	if (e == cudaSuccess)
 	{
-		optimize_immature_kernel<<<(n + TR_PTS_PER_BLOCK - 1) / TR_PTS_PER_BLOCK, 256, 0, s>>>(n, A, minObs, d_u, d_v, d_c, d_w, d_e, d_lo, d_hi, d_res, d_id, d_rs);
+		optimize_immature_kernel<<<(n + TR_PTS_PER_BLOCK - 1) / TR_PTS_PER_BLOCK, 256, 0, s>>>(ctx->settings, n, A, minObs, d_u, d_v, d_c, d_w, d_e, d_lo, d_hi, d_res, d_id, d_rs);
 		LAUNCHED(ctx, 1);
 		e = cudaGetLastError();
 	}

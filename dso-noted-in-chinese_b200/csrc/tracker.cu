@@ -1406,7 +1406,7 @@ extern "C" int dso_b200_calc_res(dso_b200_ctx* ctx, int trk, int frame_slot, int
 	if (rc) return rc;
 	CK(cudaSetDevice(ctx->device));
 	Pose p; pose_from12(p, refToNew12);
-	rc = run_eval(ctx, trk, frame_slot, lvl, p, aff_a, aff_b, new_ab_exposure, cutoffTH, 9.0f, false, nullptr, nullptr);
+	rc = run_eval(ctx, trk, frame_slot, lvl, p, aff_a, aff_b, new_ab_exposure, cutoffTH, ctx->settings.huberTH, false, nullptr, nullptr);
 	if (rc) return rc;
 	EvalResult er;
 	sums_to_result(ctx->trk[trk].h_sums, er);
@@ -1438,7 +1438,7 @@ extern "C" int dso_b200_calc_res_debug(dso_b200_ctx* ctx, int trk, int frame_slo
 	CK(cudaMalloc(&d_warped, sizeof(float) * 8 * (size_t)(n + 1)));
 	CK(cudaMemsetAsync(d_warped, 0, sizeof(float) * 8 * (size_t)(n + 1), T.stream));
 	Pose p; pose_from12(p, refToNew12);
-	rc = run_eval(ctx, trk, frame_slot, lvl, p, aff_a, aff_b, new_ab_exposure, cutoffTH, 9.0f, true, d_status, d_warped);
+	rc = run_eval(ctx, trk, frame_slot, lvl, p, aff_a, aff_b, new_ab_exposure, cutoffTH, ctx->settings.huberTH, true, d_status, d_warped);
 	if (!rc)
 	{
 		cudaMemcpy(status_out, d_status, n, cudaMemcpyDeviceToHost);
@@ -1458,7 +1458,7 @@ extern "C" int dso_b200_track_hostloop(dso_b200_ctx* ctx, int trk, int frame_slo
 	ARG_CHECK(coarsestLvl < 5, "coarsestLvl must be < 5 (CoarseTracker.cpp:561)");
 	CK(cudaSetDevice(ctx->device));
 	dso_b200_track_opts o;
-	if (opts) o = *opts; else dso_b200_track_opts_default(&o);
+	if (opts) o = *opts; else { dso_b200_track_opts_default(&o); o.huberTH = ctx->settings.huberTH; }
 	LM lm;
 	TrackLevels TL0;
 	fill_levels(ctx, ctx->trk[trk], &ctx->slots[frame_slot], new_ab_exposure, TL0);
@@ -1512,7 +1512,7 @@ static int enqueue_track(dso_b200_ctx* ctx, int trk, int frame_slot, int nHyp, c
 	CK(cudaSetDevice(ctx->device));
 	TrackerSlot& T = ctx->trk[trk];
 	dso_b200_track_opts o;
-	if (opts) o = *opts; else dso_b200_track_opts_default(&o);
+	if (opts) o = *opts; else { dso_b200_track_opts_default(&o); o.huberTH = ctx->settings.huberTH; }
 	// pageable staging: cudaMemcpyAsync returns once the source has been copied to the driver's staging
 	// area, so back-to-back asynchronous calls may reuse it
 	static_assert(sizeof(TrackIn) * DSO_B200_MAX_HYP <= TRACK_IN_BLOCK, "input block too small");

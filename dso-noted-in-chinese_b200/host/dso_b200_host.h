@@ -164,6 +164,47 @@ struct WindowArrays
 	const int *res_point, *res_target, *res_state; const double* res_energy; const unsigned char *res_isLinearized, *res_isActive;   // per residual
 };
 
+class EnergyFunctional;
+
+// PointFrameResidual (FullSystem/Residuals.h:56-112): the per-object methods remain.  FullSystem::linearizeAll works on the
+// whole window (EnergyFunctional::linearizeAll below); the serial callers of the per-object form -- flagPointsForRemoval,
+// FullSystem.cpp:776-787 -- go through a ResidualBatch that forwards a batch of 1..k residuals in one call.
+enum ResState { IN = 0, OOB, OUTLIER };             // Residuals.h:47
+struct PointFrameResidual
+{
+	int idx;                        // position in EFPoint::residualsAll order, as uploaded by EnergyFunctional::setWindow
+	ResState state_state, state_NewState;
+	double state_energy, state_NewEnergy;
+	bool isActive;                  // efResidual->isActive()
+	explicit PointFrameResidual(int i) : idx(i), state_state(IN), state_NewState(OUTLIER), state_energy(0), state_NewEnergy(0), isActive(false) {}
+};
+class ResidualBatch
+{
+public:
+	explicit ResidualBatch(DeviceContext* d) : dev(d) {}
+	void add(PointFrameResidual* r) { rs.push_back(r); }
+	// for every added residual: r->resetOOB(); r->linearize(HCalib); r->applyRes(true)   (Residuals.h:101-108, :95, :110)
+	void resetOOB_linearize_applyRes()
+	{
+		const int k = (int)rs.size();
+		if (!k) return;
+		std::vector<int> idx(k), ns(k); std::vector<float> ne(k); std::vector<unsigned char> ia(k);
+		for (int q = 0; q < k; q++) idx[q] = rs[q]->idx;
+		DSO_B200_CHECK(dso_b200_ba_linearize_residuals(dev->ctx, k, idx.data(), 1, 1, ns.data(), ne.data(), ia.data()));
+		for (int q = 0; q < k; q++)
+		{
+			PointFrameResidual* r = rs[q];
+			r->state_NewState = (ResState)ns[q]; r->state_NewEnergy = ne[q];
+			r->state_state = r->state_NewState; r->state_energy = r->state_NewEnergy;     // applyRes, Residuals.cpp:344-345
+			r->isActive = ia[q] != 0;
+		}
+		rs.clear();
+	}
+private:
+	DeviceContext* dev;
+	std::vector<PointFrameResidual*> rs;
+};
+
 class EnergyFunctional
 {
 public:

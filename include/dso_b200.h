@@ -65,6 +65,27 @@ void dso_b200_host_free(void* p);
 /* number of kernels this library has launched on this context since creation */
 long long dso_b200_launch_count(dso_b200_ctx* ctx);
 
+/* The reference's global settings that the kernels of this library read (util/settings.cpp; the line of each definition is
+ * given).  The reference reads its globals at call time, so a caller that changes them calls dso_b200_set_settings again;
+ * a new context starts with the defaults below.  The tracker's own settings travel in dso_b200_track_opts. */
+typedef struct
+{
+	float huberTH;                      /* setting_huberTH = 9 (:127): calcRes, PointFrameResidual::linearize, traceOn, linearizeResidual */
+	float outlierTHSumComponent;        /* setting_outlierTHSumComponent = 50*50 (:91): PointFrameResidual::linearize */
+	float maxPixSearch;                 /* setting_maxPixSearch = 0.027 (:156): traceOn */
+	int minTraceTestRadius;             /* setting_minTraceTestRadius = 2 (:158) */
+	int GNItsOnPointActivation;         /* setting_GNItsOnPointActivation = 3 (:159): optimizeImmaturePoint */
+	float trace_stepsize;               /* setting_trace_stepsize = 1.0 (:160) */
+	int trace_GNIterations;             /* setting_trace_GNIterations = 3 (:161) */
+	float trace_GNThreshold;            /* setting_trace_GNThreshold = 0.1 (:162) */
+	float trace_extraSlackOnTH;         /* setting_trace_extraSlackOnTH = 1.2 (:163) */
+	float trace_slackInterval;          /* setting_trace_slackInterval = 1.5 (:164) */
+	float trace_minImprovementFactor;   /* setting_trace_minImprovementFactor = 2 (:165) */
+	float minIdepthH_act;               /* setting_minIdepthH_act = 100 (:67): optimizeImmaturePoint */
+} dso_b200_settings;
+void dso_b200_settings_default(dso_b200_settings* s);
+int dso_b200_set_settings(dso_b200_ctx* ctx, const dso_b200_settings* s);
+
 /* ---- K1: FrameHessian::makeImages (FullSystem/HessianBlocks.cpp:137-211, decl HessianBlocks.h:282) */
 /* color: w*h irradiance floats (ImageAndExposure::image).  B_lut: 256 floats (CalibHessian::B,
  * HessianBlocks.h:399) or NULL (= the "HCalib==0 / setting_gammaWeightsPixelSelect!=1" branch).
@@ -300,6 +321,14 @@ int dso_b200_ba_set_residuals(dso_b200_ctx* ctx, int nR, const int* point, const
  * Jpdd(2) JIdx0(8) JIdx1(8) JabF0(8) JabF1(8) JIdx2(4) JabJIdx(4) Jab2(4)), and the energy sum. */
 int dso_b200_ba_linearize(dso_b200_ctx* ctx, int* newState, float* newEnergy, float* newEnergyWithOutlier,
                           float* centerProjectedTo3, float* projectedTo16, float* J74, double* energy_sum);
+/* The per-object form of the two calls around this comment: PointFrameResidual::linearize (decl FullSystem/Residuals.h:95)
+ * and, with apply != 0, PointFrameResidual::applyRes(true) (Residuals.h:110) for the k residuals listed in residual_idx
+ * (indices into the array given to dso_b200_ba_set_residuals); with reset_oob != 0 PointFrameResidual::resetOOB
+ * (Residuals.h:101-108) comes first.  This is the serial loop of FullSystem::flagPointsForRemoval (FullSystem.cpp:776-787)
+ * as one batch; the other residuals are not touched.  Outputs (k entries each, may be NULL): state_NewState,
+ * state_NewEnergy, EFResidual::isActive() after applyRes. */
+int dso_b200_ba_linearize_residuals(dso_b200_ctx* ctx, int k, const int* residual_idx, int reset_oob, int apply,
+                                    int* newState_out, float* newEnergy_out, unsigned char* isActive_out);
 /* PointFrameResidual::applyRes(true) for all residuals (Residuals.cpp:323-347) including
  * EFResidual::takeDataF (EnergyFunctionalStructs.cpp:39-49).  Outputs may be NULL. */
 int dso_b200_ba_apply_res(dso_b200_ctx* ctx, unsigned char* isActive_out, float* JpJdF8_out);

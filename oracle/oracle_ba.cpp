@@ -5,6 +5,7 @@
 // Compile with -ffp-contract=off.
 #include "dso_oracle.h"
 #include "oracle_math.h"
+#include "oracle_settings.h"
 #include <vector>
 #include <thread>
 #include <mutex>
@@ -28,8 +29,7 @@ static const int patternP[8][2] = { {0,-2}, {-1,-1}, {1,-1}, {-2,0}, {0,0}, {2,0
 #define SCALE_A 10.0f
 #define SCALE_B 1000.0f
 // settings.cpp:103,110,124-125
-static const float setting_outlierTHSumComponent = 50 * 50;
-static const float setting_huberTH = 9;
+// setting_outlierTHSumComponent, setting_huberTH: run-time values (oracle_settings.h)
 extern float dso_oracle_setting_affineOptModeA, dso_oracle_setting_affineOptModeB;   // oracle_tracker.cpp (settings.cpp:119-120)
 #define setting_affineOptModeA dso_oracle_setting_affineOptModeA
 #define setting_affineOptModeB dso_oracle_setting_affineOptModeB
@@ -708,12 +708,38 @@ extern "C" double dso_oracle_ba_linearize_mt(dso_oracle_ba* B, int nthreads)
 }
 
 // applyRes(true), Residuals.cpp:323-347 + EFResidual::takeDataF, EnergyFunctionalStructs.cpp:39-49
+static void apply_one(Res& r);
 extern "C" void dso_oracle_ba_apply_res(dso_oracle_ba* B, unsigned char* isActive_out, float* JpJdF_out)
 {
 	int nR = (int)B->res.size();
 	for (int i = 0; i < nR; i++)
 	{
 		Res& r = B->res[i];
+		apply_one(r);
+		if (isActive_out) isActive_out[i] = r.isActive;
+		if (JpJdF_out) memcpy(JpJdF_out + 8 * i, r.JpJdF, 32);
+	}
+}
+// the per-object sequence of FullSystem::flagPointsForRemoval (FullSystem.cpp:776-787) for the listed residuals:
+// resetOOB (Residuals.h:101-108), linearize (Residuals.cpp:78), applyRes(true) (Residuals.cpp:323)
+extern "C" void dso_oracle_ba_linearize_residuals(dso_oracle_ba* B, int k, const int* idx, int reset_oob, int apply,
+                                                  int* newState, float* newEnergy, unsigned char* isActive)
+{
+	for (int q = 0; q < k; q++)
+	{
+		Res& r = B->res[idx[q]];
+		if (reset_oob) { r.state_NewEnergy = r.state_energy = 0; r.state_NewState = ST_OUTLIER; r.state_state = ST_IN; }
+		linearize(B, r);
+		if (apply) apply_one(r);
+		if (newState) newState[q] = r.state_NewState;
+		if (newEnergy) newEnergy[q] = (float)r.state_NewEnergy;
+		if (isActive) isActive[q] = r.isActive;
+	}
+}
+static void apply_one(Res& r)
+{
+	{
+		{
 		if (r.state_state != ST_OOB)
 		{
 			if (r.state_NewState == ST_IN)
@@ -734,8 +760,7 @@ extern "C" void dso_oracle_ba_apply_res(dso_oracle_ba* B, unsigned char* isActiv
 			r.state_state = r.state_NewState;
 			r.state_energy = r.state_NewEnergy;
 		}
-		if (isActive_out) isActive_out[i] = r.isActive;
-		if (JpJdF_out) memcpy(JpJdF_out + 8 * i, r.JpJdF, 32);
+		}
 	}
 }
 

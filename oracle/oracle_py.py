@@ -76,6 +76,7 @@ def lib(kind="oracle"):
             f.restype = restype
 
     sig("dso_oracle_set_affine_modes", [C.c_float, C.c_float])
+    sig("dso_oracle_set_settings", [vp])
     sig("dso_oracle_make_images", [f32p, C.c_int, C.c_int, C.c_int, vp, C.POINTER(vp), C.POINTER(vp)])
     sig("dso_oracle_tracker_create", [C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float], vp)
     sig("dso_oracle_tracker_destroy", [vp])
@@ -101,6 +102,7 @@ def lib(kind="oracle"):
     sig("dso_oracle_ba_linearize", [vp, vp, vp, vp, vp, vp, vp, vp], C.c_double)
     sig("dso_oracle_ba_linearize_mt", [vp, C.c_int], C.c_double)
     sig("dso_oracle_ba_apply_res", [vp, vp, vp])
+    sig("dso_oracle_ba_linearize_residuals", [vp, C.c_int, vp, C.c_int, C.c_int, vp, vp, vp])
     sig("dso_oracle_ba_accumulate_A", [vp, C.c_int, C.c_int, f64p, f64p, C.POINTER(C.c_int), f32p, f32p, f32p])
     sig("dso_oracle_ba_accumulate_SC", [vp, C.c_int, C.c_int, f64p, f64p, f32p, f32p, f32p])
     sig("dso_oracle_ba_accumulate_L", [vp, C.c_int, C.c_int, f64p, f64p, C.POINTER(C.c_int), f32p, f32p, f32p])
@@ -120,6 +122,24 @@ def lib(kind="oracle"):
     sig("dso_oracle_ba_solve", [vp, C.c_int, C.c_double, C.c_int, C.c_double, C.c_int, C.c_int, vp, vp, vp, vp], C.c_int)
     _LIBS[kind] = L
     return L
+
+
+class Settings(C.Structure):
+    """util/settings.cpp values read by the restated functions; same layout as dso_b200_settings"""
+    _fields_ = [("huberTH", C.c_float), ("outlierTHSumComponent", C.c_float), ("maxPixSearch", C.c_float),
+                ("minTraceTestRadius", C.c_int), ("GNItsOnPointActivation", C.c_int), ("trace_stepsize", C.c_float),
+                ("trace_GNIterations", C.c_int), ("trace_GNThreshold", C.c_float), ("trace_extraSlackOnTH", C.c_float),
+                ("trace_slackInterval", C.c_float), ("trace_minImprovementFactor", C.c_float), ("minIdepthH_act", C.c_float)]
+
+    @staticmethod
+    def defaults():
+        return Settings(9, 50 * 50, 0.027, 2, 3, 1.0, 3, 0.1, 1.2, 1.5, 2, 100)
+
+
+def set_settings(s=None, kind="oracle"):
+    """process-wide like the reference's globals: call with no argument to restore the defaults after use.  `s` may be any
+    ctypes structure with the layout of Settings (e.g. the product binding's)."""
+    lib(kind).dso_oracle_set_settings(C.byref(s) if s is not None else None)
 
 
 def set_affine_modes(mode_a=1e12, mode_b=1e8, kind="oracle"):
@@ -327,6 +347,13 @@ class BA:
 
     def linearize_mt(self, nthreads):
         return self.L.dso_oracle_ba_linearize_mt(self.p, nthreads)
+
+    def linearize_residuals(self, idx, reset_oob=True, apply=True):
+        idx = np.ascontiguousarray(idx, dtype=np.int32)
+        k = len(idx)
+        ns, ne, ia = np.zeros(k, dtype=np.int32), np.zeros(k, dtype=np.float32), np.zeros(k, dtype=np.uint8)
+        self.L.dso_oracle_ba_linearize_residuals(self.p, k, idx.ctypes.data, int(reset_oob), int(apply), ns.ctypes.data, ne.ctypes.data, ia.ctypes.data)
+        return dict(newState=ns, newEnergy=ne, isActive=ia)
 
     def apply_res(self):
         act = np.zeros(self.nR, dtype=np.uint8)

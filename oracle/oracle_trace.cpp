@@ -8,6 +8,7 @@
 // tests/test_oracle_vs_reference.py.
 #include "dso_oracle.h"
 #include "oracle_math.h"
+#include "oracle_settings.h"
 #include <cmath>
 #include <cstring>
 #include <algorithm>
@@ -18,17 +19,8 @@ const int patternNum = 8;
 const int patternP[8][2] = { {0,-2}, {-1,-1}, {1,-1}, {-2,0}, {0,0}, {2,0}, {-1,1}, {0,2} };   // settings.cpp:274 (pattern 8)
 // util/settings.cpp:90-91, 137, 156-165, 113
 const float setting_outlierTH = 12 * 12;
-const float setting_outlierTHSumComponent = 50 * 50;
 const float setting_overallEnergyTHWeight = 1;
-const float setting_maxPixSearch = 0.027f;
-const int setting_minTraceTestRadius = 2;
-const float setting_trace_stepsize = 1.0f;
-const int setting_trace_GNIterations = 3;
-const float setting_trace_GNThreshold = 0.1f;
-const float setting_trace_extraSlackOnTH = 1.2f;
-const float setting_trace_slackInterval = 1.5f;
-const float setting_trace_minImprovementFactor = 2;
-const float setting_huberTH = 9;
+// the remaining settings of :91, :127, :156-165 are run-time values (oracle_settings.h)
 
 enum { IPS_GOOD = 0, IPS_OOB, IPS_OUTLIER, IPS_SKIPPED, IPS_BADCONDITION, IPS_UNINITIALIZED };
 
@@ -303,8 +295,7 @@ extern "C" void dso_oracle_trace_on(int w, int h, const float* frame_dI, int n, 
 // (ImmaturePoint.cpp:499-570), projectPoint (ResidualProjections.h:69-101) and derive_idepth (:39-47)
 // ---------------------------------------------------------------------------------------------------------
 namespace {
-const float setting_minIdepthH_act = 100;        // settings.cpp:67
-const int setting_GNItsOnPointActivation = 3;    // settings.cpp:159
+// setting_minIdepthH_act (settings.cpp:67) and setting_GNItsOnPointActivation (:159): oracle_settings.h
 enum { RS_IN = 0, RS_OOB = 1, RS_OUTLIER = 2 };
 
 struct Calib { float fxl, fyl, cxl, cyl, fxli, fyli, wM3G, hM3G; int w; };

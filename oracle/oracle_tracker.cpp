@@ -8,10 +8,16 @@
 #include <cstdlib>
 #include <cstdio>
 
+#include "oracle_settings.h"
 using namespace orc;
 
-// settings.cpp:110,125,138 (defaults)
-static const float setting_huberTH = 9;
+// settings.cpp defaults; run-time globals in the reference, same here (oracle_settings.h)
+dso_oracle_settings dso_oracle_set = { 9, 50 * 50, 0.027f, 2, 3, 1.0f, 3, 0.1f, 1.2f, 1.5f, 2, 100 };
+extern "C" void dso_oracle_set_settings(const dso_oracle_settings* s)
+{
+	const dso_oracle_settings d = { 9, 50 * 50, 0.027f, 2, 3, 1.0f, 3, 0.1f, 1.2f, 1.5f, 2, 100 };
+	dso_oracle_set = s ? *s : d;
+}
 static const float setting_coarseCutoffTH = 20;
 // settings.cpp:119-120 are run-time globals in the reference (-1: fixed, >= 0: optimised); same here
 float dso_oracle_setting_affineOptModeA = 1e12f;

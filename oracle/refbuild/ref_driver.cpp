@@ -96,6 +96,19 @@ struct dso_oracle_tracker
 };
 
 extern "C" void dso_ref_set_affine_modes(float modeA, float modeB) { setting_affineOptModeA = modeA; setting_affineOptModeB = modeB; }
+// the reference's own globals (util/settings.cpp), same block as dso_oracle_set_settings; NULL restores the defaults
+struct ref_settings { float huberTH, outlierTHSumComponent, maxPixSearch; int minTraceTestRadius, GNItsOnPointActivation; float trace_stepsize;
+                      int trace_GNIterations; float trace_GNThreshold, trace_extraSlackOnTH, trace_slackInterval, trace_minImprovementFactor, minIdepthH_act; };
+extern "C" void dso_ref_set_settings(const ref_settings* p)
+{
+	const ref_settings d = { 9, 50 * 50, 0.027f, 2, 3, 1.0f, 3, 0.1f, 1.2f, 1.5f, 2, 100 };
+	const ref_settings s = p ? *p : d;
+	setting_huberTH = s.huberTH; setting_outlierTHSumComponent = s.outlierTHSumComponent; setting_maxPixSearch = s.maxPixSearch;
+	setting_minTraceTestRadius = s.minTraceTestRadius; setting_GNItsOnPointActivation = s.GNItsOnPointActivation;
+	setting_trace_stepsize = s.trace_stepsize; setting_trace_GNIterations = s.trace_GNIterations; setting_trace_GNThreshold = s.trace_GNThreshold;
+	setting_trace_extraSlackOnTH = s.trace_extraSlackOnTH; setting_trace_slackInterval = s.trace_slackInterval;
+	setting_trace_minImprovementFactor = s.trace_minImprovementFactor; setting_minIdepthH_act = s.minIdepthH_act;
+}
 
 extern "C" dso_oracle_tracker* dso_ref_tracker_create(int w, int h, int levels, float fx, float fy, float cx, float cy)
 {
@@ -396,6 +409,21 @@ extern "C" void dso_ref_ba_apply_res(dso_oracle_ba* B, unsigned char* isActive_o
 		B->res[i]->applyRes(true);                             // Residuals.cpp:323
 		if (isActive_out) isActive_out[i] = B->res[i]->efResidual->isActive();
 		if (JpJdF_out) for (int k = 0; k < 8; k++) JpJdF_out[8 * i + k] = B->res[i]->efResidual->JpJdF[k];
+	}
+}
+extern "C" void dso_ref_ba_linearize_residuals(dso_oracle_ba* B, int k, const int* idx, int reset_oob, int apply,
+                                               int* newState, float* newEnergy, unsigned char* isActive)
+{
+	B->calib();
+	for (int q = 0; q < k; q++)
+	{
+		PointFrameResidual* r = B->res[idx[q]];
+		if (reset_oob) r->resetOOB();                          // Residuals.h:101
+		r->linearize(B->HCalib);                               // Residuals.cpp:78
+		if (apply) r->applyRes(true);                          // Residuals.cpp:323
+		if (newState) newState[q] = (int)r->state_NewState;
+		if (newEnergy) newEnergy[q] = (float)r->state_NewEnergy;
+		if (isActive) isActive[q] = r->efResidual->isActive();
 	}
 }
 static void export_sys(const MatXX& H, const VecX& b, double* Ho, double* bo)

@@ -156,3 +156,31 @@ def test_ba_fixed_affine_modes(pkg, oracle, window_small, modes):
     finally:
         oracle.set_affine_modes()
         ctx.close()
+
+
+@pytest.mark.parametrize("which", ["small", "vga"])
+def test_per_object_linearize_forwarder(pkg, oracle, request, which):
+    """dso_b200_ba_linearize_residuals: the per-object PointFrameResidual::linearize (Residuals.h:95) / resetOOB / applyRes
+    sequence of FullSystem::flagPointsForRemoval (FullSystem.cpp:776-787) as one batch of k residuals, against the oracle
+    (pinned to the reference build in test_oracle_vs_reference.py::test_per_object_linearize_apply)"""
+    W = request.getfixturevalue("window_" + which)
+    B, ctx = _setup(pkg, oracle, W)
+    B.linearize(); B.apply_res()
+    ctx.ba_linearize(); ctx.ba_apply_res()
+    idx = np.nonzero(W.res_point % 7 == 3)[0].astype(np.int32)
+    po = B.linearize_residuals(idx, reset_oob=True, apply=True)
+    pg = ctx.ba_linearize_residuals(idx, reset_oob=True, apply=True)
+    assert np.array_equal(po["newState"], pg["newState"]) and np.array_equal(po["isActive"], pg["isActive"])
+    assert np.array_equal(po["newEnergy"].view(np.uint32), pg["newEnergy"].view(np.uint32))
+    assert (po["newState"] == 0).sum() > 0
+    # the rest of the window is untouched and the swapped-in Jacobians feed the next accumulation
+    Ao, Ag = B.accumulate_A(False), ctx.ba_accumulate_A()
+    assert Ao["resInA"] == Ag["resInA"]
+    for key in ("Hdd", "bd", "Hcd"):
+        assert np.array_equal(Ao[key].view(np.uint32), Ag[key].view(np.uint32)), key
+    _check_system(Ag["H"], Ag["b"], Ao["H"], Ao["b"])
+    # a batch of one
+    p1o = B.linearize_residuals(idx[:1], reset_oob=True, apply=False)
+    p1g = ctx.ba_linearize_residuals(idx[:1], reset_oob=True, apply=False)
+    assert p1o["newState"][0] == p1g["newState"][0] and p1o["newEnergy"].view(np.uint32)[0] == p1g["newEnergy"].view(np.uint32)[0]
+    ctx.close()

@@ -304,3 +304,83 @@ def test_optimize_immature_point_bit_exact(pkg, win):
     assert np.array_equal(so[ro != 0], sr[rr != 0])
     good = ok & ~sc["wrong"]
     assert np.median(np.abs(io[good] - sc["idepth_true"][good]) / sc["idepth_true"][good]) < 0.01      # converges to the true depth
+
+
+def test_non_default_settings_bit_exact(pkg, window_small):
+    """the run-time settings of util/settings.cpp that the hot path reads (huberTH :127, outlierTHSumComponent :91, maxPixSearch
+    :156, the setting_trace_* family :160-165, minTraceTestRadius :158, GNItsOnPointActivation :159, minIdepthH_act :67) changed
+    in both builds: the restatement must still match the reference's own code bit for bit"""
+    W = window_small
+    syn = pkg.synthetic
+    s = O.Settings(6.0, 30.0 * 30.0, 0.02, 3, 2, 0.8, 2, 0.2, 1.5, 2.5, 3.0, 50.0)
+    try:
+        O.set_settings(s)
+        O.set_settings(s, kind="ref")
+        # tracker: calcRes / calcGSSSE with another Huber threshold
+        levels = syn.pyr_levels_for(W.w, W.h)
+        ref_pyr = O.make_images(W.images[-1], levels)
+        cu, cv, cid, hdi = syn.tracker_reference_inputs(W)
+        a0, b0 = W.aff_true[-1]
+        img, rel, aff = syn.tracking_sequence(W, 1)[0]
+        pyr = O.make_images(img, levels)
+        res = []
+        for kind in ("oracle", "ref"):
+            t = O.Tracker(W.w, W.h, levels, *W.K, kind=kind)
+            t.set_ref(cu, cv, cid, hdi, flat(ref_pyr[0]), a0, b0, 1.0)
+            t.set_new_frame(flat(pyr[0]), 1.0)
+            r = t.calc_res(1, syn.pose12(rel), aff[0], aff[1], 20.0)
+            H, b = t.calc_gs(1, aff[0], aff[1])
+            res.append((r, H, b))
+        for x, y in zip(res[0], res[1]):
+            assert np.array_equal(bits(np.asarray(x)), bits(np.asarray(y)))
+        # BA: linearize with other huber / gradient-weight thresholds
+        p0 = [O.make_images(im, 1)[0][0] for im in W.images]
+        lo, lr = O.BA(W, p0).linearize(), O.BA(W, p0, kind="ref").linearize()
+        ok = lo["newState"] != 1
+        assert np.array_equal(lo["newState"], lr["newState"]) and np.array_equal(bits(lo["J"][ok]), bits(lr["J"][ok]))
+        # immature points: traceOn and optimizeImmaturePoint
+        sc = syn.immature_scenario(W, host_idx=1, n_points=400, n_frames=2)
+        hostI = O.make_images(sc["host_image"], 1)[0][0]
+        fo = O.immature_init(hostI, sc["u"], sc["v"])
+        so, sr = O.trace_state(len(sc["u"])), O.trace_state(len(sc["u"]))
+        for fr_ in sc["frames"]:
+            dI = O.make_images(fr_["image"], 1)[0][0]
+            O.trace_on(dI, sc["u"], sc["v"], fo, so, fr_["KRKi"], fr_["Kt"], fr_["aff"])
+            O.trace_on(dI, sc["u"], sc["v"], fo, sr, fr_["KRKi"], fr_["Kt"], fr_["aff"], kind="ref")
+            assert np.array_equal(so["status"], sr["status"])
+            for k in ("idepth_min", "idepth_max", "quality", "uv", "interval"):
+                assert np.array_equal(bits(so[k]), bits(sr[k])), k
+        ac = syn.activation_scenario(W, host_idx=1, n_points=400)
+        fields = O.immature_init(O.make_images(ac["host_image"], 1)[0][0], ac["u"], ac["v"])
+        dIs = [O.make_images(im, 1)[0][0] for im in ac["images"]]
+        args = (W.K, dIs, ac["RTll"], ac["tTll"], ac["aff"], ac["u"], ac["v"], fields, ac["idepth_min"], ac["idepth_max"])
+        ro, io, _ = O.optimize_immature(*args, min_obs=1)
+        rr, ir, _ = O.optimize_immature(*args, min_obs=1, kind="ref")
+        assert np.array_equal(ro, rr) and np.array_equal(bits(io[ro == 1]), bits(ir[rr == 1]))
+    finally:
+        O.set_settings()
+        O.set_settings(kind="ref")
+    # and the change was not a no-op: the default settings give other Jacobians
+    ld = O.BA(W, p0).linearize()
+    assert not np.array_equal(bits(ld["J"]), bits(lo["J"]))
+
+
+def test_per_object_linearize_apply(pkg, win):
+    """the serial per-object calls of FullSystem::flagPointsForRemoval (FullSystem.cpp:776-787): r->resetOOB();
+    r->linearize(&Hcalib); r->applyRes(true) on the residuals of a few points, after a regular linearizeAll + applyRes"""
+    W = win
+    pyr = [O.make_images(img, 1)[0][0] for img in W.images]
+    Bo, Br = O.BA(W, pyr), O.BA(W, pyr, kind="ref")
+    idx = np.nonzero(W.res_point % 7 == 3)[0].astype(np.int32)
+    assert len(idx) > 20
+    outs = []
+    for B in (Bo, Br):
+        B.linearize(); B.apply_res()
+        outs.append(B.linearize_residuals(idx, reset_oob=True, apply=True))
+        outs.append(B.accumulate_A(False))
+    (po, Ao, pr, Ar) = outs[0], outs[1], outs[2], outs[3]
+    assert np.array_equal(po["newState"], pr["newState"]) and np.array_equal(po["isActive"], pr["isActive"])
+    assert np.array_equal(bits(po["newEnergy"]), bits(pr["newEnergy"]))
+    assert (po["newState"] == 0).sum() > 0
+    for key in ("Hdd", "bd", "Hcd"):
+        assert np.array_equal(bits(Ao[key]), bits(Ar[key])), key      # the swapped-in Jacobians feed the next accumulation
