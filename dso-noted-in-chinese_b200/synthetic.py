@@ -426,3 +426,42 @@ def activation_scenario(W, host_idx=2, n_points=800, seed=0, interval=0.05):
                 RTll=np.ascontiguousarray(np.stack(RT)), tTll=np.ascontiguousarray(np.stack(tT)), aff=np.ascontiguousarray(np.stack(aff)),
                 idepth_min=(centre * (1 - interval)).astype(np.float32), idepth_max=(centre * (1 + interval)).astype(np.float32),
                 idepth_true=idt, wrong=wrong)
+
+
+def initializer_scenario(W, lvl=1, n_points=1500, seed=0, unit_depth=False):
+    """Inputs of CoarseInitializer::calcResAndGS (FullSystem/CoarseInitializer.cpp:370-732) on pyramid level `lvl`: the
+    newest key frame plays the first frame, a follow-up frame the new one; points on textured pixels of that level with
+    their inverse depths (the truth with a little noise, or 1 as trackFrame sets them before the first snap, :111-126),
+    a tenth of them flagged bad, a few with a tiny outlier threshold (energy > outlierTH*20 exit), previous energies, iR."""
+    rng = np.random.default_rng(seed + 11000 + lvl)
+    img, rel, aff = tracking_sequence(W, 1, seed=seed)[0]
+    first = W.images[-1]
+    wl, hl = W.w >> lvl, W.h >> lvl
+    # level-lvl intensity of the first frame for picking textured pixels (2x2 means, like makeImages)
+    I = first.astype(np.float32)
+    for _ in range(lvl):
+        I = 0.25 * (I[0::2, 0::2] + I[1::2, 0::2] + I[0::2, 1::2] + I[1::2, 1::2])
+    gx = np.zeros_like(I); gy = np.zeros_like(I)
+    gx[:, 1:-1] = 0.5 * (I[:, 2:] - I[:, :-2]); gy[1:-1, :] = 0.5 * (I[2:, :] - I[:-2, :])
+    g2 = gx * gx + gy * gy
+    m = 4
+    ys, xs = np.nonzero(g2[m:hl - m, m:wl - m] > np.percentile(g2, 60))
+    sel = rng.choice(len(xs), size=min(n_points, len(xs)), replace=False)
+    u = (xs[sel] + m).astype(np.float32) + np.float32(0.1)          # setFirst stores x + 0.1, y + 0.1 (:779-780)
+    v = (ys[sel] + m).astype(np.float32) + np.float32(0.1)
+    s = 1 << lvl
+    depth = W.depths[-1][np.minimum((v * s).astype(int), W.h - 1), np.minimum((u * s).astype(int), W.w - 1)]
+    n = len(u)
+    if unit_depth:
+        idepth = np.ones(n, dtype=np.float32)
+        # the initialiser's scale: unit inverse depth <-> translation scaled by the mean depth
+        rel = (rel[0], rel[1] / float(np.mean(depth)))
+    else:
+        idepth = (1.0 / depth * (1 + rng.normal(0, 0.02, n))).astype(np.float32)
+    isGood = (rng.uniform(size=n) > 0.1).astype(np.uint8)
+    energy = np.stack([rng.uniform(50, 400, n), rng.uniform(0, 1, n)], axis=1).astype(np.float32)
+    outlierTH = np.full(n, 8 * 12 * 12, dtype=np.float32)            # patternNum * setting_outlierTH (:786)
+    outlierTH[rng.uniform(size=n) < 0.05] = 0.01
+    iR = (idepth * (1 + rng.normal(0, 0.05, n))).astype(np.float32)
+    return dict(first=first, new=img, lvl=lvl, u=u, v=v, idepth_new=idepth, isGood=isGood, energy=energy, outlierTH=outlierTH,
+                iR=iR, pose12=pose12(rel), aff=(float(aff[0]), float(aff[1])), alphaW=150.0 * 150.0, alphaK=2.5 * 2.5, couplingWeight=1.0)

@@ -77,6 +77,10 @@ def lib(kind="oracle"):
 
     sig("dso_oracle_set_affine_modes", [C.c_float, C.c_float])
     sig("dso_oracle_set_settings", [vp])
+    sig("dso_oracle_init_make_K", [C.c_float] * 4 + [C.c_int, f64p, f64p])
+    sig("dso_oracle_init_calc_res_and_gs", [C.c_int, C.c_int, C.c_int] + [C.c_float] * 4 + [f32p, f32p, f64p, C.c_double, C.c_double,
+                                            C.c_int, f32p, f32p, f32p, u8p, f32p, f32p, f32p, C.c_float, C.c_float, C.c_float,
+                                            f32p, f32p, f32p, f32p, f32p, u8p, f32p, f32p, f32p, f32p])
     sig("dso_oracle_make_images", [f32p, C.c_int, C.c_int, C.c_int, vp, C.POINTER(vp), C.POINTER(vp)])
     sig("dso_oracle_tracker_create", [C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float], vp)
     sig("dso_oracle_tracker_destroy", [vp])
@@ -199,6 +203,35 @@ def optimize_immature(K, target_dIs, RTll, tTll, aff, u, v, fields, idepth_min, 
                                            f(fields["color"]), f(fields["weights"]), f(fields["energyTH"]), f(idepth_min), f(idepth_max),
                                            min_obs, result, idp, rs)
     return result, idp, rs.reshape(n, nT)
+
+
+def init_make_K(K, lvl, kind="oracle"):
+    """CoarseInitializer::makeK for one level: (fx, fy, cx, cy) and K^-1 in double"""
+    k4, Ki = np.zeros(4), np.zeros(9)
+    lib(kind).dso_oracle_init_make_K(K[0], K[1], K[2], K[3], lvl, k4, Ki)
+    return k4, Ki.reshape(3, 3)
+
+
+def init_calc_res_and_gs(K, first_dIp, new_dIp, sc, kind="oracle"):
+    """CoarseInitializer::calcResAndGS on level sc["lvl"]; first_dIp / new_dIp: dIp[lvl] ([h_l, w_l, 3]) of the two frames;
+    sc: the scenario dict of synthetic.initializer_scenario"""
+    lvl = sc["lvl"]
+    hl, wl = first_dIp.shape[:2]
+    f = lambda a: np.ascontiguousarray(a, dtype=np.float32).reshape(-1)
+    n = len(sc["u"])
+    out = dict(H=np.zeros(64, dtype=np.float32), b=np.zeros(8, dtype=np.float32), Hsc=np.zeros(64, dtype=np.float32),
+               bsc=np.zeros(8, dtype=np.float32), res=np.zeros(3, dtype=np.float32), isGood_new=np.zeros(n, dtype=np.uint8),
+               energy_new=np.zeros(2 * n, dtype=np.float32), maxstep=np.zeros(n, dtype=np.float32),
+               lastHessian_new=np.zeros(n, dtype=np.float32), Jb=np.zeros(10 * n, dtype=np.float32))
+    lib(kind).dso_oracle_init_calc_res_and_gs(wl << lvl, hl << lvl, lvl, K[0], K[1], K[2], K[3], f(first_dIp), f(new_dIp),
+                                              np.ascontiguousarray(sc["pose12"], dtype=np.float64), sc["aff"][0], sc["aff"][1],
+                                              n, f(sc["u"]), f(sc["v"]), f(sc["idepth_new"]), np.ascontiguousarray(sc["isGood"], dtype=np.uint8),
+                                              f(sc["energy"]), f(sc["outlierTH"]), f(sc["iR"]), sc["alphaW"], sc["alphaK"], sc["couplingWeight"],
+                                              out["H"], out["b"], out["Hsc"], out["bsc"], out["res"], out["isGood_new"], out["energy_new"],
+                                              out["maxstep"], out["lastHessian_new"], out["Jb"])
+    out["H"] = out["H"].reshape(8, 8); out["Hsc"] = out["Hsc"].reshape(8, 8)
+    out["energy_new"] = out["energy_new"].reshape(n, 2); out["Jb"] = out["Jb"].reshape(n, 10)
+    return out
 
 
 def _ptr_array(arrs):

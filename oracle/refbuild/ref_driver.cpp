@@ -15,6 +15,8 @@
 #include "FullSystem/Residuals.h"
 #include "FullSystem/ImmaturePoint.h"
 #include "FullSystem/CoarseTracker.h"
+#include "FullSystem/CoarseInitializer.h"
+#include "FullSystem/PixelSelector2.h"
 #include "OptimizationBackend/EnergyFunctional.h"
 #include "OptimizationBackend/EnergyFunctionalStructs.h"
 #undef private
@@ -31,6 +33,16 @@ int PointHessian::instanceCounter = 0;
 int CalibHessian::instanceCounter = 0;
 }
 using namespace dso;
+
+// FullSystem/PixelSelector2.cpp does not compile in this annotated fork (comments swallowed code at :137 and :274), so the
+// three members CoarseInitializer::setFirst links against are stubs: setFirst (point selection, kd-tree) is outside the
+// pinned path, the driver fills the Pnt arrays itself.
+namespace dso
+{
+PixelSelector::PixelSelector(int, int) { abort(); }
+PixelSelector::~PixelSelector() {}
+int PixelSelector::makeMaps(const FrameHessian* const, float*, float, int, bool, float) { abort(); return 0; }
+}
 
 static void set_calib(int w, int h, int levels, float fx, float fy, float cx, float cy)
 {
@@ -673,4 +685,65 @@ extern "C" void dso_ref_optimize_immature(int w, int h, float fx, float fy, floa
 		for (int t = 0; t < nT; t++) res_state_out[k * nT + t] = (int)tmp[t].state_state;
 	}
 	for (FrameHessian* fh : fs->frameHessians) release_frame(fh);
+}
+
+
+// ---- N4: CoarseInitializer::calcResAndGS (FullSystem/CoarseInitializer.cpp:370-732, compiled unmodified) ----
+extern "C" void dso_ref_init_make_K(float fx0, float fy0, float cx0, float cy0, int lvl, double* fxfycxcy4, double* Ki9)
+{
+	// makeK reads wG/hG/pyrLevelsUsed and the CalibHessian; any image size will do for the intrinsics
+	set_calib(640, 480, lvl + 1, fx0, fy0, cx0, cy0);
+	CalibHessian HCalib;
+	CoarseInitializer ci(640, 480);
+	ci.makeK(&HCalib);                                           // :1126
+	fxfycxcy4[0] = ci.fx[lvl]; fxfycxcy4[1] = ci.fy[lvl]; fxfycxcy4[2] = ci.cx[lvl]; fxfycxcy4[3] = ci.cy[lvl];
+	for (int r = 0; r < 3; r++) for (int c = 0; c < 3; c++) Ki9[r * 3 + c] = ci.Ki[lvl](r, c);
+}
+extern "C" void dso_ref_init_calc_res_and_gs(int w0, int h0, int lvl, float fx0, float fy0, float cx0, float cy0,
+                                             const float* colorRef, const float* colorNew,
+                                             const double* refToNew12, double aff_a, double aff_b,
+                                             int npts, const float* pu, const float* pv, const float* idepth_new, const unsigned char* isGood,
+                                             const float* energy2, const float* outlierTH, const float* iR,
+                                             float alphaW, float alphaK, float couplingWeight,
+                                             float* H64, float* b8, float* Hsc64, float* bsc8, float* res3,
+                                             unsigned char* isGood_new, float* energy_new2, float* maxstep_out, float* lastHessian_new,
+                                             float* Jb10)
+{
+	set_calib(w0, h0, lvl + 1, fx0, fy0, cx0, cy0);
+	CalibHessian HCalib;
+	CoarseInitializer* ci = new CoarseInitializer(w0, h0);
+	ci->makeK(&HCalib);
+	FrameHessian* first = new FrameHessian(); FrameHessian* nw = new FrameHessian();
+	first->dIp[lvl] = (Eigen::Vector3f*)colorRef; nw->dIp[lvl] = (Eigen::Vector3f*)colorNew;
+	ci->firstFrame = first; ci->newFrame = nw;
+	ci->alphaW = alphaW; ci->alphaK = alphaK; ci->couplingWeight = couplingWeight; ci->regWeight = 0.8f;
+	Pnt* pts = new Pnt[npts];
+	for (int i = 0; i < npts; i++)
+	{
+		Pnt& p = pts[i];
+		memset((void*)&p, 0, sizeof(Pnt));
+		p.u = pu[i]; p.v = pv[i]; p.idepth = p.idepth_new = idepth_new[i]; p.isGood = isGood[i] != 0;
+		p.energy[0] = energy2[2 * i]; p.energy[1] = energy2[2 * i + 1];
+		p.energy_new[0] = p.energy_new[1] = 0;
+		p.iR = iR[i]; p.outlierTH = outlierTH[i]; p.my_type = 1;
+	}
+	ci->points[lvl] = pts; ci->numPoints[lvl] = npts;
+	Mat88f H, Hsc; Vec8f b, bsc;
+	Vec3f res = ci->calcResAndGS(lvl, H, b, Hsc, bsc, to_se3(refToNew12), AffLight(aff_a, aff_b), false);   // :370
+	for (int r = 0; r < 8; r++)
+	{
+		for (int c = 0; c < 8; c++) { H64[r * 8 + c] = H(r, c); Hsc64[r * 8 + c] = Hsc(r, c); }
+		b8[r] = b[r]; bsc8[r] = bsc[r];
+	}
+	for (int k = 0; k < 3; k++) res3[k] = res[k];
+	for (int i = 0; i < npts; i++)
+	{
+		isGood_new[i] = pts[i].isGood_new; energy_new2[2 * i] = pts[i].energy_new[0]; energy_new2[2 * i + 1] = pts[i].energy_new[1];
+		maxstep_out[i] = pts[i].maxstep; lastHessian_new[i] = pts[i].lastHessian_new;
+		if (Jb10) for (int k = 0; k < 10; k++) Jb10[10 * i + k] = ci->JbBuffer_new[i][k];
+	}
+	ci->points[lvl] = 0; ci->numPoints[lvl] = 0;
+	delete[] pts;
+	first->dIp[lvl] = 0; nw->dIp[lvl] = 0;       // borrowed
+	delete ci;                                    // frames leak on purpose (test process; ~FrameHessian needs more state)
 }

@@ -384,3 +384,29 @@ def test_per_object_linearize_apply(pkg, win):
     assert (po["newState"] == 0).sum() > 0
     for key in ("Hdd", "bd", "Hcd"):
         assert np.array_equal(bits(Ao[key]), bits(Ar[key])), key      # the swapped-in Jacobians feed the next accumulation
+
+
+@pytest.mark.parametrize("lvl,unit_depth", [(0, False), (1, False), (2, True), (3, False)])
+def test_initializer_calc_res_and_gs(pkg, window_vga, lvl, unit_depth):
+    """next row N4: CoarseInitializer::calcResAndGS (FullSystem/CoarseInitializer.cpp:370-732) and makeK (:1126-1155) -- the
+    restatement against the reference's own translation unit: per-point outputs, H, b, H_sc, b_sc and the returned Vec3f bit for
+    bit (Accumulator9 / Accumulator11 lanes and tiers included)"""
+    W = window_vga
+    sc = pkg.synthetic.initializer_scenario(W, lvl=lvl, n_points=2500, unit_depth=unit_depth)
+    ko, kr = O.init_make_K(W.K, lvl), O.init_make_K(W.K, lvl, kind="ref")
+    assert np.array_equal(bits(ko[0]), bits(kr[0])) and np.array_equal(bits(ko[1]), bits(kr[1]))
+    first = O.make_images(sc["first"], lvl + 1)[0][lvl]
+    new = O.make_images(sc["new"], lvl + 1)[0][lvl]
+    ro = O.init_calc_res_and_gs(W.K, first, new, sc)
+    rr = O.init_calc_res_and_gs(W.K, first, new, sc, kind="ref")
+    assert np.array_equal(ro["isGood_new"], rr["isGood_new"])
+    good = ro["isGood_new"] == 1
+    n_in = int((sc["isGood"] == 1).sum())
+    assert good.sum() > 0.5 * n_in and (~good & (sc["isGood"] == 1)).sum() > 5, (good.sum(), n_in)     # kept, and rejected by bounds / outlierTH
+    assert np.array_equal(bits(ro["energy_new"]), bits(rr["energy_new"]))
+    for k in ("maxstep", "lastHessian_new"):
+        assert np.array_equal(bits(ro[k][good]), bits(rr[k][good])), k
+    assert np.array_equal(bits(ro["Jb"][good]), bits(rr["Jb"][good]))
+    for k in ("H", "b", "Hsc", "bsc", "res"):
+        assert np.array_equal(bits(ro[k]), bits(rr[k])), (k, ro[k], rr[k])
+    assert ro["res"][2] == 2 * len(sc["u"])          # E.num counts every point twice (:617-633 feed E, not EAlpha)
