@@ -96,6 +96,8 @@ SIGNATURES = {
     "dso_b200_track_hostloop": (C.c_int, [vp, C.c_int, C.c_int, f64p, C.c_double, C.c_double, C.c_float, C.c_int, vp,
                                           C.POINTER(TrackOpts), C.POINTER(TrackResult)]),
     "dso_b200_ba_set_affine_modes": (C.c_int, [vp, C.c_float, C.c_float]),
+    "dso_b200_init_calc_res_and_gs": (C.c_int, [vp, C.c_int, C.c_int, C.c_int] + [C.c_float] * 4 + [f64p, C.c_double, C.c_double, C.c_int] +
+                                      [vp] * 7 + [C.c_float] * 3 + [vp] * 10),
     "dso_b200_ba_linearize_residuals": (C.c_int, [vp, C.c_int, i32p, C.c_int, C.c_int, vp, vp, vp]),
     "dso_b200_ba_set_calib_delta": (C.c_int, [vp, f64p]),
     "dso_b200_ba_set_priors": (C.c_int, [vp, vp, vp, vp, vp, vp, vp]),
@@ -553,6 +555,26 @@ class Context:
         sums = np.zeros(2, dtype=np.float32)
         self._check(self.L.dso_b200_ba_iteration(self.h, iteration, lam, solver_mode, stepfacD, x.ctypes.data, C.byref(e), sums.ctypes.data))
         return dict(x=x, energy=e.value, step_sums=sums)
+
+    def init_calc_res_and_gs(self, first_slot, new_slot, K, sc):
+        """CoarseInitializer::calcResAndGS; sc: the scenario dict of synthetic.initializer_scenario"""
+        f = lambda a: np.ascontiguousarray(a, dtype=np.float32).reshape(-1)
+        n = len(sc["u"])
+        a = dict(u=f(sc["u"]), v=f(sc["v"]), id=f(sc["idepth_new"]), g=np.ascontiguousarray(sc["isGood"], dtype=np.uint8), e=f(sc["energy"]),
+                 o=f(sc["outlierTH"]), r=f(sc["iR"]))
+        out = dict(H=np.zeros(64, dtype=np.float32), b=np.zeros(8, dtype=np.float32), Hsc=np.zeros(64, dtype=np.float32),
+                   bsc=np.zeros(8, dtype=np.float32), res=np.zeros(3, dtype=np.float32), isGood_new=np.zeros(n, dtype=np.uint8),
+                   energy_new=np.zeros(2 * n, dtype=np.float32), maxstep=np.zeros(n, dtype=np.float32),
+                   lastHessian_new=np.zeros(n, dtype=np.float32), Jb=np.zeros(10 * n, dtype=np.float32))
+        p = lambda x: x.ctypes.data
+        self._check(self.L.dso_b200_init_calc_res_and_gs(
+            self.h, first_slot, new_slot, sc["lvl"], K[0], K[1], K[2], K[3], np.ascontiguousarray(sc["pose12"], dtype=np.float64),
+            sc["aff"][0], sc["aff"][1], n, p(a["u"]), p(a["v"]), p(a["id"]), p(a["g"]), p(a["e"]), p(a["o"]), p(a["r"]),
+            sc["alphaW"], sc["alphaK"], sc["couplingWeight"], p(out["H"]), p(out["b"]), p(out["Hsc"]), p(out["bsc"]), p(out["res"]),
+            p(out["isGood_new"]), p(out["energy_new"]), p(out["maxstep"]), p(out["lastHessian_new"]), p(out["Jb"])))
+        out["H"] = out["H"].reshape(8, 8); out["Hsc"] = out["Hsc"].reshape(8, 8)
+        out["energy_new"] = out["energy_new"].reshape(n, 2); out["Jb"] = out["Jb"].reshape(n, 10)
+        return out
 
     def ba_linearize_residuals(self, idx, reset_oob=True, apply=True):
         idx = np.ascontiguousarray(idx, dtype=np.int32)

@@ -70,6 +70,10 @@ int ba_create(dso_b200_ctx* ctx)
 	W->nLin = 0; W->S = nullptr;
 	memset(&W->g_step, 0, sizeof(W->g_step)); memset(W->g_iter, 0, sizeof(W->g_iter));
 	W->use_graphs = !getenv("DSO_B200_NO_GRAPH");
+	CK(cudaStreamCreateWithFlags(&W->side_stream, cudaStreamNonBlocking));
+	CK(cudaEventCreateWithFlags(&W->ev_fork, cudaEventDisableTiming));
+	CK(cudaEventCreateWithFlags(&W->ev_join, cudaEventDisableTiming));
+	W->side_busy = false;
 	ctx->ba = W;
 	ba_settings_changed(ctx);
 	return 0;
@@ -128,6 +132,9 @@ void ba_destroy(dso_b200_ctx* ctx)
 	cudaFree(W->d_precalc); cudaFree(W->d_adHost); cudaFree(W->d_adTarget); cudaFree(W->d_pair_chunk_begin); cudaFree(W->d_host_pc_begin);
 	cudaFree(W->d_HA); cudaFree(W->d_bA); cudaFree(W->d_HS); cudaFree(W->d_bS); cudaFree(W->d_scalars); cudaFree(W->d_scContrib); cudaFree(W->d_scRed); cudaFree(W->d_topRed); cudaFree(W->d_topContrib);
 	cudaFreeHost(W->h_out);
+	if (W->side_stream) { cudaStreamSynchronize(W->side_stream); cudaStreamDestroy(W->side_stream); }
+	if (W->ev_fork) cudaEventDestroy(W->ev_fork);
+	if (W->ev_join) cudaEventDestroy(W->ev_join);
 	delete W;
 	ctx->ba = nullptr;
 }
@@ -1354,7 +1361,28 @@ extern "C" int dso_b200_ba_set_frames(dso_b200_ctx* ctx, const double* evalPT12,
 	return dso_b200_ba_set_glue(ctx, pre.data(), adH.data(), adT.data(), adHTd.data(), nullptr);
 }
 
-int ba_enqueue_linearize(dso_b200_ctx* ctx)
+// The step's launch sequence is not one chain: the energy sum only has to be ready at the end, and the top-Hessian stitch
+// (three kernels) is independent of the Schur-complement chain (five).  With fork = true those side branches go to a second
+// stream (captured into the same CUDA graph as parallel branches); ba_join_side makes the main stream wait for them.
+static int ba_fork(dso_b200_ctx* ctx)
+{
+	BAWorkspace* W = ctx->ba;
+	CK(cudaEventRecord(W->ev_fork, ctx->ba_stream));
+	CK(cudaStreamWaitEvent(W->side_stream, W->ev_fork, 0));
+	W->side_busy = true;
+	return 0;
+}
+int ba_join_side(dso_b200_ctx* ctx)
+{
+	BAWorkspace* W = ctx->ba;
+	if (!W->side_busy) return 0;
+	CK(cudaEventRecord(W->ev_join, W->side_stream));
+	CK(cudaStreamWaitEvent(ctx->ba_stream, W->ev_join, 0));
+	W->side_busy = false;
+	return 0;
+}
+
+int ba_enqueue_linearize(dso_b200_ctx* ctx, bool fork)
 {
 	BAWorkspace* W = ctx->ba;
 	const int nR = W->P.nR;
@@ -1363,8 +1391,10 @@ int ba_enqueue_linearize(dso_b200_ctx* ctx)
 	                                                           W->d_newState, W->d_newEnergy, W->d_newEnergyWO, W->d_cpt, W->d_proj, W->d_resEnergy,
 	                                                           nullptr, 0, 0);
 	const int nb = (nR + 255) / 256;
-	ba_energy_blocks_kernel<<<nb, 256, 0, ctx->ba_stream>>>(nR, W->d_resEnergy, W->d_energy_blocks);
-	ba_energy_final_kernel<<<1, 32, 0, ctx->ba_stream>>>(nb, W->d_energy_blocks, W->d_scalars);
+	cudaStream_t se = ctx->ba_stream;
+	if (fork) { int rc = ba_fork(ctx); if (rc) return rc; se = W->side_stream; }
+	ba_energy_blocks_kernel<<<nb, 256, 0, se>>>(nR, W->d_resEnergy, W->d_energy_blocks);
+	ba_energy_final_kernel<<<1, 32, 0, se>>>(nb, W->d_energy_blocks, W->d_scalars);
 	LAUNCHED(ctx, 3);
 	CK(cudaGetLastError());
 	W->lin_done = true;
@@ -1384,7 +1414,7 @@ int ba_enqueue_apply(dso_b200_ctx* ctx)
 }
 
 // mode 0: accumulateAF_MT -> d_HA, d_bA, per-point AF sums; mode 1: accumulateLF_MT -> d_HL, d_bL (+ priors), per-point LF sums
-int ba_enqueue_top(dso_b200_ctx* ctx, int mode, const unsigned char* d_pmask)
+int ba_enqueue_top(dso_b200_ctx* ctx, int mode, const unsigned char* d_pmask, bool fork)
 {
 	BAWorkspace* W = ctx->ba;
 	const int nF = W->P.nF;
@@ -1404,6 +1434,7 @@ int ba_enqueue_top(dso_b200_ctx* ctx, int mode, const unsigned char* d_pmask)
 		ba_accum_top_kernel<1><<<W->nChunks, 128, 0, st>>>(W->d_perm, W->d_chunk_start, W->d_chunk_cnt, W->d_isAct, W->d_isLin, W->d_efsel,
 		                                                 W->d_J[0], W->d_J[1], W->d_contrib, W->d_topPartials, W->d_chunk_nres, LA);
 	ba_point_sums_kernel<<<(W->P.nP + 127) / 128, 128, 0, st>>>(W->P.nP, W->d_res_begin, W->d_isAct, W->d_isLin, W->d_contrib, Hdd, bd, Hcd, mode, d_pmask, W->d_Hdd, W->d_bd, W->d_Hcd);
+	if (fork) { int rc = ba_fork(ctx); if (rc) return rc; st = W->side_stream; }       // the stitch: independent of what follows on the main stream
 	ba_reduce_partials_kernel<<<dim3(1, nF * nF), NTOP_PAD, 0, st>>>(W->d_topPartials, NTOP_PAD, NTOP_PAD, W->d_pair_chunk_begin, W->d_topRed);
 	ba_top_pair_kernel<<<nF * nF, 256, 0, st>>>(nF, W->d_topRed, W->d_adHost, W->d_adTarget, W->d_topContrib);
 	ba_top_gather_kernel<<<nF * nF + 1, 64, 0, st>>>(nF, W->nChunks, W->d_chunk_nres, W->d_topContrib, Hout, bout, W->d_scalars + (mode ? 2 : 0),
@@ -1608,10 +1639,11 @@ extern "C" int dso_b200_ba_step(dso_b200_ctx* ctx, double* H_A, double* b_A, dou
 	cudaStream_t s = ctx->ba_stream;
 	rc = ba_run_graphed(ctx, W->g_step, BAGraphKey{ 0.0, 0.f, 0, 0, 0, 0 }, [&]() -> int {
 		int r;
-		if ((r = ba_enqueue_linearize(ctx))) return r;
+		if ((r = ba_enqueue_linearize(ctx, true))) return r;
 		if ((r = ba_enqueue_apply(ctx))) return r;
-		if ((r = ba_enqueue_top(ctx, 0))) return r;
+		if ((r = ba_enqueue_top(ctx, 0, nullptr, true))) return r;
 		if ((r = ba_enqueue_schur(ctx))) return r;
+		if ((r = ba_join_side(ctx))) return r;
 		CK(cudaMemcpyAsync(W->h_out, W->d_HA, NN * sizeof(double), cudaMemcpyDeviceToHost, s));
 		CK(cudaMemcpyAsync(W->h_out + NN, W->d_bA, N * sizeof(double), cudaMemcpyDeviceToHost, s));
 		CK(cudaMemcpyAsync(W->h_out + NN + N, W->d_HS, NN * sizeof(double), cudaMemcpyDeviceToHost, s));

@@ -106,6 +106,7 @@ struct BAWorkspace
 	int nLin;                                                                    // linearised residuals (-1: unknown)
 	BASolve* S;
 	BAGraph g_step, g_iter[2];
+	cudaStream_t side_stream; cudaEvent_t ev_fork, ev_join; bool side_busy;     // parallel branches of the step (ba_fork / ba_join_side)
 	bool use_graphs;                                                             // DSO_B200_NO_GRAPH=1 turns them off
 };
 
@@ -142,9 +143,10 @@ static int ba_run_graphed(dso_b200_ctx* ctx, BAGraph& g, const BAGraphKey& key, 
 }
 
 int ba_check_ready(dso_b200_ctx* ctx, const char* fn);
-int ba_enqueue_linearize(dso_b200_ctx* ctx);
+int ba_enqueue_linearize(dso_b200_ctx* ctx, bool fork = false);
+int ba_join_side(dso_b200_ctx* ctx);
 int ba_enqueue_apply(dso_b200_ctx* ctx);
-int ba_enqueue_top(dso_b200_ctx* ctx, int mode, const unsigned char* d_pmask = nullptr);
+int ba_enqueue_top(dso_b200_ctx* ctx, int mode, const unsigned char* d_pmask = nullptr, bool fork = false);
 int ba_enqueue_schur(dso_b200_ctx* ctx, const unsigned char* d_pmask = nullptr);
 void ba_solve_destroy(BAWorkspace* W);
 

@@ -744,10 +744,13 @@ static int enqueue_solve(dso_b200_ctx* ctx, BASolve* S, int iteration, double la
 	int rc;
 	if (solverMode & SOLVER_USE_GN) lambda = 0;                      // :804
 	if (solverMode & SOLVER_FIX_LAMBDA) lambda = 1e-5;              // :805
-	if ((rc = ba_enqueue_top(ctx, 0))) return rc;                   // :816
+	// the stitch of the last top accumulation runs beside the Schur chain (the two top modes share their stitch buffers, so
+	// only the last one may be forked)
 	const bool haveL = W->nLin != 0;
-	if (haveL && (rc = ba_enqueue_top(ctx, 1))) return rc;          // :817 (without linearised residuals H_L, b_L are the priors alone)
+	if ((rc = ba_enqueue_top(ctx, 0, nullptr, !haveL))) return rc;  // :816
+	if (haveL && (rc = ba_enqueue_top(ctx, 1, nullptr, true))) return rc;   // :817 (without linearised residuals H_L, b_L are the priors alone)
 	if ((rc = ba_enqueue_schur(ctx))) return rc;                    // :820
+	if ((rc = ba_join_side(ctx))) return rc;
 	if ((rc = ensure_point_buffers(ctx, S))) return rc;
 	SolveArgs a;
 	a.nF = W->P.nF; a.lambda = lambda; a.haveL = haveL ? 1 : 0;
@@ -817,7 +820,7 @@ extern "C" int dso_b200_ba_iteration(dso_b200_ctx* ctx, int iteration, double la
 	const BAGraphKey key = { lambda, stepfacD, solverMode, W->nLin != 0 ? 1 : 0, S->haveP ? 1 : 0, S->d_dbg ? 1 : 0 };
 	rc = ba_run_graphed(ctx, W->g_iter[orth], key, [&]() -> int {
 		int r;
-		if ((r = ba_enqueue_linearize(ctx))) return r;
+		if ((r = ba_enqueue_linearize(ctx, true))) return r;
 		if ((r = ba_enqueue_apply(ctx))) return r;
 		if ((r = enqueue_solve(ctx, S, orth ? 2 : 0, lambda, solverMode, false))) return r;
 		ba_points_backup_kernel<<<(nP + 255) / 256, 256, 0, s>>>(nP, W->d_pt, S->d_idepth_backup, 0, nullptr, nullptr);

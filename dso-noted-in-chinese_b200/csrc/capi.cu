@@ -148,6 +148,7 @@ extern "C" void dso_b200_destroy(dso_b200_ctx* ctx)
 	if (ctx->ba) ba_destroy(ctx);
 	coarse_depth_destroy(ctx);
 	trace_destroy(ctx);
+	init_destroy(ctx);
 	if (ctx->slots)
 	{
 		for (int s = 0; s < ctx->n_slots; s++)

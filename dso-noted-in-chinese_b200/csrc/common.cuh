@@ -118,6 +118,7 @@ struct dso_b200_ctx
 	BAWorkspace* ba;
 	void* coarse_depth;        // CoarseDepthWS (coarse_depth.cu), allocated at the first dso_b200_tracker_set_ref_points
 	void* trace;               // TraceWS (trace.cu): the immature points of the window
+	void* init_ws;             // InitWS (initializer.cu): grow-only buffers of dso_b200_init_calc_res_and_gs
 	dso_b200_settings settings;                       // dso_b200_set_settings
 	void* act_scratch; size_t act_scratch_bytes;      // dso_b200_optimize_immature: grow-only device scratch
 	int tune_threads, tune_cluster, tune_nclusters;   // dso_b200_track_set_tuning (0 = automatic)
@@ -155,6 +156,7 @@ int frame_slot_produced(dso_b200_ctx* ctx, FrameSlot& F, cudaStream_t stream);
 void tracker_make_K(TrackerSlot& T, int w, int h, int levels, float fx, float fy, float cx, float cy);   // CoarseTracker::makeK
 void coarse_depth_destroy(dso_b200_ctx* ctx);
 void trace_destroy(dso_b200_ctx* ctx);
+void init_destroy(dso_b200_ctx* ctx);
 int pyramid_build(dso_b200_ctx* ctx, FrameSlot& fs, const float* color_dev, int w, int h, int levels,
                   const float* d_Blut, bool host_layout);
 int ba_create(dso_b200_ctx* ctx);

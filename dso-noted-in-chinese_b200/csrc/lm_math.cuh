@@ -137,6 +137,37 @@ HD void pose_adjoint(const Pose& T, double* Ad)
 		}
 }
 
+// Sophus SE3::log (host only): xi = (V^-1 t, w) with the closed forms of SO3::log and V^-1 = I - W/2 + k W^2
+static inline void pose_log(const Pose& T, double* xi)
+{
+	const double tr = T.R[0] + T.R[4] + T.R[8];
+	double c = (tr - 1.0) * 0.5;
+	c = c < -1.0 ? -1.0 : (c > 1.0 ? 1.0 : c);
+	const double th = acos(c);
+	double f;
+	if (th < 1e-7) f = 0.5 + th * th / 12.0;
+	else f = th / (2.0 * sin(th));
+	const double w[3] = { f * (T.R[7] - T.R[5]), f * (T.R[2] - T.R[6]), f * (T.R[3] - T.R[1]) };
+	const double th2 = th * th;
+	const double W[9] = { 0, -w[2], w[1], w[2], 0, -w[0], -w[1], w[0], 0 };
+	double W2[9];
+	mat33d_mul(W, W, W2);
+	double k;
+	if (th < 1e-5) k = 1.0 / 12.0 + th2 / 720.0;
+	else
+	{
+		const double A = sin(th) / th, B = (1.0 - cos(th)) / th2;
+		k = (1.0 - A / (2.0 * B)) / th2;
+	}
+	for (int r = 0; r < 3; r++)
+	{
+		double V[3];
+		for (int cc = 0; cc < 3; cc++) V[cc] = (r == cc ? 1.0 : 0.0) - 0.5 * W[r * 3 + cc] + k * W2[r * 3 + cc];
+		xi[r] = dot3dd(V[0], T.t[0], V[1], T.t[1], V[2], T.t[2]);
+	}
+	xi[3] = w[0]; xi[4] = w[1]; xi[5] = w[2];
+}
+
 // AffLight::fromToVecExposure (NumType.h:176-189)
 HD void aff_from_to(float exposureF, float exposureT, double Fa, double Fb, double Ta, double Tb, double& a, double& b)
 {

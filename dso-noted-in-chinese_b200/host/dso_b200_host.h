@@ -277,4 +277,60 @@ private:
 	DeviceContext* dev;
 };
 
+// ---- CoarseInitializer (FullSystem/CoarseInitializer.h:45-223): the linearisation of the two-frame bootstrap ----
+struct Vec3f { float v[3]; float& operator[](int i) { return v[i]; } };
+struct Vec8f { float v[8]; float& operator[](int i) { return v[i]; } };
+struct Mat88f { float m[64]; float& operator()(int r, int c) { return m[r * 8 + c]; } };
+struct Pnt                      // the fields calcResAndGS reads and writes (CoarseInitializer.h:45-85)
+{
+	float u, v, idepth; bool isGood; float energy[2];
+	float idepth_new; bool isGood_new; float energy_new[2];
+	float iR, lastHessian, lastHessian_new, maxstep, outlierTH;
+};
+class CoarseInitializer
+{
+public:
+	CoarseInitializer(DeviceContext* d, CalibHessian* HCalib) : firstFrame(0), newFrame(0), alphaK(2.5f * 2.5f), alphaW(150.f * 150.f), couplingWeight(1), dev(d), calib(HCalib)
+	{ for (int i = 0; i < DSO_B200_MAX_LEVELS; i++) { points[i] = 0; numPoints[i] = 0; } }
+	Pnt* points[DSO_B200_MAX_LEVELS];
+	int numPoints[DSO_B200_MAX_LEVELS];
+	FrameHessian* firstFrame;
+	FrameHessian* newFrame;
+	std::vector<float> JbBuffer_new;          // Vec10f per point of the level last linearised
+	float alphaK, alphaW, couplingWeight;     // set by trackFrame (CoarseInitializer.cpp:101-105)
+
+	// Vec3f calcResAndGS(int lvl, Mat88f&, Vec8f&, Mat88f&, Vec8f&, const SE3& refToNew, AffLight refToNew_aff, bool plot)
+	// CoarseInitializer.cpp:370: one kernel over the points of the level; the Pnt fields are gathered / scattered here
+	Vec3f calcResAndGS(int lvl, Mat88f& H_out, Vec8f& b_out, Mat88f& H_out_sc, Vec8f& b_out_sc, const SE3& refToNew, AffLight refToNew_aff, bool plot)
+	{
+		(void)plot;
+		const int n = numPoints[lvl];
+		Pnt* p = points[lvl];
+		std::vector<float> u(n), v(n), id(n), e(2 * n), oth(n), iR(n), en(2 * n), ms(n), lh(n);
+		std::vector<unsigned char> g(n), gn(n);
+		for (int i = 0; i < n; i++)
+		{
+			u[i] = p[i].u; v[i] = p[i].v; id[i] = p[i].idepth_new; g[i] = p[i].isGood; e[2 * i] = p[i].energy[0]; e[2 * i + 1] = p[i].energy[1];
+			oth[i] = p[i].outlierTH; iR[i] = p[i].iR;
+		}
+		JbBuffer_new.assign((size_t)n * 10, 0.f);
+		double pose[12];
+		pose12(refToNew, pose);
+		Vec3f res;
+		DSO_B200_CHECK(dso_b200_init_calc_res_and_gs(dev->ctx, firstFrame->frame_slot, newFrame->frame_slot, lvl, calib->fxl(), calib->fyl(),
+		                                             calib->cxl(), calib->cyl(), pose, refToNew_aff.a, refToNew_aff.b, n, u.data(), v.data(), id.data(),
+		                                             g.data(), e.data(), oth.data(), iR.data(), alphaW, alphaK, couplingWeight, H_out.m, b_out.v,
+		                                             H_out_sc.m, b_out_sc.v, res.v, gn.data(), en.data(), ms.data(), lh.data(), JbBuffer_new.data()));
+		for (int i = 0; i < n; i++)
+		{
+			p[i].isGood_new = gn[i] != 0; p[i].energy_new[0] = en[2 * i]; p[i].energy_new[1] = en[2 * i + 1]; p[i].maxstep = ms[i];
+			if (p[i].isGood_new) p[i].lastHessian_new = lh[i];
+		}
+		return res;
+	}
+private:
+	DeviceContext* dev;
+	CalibHessian* calib;
+};
+
 }   // namespace dso

@@ -439,6 +439,27 @@ int dso_b200_optimize_immature(dso_b200_ctx* ctx, int n_targets, const int* targ
                                const float* idepth_min, const float* idepth_max, int minObs,
                                int* result, float* idepth_out, int* res_state_out);
 
+/* ---- next row N4: the two-frame initialiser (FullSystem/CoarseInitializer.{h,cpp}) -------------------------------------
+ * CoarseInitializer::calcResAndGS (CoarseInitializer.cpp:370-732, decl CoarseInitializer.h:166-171) on pyramid level lvl:
+ * first_slot / new_slot hold the device pyramids of firstFrame / newFrame (dso_b200_make_images*), fx..cy are
+ * HCalib->fxl() ... cyl() (the per-level intrinsics follow CoarseInitializer::makeK, :1126-1155, in double), the Pnt fields
+ * (CoarseInitializer.h:45-85) come as arrays of npts entries: u, v, idepth_new, isGood, energy (2 per point), outlierTH,
+ * iR; alphaW, alphaK, couplingWeight are the members trackFrame sets (:101-105); setting_huberTH comes from
+ * dso_b200_set_settings.  Outputs: H_out, b_out, H_out_sc, b_out_sc (row-major 8x8 / 8 floats), res3 = the returned Vec3f
+ * (E.A, alphaEnergy, E.num), and per point (each may be NULL) isGood_new, energy_new (2), maxstep, lastHessian_new and
+ * JbBuffer_new (10).  The per-point outputs are bit-identical to the reference for the points it keeps (isGood_new); for the
+ * others JbBuffer_new / lastHessian_new, which the reference leaves stale, are written as 0.  Points must keep the border
+ * CoarseInitializer::setFirst gives them (pattern + 1 pixel); closer ones are dropped instead of read out of bounds. */
+int dso_b200_init_calc_res_and_gs(dso_b200_ctx* ctx, int first_slot, int new_slot, int lvl,
+                                  float fx, float fy, float cx, float cy,
+                                  const double* refToNew12, double aff_a, double aff_b,
+                                  int npts, const float* u, const float* v, const float* idepth_new, const unsigned char* isGood,
+                                  const float* energy2, const float* outlierTH, const float* iR,
+                                  float alphaW, float alphaK, float couplingWeight,
+                                  float* H64, float* b8, float* Hsc64, float* bsc8, float* res3,
+                                  unsigned char* isGood_new, float* energy_new2, float* maxstep, float* lastHessian_new,
+                                  float* JbBuffer_new10);
+
 #ifdef __cplusplus
 }
 #endif
