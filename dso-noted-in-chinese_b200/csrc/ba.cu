@@ -163,15 +163,19 @@ __device__ __forceinline__ float seq8(float v, int base)
 	return s;
 }
 
-// PointFrameResidual::linearize, Residuals.cpp:78-291
+// PointFrameResidual::linearize, Residuals.cpp:78-291.  APPLY = true fuses applyRes(true) + EFResidual::takeDataF
+// (Residuals.cpp:323-347, EnergyFunctionalStructs.cpp:39-49) for the same residual into the tail of the kernel (the window
+// step always applies what it has just linearised; saves a launch and the re-read of the Jacobian).
+template <bool APPLY>
 __global__ void __launch_bounds__(256) ba_linearize_kernel(BAParams B, const float* __restrict__ precalc, const float4* __restrict__ pt,
                                                            const float* __restrict__ color, const float* __restrict__ weights,
                                                            const int* __restrict__ phost, const int* __restrict__ rpoint,
-                                                           const int* __restrict__ rtarget, const int* __restrict__ state,
-                                                           const double* __restrict__ state_energy, const unsigned char* __restrict__ efsel,
+                                                           const int* __restrict__ rtarget, int* state,
+                                                           double* state_energy, unsigned char* efsel,
                                                            float* J0, float* J1, int* newState, float* newEnergy, float* newEnergyWO,
                                                            float* cpt, float* proj, double* resEnergy,
-                                                           const int* __restrict__ subset, int nsub, int reset_oob)
+                                                           const int* __restrict__ subset, int nsub, int reset_oob,
+                                                           unsigned char* isAct, float* JpJdF)
 {
 	__shared__ float sJ[32][JSZ + 2];
 	const int tid = threadIdx.x, lane = tid & 31, g = tid >> 3, idx = tid & 7, base = lane & ~7;
@@ -240,6 +244,8 @@ __global__ void __launch_bounds__(256) ba_linearize_kernel(BAParams B, const flo
 	const float AA00 = seq8(fmul(fmul(fmul(drdA, drdA), hw), hw), base), AA01 = seq8(fmul(fmul(drdA, hw), hw), base), AA11 = seq8(fmul(hw, hw), base);
 	const float wJI2 = seq8(fmul(fmul(hw, hw), fadd(fmul(g1, g1), fmul(g2, g2))), base);
 
+	bool outlier_f = false;
+	float eLeft_f = 0.f;
 	if (valid)
 	{
 		if (oob)
@@ -258,6 +264,7 @@ __global__ void __launch_bounds__(256) ba_linearize_kernel(BAParams B, const flo
 			const float th = fmaxf(B.frameEnergyTH[h], B.frameEnergyTH[t]);
 			const bool outlier = (energy > th) || (wJI2 < 2.f);                 // :278
 			const float eLeft = outlier ? th : energy;
+			outlier_f = outlier; eLeft_f = eLeft;
 			proj[16 * (size_t)r + 2 * idx] = Ku; proj[16 * (size_t)r + 2 * idx + 1] = Kv;
 			float* s = sJ[g];
 			s[J_RESF + idx] = resF; s[J_IDX0 + idx] = g1; s[J_IDX1 + idx] = g2; s[J_AB0 + idx] = B.fixA ? 0.f : ja; s[J_AB1 + idx] = B.fixB ? 0.f : hw;   // :257-258
@@ -311,6 +318,29 @@ __global__ void __launch_bounds__(256) ba_linearize_kernel(BAParams B, const flo
 		// PointFrameResidual::J is the buffer EFResidual is not holding
 		float* dst = (efsel[r] ? J0 : J1) + (size_t)r * JSZ;
 		for (int k = idx; k < JSZ; k += 8) dst[k] = sJ[g][k];
+	}
+	if (APPLY && valid && st != ST_OOB)                   // applyRes: can never go back from OOB
+	{
+		const bool in = !oob && !outlier_f;
+		if (in)
+		{
+			// takeDataF: JpJdF from the Jacobian just written (std::swap(J, data->J) = flipping efsel below)
+			const float* Jl = sJ[g];
+			const float d0 = Jl[J_PDD], d1 = Jl[J_PDD + 1];
+			const float a0 = fadd(fmul(Jl[J_IDX2 + 0], d0), fmul(Jl[J_IDX2 + 1], d1));
+			const float a1 = fadd(fmul(Jl[J_IDX2 + 2], d0), fmul(Jl[J_IDX2 + 3], d1));
+			float val;
+			if (idx < 6) val = fadd(fmul(Jl[J_PDXI0 + idx], a0), fmul(Jl[J_PDXI1 + idx], a1));
+			else val = fadd(fmul(Jl[J_ABIDX + 2 * (idx - 6)], d0), fmul(Jl[J_ABIDX + 2 * (idx - 6) + 1], d1));
+			JpJdF[8 * (size_t)r + idx] = val;
+		}
+		if (idx == 0)
+		{
+			isAct[r] = in ? 1 : 0;
+			if (in) efsel[r] = efsel[r] ^ 1;
+			state[r] = oob ? ST_OOB : (outlier_f ? ST_OUTLIER : ST_IN);
+			state_energy[r] = oob ? (double)newEnergy[r] : (double)eLeft_f;      // the OOB exits leave state_NewEnergy as it was
+		}
 	}
 }
 
@@ -882,49 +912,52 @@ __device__ __forceinline__ void mm8(const double* A, const double* Bm, double* C
 
 // stage 1 of stitchDoubleInternal (AccumulatedSCHessian.cpp:86-165) for the pair (i = host, j = target):
 // every adjoint sandwich that involves accD[i,j,*], accE[i,j], accEB[i,j], written out as separate contributions.
-__global__ void __launch_bounds__(64) ba_schur_stage1_kernel(int nF, const double* __restrict__ scRed, int nRed,
-                                                             const double* __restrict__ adHost, const double* __restrict__ adTarget,
-                                                             double* contrib)
+__global__ void __launch_bounds__(64 * MAXF) ba_schur_stage1_kernel(int nF, const double* __restrict__ scRed, int nRed,
+                                                                    const double* __restrict__ adHost, const double* __restrict__ adTarget,
+                                                                    double* contrib)
 {
-	__shared__ double Dk[MAXF][64], AHk[MAXF][64], ATk[MAXF][64];   // all k-dependent operands, loaded in one go
-	__shared__ double S1[64], Q[64], AHij[64], ATij[64], E[32], EB[8];
-	const int i = blockIdx.x % nF, j = blockIdx.x / nF, o = threadIdx.x;
+	// one CTA per pair, one 64-thread slice per third frame k (the k-dependent products are independent of each other)
+	__shared__ double Dk[MAXF][64], AHk[MAXF][64], ATk[MAXF][64], Vk[MAXF][64], Qk[MAXF][64];
+	__shared__ double S1[64], AHij[64], ATij[64], E[32], EB[8];
+	const int i = blockIdx.x % nF, j = blockIdx.x / nF, o = threadIdx.x & 63, k = threadIdx.x >> 6;
 	const int ij = i + nF * j;
 	const int nD = nF * nF * 64, nE = nF * 32;
 	const double* red = scRed + (size_t)i * nRed;      // chunk partials of host i, already summed
 	double* out = contrib + (size_t)ij * SCC_STRIDE;
-	AHij[o] = adHost[(size_t)ij * 64 + o]; ATij[o] = adTarget[(size_t)ij * 64 + o];
-	S1[o] = 0.0;
-	if (o < 32) E[o] = red[nD + j * 32 + o];
-	if (o < 8) EB[o] = red[nD + nE + j * 8 + o];
-#pragma unroll
-	for (int k = 0; k < MAXF; k++)
-		if (k < nF)
-		{
-			const int ik = i + nF * k;
-			Dk[k][o] = red[(j * nF + k) * 64 + o];
-			AHk[k][o] = adHost[(size_t)ik * 64 + o]; ATk[k][o] = adTarget[(size_t)ik * 64 + o];
-		}
+	const bool act = k < nF;
+	if (k == 0) { AHij[o] = adHost[(size_t)ij * 64 + o]; ATij[o] = adTarget[(size_t)ij * 64 + o]; }
+	if (k == 1 && o < 32) E[o] = red[nD + j * 32 + o];
+	if (k == 1 && o >= 32 && o < 40) EB[o - 32] = red[nD + nE + j * 8 + o - 32];
+	if (act)
+	{
+		const int ik = i + nF * k;
+		Dk[k][o] = red[(j * nF + k) * 64 + o];
+		AHk[k][o] = adHost[(size_t)ik * 64 + o]; ATk[k][o] = adTarget[(size_t)ik * 64 + o];
+	}
 	__syncthreads();
-	for (int k = 0; k < nF; k++)
+	if (act)
 	{
 		const double* D = Dk[k]; const double* AHik = AHk[k]; const double* ATik = ATk[k];
-		{
-			const int r = o >> 3, c = o & 7;
-			double v = 0.0, q = 0.0;
+		const int r = o >> 3, c = o & 7;
+		double v = 0.0, q = 0.0;
 #pragma unroll
-			for (int m = 0; m < 8; m++) { v += D[r * 8 + m] * AHik[c * 8 + m]; q += D[r * 8 + m] * ATik[c * 8 + m]; }
-			S1[o] += v;            // sum_k D[i,j,k] adHost[i,k]^T
-			Q[o] = q;              // D[i,j,k] adTarget[i,k]^T
-		}
-		__syncthreads();
-		mm8(ATij, Q, out + SCC_C3 + k * 64, false, o);   // -> block (j,k)
-		mm8(AHij, Q, out + SCC_C4 + k * 64, false, o);   // -> block (i,k)
-		__syncthreads();
+		for (int m = 0; m < 8; m++) { v += D[r * 8 + m] * AHik[c * 8 + m]; q += D[r * 8 + m] * ATik[c * 8 + m]; }
+		Vk[k][o] = v;          // D[i,j,k] adHost[i,k]^T
+		Qk[k][o] = q;          // D[i,j,k] adTarget[i,k]^T
 	}
-	mm8(AHij, S1, out + SCC_C1, false, o);               // -> block (i,i)
-	mm8(ATij, S1, out + SCC_C2, false, o);               // -> block (j,i)
-	if (o < 32)
+	__syncthreads();
+	if (act)
+	{
+		mm8(ATij, Qk[k], out + SCC_C3 + k * 64, false, o);   // -> block (j,k)
+		mm8(AHij, Qk[k], out + SCC_C4 + k * 64, false, o);   // -> block (i,k)
+	}
+	if (k == 0)
+	{
+		double sacc = 0.0;                                   // sum_k D[i,j,k] adHost[i,k]^T, k in order
+		for (int q = 0; q < nF; q++) sacc += Vk[q][o];
+		S1[o] = sacc;
+	}
+	if (k == 1 && o < 32)
 	{
 		const int r = o >> 2, c = o & 3;
 		double vh = 0.0, vt = 0.0;
@@ -932,13 +965,17 @@ __global__ void __launch_bounds__(64) ba_schur_stage1_kernel(int nF, const doubl
 		for (int m = 0; m < 8; m++) { vh += AHij[r * 8 + m] * E[m * 4 + c]; vt += ATij[r * 8 + m] * E[m * 4 + c]; }
 		out[SCC_CEH + o] = vh; out[SCC_CET + o] = vt;
 	}
-	if (o < 8)
+	if (k == 1 && o >= 32 && o < 40)
 	{
+		const int e = o - 32;
 		double vh = 0.0, vt = 0.0;
 #pragma unroll
-		for (int m = 0; m < 8; m++) { vh += AHij[o * 8 + m] * EB[m]; vt += ATij[o * 8 + m] * EB[m]; }
-		out[SCC_CBH + o] = vh; out[SCC_CBT + o] = vt;
+		for (int m = 0; m < 8; m++) { vh += AHij[e * 8 + m] * EB[m]; vt += ATij[e * 8 + m] * EB[m]; }
+		out[SCC_CBH + e] = vh; out[SCC_CBT + e] = vt;
 	}
+	__syncthreads();
+	if (k == 0) mm8(AHij, S1, out + SCC_C1, false, o);       // -> block (i,i)
+	if (k == 1) mm8(ATij, S1, out + SCC_C2, false, o);       // -> block (j,i)
 }
 
 // stage 2: gather the contributions of every output block in a fixed order
@@ -957,13 +994,13 @@ __global__ void __launch_bounds__(64) ba_schur_gather_kernel(int nF, const doubl
 		ORDERED_SUM_MAXF(v, nF, j, contrib[(size_t)(r + nF * j) * SCC_STRIDE + SCC_C4 + c * 64 + o]);      // i = r, k = c
 		Hout[(CPARS + r * 8 + (o >> 3)) * N + CPARS + c * 8 + (o & 7)] = v;
 	}
-	else
+	else if ((int)blockIdx.x < nF * nF + nF)
 	{
-		// calibration rows / columns, b, Hcc, bc
-		const int nD = nF * nF * 64, nE = nF * 32, nEB = nF * 8;
-		for (int e = o; e < nF * 32; e += 64)
+		// calibration rows / columns and b of frame r: one block per frame, one entry per thread (a single round of loads)
+		const int r = blockIdx.x - nF * nF;
+		if (o < 32)
 		{
-			const int r = e / 32, q = e % 32;
+			const int q = o;
 			double v = 0.0;
 			ORDERED_SUM_MAXF(v, nF, j, contrib[(size_t)(r + nF * j) * SCC_STRIDE + SCC_CEH + q]);
 			ORDERED_SUM_MAXF(v, nF, i, contrib[(size_t)(i + nF * r) * SCC_STRIDE + SCC_CET + q]);
@@ -971,21 +1008,22 @@ __global__ void __launch_bounds__(64) ba_schur_gather_kernel(int nF, const doubl
 			Hout[row * N + col] = v;
 			Hout[col * N + row] = v;                                  // AccumulatedSCHessian.h:130-134
 		}
-		for (int e = o; e < nF * 8; e += 64)
+		else if (o < 40)
 		{
-			const int r = e / 8, q = e % 8;
+			const int q = o - 32;
 			double v = 0.0;
 			ORDERED_SUM_MAXF(v, nF, j, contrib[(size_t)(r + nF * j) * SCC_STRIDE + SCC_CBH + q]);
 			ORDERED_SUM_MAXF(v, nF, i, contrib[(size_t)(i + nF * r) * SCC_STRIDE + SCC_CBT + q]);
-			bout[CPARS + e] = v;
+			bout[CPARS + r * 8 + q] = v;
 		}
-		if (o < 20)
-		{
-			double v = 0.0;
-			// accHcc / accbc: chunk partials already summed per host by ba_reduce_partials_kernel, hosts in order here
-			ORDERED_SUM_MAXF(v, nF, i, scRed[(size_t)i * (nD + nE + nEB + 20) + nD + nE + nEB + o]);
-			if (o < 16) Hout[(o >> 2) * N + (o & 3)] = v; else bout[o - 16] = v;
-		}
+	}
+	else if (o < 20)
+	{
+		// accHcc / accbc: chunk partials already summed per host by ba_reduce_partials_kernel, hosts in order here
+		const int nD = nF * nF * 64, nE = nF * 32, nEB = nF * 8;
+		double v = 0.0;
+		ORDERED_SUM_MAXF(v, nF, i, scRed[(size_t)i * (nD + nE + nEB + 20) + nD + nE + nEB + o]);
+		if (o < 16) Hout[(o >> 2) * N + (o & 3)] = v; else bout[o - 16] = v;
 	}
 }
 
@@ -1382,14 +1420,21 @@ int ba_join_side(dso_b200_ctx* ctx)
 	return 0;
 }
 
-int ba_enqueue_linearize(dso_b200_ctx* ctx, bool fork)
+int ba_enqueue_linearize(dso_b200_ctx* ctx, bool fork, bool apply)
 {
 	BAWorkspace* W = ctx->ba;
 	const int nR = W->P.nR;
-	ba_linearize_kernel<<<(nR + 31) / 32, 256, 0, ctx->ba_stream>>>(W->P, W->d_precalc, W->d_pt, W->d_color, W->d_weights, W->d_phost, W->d_rpoint,
-	                                                           W->d_rtarget, W->d_state, W->d_energy, W->d_efsel, W->d_J[0], W->d_J[1],
-	                                                           W->d_newState, W->d_newEnergy, W->d_newEnergyWO, W->d_cpt, W->d_proj, W->d_resEnergy,
-	                                                           nullptr, 0, 0);
+	if (apply)
+		ba_linearize_kernel<true><<<(nR + 31) / 32, 256, 0, ctx->ba_stream>>>(W->P, W->d_precalc, W->d_pt, W->d_color, W->d_weights, W->d_phost, W->d_rpoint,
+		                                                                 W->d_rtarget, W->d_state, W->d_energy, W->d_efsel, W->d_J[0], W->d_J[1],
+		                                                                 W->d_newState, W->d_newEnergy, W->d_newEnergyWO, W->d_cpt, W->d_proj, W->d_resEnergy,
+		                                                                 nullptr, 0, 0, W->d_isAct, W->d_JpJdF);
+	else
+		ba_linearize_kernel<false><<<(nR + 31) / 32, 256, 0, ctx->ba_stream>>>(W->P, W->d_precalc, W->d_pt, W->d_color, W->d_weights, W->d_phost, W->d_rpoint,
+		                                                                  W->d_rtarget, W->d_state, W->d_energy, W->d_efsel, W->d_J[0], W->d_J[1],
+		                                                                  W->d_newState, W->d_newEnergy, W->d_newEnergyWO, W->d_cpt, W->d_proj, W->d_resEnergy,
+		                                                                  nullptr, 0, 0, nullptr, nullptr);
+	if (apply) W->top_done = false;
 	const int nb = (nR + 255) / 256;
 	cudaStream_t se = ctx->ba_stream;
 	if (fork) { int rc = ba_fork(ctx); if (rc) return rc; se = W->side_stream; }
@@ -1457,8 +1502,8 @@ int ba_enqueue_schur(dso_b200_ctx* ctx, const unsigned char* d_pmask)
 	                                                     HdiF, bdSumF, W->d_HcdSum, W->d_scPartials, W->scN);
 	const int nRed = nF * nF * 64 + nF * 32 + nF * 8 + 20;          // accD, accE, accEB, accHcc + accbc per host
 	ba_reduce_partials_kernel<<<dim3((nRed + 255) / 256, nF), 256, 0, ctx->ba_stream>>>(W->d_scPartials, W->scN, nRed, W->d_host_pc_begin, W->d_scRed);
-	ba_schur_stage1_kernel<<<nF * nF, 64, 0, ctx->ba_stream>>>(nF, W->d_scRed, nRed, W->d_adHost, W->d_adTarget, W->d_scContrib);
-	ba_schur_gather_kernel<<<nF * nF + 1, 64, 0, ctx->ba_stream>>>(nF, W->d_scRed, W->d_scContrib, W->d_HS, W->d_bS);
+	ba_schur_stage1_kernel<<<nF * nF, 64 * MAXF, 0, ctx->ba_stream>>>(nF, W->d_scRed, nRed, W->d_adHost, W->d_adTarget, W->d_scContrib);
+	ba_schur_gather_kernel<<<nF * nF + nF + 1, 64, 0, ctx->ba_stream>>>(nF, W->d_scRed, W->d_scContrib, W->d_HS, W->d_bS);
 	LAUNCHED(ctx, 5);
 	CK(cudaGetLastError());
 	return 0;
@@ -1525,10 +1570,10 @@ extern "C" int dso_b200_ba_linearize_residuals(dso_b200_ctx* ctx, int k, const i
 	BA_CHECK(k <= nR, "more indices than residuals");
 	int* d_sub = W->d_subset;
 	CK(cudaMemcpyAsync(d_sub, residual_idx, (size_t)k * sizeof(int), cudaMemcpyHostToDevice, s));
-	ba_linearize_kernel<<<(k + 31) / 32, 256, 0, s>>>(W->P, W->d_precalc, W->d_pt, W->d_color, W->d_weights, W->d_phost, W->d_rpoint,
+	ba_linearize_kernel<false><<<(k + 31) / 32, 256, 0, s>>>(W->P, W->d_precalc, W->d_pt, W->d_color, W->d_weights, W->d_phost, W->d_rpoint,
 	                                                  W->d_rtarget, W->d_state, W->d_energy, W->d_efsel, W->d_J[0], W->d_J[1],
 	                                                  W->d_newState, W->d_newEnergy, W->d_newEnergyWO, W->d_cpt, W->d_proj, W->d_resEnergy,
-	                                                  d_sub, k, reset_oob);
+	                                                  d_sub, k, reset_oob, nullptr, nullptr);
 	LAUNCHED(ctx, 1);
 	if (apply)
 	{
@@ -1639,8 +1684,7 @@ extern "C" int dso_b200_ba_step(dso_b200_ctx* ctx, double* H_A, double* b_A, dou
 	cudaStream_t s = ctx->ba_stream;
 	rc = ba_run_graphed(ctx, W->g_step, BAGraphKey{ 0.0, 0.f, 0, 0, 0, 0 }, [&]() -> int {
 		int r;
-		if ((r = ba_enqueue_linearize(ctx, true))) return r;
-		if ((r = ba_enqueue_apply(ctx))) return r;
+		if ((r = ba_enqueue_linearize(ctx, true, true))) return r;        // linearize + applyRes in one kernel
 		if ((r = ba_enqueue_top(ctx, 0, nullptr, true))) return r;
 		if ((r = ba_enqueue_schur(ctx))) return r;
 		if ((r = ba_join_side(ctx))) return r;

@@ -143,7 +143,7 @@ static int ba_run_graphed(dso_b200_ctx* ctx, BAGraph& g, const BAGraphKey& key, 
 }
 
 int ba_check_ready(dso_b200_ctx* ctx, const char* fn);
-int ba_enqueue_linearize(dso_b200_ctx* ctx, bool fork = false);
+int ba_enqueue_linearize(dso_b200_ctx* ctx, bool fork = false, bool apply = false);
 int ba_join_side(dso_b200_ctx* ctx);
 int ba_enqueue_apply(dso_b200_ctx* ctx);
 int ba_enqueue_top(dso_b200_ctx* ctx, int mode, const unsigned char* d_pmask = nullptr, bool fork = false);

@@ -820,8 +820,7 @@ extern "C" int dso_b200_ba_iteration(dso_b200_ctx* ctx, int iteration, double la
 	const BAGraphKey key = { lambda, stepfacD, solverMode, W->nLin != 0 ? 1 : 0, S->haveP ? 1 : 0, S->d_dbg ? 1 : 0 };
 	rc = ba_run_graphed(ctx, W->g_iter[orth], key, [&]() -> int {
 		int r;
-		if ((r = ba_enqueue_linearize(ctx, true))) return r;
-		if ((r = ba_enqueue_apply(ctx))) return r;
+		if ((r = ba_enqueue_linearize(ctx, true, true))) return r;        // linearize + applyRes in one kernel
 		if ((r = enqueue_solve(ctx, S, orth ? 2 : 0, lambda, solverMode, false))) return r;
 		ba_points_backup_kernel<<<(nP + 255) / 256, 256, 0, s>>>(nP, W->d_pt, S->d_idepth_backup, 0, nullptr, nullptr);
 		ba_points_step_kernel<<<nb, 256, 0, s>>>(nP, stepfacD, S->d_step, S->d_idepth_backup, W->d_pt, W->d_deltaF, S->d_stepBlocks);
