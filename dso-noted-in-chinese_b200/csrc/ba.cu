@@ -42,17 +42,16 @@ int ba_create(dso_b200_ctx* ctx)
 	CK(cudaMalloc(&W->d_adTarget, MAXF * MAXF * 64 * sizeof(double)));
 	CK(cudaMalloc(&W->d_pair_chunk_begin, (MAXF * MAXF + 1) * sizeof(int)));
 	CK(cudaMalloc(&W->d_host_pc_begin, (MAXF + 1) * sizeof(int)));
-	CK(cudaMalloc(&W->d_HA, (size_t)N * N * sizeof(double)));
-	CK(cudaMalloc(&W->d_bA, N * sizeof(double)));
-	CK(cudaMalloc(&W->d_HS, (size_t)N * N * sizeof(double)));
-	CK(cudaMalloc(&W->d_bS, N * sizeof(double)));
-	CK(cudaMalloc(&W->d_scalars, 8 * sizeof(double)));
+	// H_A | b_A | H_sc | b_sc | scalars in one block (fixed strides for the largest window): the step ends with one copy
+	CK(cudaMalloc(&W->d_outblk, BA_OUT_DOUBLES * sizeof(double)));
+	CK(cudaMemset(W->d_outblk, 0, BA_OUT_DOUBLES * sizeof(double)));
+	W->d_HA = W->d_outblk; W->d_bA = W->d_HA + (size_t)N * N; W->d_HS = W->d_bA + N; W->d_bS = W->d_HS + (size_t)N * N; W->d_scalars = W->d_bS + N;
 	// stage-1 contributions: per (i,j): C1,C2 (64 each), C3,C4 (MAXF*64 each), CEh,CEt (32 each), Cbh,Cbt (8 each)
 	CK(cudaMalloc(&W->d_scContrib, (size_t)MAXF * MAXF * (128 + 2 * MAXF * 64 + 64 + 16) * sizeof(double)));
 	CK(cudaMalloc(&W->d_scRed, (size_t)MAXF * (MAXF * MAXF * 64 + MAXF * 40 + 24) * sizeof(double)));
 	CK(cudaMalloc(&W->d_topRed, (size_t)MAXF * MAXF * NTOP_PAD * sizeof(double)));
 	CK(cudaMalloc(&W->d_topContrib, (size_t)MAXF * MAXF * 292 * sizeof(double)));
-	CK(cudaHostAlloc((void**)&W->h_out, (2 * (size_t)N * N + 2 * N + 8) * sizeof(double), cudaHostAllocDefault));
+	CK(cudaHostAlloc((void**)&W->h_out, BA_OUT_DOUBLES * sizeof(double), cudaHostAllocDefault));
 	W->d_energy_blocks = nullptr;
 	CK(cudaMalloc(&W->d_adHTdeltaF, MAXF * MAXF * 8 * sizeof(float)));
 	CK(cudaMalloc(&W->d_cDeltaF, 4 * sizeof(float)));
@@ -130,7 +129,7 @@ void ba_destroy(dso_b200_ctx* ctx)
 	free_points(W); free_res(W);
 	cudaFree(W->d_adHTdeltaF); cudaFree(W->d_cDeltaF); cudaFree(W->d_HL); cudaFree(W->d_bL); cudaFree(W->d_priorH); cudaFree(W->d_priorD); cudaFree(W->d_delta);
 	cudaFree(W->d_precalc); cudaFree(W->d_adHost); cudaFree(W->d_adTarget); cudaFree(W->d_pair_chunk_begin); cudaFree(W->d_host_pc_begin);
-	cudaFree(W->d_HA); cudaFree(W->d_bA); cudaFree(W->d_HS); cudaFree(W->d_bS); cudaFree(W->d_scalars); cudaFree(W->d_scContrib); cudaFree(W->d_scRed); cudaFree(W->d_topRed); cudaFree(W->d_topContrib);
+	cudaFree(W->d_outblk); cudaFree(W->d_scContrib); cudaFree(W->d_scRed); cudaFree(W->d_topRed); cudaFree(W->d_topContrib);
 	cudaFreeHost(W->h_out);
 	if (W->side_stream) { cudaStreamSynchronize(W->side_stream); cudaStreamDestroy(W->side_stream); }
 	if (W->ev_fork) cudaEventDestroy(W->ev_fork);
@@ -1688,22 +1687,19 @@ extern "C" int dso_b200_ba_step(dso_b200_ctx* ctx, double* H_A, double* b_A, dou
 		if ((r = ba_enqueue_top(ctx, 0, nullptr, true))) return r;
 		if ((r = ba_enqueue_schur(ctx))) return r;
 		if ((r = ba_join_side(ctx))) return r;
-		CK(cudaMemcpyAsync(W->h_out, W->d_HA, NN * sizeof(double), cudaMemcpyDeviceToHost, s));
-		CK(cudaMemcpyAsync(W->h_out + NN, W->d_bA, N * sizeof(double), cudaMemcpyDeviceToHost, s));
-		CK(cudaMemcpyAsync(W->h_out + NN + N, W->d_HS, NN * sizeof(double), cudaMemcpyDeviceToHost, s));
-		CK(cudaMemcpyAsync(W->h_out + 2 * NN + N, W->d_bS, N * sizeof(double), cudaMemcpyDeviceToHost, s));
-		CK(cudaMemcpyAsync(W->h_out + 2 * NN + 2 * N, W->d_scalars, 2 * sizeof(double), cudaMemcpyDeviceToHost, s));
+		CK(cudaMemcpyAsync(W->h_out, W->d_outblk, BA_OUT_DOUBLES * sizeof(double), cudaMemcpyDeviceToHost, s));
 		return 0;
 	});
 	if (rc) return rc;
 	W->top_done = true;
 	CK(cudaStreamSynchronize(s));
+	const size_t NM = 8 * MAXF + CPARS, oB = NM * NM, oS = oB + NM, oBS = oS + NM * NM, oSc = oBS + NM;   // strides of the block
 	memcpy(H_A, W->h_out, NN * sizeof(double));
-	memcpy(b_A, W->h_out + NN, N * sizeof(double));
-	memcpy(H_sc, W->h_out + NN + N, NN * sizeof(double));
-	memcpy(b_sc, W->h_out + 2 * NN + N, N * sizeof(double));
-	if (energy_sum) *energy_sum = W->h_out[2 * NN + 2 * N];
-	if (resInA) *resInA = (int)W->h_out[2 * NN + 2 * N + 1];
+	memcpy(b_A, W->h_out + oB, N * sizeof(double));
+	memcpy(H_sc, W->h_out + oS, NN * sizeof(double));
+	memcpy(b_sc, W->h_out + oBS, N * sizeof(double));
+	if (energy_sum) *energy_sum = W->h_out[oSc];
+	if (resInA) *resInA = (int)W->h_out[oSc + 1];
 	W->lin_done = false;
 	return 0;
 }

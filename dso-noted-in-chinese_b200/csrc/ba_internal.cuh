@@ -4,6 +4,7 @@
 #include <vector>
 
 #define CPARS 4
+#define BA_OUT_DOUBLES (2 * (size_t)(8 * MAXF + CPARS) * (8 * MAXF + CPARS) + 2 * (8 * MAXF + CPARS) + 8)
 #define CHUNK_R 64
 #define CHUNK_P 16
 #define NTOP 91           // 55 + 30 + 6 unique entries of the 13x13 block
@@ -93,6 +94,7 @@ struct BAWorkspace
 	double* d_scContrib;       // stage-1 contributions
 	double* d_scRed; double* d_topRed; double* d_topContrib;
 	// outputs
+	double* d_outblk;          // one allocation holding the five buffers below
 	double* d_HA; double* d_bA; double* d_HS; double* d_bS; double* d_energy_blocks; double* d_scalars;   // [0] energy sum, [1] resInA
 	double* h_out;             // pinned: HA, bA, HS, bS, scalars
 	std::vector<int> h_rpoint, h_res_begin, h_phost;
