@@ -1,16 +1,20 @@
 // K1 -- image / gradient pyramid, replaces FrameHessian::makeImages
 // (reference: FullSystem/HessianBlocks.cpp:137-211).
 //
-// Two launches per frame, whatever the number of levels:
-//   1. pyr_intensity_kernel: each CTA owns a 64x64 tile of the input image and cascades the exact
-//      2x2 box sums  0.25f*(((a+b)+c)+d)  (:179-182) through shared memory for all coarser levels,
-//      so level l+1 is bit-identical to the reference's level-by-level loop.
-//   2. pyr_gradient_kernel: all levels in one grid; each thread handles 4 consecutive pixels with
-//      float4 loads of the three rows and writes (I,dx,dy,|grad|^2) as one float4 per pixel (the
-//      device-resident layout every gather in the tracker / BA uses) and, on request, the
-//      reference's 12-byte AoS + absSquaredGrad arrays through 16-byte stores for the host copy.
+// One launch per frame, one pass over the input (pyr_fused_kernel): each CTA owns a 64x64 tile of the input image and
+// the matching tiles of all coarser levels.  It brings the tile plus a halo of 2^(levels-1) pixels into shared memory --
+// with one TMA tile load (cp.async.bulk.tensor.2d, out-of-image elements zero-filled by the hardware) when the image
+// pitch and address allow, with plain loads otherwise -- cascades the exact 2x2 box sums 0.25f*(((a+b)+c)+d) (:179-182)
+// through shared memory, so that level l+1 is bit-identical to the reference's level-by-level loop, and computes the
+// gradients of EVERY level from the shared-memory tiles (the halo shrinks to one pixel at the coarsest level), writing
+// (I,dx,dy,|grad|^2) as one float4 per pixel -- the device-resident layout every gather in the tracker / BA uses -- and, on
+// request, the reference's 12-byte AoS + absSquaredGrad arrays for the host copy.  The halo pixels are re-read through L2
+// (they are the neighbouring CTAs' tiles), DRAM sees the input once.  The reference's dx at x = 0 / w-1 reads the pixel of
+// the neighbouring row (linear index +-1): those few pixels are rebuilt from the input by the exact cascade.
+// The two-launch form (pyr_intensity_kernel + pyr_gradient_kernel) remains for DSO_B200_K1_TWO_PASS=1 (A/B timing).
 // HBM-bound stencil: algorithmic bytes per frame = 4*w*h in + 16*sum_l(w_l*h_l) out.
 #include "common.cuh"
+#include <cuda.h>
 
 #define TILE 64
 
@@ -151,6 +155,120 @@ __global__ void __launch_bounds__(256) pyr_gradient_kernel(GradArgs a)
 	}
 }
 
+// ---- single-pass kernel ---------------------------------------------------------------------------------------
+struct FusedArgs
+{
+	const float* src;
+	int w, h, levels, H;      // H: halo of the level-0 tile (a multiple of 2^(levels-1), >= 4)
+	float4* out[MAXL];
+	float* aos[MAXL];         // may be null
+	float* absg[MAXL];        // may be null
+	const float* Blut;        // may be null
+};
+
+// pixel (x, y) of pyramid level l rebuilt from the level-0 input with the reference's cascade (only for the handful of
+// row-wrap neighbours at the image's left / right edge)
+__device__ __noinline__ float pyr_pixel_from_input(const float* __restrict__ src, int w, int l, int x, int y)
+{
+	if (l == 0) return __ldg(src + (size_t)y * w + x);
+	const float a = pyr_pixel_from_input(src, w, l - 1, 2 * x, 2 * y), b = pyr_pixel_from_input(src, w, l - 1, 2 * x + 1, 2 * y);
+	const float c = pyr_pixel_from_input(src, w, l - 1, 2 * x, 2 * y + 1), d = pyr_pixel_from_input(src, w, l - 1, 2 * x + 1, 2 * y + 1);
+	return fmul(0.25f, fadd(fadd(fadd(a, b), c), d));
+}
+
+template <bool USE_TMA>
+__global__ void __launch_bounds__(256) pyr_fused_kernel(const __grid_constant__ CUtensorMap tmap, FusedArgs a)
+{
+	extern __shared__ __align__(128) float sm[];
+	__shared__ __align__(8) unsigned long long bar;
+	const int tid = threadIdx.x;
+	const int x0 = blockIdx.x * TILE, y0 = blockIdx.y * TILE;
+	const int S0 = TILE + 2 * a.H;
+	float* reg[MAXL];
+	{
+		float* p = sm;
+		for (int l = 0; l < a.levels; l++) { reg[l] = p; const int S = S0 >> l; p += S * S; }
+	}
+	if (USE_TMA)
+	{
+		const unsigned bar_s = (unsigned)__cvta_generic_to_shared(&bar), dst_s = (unsigned)__cvta_generic_to_shared(sm);
+		if (tid == 0)
+		{
+			asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar_s) : "memory");
+			asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+			asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar_s), "r"((unsigned)(S0 * S0 * 4)) : "memory");
+			asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+			             ::"r"(dst_s), "l"(&tmap), "r"(x0 - a.H), "r"(y0 - a.H), "r"(bar_s) : "memory");
+		}
+		__syncthreads();      // the barrier is initialised before anybody polls it
+		asm volatile(
+			"{\n"
+			".reg .pred p;\n"
+			"PYR_WAIT:\n"
+			"mbarrier.try_wait.parity.shared::cta.b64 p, [%0], 0;\n"
+			"@p bra PYR_DONE;\n"
+			"bra PYR_WAIT;\n"
+			"PYR_DONE:\n"
+			"}\n" ::"r"(bar_s) : "memory");
+	}
+	else
+	{
+		for (int i = tid; i < S0 * S0; i += 256)
+		{
+			const int r = i / S0, c = i - r * S0;
+			const int x = x0 - a.H + c, y = y0 - a.H + r;
+			sm[i] = (x >= 0 && y >= 0 && x < a.w && y < a.h) ? __ldg(a.src + (size_t)y * a.w + x) : 0.f;
+		}
+		__syncthreads();
+	}
+	// ---- intensity cascade over the whole region (:179-182) ----
+	for (int l = 1; l < a.levels; l++)
+	{
+		const int Ss = S0 >> (l - 1), Sd = S0 >> l;
+		const float* cur = reg[l - 1];
+		float* nxt = reg[l];
+		for (int i = tid; i < Sd * Sd; i += 256)
+		{
+			const int yy = i / Sd, xx = i - yy * Sd;
+			const float* p = cur + (2 * yy) * Ss + 2 * xx;
+			nxt[i] = fmul(0.25f, fadd(fadd(fadd(p[0], p[1]), p[Ss]), p[Ss + 1]));
+		}
+		__syncthreads();
+	}
+	// ---- gradients of every level from shared memory (:186-209) ----
+	for (int l = 0; l < a.levels; l++)
+	{
+		const int S = S0 >> l, T = TILE >> l, hl0 = a.H >> l;
+		const int wl = a.w >> l, hl = a.h >> l;
+		const int gx0 = x0 >> l, gy0 = y0 >> l;
+		const float* R = reg[l];
+		float4* out = a.out[l];
+		const int nT = T * T;
+		for (int i = tid; i < nT; i += 256)
+		{
+			const int py = i / T, px = i - py * T;
+			const int gx = gx0 + px, gy = gy0 + py;
+			if (gx >= wl || gy >= hl) continue;
+			const float* q = R + (hl0 + py) * S + hl0 + px;
+			const float c = q[0];
+			const bool interior = gy >= 1 && gy < hl - 1;                 // idx in [wl, wl*(hl-1)), :188
+			float lf = 0.f, rt = 0.f, u = 0.f, d = 0.f;
+			if (interior)
+			{
+				u = q[-S]; d = q[S];
+				lf = gx > 0 ? q[-1] : pyr_pixel_from_input(a.src, a.w, l, wl - 1, gy - 1);     // I[idx-1] wraps to the previous row
+				rt = gx < wl - 1 ? q[1] : pyr_pixel_from_input(a.src, a.w, l, 0, gy + 1);      // I[idx+1] wraps to the next row
+			}
+			float dx, dy, ab;
+			grad_px(c, lf, rt, u, d, a.Blut, interior, dx, dy, ab);
+			const size_t idx = (size_t)gy * wl + gx;
+			out[idx] = make_float4(c, dx, dy, ab);
+			if (a.aos[l]) { a.aos[l][3 * idx] = c; a.aos[l][3 * idx + 1] = dx; a.aos[l][3 * idx + 2] = dy; }
+			if (a.absg[l]) a.absg[l][idx] = ab;
+		}
+	}
+}
+
 int pyramid_build(dso_b200_ctx* ctx, FrameSlot& fs, const float* color_dev, int w, int h, int levels,
                   const float* d_Blut, bool host_layout)
 {
@@ -161,6 +279,69 @@ int pyramid_build_on(dso_b200_ctx* ctx, cudaStream_t stream, FrameSlot& fs, cons
                      const float* d_Blut, bool host_layout)
 {
 	fs.w = w; fs.h = h; fs.levels = levels;
+	static int two_pass = -1;
+	if (two_pass < 0) { const char* e = getenv("DSO_B200_K1_TWO_PASS"); two_pass = (e && atoi(e)) ? 1 : 0; }
+	if (!two_pass)
+	{
+		FusedArgs fa;
+		memset(&fa, 0, sizeof(fa));
+		fa.src = color_dev; fa.w = w; fa.h = h; fa.levels = levels;
+		fa.H = levels > 3 ? (1 << (levels - 1)) : 4;
+		fa.Blut = d_Blut;
+		for (int l = 0; l < levels; l++)
+		{
+			fa.out[l] = fs.pyr[l];
+			fa.aos[l] = host_layout ? ctx->d_aos[l] : nullptr;
+			fa.absg[l] = host_layout ? ctx->d_abs[l] : nullptr;
+		}
+		const int S0 = TILE + 2 * fa.H;
+		size_t smem = 0;
+		for (int l = 0; l < levels; l++) smem += (size_t)(S0 >> l) * (S0 >> l) * sizeof(float);
+		static bool attr_done[64] = { false };
+		if (!attr_done[ctx->device & 63])
+		{
+			CK(cudaFuncSetAttribute(pyr_fused_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+			CK(cudaFuncSetAttribute(pyr_fused_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+			attr_done[ctx->device & 63] = true;
+		}
+		// TMA tile load: needs a 16-byte aligned base and pitch; anything else takes the plain-load instantiation
+		CUtensorMap tm;
+		memset(&tm, 0, sizeof(tm));
+		bool tma = ((w & 3) == 0) && ((reinterpret_cast<size_t>(color_dev) & 15) == 0);
+		if (tma)
+		{
+			typedef CUresult (*encode_fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+			                              const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+			static encode_fn encode = nullptr;
+			static bool looked = false;
+			if (!looked)
+			{
+				void* fn = nullptr;
+				cudaDriverEntryPointQueryResult q;
+				if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess) encode = (encode_fn)fn;
+				looked = true;
+			}
+			if (!encode) tma = false;
+			else
+			{
+				const cuuint64_t gdim[2] = { (cuuint64_t)w, (cuuint64_t)h };
+				const cuuint64_t gstr[1] = { (cuuint64_t)w * sizeof(float) };
+				const cuuint32_t box[2] = { (cuuint32_t)S0, (cuuint32_t)S0 };
+				const cuuint32_t estr[2] = { 1, 1 };
+				const CUresult r = encode(&tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(color_dev), gdim, gstr, box, estr,
+				                          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+				                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+				if (r != CUDA_SUCCESS) tma = false;
+			}
+		}
+		const dim3 grid((w + TILE - 1) / TILE, (h + TILE - 1) / TILE);
+		if (tma) pyr_fused_kernel<true><<<grid, 256, smem, stream>>>(tm, fa);
+		else pyr_fused_kernel<false><<<grid, 256, smem, stream>>>(tm, fa);
+		LAUNCHED(ctx, 1);
+		CK(cudaGetLastError());
+		fs.valid = true;
+		return 0;
+	}
 	IntensityArgs ia;
 	ia.src = color_dev; ia.w = w; ia.h = h; ia.levels = levels;
 	for (int l = 0; l < MAXL; l++) ia.inten[l] = fs.inten[l];
