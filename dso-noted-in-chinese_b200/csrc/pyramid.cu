@@ -166,16 +166,6 @@ struct FusedArgs
 	const float* Blut;        // may be null
 };
 
-// pixel (x, y) of pyramid level l rebuilt from the level-0 input with the reference's cascade (only for the handful of
-// row-wrap neighbours at the image's left / right edge)
-__device__ __noinline__ float pyr_pixel_from_input(const float* __restrict__ src, int w, int l, int x, int y)
-{
-	if (l == 0) return __ldg(src + (size_t)y * w + x);
-	const float a = pyr_pixel_from_input(src, w, l - 1, 2 * x, 2 * y), b = pyr_pixel_from_input(src, w, l - 1, 2 * x + 1, 2 * y);
-	const float c = pyr_pixel_from_input(src, w, l - 1, 2 * x, 2 * y + 1), d = pyr_pixel_from_input(src, w, l - 1, 2 * x + 1, 2 * y + 1);
-	return fmul(0.25f, fadd(fadd(fadd(a, b), c), d));
-}
-
 template <bool USE_TMA>
 __global__ void __launch_bounds__(256) pyr_fused_kernel(const __grid_constant__ CUtensorMap tmap, FusedArgs a)
 {
@@ -184,11 +174,6 @@ __global__ void __launch_bounds__(256) pyr_fused_kernel(const __grid_constant__ 
 	const int tid = threadIdx.x;
 	const int x0 = blockIdx.x * TILE, y0 = blockIdx.y * TILE;
 	const int S0 = TILE + 2 * a.H;
-	float* reg[MAXL];
-	{
-		float* p = sm;
-		for (int l = 0; l < a.levels; l++) { reg[l] = p; const int S = S0 >> l; p += S * S; }
-	}
 	if (USE_TMA)
 	{
 		const unsigned bar_s = (unsigned)__cvta_generic_to_shared(&bar), dst_s = (unsigned)__cvta_generic_to_shared(sm);
@@ -221,51 +206,104 @@ __global__ void __launch_bounds__(256) pyr_fused_kernel(const __grid_constant__ 
 		}
 		__syncthreads();
 	}
-	// ---- intensity cascade over the whole region (:179-182) ----
-	for (int l = 1; l < a.levels; l++)
-	{
-		const int Ss = S0 >> (l - 1), Sd = S0 >> l;
-		const float* cur = reg[l - 1];
-		float* nxt = reg[l];
-		for (int i = tid; i < Sd * Sd; i += 256)
-		{
-			const int yy = i / Sd, xx = i - yy * Sd;
-			const float* p = cur + (2 * yy) * Ss + 2 * xx;
-			nxt[i] = fmul(0.25f, fadd(fadd(fadd(p[0], p[1]), p[Ss]), p[Ss + 1]));
-		}
-		__syncthreads();
-	}
-	// ---- gradients of every level from shared memory (:186-209) ----
+	// ---- level by level: gradients of level l from its shared-memory region (:186-209), then the region of level l+1 by the
+	// box cascade (:179-182); the two do not depend on each other, one barrier per level ----
+	float* R = sm;
 	for (int l = 0; l < a.levels; l++)
 	{
-		const int S = S0 >> l, T = TILE >> l, hl0 = a.H >> l;
+		const int S = S0 >> l, sh = 6 - l, T = TILE >> l, hl0 = a.H >> l;
 		const int wl = a.w >> l, hl = a.h >> l;
 		const int gx0 = x0 >> l, gy0 = y0 >> l;
-		const float* R = reg[l];
-		float4* out = a.out[l];
-		const int nT = T * T;
-		for (int i = tid; i < nT; i += 256)
+		float* nxt = R + S * S;
+		if (l + 1 < a.levels)
 		{
-			const int py = i / T, px = i - py * T;
+			const int Sd = S >> 1;
+			for (int i = tid; i < Sd * Sd; i += 256)
+			{
+				const int yy = i / Sd, xx = i - yy * Sd;
+				const float* p = R + (2 * yy) * S + 2 * xx;
+				nxt[i] = fmul(0.25f, fadd(fadd(fadd(p[0], p[1]), p[S]), p[S + 1]));
+			}
+		}
+		float4* out = a.out[l];
+		float* aos = a.aos[l];
+		float* absg = a.absg[l];
+		for (int i = tid; i < T * T; i += 256)
+		{
+			const int py = i >> sh, px = i & (T - 1);
 			const int gx = gx0 + px, gy = gy0 + py;
 			if (gx >= wl || gy >= hl) continue;
 			const float* q = R + (hl0 + py) * S + hl0 + px;
 			const float c = q[0];
 			const bool interior = gy >= 1 && gy < hl - 1;                 // idx in [wl, wl*(hl-1)), :188
-			float lf = 0.f, rt = 0.f, u = 0.f, d = 0.f;
-			if (interior)
-			{
-				u = q[-S]; d = q[S];
-				lf = gx > 0 ? q[-1] : pyr_pixel_from_input(a.src, a.w, l, wl - 1, gy - 1);     // I[idx-1] wraps to the previous row
-				rt = gx < wl - 1 ? q[1] : pyr_pixel_from_input(a.src, a.w, l, 0, gy + 1);      // I[idx+1] wraps to the next row
-			}
+			if (interior && (gx == 0 || gx == wl - 1)) continue;          // written by the row-wrap pass below
 			float dx, dy, ab;
-			grad_px(c, lf, rt, u, d, a.Blut, interior, dx, dy, ab);
+			grad_px(c, q[-1], q[1], q[-S], q[S], a.Blut, interior, dx, dy, ab);
 			const size_t idx = (size_t)gy * wl + gx;
 			out[idx] = make_float4(c, dx, dy, ab);
-			if (a.aos[l]) { a.aos[l][3 * idx] = c; a.aos[l][3 * idx + 1] = dx; a.aos[l][3 * idx + 2] = dy; }
-			if (a.absg[l]) a.absg[l][idx] = ab;
+			if (aos) { aos[3 * idx] = c; aos[3 * idx + 1] = dx; aos[3 * idx + 2] = dy; }
+			if (absg) absg[idx] = ab;
 		}
+		// the reference's dx at x = 0 / w-1 reads the pixel of the neighbouring row (linear index +-1): the CTAs on the
+		// image's left / right edge write those pixels with the wrapped neighbour rebuilt from the input
+		const bool left = (gx0 == 0), right = (gx0 <= wl - 1 && wl - 1 < gx0 + T);
+		for (int side = 0; side < 2; side++)
+		{
+			if (!(side == 0 ? left : right)) continue;                     // uniform over the CTA
+			// the T wrapped neighbours of this tile: column cx of level l, rows ry0 .. ry0 + T - 1.  For l >= 1 they are rebuilt
+			// by the whole CTA: the 64 x 2^l strip of the input under that column goes to shared memory (the level-0 region is
+			// dead by now) and runs through the same cascade
+			const int cx = side == 0 ? wl - 1 : 0, ry0 = side == 0 ? gy0 - 1 : gy0 + 1;
+			const float* col = nullptr;
+			if (l >= 1)
+			{
+				__syncthreads();
+				float* ping = sm; float* pong = sm + 2048;
+				const int Ws = 1 << l;
+				for (int i = tid; i < 64 * Ws; i += 256)
+				{
+					const int r = i >> l, c = i & (Ws - 1);
+					const int y = (ry0 << l) + r, x = (cx << l) + c;
+					ping[i] = (y >= 0 && y < a.h && x < a.w) ? __ldg(a.src + (size_t)y * a.w + x) : 0.f;
+				}
+				__syncthreads();
+				int wk = Ws, hk = 64;
+				for (int k = 0; k < l; k++)
+				{
+					const int wd = wk >> 1, hd = hk >> 1;
+					for (int i = tid; i < wd * hd; i += 256)
+					{
+						const int yy = i / wd, xx = i - yy * wd;
+						const float* p = ping + (2 * yy) * wk + 2 * xx;
+						pong[i] = fmul(0.25f, fadd(fadd(fadd(p[0], p[1]), p[wk]), p[wk + 1]));
+					}
+					__syncthreads();
+					float* t = ping; ping = pong; pong = t;
+					wk = wd; hk = hd;
+				}
+				col = ping;                                                // T values: level-l pixel (cx, ry0 + py)
+			}
+			for (int py = tid; py < T; py += 256)
+			{
+				const int gx = side == 0 ? 0 : wl - 1, gy = gy0 + py;
+				if (gy < 1 || gy >= hl - 1) continue;
+				const float wrap = l >= 1 ? col[py] : __ldg(a.src + (size_t)(ry0 + py) * a.w + cx);
+				const int px = gx - gx0;
+				const float* q = R + (hl0 + py) * S + hl0 + px;
+				const float c = q[0];
+				// I[idx-1] of x = 0 is the last pixel of the previous row, I[idx+1] of x = w-1 the first of the next (:190)
+				const float lf = (side == 0) ? wrap : ((wl > 1) ? q[-1] : wrap);
+				const float rt = (side == 1) ? wrap : q[1];
+				float dx, dy, ab;
+				grad_px(c, lf, rt, q[-S], q[S], a.Blut, true, dx, dy, ab);
+				const size_t idx = (size_t)gy * wl + gx;
+				out[idx] = make_float4(c, dx, dy, ab);
+				if (aos) { aos[3 * idx] = c; aos[3 * idx + 1] = dx; aos[3 * idx + 2] = dy; }
+				if (absg) absg[idx] = ab;
+			}
+		}
+		__syncthreads();      // region l+1 complete
+		R = nxt;
 	}
 }
 
@@ -307,7 +345,9 @@ int pyramid_build_on(dso_b200_ctx* ctx, cudaStream_t stream, FrameSlot& fs, cons
 		// TMA tile load: needs a 16-byte aligned base and pitch; anything else takes the plain-load instantiation
 		CUtensorMap tm;
 		memset(&tm, 0, sizeof(tm));
-		bool tma = ((w & 3) == 0) && ((reinterpret_cast<size_t>(color_dev) & 15) == 0);
+		static int no_tma = -1;
+		if (no_tma < 0) { const char* e = getenv("DSO_B200_K1_NO_TMA"); no_tma = (e && atoi(e)) ? 1 : 0; }
+		bool tma = !no_tma && ((w & 3) == 0) && ((reinterpret_cast<size_t>(color_dev) & 15) == 0);
 		if (tma)
 		{
 			typedef CUresult (*encode_fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
