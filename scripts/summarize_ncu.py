@@ -48,8 +48,23 @@ def full(rep, out):
                     f.write("  %-66s %16s %s\n" % (k, r[i], units[i]))
 
 
+def traffic(rep, out, pattern="track_persistent"):
+    """mean dram__bytes_read + dram__bytes_write per launch of the kernels matching `pattern` -> small JSON read by bench.py"""
+    import json
+    txt = subprocess.check_output(["ncu", "-i", rep, "--page", "raw", "--csv"], text=True)
+    rows = list(csv.reader(txt.splitlines()))
+    hdr, units = rows[0], rows[1]
+    ik, ir, iw = hdr.index("Kernel Name"), hdr.index("dram__bytes_read.sum"), hdr.index("dram__bytes_write.sum")
+    scale = {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    vals = [float(r[ir].replace(",", "")) * scale[units[ir]] + float(r[iw].replace(",", "")) * scale[units[iw]] for r in rows[2:] if pattern in r[ik]]
+    json.dump({"kernel": pattern, "launches": len(vals), "dram_bytes_per_launch": sum(vals) / len(vals),
+               "source": "ncu --set full --clock-control none, %s, dram__bytes_read.sum + dram__bytes_write.sum, cold L2" % rep}, open(out, "w"), indent=1)
+
+
 if __name__ == "__main__":
-    if sys.argv[1] == "list":
+    if sys.argv[1] == "traffic":
+        traffic(sys.argv[2], sys.argv[3])
+    elif sys.argv[1] == "list":
         launch_list(sys.argv[2], sys.argv[3])
     else:
         full(sys.argv[2], sys.argv[3])
