@@ -166,7 +166,42 @@ struct FusedArgs
 	const float* Blut;        // may be null
 };
 
-template <bool USE_TMA>
+// gradients of one level's owned tile (T = 2^SH pixels square) from its shared-memory region; compile-time tile size so
+// that the pixel loop is unrolled with shifts only; EXTRA = gamma LUT and / or the host-layout copies are wanted
+template <int SH, bool EXTRA>
+__device__ __forceinline__ void pyr_grad_tile(const FusedArgs& a, int l, const float* __restrict__ R, int S, int hl0, int wl, int hl,
+                                              int gx0, int gy0, int tid)
+{
+	constexpr int T = 1 << SH, N = T * T, ITER = (N + 255) / 256;
+	float4* __restrict__ out = a.out[l];
+	float* aos = EXTRA ? a.aos[l] : nullptr;
+	float* absg = EXTRA ? a.absg[l] : nullptr;
+	const float* Blut = EXTRA ? a.Blut : nullptr;
+#pragma unroll
+	for (int it = 0; it < ITER; it++)
+	{
+		const int i = tid + 256 * it;
+		if (N < 256 && i >= N) break;
+		const int py = i >> SH, px = i & (T - 1);
+		const int gx = gx0 + px, gy = gy0 + py;
+		if (gx >= wl || gy >= hl) continue;
+		const float* q = R + (hl0 + py) * S + hl0 + px;
+		const float c = q[0];
+		const bool interior = gy >= 1 && gy < hl - 1;                 // idx in [wl, wl*(hl-1)), :188
+		if (interior && (gx == 0 || gx == wl - 1)) continue;          // written by the row-wrap pass
+		float dx, dy, ab;
+		grad_px(c, q[-1], q[1], q[-S], q[S], Blut, interior, dx, dy, ab);
+		const size_t idx = (size_t)gy * wl + gx;
+		out[idx] = make_float4(c, dx, dy, ab);
+		if (EXTRA)
+		{
+			if (aos) { aos[3 * idx] = c; aos[3 * idx + 1] = dx; aos[3 * idx + 2] = dy; }
+			if (absg) absg[idx] = ab;
+		}
+	}
+}
+
+template <bool USE_TMA, bool EXTRA>
 __global__ void __launch_bounds__(256) pyr_fused_kernel(const __grid_constant__ CUtensorMap tmap, FusedArgs a)
 {
 	extern __shared__ __align__(128) float sm[];
@@ -211,7 +246,7 @@ __global__ void __launch_bounds__(256) pyr_fused_kernel(const __grid_constant__ 
 	float* R = sm;
 	for (int l = 0; l < a.levels; l++)
 	{
-		const int S = S0 >> l, sh = 6 - l, T = TILE >> l, hl0 = a.H >> l;
+		const int S = S0 >> l, T = TILE >> l, hl0 = a.H >> l;
 		const int wl = a.w >> l, hl = a.h >> l;
 		const int gx0 = x0 >> l, gy0 = y0 >> l;
 		float* nxt = R + S * S;
@@ -225,25 +260,18 @@ __global__ void __launch_bounds__(256) pyr_fused_kernel(const __grid_constant__ 
 				nxt[i] = fmul(0.25f, fadd(fadd(fadd(p[0], p[1]), p[S]), p[S + 1]));
 			}
 		}
+		switch (l)
+		{
+		case 0: pyr_grad_tile<6, EXTRA>(a, l, R, S, hl0, wl, hl, gx0, gy0, tid); break;
+		case 1: pyr_grad_tile<5, EXTRA>(a, l, R, S, hl0, wl, hl, gx0, gy0, tid); break;
+		case 2: pyr_grad_tile<4, EXTRA>(a, l, R, S, hl0, wl, hl, gx0, gy0, tid); break;
+		case 3: pyr_grad_tile<3, EXTRA>(a, l, R, S, hl0, wl, hl, gx0, gy0, tid); break;
+		case 4: pyr_grad_tile<2, EXTRA>(a, l, R, S, hl0, wl, hl, gx0, gy0, tid); break;
+		default: pyr_grad_tile<1, EXTRA>(a, l, R, S, hl0, wl, hl, gx0, gy0, tid); break;
+		}
 		float4* out = a.out[l];
 		float* aos = a.aos[l];
 		float* absg = a.absg[l];
-		for (int i = tid; i < T * T; i += 256)
-		{
-			const int py = i >> sh, px = i & (T - 1);
-			const int gx = gx0 + px, gy = gy0 + py;
-			if (gx >= wl || gy >= hl) continue;
-			const float* q = R + (hl0 + py) * S + hl0 + px;
-			const float c = q[0];
-			const bool interior = gy >= 1 && gy < hl - 1;                 // idx in [wl, wl*(hl-1)), :188
-			if (interior && (gx == 0 || gx == wl - 1)) continue;          // written by the row-wrap pass below
-			float dx, dy, ab;
-			grad_px(c, q[-1], q[1], q[-S], q[S], a.Blut, interior, dx, dy, ab);
-			const size_t idx = (size_t)gy * wl + gx;
-			out[idx] = make_float4(c, dx, dy, ab);
-			if (aos) { aos[3 * idx] = c; aos[3 * idx + 1] = dx; aos[3 * idx + 2] = dy; }
-			if (absg) absg[idx] = ab;
-		}
 		// the reference's dx at x = 0 / w-1 reads the pixel of the neighbouring row (linear index +-1): the CTAs on the
 		// image's left / right edge write those pixels with the wrapped neighbour rebuilt from the input
 		const bool left = (gx0 == 0), right = (gx0 <= wl - 1 && wl - 1 < gx0 + T);
@@ -338,8 +366,10 @@ int pyramid_build_on(dso_b200_ctx* ctx, cudaStream_t stream, FrameSlot& fs, cons
 		static bool attr_done[64] = { false };
 		if (!attr_done[ctx->device & 63])
 		{
-			CK(cudaFuncSetAttribute(pyr_fused_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
-			CK(cudaFuncSetAttribute(pyr_fused_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+			CK(cudaFuncSetAttribute(pyr_fused_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+			CK(cudaFuncSetAttribute(pyr_fused_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+			CK(cudaFuncSetAttribute(pyr_fused_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+			CK(cudaFuncSetAttribute(pyr_fused_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
 			attr_done[ctx->device & 63] = true;
 		}
 		// TMA tile load: needs a 16-byte aligned base and pitch; anything else takes the plain-load instantiation
@@ -375,8 +405,9 @@ int pyramid_build_on(dso_b200_ctx* ctx, cudaStream_t stream, FrameSlot& fs, cons
 			}
 		}
 		const dim3 grid((w + TILE - 1) / TILE, (h + TILE - 1) / TILE);
-		if (tma) pyr_fused_kernel<true><<<grid, 256, smem, stream>>>(tm, fa);
-		else pyr_fused_kernel<false><<<grid, 256, smem, stream>>>(tm, fa);
+		const bool extra = host_layout || d_Blut != nullptr;
+		if (tma) { if (extra) pyr_fused_kernel<true, true><<<grid, 256, smem, stream>>>(tm, fa); else pyr_fused_kernel<true, false><<<grid, 256, smem, stream>>>(tm, fa); }
+		else { if (extra) pyr_fused_kernel<false, true><<<grid, 256, smem, stream>>>(tm, fa); else pyr_fused_kernel<false, false><<<grid, 256, smem, stream>>>(tm, fa); }
 		LAUNCHED(ctx, 1);
 		CK(cudaGetLastError());
 		fs.valid = true;
