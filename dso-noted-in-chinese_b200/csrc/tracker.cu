@@ -979,18 +979,33 @@ __device__ __noinline__ void lm_finalize(dso_b200_track_result* res, const float
                                          float oldFT, float oldFRT, float oldFN, float modeA, float modeB,
                                          float ref_exposure, float new_exposure, double ref_a, double ref_b)
 {
-	if (lane < n_passes) res->pass_rmse[lane] = (double)sqrtf((float)((double)s_passE[lane] / (double)s_passN[lane]));
+	// spread over the lanes (this runs once per frame, in front of the result's trip to the host): the passes' RMSEs by
+	// one lane each, the flow indicators by lanes 1 and 2, the counters by lane 3, the acceptance test by lane 0
+	static_assert(DSO_B200_MAX_PASSES <= 16, "one lane per pass below lane 16");
+	const bool isPass = lane < n_passes;
+	const double rmse = isPass ? (double)sqrtf((float)((double)s_passE[lane] / (double)s_passN[lane])) : 0.0;
+	const int plv = isPass ? res->pass_level[lane] : -1 - lane;
+	bool lastOfLevel = isPass;            // the reference's loop lets the last pass of a level win (:710)
+	for (int q = 1; q < DSO_B200_MAX_PASSES; q++)
+	{
+		const int lq = __shfl_sync(0xffffffffu, plv, q);
+		if (q > lane && q < n_passes && lq == plv) lastOfLevel = false;
+	}
+	if (isPass) res->pass_rmse[lane] = rmse;
 	if (lane < 12) res->pose[lane] = pe_cur;
 	if (lane >= 16 && lane < 21) res->lastResiduals[lane - 16] = NAN;      // :563
 	__syncwarp();
-	if (lane == 0)
+	if (lastOfLevel) res->lastResiduals[plv] = rmse;
+	if (lane == 1) { res->lastFlowIndicators[0] = (double)oldFT / ((double)oldFN + 0.1); res->lastFlowIndicators[1] = 0; }
+	if (lane == 2) res->lastFlowIndicators[2] = (double)oldFRT / ((double)oldFN + 0.1);
+	if (lane == 3)
 	{
 		res->reserved = -1;
 		res->n_passes = n_passes; res->n_iterations = n_iter; res->n_evals = n_evals; res->trace_len = trace_len;
 		res->point_evals = point_evals;
-		for (int p = 0; p < n_passes; p++) res->lastResiduals[res->pass_level[p]] = res->pass_rmse[p];
-		res->lastFlowIndicators[0] = (double)oldFT / ((double)oldFN + 0.1); res->lastFlowIndicators[1] = 0;
-		res->lastFlowIndicators[2] = (double)oldFRT / ((double)oldFN + 0.1);
+	}
+	if (lane == 0)
+	{
 		res->aff_a = a_cur; res->aff_b = b_cur;
 		int ok = 1;
 		if ((modeA != 0 && (fabsf((float)a_cur) > 1.2f)) || (modeB != 0 && (fabsf((float)b_cur) > 200.f))) ok = 0;
@@ -1017,8 +1032,10 @@ __global__ void __launch_bounds__(NT, 1)
 track_persistent_kernel(TrackLevels TL, dso_b200_track_opts opt, const TrackIn* __restrict__ in,
                         dso_b200_track_result* out, int coarsestLvl, int smem_pts_cap, long long* phase_cycles,
                         dso_b200_track_result* host_out, unsigned int* host_flags, unsigned int seq,
-                        int NC, float* mc_part, unsigned int* mc_count)
+                        int NC, float* mc_part, unsigned int* mc_count, const __grid_constant__ TrackIn in0)
 {
+	// in == nullptr: the single hypothesis travels in the launch parameters (in0), which saves the kernel's PCIe read
+	// of the mapped input block.
 	// NC > 1: one hypothesis is spread over NC clusters (large clouds); every CTA of the grid must be resident
 	// (cooperative launch, see enqueue_track)
 	cg::cluster_group cluster = cg::this_cluster();
@@ -1031,6 +1048,7 @@ track_persistent_kernel(TrackLevels TL, dso_b200_track_opts opt, const TrackIn* 
 	long long tph[5] = { 0, 0, 0, 0, 0 };
 	long long tc0 = 0, tk0 = 0, tg0 = 0;
 	long long lmt[6] = { 0, 0, 0, 0, 0, 0 };   // LM step split: level, solve, exp+pose, params, sums->H, control
+	long long t_pro = 0, t_stage = 0, t_loop_end = 0, t_x[5] = { 0, 0, 0, 0, 0 };   // outside the evaluations: prologue, cloud staging, epilogue
 	if (PROF) { tk0 = clock64(); asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tg0)); }
 
 	__shared__ EvalParams sP;
@@ -1053,7 +1071,7 @@ track_persistent_kernel(TrackLevels TL, dso_b200_track_opts opt, const TrackIn* 
 		// the input block may live in mapped host memory: one coalesced read by 19 lanes; the pose entries stay in the
 		// lanes that read them
 		static_assert(sizeof(TrackIn) == 19 * sizeof(double), "TrackIn layout");
-		const double vin = (lane < 19) ? reinterpret_cast<const double*>(in + hyp)[lane] : 0.0;
+		const double vin = (lane < 19) ? (in ? reinterpret_cast<const double*>(in + hyp)[lane] : reinterpret_cast<const double*>(&in0)[lane]) : 0.0;
 		R.pe_cur = R.pe_new = vin;
 		if (lane < 12) s_lm.cur[lane] = vin;
 		if (lane < 8) s_lm.x[lane] = 0.0;
@@ -1069,10 +1087,51 @@ track_persistent_kernel(TrackLevels TL, dso_b200_track_opts opt, const TrackIn* 
 		aff_ref_to_new(TL, R.a_cur, R.b_cur, affA, affB);
 		lm_write_params(sP, TL, opt, lane, coarsestLvl, R.pe_cur, affA, affB, 1.f, true, true);
 		if (lane == 0) { sCtl[0] = coarsestLvl; sCtl[1] = 0; }
+		if (PROF) t_x[0] = clock64() - tk0;
 	}
 	if (tid == 0) { mbar_init(&xbar[0], 1); mbar_init(&xbar[1], 1); asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+	// this CTA's slice of the cloud of EVERY level goes into shared memory now, by the warps that have nothing to do with
+	// the LM set-up: one round of (possibly cold) memory latency for all levels instead of one per level change
+	int tot_slots = 0;
+#pragma unroll
+	for (int l = 0; l < 5; l++)
+		if (l <= coarsestLvl) tot_slots += (TL.pc_n[l] + CS * NC - 1) / (CS * NC);
+	const bool all_staged = tot_slots <= smem_pts_cap;
+	if (all_staged && NT > 32 && warp > 0)
+	{
+		const int NS = NT - 32, t = tid - 32;
+		for (int j0 = t; j0 < tot_slots; j0 += 4 * NS)
+		{
+			float4 v[4];
+			bool have[4];
+#pragma unroll
+			for (int q = 0; q < 4; q++)
+			{
+				const int j = j0 + q * NS;
+				have[q] = false;
+				int off = 0;
+#pragma unroll
+				for (int l = 0; l < 5; l++)
+					if (l <= coarsestLvl)
+					{
+						const int nl = TL.pc_n[l], per = (nl + CS * NC - 1) / (CS * NC);
+						const int b = min((int)(cidx * CS + rank) * per, nl), e = min(b + per, nl);
+						if (j >= off && j - off < e - b) { v[q] = __ldg(TL.pc[l] + b + (j - off)); have[q] = true; }
+						off += per;
+					}
+			}
+#pragma unroll
+			for (int q = 0; q < 4; q++)
+				if (have[q]) s_pts[j0 + q * NS] = v[q];
+		}
+	}
 	__syncthreads();
-	cluster.sync();            // every CTA's barriers exist before anybody signals them
+	if (PROF) t_x[1] = clock64() - tk0;
+	// every CTA's barriers must exist before anybody signals them: arrive here, wait in front of the first push, so the
+	// first evaluation hides the cluster's launch skew and the barrier's own latency
+	asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory");
+	bool peers_ready = false;
+	if (PROF) t_pro = clock64() - tk0;
 	int buf = 0;
 	unsigned xphase[2] = { 0u, 0u };
 	int staged_lvl = -1;
@@ -1083,12 +1142,22 @@ track_persistent_kernel(TrackLevels TL, dso_b200_track_opts opt, const TrackIn* 
 		const int per = (n + CS * NC - 1) / (CS * NC);
 		const int beg = min((int)(cidx * CS + rank) * per, n), end = min(beg + per, n);
 		const float4* __restrict__ gp = TL.pc[lvl];
-		const bool use_smem = (end - beg) <= smem_pts_cap;
-		if (use_smem && staged_lvl != lvl)
+		const bool use_smem = all_staged || (end - beg) <= smem_pts_cap;
+		int s_base = 0;
+		if (all_staged)
 		{
+#pragma unroll
+			for (int l = 0; l < 5; l++)
+				if (l < lvl) s_base += (TL.pc_n[l] + CS * NC - 1) / (CS * NC);
+		}
+		else if (use_smem && staged_lvl != lvl)
+		{
+			long long ts0 = 0;
+			if (PROF) ts0 = clock64();
 			for (int i = beg + tid; i < end; i += NT) s_pts[i - beg] = __ldg(gp + i);
 			staged_lvl = lvl;
 			__syncthreads();
+			if (PROF) t_stage += clock64() - ts0;
 		}
 		const EvalParams P = sP;
 		const float4* __restrict__ img = TL.img[lvl];
@@ -1099,7 +1168,7 @@ track_persistent_kernel(TrackLevels TL, dso_b200_track_opts opt, const TrackIn* 
 		for (int i = beg + tid; i < end; i += NT)      // one copy of the evaluation code (instruction footprint)
 		{
 			float4 pc;
-			if (use_smem) pc = s_pts[i - beg]; else pc = __ldg(gp + i);
+			if (use_smem) pc = s_pts[s_base + i - beg]; else pc = __ldg(gp + i);
 			eval_point<false>(pc, i, P, img, acc, nullptr, nullptr);
 		}
 		if (PROF) { __syncthreads(); long long t = clock64(); tph[0] += t - tc0; tc0 = t; }
@@ -1107,6 +1176,7 @@ track_persistent_kernel(TrackLevels TL, dso_b200_track_opts opt, const TrackIn* 
 		s_w[warp][2 * lane] = acc[0];
 		s_w[warp][2 * lane + 1] = acc[1];
 		__syncthreads();
+		if (!peers_ready) { asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory"); peers_ready = true; }
 		// CTA partial (warps in index order), pushed into every CTA of the cluster through DSMEM
 		if (tid < S_COUNT)
 		{
@@ -1153,28 +1223,41 @@ track_persistent_kernel(TrackLevels TL, dso_b200_track_opts opt, const TrackIn* 
 		if (sCtl[1]) break;
 		buf ^= 1;
 	}
-	cluster.sync();                // nobody leaves while a peer may still be writing into it
+	if (PROF) t_loop_end = clock64();
+	// nobody leaves while a peer may still be writing into it: arrive now, wait after the result has been written (the
+	// peers only wait for this CTA's arrival, and this CTA finds them all arrived when it gets there)
+	asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory");
 	if (rank == 0 && cidx == 0)
 	{
 		if (warp == 0)
 			lm_finalize(&s_res, s_passE, s_passN, lane, R.n_passes, R.n_iter, R.n_evals, R.trace_len, R.point_evals, R.pe_cur, R.a_cur, R.b_cur,
 			            R.oldFT, R.oldFRT, R.oldFN, opt.affineOptModeA, opt.affineOptModeB, TL.ref_exposure, TL.new_exposure, TL.ref_a, TL.ref_b);
 		__syncthreads();
-		const int nwords = sizeof(dso_b200_track_result) / 4;
-		const unsigned int* src = reinterpret_cast<const unsigned int*>(&s_res);
-		unsigned int* dst = reinterpret_cast<unsigned int*>(out + hyp);
-		for (int i = tid; i < nwords; i += NT) dst[i] = src[i];
-		if (host_out)
+		if (PROF) t_x[2] = clock64() - t_loop_end;
+		static_assert(sizeof(dso_b200_track_result) % 8 == 0, "result copied in 8-byte words");
+		const int nwords = sizeof(dso_b200_track_result) / 8;
+		const uint2* src = reinterpret_cast<const uint2*>(&s_res);
+		if (host_out && warp == 0)
 		{
-			// results straight into mapped host memory, then the per-hypothesis flag: the host polls it instead of waiting
-			// for a copy node and a stream synchronisation
-			unsigned int* hdst = reinterpret_cast<unsigned int*>(host_out + hyp);
-			for (int i = tid; i < nwords; i += NT) hdst[i] = src[i];
+			// results straight into mapped host memory by ONE warp, then the per-hypothesis flag: the host polls it instead
+			// of waiting for a copy node and a stream synchronisation.  One warp = one system-scope fence to wait for.
+			uint2* hdst = reinterpret_cast<uint2*>(host_out + hyp);
+			for (int i = lane; i < nwords; i += 32) hdst[i] = src[i];
+			if (PROF) t_x[3] = clock64() - t_loop_end;
 			__threadfence_system();
-			__syncthreads();
-			if (tid == 0) { *reinterpret_cast<volatile unsigned int*>(host_flags + hyp) = seq; __threadfence_system(); }
+			__syncwarp();
+			if (PROF) t_x[4] = clock64() - t_loop_end;
+			// no fence behind the flag: the end of the kernel publishes it at the latest, a fence would not make it earlier
+			if (lane == 0) *reinterpret_cast<volatile unsigned int*>(host_flags + hyp) = seq;
+		}
+		else if (!host_out || warp > 0)
+		{
+			const int t0 = host_out ? tid - 32 : tid, nthr = host_out ? NT - 32 : NT;
+			uint2* dst = reinterpret_cast<uint2*>(out + hyp);
+			for (int i = t0; i < nwords; i += nthr) dst[i] = src[i];
 		}
 	}
+	asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
 	if (PROF && blockIdx.x == 0 && tid == 0)
 	{
 		for (int k = 0; k < 5; k++) phase_cycles[k] = tph[k];
@@ -1182,6 +1265,8 @@ track_persistent_kernel(TrackLevels TL, dso_b200_track_opts opt, const TrackIn* 
 		phase_cycles[5] = clock64() - tk0;
 		phase_cycles[6] = tg1 - tg0;
 		for (int k = 0; k < 6; k++) phase_cycles[8 + k] = lmt[k];
+		for (int k = 0; k < 5; k++) phase_cycles[16 + k] = t_x[k];
+		phase_cycles[7] = t_pro; phase_cycles[14] = t_stage; phase_cycles[15] = clock64() - t_loop_end;
 	}
 }
 
@@ -1548,9 +1633,16 @@ static int enqueue_track(dso_b200_ctx* ctx, int trk, int frame_slot, int nHyp, c
 	while (cs > 1 && nHyp * cs > ctx->sm_count) cs >>= 1;
 	int max_n = 0;
 	for (int l = 0; l <= coarsestLvl; l++) max_n = T.pc_n[l] > max_n ? T.pc_n[l] : max_n;
-	int per = (max_n + cs - 1) / cs;
-	size_t smem_cap_bytes = 160 * 1024;
-	int cap = (int)std::min<size_t>((size_t)per, smem_cap_bytes / sizeof(float4));
+	const size_t smem_cap_bytes = 160 * 1024;
+	// shared-memory slots (cloud records) per CTA when the levels are split over `div` CTAs: the slices of all levels if
+	// they fit together (the kernel then stages them once, up front), else the largest level's slice
+	auto slots_for = [&](int div) -> int {
+		size_t all = 0;
+		for (int l = 0; l <= coarsestLvl; l++) all += (size_t)(T.pc_n[l] + div - 1) / div;
+		if (all * sizeof(float4) <= smem_cap_bytes) return (int)all;
+		return (int)std::min<size_t>((size_t)((max_n + div - 1) / div), smem_cap_bytes / sizeof(float4));
+	};
+	int cap = slots_for(cs);
 	size_t dyn = (size_t)cap * sizeof(float4);
 	// tuning knobs (dso_b200_track_set_tuning; the DSO_B200_TRACK_* environment variables give the defaults): threads per
 	// CTA and cluster size
@@ -1565,13 +1657,12 @@ static int enqueue_track(dso_b200_ctx* ctx, int trk, int frame_slot, int nHyp, c
 	int nt = want_threads ? want_threads : PERS_THREADS;
 	if (want_cluster) cs = want_cluster;
 	while (cs > 1 && nHyp * cs > ctx->sm_count) cs >>= 1;
-	per = (max_n + cs - 1) / cs;
-	cap = (int)std::min<size_t>((size_t)per, smem_cap_bytes / sizeof(float4));
+	cap = slots_for(cs);
 	dyn = (size_t)cap * sizeof(float4);
 	if (nt != 128) nt = 256;
 	const bool prof = ctx->d_phase_cycles != nullptr;
 	typedef void (*kern_t)(TrackLevels, dso_b200_track_opts, const TrackIn*, dso_b200_track_result*, int, int, long long*,
-	                       dso_b200_track_result*, unsigned int*, unsigned int, int, float*, unsigned int*);
+	                       dso_b200_track_result*, unsigned int*, unsigned int, int, float*, unsigned int*, TrackIn);
 	kern_t kern = nt == 128 ? (prof ? (kern_t)track_persistent_kernel<128, true> : (kern_t)track_persistent_kernel<128, false>)
 	                        : (prof ? (kern_t)track_persistent_kernel<256, true> : (kern_t)track_persistent_kernel<256, false>);
 	static bool attr_set[64][4] = { { false } };
@@ -1601,7 +1692,7 @@ static int enqueue_track(dso_b200_ctx* ctx, int trk, int frame_slot, int nHyp, c
 		// the per-CTA slice shrinks with nc, and so does the dynamic shared memory the query must assume
 		for (int it = 0; it < 4; it++)
 		{
-			q.dynamicSmemBytes = std::min<size_t>((size_t)((max_n + cs * nc - 1) / (cs * nc)), smem_cap_bytes / sizeof(float4)) * sizeof(float4);
+			q.dynamicSmemBytes = (size_t)slots_for(cs * nc) * sizeof(float4);
 			CK(cudaOccupancyMaxActiveClusters(&maxc, kern, &q));
 			if (maxc < 1) maxc = 1;
 			if (nc <= maxc) break;
@@ -1609,11 +1700,16 @@ static int enqueue_track(dso_b200_ctx* ctx, int trk, int frame_slot, int nHyp, c
 		}
 		if (nc > DSO_B200_TRACK_MAX_NC) nc = DSO_B200_TRACK_MAX_NC;
 		if (nc < 1) nc = 1;
-		per = (max_n + cs * nc - 1) / (cs * nc);
-		cap = (int)std::min<size_t>((size_t)per, smem_cap_bytes / sizeof(float4));
+		cap = slots_for(cs * nc);
 		dyn = (size_t)cap * sizeof(float4);
 		if (nc > 1) CK(cudaMemsetAsync(T.d_mc_count, 0, sizeof(unsigned int) * DSO_B200_MAX_HYP, T.stream));
 	}
+	// one hypothesis: its input block rides in the launch parameters (the ring block, host memory, stays the record the
+	// pose-less replay reads); the device-resident default block of a fresh slot is passed by pointer
+	const bool inline_in = nHyp == 1 && (const void*)kin != (const void*)T.d_track_in;
+	TrackIn in0;
+	memset(&in0, 0, sizeof(in0));
+	if (inline_in) in0 = kin[0];
 	cudaLaunchConfig_t cfg = {};
 	cfg.blockDim = dim3(nt, 1, 1);
 	cfg.stream = T.stream;
@@ -1630,17 +1726,16 @@ static int enqueue_track(dso_b200_ctx* ctx, int trk, int frame_slot, int nHyp, c
 		cfg.gridDim = dim3(nHyp * cs * nc, 1, 1);
 		cfg.dynamicSmemBytes = dyn;
 		cfg.numAttrs = nc > 1 ? 2 : 1;
-		cudaError_t le = cudaLaunchKernelEx(&cfg, kern, TL, o, kin, (dso_b200_track_result*)T.d_track_out, coarsestLvl, cap, (long long*)ctx->d_phase_cycles,
+		cudaError_t le = cudaLaunchKernelEx(&cfg, kern, TL, o, inline_in ? (const TrackIn*)nullptr : kin, (dso_b200_track_result*)T.d_track_out, coarsestLvl, cap, (long long*)ctx->d_phase_cycles,
 		                                    seq ? (dso_b200_track_result*)T.h_track_out + (size_t)(seq % TRACK_IN_RING) * DSO_B200_MAX_HYP : (dso_b200_track_result*)nullptr,
 		                                    T.h_flags + (size_t)(seq % TRACK_IN_RING) * DSO_B200_MAX_HYP, seq,
-		                                    nc, T.d_mc_part, T.d_mc_count);
+		                                    nc, T.d_mc_part, T.d_mc_count, in0);
 		if (le == cudaSuccess) break;
 		if (nc > 1 && attempt == 0)
 		{
 			(void)cudaGetLastError();
 			nc = 1;
-			per = (max_n + cs - 1) / cs;
-			cap = (int)std::min<size_t>((size_t)per, smem_cap_bytes / sizeof(float4));
+			cap = slots_for(cs);
 			dyn = (size_t)cap * sizeof(float4);
 			continue;
 		}
@@ -1679,12 +1774,12 @@ extern "C" int dso_b200_track_phase_cycles(dso_b200_ctx* ctx, int enable, long l
 {
 	ARG_CHECK(ctx, "null context");
 	CK(cudaSetDevice(ctx->device));
-	if (enable && !ctx->d_phase_cycles) { CK(cudaMalloc(&ctx->d_phase_cycles, 128)); CK(cudaMemset(ctx->d_phase_cycles, 0, 128)); }
+	if (enable && !ctx->d_phase_cycles) { CK(cudaMalloc(&ctx->d_phase_cycles, 192)); CK(cudaMemset(ctx->d_phase_cycles, 0, 192)); }
 	if (cycles7 && ctx->d_phase_cycles)
 	{
 		CK(cudaStreamSynchronize(ctx->trk[0].stream));
 		CK(cudaStreamSynchronize(ctx->trk[1].stream));
-		CK(cudaMemcpy(cycles7, ctx->d_phase_cycles, 112, cudaMemcpyDeviceToHost));
+		CK(cudaMemcpy(cycles7, ctx->d_phase_cycles, 192, cudaMemcpyDeviceToHost));
 	}
 	if (!enable && ctx->d_phase_cycles) { cudaFree(ctx->d_phase_cycles); ctx->d_phase_cycles = nullptr; }
 	return 0;
