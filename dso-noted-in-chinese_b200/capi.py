@@ -384,7 +384,7 @@ class Context:
         return list(res)
 
     def phase_cycles(self, enable=True, read=False):
-        out = np.zeros(24, dtype=np.int64)
+        out = np.zeros(120, dtype=np.int64)
         self._check(self.L.dso_b200_track_phase_cycles(self.h, int(enable), out.ctypes.data if read else None))
         return out
 

@@ -1125,6 +1125,20 @@ track_persistent_kernel(TrackLevels TL, dso_b200_track_opts opt, const TrackIn* 
 				if (have[q]) s_pts[j0 + q * NS] = v[q];
 		}
 	}
+	// the new frame's pyramid may be cold (it has just come from the host, or other work has gone through the L2 since
+	// makeImages wrote it): ask for it now, coarsest level first, behind the cloud loads above.  Fire and forget; the
+	// levels are walked minutes (in GPU terms) later.  Only the levels this call uses.
+	// (cp.async.bulk.prefetch.L2 in 16 KB pieces was tried instead: same first-evaluation times, kernel 3 us longer)
+	if (warp > 0)
+	{
+		const int G = (int)(CS * NC) * (NT - 32), g = (int)(cidx * CS + rank) * (NT - 32) + (tid - 32);
+		for (int l = coarsestLvl; l >= 0; l--)
+		{
+			const char* base = reinterpret_cast<const char*>(TL.img[l]);
+			const int lines = (TL.w[l] * TL.h[l] * (int)sizeof(float4) + 127) >> 7;
+			for (int i = g; i < lines; i += G) asm volatile("prefetch.global.L2 [%0];" :: "l"(base + ((size_t)i << 7)));
+		}
+	}
 	__syncthreads();
 	if (PROF) t_x[1] = clock64() - tk0;
 	// every CTA's barriers must exist before anybody signals them: arrive here, wait in front of the first push, so the
@@ -1171,7 +1185,7 @@ track_persistent_kernel(TrackLevels TL, dso_b200_track_opts opt, const TrackIn* 
 			if (use_smem) pc = s_pts[s_base + i - beg]; else pc = __ldg(gp + i);
 			eval_point<false>(pc, i, P, img, acc, nullptr, nullptr);
 		}
-		if (PROF) { __syncthreads(); long long t = clock64(); tph[0] += t - tc0; tc0 = t; }
+		if (PROF) { __syncthreads(); long long t = clock64(); tph[0] += t - tc0; if (tid == 0 && blockIdx.x == 0 && tph[4] < 24) phase_cycles[24 + 4 * tph[4]] = t - tc0; tc0 = t; }
 		warp_reduce_halving(acc, lane);
 		s_w[warp][2 * lane] = acc[0];
 		s_w[warp][2 * lane + 1] = acc[1];
@@ -1186,7 +1200,7 @@ track_persistent_kernel(TrackLevels TL, dso_b200_track_opts opt, const TrackIn* 
 			for (unsigned r = 0; r < CS; r++) st_async_remote(&xchg[buf][rank][tid], &xbar[buf], r, s);
 		}
 		if (tid == 0) mbar_arrive_expect_tx(&xbar[buf], CS * S_COUNT * 4);   // this CTA expects CS partials of S_COUNT floats
-		if (PROF) { long long t = clock64(); tph[1] += t - tc0; tc0 = t; }
+		if (PROF) { long long t = clock64(); tph[1] += t - tc0; if (tid == 0 && blockIdx.x == 0 && tph[4] < 24) phase_cycles[25 + 4 * tph[4]] = t - tc0; tc0 = t; }
 		// only the LM warp needs the totals: the first 52 threads (two warps) add the ranks in index order and hand them
 		// over through a two-warp named barrier; everybody else goes straight to the barrier at the end of the iteration
 		if (warp < 2)
@@ -1214,9 +1228,9 @@ track_persistent_kernel(TrackLevels TL, dso_b200_track_opts opt, const TrackIn* 
 				s_tot[lane] = g.x; s_tot[32 + lane] = g.y;
 				__syncwarp();
 			}
-			if (PROF) { long long t = clock64(); tph[2] += t - tc0; tc0 = t; }
+			if (PROF) { long long t = clock64(); tph[2] += t - tc0; if (tid == 0 && blockIdx.x == 0 && tph[4] < 24) phase_cycles[26 + 4 * tph[4]] = t - tc0; tc0 = t; }
 			lm_step_warp(R, K, s_lm, s_tot, TL, opt, &s_res, s_passE, s_passN, sP, sCtl, n, lane, PROF ? lmt : nullptr);
-			if (PROF) { long long t = clock64(); tph[3] += t - tc0; tph[4]++; }
+			if (PROF) { long long t = clock64(); tph[3] += t - tc0; if (tid == 0 && blockIdx.x == 0 && tph[4] < 24) phase_cycles[27 + 4 * tph[4]] = t - tc0; tph[4]++; }
 		}
 		xphase[buf] ^= 1u;
 		__syncthreads();           // the next EvalParams / level / done flag are in shared memory
@@ -1774,12 +1788,12 @@ extern "C" int dso_b200_track_phase_cycles(dso_b200_ctx* ctx, int enable, long l
 {
 	ARG_CHECK(ctx, "null context");
 	CK(cudaSetDevice(ctx->device));
-	if (enable && !ctx->d_phase_cycles) { CK(cudaMalloc(&ctx->d_phase_cycles, 192)); CK(cudaMemset(ctx->d_phase_cycles, 0, 192)); }
+	if (enable && !ctx->d_phase_cycles) { CK(cudaMalloc(&ctx->d_phase_cycles, 960)); CK(cudaMemset(ctx->d_phase_cycles, 0, 960)); }
 	if (cycles7 && ctx->d_phase_cycles)
 	{
 		CK(cudaStreamSynchronize(ctx->trk[0].stream));
 		CK(cudaStreamSynchronize(ctx->trk[1].stream));
-		CK(cudaMemcpy(cycles7, ctx->d_phase_cycles, 192, cudaMemcpyDeviceToHost));
+		CK(cudaMemcpy(cycles7, ctx->d_phase_cycles, 960, cudaMemcpyDeviceToHost));
 	}
 	if (!enable && ctx->d_phase_cycles) { cudaFree(ctx->d_phase_cycles); ctx->d_phase_cycles = nullptr; }
 	return 0;

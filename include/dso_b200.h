@@ -242,7 +242,7 @@ int dso_b200_track_frame(dso_b200_ctx* ctx, int trk, int frame_slot, const float
 /* Profiling aid (no counterpart in the reference): with enable != 0 the persistent kernel records, for
  * thread 0 of CTA 0 of the last launch, the SM cycles spent in [point evaluation, CTA reduction, cluster
  * exchange + barrier, LM step], the number of evaluations, and the whole kernel in SM cycles and in ns;
- * cycles7 (24 values, may be NULL; [7] prologue, [14] cloud staging, [15] epilogue cycles, [16..20] their split) receives them; [8..11] split the LM step into sums+control, solve,
+ * cycles7 (120 values, may be NULL; [24+4e..27+4e] the four phases of evaluation e < 24; [7] prologue, [14] cloud staging, [15] epilogue cycles, [16..20] their split) receives them; [8..11] split the LM step into sums+control, solve,
  * exponential+pose update, parameter build. */
 int dso_b200_track_phase_cycles(dso_b200_ctx* ctx, int enable, long long* cycles7);
 /* Launch shape of the persistent tracker (no counterpart in the reference; tests and tuning): threads per CTA (128, 256),

@@ -28,6 +28,9 @@ for k in range(6):
           "| outside the evaluations: prologue %d staging %d epilogue %d other %d" % (c[7], c[14], c[15], c[5] - c[:4].sum() - c[7] - c[14] - c[15]),
           "| prologue: LM set-up %d, +staging/syncthreads %d, +cluster.sync %d | epilogue: finalize %d, +result stores %d, +system fence %d, end %d" %
           (c[16], c[17], c[7], c[18], c[19], c[20], c[15]))
+    if "--per-eval" in sys.argv:
+        for e in range(min(int(n), 24)):
+            print("    eval %2d: eval %5d reduce %5d xchg %5d lm %5d" % ((e,) + tuple(c[24 + 4 * e:28 + 4 * e])))
 hy = np.stack([wl["inits"][2]] * 31)
 ctx.track_batched(0, 3, hy, *wl["affs"][2], levels - 1)
 c = ctx.phase_cycles(True, read=True)
