@@ -550,11 +550,34 @@ __global__ void __launch_bounds__(128) ba_accum_top_kernel(const int* __restrict
 // TopRight argument order of updateTopRight (AccumulatedTopHessian.cpp:134-139): TR00=JabJIdx(0,0), TR10=JabJIdx(0,1),
 // TR01=JabJIdx(1,0), TR11=JabJIdx(1,1), TR02=JI_r[0], TR12=JI_r[1]  -> sw[3..8] above is already in (k0,k1) pairs.
 
-// per-point sums in EFPoint::residualsAll order, AccumulatedTopHessian.cpp:142-160
+// AccumulatedSCHessianSSE::addPoint (AccumulatedSCHessian.cpp:35-60) for one point without marginalisation mask: inverse
+// Hessian and b from the AF and LF sums (shiftPriorToZero = true, EnergyFunctional.cpp:263, 271)
+struct SchurPrepOut { float* HdiF; float* bdSumF; float* idh; float* HcdSum; const float* priorF; const float* deltaF; };
+__device__ __forceinline__ void schur_prep_point(int p, const int* __restrict__ res_begin, const unsigned char* __restrict__ isAct,
+                                                 float HddA, float bdA, const float* hcA, float HddL, float bdL, const float* hcL,
+                                                 const SchurPrepOut& o)
+{
+#pragma unroll
+	for (int k = 0; k < 4; k++) o.HcdSum[4 * p + k] = fadd(hcA[k], hcL[k]);   // Hcd_accAF + Hcd_accLF (:62)
+	int ngood = 0;
+	for (int r = res_begin[p]; r < res_begin[p + 1]; r++) ngood += isAct[r] ? 1 : 0;
+	if (ngood == 0) { o.HdiF[p] = 0.f; o.bdSumF[p] = 0.f; o.idh[p] = 0.f; return; }
+	float H = fadd(fadd(HddA, HddL), o.priorF[p]);   // Hdd_accAF + Hdd_accLF + priorF
+	if (H < 1e-10) H = 1e-10;
+	o.idh[p] = H;
+	o.HdiF[p] = (float)(1.0 / (double)H);
+	o.bdSumF[p] = fadd(fadd(bdA, bdL), fmul(o.priorF[p], o.deltaF[p]));
+}
+
+// per-point sums in EFPoint::residualsAll order, AccumulatedTopHessian.cpp:142-160.  prep (modes 0 and 1, no mask): the
+// Schur preparation of the same point follows in the same thread (saves a launch on the critical path); the sums of the
+// other mode are read from where its own pass left them.
 __global__ void ba_point_sums_kernel(int nP, const int* __restrict__ res_begin, const unsigned char* __restrict__ isAct,
                                      const unsigned char* __restrict__ isLin, const float* __restrict__ contrib,
                                      float* Hdd, float* bd, float* Hcd, int mode, const unsigned char* __restrict__ pmask,
-                                     float* Hdd_A, float* bd_A, float* Hcd_A)
+                                     float* Hdd_A, float* bd_A, float* Hcd_A,
+                                     bool prep = false, const float* Hdd_L = nullptr, const float* bd_L = nullptr, const float* Hcd_L = nullptr,
+                                     SchurPrepOut po = SchurPrepOut())
 {
 	const int p = blockIdx.x * blockDim.x + threadIdx.x;
 	if (p >= nP) return;
@@ -587,6 +610,16 @@ __global__ void ba_point_sums_kernel(int nP, const int* __restrict__ res_begin, 
 		Hdd_A[p] = 0.f; bd_A[p] = 0.f;
 		Hcd_A[4 * p] = 0.f; Hcd_A[4 * p + 1] = 0.f; Hcd_A[4 * p + 2] = 0.f; Hcd_A[4 * p + 3] = 0.f;
 	}
+	if (prep)
+	{
+		const float own[4] = { h0, h1, h2, h3 };
+		float oth[4];
+		const float* src = mode == 0 ? Hcd_L : Hcd_A;
+#pragma unroll
+		for (int k = 0; k < 4; k++) oth[k] = src[4 * p + k];
+		if (mode == 0) schur_prep_point(p, res_begin, isAct, Hdd_acc, bd_acc, own, Hdd_L[p], bd_L[p], oth, po);
+		else schur_prep_point(p, res_begin, isAct, Hdd_A[p], bd_A[p], oth, Hdd_acc, bd_acc, own, po);
+	}
 }
 
 // index of entry (i,j) of the symmetric 13x13 block in the 91-vector written by ba_accum_top_kernel
@@ -605,15 +638,11 @@ __device__ __forceinline__ int top_index(int i, int j)
 #define ORDERED_SUM_MAXF(v, n, k, EXPR) do { double t_[MAXF]; _Pragma("unroll") for (int k = 0; k < MAXF; k++) t_[k] = (k < (n)) ? (EXPR) : 0.0; \
 	_Pragma("unroll") for (int k = 0; k < MAXF; k++) if (k < (n)) v += t_[k]; } while (0)
 
-// sum of the per-chunk partials of every group (pair or host) in chunk order, FP64: one thread per entry
-__global__ void ba_reduce_partials_kernel(const float* __restrict__ partials, int stride, int nEntries,
-                                          const int* __restrict__ group_begin, double* out)
+// sum of the per-chunk partials of one entry over the chunks [cb, c1) in chunk order, FP64
+__device__ __forceinline__ double ordered_chunk_sum(const float* __restrict__ partials, int stride, int e, int cb, int c1)
 {
-	const int e = blockIdx.x * blockDim.x + threadIdx.x, g = blockIdx.y;
-	if (e >= nEntries) return;
 	double s = 0.0;
-	const int c1 = group_begin[g + 1];
-	for (int c0 = group_begin[g]; c0 < c1; c0 += 8)              // eight loads in flight, adds in chunk order
+	for (int c0 = cb; c0 < c1; c0 += 8)                          // eight loads in flight, adds in chunk order
 	{
 		float t[8];
 #pragma unroll
@@ -621,7 +650,35 @@ __global__ void ba_reduce_partials_kernel(const float* __restrict__ partials, in
 #pragma unroll
 		for (int u = 0; u < 8; u++) if (c0 + u < c1) s += (double)t[u];
 	}
-	out[(size_t)g * nEntries + e] = s;
+	return s;
+}
+
+// two entries at once (either may be -1): one loop, sixteen loads in flight, the same additions per entry as above
+__device__ __forceinline__ void ordered_chunk_sum2(const float* __restrict__ partials, int stride, int eA, int eB, int cb, int c1,
+                                                   double& sA, double& sB)
+{
+	sA = 0.0; sB = 0.0;
+	for (int c0 = cb; c0 < c1; c0 += 8)
+	{
+		float ta[8], tb[8];
+#pragma unroll
+		for (int u = 0; u < 8; u++)
+		{
+			ta[u] = (eA >= 0 && c0 + u < c1) ? partials[(size_t)(c0 + u) * stride + eA] : 0.f;
+			tb[u] = (eB >= 0 && c0 + u < c1) ? partials[(size_t)(c0 + u) * stride + eB] : 0.f;
+		}
+#pragma unroll
+		for (int u = 0; u < 8; u++) if (c0 + u < c1) { sA += (double)ta[u]; sB += (double)tb[u]; }
+	}
+}
+
+// the same for every group (pair or host): one thread per entry
+__global__ void ba_reduce_partials_kernel(const float* __restrict__ partials, int stride, int nEntries,
+                                          const int* __restrict__ group_begin, double* out)
+{
+	const int e = blockIdx.x * blockDim.x + threadIdx.x, g = blockIdx.y;
+	if (e >= nEntries) return;
+	out[(size_t)g * nEntries + e] = ordered_chunk_sum(partials, stride, e, group_begin[g], group_begin[g + 1]);
 }
 
 // contribution layout per (host,target) pair: [HH 64][TT 64][HT 64][CH 32][CT 32][BH 8][BT 8][CC 16][BC 4]
@@ -911,7 +968,11 @@ __device__ __forceinline__ void mm8(const double* A, const double* Bm, double* C
 
 // stage 1 of stitchDoubleInternal (AccumulatedSCHessian.cpp:86-165) for the pair (i = host, j = target):
 // every adjoint sandwich that involves accD[i,j,*], accE[i,j], accEB[i,j], written out as separate contributions.
-__global__ void __launch_bounds__(64 * MAXF) ba_schur_stage1_kernel(int nF, const double* __restrict__ scRed, int nRed,
+// The chunk partials of host i (accD[i,j,*], accE[i,j], accEB[i,j]) are summed here, in chunk order, by the threads that
+// use them -- each entry has exactly one consumer -- and the pairs (i, 0) also sum accHcc / accbc of their host into scRed
+// for the gather kernel: no separate reduction launch on the critical path.
+__global__ void __launch_bounds__(64 * MAXF) ba_schur_stage1_kernel(int nF, const float* __restrict__ partials, int scN,
+                                                                    const int* __restrict__ host_pc_begin, double* scRed, int nRed,
                                                                     const double* __restrict__ adHost, const double* __restrict__ adTarget,
                                                                     double* contrib)
 {
@@ -921,16 +982,28 @@ __global__ void __launch_bounds__(64 * MAXF) ba_schur_stage1_kernel(int nF, cons
 	const int i = blockIdx.x % nF, j = blockIdx.x / nF, o = threadIdx.x & 63, k = threadIdx.x >> 6;
 	const int ij = i + nF * j;
 	const int nD = nF * nF * 64, nE = nF * 32;
-	const double* red = scRed + (size_t)i * nRed;      // chunk partials of host i, already summed
+	const int cb = host_pc_begin[i], ce = host_pc_begin[i + 1];      // chunks of host i
 	double* out = contrib + (size_t)ij * SCC_STRIDE;
 	const bool act = k < nF;
 	if (k == 0) { AHij[o] = adHost[(size_t)ij * 64 + o]; ATij[o] = adTarget[(size_t)ij * 64 + o]; }
-	if (k == 1 && o < 32) E[o] = red[nD + j * 32 + o];
-	if (k == 1 && o >= 32 && o < 40) EB[o - 32] = red[nD + nE + j * 8 + o - 32];
+	// one pass over the chunks per thread: its accD entry and, for slice k = 1, one of accE / accEB / accHcc+accbc (no
+	// divergent second and third pass)
+	int eB = -1;
+	if (k == 1)
+	{
+		if (o < 32) eB = nD + j * 32 + o;
+		else if (o < 40) eB = nD + nE + j * 8 + (o - 32);
+		else if (o < 60 && j == 0) eB = nD + nE + nF * 8 + (o - 40);
+	}
+	double sA, sB;
+	ordered_chunk_sum2(partials, scN, act ? (j * nF + k) * 64 + o : -1, eB, cb, ce, sA, sB);
+	if (k == 1 && o < 32) E[o] = sB;
+	if (k == 1 && o >= 32 && o < 40) EB[o - 32] = sB;
+	if (k == 1 && o >= 40 && o < 60 && j == 0) scRed[(size_t)i * nRed + nD + nE + nF * 8 + (o - 40)] = sB;
 	if (act)
 	{
 		const int ik = i + nF * k;
-		Dk[k][o] = red[(j * nF + k) * 64 + o];
+		Dk[k][o] = sA;
 		AHk[k][o] = adHost[(size_t)ik * 64 + o]; ATk[k][o] = adTarget[(size_t)ik * 64 + o];
 	}
 	__syncthreads();
@@ -1458,7 +1531,7 @@ int ba_enqueue_apply(dso_b200_ctx* ctx)
 }
 
 // mode 0: accumulateAF_MT -> d_HA, d_bA, per-point AF sums; mode 1: accumulateLF_MT -> d_HL, d_bL (+ priors), per-point LF sums
-int ba_enqueue_top(dso_b200_ctx* ctx, int mode, const unsigned char* d_pmask, bool fork)
+int ba_enqueue_top(dso_b200_ctx* ctx, int mode, const unsigned char* d_pmask, bool fork, bool prep)
 {
 	BAWorkspace* W = ctx->ba;
 	const int nF = W->P.nF;
@@ -1477,7 +1550,11 @@ int ba_enqueue_top(dso_b200_ctx* ctx, int mode, const unsigned char* d_pmask, bo
 	else
 		ba_accum_top_kernel<1><<<W->nChunks, 128, 0, st>>>(W->d_perm, W->d_chunk_start, W->d_chunk_cnt, W->d_isAct, W->d_isLin, W->d_efsel,
 		                                                 W->d_J[0], W->d_J[1], W->d_contrib, W->d_topPartials, W->d_chunk_nres, LA);
-	ba_point_sums_kernel<<<(W->P.nP + 127) / 128, 128, 0, st>>>(W->P.nP, W->d_res_begin, W->d_isAct, W->d_isLin, W->d_contrib, Hdd, bd, Hcd, mode, d_pmask, W->d_Hdd, W->d_bd, W->d_Hcd);
+	SchurPrepOut po;
+	po.HdiF = W->d_HdiF; po.bdSumF = W->d_bdSumF; po.idh = W->d_idh; po.HcdSum = W->d_HcdSum; po.priorF = W->d_priorF; po.deltaF = W->d_deltaF;
+	if (prep && (mode == 2 || d_pmask)) { dso_set_error("ba_enqueue_top: the fused Schur preparation has no marginalisation form"); return DSO_B200_E_ARG; }
+	ba_point_sums_kernel<<<(W->P.nP + 127) / 128, 128, 0, st>>>(W->P.nP, W->d_res_begin, W->d_isAct, W->d_isLin, W->d_contrib, Hdd, bd, Hcd, mode, d_pmask, W->d_Hdd, W->d_bd, W->d_Hcd,
+	                                                            prep, W->d_Hdd_L, W->d_bd_L, W->d_Hcd_L, po);
 	if (fork) { int rc = ba_fork(ctx); if (rc) return rc; st = W->side_stream; }       // the stitch: independent of what follows on the main stream
 	ba_reduce_partials_kernel<<<dim3(1, nF * nF), NTOP_PAD, 0, st>>>(W->d_topPartials, NTOP_PAD, NTOP_PAD, W->d_pair_chunk_begin, W->d_topRed);
 	ba_top_pair_kernel<<<nF * nF, 256, 0, st>>>(nF, W->d_topRed, W->d_adHost, W->d_adTarget, W->d_topContrib);
@@ -1489,21 +1566,22 @@ int ba_enqueue_top(dso_b200_ctx* ctx, int mode, const unsigned char* d_pmask, bo
 	return 0;
 }
 
-int ba_enqueue_schur(dso_b200_ctx* ctx, const unsigned char* d_pmask)
+int ba_enqueue_schur(dso_b200_ctx* ctx, const unsigned char* d_pmask, bool prep_done)
 {
 	BAWorkspace* W = ctx->ba;
 	const int nF = W->P.nF, nP = W->P.nP;
 	float* HdiF = d_pmask ? W->d_HdiF_m : W->d_HdiF; float* bdSumF = d_pmask ? W->d_bdSumF_m : W->d_bdSumF;
-	ba_schur_prep_kernel<<<(nP + 127) / 128, 128, 0, ctx->ba_stream>>>(nP, W->d_res_begin, W->d_isAct, W->d_Hdd, W->d_bd, W->d_Hcd,
-	                                                              W->d_Hdd_L, W->d_bd_L, W->d_Hcd_L, W->d_priorF, W->d_deltaF,
-	                                                              HdiF, bdSumF, W->d_idh, W->d_HcdSum, d_pmask);
+	if (!prep_done)
+		ba_schur_prep_kernel<<<(nP + 127) / 128, 128, 0, ctx->ba_stream>>>(nP, W->d_res_begin, W->d_isAct, W->d_Hdd, W->d_bd, W->d_Hcd,
+		                                                              W->d_Hdd_L, W->d_bd_L, W->d_Hcd_L, W->d_priorF, W->d_deltaF,
+		                                                              HdiF, bdSumF, W->d_idh, W->d_HcdSum, d_pmask);
 	ba_schur_accum_kernel<<<W->nPC, 256, 0, ctx->ba_stream>>>(nF, W->d_pc_start, W->d_pc_cnt, W->d_res_begin, W->d_rtarget, W->d_isAct, W->d_JpJdF,
 	                                                     HdiF, bdSumF, W->d_HcdSum, W->d_scPartials, W->scN);
 	const int nRed = nF * nF * 64 + nF * 32 + nF * 8 + 20;          // accD, accE, accEB, accHcc + accbc per host
-	ba_reduce_partials_kernel<<<dim3((nRed + 255) / 256, nF), 256, 0, ctx->ba_stream>>>(W->d_scPartials, W->scN, nRed, W->d_host_pc_begin, W->d_scRed);
-	ba_schur_stage1_kernel<<<nF * nF, 64 * MAXF, 0, ctx->ba_stream>>>(nF, W->d_scRed, nRed, W->d_adHost, W->d_adTarget, W->d_scContrib);
+	ba_schur_stage1_kernel<<<nF * nF, 64 * MAXF, 0, ctx->ba_stream>>>(nF, W->d_scPartials, W->scN, W->d_host_pc_begin, W->d_scRed, nRed,
+	                                                               W->d_adHost, W->d_adTarget, W->d_scContrib);
 	ba_schur_gather_kernel<<<nF * nF + nF + 1, 64, 0, ctx->ba_stream>>>(nF, W->d_scRed, W->d_scContrib, W->d_HS, W->d_bS);
-	LAUNCHED(ctx, 5);
+	LAUNCHED(ctx, prep_done ? 3 : 4);
 	CK(cudaGetLastError());
 	return 0;
 }
@@ -1684,8 +1762,8 @@ extern "C" int dso_b200_ba_step(dso_b200_ctx* ctx, double* H_A, double* b_A, dou
 	rc = ba_run_graphed(ctx, W->g_step, BAGraphKey{ 0.0, 0.f, 0, 0, 0, 0 }, [&]() -> int {
 		int r;
 		if ((r = ba_enqueue_linearize(ctx, true, true))) return r;        // linearize + applyRes in one kernel
-		if ((r = ba_enqueue_top(ctx, 0, nullptr, true))) return r;
-		if ((r = ba_enqueue_schur(ctx))) return r;
+		if ((r = ba_enqueue_top(ctx, 0, nullptr, true, true))) return r;      // + the Schur preparation per point
+		if ((r = ba_enqueue_schur(ctx, nullptr, true))) return r;
 		if ((r = ba_join_side(ctx))) return r;
 		CK(cudaMemcpyAsync(W->h_out, W->d_outblk, BA_OUT_DOUBLES * sizeof(double), cudaMemcpyDeviceToHost, s));
 		return 0;

@@ -148,8 +148,8 @@ int ba_check_ready(dso_b200_ctx* ctx, const char* fn);
 int ba_enqueue_linearize(dso_b200_ctx* ctx, bool fork = false, bool apply = false);
 int ba_join_side(dso_b200_ctx* ctx);
 int ba_enqueue_apply(dso_b200_ctx* ctx);
-int ba_enqueue_top(dso_b200_ctx* ctx, int mode, const unsigned char* d_pmask = nullptr, bool fork = false);
-int ba_enqueue_schur(dso_b200_ctx* ctx, const unsigned char* d_pmask = nullptr);
+int ba_enqueue_top(dso_b200_ctx* ctx, int mode, const unsigned char* d_pmask = nullptr, bool fork = false, bool prep = false);
+int ba_enqueue_schur(dso_b200_ctx* ctx, const unsigned char* d_pmask = nullptr, bool prep_done = false);
 void ba_solve_destroy(BAWorkspace* W);
 
 #define BA_CHECK(cond, msg) do { if (!(cond)) { dso_set_error("%s: %s", __func__, msg); return DSO_B200_E_STATE; } } while (0)

@@ -73,7 +73,8 @@ static int ensure_point_buffers(dso_b200_ctx* ctx, BASolve* S)
 		const size_t n = (size_t)W->P.nP;
 		CK(cudaMalloc(&S->d_step, n * sizeof(float)));
 		CK(cudaMalloc(&S->d_idepth_backup, n * sizeof(float)));
-		CK(cudaMalloc(&S->d_stepBlocks, ((n + 255) / 256) * 2 * sizeof(double)));
+		CK(cudaMalloc(&S->d_stepBlocks, (((n + 255) / 256) * 2 + 1) * sizeof(double)));     // + the fused kernel's block counter
+		CK(cudaMemset(S->d_stepBlocks, 0, (((n + 255) / 256) * 2 + 1) * sizeof(double)));
 		CK(cudaMemset(S->d_step, 0, n * sizeof(float)));
 		S->capP = W->P.nP;
 	}
@@ -161,7 +162,7 @@ struct SolveArgs
 __global__ void __launch_bounds__(SOLVE_NT) ba_solve_kernel(SolveArgs a)
 {
 	__shared__ double A[NMAX * LDH];
-	__shared__ double sv[NMAX], rhs[NMAX], yv[NMAX], xv[NMAX], dg[NMAX], Lk[NMAX], dl[NMAX];
+	__shared__ double sv[NMAX], rhs[NMAX], yv[NMAX], xv[NMAX], dg[NMAX], dl[NMAX];
 	__shared__ int ord[NMAX];
 	const int tid = threadIdx.x, N = 8 * a.nF + CPARS;
 #define STAMP(i) do { if (a.dbg && tid == 0) a.dbg[i] = clock64(); } while (0)
@@ -462,16 +463,14 @@ __global__ void __launch_bounds__(SOLVE_NT) ba_solve_kernel(SolveArgs a)
 }
 
 // resubstituteFPt, EnergyFunctional.cpp:304-330
-__global__ void ba_resubstitute_kernel(int nP, int nF, const int* __restrict__ res_begin, const int* __restrict__ rtarget,
-                                       const int* __restrict__ phost, const unsigned char* __restrict__ isAct,
-                                       const float* __restrict__ JpJdF, const float* __restrict__ HcdSum, const float* __restrict__ bdSumF,
-                                       const float* __restrict__ HdiF, const double* __restrict__ x, const float* __restrict__ xAd, float* step)
+__device__ __forceinline__ float resubstitute_point(int p, int nF, const int* __restrict__ res_begin, const int* __restrict__ rtarget,
+                                                    const int* __restrict__ phost, const unsigned char* __restrict__ isAct,
+                                                    const float* __restrict__ JpJdF, const float* __restrict__ HcdSum, const float* __restrict__ bdSumF,
+                                                    const float* __restrict__ HdiF, const double* __restrict__ x, const float* __restrict__ xAd)
 {
-	const int p = blockIdx.x * blockDim.x + threadIdx.x;
-	if (p >= nP) return;
 	int ngood = 0;
 	for (int r = res_begin[p]; r < res_begin[p + 1]; r++) ngood += isAct[r] ? 1 : 0;
-	if (ngood == 0) { step[p] = 0.f; return; }
+	if (ngood == 0) return 0.f;
 	float b = bdSumF[p];
 	const float* hc = HcdSum + 4 * (size_t)p;
 	const float x0 = (float)x[0], x1 = (float)x[1], x2 = (float)x[2], x3 = (float)x[3];
@@ -499,7 +498,15 @@ __global__ void ba_resubstitute_kernel(int nP, int nF, const int* __restrict__ r
 #pragma unroll
 		for (int u = 0; u < 4; u++) if (use[u]) b = fsub(b, d[u]);
 	}
-	step[p] = fmul(-b, HdiF[p]);
+	return fmul(-b, HdiF[p]);
+}
+__global__ void ba_resubstitute_kernel(int nP, int nF, const int* __restrict__ res_begin, const int* __restrict__ rtarget,
+                                       const int* __restrict__ phost, const unsigned char* __restrict__ isAct,
+                                       const float* __restrict__ JpJdF, const float* __restrict__ HcdSum, const float* __restrict__ bdSumF,
+                                       const float* __restrict__ HdiF, const double* __restrict__ x, const float* __restrict__ xAd, float* step)
+{
+	const int p = blockIdx.x * blockDim.x + threadIdx.x;
+	if (p < nP) step[p] = resubstitute_point(p, nF, res_begin, rtarget, phost, isAct, JpJdF, HcdSum, bdSumF, HdiF, x, xAd);
 }
 
 // per-point half of FullSystem::doStepFromBackup (FullSystemOptimize.cpp:272-286): idepth = idepth_backup + stepfacD * step,
@@ -552,6 +559,66 @@ __global__ void ba_points_backup_kernel(int nP, const float4* __restrict__ pt, f
 	if (p >= nP) return;
 	if (!restore) backup[p] = pt[p].z;                      // FullSystem::backupState: ph->idepth_backup = ph->idepth
 	else { float4 q = pt_rw[p]; q.z = backup[p]; q.w = backup[p]; pt_rw[p] = q; deltaF[p] = 0.f; }   // loadSateBackup
+}
+
+// resubstituteFPt + backupState + the point half of doStepFromBackup + the two step sums in ONE launch (the Gauss-Newton
+// iteration's tail; each piece computes exactly what its stand-alone kernel above computes).  The last block to finish adds
+// the block sums in index order, as ba_points_step_final_kernel does, and re-arms the counter for the next launch.
+__global__ void __launch_bounds__(256) ba_resub_step_kernel(int nP, int nF, const int* __restrict__ res_begin, const int* __restrict__ rtarget,
+                                                            const int* __restrict__ phost, const unsigned char* __restrict__ isAct,
+                                                            const float* __restrict__ JpJdF, const float* __restrict__ HcdSum,
+                                                            const float* __restrict__ bdSumF, const float* __restrict__ HdiF,
+                                                            const double* __restrict__ x, const float* __restrict__ xAd, float* step,
+                                                            float stepfacD, float* backup, float4* pt, float* deltaF, double* blocks,
+                                                            unsigned int* counter, double* out)
+{
+	__shared__ double s0[256], s1[256];
+	__shared__ bool last;
+	const int p = blockIdx.x * 256 + threadIdx.x;
+	double a = 0.0, b = 0.0;
+	if (p < nP)
+	{
+		const float st = resubstitute_point(p, nF, res_begin, rtarget, phost, isAct, JpJdF, HcdSum, bdSumF, HdiF, x, xAd);
+		step[p] = st;
+		float4 q = pt[p];
+		const float bk = q.z;                                   // backupState: idepth_backup = idepth
+		backup[p] = bk;
+		const float v = fadd(bk, fmul(stepfacD, st));
+		q.z = v; q.w = v;
+		pt[p] = q;
+		deltaF[p] = 0.f;
+		a = (double)fmul(st, st); b = (double)fabsf(bk);
+	}
+	s0[threadIdx.x] = a; s1[threadIdx.x] = b;
+	__syncthreads();
+	for (int o = 128; o > 0; o >>= 1)
+	{
+		if (threadIdx.x < o) { s0[threadIdx.x] += s0[threadIdx.x + o]; s1[threadIdx.x] += s1[threadIdx.x + o]; }
+		__syncthreads();
+	}
+	if (threadIdx.x == 0)
+	{
+		blocks[2 * blockIdx.x] = s0[0]; blocks[2 * blockIdx.x + 1] = s1[0];
+		__threadfence();
+		last = atomicAdd(counter, 1u) == gridDim.x - 1;
+	}
+	__syncthreads();
+	if (last && threadIdx.x == 0)
+	{
+		__threadfence();
+		const int nb = gridDim.x;
+		double sa = 0, sb = 0;
+		for (int i0 = 0; i0 < nb; i0 += 8)
+		{
+			double ta[8], tb[8];
+#pragma unroll
+			for (int u = 0; u < 8; u++) { ta[u] = (i0 + u < nb) ? __ldcg(blocks + 2 * (i0 + u)) : 0.0; tb[u] = (i0 + u < nb) ? __ldcg(blocks + 2 * (i0 + u) + 1) : 0.0; }
+#pragma unroll
+			for (int u = 0; u < 8; u++) if (i0 + u < nb) { sa += ta[u]; sb += tb[u]; }
+		}
+		out[0] = sa; out[1] = sb;
+		*counter = 0u;
+	}
 }
 
 // =========================================================================================================
@@ -738,7 +805,7 @@ extern "C" int dso_b200_ba_accumulate_L(dso_b200_ctx* ctx, double* H, double* b,
 
 // EnergyFunctional::solveSystemF (EnergyFunctional.cpp:802-924): accumulateAF_MT, accumulateLF_MT, accumulateSCF_MT, the
 // solve and resubstituteF_MT, all enqueued on the context stream; one synchronisation at the end.
-static int enqueue_solve(dso_b200_ctx* ctx, BASolve* S, int iteration, double lambda, int solverMode, bool debug)
+static int enqueue_solve(dso_b200_ctx* ctx, BASolve* S, int iteration, double lambda, int solverMode, bool debug, bool withStep = false, float stepfacD = 0.f)
 {
 	BAWorkspace* W = ctx->ba;
 	int rc;
@@ -747,9 +814,10 @@ static int enqueue_solve(dso_b200_ctx* ctx, BASolve* S, int iteration, double la
 	// the stitch of the last top accumulation runs beside the Schur chain (the two top modes share their stitch buffers, so
 	// only the last one may be forked)
 	const bool haveL = W->nLin != 0;
-	if ((rc = ba_enqueue_top(ctx, 0, nullptr, !haveL))) return rc;  // :816
-	if (haveL && (rc = ba_enqueue_top(ctx, 1, nullptr, true))) return rc;   // :817 (without linearised residuals H_L, b_L are the priors alone)
-	if ((rc = ba_enqueue_schur(ctx))) return rc;                    // :820
+	// the last top accumulation also prepares the Schur step per point (one launch less on the critical path)
+	if ((rc = ba_enqueue_top(ctx, 0, nullptr, !haveL, !haveL))) return rc;  // :816
+	if (haveL && (rc = ba_enqueue_top(ctx, 1, nullptr, true, true))) return rc;   // :817 (without linearised residuals H_L, b_L are the priors alone)
+	if ((rc = ba_enqueue_schur(ctx, nullptr, true))) return rc;     // :820
 	if ((rc = ba_join_side(ctx))) return rc;
 	if ((rc = ensure_point_buffers(ctx, S))) return rc;
 	SolveArgs a;
@@ -762,8 +830,17 @@ static int enqueue_solve(dso_b200_ctx* ctx, BASolve* S, int iteration, double la
 	a.dbg = S->d_dbg;
 	if (S->d_dbg) CK(cudaMemsetAsync(S->d_dbg, 0, 16 * sizeof(long long), ctx->ba_stream));
 	ba_solve_kernel<<<1, SOLVE_NT, 0, ctx->ba_stream>>>(a);
-	ba_resubstitute_kernel<<<(W->P.nP + 127) / 128, 128, 0, ctx->ba_stream>>>(W->P.nP, W->P.nF, W->d_res_begin, W->d_rtarget, W->d_phost, W->d_isAct,
-	                                                                    W->d_JpJdF, W->d_HcdSum, W->d_bdSumF, W->d_HdiF, S->d_x, S->d_xAd, S->d_step);
+	if (withStep)
+	{
+		const int nb = (W->P.nP + 255) / 256;
+		ba_resub_step_kernel<<<nb, 256, 0, ctx->ba_stream>>>(W->P.nP, W->P.nF, W->d_res_begin, W->d_rtarget, W->d_phost, W->d_isAct,
+		                                                     W->d_JpJdF, W->d_HcdSum, W->d_bdSumF, W->d_HdiF, S->d_x, S->d_xAd, S->d_step,
+		                                                     stepfacD, S->d_idepth_backup, W->d_pt, W->d_deltaF, S->d_stepBlocks,
+		                                                     reinterpret_cast<unsigned int*>(S->d_stepBlocks + 2 * nb), W->d_scalars + 4);
+	}
+	else
+		ba_resubstitute_kernel<<<(W->P.nP + 127) / 128, 128, 0, ctx->ba_stream>>>(W->P.nP, W->P.nF, W->d_res_begin, W->d_rtarget, W->d_phost, W->d_isAct,
+		                                                                    W->d_JpJdF, W->d_HcdSum, W->d_bdSumF, W->d_HdiF, S->d_x, S->d_xAd, S->d_step);
 	LAUNCHED(ctx, 2);
 	CK(cudaGetLastError());
 	return 0;
@@ -814,19 +891,15 @@ extern "C" int dso_b200_ba_iteration(dso_b200_ctx* ctx, int iteration, double la
 	if ((rc = solve_state(ctx, &S))) return rc;
 	if ((rc = ensure_point_buffers(ctx, S))) return rc;
 	cudaStream_t s = ctx->ba_stream;
-	const int nP = W->P.nP, nb = (nP + 255) / 256, N = 8 * W->P.nF + CPARS;
+	const int N = 8 * W->P.nF + CPARS;
 	// by-value kernel arguments of the captured sequence: orthogonalisation on/off, lambda, stepfacD, solver mode, L path
 	const int orth = ((solverMode & SOLVER_ORTHOGONALIZE_X) || (iteration >= 2 && (solverMode & SOLVER_ORTHOGONALIZE_X_LATER))) ? 1 : 0;
 	const BAGraphKey key = { lambda, stepfacD, solverMode, W->nLin != 0 ? 1 : 0, S->haveP ? 1 : 0, S->d_dbg ? 1 : 0 };
 	rc = ba_run_graphed(ctx, W->g_iter[orth], key, [&]() -> int {
 		int r;
 		if ((r = ba_enqueue_linearize(ctx, true, true))) return r;        // linearize + applyRes in one kernel
-		if ((r = enqueue_solve(ctx, S, orth ? 2 : 0, lambda, solverMode, false))) return r;
-		ba_points_backup_kernel<<<(nP + 255) / 256, 256, 0, s>>>(nP, W->d_pt, S->d_idepth_backup, 0, nullptr, nullptr);
-		ba_points_step_kernel<<<nb, 256, 0, s>>>(nP, stepfacD, S->d_step, S->d_idepth_backup, W->d_pt, W->d_deltaF, S->d_stepBlocks);
-		ba_points_step_final_kernel<<<1, 32, 0, s>>>(nb, S->d_stepBlocks, W->d_scalars + 4);
-		LAUNCHED(ctx, 3);
-		CK(cudaGetLastError());
+		// solve, then resubstitute + backup + point step + step sums in one launch
+		if ((r = enqueue_solve(ctx, S, orth ? 2 : 0, lambda, solverMode, false, true, stepfacD))) return r;
 		CK(cudaMemcpyAsync(S->h_x, S->d_x, N * sizeof(double), cudaMemcpyDeviceToHost, s));
 		CK(cudaMemcpyAsync(S->h_x + NMAX, W->d_scalars, 6 * sizeof(double), cudaMemcpyDeviceToHost, s));
 		return 0;
