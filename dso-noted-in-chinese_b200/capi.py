@@ -86,6 +86,8 @@ SIGNATURES = {
     "dso_b200_track_batched_async": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, f64p, C.c_double, C.c_double, C.c_float, C.c_int,
                                                C.POINTER(TrackOpts)]),
     "dso_b200_track_fetch": (C.c_int, [vp, C.c_int, C.c_int, C.POINTER(TrackResult)]),
+    "dso_b200_track_and_prefetch": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, vp, C.c_double, C.c_double, C.c_float, C.c_int, vp,
+                                              C.c_int, vp, C.c_int, C.c_int, C.c_int, vp]),
     "dso_b200_track_frame": (C.c_int, [vp, C.c_int, C.c_int, vp, C.c_int, C.c_int, C.c_int, C.c_int, f64p, C.c_double, C.c_double,
                                        C.c_float, C.c_int, C.POINTER(TrackOpts), C.POINTER(TrackResult)]),
     "dso_b200_track_phase_cycles": (C.c_int, [vp, C.c_int, vp]),
@@ -366,6 +368,16 @@ class Context:
         poses12 = np.ascontiguousarray(poses12, dtype=np.float64).reshape(-1, 12)
         self._check(self.L.dso_b200_track_batched_async(self.h, trk, slot, poses12.shape[0], poses12.reshape(-1), a, b,
                                                         new_exposure, coarsest, None if opts is None else C.byref(opts)))
+
+    def track_and_prefetch(self, trk, slot, pose12, a, b, coarsest, next_slot, next_color_ptr, w, h, levels, out=None,
+                           new_exposure=1.0):
+        """one hypothesis; pose12: contiguous float64 array of 12 kept alive by the caller for the call; out: a TrackResult
+        to fill (re-used by a caller that tracks in a loop)"""
+        if out is None:
+            out = TrackResult()
+        self._check(self.L.dso_b200_track_and_prefetch(self.h, trk, slot, 1, pose12.ctypes.data, a, b, new_exposure, coarsest, None,
+                                                       next_slot, next_color_ptr, w, h, levels, C.addressof(out)))
+        return out
 
     def track_fetch(self, trk, n=1):
         res = (TrackResult * n)()

@@ -1843,6 +1843,24 @@ extern "C" int dso_b200_track_batched(dso_b200_ctx* ctx, int trk, int frame_slot
 	return dso_b200_track_fetch(ctx, trk, nHyp, out);
 }
 
+// The pipelined front end in one call: track the (already built) frame_slot, enqueue the upload + pyramid of the NEXT
+// image into next_slot on the mapping stream while the tracker runs, then wait for the tracking result.
+extern "C" int dso_b200_track_and_prefetch(dso_b200_ctx* ctx, int trk, int frame_slot, int nHyp, const double* pose12_init,
+                                           double aff_a_init, double aff_b_init, float new_ab_exposure, int coarsestLvl,
+                                           const dso_b200_track_opts* opts, int next_slot, const float* next_color_host,
+                                           int w, int h, int levels, dso_b200_track_result* out)
+{
+	ARG_CHECK(pose12_init && out, "null argument");
+	int rc = enqueue_track(ctx, trk, frame_slot, nHyp, pose12_init, aff_a_init, aff_b_init, new_ab_exposure, coarsestLvl, opts);
+	if (rc) return rc;
+	if (next_slot >= 0 && next_color_host)
+	{
+		rc = dso_b200_make_images_async(ctx, next_slot, next_color_host, w, h, levels);
+		if (rc) return rc;                      // the tracking call stays in flight: dso_b200_track_fetch still returns it
+	}
+	return dso_b200_track_fetch(ctx, trk, nHyp, out);
+}
+
 extern "C" int dso_b200_track_frame(dso_b200_ctx* ctx, int trk, int frame_slot, const float* color_host, int w, int h,
                                     int levels, int nHyp, const double* pose12_init, double aff_a_init, double aff_b_init,
                                     float new_ab_exposure, int coarsestLvl, const dso_b200_track_opts* opts,

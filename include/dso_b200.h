@@ -232,6 +232,15 @@ int dso_b200_track_batched_async(dso_b200_ctx* ctx, int trk, int frame_slot, int
                                  double aff_a_init, double aff_b_init, float new_ab_exposure, int coarsestLvl,
                                  const dso_b200_track_opts* opts);
 int dso_b200_track_fetch(dso_b200_ctx* ctx, int trk, int nHyp, dso_b200_track_result* out);
+/* The pipelined per-frame call of a live front end (FullSystem::addActiveFrame, FullSystem.cpp:860 + :905, with the next
+ * image's makeImages taken off the critical path): dso_b200_track_batched_async on frame_slot (whose pyramid a previous
+ * call built), dso_b200_make_images_async of the NEXT image into next_slot (skipped when next_slot < 0 or the pointer is
+ * NULL; next_color_host must stay valid until that slot is consumed), then dso_b200_track_fetch.  Same results and errors
+ * as the three calls; if the prefetch is refused, its error is returned and the tracking result stays fetchable. */
+int dso_b200_track_and_prefetch(dso_b200_ctx* ctx, int trk, int frame_slot, int nHyp, const double* pose12_init,
+                                double aff_a_init, double aff_b_init, float new_ab_exposure, int coarsestLvl,
+                                const dso_b200_track_opts* opts, int next_slot, const float* next_color_host,
+                                int w, int h, int levels, dso_b200_track_result* out);
 /* One frame end to end -- what FullSystem::addActiveFrame does per frame (FullSystem.cpp:860 makeImages,
  * :905 trackNewCoarse -> :387 trackNewestCoarse): upload of the image from host memory, pyramid into
  * frame_slot, nHyp hypotheses, download of the results; one synchronisation at the end. */

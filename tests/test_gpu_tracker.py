@@ -261,3 +261,23 @@ def test_track_fixed_affine_modes(ctx_vga, scen_vga, oracle, modes):
         if modes[1] < 0:
             assert rg.aff_b == 0 == ro.aff_b
         _compare_track(syn, ro, rg, scen_vga.levels)
+
+
+@pytest.mark.gpu
+def test_track_and_prefetch_equals_the_three_calls(ctx_vga, scen_vga):
+    """dso_b200_track_and_prefetch = track_batched_async + make_images_async(next image) + track_fetch: same tracking
+    result, and the prefetched slot tracks exactly like the slot built by dso_b200_make_images from the same image."""
+    syn = scen_vga.syn
+    pose = np.ascontiguousarray(syn.pose12(scen_vga.frames[0][1]), dtype=np.float64).reshape(-1)
+    lv = scen_vga.levels
+    ref = ctx_vga.track_batched(0, 2, pose, scen_vga.a0, scen_vga.b0, lv - 1)[0]
+    nxt = np.ascontiguousarray(scen_vga.frames[2][0], dtype=np.float32)
+    got = ctx_vga.track_and_prefetch(0, 2, pose, scen_vga.a0, scen_vga.b0, lv - 1, 5, nxt.ctypes.data, 640, 480, lv)
+    assert got.ok == ref.ok and got.n_evals == ref.n_evals and list(got.pose) == list(ref.pose)
+    assert list(got.trace[:got.trace_len]) == list(ref.trace[:ref.trace_len])
+    a = ctx_vga.track_batched(0, 3, pose, scen_vga.a0, scen_vga.b0, lv - 1)[0]       # slot 3: frame 2 through make_images
+    b = ctx_vga.track_batched(0, 5, pose, scen_vga.a0, scen_vga.b0, lv - 1)[0]       # slot 5: the same image, prefetched
+    assert list(a.pose) == list(b.pose) and a.n_evals == b.n_evals
+    # no next image: plain tracking
+    got2 = ctx_vga.track_and_prefetch(0, 2, pose, scen_vga.a0, scen_vga.b0, lv - 1, -1, None, 640, 480, lv)
+    assert list(got2.pose) == list(ref.pose)
