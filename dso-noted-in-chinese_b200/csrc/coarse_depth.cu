@@ -5,7 +5,7 @@
 // point -> thread assignment is the one the uploaded-cloud path gets).
 //
 //   cd_hits / cd_splat / cd_splat_serial  :141-158   one thread per point, float atomics where at most two points share a
-//                                  pixel (exact: addition commutes), the rest added in point order by one thread
+//                                  pixel (exact: addition commutes), the rest added in point order, one thread per pixel
 //   cd_down_kernel      :161-186   ((a + b) + c) + d per output pixel, level by level
 //   cd_dilate_kernel    :190-242   diagonal neighbours on levels 0-1, 4-neighbours above; reads only pixels that had a
 //                                  weight before the pass, writes only pixels that had none: no ordering hazard
@@ -67,7 +67,7 @@ __global__ void cd_splat_kernel(int n, const float* __restrict__ cu, const float
 }
 
 // the (rare) pixels with three or more points: chunks of 1024 points, flagged ones compacted in point order, then added
-// one after the other by a single thread
+// per pixel in that order, one thread per pixel
 __global__ void __launch_bounds__(1024) cd_splat_serial_kernel(int n, const float* __restrict__ cu, const float* __restrict__ cv,
                                                                const float* __restrict__ cid, const float* __restrict__ hdi, int w, int h,
                                                                const int* __restrict__ hits, float* idepth, float* wsum)
@@ -88,12 +88,21 @@ __global__ void __launch_bounds__(1024) cd_splat_serial_kernel(int n, const floa
 		for (int q = 0; q < 32; q++) { const int c = s_warp[q]; if (q < warp) pre += c; tot += c; }
 		if (f) { const int pos = pre + __popc(m & ((1u << lane) - 1u)); s_pix[pos] = pix; s_idw[pos] = idw; s_w[pos] = weight; }
 		__syncthreads();
-		if (tid == 0)
-			for (int q = 0; q < tot; q++)
+		// different pixels are independent; the entries of one pixel are added in point order by the thread that holds the
+		// first of them (the compacted list is in point order)
+		if (tid < tot)
+		{
+			const int p = s_pix[tid];
+			bool first = true;
+			for (int q = 0; q < tid; q++) if (s_pix[q] == p) { first = false; break; }
+			if (first)
 			{
-				idepth[s_pix[q]] = fadd(idepth[s_pix[q]], s_idw[q]);
-				wsum[s_pix[q]] = fadd(wsum[s_pix[q]], s_w[q]);
+				float a = idepth[p], b = wsum[p];
+				for (int q = tid; q < tot; q++)
+					if (s_pix[q] == p) { a = fadd(a, s_idw[q]); b = fadd(b, s_w[q]); }
+				idepth[p] = a; wsum[p] = b;
 			}
+		}
 		__syncthreads();
 	}
 }

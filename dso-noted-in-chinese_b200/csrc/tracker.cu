@@ -1673,14 +1673,15 @@ static int enqueue_track(dso_b200_ctx* ctx, int trk, int frame_slot, int nHyp, c
 	while (cs > 1 && nHyp * cs > ctx->sm_count) cs >>= 1;
 	cap = slots_for(cs);
 	dyn = (size_t)cap * sizeof(float4);
-	if (nt != 128) nt = 256;
+	if (nt != 128 && nt != 384) nt = 256;
 	const bool prof = ctx->d_phase_cycles != nullptr;
 	typedef void (*kern_t)(TrackLevels, dso_b200_track_opts, const TrackIn*, dso_b200_track_result*, int, int, long long*,
 	                       dso_b200_track_result*, unsigned int*, unsigned int, int, float*, unsigned int*, TrackIn);
 	kern_t kern = nt == 128 ? (prof ? (kern_t)track_persistent_kernel<128, true> : (kern_t)track_persistent_kernel<128, false>)
+	            : nt == 384 ? (prof ? (kern_t)track_persistent_kernel<384, true> : (kern_t)track_persistent_kernel<384, false>)
 	                        : (prof ? (kern_t)track_persistent_kernel<256, true> : (kern_t)track_persistent_kernel<256, false>);
-	static bool attr_set[64][4] = { { false } };
-	const int ki = (nt == 128 ? 0 : 2) + (prof ? 1 : 0);
+	static bool attr_set[64][6] = { { false } };
+	const int ki = (nt == 128 ? 0 : (nt == 384 ? 4 : 2)) + (prof ? 1 : 0);
 	if (!attr_set[ctx->device & 63][ki])
 	{
 		CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_cap_bytes));

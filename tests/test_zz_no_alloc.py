@@ -68,6 +68,13 @@ def test_noalloc_matches_context_path_twice(pkg, oracle, window_small):
         assert rel_err_matrix(H, Href).max() <= 1e-4
         scale = np.sqrt(np.abs(np.diag(Href)) * max(ref6[0] / ref6[1], 1e-12)) + 1e-30
         assert (np.abs(bb - bref) / scale).max() <= 1e-4
+        # and directly against the oracle (CoarseTracker::calcRes / calcGSSSE): same term count, H and b within 1e-4
+        scen.oracle_set_frame(0)
+        ro = scen.trk.calc_res(lvl, pose, a, b, cutoff)
+        Ho, bo = scen.trk.calc_gs(lvl, a, b)
+        assert v6[1] == ro[1] and v6[5] == ro[5] or (np.isnan(v6[5]) and np.isnan(ro[5]))
+        assert rel_err_matrix(H, Ho).max() <= 1e-4
+        assert (np.abs(bb - bo) / scale).max() <= 1e-4
     ctx.close()
 
 
