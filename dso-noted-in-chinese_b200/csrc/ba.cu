@@ -638,38 +638,47 @@ __device__ __forceinline__ int top_index(int i, int j)
 #define ORDERED_SUM_MAXF(v, n, k, EXPR) do { double t_[MAXF]; _Pragma("unroll") for (int k = 0; k < MAXF; k++) t_[k] = (k < (n)) ? (EXPR) : 0.0; \
 	_Pragma("unroll") for (int k = 0; k < MAXF; k++) if (k < (n)) v += t_[k]; } while (0)
 
-// sum of the per-chunk partials of one entry over the chunks [cb, c1) in chunk order, FP64
+// sum of the per-chunk partials of one entry over the chunks [cb, c1) in chunk order, FP64.  The loop is a chain of
+// memory round trips (large windows have hundreds of chunks per group), so 32 loads are in flight per round.
+#define CHUNK_SUM_U 32
 __device__ __forceinline__ double ordered_chunk_sum(const float* __restrict__ partials, int stride, int e, int cb, int c1)
 {
 	double s = 0.0;
-	for (int c0 = cb; c0 < c1; c0 += 8)                          // eight loads in flight, adds in chunk order
+	for (int c0 = cb; c0 < c1; c0 += CHUNK_SUM_U)                // adds in chunk order
 	{
-		float t[8];
+		float t[CHUNK_SUM_U];
 #pragma unroll
-		for (int u = 0; u < 8; u++) t[u] = (c0 + u < c1) ? partials[(size_t)(c0 + u) * stride + e] : 0.f;
+		for (int u = 0; u < CHUNK_SUM_U; u++) t[u] = partials[(size_t)min(c0 + u, c1 - 1) * stride + e];   // clamped, not predicated:
+		// predicated loads would be batched by the number of predicate registers (7), not by CHUNK_SUM_U
+		asm volatile("" ::: "memory");                             // every load of the round is issued before the first add
 #pragma unroll
-		for (int u = 0; u < 8; u++) if (c0 + u < c1) s += (double)t[u];
+		for (int u = 0; u < CHUNK_SUM_U; u++) if (c0 + u < c1) s += (double)t[u];
 	}
 	return s;
 }
 
-// two entries at once (either may be -1): one loop, sixteen loads in flight, the same additions per entry as above
+// two entries at once (either may be -1): one loop, the same additions per entry as above
 __device__ __forceinline__ void ordered_chunk_sum2(const float* __restrict__ partials, int stride, int eA, int eB, int cb, int c1,
                                                    double& sA, double& sB)
 {
 	sA = 0.0; sB = 0.0;
-	for (int c0 = cb; c0 < c1; c0 += 8)
+	const bool hasB = __any_sync(0xffffffffu, eB >= 0);          // warp-uniform: only slice k = 1 has second entries
+	for (int c0 = cb; c0 < c1; c0 += CHUNK_SUM_U)
 	{
-		float ta[8], tb[8];
+		float ta[CHUNK_SUM_U], tb[CHUNK_SUM_U];
 #pragma unroll
-		for (int u = 0; u < 8; u++)
+		for (int u = 0; u < CHUNK_SUM_U; u++)
 		{
-			ta[u] = (eA >= 0 && c0 + u < c1) ? partials[(size_t)(c0 + u) * stride + eA] : 0.f;
-			tb[u] = (eB >= 0 && c0 + u < c1) ? partials[(size_t)(c0 + u) * stride + eB] : 0.f;
+			const size_t row = (size_t)min(c0 + u, c1 - 1) * stride;
+			ta[u] = partials[row + max(eA, 0)];
+			tb[u] = hasB ? partials[row + max(eB, 0)] : 0.f;
 		}
+		asm volatile("" ::: "memory");
 #pragma unroll
-		for (int u = 0; u < 8; u++) if (c0 + u < c1) { sA += (double)ta[u]; sB += (double)tb[u]; }
+		for (int u = 0; u < CHUNK_SUM_U; u++) if (c0 + u < c1) { sA += (double)ta[u]; sB += (double)tb[u]; }
 	}
+	if (eA < 0) sA = 0.0;
+	if (eB < 0) sB = 0.0;
 }
 
 // the same for every group (pair or host): one thread per entry
@@ -995,11 +1004,19 @@ __global__ void __launch_bounds__(64 * MAXF) ba_schur_stage1_kernel(int nF, cons
 		else if (o < 40) eB = nD + nE + j * 8 + (o - 32);
 		else if (o < 60 && j == 0) eB = nD + nE + nF * 8 + (o - 40);
 	}
-	double sA, sB;
-	ordered_chunk_sum2(partials, scN, act ? (j * nF + k) * 64 + o : -1, eB, cb, ce, sA, sB);
+	double sA = 0.0, sB = 0.0;
+	const int eA = act ? (j * nF + k) * 64 + o : -1;
+	if (partials) ordered_chunk_sum2(partials, scN, eA, eB, cb, ce, sA, sB);
+	else
+	{
+		// large windows (hundreds of chunks per host): ba_reduce_partials_kernel has summed them with far more threads
+		const double* red = scRed + (size_t)i * nRed;
+		if (eA >= 0) sA = red[eA];
+		if (eB >= 0) sB = red[eB];
+	}
 	if (k == 1 && o < 32) E[o] = sB;
 	if (k == 1 && o >= 32 && o < 40) EB[o - 32] = sB;
-	if (k == 1 && o >= 40 && o < 60 && j == 0) scRed[(size_t)i * nRed + nD + nE + nF * 8 + (o - 40)] = sB;
+	if (partials && k == 1 && o >= 40 && o < 60 && j == 0) scRed[(size_t)i * nRed + nD + nE + nF * 8 + (o - 40)] = sB;
 	if (act)
 	{
 		const int ik = i + nF * k;
@@ -1578,10 +1595,15 @@ int ba_enqueue_schur(dso_b200_ctx* ctx, const unsigned char* d_pmask, bool prep_
 	ba_schur_accum_kernel<<<W->nPC, 256, 0, ctx->ba_stream>>>(nF, W->d_pc_start, W->d_pc_cnt, W->d_res_begin, W->d_rtarget, W->d_isAct, W->d_JpJdF,
 	                                                     HdiF, bdSumF, W->d_HcdSum, W->d_scPartials, W->scN);
 	const int nRed = nF * nF * 64 + nF * 32 + nF * 8 + 20;          // accD, accE, accEB, accHcc + accbc per host
-	ba_schur_stage1_kernel<<<nF * nF, 64 * MAXF, 0, ctx->ba_stream>>>(nF, W->d_scPartials, W->scN, W->d_host_pc_begin, W->d_scRed, nRed,
+	// few chunks per host (a VGA window has ~18): stage 1 sums them itself, one launch less on the critical path; many
+	// chunks: the reduction runs as its own, much wider launch (stage 1 has only nF^2 blocks)
+	const bool fused_reduce = W->nPC <= 48 * nF;
+	if (!fused_reduce)
+		ba_reduce_partials_kernel<<<dim3((nRed + 255) / 256, nF), 256, 0, ctx->ba_stream>>>(W->d_scPartials, W->scN, nRed, W->d_host_pc_begin, W->d_scRed);
+	ba_schur_stage1_kernel<<<nF * nF, 64 * MAXF, 0, ctx->ba_stream>>>(nF, fused_reduce ? W->d_scPartials : nullptr, W->scN, W->d_host_pc_begin, W->d_scRed, nRed,
 	                                                               W->d_adHost, W->d_adTarget, W->d_scContrib);
 	ba_schur_gather_kernel<<<nF * nF + nF + 1, 64, 0, ctx->ba_stream>>>(nF, W->d_scRed, W->d_scContrib, W->d_HS, W->d_bS);
-	LAUNCHED(ctx, prep_done ? 3 : 4);
+	LAUNCHED(ctx, (prep_done ? 3 : 4) + (fused_reduce ? 0 : 1));
 	CK(cudaGetLastError());
 	return 0;
 }

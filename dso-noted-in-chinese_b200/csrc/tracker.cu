@@ -1135,7 +1135,9 @@ track_persistent_kernel(TrackLevels TL, dso_b200_track_opts opt, const TrackIn* 
 		for (int l = coarsestLvl; l >= 0; l--)
 		{
 			const char* base = reinterpret_cast<const char*>(TL.img[l]);
-			const int lines = (TL.w[l] * TL.h[l] * (int)sizeof(float4) + 127) >> 7;
+			const int bytes = TL.w[l] * TL.h[l] * (int)sizeof(float4);
+			if (bytes > (8 << 20)) continue;                      // a large level is sampled sparsely: fetching all of it would cost more than it saves
+			const int lines = (bytes + 127) >> 7;
 			for (int i = g; i < lines; i += G) asm volatile("prefetch.global.L2 [%0];" :: "l"(base + ((size_t)i << 7)));
 		}
 	}
