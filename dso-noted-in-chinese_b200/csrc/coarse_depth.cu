@@ -75,6 +75,7 @@ __global__ void __launch_bounds__(1024) cd_splat_serial_kernel(int n, const floa
 	__shared__ int s_pix[1024];
 	__shared__ float s_idw[1024], s_w[1024];
 	__shared__ int s_warp[32];
+	__shared__ unsigned long long s_key[1024];
 	const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 	for (int base = 0; base < n; base += 1024)
 	{
@@ -88,18 +89,37 @@ __global__ void __launch_bounds__(1024) cd_splat_serial_kernel(int n, const floa
 		for (int q = 0; q < 32; q++) { const int c = s_warp[q]; if (q < warp) pre += c; tot += c; }
 		if (f) { const int pos = pre + __popc(m & ((1u << lane) - 1u)); s_pix[pos] = pix; s_idw[pos] = idw; s_w[pos] = weight; }
 		__syncthreads();
-		// different pixels are independent; the entries of one pixel are added in point order by the thread that holds the
-		// first of them (the compacted list is in point order)
+		// different pixels are independent; the entries of one pixel must be added in point order.  Sort (pixel, position
+		// in the compacted list) -- a bitonic network over the next power of two, in shared memory -- so that the entries of
+		// a pixel sit next to each other in point order; the thread holding the first entry of a run adds the whole run.
+		int P2 = 1;
+		while (P2 < tot) P2 <<= 1;
+		if (tid < P2) s_key[tid] = tid < tot ? (((unsigned long long)s_pix[tid] << 10) | (unsigned long long)tid) : ~0ull;
+		__syncthreads();
+		for (int kk = 2; kk <= P2; kk <<= 1)
+			for (int j = kk >> 1; j > 0; j >>= 1)
+			{
+				const int partner = tid ^ j;
+				if (tid < P2 && partner > tid)
+				{
+					const unsigned long long x = s_key[tid], y = s_key[partner];
+					const bool up = (tid & kk) == 0;
+					if ((x > y) == up) { s_key[tid] = y; s_key[partner] = x; }
+				}
+				__syncthreads();
+			}
 		if (tid < tot)
 		{
-			const int p = s_pix[tid];
-			bool first = true;
-			for (int q = 0; q < tid; q++) if (s_pix[q] == p) { first = false; break; }
-			if (first)
+			const unsigned long long me = s_key[tid];
+			const int p = (int)(me >> 10);
+			if (tid == 0 || (int)(s_key[tid - 1] >> 10) != p)
 			{
 				float a = idepth[p], b = wsum[p];
-				for (int q = tid; q < tot; q++)
-					if (s_pix[q] == p) { a = fadd(a, s_idw[q]); b = fadd(b, s_w[q]); }
+				for (int q = tid; q < tot && (int)(s_key[q] >> 10) == p; q++)
+				{
+					const int pos = (int)(s_key[q] & 1023ull);
+					a = fadd(a, s_idw[pos]); b = fadd(b, s_w[pos]);
+				}
 				idepth[p] = a; wsum[p] = b;
 			}
 		}
