@@ -637,7 +637,7 @@ def run_ours(args):
         ctx.track_fetch(0, 1)
     # one nvidia-smi poller for the whole job (rank 0 watches every GPU of the run): a poller per rank multiplies the
     # driver-lock stalls its queries cause in every process
-    sampler = ClockSampler(",".join(str(i) for i in range(world)) if world > 1 else dev) if rank == 0 else None
+    sampler = ClockSampler(",".join(str(i) for i in range(world)) if world > 1 else dev) if (rank == 0 and not os.environ.get("DSO_B200_NO_CLOCKS")) else None
     time.sleep(0.25)
     barrier()
     launches0 = ctx.launch_count()
@@ -715,9 +715,9 @@ def run_ours(args):
     t_pipe = reduce_max(dist, t_pipe, device)
     conv_p = reduce_sum(dist, float(ok_p), device)
 
-    per_rank = [[t_value / args.steps * 1e3, float(np.mean(ms_k)), float(np.mean([r.n_evals for r in results]))]]
+    per_rank = [[t_value / args.steps * 1e3, float(np.mean(ms_k)), float(np.mean([r.n_evals for r in results])), float(np.max(ms))]]
     if dist is not None:
-        g = [torch.zeros(3, dtype=torch.float64, device=device) for _ in range(world)]
+        g = [torch.zeros(4, dtype=torch.float64, device=device) for _ in range(world)]
         dist.all_gather(g, torch.tensor(per_rank[0], dtype=torch.float64, device=device))
         per_rank = [[float(v) for v in x.tolist()] for x in g]
     t_value = reduce_max(dist, t_value, device)
@@ -765,7 +765,7 @@ def run_ours(args):
                 "more_tracker_rows": rows,
                 "launch_gap_ms": t_value / args.steps * 1e3 - roofline["kernel_ms"],
                 "step_ms_rank0": {"median": float(np.median(ms)), "max": float(np.max(ms)), "min": float(np.min(ms))},
-                "by_rank_ms_per_step_kernel_ms_evals": per_rank,
+                "by_rank_ms_per_step_kernel_ms_evals_max_step_ms": per_rank,
                 "value_without_launch_gap": total_steps / (roofline["kernel_ms"] * 1e-3 * args.steps),
                 "host_cores_of_rank0": sorted(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else None,
                 "wall_s_timed_region": t_wall1 - t_wall0,
