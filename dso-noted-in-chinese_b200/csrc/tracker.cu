@@ -1059,6 +1059,7 @@ track_persistent_kernel(TrackLevels TL, dso_b200_track_opts opt, const TrackIn* 
 	__shared__ float s_tot[64];
 	__shared__ float s_passE[DSO_B200_MAX_PASSES], s_passN[DSO_B200_MAX_PASSES];
 	__shared__ LMShared s_lm;
+	__shared__ int s_lvl_per[5], s_lvl_base[5];
 	__shared__ dso_b200_track_result s_res;
 	extern __shared__ float4 s_pts[];
 
@@ -1095,7 +1096,12 @@ track_persistent_kernel(TrackLevels TL, dso_b200_track_opts opt, const TrackIn* 
 	int tot_slots = 0;
 #pragma unroll
 	for (int l = 0; l < 5; l++)
-		if (l <= coarsestLvl) tot_slots += (TL.pc_n[l] + CS * NC - 1) / (CS * NC);
+		if (l <= coarsestLvl)
+		{
+			const int per = (TL.pc_n[l] + CS * NC - 1) / (CS * NC);
+			if (tid == 32) { s_lvl_per[l] = per; s_lvl_base[l] = tot_slots; }
+			tot_slots += per;
+		}
 	const bool all_staged = tot_slots <= smem_pts_cap;
 	if (all_staged && NT > 32 && warp > 0)
 	{
@@ -1129,10 +1135,13 @@ track_persistent_kernel(TrackLevels TL, dso_b200_track_opts opt, const TrackIn* 
 	// makeImages wrote it): ask for it now, coarsest level first, behind the cloud loads above.  Fire and forget; the
 	// levels are walked minutes (in GPU terms) later.  Only the levels this call uses.
 	// (cp.async.bulk.prefetch.L2 in 16 KB pieces was tried instead: same first-evaluation times, kernel 3 us longer)
+	// Only the two coarsest levels are requested here; the finer ones follow in slices, issued by the warps that idle
+	// during the LM steps of the first evaluations (below), so that the requests do not queue in front of the first
+	// evaluation's own loads (3 200 line requests per CTA are ~3 k cycles of load/store-unit time).
 	if (warp > 0)
 	{
 		const int G = (int)(CS * NC) * (NT - 32), g = (int)(cidx * CS + rank) * (NT - 32) + (tid - 32);
-		for (int l = coarsestLvl; l >= 0; l--)
+		for (int l = coarsestLvl; l >= 0 && l >= coarsestLvl - 1; l--)
 		{
 			const char* base = reinterpret_cast<const char*>(TL.img[l]);
 			const int bytes = TL.w[l] * TL.h[l] * (int)sizeof(float4);
@@ -1151,22 +1160,20 @@ track_persistent_kernel(TrackLevels TL, dso_b200_track_opts opt, const TrackIn* 
 	int buf = 0;
 	unsigned xphase[2] = { 0u, 0u };
 	int staged_lvl = -1;
+	constexpr int PF_PER_EVAL = 4;
+	int pf_lvl = coarsestLvl - 2, pf_round = 0;            // prefetch cursor of the idle warps: level, round of G lines
 	while (true)
 	{
 		const int lvl = sCtl[0];
 		const int n = TL.pc_n[lvl];
-		const int per = (n + CS * NC - 1) / (CS * NC);
+		// slice of this CTA and its offset in the staged cloud: tabulated in the prologue (run-time integer divisions are
+		// ~100 cycles each, and this is the top of every evaluation)
+		const int per = s_lvl_per[lvl];
 		const int beg = min((int)(cidx * CS + rank) * per, n), end = min(beg + per, n);
 		const float4* __restrict__ gp = TL.pc[lvl];
 		const bool use_smem = all_staged || (end - beg) <= smem_pts_cap;
-		int s_base = 0;
-		if (all_staged)
-		{
-#pragma unroll
-			for (int l = 0; l < 5; l++)
-				if (l < lvl) s_base += (TL.pc_n[l] + CS * NC - 1) / (CS * NC);
-		}
-		else if (use_smem && staged_lvl != lvl)
+		const int s_base = all_staged ? s_lvl_base[lvl] : 0;
+		if (!all_staged && use_smem && staged_lvl != lvl)
 		{
 			long long ts0 = 0;
 			if (PROF) ts0 = clock64();
@@ -1233,6 +1240,22 @@ track_persistent_kernel(TrackLevels TL, dso_b200_track_opts opt, const TrackIn* 
 			if (PROF) { long long t = clock64(); tph[2] += t - tc0; if (tid == 0 && blockIdx.x == 0 && tph[4] < 24) phase_cycles[26 + 4 * tph[4]] = t - tc0; tc0 = t; }
 			lm_step_warp(R, K, s_lm, s_tot, TL, opt, &s_res, s_passE, s_passN, sP, sCtl, n, lane, PROF ? lmt : nullptr);
 			if (PROF) { long long t = clock64(); tph[3] += t - tc0; if (tid == 0 && blockIdx.x == 0 && tph[4] < 24) phase_cycles[27 + 4 * tph[4]] = t - tc0; tph[4]++; }
+		}
+		if (NT > 64 && warp >= 2 && pf_lvl >= 0)
+		{
+			// idle until the LM warp is done: the next slice of the finer levels' prefetch (PF_PER_EVAL lines per thread)
+			const int G = (int)(CS * NC) * (NT - 64), g = (int)(cidx * CS + rank) * (NT - 64) + (tid - 64);
+#pragma unroll
+			for (int q = 0; q < PF_PER_EVAL; q++)
+			{
+				if (pf_lvl < 0) break;
+				const int bytes = TL.w[pf_lvl] * TL.h[pf_lvl] * (int)sizeof(float4);
+				const int lines = bytes > (8 << 20) ? 0 : (bytes + 127) >> 7;
+				const int i = pf_round * G + g;
+				if (i < lines) asm volatile("prefetch.global.L2 [%0];" :: "l"(reinterpret_cast<const char*>(TL.img[pf_lvl]) + ((size_t)i << 7)));
+				pf_round++;
+				if (pf_round * G >= lines) { pf_lvl--; pf_round = 0; }        // uniform over the cluster: G and lines are
+			}
 		}
 		xphase[buf] ^= 1u;
 		__syncthreads();           // the next EvalParams / level / done flag are in shared memory
