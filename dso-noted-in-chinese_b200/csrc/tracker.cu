@@ -1094,14 +1094,18 @@ track_persistent_kernel(TrackLevels TL, dso_b200_track_opts opt, const TrackIn* 
 	// this CTA's slice of the cloud of EVERY level goes into shared memory now, by the warps that have nothing to do with
 	// the LM set-up: one round of (possibly cold) memory latency for all levels instead of one per level change
 	int tot_slots = 0;
+	int perL[5];                                           // one run-time division per level, not one per use
 #pragma unroll
 	for (int l = 0; l < 5; l++)
+	{
+		perL[l] = 0;
 		if (l <= coarsestLvl)
 		{
-			const int per = (TL.pc_n[l] + CS * NC - 1) / (CS * NC);
-			if (tid == 32) { s_lvl_per[l] = per; s_lvl_base[l] = tot_slots; }
-			tot_slots += per;
+			perL[l] = (TL.pc_n[l] + CS * NC - 1) / (CS * NC);
+			if (tid == 32) { s_lvl_per[l] = perL[l]; s_lvl_base[l] = tot_slots; }
+			tot_slots += perL[l];
 		}
+	}
 	const bool all_staged = tot_slots <= smem_pts_cap;
 	if (all_staged && NT > 32 && warp > 0)
 	{
@@ -1120,7 +1124,7 @@ track_persistent_kernel(TrackLevels TL, dso_b200_track_opts opt, const TrackIn* 
 				for (int l = 0; l < 5; l++)
 					if (l <= coarsestLvl)
 					{
-						const int nl = TL.pc_n[l], per = (nl + CS * NC - 1) / (CS * NC);
+						const int nl = TL.pc_n[l], per = perL[l];
 						const int b = min((int)(cidx * CS + rank) * per, nl), e = min(b + per, nl);
 						if (j >= off && j - off < e - b) { v[q] = __ldg(TL.pc[l] + b + (j - off)); have[q] = true; }
 						off += per;
