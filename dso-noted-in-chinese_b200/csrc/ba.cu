@@ -36,6 +36,7 @@ int ba_create(dso_b200_ctx* ctx)
 	W->window_set = W->glue_set = W->points_set = W->res_set = W->lin_done = W->top_done = false;
 	W->capP = W->capR = W->capChunks = W->capPC = 0;
 	W->nChunks = W->nPC = 0;
+	W->contrib_from_lin = false;
 	const int N = 8 * MAXF + CPARS;
 	CK(cudaMalloc(&W->d_precalc, MAXF * MAXF * 28 * sizeof(float)));
 	CK(cudaMalloc(&W->d_adHost, MAXF * MAXF * 64 * sizeof(double)));
@@ -174,7 +175,7 @@ __global__ void __launch_bounds__(256) ba_linearize_kernel(BAParams B, const flo
                                                            float* J0, float* J1, int* newState, float* newEnergy, float* newEnergyWO,
                                                            float* cpt, float* proj, double* resEnergy,
                                                            const int* __restrict__ subset, int nsub, int reset_oob,
-                                                           unsigned char* isAct, float* JpJdF)
+                                                           unsigned char* isAct, float* JpJdF, float* contrib = nullptr)
 {
 	__shared__ float sJ[32][JSZ + 2];
 	const int tid = threadIdx.x, lane = tid & 31, g = tid >> 3, idx = tid & 7, base = lane & ~7;
@@ -242,6 +243,16 @@ __global__ void __launch_bounds__(256) ba_linearize_kernel(BAParams B, const flo
 	const float JA00 = seq8(fmul(ja, g1), base), JA01 = seq8(fmul(ja, g2), base), JA10 = seq8(fmul(hw, g1), base), JA11 = seq8(fmul(hw, g2), base);
 	const float AA00 = seq8(fmul(fmul(fmul(drdA, drdA), hw), hw), base), AA01 = seq8(fmul(fmul(drdA, hw), hw), base), AA11 = seq8(fmul(hw, hw), base);
 	const float wJI2 = seq8(fmul(fmul(hw, hw), fadd(fmul(g1, g1), fmul(g2, g2))), base);
+	// APPLY: JI_r = sum_i resF_i * JIdx_i of AccumulatedTopHessianSSE::addPoint<0> (AccumulatedTopHessian.cpp:107-118: a scalar
+	// "+=" loop that starts from 0.f, hence the 0 + p of lane 0), so that the per-point terms of this residual (:142-150) can
+	// leave with the Jacobian and the per-point sums need not wait for the top accumulation
+	float JIr0 = 0.f, JIr1 = 0.f;
+	if (APPLY)
+	{
+		const float p0 = fmul(resF, g1), p1 = fmul(resF, g2);
+		JIr0 = seq8(idx == 0 ? fadd(0.f, p0) : p0, base);
+		JIr1 = seq8(idx == 0 ? fadd(0.f, p1) : p1, base);
+	}
 
 	bool outlier_f = false;
 	float eLeft_f = 0.f;
@@ -332,6 +343,14 @@ __global__ void __launch_bounds__(256) ba_linearize_kernel(BAParams B, const flo
 			if (idx < 6) val = fadd(fmul(Jl[J_PDXI0 + idx], a0), fmul(Jl[J_PDXI1 + idx], a1));
 			else val = fadd(fmul(Jl[J_ABIDX + 2 * (idx - 6)], d0), fmul(Jl[J_ABIDX + 2 * (idx - 6) + 1], d1));
 			JpJdF[8 * (size_t)r + idx] = val;
+			if (contrib && idx < 6)
+			{
+				float c;
+				if (idx == 0) c = fadd(fmul(JIr0, d0), fmul(JIr1, d1));
+				else if (idx == 1) c = fadd(fmul(a0, d0), fmul(a1, d1));
+				else c = fadd(fmul(Jl[J_PDC0 + idx - 2], a0), fmul(Jl[J_PDC1 + idx - 2], a1));
+				contrib[6 * (size_t)r + idx] = c;
+			}
 		}
 		if (idx == 0)
 		{
@@ -385,6 +404,39 @@ __global__ void ba_energy_blocks_kernel(int n, const double* __restrict__ e, dou
 	for (int o = 128; o > 0; o >>= 1) { if ((int)threadIdx.x < o) s[threadIdx.x] += s[threadIdx.x + o]; __syncthreads(); }
 	if (threadIdx.x == 0) blocks[blockIdx.x] = s[0];
 }
+// both in one launch: the last block to finish adds the block sums in block order and re-arms the counter
+__global__ void __launch_bounds__(256) ba_energy_kernel(int n, const double* __restrict__ e, double* blocks, unsigned int* counter, double* out)
+{
+	__shared__ double s[256];
+	__shared__ bool last;
+	const int i = blockIdx.x * 256 + threadIdx.x;
+	s[threadIdx.x] = i < n ? e[i] : 0.0;
+	__syncthreads();
+	for (int o = 128; o > 0; o >>= 1) { if ((int)threadIdx.x < o) s[threadIdx.x] += s[threadIdx.x + o]; __syncthreads(); }
+	if (threadIdx.x == 0)
+	{
+		blocks[blockIdx.x] = s[0];
+		__threadfence();
+		last = atomicAdd(counter, 1u) == gridDim.x - 1;
+	}
+	__syncthreads();
+	if (last && threadIdx.x == 0)
+	{
+		__threadfence();
+		const int nb = gridDim.x;
+		double t = 0;
+		for (int i0 = 0; i0 < nb; i0 += 16)                   // sixteen loads in flight, adds in block order
+		{
+			double v[16];
+#pragma unroll
+			for (int u = 0; u < 16; u++) v[u] = (i0 + u < nb) ? __ldcg(blocks + i0 + u) : 0.0;
+#pragma unroll
+			for (int u = 0; u < 16; u++) if (i0 + u < nb) t += v[u];
+		}
+		out[0] = t;
+		*counter = 0u;
+	}
+}
 __global__ void ba_energy_final_kernel(int nb, const double* __restrict__ blocks, double* out)
 {
 	if (threadIdx.x == 0 && blockIdx.x == 0)
@@ -429,6 +481,7 @@ __global__ void __launch_bounds__(128) ba_accum_top_kernel(const int* __restrict
                                                            const float* __restrict__ J0, const float* __restrict__ J1, float* contrib,
                                                            float* partials, int* chunk_nres, BALinArgs LA)
 {
+	// contrib == NULL: the fused linearisation has already written the per-point terms of every active residual
 	__shared__ float sx[CHUNK_R][10], sy[CHUNK_R][10], sw[CHUNK_R][16];   // sw: a,b,c | TR00,TR10,TR01,TR11,TR02,TR12 | BR0..5
 	__shared__ int s_n;
 	const int chunk = blockIdx.x, tid = threadIdx.x;
@@ -494,11 +547,14 @@ __global__ void __launch_bounds__(128) ba_accum_top_kernel(const int* __restrict
 			const float d0 = J[J_PDD], d1 = J[J_PDD + 1];
 			const float q0 = fadd(fmul(J[J_IDX2 + 0], d0), fmul(J[J_IDX2 + 1], d1));
 			const float q1 = fadd(fmul(J[J_IDX2 + 2], d0), fmul(J[J_IDX2 + 3], d1));
-			float* c = contrib + 6 * (size_t)r;
-			c[0] = fadd(fmul(JI_r0, d0), fmul(JI_r1, d1));
-			c[1] = fadd(fmul(q0, d0), fmul(q1, d1));
+			if (contrib)
+			{
+				float* c = contrib + 6 * (size_t)r;
+				c[0] = fadd(fmul(JI_r0, d0), fmul(JI_r1, d1));
+				c[1] = fadd(fmul(q0, d0), fmul(q1, d1));
 #pragma unroll
-			for (int k = 0; k < 4; k++) c[2 + k] = fadd(fmul(J[J_PDC0 + k], q0), fmul(J[J_PDC1 + k], q1));
+				for (int k = 0; k < 4; k++) c[2 + k] = fadd(fmul(J[J_PDC0 + k], q0), fmul(J[J_PDC1 + k], q1));
+			}
 			atomicAdd(&s_n, 1);
 		}
 		else
@@ -703,13 +759,21 @@ __global__ void ba_reduce_partials_kernel(const float* __restrict__ partials, in
 #define TC_BC 288
 
 // stitchDoubleInternal (AccumulatedTopHessian.cpp:259-310) for one pair: the adjoint sandwiches of its 13x13 block
+// partials != NULL (few chunks per pair): the block sums the chunk partials of its pair itself, in chunk order, instead of
+// reading the output of a separate reduction launch
 __global__ void __launch_bounds__(256) ba_top_pair_kernel(int nF, const double* __restrict__ topRed, const double* __restrict__ adHost,
-                                                          const double* __restrict__ adTarget, double* contrib)
+                                                          const double* __restrict__ adTarget, double* contrib,
+                                                          const float* __restrict__ partials = nullptr, const int* __restrict__ pair_chunk_begin = nullptr)
 {
 	__shared__ double accH[176], AH[64], AT[64], T1[192];
 	const int k = blockIdx.x, tid = threadIdx.x;
 	double* out = contrib + (size_t)k * TC_STRIDE;
-	if (tid < 169) { const int i = tid / 13, j = tid - 13 * i; accH[tid] = topRed[(size_t)k * NTOP_PAD + top_index(i, j)]; }
+	if (tid < 169)
+	{
+		const int i = tid / 13, j = tid - 13 * i;
+		accH[tid] = partials ? ordered_chunk_sum(partials, NTOP_PAD, top_index(i, j), pair_chunk_begin[k], pair_chunk_begin[k + 1])
+		                     : topRed[(size_t)k * NTOP_PAD + top_index(i, j)];
+	}
 	else if (tid < 233) AH[tid - 169] = adHost[(size_t)k * 64 + tid - 169];
 	if (tid >= 192) AT[tid - 192] = adTarget[(size_t)k * 64 + tid - 192];
 	__syncthreads();
@@ -1286,7 +1350,8 @@ extern "C" int dso_b200_ba_set_residuals(dso_b200_ctx* ctx, int nR, const int* p
 		CK(cudaMalloc(&W->d_JpJdF, n * 8 * sizeof(float))); CK(cudaMalloc(&W->d_contrib, n * 6 * sizeof(float))); CK(cudaMalloc(&W->d_resEnergy, n * sizeof(double)));
 		CK(cudaMalloc(&W->d_perm, n * sizeof(int)));
 		CK(cudaMalloc(&W->d_subset, n * sizeof(int)));
-		CK(cudaMalloc(&W->d_energy_blocks, ((n + 255) / 256) * sizeof(double)));
+		CK(cudaMalloc(&W->d_energy_blocks, ((n + 255) / 256 + 1) * sizeof(double)));      // + the fused kernel's block counter
+		CK(cudaMemset(W->d_energy_blocks, 0, ((n + 255) / 256 + 1) * sizeof(double)));
 		CK(cudaMalloc(&W->d_resToZero, n * 8 * sizeof(float)));
 		W->capR = nR;
 	}
@@ -1517,7 +1582,7 @@ int ba_enqueue_linearize(dso_b200_ctx* ctx, bool fork, bool apply)
 		ba_linearize_kernel<true><<<(nR + 31) / 32, 256, 0, ctx->ba_stream>>>(W->P, W->d_precalc, W->d_pt, W->d_color, W->d_weights, W->d_phost, W->d_rpoint,
 		                                                                 W->d_rtarget, W->d_state, W->d_energy, W->d_efsel, W->d_J[0], W->d_J[1],
 		                                                                 W->d_newState, W->d_newEnergy, W->d_newEnergyWO, W->d_cpt, W->d_proj, W->d_resEnergy,
-		                                                                 nullptr, 0, 0, W->d_isAct, W->d_JpJdF);
+		                                                                 nullptr, 0, 0, W->d_isAct, W->d_JpJdF, W->d_contrib);
 	else
 		ba_linearize_kernel<false><<<(nR + 31) / 32, 256, 0, ctx->ba_stream>>>(W->P, W->d_precalc, W->d_pt, W->d_color, W->d_weights, W->d_phost, W->d_rpoint,
 		                                                                  W->d_rtarget, W->d_state, W->d_energy, W->d_efsel, W->d_J[0], W->d_J[1],
@@ -1527,11 +1592,11 @@ int ba_enqueue_linearize(dso_b200_ctx* ctx, bool fork, bool apply)
 	const int nb = (nR + 255) / 256;
 	cudaStream_t se = ctx->ba_stream;
 	if (fork) { int rc = ba_fork(ctx); if (rc) return rc; se = W->side_stream; }
-	ba_energy_blocks_kernel<<<nb, 256, 0, se>>>(nR, W->d_resEnergy, W->d_energy_blocks);
-	ba_energy_final_kernel<<<1, 32, 0, se>>>(nb, W->d_energy_blocks, W->d_scalars);
-	LAUNCHED(ctx, 3);
+	ba_energy_kernel<<<nb, 256, 0, se>>>(nR, W->d_resEnergy, W->d_energy_blocks, reinterpret_cast<unsigned int*>(W->d_energy_blocks + nb), W->d_scalars);
+	LAUNCHED(ctx, 2);
 	CK(cudaGetLastError());
 	W->lin_done = true;
+	W->contrib_from_lin = apply;       // the fused form has written the per-point terms of every active residual
 	return 0;
 }
 
@@ -1558,26 +1623,34 @@ int ba_enqueue_top(dso_b200_ctx* ctx, int mode, const unsigned char* d_pmask, bo
 	LA.adHTdeltaF = W->d_adHTdeltaF; LA.cDeltaF = W->d_cDeltaF; LA.resToZero = W->d_resToZero; LA.nF = nF; LA.pmask = d_pmask;
 	float* Hdd = mode ? W->d_Hdd_L : W->d_Hdd; float* bd = mode ? W->d_bd_L : W->d_bd; float* Hcd = mode ? W->d_Hcd_L : W->d_Hcd;
 	double* Hout = mode ? W->d_HL : W->d_HA; double* bout = mode ? W->d_bL : W->d_bA;
+	// mode 0 right after the fused linearisation: the per-point terms are already there, so the per-point sums (and with
+	// them the whole Schur chain) do not wait for the top accumulation, which moves to the side branch with its stitch
+	const bool early_sums = mode == 0 && fork && W->contrib_from_lin && !d_pmask;
+	if (mode == 2) W->contrib_from_lin = false;               // addPoint<2> rewrites the terms of the marginalised points
+	if (early_sums) { int rc = ba_fork(ctx); if (rc) return rc; st = W->side_stream; }
 	if (mode == 2)
 		ba_accum_top_kernel<2><<<W->nChunks, 128, 0, st>>>(W->d_perm, W->d_chunk_start, W->d_chunk_cnt, W->d_isAct, W->d_isLin, W->d_efsel,
 		                                                 W->d_J[0], W->d_J[1], W->d_contrib, W->d_topPartials, W->d_chunk_nres, LA);
 	else if (mode == 0)
 		ba_accum_top_kernel<0><<<W->nChunks, 128, 0, st>>>(W->d_perm, W->d_chunk_start, W->d_chunk_cnt, W->d_isAct, W->d_isLin, W->d_efsel,
-		                                                 W->d_J[0], W->d_J[1], W->d_contrib, W->d_topPartials, W->d_chunk_nres, LA);
+		                                                 W->d_J[0], W->d_J[1], early_sums ? nullptr : W->d_contrib, W->d_topPartials, W->d_chunk_nres, LA);
 	else
 		ba_accum_top_kernel<1><<<W->nChunks, 128, 0, st>>>(W->d_perm, W->d_chunk_start, W->d_chunk_cnt, W->d_isAct, W->d_isLin, W->d_efsel,
 		                                                 W->d_J[0], W->d_J[1], W->d_contrib, W->d_topPartials, W->d_chunk_nres, LA);
 	SchurPrepOut po;
 	po.HdiF = W->d_HdiF; po.bdSumF = W->d_bdSumF; po.idh = W->d_idh; po.HcdSum = W->d_HcdSum; po.priorF = W->d_priorF; po.deltaF = W->d_deltaF;
 	if (prep && (mode == 2 || d_pmask)) { dso_set_error("ba_enqueue_top: the fused Schur preparation has no marginalisation form"); return DSO_B200_E_ARG; }
-	ba_point_sums_kernel<<<(W->P.nP + 127) / 128, 128, 0, st>>>(W->P.nP, W->d_res_begin, W->d_isAct, W->d_isLin, W->d_contrib, Hdd, bd, Hcd, mode, d_pmask, W->d_Hdd, W->d_bd, W->d_Hcd,
+	ba_point_sums_kernel<<<(W->P.nP + 127) / 128, 128, 0, early_sums ? ctx->ba_stream : st>>>(W->P.nP, W->d_res_begin, W->d_isAct, W->d_isLin, W->d_contrib, Hdd, bd, Hcd, mode, d_pmask, W->d_Hdd, W->d_bd, W->d_Hcd,
 	                                                            prep, W->d_Hdd_L, W->d_bd_L, W->d_Hcd_L, po);
-	if (fork) { int rc = ba_fork(ctx); if (rc) return rc; st = W->side_stream; }       // the stitch: independent of what follows on the main stream
-	ba_reduce_partials_kernel<<<dim3(1, nF * nF), NTOP_PAD, 0, st>>>(W->d_topPartials, NTOP_PAD, NTOP_PAD, W->d_pair_chunk_begin, W->d_topRed);
-	ba_top_pair_kernel<<<nF * nF, 256, 0, st>>>(nF, W->d_topRed, W->d_adHost, W->d_adTarget, W->d_topContrib);
+	if (fork && !early_sums) { int rc = ba_fork(ctx); if (rc) return rc; st = W->side_stream; }       // the stitch: independent of what follows on the main stream
+	const bool fused_reduce = W->nChunks <= 48 * nF * nF;            // few chunks per pair: the pair kernel sums them itself
+	if (!fused_reduce)
+		ba_reduce_partials_kernel<<<dim3(1, nF * nF), NTOP_PAD, 0, st>>>(W->d_topPartials, NTOP_PAD, NTOP_PAD, W->d_pair_chunk_begin, W->d_topRed);
+	ba_top_pair_kernel<<<nF * nF, 256, 0, st>>>(nF, W->d_topRed, W->d_adHost, W->d_adTarget, W->d_topContrib,
+	                                          fused_reduce ? W->d_topPartials : nullptr, W->d_pair_chunk_begin);
 	ba_top_gather_kernel<<<nF * nF + 1, 64, 0, st>>>(nF, W->nChunks, W->d_chunk_nres, W->d_topContrib, Hout, bout, W->d_scalars + (mode ? 2 : 0),
 	                                               mode == 1 ? W->d_priorH : nullptr, W->d_priorD, W->d_cDeltaF);
-	LAUNCHED(ctx, 5);
+	LAUNCHED(ctx, fused_reduce ? 4 : 5);
 	CK(cudaGetLastError());
 	if (mode == 0) W->top_done = true;
 	return 0;
@@ -1669,6 +1742,7 @@ extern "C" int dso_b200_ba_linearize_residuals(dso_b200_ctx* ctx, int k, const i
 	BA_CHECK(k <= nR, "more indices than residuals");
 	int* d_sub = W->d_subset;
 	CK(cudaMemcpyAsync(d_sub, residual_idx, (size_t)k * sizeof(int), cudaMemcpyHostToDevice, s));
+	W->contrib_from_lin = false;            // the subset's Jacobians change under the per-point terms
 	ba_linearize_kernel<false><<<(k + 31) / 32, 256, 0, s>>>(W->P, W->d_precalc, W->d_pt, W->d_color, W->d_weights, W->d_phost, W->d_rpoint,
 	                                                  W->d_rtarget, W->d_state, W->d_energy, W->d_efsel, W->d_J[0], W->d_J[1],
 	                                                  W->d_newState, W->d_newEnergy, W->d_newEnergyWO, W->d_cpt, W->d_proj, W->d_resEnergy,
