@@ -7,6 +7,7 @@
 #include "oracle_math.h"
 #include "oracle_settings.h"
 #include <vector>
+#include <algorithm>
 #include <thread>
 #include <mutex>
 #include <condition_variable>
@@ -307,9 +308,11 @@ struct dso_oracle_ba
 	double cPrior[4];
 	std::vector<double> framePrior, frameDeltaPrior, frameDelta, HM, bM;
 	std::vector<double> nullspaces; int nNullspaces;     // lastNullspaces_pose then _scale, each 8nF+4 long
+	int haveFirstFrame;                                  // "for(EFFrame* f : frames) if(f->frameID==0)" (EnergyFunctional.cpp:688, :835)
+	int margSolverMode; double margSolverModeDelta;      // setting_solverMode / setting_solverModeDelta seen by marginalizePointsF
 	std::vector<float> pointStep;
 	Pool* pool; int poolN;
-	dso_oracle_ba() : nNullspaces(0), pool(0), poolN(0) { for (int i = 0; i < 4; i++) cPrior[i] = 0; }
+	dso_oracle_ba() : nNullspaces(0), haveFirstFrame(1), margSolverMode(128 | 2048), margSolverModeDelta(1e-5), pool(0), poolN(0) { for (int i = 0; i < 4; i++) cPrior[i] = 0; }
 	Pool* getPool(int n) { if (!pool || poolN != n) { delete pool; pool = new Pool(n); poolN = n; } return pool; }
 };
 
@@ -1196,11 +1199,12 @@ extern "C" void dso_oracle_ba_fix_linearization(dso_oracle_ba* B, const unsigned
 	}
 }
 
-// EnergyFunctional::orthogonalize(VecX* b, 0), :741-792: x -= 0.5 (N Npi^T + Npi N^T) x
-static void orthogonalize_vec(const dso_oracle_ba* B, double solverModeDelta, std::vector<double>& x)
+// EnergyFunctional::orthogonalize(VecX* b, MatXX* H), :741-792: NNpiTS = 0.5 (N Npi^T + Npi N^T) from the normalised
+// null-space vectors; b -= NNpiTS b; H -= NNpiTS H NNpiTS
+static bool nullspace_projector(const dso_oracle_ba* B, double solverModeDelta, int N, std::vector<double>& PS)
 {
-	const int N = (int)x.size(), k = B->nNullspaces;
-	if (k == 0) return;
+	const int k = B->nNullspaces;
+	if (k == 0) return false;
 	std::vector<double> Nn((size_t)N * k), U((size_t)N * k), S(k), V((size_t)k * k);
 	for (int j = 0; j < k; j++)
 	{
@@ -1229,14 +1233,49 @@ static void orthogonalize_vec(const dso_oracle_ba* B, double solverModeDelta, st
 			for (int q = 0; q < k; q++) s += Nn[(size_t)i * k + q] * Npi[(size_t)j * k + q];
 			P[(size_t)i * N + j] = s;
 		}
-	std::vector<double> y(N);
+	PS.assign((size_t)N * N, 0.0);
 	for (int i = 0; i < N; i++)
+		for (int j = 0; j < N; j++) PS[(size_t)i * N + j] = 0.5 * (P[(size_t)i * N + j] + P[(size_t)j * N + i]);
+	return true;
+}
+static void orthogonalize_sys(const dso_oracle_ba* B, double solverModeDelta, int N, double* b, double* H)
+{
+	std::vector<double> PS;
+	if (!nullspace_projector(B, solverModeDelta, N, PS)) return;
+	if (b)
 	{
-		double s = 0;
-		for (int j = 0; j < N; j++) s += 0.5 * (P[(size_t)i * N + j] + P[(size_t)j * N + i]) * x[j];
-		y[i] = s;
+		std::vector<double> y(N);
+		for (int i = 0; i < N; i++)
+		{
+			double s = 0;
+			for (int j = 0; j < N; j++) s += PS[(size_t)i * N + j] * b[j];
+			y[i] = s;
+		}
+		for (int i = 0; i < N; i++) b[i] -= y[i];
 	}
-	for (int i = 0; i < N; i++) x[i] -= y[i];
+	if (H)
+	{
+		std::vector<double> T((size_t)N * N), T2((size_t)N * N);
+		for (int i = 0; i < N; i++)
+			for (int j = 0; j < N; j++)
+			{
+				double s = 0;
+				for (int q = 0; q < N; q++) s += PS[(size_t)i * N + q] * H[(size_t)q * N + j];
+				T[(size_t)i * N + j] = s;
+			}
+		for (int i = 0; i < N; i++)
+			for (int j = 0; j < N; j++)
+			{
+				double s = 0;
+				for (int q = 0; q < N; q++) s += T[(size_t)i * N + q] * PS[(size_t)q * N + j];
+				T2[(size_t)i * N + j] = s;
+			}
+		for (size_t i = 0; i < (size_t)N * N; i++) H[i] -= T2[i];
+	}
+}
+static void orthogonalize_vec(const dso_oracle_ba* B, double solverModeDelta, std::vector<double>& x)
+{
+	orthogonalize_sys(B, solverModeDelta, (int)x.size(), x.data(), 0);
 }
 
 #define SOLVER_SVD 1
@@ -1301,14 +1340,13 @@ extern "C" void dso_oracle_scaled_ldlt_solve(const double* HF, const double* bF,
 }
 
 // EnergyFunctional::solveSystemF, :802-924.  Restated: the default solver (LDLT on the diagonally scaled system) with
-// SOLVER_USE_GN / SOLVER_FIX_LAMBDA / SOLVER_ORTHOGONALIZE_X(_LATER); the SVD and ORTHOGONALIZE_SYSTEM branches return -1.
+// SOLVER_USE_GN / SOLVER_FIX_LAMBDA / SOLVER_ORTHOGONALIZE_X(_LATER), and the non-default SVD (+CUT7) and ORTHOGONALIZE_SYSTEM branches.
 // x_out: 8nF+4 (= lastX; frame steps are -x segments, the calibration step -x.head<4>), pointStep_out: nP (PointHessian::step).
 extern "C" int dso_oracle_ba_solve(dso_oracle_ba* B, int iteration, double lambda, int solverMode, double solverModeDelta, int MT, int nthreads,
                                    double* x_out, float* pointStep_out, double* HFinal_out, double* bFinal_out)
 {
 	if (solverMode & SOLVER_USE_GN) lambda = 0;
 	if (solverMode & SOLVER_FIX_LAMBDA) lambda = 1e-5;
-	if (solverMode & (SOLVER_SVD | SOLVER_ORTHOGONALIZE_SYSTEM)) return -1;
 	const int nF = B->nF, N = 8 * nF + CPARS;
 	if ((int)B->bM.size() != N) dso_oracle_ba_set_priors(B, B->cPrior, 0, 0, 0, 0, 0);
 	std::vector<double> HA((size_t)N * N), bA(N), HL((size_t)N * N), bL(N), HS((size_t)N * N), bS(N);
@@ -1324,15 +1362,67 @@ extern "C" int dso_oracle_ba_solve(dso_oracle_ba* B, int iteration, double lambd
 		for (int j = 0; j < N; j++) s += B->HM[(size_t)i * N + j] * d[j];
 		bMtop[i] = B->bM[i] + s;                                                       // :824
 	}
+	if (solverMode & SOLVER_ORTHOGONALIZE_SYSTEM)
+	{
+		// :832-851: HT_act = HL + HA - H_sc, bT_act = bL + bA - b_sc, projected off the null spaces unless the first frame
+		// (the gauge anchor) is still in the window; then the marginalisation prior, then the damping
+		for (size_t i = 0; i < (size_t)N * N; i++) HF[i] = (HL[i] + HA[i]) - HS[i];
+		for (int i = 0; i < N; i++) bF[i] = (bL[i] + bA[i]) - bS[i];
+		if (!B->haveFirstFrame) orthogonalize_sys(B, solverModeDelta, N, bF.data(), HF.data());
+		for (size_t i = 0; i < (size_t)N * N; i++) HF[i] = HF[i] + B->HM[i];
+		for (int i = 0; i < N; i++) bF[i] = bF[i] + bMtop[i];
+		for (int i = 0; i < N; i++) HF[(size_t)i * N + i] *= (1 + lambda);
+	}
+	else
+	{
 	for (size_t i = 0; i < (size_t)N * N; i++) HF[i] = (HL[i] + B->HM[i]) + HA[i];     // :857
 	for (int i = 0; i < N; i++) bF[i] = ((bL[i] + bMtop[i]) + bA[i]) - bS[i];          // :859
 	for (int i = 0; i < N; i++) HF[(size_t)i * N + i] *= (1 + lambda);                  // :865
 	const double isc = 1.0f / (1 + lambda);                                             // :866
 	for (size_t i = 0; i < (size_t)N * N; i++) HF[i] -= HS[i] * isc;
+	}
 	if (HFinal_out) memcpy(HFinal_out, HF.data(), sizeof(double) * N * N);
 	if (bFinal_out) memcpy(bFinal_out, bF.data(), sizeof(double) * N);
 	std::vector<double> x(N);
-	dso_oracle_scaled_ldlt_solve(HF.data(), bF.data(), N, x.data());                    // :905-908
+	if (solverMode & SOLVER_SVD)
+	{
+		// :870-900: SVecI = 1/sqrt(diag) (no +10 here), thin SVD of the scaled matrix, singular values below
+		// solverModeDelta * max zeroed (SVD_CUT7: also the last seven), x = SVecI V (U^T b ./ S)
+		std::vector<double> sv(N), Hs((size_t)N * N), bs(N), U((size_t)N * N), S(N), V((size_t)N * N);
+		for (int i = 0; i < N; i++) sv[i] = 1.0 / std::sqrt(HF[(size_t)i * N + i]);
+		for (int i = 0; i < N; i++)
+			for (int j = 0; j < N; j++) Hs[(size_t)i * N + j] = (sv[i] * HF[(size_t)i * N + j]) * sv[j];
+		for (int i = 0; i < N; i++) bs[i] = sv[i] * bF[i];
+		orc::jacobi_svd_thin(Hs.data(), N, N, U.data(), S.data(), V.data());
+		double maxSv = 0;
+		for (int i = 0; i < N; i++) if (S[i] > maxSv) maxSv = S[i];
+		// Eigen::JacobiSVD returns the singular values in decreasing order (SVD_CUT7 drops "the last seven")
+		std::vector<int> ord(N);
+		for (int i = 0; i < N; i++) ord[i] = i;
+		std::stable_sort(ord.begin(), ord.end(), [&](int a, int b) { return S[a] > S[b]; });
+		std::vector<double> Ub(N);
+		for (int i = 0; i < N; i++)
+		{
+			double t = 0;
+			for (int j = 0; j < N; j++) t += U[(size_t)j * N + ord[i]] * bs[j];
+			Ub[i] = t;
+		}
+		for (int i = 0; i < N; i++)
+		{
+			const double Si = S[ord[i]];
+			if (Si < solverModeDelta * maxSv) Ub[i] = 0;
+			if ((solverMode & 16) && (i >= N - 7)) Ub[i] = 0;                              // SOLVER_SVD_CUT7
+			else Ub[i] /= Si;
+		}
+		for (int i = 0; i < N; i++)
+		{
+			double t = 0;
+			for (int j = 0; j < N; j++) t += V[(size_t)i * N + ord[j]] * Ub[j];
+			x[i] = sv[i] * t;
+		}
+	}
+	else
+		dso_oracle_scaled_ldlt_solve(HF.data(), bF.data(), N, x.data());                // :905-908
 	if ((solverMode & SOLVER_ORTHOGONALIZE_X) || (iteration >= 2 && (solverMode & SOLVER_ORTHOGONALIZE_X_LATER)))
 		orthogonalize_vec(B, solverModeDelta, x);                                       // :913-917
 	resubstitute(B, x);                                                                 // :925
@@ -1460,20 +1550,32 @@ extern "C" void dso_oracle_ba_marginalize_points(dso_oracle_ba* B, const unsigne
 		int hIdx = CPARS + h * 8;
 		for (int i = 0; i < CPARS; i++) for (int j = 0; j < 8; j++) Msc[i * N + hIdx + j] = Msc[(hIdx + j) * N + i];
 	}
+	std::vector<double> Hm((size_t)N * N), bm(N);
+	for (size_t i = 0; i < (size_t)N * N; i++) Hm[i] = M[i] - Msc[i];
+	for (int i = 0; i < N; i++) bm[i] = Mb[i] - Mbsc[i];
+	if ((B->margSolverMode & 4) && !B->haveFirstFrame)                                    // SOLVER_ORTHOGONALIZE_POINTMARG, :684-692
+		orthogonalize_sys(B, B->margSolverModeDelta, N, bm.data(), Hm.data());
 	for (size_t i = 0; i < (size_t)N * N; i++)
 	{
-		const double h = M[i] - Msc[i];
-		if (H_out) H_out[i] = h;
-		B->HM[i] += margWeightFac * h;
+		if (H_out) H_out[i] = Hm[i];
+		B->HM[i] += margWeightFac * Hm[i];
 	}
 	for (int i = 0; i < N; i++)
 	{
-		const double v = Mb[i] - Mbsc[i];
-		if (b_out) b_out[i] = v;
-		B->bM[i] += margWeightFac * v;
+		if (b_out) b_out[i] = bm[i];
+		B->bM[i] += margWeightFac * bm[i];
 	}
+	if (B->margSolverMode & 8)                                                            // SOLVER_ORTHOGONALIZE_FULL, :698-699
+		orthogonalize_sys(B, B->margSolverModeDelta, N, B->bM.data(), B->HM.data());
 	if (idepth_hessian_out) for (int i = 0; i < nP; i++) idepth_hessian_out[i] = B->points[i].idepth_hessian;
 }
+// the pieces of global state the non-default solver branches look at: whether the frame with frameID 0 is still in the
+// window (:688, :835) and setting_solverMode / setting_solverModeDelta as seen by marginalizePointsF
+extern "C" void dso_oracle_ba_set_solver_state(dso_oracle_ba* B, int haveFirstFrame, int margSolverMode, double margSolverModeDelta)
+{
+	B->haveFirstFrame = haveFirstFrame; B->margSolverMode = margSolverMode; B->margSolverModeDelta = margSolverModeDelta;
+}
+
 extern "C" void dso_oracle_ba_get_marg_prior(dso_oracle_ba* B, double* HM, double* bM)
 {
 	const int N = 8 * B->nF + CPARS;

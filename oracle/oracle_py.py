@@ -435,6 +435,10 @@ class BA:
         ns = np.ascontiguousarray(ns, dtype=np.float64).reshape(-1, 8 * self.nF + 4)
         self.L.dso_oracle_ba_set_nullspaces(self.p, ns.reshape(-1), ns.shape[0])
 
+    def set_solver_state(self, have_first_frame=True, marg_solver_mode=128 | 2048, marg_delta=1e-5):
+        self.L.dso_oracle_ba_set_solver_state.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_double]
+        self.L.dso_oracle_ba_set_solver_state(self.p, int(have_first_frame), int(marg_solver_mode), float(marg_delta))
+
     def fix_linearization(self, which=None):
         out = np.zeros(self.nR * 8, dtype=np.float32)
         w = None if which is None else np.ascontiguousarray(which, dtype=np.uint8)

@@ -242,6 +242,7 @@ struct dso_oracle_ba
 	std::vector<PointFrameResidual*> res;
 	IndexThreadReduce<Vec10>* red;
 	bool frames_inserted;
+	int margSolverMode; double margSolverModeDelta;
 	void calib() { set_calib(w, h, 1, fx, fy, cx, cy); }
 };
 
@@ -257,6 +258,7 @@ extern "C" dso_oracle_ba* dso_ref_ba_create(int w, int h, int nF, float fx, floa
 	B->frames.assign(nF, (FrameHessian*)0);
 	B->shells.assign(nF, (FrameShell*)0);
 	B->frames_inserted = false;
+	B->margSolverMode = setting_solverMode; B->margSolverModeDelta = setting_solverModeDelta;
 	return B;
 }
 extern "C" void dso_ref_ba_destroy(dso_oracle_ba* B) { delete B->red; delete B; }   // the object graph leaks on purpose (test process)
@@ -549,6 +551,15 @@ extern "C" int dso_ref_ba_solve(dso_oracle_ba* B, int iteration, double lambda, 
 	return 0;
 }
 
+// the global state the non-default solver branches look at: frameID of the first frame of the window (0 = the gauge anchor is
+// still there, EnergyFunctional.cpp:688, :835) and setting_solverMode / setting_solverModeDelta for marginalizePointsF
+extern "C" void dso_ref_ba_set_solver_state(dso_oracle_ba* B, int haveFirstFrame, int margSolverMode, double margSolverModeDelta)
+{
+	B->calib();
+	B->ef->frames[0]->frameID = haveFirstFrame ? 0 : 1000;
+	B->margSolverMode = margSolverMode; B->margSolverModeDelta = margSolverModeDelta;
+}
+
 // ---- rest of N2: marginalizePointsF, calcLEnergyF_MT, calcMEnergyF (the reference's own code) ----
 extern "C" double dso_ref_ba_calc_L_energy(dso_oracle_ba* B, int nthreads)
 {
@@ -581,7 +592,10 @@ extern "C" void dso_ref_ba_marginalize_points(dso_oracle_ba* B, const unsigned c
 	for (size_t i = 0; i < B->pts.size(); i++)
 		if (flags[i]) B->pts[i]->efPoint->stateFlag = EFPointStatus::PS_MARGINALIZE;
 	const int res0 = B->ef->resInM;
+	const int sm0 = setting_solverMode; const double sd0 = setting_solverModeDelta;
+	setting_solverMode = B->margSolverMode; setting_solverModeDelta = B->margSolverModeDelta;
 	B->ef->marginalizePointsF();                               // EnergyFunctional.cpp:642
+	setting_solverMode = sm0; setting_solverModeDelta = sd0;
 	setting_idepthFixPriorMargFac = f0; setting_margWeightFac = w0;
 	if (resInM) *resInM = B->ef->resInM - res0;
 	for (int r = 0; r < N; r++)

@@ -230,6 +230,78 @@ def test_solve_system_and_resubstitute(pkg, win, iteration, with_lin):
     assert np.isfinite(so["step"]).all() and np.abs(so["step"]).max() > 0
 
 
+SOLVER_SVD, SOLVER_ORTH_SYSTEM, SOLVER_ORTH_POINTMARG, SOLVER_ORTH_FULL, SOLVER_SVD_CUT7 = 1, 2, 4, 8, 16
+SOLVER_DEFAULT = 128 | 2048
+
+
+def _no_first_frame_inputs(W, pyr):
+    """a window whose frame 0 is not the sequence's first frame: no gauge prior on any frame (FrameHessian::getPrior gives
+    zeros for frameID != 0), the seven near-null directions of the active system as null spaces (what
+    FullSystem::getNullspaces hands over is that space), and a marginalisation prior of full rank"""
+    inp = list(_solve_inputs(W))
+    N = 8 * W.nF + 4
+    inp[1] = np.zeros_like(inp[1])
+    B = O.BA(W, pyr)
+    B.linearize(); B.apply_res()
+    B.set_priors(inp[0], inp[1], inp[2], inp[3], np.zeros((N, N)), np.zeros(N))
+    H0 = B.solve(0, 0.0, solver_mode=64)["HFinal"]
+    w, V = np.linalg.eigh(0.5 * (H0 + H0.T))
+    assert w[6] < 1e-6 * w[-1]
+    inp[6] = np.ascontiguousarray(V[:, :7].T)
+    inp[4] = inp[4] + np.eye(N) * 1e3
+    return inp
+
+
+@pytest.mark.parametrize("mode,first", [(SOLVER_DEFAULT | SOLVER_ORTH_SYSTEM, False), (SOLVER_DEFAULT | SOLVER_ORTH_SYSTEM, True),
+                                        (SOLVER_DEFAULT | SOLVER_SVD, True), (SOLVER_DEFAULT | SOLVER_SVD | SOLVER_SVD_CUT7, True),
+                                        (SOLVER_DEFAULT | SOLVER_SVD | SOLVER_ORTH_SYSTEM, False)])
+def test_solve_system_non_default_branches(pkg, window_small, mode, first):
+    """the SVD / SVD_CUT7 / ORTHOGONALIZE_SYSTEM branches of solveSystemF (EnergyFunctional.cpp:832-900) with and without the
+    gauge-fixing first frame in the window.  (The reference build's JacobiSVD is the stand-in Hestenes SVD, so these branches
+    are pinned up to the SVD algorithm: x agrees to 1e-7, not to rounding.)"""
+    W = window_small
+    pyr = [O.make_images(img, 1)[0][0] for img in W.images]
+    inp = _solve_inputs(W) if first else _no_first_frame_inputs(W, pyr)
+    Bo, Br = O.BA(W, pyr), O.BA(W, pyr, kind="ref")
+    for B in (Bo, Br):
+        B.linearize()
+        B.apply_res()
+        B.set_priors(*inp[:6])
+        B.set_nullspaces(inp[6])
+        B.set_solver_state(have_first_frame=first)
+    so, sr = Bo.solve(2, 1e-1, solver_mode=mode), Br.solve(2, 1e-1, solver_mode=mode)
+    assert np.isfinite(so["x"]).all() and np.abs(so["x"]).max() > 0
+    assert np.abs(so["x"] - sr["x"]).max() <= 1e-7 * np.abs(sr["x"]).max()
+    assert np.abs(so["step"] - sr["step"]).max() <= 1e-4 * np.abs(sr["step"]).max()
+    # the branch really is a different computation
+    sd = Bo.solve(2, 1e-1)
+    assert np.abs(so["x"] - sd["x"]).max() > 1e-9 * np.abs(sd["x"]).max()
+
+
+@pytest.mark.parametrize("mode", [SOLVER_DEFAULT | SOLVER_ORTH_POINTMARG, SOLVER_DEFAULT | SOLVER_ORTH_FULL])
+def test_marginalize_points_orthogonalize_branches(pkg, window_small, mode):
+    """SOLVER_ORTHOGONALIZE_POINTMARG / _FULL of marginalizePointsF (EnergyFunctional.cpp:684-699), first frame gone"""
+    W = window_small
+    pyr = [O.make_images(img, 1)[0][0] for img in W.images]
+    inp = _solve_inputs(W)            # random "null-space" vectors: with the true ones H P ~ 0 and the projection is a no-op
+    pflags = (np.arange(W.nP) % 3 == 1).astype(np.uint8)
+    rflags = pflags[W.res_point]
+
+    def run(kind, m):
+        B = O.BA(W, pyr, kind=kind)
+        B.linearize()
+        B.apply_res()
+        B.fix_linearization(rflags)
+        B.set_priors(*inp[:6])
+        B.set_nullspaces(inp[6])
+        B.set_solver_state(have_first_frame=False, marg_solver_mode=m)
+        return B.marginalize_points(pflags)
+    mo, mr, md = run("oracle", mode), run("ref", mode), run("oracle", SOLVER_DEFAULT)
+    assert np.abs(mo["HM"] - mr["HM"]).max() <= 1e-9 * np.abs(mr["HM"]).max()
+    assert np.abs(mo["bM"] - mr["bM"]).max() <= 1e-9 * np.abs(mr["bM"]).max()
+    assert np.abs(mo["HM"] - md["HM"]).max() > 1e-9 * np.abs(md["HM"]).max()       # the projection changed the prior
+
+
 def test_marginalize_points_and_energies(pkg, win):
     """rest of N2: calcLEnergyF_MT, calcMEnergyF and marginalizePointsF (EnergyFunctional.cpp:334-428, 642-703).  A third of
     the points are flagged; their residuals are linearised first (FullSystem::flagPointsForRemoval does the same)."""
