@@ -104,6 +104,7 @@ SIGNATURES = {
     "dso_b200_ba_set_calib_delta": (C.c_int, [vp, f64p]),
     "dso_b200_ba_set_priors": (C.c_int, [vp, vp, vp, vp, vp, vp, vp]),
     "dso_b200_ba_set_nullspaces": (C.c_int, [vp, vp, C.c_int, C.c_double]),
+    "dso_b200_ba_set_solver_state": (C.c_int, [vp, C.c_int, C.c_int, C.c_double]),
     "dso_b200_ba_fix_linearization": (C.c_int, [vp, vp, vp]),
     "dso_b200_ba_accumulate_L": (C.c_int, [vp, f64p, f64p, C.POINTER(C.c_int), vp, vp, vp]),
     "dso_b200_ba_solve": (C.c_int, [vp, C.c_int, C.c_double, C.c_int, vp, vp, vp, vp]),
@@ -518,6 +519,9 @@ class Context:
         N = 8 * self.nF + 4
         ns = np.ascontiguousarray(ns, dtype=np.float64).reshape(-1, N)
         self._check(self.L.dso_b200_ba_set_nullspaces(self.h, ns.ctypes.data, ns.shape[0], delta))
+
+    def ba_set_solver_state(self, have_first_frame=True, marg_solver_mode=128 | 2048, delta=1e-5):
+        self._check(self.L.dso_b200_ba_set_solver_state(self.h, int(have_first_frame), int(marg_solver_mode), float(delta)))
 
     def ba_fix_linearization(self, which=None):
         out = np.zeros(self.nR * 8, dtype=np.float32)

@@ -22,6 +22,9 @@
 
 #define SOLVER_SVD 1
 #define SOLVER_ORTHOGONALIZE_SYSTEM 2
+#define SOLVER_ORTHOGONALIZE_POINTMARG 4
+#define SOLVER_ORTHOGONALIZE_FULL 8
+#define SOLVER_SVD_CUT7 16
 #define SOLVER_USE_GN 64
 #define SOLVER_FIX_LAMBDA 128
 #define SOLVER_ORTHOGONALIZE_X 256
@@ -38,6 +41,11 @@ struct BASolve
 	unsigned char* d_pmask; int capPm; double* d_margH; double* d_eblocks;   // marginalisation / energy scratch
 	long long* d_dbg;                                // DSO_B200_SOLVE_TIMING=1: clock64 stamps of ba_solve_kernel's phases
 	bool priors_set;
+	// non-default solver branches: "a frame with frameID 0 is in the window" (EnergyFunctional.cpp:688, :835), the solver
+	// mode / delta marginalizePointsF sees, scratch for HT_act, bT_act and the products of orthogonalize()
+	int haveFirstFrame, margSolverMode;
+	double solverModeDelta;                          // setting_solverModeDelta (given with the null spaces or the solver state)
+	double* d_work;
 };
 
 static int solve_state(dso_b200_ctx* ctx, BASolve** out)
@@ -47,6 +55,7 @@ static int solve_state(dso_b200_ctx* ctx, BASolve** out)
 	{
 		BASolve* S = new BASolve();
 		memset(S, 0, sizeof(*S));
+		S->haveFirstFrame = 1; S->margSolverMode = SOLVER_FIX_LAMBDA | SOLVER_ORTHOGONALIZE_X_LATER; S->solverModeDelta = 1e-5;   // util/settings.cpp:60-61
 		CK(cudaMalloc(&S->d_HM, (size_t)NMAX * NMAX * sizeof(double)));
 		CK(cudaMalloc(&S->d_bM, NMAX * sizeof(double)));
 		CK(cudaMalloc(&S->d_P, (size_t)NMAX * NMAX * sizeof(double)));
@@ -61,6 +70,12 @@ static int solve_state(dso_b200_ctx* ctx, BASolve** out)
 		W->S = S;
 	}
 	*out = W->S;
+	return 0;
+}
+
+static int nondefault_buffers(BASolve* S)
+{
+	if (!S->d_work) CK(cudaMalloc(&S->d_work, ((size_t)3 * NMAX * NMAX + 4 * NMAX) * sizeof(double)));   // Hact | bact | T (+ y) | spare
 	return 0;
 }
 
@@ -91,6 +106,7 @@ void ba_solve_destroy(BAWorkspace* W)
 	if (S->capR) cudaFree(S->d_which);
 	cudaFreeHost(S->h_x);
 	if (S->d_dbg) cudaFree(S->d_dbg);
+	if (S->d_work) cudaFree(S->d_work);
 	if (S->capPm) { cudaFree(S->d_pmask); cudaFree(S->d_eblocks); }
 	if (S->d_margH) cudaFree(S->d_margH);
 	delete S;
@@ -152,6 +168,8 @@ struct SolveArgs
 	const double* HM; const double* bM; const double* delta; const double* priorH; const double* priorD; const float* cDeltaF;
 	const double* P; const double* adHost; const double* adTarget;
 	double* x; float* xAd; double* HF; double* bF;
+	const double* Hpre; const double* bpre;          // SOLVER_ORTHOGONALIZE_SYSTEM: HT_act / bT_act, already projected (:832-851)
+	int assemble_only;                               // SOLVER_SVD: stop after HFinal / bFinal (written to HF / bF)
 	long long* dbg;
 };
 
@@ -192,7 +210,8 @@ __global__ void __launch_bounds__(SOLVE_NT) ba_solve_kernel(SolveArgs a)
 		for (int j = 0; j < N; j++) s = __dadd_rn(s, __dmul_rn(A[tid * LDH + j], dl[j]));
 		const double bMtop = __dadd_rn(a.bM[tid], s);
 		const double bl = a.haveL ? a.bL[tid] : __dmul_rn(a.priorH[tid], tid < CPARS ? (double)a.cDeltaF[tid] : a.priorD[tid]);
-		rhs[tid] = __dsub_rn(__dadd_rn(__dadd_rn(bl, bMtop), a.bA[tid]), a.bS[tid]);
+		rhs[tid] = a.bpre ? __dadd_rn(a.bpre[tid], bMtop)                                  // :844
+		                  : __dsub_rn(__dadd_rn(__dadd_rn(bl, bMtop), a.bA[tid]), a.bS[tid]);
 	}
 	STAMP(1);
 	// HFinal_top = HL_top + HM + HA_top; diagonal *= (1+lambda); -= H_sc * (1.0f/(1+lambda))  (:857-866); every thread
@@ -208,21 +227,28 @@ __global__ void __launch_bounds__(SOLVE_NT) ba_solve_kernel(SolveArgs a)
 			int i = (int)((float)e * invN);
 			i += ((i + 1) * N <= e) ? 1 : 0; i -= (i * N > e) ? 1 : 0;
 			const int j = e - i * N;
-			const double hl = a.haveL ? a.HL[e] : (i == j ? a.priorH[i] : 0.0);
-			double v = __dadd_rn(__dadd_rn(hl, A[i * LDH + j]), a.HA[e]);
-			if (i == j) v = __dmul_rn(v, damp);
-			v = __dsub_rn(v, __dmul_rn(a.HS[e], isc));
+			double v;
+			if (a.Hpre)
+			{
+				v = __dadd_rn(a.Hpre[e], A[i * LDH + j]);                                   // HT_act + HM (:843), damping (:849)
+				if (i == j) v = __dmul_rn(v, damp);
+			}
+			else
+			{
+				const double hl = a.haveL ? a.HL[e] : (i == j ? a.priorH[i] : 0.0);
+				v = __dadd_rn(__dadd_rn(hl, A[i * LDH + j]), a.HA[e]);
+				if (i == j) v = __dmul_rn(v, damp);
+				v = __dsub_rn(v, __dmul_rn(a.HS[e], isc));
+			}
 			A[i * LDH + j] = v;
 			if (a.HF) a.HF[e] = v;
 		}
 	}
 	__syncthreads();
 	STAMP(2);
-	if (tid < N)
-	{
-		if (a.bF) a.bF[tid] = rhs[tid];
-		sv[tid] = __ddiv_rn(1.0, sqrt(__dadd_rn(A[tid * LDH + tid], 10.0)));    // :905
-	}
+	if (tid < N && a.bF) a.bF[tid] = rhs[tid];
+	if (a.assemble_only) return;                     // uniform: the SVD branch continues in ba_svd_solve_kernel
+	if (tid < N) sv[tid] = __ddiv_rn(1.0, sqrt(__dadd_rn(A[tid * LDH + tid], 10.0)));    // :905
 	__syncthreads();
 	for (int e = tid; e < N * N; e += SOLVE_NT)
 	{
@@ -621,6 +647,234 @@ __global__ void __launch_bounds__(256) ba_resub_step_kernel(int nP, int nF, cons
 	}
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// Non-default solver branches (setting_solverMode bits 1, 2, 4, 8, 16; the default is 128 | 2048)
+// ---------------------------------------------------------------------------------------------------------
+// SOLVER_ORTHOGONALIZE_SYSTEM, EnergyFunctional.cpp:837-838: HT_act = HL_top + HA_top - H_sc, bT_act = bL_top + bA_top - b_sc
+__global__ void ba_assemble_act_kernel(int N, int haveL, const double* __restrict__ HL, const double* __restrict__ bL,
+                                       const double* __restrict__ HA, const double* __restrict__ bA,
+                                       const double* __restrict__ HS, const double* __restrict__ bS,
+                                       const double* __restrict__ priorH, const double* __restrict__ priorD, const float* __restrict__ cDeltaF,
+                                       double* Hact, double* bact)
+{
+	const int e = blockIdx.x * blockDim.x + threadIdx.x;
+	if (e < N * N)
+	{
+		const int i = e / N, j = e - i * N;
+		const double hl = haveL ? HL[e] : (i == j ? priorH[i] : 0.0);        // without linearised residuals H_L is the prior alone
+		Hact[e] = __dsub_rn(__dadd_rn(hl, HA[e]), HS[e]);
+	}
+	if (e < N)
+	{
+		const double bl = haveL ? bL[e] : __dmul_rn(priorH[e], e < CPARS ? (double)cDeltaF[e] : priorD[e]);
+		bact[e] = __dsub_rn(__dadd_rn(bl, bA[e]), bS[e]);
+	}
+}
+
+// EnergyFunctional::orthogonalize(VecX* b, MatXX* H), :741-792, with NNpiTS = P prepared by dso_b200_ba_set_nullspaces:
+// b -= P b; H -= (P H) P.  Stage 1: T = P H (row i per block) and y = P b (block N); stage 2: H -= T P, b -= y.
+__global__ void __launch_bounds__(128) ba_orth_stage1_kernel(int N, const double* __restrict__ P, const double* __restrict__ H,
+                                                             const double* __restrict__ b, double* T)
+{
+	const int i = blockIdx.x, j = threadIdx.x;
+	if (j >= N) return;
+	double s = 0.0;
+	if (i < N)
+	{
+		for (int q = 0; q < N; q++) s = __dadd_rn(s, __dmul_rn(P[(size_t)i * N + q], H[(size_t)q * N + j]));
+		T[(size_t)i * N + j] = s;
+	}
+	else
+	{
+		for (int q = 0; q < N; q++) s = __dadd_rn(s, __dmul_rn(P[(size_t)j * N + q], b[q]));
+		T[(size_t)N * N + j] = s;
+	}
+}
+__global__ void __launch_bounds__(128) ba_orth_stage2_kernel(int N, const double* __restrict__ P, double* H, double* b, const double* __restrict__ T)
+{
+	const int i = blockIdx.x, j = threadIdx.x;
+	if (j >= N) return;
+	if (i < N)
+	{
+		double s = 0.0;
+		for (int q = 0; q < N; q++) s = __dadd_rn(s, __dmul_rn(T[(size_t)i * N + q], P[(size_t)q * N + j]));
+		H[(size_t)i * N + j] = __dsub_rn(H[(size_t)i * N + j], s);
+	}
+	else if (b)
+		b[j] = __dsub_rn(b[j], T[(size_t)N * N + j]);
+}
+
+// marginalizePointsF with the orthogonalisation options: stage 1 = H, b alone (:681-682), stage 2 = the accumulation (:694-695)
+__global__ void ba_marg_accumulate_kernel(int N, double w, const double* __restrict__ H, const double* __restrict__ b, double* HM, double* bM)
+{
+	const int e = blockIdx.x * blockDim.x + threadIdx.x;
+	if (e < N * N) HM[e] = __dadd_rn(HM[e], __dmul_rn(w, H[e]));
+	if (e < N) bM[e] = __dadd_rn(bM[e], __dmul_rn(w, b[e]));
+}
+__global__ void ba_marg_diff_kernel(int N, const double* __restrict__ M, const double* __restrict__ Mb,
+                                    const double* __restrict__ Msc, const double* __restrict__ Mbsc, double* H, double* b)
+{
+	const int e = blockIdx.x * blockDim.x + threadIdx.x;
+	if (e < N * N) H[e] = __dsub_rn(M[e], Msc[e]);
+	if (e < N) b[e] = __dsub_rn(Mb[e], Mbsc[e]);
+}
+
+// SOLVER_SVD (+ SOLVER_SVD_CUT7), EnergyFunctional.cpp:870-900, on HFinal / bFinal left in global memory by ba_solve_kernel's
+// assemble-only mode: SVecI = 1/sqrt(diag), thin SVD of the scaled matrix, small singular values (and with CUT7 the last
+// seven of the decreasing order Eigen returns) dropped, x = SVecI V (U^T b ./ S).  The SVD is a one-sided Jacobi (Hestenes)
+// iteration like the oracle's, but with the N/2 disjoint column pairs of a round-robin schedule rotated at once, 16 lanes
+// per pair; the singular triplets agree with any other SVD up to rounding.  One CTA; A and V column-major in dynamic smem.
+#define SVD_NT 576
+__global__ void __launch_bounds__(SVD_NT) ba_svd_solve_kernel(int N, const double* __restrict__ HF, const double* __restrict__ bF,
+                                                             double delta, int cut7, double* x)
+{
+	extern __shared__ double sm[];
+	const int LD = N + 1;
+	double* A = sm;                       // [col * LD + row]
+	double* V = sm + (size_t)N * LD;
+	double* sv = V + (size_t)N * LD;      // N
+	double* bs = sv + N;                  // N
+	double* S = bs + N;                   // N
+	double* Ub = S + N;                   // N
+	int* ord = reinterpret_cast<int*>(Ub + N);
+	__shared__ unsigned long long s_off;
+	const int tid = threadIdx.x, grp = tid >> 4, l = tid & 15, npairs = N >> 1;
+	if (tid < N) sv[tid] = __ddiv_rn(1.0, sqrt(HF[(size_t)tid * N + tid]));
+	__syncthreads();
+	for (int e = tid; e < N * N; e += SVD_NT)
+	{
+		const int i = e / N, j = e - i * N;
+		A[j * LD + i] = __dmul_rn(__dmul_rn(sv[i], HF[e]), sv[j]);
+		V[j * LD + i] = (i == j) ? 1.0 : 0.0;
+	}
+	if (tid < N) bs[tid] = __dmul_rn(sv[tid], bF[tid]);
+	__syncthreads();
+	for (int sweep = 0; sweep < 60; sweep++)
+	{
+		if (tid == 0) s_off = 0ull;
+		__syncthreads();
+		for (int step = 0; step < N - 1; step++)
+		{
+			// circle method: player N-1 stays, the others rotate
+			int p = 0, q = 0;
+			const bool active = grp < npairs;
+			if (active)
+			{
+				const int m = N - 1;
+				const int a = grp == 0 ? N - 1 : (step + grp) % m;
+				const int b = grp == 0 ? step % m : (step - grp + m) % m;
+				p = min(a, b); q = max(a, b);
+			}
+			double alpha = 0.0, beta = 0.0, gamma = 0.0;
+			if (active)
+				for (int r = l; r < N; r += 16)
+				{
+					const double ap = A[p * LD + r], aq = A[q * LD + r];
+					alpha = fma(ap, ap, alpha); beta = fma(aq, aq, beta); gamma = fma(ap, aq, gamma);
+				}
+#pragma unroll
+			for (int o = 8; o > 0; o >>= 1)
+			{
+				alpha += __shfl_xor_sync(0xffffffffu, alpha, o);
+				beta += __shfl_xor_sync(0xffffffffu, beta, o);
+				gamma += __shfl_xor_sync(0xffffffffu, gamma, o);
+			}
+			if (active && fabs(gamma) > 1e-300)
+			{
+				const double nrm = sqrt(alpha * beta);
+				if (l == 0) atomicMax(&s_off, (unsigned long long)__double_as_longlong(fabs(gamma) / nrm));
+				if (fabs(gamma) > 1e-17 * nrm)
+				{
+					const double zeta = (beta - alpha) / (2.0 * gamma);
+					const double t = (zeta >= 0 ? 1.0 : -1.0) / (fabs(zeta) + sqrt(1.0 + zeta * zeta));
+					const double c = 1.0 / sqrt(1.0 + t * t), sn = c * t;
+					for (int r = l; r < N; r += 16)
+					{
+						const double ap = A[p * LD + r], aq = A[q * LD + r];
+						A[p * LD + r] = c * ap - sn * aq; A[q * LD + r] = sn * ap + c * aq;
+						const double vp = V[p * LD + r], vq = V[q * LD + r];
+						V[p * LD + r] = c * vp - sn * vq; V[q * LD + r] = sn * vp + c * vq;
+					}
+				}
+			}
+			__syncthreads();
+		}
+		if (__longlong_as_double((long long)s_off) < 1e-15) break;      // uniform: read after the step's barrier
+		__syncthreads();
+	}
+	// singular values = column norms, U = normalised columns (kept in A)
+	if (tid < N)
+	{
+		double n2 = 0.0;
+		for (int r = 0; r < N; r++) n2 = fma(A[tid * LD + r], A[tid * LD + r], n2);
+		S[tid] = sqrt(n2);
+	}
+	__syncthreads();
+	if (tid < N)
+	{
+		// position of column tid in the decreasing order (ties by index, like a stable sort)
+		const double v = S[tid];
+		int rank = 0;
+		for (int j = 0; j < N; j++) rank += (S[j] > v || (S[j] == v && j < tid)) ? 1 : 0;
+		ord[rank] = tid;
+	}
+	__syncthreads();
+	if (tid < N)
+	{
+		const int c = ord[tid];
+		const double Sc = S[c];
+		double maxSv = 0.0;
+		for (int j = 0; j < N; j++) maxSv = fmax(maxSv, S[j]);
+		double t = 0.0;
+		for (int r = 0; r < N; r++) t += (Sc > 0 ? A[c * LD + r] / Sc : 0.0) * bs[r];      // U^T b
+		if (Sc < delta * maxSv) t = 0.0;                                                   // :886-887
+		if (cut7 && tid >= N - 7) t = 0.0;                                                 // :889-890
+		else t /= Sc;
+		Ub[tid] = t;
+	}
+	__syncthreads();
+	if (tid < N)
+	{
+		double t = 0.0;
+		for (int j = 0; j < N; j++) t += V[ord[j] * LD + tid] * Ub[j];
+		x[tid] = sv[tid] * t;
+	}
+}
+
+// what follows the solve in solveSystemF when the solve itself ran elsewhere: orthogonalize(&x, 0) (:910-914) and the xAd of
+// resubstituteF_MT (:283-293), exactly as at the end of ba_solve_kernel
+__global__ void __launch_bounds__(512) ba_solve_tail_kernel(SolveArgs a)
+{
+	__shared__ double xv[NMAX];
+	const int tid = threadIdx.x, N = 8 * a.nF + CPARS;
+	if (tid < N) xv[tid] = a.x[tid];
+	__syncthreads();
+	if (a.orth)
+	{
+		double s = 0.0;
+		if (tid < N) for (int j = 0; j < N; j++) s = __dadd_rn(s, __dmul_rn(a.P[(size_t)tid * N + j], xv[j]));
+		__syncthreads();
+		if (tid < N) { xv[tid] = __dsub_rn(xv[tid], s); a.x[tid] = xv[tid]; }
+		__syncthreads();
+	}
+	for (int e = tid; e < a.nF * a.nF * 8; e += 512)
+	{
+		const int j = e & 7, ht = e >> 3, h = ht / a.nF, t = ht - h * a.nF;
+		const double* AH = a.adHost + (size_t)(h + a.nF * t) * 64;
+		const double* AT_ = a.adTarget + (size_t)(h + a.nF * t) * 64;
+		float ph[8], pt[8];
+#pragma unroll
+		for (int i = 0; i < 8; i++)
+		{
+			ph[i] = fmul((float)xv[CPARS + 8 * h + i], (float)AH[i * 8 + j]);
+			pt[i] = fmul((float)xv[CPARS + 8 * t + i], (float)AT_[i * 8 + j]);
+		}
+		const float sh = fadd(fadd(fadd(ph[0], ph[1]), fadd(ph[2], ph[3])), fadd(fadd(ph[4], ph[5]), fadd(ph[6], ph[7])));
+		const float st = fadd(fadd(fadd(pt[0], pt[1]), fadd(pt[2], pt[3])), fadd(fadd(pt[4], pt[5]), fadd(pt[6], pt[7])));
+		a.xAd[e] = fadd(sh, st);
+	}
+}
+
 // =========================================================================================================
 // host API
 // =========================================================================================================
@@ -743,6 +997,23 @@ extern "C" int dso_b200_ba_set_nullspaces(dso_b200_ctx* ctx, const double* ns, i
 	CK(cudaMemcpyAsync(S->d_P, PS.data(), (size_t)N * N * sizeof(double), cudaMemcpyHostToDevice, ctx->ba_stream));
 	CK(cudaStreamSynchronize(ctx->ba_stream));
 	S->haveP = true;
+	S->solverModeDelta = solverModeDelta;
+	return 0;
+}
+
+// The global state the non-default solver branches read besides setting_solverMode: whether a frame with frameID 0 is
+// in the window ("haveFirstFrame", EnergyFunctional.cpp:686-688, :833-835) and the solver mode / delta marginalizePointsF
+// sees (util/settings.cpp:60-61).  Defaults: first frame present, 128 | 2048, 1e-5.
+extern "C" int dso_b200_ba_set_solver_state(dso_b200_ctx* ctx, int haveFirstFrame, int margSolverMode, double solverModeDelta)
+{
+	ARG_CHECK(ctx && ctx->ba, "null context");
+	BASolve* S;
+	int rc = solve_state(ctx, &S);
+	if (rc) return rc;
+	S->haveFirstFrame = haveFirstFrame ? 1 : 0;
+	S->margSolverMode = margSolverMode;
+	S->solverModeDelta = solverModeDelta;
+	ba_graphs_invalidate(ctx->ba);
 	return 0;
 }
 
@@ -828,8 +1099,45 @@ static int enqueue_solve(dso_b200_ctx* ctx, BASolve* S, int iteration, double la
 	a.P = S->d_P; a.adHost = W->d_adHost; a.adTarget = W->d_adTarget;
 	a.x = S->d_x; a.xAd = S->d_xAd; a.HF = debug ? S->d_HF : nullptr; a.bF = debug ? S->d_bF : nullptr;
 	a.dbg = S->d_dbg;
-	if (S->d_dbg) CK(cudaMemsetAsync(S->d_dbg, 0, 16 * sizeof(long long), ctx->ba_stream));
-	ba_solve_kernel<<<1, SOLVE_NT, 0, ctx->ba_stream>>>(a);
+	a.Hpre = nullptr; a.bpre = nullptr; a.assemble_only = 0;
+	const int N = 8 * W->P.nF + CPARS;
+	cudaStream_t s = ctx->ba_stream;
+	if (solverMode & (SOLVER_SVD | SOLVER_ORTHOGONALIZE_SYSTEM))
+	{
+		if ((rc = nondefault_buffers(S))) return rc;
+		BA_CHECK(!(solverMode & SOLVER_ORTHOGONALIZE_SYSTEM) || S->haveFirstFrame || S->haveP,
+		         "SOLVER_ORTHOGONALIZE_SYSTEM without the first frame needs dso_b200_ba_set_nullspaces");
+	}
+	if (solverMode & SOLVER_ORTHOGONALIZE_SYSTEM)
+	{
+		// :832-851: HT_act / bT_act, projected off the null spaces unless the gauge-fixing first frame is in the window
+		double* Hact = S->d_work; double* bact = Hact + (size_t)NMAX * NMAX; double* T = bact + NMAX;
+		ba_assemble_act_kernel<<<(N * N + 255) / 256, 256, 0, s>>>(N, a.haveL, W->d_HL, W->d_bL, W->d_HA, W->d_bA, W->d_HS, W->d_bS,
+		                                                          W->d_priorH, W->d_priorD, W->d_cDeltaF, Hact, bact);
+		LAUNCHED(ctx, 1);
+		if (!S->haveFirstFrame)
+		{
+			ba_orth_stage1_kernel<<<N + 1, 128, 0, s>>>(N, S->d_P, Hact, bact, T);
+			ba_orth_stage2_kernel<<<N + 1, 128, 0, s>>>(N, S->d_P, Hact, bact, T);
+			LAUNCHED(ctx, 2);
+		}
+		a.Hpre = Hact; a.bpre = bact;
+	}
+	if (S->d_dbg) CK(cudaMemsetAsync(S->d_dbg, 0, 16 * sizeof(long long), s));
+	if (solverMode & SOLVER_SVD)
+	{
+		// :870-900: the assembled system goes through global memory to the SVD kernel; orthogonalize(x) and xAd follow
+		a.assemble_only = 1; a.HF = S->d_HF; a.bF = S->d_bF;
+		ba_solve_kernel<<<1, SOLVE_NT, 0, s>>>(a);
+		const size_t smem = ((size_t)2 * N * (N + 1) + 4 * N) * sizeof(double) + (size_t)N * sizeof(int);
+		static bool attr[64] = { false };
+		if (!attr[ctx->device & 63]) { CK(cudaFuncSetAttribute(ba_svd_solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024)); attr[ctx->device & 63] = true; }
+		ba_svd_solve_kernel<<<1, SVD_NT, smem, s>>>(N, S->d_HF, S->d_bF, S->solverModeDelta, (solverMode & SOLVER_SVD_CUT7) ? 1 : 0, S->d_x);
+		ba_solve_tail_kernel<<<1, 512, 0, s>>>(a);
+		LAUNCHED(ctx, 2);
+	}
+	else
+		ba_solve_kernel<<<1, SOLVE_NT, 0, s>>>(a);
 	if (withStep)
 	{
 		const int nb = (W->P.nP + 255) / 256;
@@ -851,8 +1159,6 @@ extern "C" int dso_b200_ba_solve(dso_b200_ctx* ctx, int iteration, double lambda
 {
 	int rc = ba_check_ready(ctx, __func__);
 	if (rc) return rc;
-	ARG_CHECK(!(solverMode & (SOLVER_SVD | SOLVER_ORTHOGONALIZE_SYSTEM)),
-	          "the SOLVER_SVD and SOLVER_ORTHOGONALIZE_SYSTEM branches of solveSystemF are not implemented (default mode is 128|2048)");
 	CK(cudaSetDevice(ctx->device));
 	BAWorkspace* W = ctx->ba;
 	BASolve* S;
@@ -884,7 +1190,6 @@ extern "C" int dso_b200_ba_iteration(dso_b200_ctx* ctx, int iteration, double la
 {
 	int rc = ba_check_ready(ctx, __func__);
 	if (rc) return rc;
-	ARG_CHECK(!(solverMode & (SOLVER_SVD | SOLVER_ORTHOGONALIZE_SYSTEM)), "solver mode not implemented");
 	CK(cudaSetDevice(ctx->device));
 	BAWorkspace* W = ctx->ba;
 	BASolve* S;
@@ -894,7 +1199,7 @@ extern "C" int dso_b200_ba_iteration(dso_b200_ctx* ctx, int iteration, double la
 	const int N = 8 * W->P.nF + CPARS;
 	// by-value kernel arguments of the captured sequence: orthogonalisation on/off, lambda, stepfacD, solver mode, L path
 	const int orth = ((solverMode & SOLVER_ORTHOGONALIZE_X) || (iteration >= 2 && (solverMode & SOLVER_ORTHOGONALIZE_X_LATER))) ? 1 : 0;
-	const BAGraphKey key = { lambda, stepfacD, solverMode, W->nLin != 0 ? 1 : 0, S->haveP ? 1 : 0, S->d_dbg ? 1 : 0 };
+	const BAGraphKey key = { lambda, stepfacD, solverMode | (S->haveFirstFrame << 20), W->nLin != 0 ? 1 : 0, S->haveP ? 1 : 0, S->d_dbg ? 1 : 0 };
 	rc = ba_run_graphed(ctx, W->g_iter[orth], key, [&]() -> int {
 		int r;
 		if ((r = ba_enqueue_linearize(ctx, true, true))) return r;        // linearize + applyRes in one kernel
@@ -1121,8 +1426,36 @@ extern "C" int dso_b200_ba_marginalize_points(dso_b200_ctx* ctx, const unsigned 
 	if ((rc = ba_enqueue_top(ctx, 2, S->d_pmask))) return rc;      // accSSE_top_A->addPoint<2> + stitchDouble -> d_HL, d_bL
 	if ((rc = ba_enqueue_schur(ctx, S->d_pmask))) return rc;       // accSSE_bot->addPoint(p, false) + stitchDouble -> d_HS, d_bS
 	double* dH = S->d_margH; double* db = S->d_margH + (size_t)NMAX * NMAX;
-	ba_marg_combine_kernel<<<(N * N + 255) / 256, 256, 0, s>>>(N, margWeightFac, W->d_HL, W->d_bL, W->d_HS, W->d_bS, dH, db, S->d_HM, S->d_bM);
-	LAUNCHED(ctx, 1);
+	const int orthPt = (S->margSolverMode & SOLVER_ORTHOGONALIZE_POINTMARG) && !S->haveFirstFrame, orthFull = S->margSolverMode & SOLVER_ORTHOGONALIZE_FULL;
+	if (!orthPt && !orthFull)
+	{
+		ba_marg_combine_kernel<<<(N * N + 255) / 256, 256, 0, s>>>(N, margWeightFac, W->d_HL, W->d_bL, W->d_HS, W->d_bS, dH, db, S->d_HM, S->d_bM);
+		LAUNCHED(ctx, 1);
+	}
+	else
+	{
+		// :681-699 with SOLVER_ORTHOGONALIZE_POINTMARG (H, b of the marginalised points projected, first frame gone) and / or
+		// SOLVER_ORTHOGONALIZE_FULL (the accumulated prior projected)
+		BA_CHECK(S->haveP, "the orthogonalising marginalisation modes need dso_b200_ba_set_nullspaces");
+		if ((rc = nondefault_buffers(S))) return rc;
+		double* T = S->d_work;
+		ba_marg_diff_kernel<<<(N * N + 255) / 256, 256, 0, s>>>(N, W->d_HL, W->d_bL, W->d_HS, W->d_bS, dH, db);
+		LAUNCHED(ctx, 1);
+		if (orthPt)
+		{
+			ba_orth_stage1_kernel<<<N + 1, 128, 0, s>>>(N, S->d_P, dH, db, T);
+			ba_orth_stage2_kernel<<<N + 1, 128, 0, s>>>(N, S->d_P, dH, db, T);
+			LAUNCHED(ctx, 2);
+		}
+		ba_marg_accumulate_kernel<<<(N * N + 255) / 256, 256, 0, s>>>(N, margWeightFac, dH, db, S->d_HM, S->d_bM);
+		LAUNCHED(ctx, 1);
+		if (orthFull)
+		{
+			ba_orth_stage1_kernel<<<N + 1, 128, 0, s>>>(N, S->d_P, S->d_HM, S->d_bM, T);
+			ba_orth_stage2_kernel<<<N + 1, 128, 0, s>>>(N, S->d_P, S->d_HM, S->d_bM, T);
+			LAUNCHED(ctx, 2);
+		}
+	}
 	CK(cudaGetLastError());
 	if (H_out) CK(cudaMemcpyAsync(H_out, dH, (size_t)N * N * sizeof(double), cudaMemcpyDeviceToHost, s));
 	if (b_out) CK(cudaMemcpyAsync(b_out, db, N * sizeof(double), cudaMemcpyDeviceToHost, s));

@@ -371,6 +371,11 @@ int dso_b200_ba_set_priors(dso_b200_ctx* ctx, const double* cPrior4, const doubl
  * EnergyFunctional::orthogonalize (EnergyFunctional.cpp:741-785; solverModeDelta = setting_solverModeDelta) once, on the
  * host, and keeps it on the device.  n = 0 removes it. */
 int dso_b200_ba_set_nullspaces(dso_b200_ctx* ctx, const double* nullspaces, int n, double solverModeDelta);
+/* The global state the non-default solver branches read besides the solverMode argument: haveFirstFrame = "a frame with
+ * frameID 0 is in the window" (EnergyFunctional.cpp:686-688, :833-835; decides whether SOLVER_ORTHOGONALIZE_SYSTEM /
+ * _POINTMARG project at all), margSolverMode = setting_solverMode as dso_b200_ba_marginalize_points sees it, and
+ * setting_solverModeDelta (util/settings.cpp:60-61).  Defaults: 1, 128|2048, 1e-5. */
+int dso_b200_ba_set_solver_state(dso_b200_ctx* ctx, int haveFirstFrame, int margSolverMode, double solverModeDelta);
 /* EFResidual::fixLinearizationF (EnergyFunctionalStructs.cpp:89-115) on the active residuals flagged in `which`
  * (nR bytes, NULL = every active residual): res_toZeroF = resF - J*delta, isLinearized = true.
  * res_toZeroF_out: nR*8 floats or NULL. */
@@ -383,8 +388,10 @@ int dso_b200_ba_accumulate_L(dso_b200_ctx* ctx, double* H_L, double* b_L, int* r
 /* EnergyFunctional::solveSystemF (EnergyFunctional.cpp:802-924) after linearize + applyRes: the three accumulate calls,
  * HFinal_top / bFinal_top, damping, the diagonally scaled LDL^T solve, orthogonalize(&x) when solverMode asks for it
  * (and null spaces were set), and resubstituteF_MT (EnergyFunctional.cpp:276-330).  solverMode = setting_solverMode
- * (util/settings.h:35-46; the reference default is 128|2048); the SOLVER_SVD and SOLVER_ORTHOGONALIZE_SYSTEM branches
- * return DSO_B200_E_ARG.  x_out: N doubles (= lastX; frame steps are -x segments, HCalib->step = -x.head<4>()),
+ * (util/settings.h:35-46; the reference default is 128|2048).  The non-default branches are there too:
+ * SOLVER_ORTHOGONALIZE_SYSTEM (:832-851: HT_act / bT_act projected off the null spaces unless the first frame is in the
+ * window, see dso_b200_ba_set_solver_state) and SOLVER_SVD / SOLVER_SVD_CUT7 (:870-900: one-sided Jacobi SVD of the scaled
+ * system on the device; agrees with Eigen's JacobiSVD up to rounding of the singular triplets).  x_out: N doubles (= lastX; frame steps are -x segments, HCalib->step = -x.head<4>()),
  * pointStep_out: nP floats (PointHessian::step), both may be NULL (results stay on the device);
  * HFinal_out/bFinal_out: the system that was solved, for inspection (may be NULL). */
 int dso_b200_ba_solve(dso_b200_ctx* ctx, int iteration, double lambda, int solverMode, double* x_out, float* pointStep_out,
@@ -407,7 +414,8 @@ int dso_b200_ba_iteration(dso_b200_ctx* ctx, int iteration, double lambda, int s
  * both stitched, H = M - Msc, b = Mb - Mbsc, and on the device HM += margWeightFac * H, bM += margWeightFac * b.  H_out, b_out
  * (may be NULL) return H and b, resInM the residual count, idepth_hessian_out (nP, may be NULL) PointHessian::idepth_hessian.
  * The structural part (removePoint, makeIDX, connectivityMap) stays with the caller, who re-uploads the window afterwards.
- * The SOLVER_ORTHOGONALIZE_POINTMARG / _FULL variants (not the default solver mode) are not implemented. */
+ * SOLVER_ORTHOGONALIZE_POINTMARG (H, b projected off the null spaces when the first frame is gone, :684-692) and
+ * SOLVER_ORTHOGONALIZE_FULL (the accumulated HM, bM projected, :698-699) follow the mode given to dso_b200_ba_set_solver_state. */
 int dso_b200_ba_marginalize_points(dso_b200_ctx* ctx, const unsigned char* point_flags, float idepthFixPriorMargFac,
                                    double margWeightFac, double* H_out, double* b_out, int* resInM, float* idepth_hessian_out);
 /* The marginalisation prior as it stands on the device (after dso_b200_ba_set_priors and any marginalisation). */

@@ -149,3 +149,72 @@ def test_marginalize_points_and_energies(pkg, oracle, window_small):
     _check_system(mg["HM"], mg["bM"], mo["HM"], mo["bM"])
     assert np.allclose(mg["HM"], inp[4] + 0.25 * mg["H"], rtol=0, atol=1e-9 * np.abs(mg["HM"]).max())
     ctx.close()
+
+
+from test_oracle_vs_reference import (_no_first_frame_inputs, SOLVER_DEFAULT, SOLVER_SVD, SOLVER_SVD_CUT7, SOLVER_ORTH_SYSTEM,
+                                      SOLVER_ORTH_POINTMARG, SOLVER_ORTH_FULL)
+
+
+@pytest.mark.parametrize("mode,first", [(SOLVER_DEFAULT | SOLVER_ORTH_SYSTEM, False), (SOLVER_DEFAULT | SOLVER_ORTH_SYSTEM, True),
+                                        (SOLVER_DEFAULT | SOLVER_SVD, True), (SOLVER_DEFAULT | SOLVER_SVD | SOLVER_SVD_CUT7, True),
+                                        (SOLVER_DEFAULT | SOLVER_SVD | SOLVER_ORTH_SYSTEM, False)])
+def test_solve_non_default_branches(pkg, oracle, window_small, mode, first):
+    """SOLVER_ORTHOGONALIZE_SYSTEM / SOLVER_SVD / SOLVER_SVD_CUT7 of solveSystemF (EnergyFunctional.cpp:832-900) on the device
+    vs the oracle (pinned against the reference build in test_oracle_vs_reference.py::test_solve_system_non_default_branches).
+    HFinal / bFinal to the H_A / H_sc bar; x to the first-order image of the system difference, as in test_solve_parity."""
+    W = window_small
+    pyr = [oracle.make_images(img, 1)[0][0] for img in W.images]
+    inp = _solve_inputs(W) if first else _no_first_frame_inputs(W, pyr)
+    B, ctx = _setup(pkg, oracle, W)
+    B.linearize(); ctx.ba_linearize()
+    B.apply_res(); ctx.ba_apply_res()
+    B.set_priors(*inp[:6]); B.set_nullspaces(inp[6]); B.set_solver_state(have_first_frame=first)
+    ctx.ba_set_priors(*inp[:6]); ctx.ba_set_nullspaces(inp[6]); ctx.ba_set_solver_state(have_first_frame=first)
+    so = B.solve(2, 0.1, solver_mode=mode)
+    sg = ctx.ba_solve(2, 0.1, solver_mode=mode, debug=True)
+    _check_system(sg["HFinal"], sg["bFinal"], so["HFinal"], so["bFinal"])
+    assert np.isfinite(sg["x"]).all()
+    scale = np.abs(so["x"]).max()
+    assert np.abs(sg["x"] - so["x"]).max() <= 2e-3 * scale
+    if mode & SOLVER_SVD:
+        # the device SVD on the device's own system against numpy's: same truncated pseudo-inverse
+        H, b = sg["HFinal"], sg["bFinal"]
+        sv = 1.0 / np.sqrt(np.diag(H))
+        U, S, Vt = np.linalg.svd(sv[:, None] * H * sv[None, :])
+        Ub = U.T @ (sv * b)
+        N = len(b)
+        for i in range(N):
+            if S[i] < 1e-5 * S.max():
+                Ub[i] = 0
+            if (mode & SOLVER_SVD_CUT7) and i >= N - 7:
+                Ub[i] = 0
+            else:
+                Ub[i] /= S[i]
+        xn = sv * (Vt.T @ Ub)
+        if first:          # without orthogonalize(x): iteration 2 with X_LATER projects x afterwards, so compare before it
+            sg0 = ctx.ba_solve(0, 0.1, solver_mode=mode, debug=True)
+            assert np.abs(sg0["x"] - xn).max() <= 1e-9 * np.abs(xn).max()
+    good = np.abs(so["step"]) > 1e-3 * np.abs(so["step"]).max()
+    assert np.abs(sg["step"] - so["step"])[good].max() <= 1e-2 * np.abs(so["step"]).max()
+    ctx.close()
+
+
+@pytest.mark.parametrize("mode", [SOLVER_DEFAULT | SOLVER_ORTH_POINTMARG, SOLVER_DEFAULT | SOLVER_ORTH_FULL,
+                                  SOLVER_DEFAULT | SOLVER_ORTH_POINTMARG | SOLVER_ORTH_FULL])
+def test_marginalize_points_orthogonalize_branches(pkg, oracle, window_small, mode):
+    """SOLVER_ORTHOGONALIZE_POINTMARG / _FULL of marginalizePointsF (EnergyFunctional.cpp:684-699) on the device vs the oracle"""
+    W = window_small
+    inp = _solve_inputs(W)
+    B, ctx = _setup(pkg, oracle, W)
+    pflags = (np.arange(W.nP) % 3 == 1).astype(np.uint8)
+    rflags = pflags[W.res_point]
+    B.linearize(); ctx.ba_linearize()
+    B.apply_res(); ctx.ba_apply_res()
+    B.fix_linearization(rflags); ctx.ba_fix_linearization(rflags)
+    B.set_priors(*inp[:6]); B.set_nullspaces(inp[6]); B.set_solver_state(have_first_frame=False, marg_solver_mode=mode)
+    ctx.ba_set_priors(*inp[:6]); ctx.ba_set_nullspaces(inp[6]); ctx.ba_set_solver_state(have_first_frame=False, marg_solver_mode=mode)
+    mo, mg = B.marginalize_points(pflags), ctx.ba_marginalize_points(pflags)
+    assert mo["resInM"] == mg["resInM"] > 100
+    _check_system(mg["H"], mg["b"], mo["H"], mo["b"])
+    _check_system(mg["HM"], mg["bM"], mo["HM"], mo["bM"])
+    ctx.close()
