@@ -246,6 +246,10 @@ public:
 	void setPriors(const double* cPrior4, const double* framePrior8, const MatXX& HM, const VecX& bM)
 	{ DSO_B200_CHECK(dso_b200_ba_set_priors(dev->ctx, cPrior4, framePrior8, 0, 0, HM.m.data(), bM.v.data())); }
 	void setNullspaces(const double* ns, int n, double setting_solverModeDelta) { DSO_B200_CHECK(dso_b200_ba_set_nullspaces(dev->ctx, ns, n, setting_solverModeDelta)); }
+	// the globals the non-default solver branches read: "for(EFFrame* f : frames) if(f->frameID==0) haveFirstFrame=true"
+	// (EnergyFunctional.cpp:686-688, :833-835), setting_solverMode as marginalizePointsF sees it, setting_solverModeDelta
+	void setSolverState(bool haveFirstFrame, int setting_solverMode, double setting_solverModeDelta)
+	{ DSO_B200_CHECK(dso_b200_ba_set_solver_state(dev->ctx, haveFirstFrame ? 1 : 0, setting_solverMode, setting_solverModeDelta)); }
 
 	// void solveSystemF(int iteration, double lambda, CalibHessian* HCalib)   EnergyFunctional.cpp:802; lastX as in :921,
 	// frame / calibration steps are -x segments (:281-288); point steps stay on the device (doStepFromBackupPoints)
