@@ -613,6 +613,7 @@ def run_ours(args):
         return ctx.track_frame(0, nfr + 1, pinned[k], W.w, W.h, levels, wl["inits"][k], a, b, coarsest)[0]
 
     inits64 = [np.ascontiguousarray(x, dtype=np.float64).reshape(-1) for x in wl["inits"]]
+    inits64_ptr = [x.ctypes.data for x in inits64]         # addresses taken once: the arrays stay alive in inits64
     res_pipe = pkg.capi.TrackResult()
 
     def step_pipe(i, first=False):
@@ -622,7 +623,7 @@ def run_ours(args):
             ctx.make_images_async(nfr + 2 + i % RING, pinned[i % nfr], W.w, W.h, levels)
         a, b = wl["affs"][i % nfr]
         # one C-ABI call: enqueue the tracker, enqueue upload + pyramid of frame i+1 (runs while the GPU tracks), fetch
-        return ctx.track_and_prefetch(0, nfr + 2 + i % RING, inits64[i % nfr], a, b, coarsest,
+        return ctx.track_and_prefetch(0, nfr + 2 + i % RING, inits64_ptr[i % nfr], a, b, coarsest,
                                       nfr + 2 + (i + 1) % RING, pinned[(i + 1) % nfr], W.w, W.h, levels, out=res_pipe)
 
     def barrier():

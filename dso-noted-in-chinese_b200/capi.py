@@ -372,12 +372,14 @@ class Context:
 
     def track_and_prefetch(self, trk, slot, pose12, a, b, coarsest, next_slot, next_color_ptr, w, h, levels, out=None,
                            new_exposure=1.0):
-        """one hypothesis; pose12: contiguous float64 array of 12 kept alive by the caller for the call; out: a TrackResult
-        to fill (re-used by a caller that tracks in a loop)"""
+        """one hypothesis; pose12: contiguous float64 array of 12 kept alive by the caller for the call (or its address as an
+        int); out: a TrackResult to fill (re-used by a caller that tracks in a loop)"""
         if out is None:
             out = TrackResult()
-        self._check(self.L.dso_b200_track_and_prefetch(self.h, trk, slot, 1, pose12.ctypes.data, a, b, new_exposure, coarsest, None,
-                                                       next_slot, next_color_ptr, w, h, levels, C.addressof(out)))
+        rc = self.L.dso_b200_track_and_prefetch(self.h, trk, slot, 1, pose12 if isinstance(pose12, int) else pose12.ctypes.data, a, b,
+                                                new_exposure, coarsest, None, next_slot, next_color_ptr, w, h, levels, C.addressof(out))
+        if rc:
+            self._check(rc)
         return out
 
     def track_fetch(self, trk, n=1):
