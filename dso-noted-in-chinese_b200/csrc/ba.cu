@@ -966,22 +966,32 @@ __global__ void __launch_bounds__(256) ba_schur_accum_kernel(int nF, const int* 
 	__shared__ float sa[CHUNK_P][MAXF * 8];     // JpJdF by target slot (0 when inactive)
 	__shared__ float swa[CHUNK_P][MAXF * 8];    // HdiF * JpJdF
 	__shared__ float sh[CHUNK_P][8];            // Hcd[4], w, w*bdSum, w*Hcd handled on the fly
+	__shared__ unsigned char s_t1[MAXF * MAXF], s_t2[MAXF * MAXF];   // pair index -> (t1, t2): no run-time divisions per entry
+	static_assert(CHUNK_P * 16 == 256, "16 threads per point below");
 	const int chunk = blockIdx.x, tid = threadIdx.x;
 	const int start = pc_start[chunk], cnt = pc_cnt[chunk];
 	for (int i = tid; i < CHUNK_P * MAXF * 8; i += 256) { (&sa[0][0])[i] = 0.f; (&swa[0][0])[i] = 0.f; }
+	if (tid < nF * nF) { s_t1[tid] = (unsigned char)(tid / nF); s_t2[tid] = (unsigned char)(tid % nF); }
 	__syncthreads();
-	if (tid < cnt)
 	{
-		const int p = start + tid;
-		const float w = HdiF[p];
-		sh[tid][0] = Hcd[4 * p]; sh[tid][1] = Hcd[4 * p + 1]; sh[tid][2] = Hcd[4 * p + 2]; sh[tid][3] = Hcd[4 * p + 3];
-		sh[tid][4] = w; sh[tid][5] = fmul(w, bdSumF[p]);
-		for (int r = res_begin[p]; r < res_begin[p + 1]; r++)
+		// 16 threads per point: two residuals at a time, one JpJdF entry each (the serial per-point loop was a chain of
+		// dependent global loads: begin -> flag -> target -> eight values, residual after residual)
+		const int pl = tid >> 4, sub = tid & 15, k = sub & 7;
+		if (pl < cnt)
 		{
-			if (!isAct[r]) continue;
-			const int t = rtarget[r];
-#pragma unroll
-			for (int k = 0; k < 8; k++) { const float a = JpJdF[8 * (size_t)r + k]; sa[tid][t * 8 + k] = a; swa[tid][t * 8 + k] = fmul(w, a); }
+			const int p = start + pl;
+			const float w = HdiF[p];
+			if (sub < 4) sh[pl][sub] = Hcd[4 * p + sub];
+			else if (sub == 4) sh[pl][4] = w;
+			else if (sub == 5) sh[pl][5] = fmul(w, bdSumF[p]);
+			const int r1 = res_begin[p + 1];
+			for (int r = res_begin[p] + (sub >> 3); r < r1; r += 2)
+			{
+				if (!isAct[r]) continue;
+				const int t = rtarget[r];
+				const float a = JpJdF[8 * (size_t)r + k];
+				sa[pl][t * 8 + k] = a; swa[pl][t * 8 + k] = fmul(w, a);
+			}
 		}
 	}
 	__syncthreads();
@@ -992,12 +1002,12 @@ __global__ void __launch_bounds__(256) ba_schur_accum_kernel(int nF, const int* 
 		float acc = 0.f;
 		if (e < nD)
 		{
-			const int t1 = e / (nF * 64), t2 = (e / 64) % nF, i = (e % 64) / 8, j = e % 8;
+			const int t1 = s_t1[e >> 6], t2 = s_t2[e >> 6], i = (e >> 3) & 7, j = e & 7;
 			for (int p = 0; p < cnt; p++) acc = fadd(acc, fmul(sa[p][t2 * 8 + j], swa[p][t1 * 8 + i]));       // A += (w L) R^T
 		}
 		else if (e < nD + nE)
 		{
-			const int o = e - nD, t = o / 32, i = (o % 32) / 4, c = o % 4;
+			const int o = e - nD, t = o >> 5, i = (o >> 2) & 7, c = o & 3;
 			for (int p = 0; p < cnt; p++) acc = fadd(acc, fmul(sh[p][c], swa[p][t * 8 + i]));                   // accE: L = JpJdF, R = Hcd
 		}
 		else if (e < nD + nE + nEB)
@@ -1007,7 +1017,7 @@ __global__ void __launch_bounds__(256) ba_schur_accum_kernel(int nF, const int* 
 		}
 		else if (e < nD + nE + nEB + 16)
 		{
-			const int o = e - nD - nE - nEB, i = o / 4, j = o % 4;
+			const int o = e - nD - nE - nEB, i = o >> 2, j = o & 3;
 			for (int p = 0; p < cnt; p++) acc = fadd(acc, fmul(sh[p][j], fmul(sh[p][4], sh[p][i])));            // accHcc: (w Hcd) Hcd^T
 		}
 		else
