@@ -611,12 +611,16 @@ __global__ void __launch_bounds__(128) ba_accum_top_kernel(const int* __restrict
 struct SchurPrepOut { float* HdiF; float* bdSumF; float* idh; float* HcdSum; const float* priorF; const float* deltaF; };
 __device__ __forceinline__ void schur_prep_point(int p, const int* __restrict__ res_begin, const unsigned char* __restrict__ isAct,
                                                  float HddA, float bdA, const float* hcA, float HddL, float bdL, const float* hcL,
-                                                 const SchurPrepOut& o)
+                                                 const SchurPrepOut& o, int ngood_known = -1)
 {
 #pragma unroll
 	for (int k = 0; k < 4; k++) o.HcdSum[4 * p + k] = fadd(hcA[k], hcL[k]);   // Hcd_accAF + Hcd_accLF (:62)
-	int ngood = 0;
-	for (int r = res_begin[p]; r < res_begin[p + 1]; r++) ngood += isAct[r] ? 1 : 0;
+	int ngood = ngood_known;
+	if (ngood < 0)
+	{
+		ngood = 0;
+		for (int r = res_begin[p]; r < res_begin[p + 1]; r++) ngood += isAct[r] ? 1 : 0;
+	}
 	if (ngood == 0) { o.HdiF[p] = 0.f; o.bdSumF[p] = 0.f; o.idh[p] = 0.f; return; }
 	float H = fadd(fadd(HddA, HddL), o.priorF[p]);   // Hdd_accAF + Hdd_accLF + priorF
 	if (H < 1e-10) H = 1e-10;
@@ -639,6 +643,7 @@ __global__ void ba_point_sums_kernel(int nP, const int* __restrict__ res_begin, 
 	if (p >= nP) return;
 	if (mode == 2 && !pmask[p]) return;                        // addPoint<2> only visits the points being marginalised
 	float bd_acc = 0.f, Hdd_acc = 0.f, h0 = 0.f, h1 = 0.f, h2 = 0.f, h3 = 0.f;
+	int nact = 0;                                              // active residuals of the point (the Schur preparation's "ngood")
 	const int r1 = res_begin[p + 1];
 	for (int r0 = res_begin[p]; r0 < r1; r0 += 4)              // four residuals' loads in flight, sums in residualsAll order
 	{
@@ -647,7 +652,9 @@ __global__ void ba_point_sums_kernel(int nP, const int* __restrict__ res_begin, 
 		for (int u = 0; u < 4; u++)
 		{
 			const int r = r0 + u;
-			use[u] = r < r1 && isAct[r] && (mode == 0 ? !isLin[r] : (mode == 1 ? isLin[r] != 0 : true));
+			const bool act = r < r1 && isAct[r];
+			nact += act ? 1 : 0;
+			use[u] = act && (mode == 0 ? !isLin[r] : (mode == 1 ? isLin[r] != 0 : true));
 #pragma unroll
 			for (int k = 0; k < 6; k++) c[u][k] = use[u] ? contrib[6 * (size_t)r + k] : 0.f;
 		}
@@ -673,8 +680,8 @@ __global__ void ba_point_sums_kernel(int nP, const int* __restrict__ res_begin, 
 		const float* src = mode == 0 ? Hcd_L : Hcd_A;
 #pragma unroll
 		for (int k = 0; k < 4; k++) oth[k] = src[4 * p + k];
-		if (mode == 0) schur_prep_point(p, res_begin, isAct, Hdd_acc, bd_acc, own, Hdd_L[p], bd_L[p], oth, po);
-		else schur_prep_point(p, res_begin, isAct, Hdd_A[p], bd_A[p], oth, Hdd_acc, bd_acc, own, po);
+		if (mode == 0) schur_prep_point(p, res_begin, isAct, Hdd_acc, bd_acc, own, Hdd_L[p], bd_L[p], oth, po, nact);
+		else schur_prep_point(p, res_begin, isAct, Hdd_A[p], bd_A[p], oth, Hdd_acc, bd_acc, own, po, nact);
 	}
 }
 

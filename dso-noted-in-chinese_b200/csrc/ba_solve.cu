@@ -494,9 +494,8 @@ __device__ __forceinline__ float resubstitute_point(int p, int nF, const int* __
                                                     const float* __restrict__ JpJdF, const float* __restrict__ HcdSum, const float* __restrict__ bdSumF,
                                                     const float* __restrict__ HdiF, const double* __restrict__ x, const float* __restrict__ xAd)
 {
+	// (the reference's "ngood == 0 -> step 0" is decided at the end: the loop below sees the same flags)
 	int ngood = 0;
-	for (int r = res_begin[p]; r < res_begin[p + 1]; r++) ngood += isAct[r] ? 1 : 0;
-	if (ngood == 0) return 0.f;
 	float b = bdSumF[p];
 	const float* hc = HcdSum + 4 * (size_t)p;
 	const float x0 = (float)x[0], x1 = (float)x[1], x2 = (float)x[2], x3 = (float)x[3];
@@ -511,6 +510,7 @@ __device__ __forceinline__ float resubstitute_point(int p, int nF, const int* __
 		{
 			const int r = r0 + u;
 			use[u] = r < r1 && isAct[r];
+			ngood += use[u] ? 1 : 0;
 			d[u] = 0.f;
 			if (use[u])
 			{
@@ -524,7 +524,7 @@ __device__ __forceinline__ float resubstitute_point(int p, int nF, const int* __
 #pragma unroll
 		for (int u = 0; u < 4; u++) if (use[u]) b = fsub(b, d[u]);
 	}
-	return fmul(-b, HdiF[p]);
+	return ngood == 0 ? 0.f : fmul(-b, HdiF[p]);
 }
 __global__ void ba_resubstitute_kernel(int nP, int nF, const int* __restrict__ res_begin, const int* __restrict__ rtarget,
                                        const int* __restrict__ phost, const unsigned char* __restrict__ isAct,
