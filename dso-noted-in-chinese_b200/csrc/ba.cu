@@ -611,8 +611,9 @@ __global__ void __launch_bounds__(128) ba_accum_top_kernel(const int* __restrict
 struct SchurPrepOut { float* HdiF; float* bdSumF; float* idh; float* HcdSum; const float* priorF; const float* deltaF; };
 __device__ __forceinline__ void schur_prep_point(int p, const int* __restrict__ res_begin, const unsigned char* __restrict__ isAct,
                                                  float HddA, float bdA, const float* hcA, float HddL, float bdL, const float* hcL,
-                                                 const SchurPrepOut& o, int ngood_known = -1)
+                                                 const SchurPrepOut& o, int ngood_known = -1, bool have_prior = false, float priorF_v = 0.f, float deltaF_v = 0.f)
 {
+	const float prF = have_prior ? priorF_v : o.priorF[p], dlF = have_prior ? deltaF_v : o.deltaF[p];
 #pragma unroll
 	for (int k = 0; k < 4; k++) o.HcdSum[4 * p + k] = fadd(hcA[k], hcL[k]);   // Hcd_accAF + Hcd_accLF (:62)
 	int ngood = ngood_known;
@@ -622,11 +623,11 @@ __device__ __forceinline__ void schur_prep_point(int p, const int* __restrict__ 
 		for (int r = res_begin[p]; r < res_begin[p + 1]; r++) ngood += isAct[r] ? 1 : 0;
 	}
 	if (ngood == 0) { o.HdiF[p] = 0.f; o.bdSumF[p] = 0.f; o.idh[p] = 0.f; return; }
-	float H = fadd(fadd(HddA, HddL), o.priorF[p]);   // Hdd_accAF + Hdd_accLF + priorF
+	float H = fadd(fadd(HddA, HddL), prF);           // Hdd_accAF + Hdd_accLF + priorF
 	if (H < 1e-10) H = 1e-10;
 	o.idh[p] = H;
 	o.HdiF[p] = (float)(1.0 / (double)H);
-	o.bdSumF[p] = fadd(fadd(bdA, bdL), fmul(o.priorF[p], o.deltaF[p]));
+	o.bdSumF[p] = fadd(fadd(bdA, bdL), fmul(prF, dlF));
 }
 
 // per-point sums in EFPoint::residualsAll order, AccumulatedTopHessian.cpp:142-160.  prep (modes 0 and 1, no mask): the
@@ -645,21 +646,35 @@ __global__ void ba_point_sums_kernel(int nP, const int* __restrict__ res_begin, 
 	float bd_acc = 0.f, Hdd_acc = 0.f, h0 = 0.f, h1 = 0.f, h2 = 0.f, h3 = 0.f;
 	int nact = 0;                                              // active residuals of the point (the Schur preparation's "ngood")
 	const int r1 = res_begin[p + 1];
-	for (int r0 = res_begin[p]; r0 < r1; r0 += 4)              // four residuals' loads in flight, sums in residualsAll order
+	// what the Schur preparation needs from elsewhere does not depend on the residual loop: asked for now
+	float oHdd = 0.f, obd = 0.f, oth[4] = { 0.f, 0.f, 0.f, 0.f }, prF = 0.f, dlF = 0.f;
+	if (prep)
 	{
-		float c[4][6]; bool use[4];
+		prF = po.priorF[p]; dlF = po.deltaF[p];
+		const float* src = mode == 0 ? Hcd_L : Hcd_A;
 #pragma unroll
-		for (int u = 0; u < 4; u++)
+		for (int k = 0; k < 4; k++) oth[k] = src[4 * p + k];
+		oHdd = mode == 0 ? Hdd_L[p] : Hdd_A[p];
+		obd = mode == 0 ? bd_L[p] : bd_A[p];
+	}
+	for (int r0 = res_begin[p]; r0 < r1; r0 += 8)              // eight residuals' loads in flight (a point has at most nF-1), sums in residualsAll order
+	{
+		float c[8][6]; bool use[8];
+#pragma unroll
+		for (int u = 0; u < 8; u++)
 		{
 			const int r = r0 + u;
 			const bool act = r < r1 && isAct[r];
 			nact += act ? 1 : 0;
 			use[u] = act && (mode == 0 ? !isLin[r] : (mode == 1 ? isLin[r] != 0 : true));
+			// unconditional (clamped) loads: they go out together with the flag loads instead of one round behind them, and
+			// predicated loads would be batched by the seven predicate registers; unused values are never touched
+			const size_t rc = (size_t)min(r, r1 - 1);
 #pragma unroll
-			for (int k = 0; k < 6; k++) c[u][k] = use[u] ? contrib[6 * (size_t)r + k] : 0.f;
+			for (int k = 0; k < 6; k++) c[u][k] = contrib[6 * rc + k];
 		}
 #pragma unroll
-		for (int u = 0; u < 4; u++)
+		for (int u = 0; u < 8; u++)
 			if (use[u])
 			{
 				bd_acc = fadd(bd_acc, c[u][0]); Hdd_acc = fadd(Hdd_acc, c[u][1]);
@@ -676,12 +691,8 @@ __global__ void ba_point_sums_kernel(int nP, const int* __restrict__ res_begin, 
 	if (prep)
 	{
 		const float own[4] = { h0, h1, h2, h3 };
-		float oth[4];
-		const float* src = mode == 0 ? Hcd_L : Hcd_A;
-#pragma unroll
-		for (int k = 0; k < 4; k++) oth[k] = src[4 * p + k];
-		if (mode == 0) schur_prep_point(p, res_begin, isAct, Hdd_acc, bd_acc, own, Hdd_L[p], bd_L[p], oth, po, nact);
-		else schur_prep_point(p, res_begin, isAct, Hdd_A[p], bd_A[p], oth, Hdd_acc, bd_acc, own, po, nact);
+		if (mode == 0) schur_prep_point(p, res_begin, isAct, Hdd_acc, bd_acc, own, oHdd, obd, oth, po, nact, true, prF, dlF);
+		else schur_prep_point(p, res_begin, isAct, oHdd, obd, oth, Hdd_acc, bd_acc, own, po, nact, true, prF, dlF);
 	}
 }
 
@@ -854,11 +865,14 @@ __global__ void __launch_bounds__(64) ba_top_gather_kernel(int nF, int nChunks, 
 			v = contrib[(size_t)(r + nF * c) * TC_STRIDE + TC_HT + o] + contrib[(size_t)(c + nF * r) * TC_STRIDE + TC_HT + j * 8 + i];
 		Hout[(CPARS + r * 8 + i) * N + CPARS + c * 8 + j] = v;
 	}
-	else
+	else if ((int)blockIdx.x < nF * nF + nF)
 	{
-		for (int e = o; e < nF * 32; e += 64)
+		// calibration rows / columns and b of frame r: one block per frame, one entry per thread (a single round of loads;
+		// one block doing this for all frames, then the calibration block, then resInA was a dozen dependent rounds)
+		const int r = blockIdx.x - nF * nF;
+		if (o < 32)
 		{
-			const int r = e / 32, q = e % 32;
+			const int q = o;
 			double v = 0.0;
 			{
 				double th[MAXF], tt[MAXF];
@@ -874,9 +888,9 @@ __global__ void __launch_bounds__(64) ba_top_gather_kernel(int nF, int nChunks, 
 			const int row = CPARS + r * 8 + (q >> 2), col = q & 3;
 			Hout[row * N + col] = v; Hout[col * N + row] = v;
 		}
-		for (int e = o; e < nF * 8; e += 64)
+		else if (o < 40)
 		{
-			const int r = e / 8, q = e % 8;
+			const int q = o - 32, e = r * 8 + q;
 			double v = 0.0;
 			{
 				double th[MAXF], tt[MAXF];
@@ -892,6 +906,9 @@ __global__ void __launch_bounds__(64) ba_top_gather_kernel(int nF, int nChunks, 
 			if (priorH) v += __dmul_rn(priorH[CPARS + e], priorD[CPARS + e]);   // prior.cwiseProduct(delta_prior)
 			bout[CPARS + e] = v;
 		}
+	}
+	else if ((int)blockIdx.x == nF * nF + nF)
+	{
 		// calibration block / vector: sum over all pairs, three threads per entry (each a third of the pairs, in order), then
 		// the three parts in order
 		__shared__ double s_cc[3][20];
@@ -918,15 +935,25 @@ __global__ void __launch_bounds__(64) ba_top_gather_kernel(int nF, int nChunks, 
 			if (priorH && o >= 16) v += __dmul_rn(priorH[o - 16], (double)cDeltaF[o - 16]);   // cPrior.cwiseProduct(cDeltaF.cast<double>())
 			if (o < 16) Hout[(o >> 2) * N + (o & 3)] = v; else bout[o - 16] = v;
 		}
-		if (o >= 32)
+	}
+	else
+	{
+		// resInA: integer sum over the chunks, own block, eight loads per thread in flight
+		__shared__ int s_n[2];
+		int n = 0;
+		for (int c0 = o; c0 < nChunks; c0 += 64 * 8)
 		{
-			// resInA: integer sum over the chunks, one warp
-			int n = 0;
-			for (int c = o - 32; c < nChunks; c += 32) n += chunk_nres[c];
+			int t[8];
 #pragma unroll
-			for (int d = 16; d > 0; d >>= 1) n += __shfl_xor_sync(0xffffffffu, n, d);
-			if (o == 32) scalars[1] = (double)n;
+			for (int u = 0; u < 8; u++) t[u] = chunk_nres[min(c0 + 64 * u, nChunks - 1)];
+#pragma unroll
+			for (int u = 0; u < 8; u++) if (c0 + 64 * u < nChunks) n += t[u];
 		}
+#pragma unroll
+		for (int d = 16; d > 0; d >>= 1) n += __shfl_xor_sync(0xffffffffu, n, d);
+		if ((o & 31) == 0) s_n[o >> 5] = n;
+		__syncthreads();
+		if (o == 0) scalars[1] = (double)(s_n[0] + s_n[1]);
 	}
 }
 
@@ -1665,7 +1692,7 @@ int ba_enqueue_top(dso_b200_ctx* ctx, int mode, const unsigned char* d_pmask, bo
 		ba_reduce_partials_kernel<<<dim3(1, nF * nF), NTOP_PAD, 0, st>>>(W->d_topPartials, NTOP_PAD, NTOP_PAD, W->d_pair_chunk_begin, W->d_topRed);
 	ba_top_pair_kernel<<<nF * nF, 256, 0, st>>>(nF, W->d_topRed, W->d_adHost, W->d_adTarget, W->d_topContrib,
 	                                          fused_reduce ? W->d_topPartials : nullptr, W->d_pair_chunk_begin);
-	ba_top_gather_kernel<<<nF * nF + 1, 64, 0, st>>>(nF, W->nChunks, W->d_chunk_nres, W->d_topContrib, Hout, bout, W->d_scalars + (mode ? 2 : 0),
+	ba_top_gather_kernel<<<nF * nF + nF + 2, 64, 0, st>>>(nF, W->nChunks, W->d_chunk_nres, W->d_topContrib, Hout, bout, W->d_scalars + (mode ? 2 : 0),
 	                                               mode == 1 ? W->d_priorH : nullptr, W->d_priorD, W->d_cDeltaF);
 	LAUNCHED(ctx, fused_reduce ? 4 : 5);
 	CK(cudaGetLastError());

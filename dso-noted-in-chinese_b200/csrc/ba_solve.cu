@@ -502,27 +502,32 @@ __device__ __forceinline__ float resubstitute_point(int p, int nF, const int* __
 	b = fsub(b, fadd(fadd(fmul(x0, hc[0]), fmul(x1, hc[1])), fadd(fmul(x2, hc[2]), fmul(x3, hc[3]))));
 	const int h = phost[p];
 	const int r1 = res_begin[p + 1];
-	for (int r0 = res_begin[p]; r0 < r1; r0 += 4)              // four residuals' loads in flight, subtractions in residualsAll order
+	for (int r0 = res_begin[p]; r0 < r1; r0 += 8)              // eight residuals per round (a point has at most nF-1), subtractions in residualsAll order
 	{
-		float d[4]; bool use[4];
+		// round 1: flags, targets and the Jacobian terms of all eight (clamped, unconditional: nothing waits for a flag);
+		// round 2: the xAd rows the targets point at
+		bool use[8]; int tg[8]; float4 j0[8], j1[8];
 #pragma unroll
-		for (int u = 0; u < 4; u++)
+		for (int u = 0; u < 8; u++)
 		{
-			const int r = r0 + u;
-			use[u] = r < r1 && isAct[r];
+			const int r = r0 + u, rc = min(r, r1 - 1);
+			use[u] = r < r1 && isAct[rc];
+			tg[u] = rtarget[rc];
+			const float4* jp = reinterpret_cast<const float4*>(JpJdF + 8 * (size_t)rc);
+			j0[u] = jp[0]; j1[u] = jp[1];
 			ngood += use[u] ? 1 : 0;
-			d[u] = 0.f;
-			if (use[u])
-			{
-				const float4* xa = reinterpret_cast<const float4*>(xAd + 8 * (h * nF + rtarget[r]));
-				const float4* jp = reinterpret_cast<const float4*>(JpJdF + 8 * (size_t)r);
-				const float4 x0 = xa[0], x1 = xa[1], j0 = jp[0], j1 = jp[1];
-				d[u] = fadd(fadd(fadd(fmul(x0.x, j0.x), fmul(x0.y, j0.y)), fadd(fmul(x0.z, j0.z), fmul(x0.w, j0.w))),
-				            fadd(fadd(fmul(x1.x, j1.x), fmul(x1.y, j1.y)), fadd(fmul(x1.z, j1.z), fmul(x1.w, j1.w))));
-			}
+		}
+		float d[8];
+#pragma unroll
+		for (int u = 0; u < 8; u++)
+		{
+			const float4* xa = reinterpret_cast<const float4*>(xAd + 8 * (h * nF + tg[u]));
+			const float4 x0 = xa[0], x1 = xa[1];
+			d[u] = fadd(fadd(fadd(fmul(x0.x, j0[u].x), fmul(x0.y, j0[u].y)), fadd(fmul(x0.z, j0[u].z), fmul(x0.w, j0[u].w))),
+			            fadd(fadd(fmul(x1.x, j1[u].x), fmul(x1.y, j1[u].y)), fadd(fmul(x1.z, j1[u].z), fmul(x1.w, j1[u].w))));
 		}
 #pragma unroll
-		for (int u = 0; u < 4; u++) if (use[u]) b = fsub(b, d[u]);
+		for (int u = 0; u < 8; u++) if (use[u]) b = fsub(b, d[u]);
 	}
 	return ngood == 0 ? 0.f : fmul(-b, HdiF[p]);
 }
