@@ -102,7 +102,7 @@ static void free_points(BAWorkspace* W)
 static void free_res(BAWorkspace* W)
 {
 	if (!W->capR) return;
-	cudaFree(W->d_rpoint); cudaFree(W->d_rtarget); cudaFree(W->d_state); cudaFree(W->d_newState); cudaFree(W->d_energy); cudaFree(W->d_newEnergy);
+	cudaFree(W->d_rhost); cudaFree(W->d_rpoint); cudaFree(W->d_rtarget); cudaFree(W->d_state); cudaFree(W->d_newState); cudaFree(W->d_energy); cudaFree(W->d_newEnergy);
 	cudaFree(W->d_newEnergyWO); cudaFree(W->d_isLin); cudaFree(W->d_isAct); cudaFree(W->d_efsel); cudaFree(W->d_cpt); cudaFree(W->d_proj);
 	cudaFree(W->d_J[0]); cudaFree(W->d_J[1]); cudaFree(W->d_JpJdF); cudaFree(W->d_contrib); cudaFree(W->d_resEnergy); cudaFree(W->d_perm); cudaFree(W->d_subset);
 	cudaFree(W->d_energy_blocks); cudaFree(W->d_resToZero);
@@ -175,7 +175,8 @@ __global__ void __launch_bounds__(256) ba_linearize_kernel(BAParams B, const flo
                                                            float* J0, float* J1, int* newState, float* newEnergy, float* newEnergyWO,
                                                            float* cpt, float* proj, double* resEnergy,
                                                            const int* __restrict__ subset, int nsub, int reset_oob,
-                                                           unsigned char* isAct, float* JpJdF, float* contrib = nullptr)
+                                                           unsigned char* isAct, float* JpJdF, float* contrib = nullptr,
+                                                           const int* __restrict__ rhost = nullptr)
 {
 	__shared__ float sJ[32][JSZ + 2];
 	const int tid = threadIdx.x, lane = tid & 31, g = tid >> 3, idx = tid & 7, base = lane & ~7;
@@ -185,7 +186,7 @@ __global__ void __launch_bounds__(256) ba_linearize_kernel(BAParams B, const flo
 	const bool valid = slot < (subset ? nsub : B.nR);
 	const int r = valid ? (subset ? subset[slot] : slot) : 0;
 	const int rr = r;
-	const int p = rpoint[rr], t = rtarget[rr], h = phost[p];
+	const int p = rpoint[rr], t = rtarget[rr], h = rhost ? rhost[rr] : phost[p];
 	const int st = reset_oob ? ST_IN : state[rr];
 	const float4 P4 = __ldg(pt + p);            // u, v, idepth_scaled, idepth_zero_scaled
 	const float* pre = precalc + (size_t)(h * B.nF + t) * 28;
@@ -1387,6 +1388,7 @@ extern "C" int dso_b200_ba_set_residuals(dso_b200_ctx* ctx, int nR, const int* p
 		free_res(W);
 		const size_t n = (size_t)nR;
 		CK(cudaMalloc(&W->d_rpoint, n * sizeof(int))); CK(cudaMalloc(&W->d_rtarget, n * sizeof(int))); CK(cudaMalloc(&W->d_state, n * sizeof(int)));
+		CK(cudaMalloc(&W->d_rhost, n * sizeof(int)));
 		CK(cudaMalloc(&W->d_newState, n * sizeof(int))); CK(cudaMalloc(&W->d_energy, n * sizeof(double))); CK(cudaMalloc(&W->d_newEnergy, n * sizeof(float)));
 		CK(cudaMalloc(&W->d_newEnergyWO, n * sizeof(float))); CK(cudaMalloc(&W->d_isLin, n)); CK(cudaMalloc(&W->d_isAct, n)); CK(cudaMalloc(&W->d_efsel, n));
 		CK(cudaMalloc(&W->d_cpt, n * 3 * sizeof(float))); CK(cudaMalloc(&W->d_proj, n * 16 * sizeof(float)));
@@ -1439,6 +1441,13 @@ extern "C" int dso_b200_ba_set_residuals(dso_b200_ctx* ctx, int nR, const int* p
 	cudaStream_t s = ctx->ba_stream;
 	CK(cudaMemcpyAsync(W->d_rpoint, point, (size_t)nR * sizeof(int), cudaMemcpyHostToDevice, s));
 	CK(cudaMemcpyAsync(W->d_rtarget, target, (size_t)nR * sizeof(int), cudaMemcpyHostToDevice, s));
+	{
+		// host frame per residual: the linearisation reaches the (host, target) precalc without the point -> host hop
+		std::vector<int> rh((size_t)nR);
+		for (int i = 0; i < nR; i++) rh[i] = W->h_phost[point[i]];
+		CK(cudaMemcpyAsync(W->d_rhost, rh.data(), (size_t)nR * sizeof(int), cudaMemcpyHostToDevice, s));
+		CK(cudaStreamSynchronize(s));          // rh leaves scope
+	}
 	CK(cudaMemcpyAsync(W->d_state, state_state, (size_t)nR * sizeof(int), cudaMemcpyHostToDevice, s));
 	CK(cudaMemcpyAsync(W->d_energy, en.data(), (size_t)nR * sizeof(double), cudaMemcpyHostToDevice, s));
 	CK(cudaMemcpyAsync(W->d_newEnergy, nen.data(), (size_t)nR * sizeof(float), cudaMemcpyHostToDevice, s));
@@ -1626,12 +1635,12 @@ int ba_enqueue_linearize(dso_b200_ctx* ctx, bool fork, bool apply)
 		ba_linearize_kernel<true><<<(nR + 31) / 32, 256, 0, ctx->ba_stream>>>(W->P, W->d_precalc, W->d_pt, W->d_color, W->d_weights, W->d_phost, W->d_rpoint,
 		                                                                 W->d_rtarget, W->d_state, W->d_energy, W->d_efsel, W->d_J[0], W->d_J[1],
 		                                                                 W->d_newState, W->d_newEnergy, W->d_newEnergyWO, W->d_cpt, W->d_proj, W->d_resEnergy,
-		                                                                 nullptr, 0, 0, W->d_isAct, W->d_JpJdF, W->d_contrib);
+		                                                                 nullptr, 0, 0, W->d_isAct, W->d_JpJdF, W->d_contrib, W->d_rhost);
 	else
 		ba_linearize_kernel<false><<<(nR + 31) / 32, 256, 0, ctx->ba_stream>>>(W->P, W->d_precalc, W->d_pt, W->d_color, W->d_weights, W->d_phost, W->d_rpoint,
 		                                                                  W->d_rtarget, W->d_state, W->d_energy, W->d_efsel, W->d_J[0], W->d_J[1],
 		                                                                  W->d_newState, W->d_newEnergy, W->d_newEnergyWO, W->d_cpt, W->d_proj, W->d_resEnergy,
-		                                                                  nullptr, 0, 0, nullptr, nullptr);
+		                                                                  nullptr, 0, 0, nullptr, nullptr, nullptr, W->d_rhost);
 	if (apply) W->top_done = false;
 	const int nb = (nR + 255) / 256;
 	cudaStream_t se = ctx->ba_stream;

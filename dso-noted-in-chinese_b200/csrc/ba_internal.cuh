@@ -82,7 +82,7 @@ struct BAWorkspace
 	float* d_Hdd; float* d_bd; float* d_Hcd; float* d_HdiF; float* d_bdSumF; float* d_idh;
 	// residuals
 	int capR;
-	int* d_rpoint; int* d_rtarget; int* d_state; int* d_newState; double* d_energy; float* d_newEnergy; float* d_newEnergyWO;
+	int* d_rhost; int* d_rpoint; int* d_rtarget; int* d_state; int* d_newState; double* d_energy; float* d_newEnergy; float* d_newEnergyWO;
 	unsigned char* d_isLin; unsigned char* d_isAct; unsigned char* d_efsel;
 	float* d_cpt; float* d_proj; float* d_J[2]; float* d_JpJdF; float* d_contrib; double* d_resEnergy;
 	int* d_perm; int* d_subset;      // d_subset: index list of dso_b200_ba_linearize_residuals
