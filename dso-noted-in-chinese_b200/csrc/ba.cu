@@ -990,13 +990,23 @@ __global__ void ba_schur_prep_kernel(int nP, const int* __restrict__ res_begin, 
 	bdSumF[p] = bs;
 }
 
+// optional fusion: the per-point sums of addPoint<0> and the Schur preparation of the chunk's own points (contrib == NULL: off)
+struct SchurFusedSums
+{
+	const float* contrib; const unsigned char* isLin;
+	float* Hdd; float* bd; float* Hcd;                       // out: the AF sums (what ba_point_sums_kernel writes in mode 0)
+	const float* Hdd_L; const float* bd_L; const float* Hcd_L; const float* priorF; const float* deltaF;
+	float* HdiF; float* bdSumF; float* idh; float* HcdSum;   // out: what the preparation writes
+};
+
 // accD / accE / accEB / accHcc / accbc contributions of one chunk of points of one host frame
 // (AccumulatedSCHessian.cpp:64-84): thread-owned output entries, points visited in order.
 __global__ void __launch_bounds__(256) ba_schur_accum_kernel(int nF, const int* __restrict__ pc_start, const int* __restrict__ pc_cnt,
                                                              const int* __restrict__ res_begin, const int* __restrict__ rtarget,
                                                              const unsigned char* __restrict__ isAct, const float* __restrict__ JpJdF,
                                                              const float* __restrict__ HdiF, const float* __restrict__ bdSumF,
-                                                             const float* __restrict__ Hcd, float* partials, int scN)
+                                                             const float* __restrict__ Hcd, float* partials, int scN,
+                                                             SchurFusedSums fs = SchurFusedSums())
 {
 	__shared__ float sa[CHUNK_P][MAXF * 8];     // JpJdF by target slot (0 when inactive)
 	__shared__ float swa[CHUNK_P][MAXF * 8];    // HdiF * JpJdF
@@ -1012,13 +1022,58 @@ __global__ void __launch_bounds__(256) ba_schur_accum_kernel(int nF, const int* 
 		// 16 threads per point: two residuals at a time, one JpJdF entry each (the serial per-point loop was a chain of
 		// dependent global loads: begin -> flag -> target -> eight values, residual after residual)
 		const int pl = tid >> 4, sub = tid & 15, k = sub & 7;
+		float w_f = 0.f, hc_f = 0.f, wb_f = 0.f;
+		if (fs.contrib)
+		{
+			// the per-point sums of addPoint<0> (AccumulatedTopHessian.cpp:142-160, residualsAll order) and the Schur
+			// preparation (AccumulatedSCHessian.cpp:35-60) of this chunk's own points, here instead of in a launch of their own:
+			// lanes 0-5 of a point's 16 sum one component each (bd, Hdd, Hcd[0..3]), lane 0 then prepares the point
+			const int p = start + min(pl, cnt - 1);
+			const int r0 = res_begin[p], r1 = res_begin[p + 1];
+			const float prF = fs.priorF[p], dlF = fs.deltaF[p];
+			const float oth = sub < 6 ? (sub == 0 ? fs.bd_L[p] : (sub == 1 ? fs.Hdd_L[p] : fs.Hcd_L[4 * p + sub - 2])) : 0.f;
+			float acc = 0.f;
+			int nact = 0;
+			const int comp = min(sub, 5);
+			for (int rb = r0; rb < r1; rb += 8)
+			{
+				float c[8]; bool use[8];
+#pragma unroll
+				for (int u = 0; u < 8; u++)
+				{
+					const int r = rb + u, rc = min(r, r1 - 1);
+					const bool act = r < r1 && isAct[rc];
+					nact += act ? 1 : 0;
+					use[u] = act && !fs.isLin[rc];
+					c[u] = fs.contrib[6 * (size_t)rc + comp];
+				}
+#pragma unroll
+				for (int u = 0; u < 8; u++) if (use[u]) acc = fadd(acc, c[u]);
+			}
+			const int b16 = (tid & 31) & ~15;
+			const float s_bd = __shfl_sync(0xffffffffu, acc, b16 + 0), s_Hdd = __shfl_sync(0xffffffffu, acc, b16 + 1);
+			const float o_bd = __shfl_sync(0xffffffffu, oth, b16 + 0), o_Hdd = __shfl_sync(0xffffffffu, oth, b16 + 1);
+			const float hsum = fadd(acc, oth);                          // lanes 2-5: Hcd_accAF + Hcd_accLF (:62)
+			float H = fadd(fadd(s_Hdd, o_Hdd), prF);                   // Hdd_accAF + Hdd_accLF + priorF
+			if (H < 1e-10) H = 1e-10;
+			const float wv = nact == 0 ? 0.f : (float)(1.0 / (double)H);
+			const float bs = nact == 0 ? 0.f : fadd(fadd(s_bd, o_bd), fmul(prF, dlF));
+			if (pl < cnt)
+			{
+				if (sub == 0) { fs.bd[p] = acc; fs.HdiF[p] = wv; fs.bdSumF[p] = bs; fs.idh[p] = nact == 0 ? 0.f : H; }
+				else if (sub == 1) fs.Hdd[p] = acc;
+				else if (sub < 6) { fs.Hcd[4 * p + sub - 2] = acc; fs.HcdSum[4 * p + sub - 2] = hsum; }
+			}
+			w_f = wv; wb_f = fmul(wv, bs);
+			hc_f = __shfl_sync(0xffffffffu, hsum, b16 + min(sub + 2, 5));   // lanes 0-3 fetch HcdSum[0..3] from lanes 2-5
+		}
 		if (pl < cnt)
 		{
 			const int p = start + pl;
-			const float w = HdiF[p];
-			if (sub < 4) sh[pl][sub] = Hcd[4 * p + sub];
+			const float w = fs.contrib ? w_f : HdiF[p];
+			if (sub < 4) sh[pl][sub] = fs.contrib ? hc_f : Hcd[4 * p + sub];
 			else if (sub == 4) sh[pl][4] = w;
-			else if (sub == 5) sh[pl][5] = fmul(w, bdSumF[p]);
+			else if (sub == 5) sh[pl][5] = fs.contrib ? wb_f : fmul(w, bdSumF[p]);
 			const int r1 = res_begin[p + 1];
 			for (int r = res_begin[p] + (sub >> 3); r < r1; r += 2)
 			{
@@ -1693,6 +1748,10 @@ int ba_enqueue_top(dso_b200_ctx* ctx, int mode, const unsigned char* d_pmask, bo
 	SchurPrepOut po;
 	po.HdiF = W->d_HdiF; po.bdSumF = W->d_bdSumF; po.idh = W->d_idh; po.HcdSum = W->d_HcdSum; po.priorF = W->d_priorF; po.deltaF = W->d_deltaF;
 	if (prep && (mode == 2 || d_pmask)) { dso_set_error("ba_enqueue_top: the fused Schur preparation has no marginalisation form"); return DSO_B200_E_ARG; }
+	// no linearised residuals to add afterwards (prep with early sums): the Schur accumulation, which is next on the main
+	// stream, computes the per-point sums and the preparation of its own points itself -- one launch less on the critical path
+	W->sums_in_schur = early_sums && prep;
+	if (!W->sums_in_schur)
 	ba_point_sums_kernel<<<(W->P.nP + 127) / 128, 128, 0, early_sums ? ctx->ba_stream : st>>>(W->P.nP, W->d_res_begin, W->d_isAct, W->d_isLin, W->d_contrib, Hdd, bd, Hcd, mode, d_pmask, W->d_Hdd, W->d_bd, W->d_Hcd,
 	                                                            prep, W->d_Hdd_L, W->d_bd_L, W->d_Hcd_L, po);
 	if (fork && !early_sums) { int rc = ba_fork(ctx); if (rc) return rc; st = W->side_stream; }       // the stitch: independent of what follows on the main stream
@@ -1703,7 +1762,7 @@ int ba_enqueue_top(dso_b200_ctx* ctx, int mode, const unsigned char* d_pmask, bo
 	                                          fused_reduce ? W->d_topPartials : nullptr, W->d_pair_chunk_begin);
 	ba_top_gather_kernel<<<nF * nF + nF + 2, 64, 0, st>>>(nF, W->nChunks, W->d_chunk_nres, W->d_topContrib, Hout, bout, W->d_scalars + (mode ? 2 : 0),
 	                                               mode == 1 ? W->d_priorH : nullptr, W->d_priorD, W->d_cDeltaF);
-	LAUNCHED(ctx, fused_reduce ? 4 : 5);
+	LAUNCHED(ctx, (fused_reduce ? 4 : 5) - (W->sums_in_schur ? 1 : 0));
 	CK(cudaGetLastError());
 	if (mode == 0) W->top_done = true;
 	return 0;
@@ -1718,8 +1777,17 @@ int ba_enqueue_schur(dso_b200_ctx* ctx, const unsigned char* d_pmask, bool prep_
 		ba_schur_prep_kernel<<<(nP + 127) / 128, 128, 0, ctx->ba_stream>>>(nP, W->d_res_begin, W->d_isAct, W->d_Hdd, W->d_bd, W->d_Hcd,
 		                                                              W->d_Hdd_L, W->d_bd_L, W->d_Hcd_L, W->d_priorF, W->d_deltaF,
 		                                                              HdiF, bdSumF, W->d_idh, W->d_HcdSum, d_pmask);
+	SchurFusedSums fs = SchurFusedSums();
+	if (W->sums_in_schur)
+	{
+		BA_CHECK(prep_done && !d_pmask, "internal: fused per-point sums without the matching top accumulation");
+		fs.contrib = W->d_contrib; fs.isLin = W->d_isLin; fs.Hdd = W->d_Hdd; fs.bd = W->d_bd; fs.Hcd = W->d_Hcd;
+		fs.Hdd_L = W->d_Hdd_L; fs.bd_L = W->d_bd_L; fs.Hcd_L = W->d_Hcd_L; fs.priorF = W->d_priorF; fs.deltaF = W->d_deltaF;
+		fs.HdiF = W->d_HdiF; fs.bdSumF = W->d_bdSumF; fs.idh = W->d_idh; fs.HcdSum = W->d_HcdSum;
+		W->sums_in_schur = false;
+	}
 	ba_schur_accum_kernel<<<W->nPC, 256, 0, ctx->ba_stream>>>(nF, W->d_pc_start, W->d_pc_cnt, W->d_res_begin, W->d_rtarget, W->d_isAct, W->d_JpJdF,
-	                                                     HdiF, bdSumF, W->d_HcdSum, W->d_scPartials, W->scN);
+	                                                     HdiF, bdSumF, W->d_HcdSum, W->d_scPartials, W->scN, fs);
 	const int nRed = nF * nF * 64 + nF * 32 + nF * 8 + 20;          // accD, accE, accEB, accHcc + accbc per host
 	// few chunks per host (a VGA window has ~18): stage 1 sums them itself, one launch less on the critical path; many
 	// chunks: the reduction runs as its own, much wider launch (stage 1 has only nF^2 blocks)

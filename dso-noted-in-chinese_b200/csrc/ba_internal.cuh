@@ -108,6 +108,7 @@ struct BAWorkspace
 	int nLin;                                                                    // linearised residuals (-1: unknown)
 	BASolve* S;
 	BAGraph g_step, g_iter[2];
+	bool sums_in_schur;                // the next Schur accumulation computes the per-point sums + preparation itself
 	bool contrib_from_lin;             // d_contrib holds addPoint<0>'s per-point terms already (written by the fused linearisation)
 	cudaStream_t side_stream; cudaEvent_t ev_fork, ev_join; bool side_busy;     // parallel branches of the step (ba_fork / ba_join_side)
 	bool use_graphs;                                                             // DSO_B200_NO_GRAPH=1 turns them off
