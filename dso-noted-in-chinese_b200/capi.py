@@ -105,6 +105,7 @@ SIGNATURES = {
     "dso_b200_ba_set_priors": (C.c_int, [vp, vp, vp, vp, vp, vp, vp]),
     "dso_b200_ba_set_nullspaces": (C.c_int, [vp, vp, C.c_int, C.c_double]),
     "dso_b200_ba_set_solver_state": (C.c_int, [vp, C.c_int, C.c_int, C.c_double]),
+    "dso_b200_ba_get_point_terms": (C.c_int, [vp, vp, vp, vp, vp, vp, vp]),
     "dso_b200_ba_fix_linearization": (C.c_int, [vp, vp, vp]),
     "dso_b200_ba_accumulate_L": (C.c_int, [vp, f64p, f64p, C.POINTER(C.c_int), vp, vp, vp]),
     "dso_b200_ba_solve": (C.c_int, [vp, C.c_int, C.c_double, C.c_int, vp, vp, vp, vp]),
@@ -617,6 +618,13 @@ class Context:
         l, m = C.c_double(0), C.c_double(0)
         self._check(self.L.dso_b200_ba_calc_energies(self.h, C.byref(l), C.byref(m)))
         return l.value, m.value
+
+    def ba_get_point_terms(self):
+        f = lambda n: np.zeros(n, dtype=np.float32)
+        out = dict(Hdd=f(self.nP), bd=f(self.nP), Hcd=f(4 * self.nP), HdiF=f(self.nP), bdSumF=f(self.nP), idepth_hessian=f(self.nP))
+        self._check(self.L.dso_b200_ba_get_point_terms(self.h, *[out[k].ctypes.data for k in ("Hdd", "bd", "Hcd", "HdiF", "bdSumF", "idepth_hessian")]))
+        out["Hcd"] = out["Hcd"].reshape(self.nP, 4)
+        return out
 
     def ba_step(self):
         N = 8 * self.nF + 4

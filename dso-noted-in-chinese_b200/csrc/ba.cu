@@ -1940,6 +1940,28 @@ extern "C" int dso_b200_ba_accumulate_A(dso_b200_ctx* ctx, double* H, double* b,
 	return 0;
 }
 
+// The per-point results of the last accumulation as they stand on the device (after dso_b200_ba_step / _iteration /
+// _solve or the piecewise calls): EFPoint::Hdd_accAF, bd_accAF, Hcd_accAF, HdiF, bdSumF and PointHessian::idepth_hessian
+// (AccumulatedTopHessian.cpp:162-166, AccumulatedSCHessian.cpp:50-60).  Every pointer may be NULL.
+extern "C" int dso_b200_ba_get_point_terms(dso_b200_ctx* ctx, float* Hdd_accAF, float* bd_accAF, float* Hcd_accAF4,
+                                           float* HdiF, float* bdSumF, float* idepth_hessian)
+{
+	int rc = ba_check_ready(ctx, __func__);
+	if (rc) return rc;
+	CK(cudaSetDevice(ctx->device));
+	BAWorkspace* W = ctx->ba;
+	const size_t nP = (size_t)W->P.nP;
+	cudaStream_t s = ctx->ba_stream;
+	if (Hdd_accAF) CK(cudaMemcpyAsync(Hdd_accAF, W->d_Hdd, nP * sizeof(float), cudaMemcpyDeviceToHost, s));
+	if (bd_accAF) CK(cudaMemcpyAsync(bd_accAF, W->d_bd, nP * sizeof(float), cudaMemcpyDeviceToHost, s));
+	if (Hcd_accAF4) CK(cudaMemcpyAsync(Hcd_accAF4, W->d_Hcd, nP * 4 * sizeof(float), cudaMemcpyDeviceToHost, s));
+	if (HdiF) CK(cudaMemcpyAsync(HdiF, W->d_HdiF, nP * sizeof(float), cudaMemcpyDeviceToHost, s));
+	if (bdSumF) CK(cudaMemcpyAsync(bdSumF, W->d_bdSumF, nP * sizeof(float), cudaMemcpyDeviceToHost, s));
+	if (idepth_hessian) CK(cudaMemcpyAsync(idepth_hessian, W->d_idh, nP * sizeof(float), cudaMemcpyDeviceToHost, s));
+	CK(cudaStreamSynchronize(s));
+	return 0;
+}
+
 extern "C" int dso_b200_ba_accumulate_SC(dso_b200_ctx* ctx, double* H_sc, double* b_sc,
                                          float* HdiF, float* bdSumF, float* idepth_hessian)
 {

@@ -350,6 +350,11 @@ int dso_b200_ba_accumulate_A(dso_b200_ctx* ctx, double* H, double* b, int* resIn
  * (AccumulatedSCHessian.cpp:35-85) + stitchDoubleMT (AccumulatedSCHessian.h:93-135). */
 int dso_b200_ba_accumulate_SC(dso_b200_ctx* ctx, double* H_sc, double* b_sc,
                               float* HdiF, float* bdSumF, float* idepth_hessian);
+/* The per-point results of the last accumulation as they stand on the device (after dso_b200_ba_step, _iteration, _solve or
+ * the piecewise calls above): EFPoint::Hdd_accAF, bd_accAF, Hcd_accAF (AccumulatedTopHessian.cpp:162-166), HdiF, bdSumF and
+ * PointHessian::idepth_hessian (AccumulatedSCHessian.cpp:50-60), nP (4 nP for Hcd) floats each; any pointer may be NULL. */
+int dso_b200_ba_get_point_terms(dso_b200_ctx* ctx, float* Hdd_accAF, float* bd_accAF, float* Hcd_accAF4,
+                                float* HdiF, float* bdSumF, float* idepth_hessian);
 /* linearize -> applyRes(true) -> accumulateAF -> accumulateSCF back to back with a single
  * synchronisation; H_A/b_A/H_sc/b_sc as above (one GN iteration's worth of FullSystem::optimize,
  * FullSystemOptimize.cpp:455-486 + EnergyFunctional.cpp:816-820). */

@@ -89,6 +89,12 @@ def test_ba_fused_step_equals_separate_calls(pkg, oracle, window_small):
     _check_system(st["H_A"], st["b_A"], Ao["H"], Ao["b"])
     _check_system(st["H_sc"], st["b_sc"], So["H"], So["b"])
     assert st["resInA"] == Ao["resInA"]
+    # the per-point terms the fused step leaves on the device (per-point sums written with the Jacobians, summed and prepared
+    # inside the Schur accumulation): bit for bit the oracle's
+    pt = ctx.ba_get_point_terms()
+    for key, ref in (("Hdd", Ao["Hdd"]), ("bd", Ao["bd"]), ("Hcd", Ao["Hcd"]), ("HdiF", So["HdiF"]), ("bdSumF", So["bdSumF"]),
+                     ("idepth_hessian", So["idepth_hessian"])):
+        assert np.array_equal(pt[key].reshape(-1).view(np.uint32), np.asarray(ref, dtype=np.float32).reshape(-1).view(np.uint32)), key
     ctx.close()
 
 
