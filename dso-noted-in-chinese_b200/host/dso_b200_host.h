@@ -264,6 +264,11 @@ public:
 	// void marginalizePointsF()   EnergyFunctional.cpp:642 (accumulation + HM/bM update; removePoint/makeIDX stay with the caller)
 	void marginalizePointsF(const unsigned char* isMarginalizeFlag, float setting_idepthFixPriorMargFac, double setting_margWeightFac)
 	{ DSO_B200_CHECK(dso_b200_ba_marginalize_points(dev->ctx, isMarginalizeFlag, setting_idepthFixPriorMargFac, setting_margWeightFac, 0, 0, &resInM, 0)); }
+	// the per-point results of the last accumulation (EFPoint::Hdd_accAF / bd_accAF / Hcd_accAF / HdiF / bdSumF and
+	// PointHessian::idepth_hessian, which FullSystem::flagPointsForRemoval and the point marginalisation read); nPoints floats
+	// each (4 nPoints for Hcd_accAF), any pointer may be null
+	void getPointTerms(float* Hdd_accAF, float* bd_accAF, float* Hcd_accAF4, float* HdiF, float* bdSumF, float* idepth_hessian)
+	{ DSO_B200_CHECK(dso_b200_ba_get_point_terms(dev->ctx, Hdd_accAF, bd_accAF, Hcd_accAF4, HdiF, bdSumF, idepth_hessian)); }
 	// double calcLEnergyF_MT() / double calcMEnergyF()   EnergyFunctional.cpp:411, :334
 	double calcLEnergyF_MT() { double l = 0, m = 0; DSO_B200_CHECK(dso_b200_ba_calc_energies(dev->ctx, &l, &m)); return l; }
 	double calcMEnergyF() { double l = 0, m = 0; DSO_B200_CHECK(dso_b200_ba_calc_energies(dev->ctx, &l, &m)); return m; }
