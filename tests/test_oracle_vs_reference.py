@@ -255,11 +255,11 @@ def _no_first_frame_inputs(W, pyr):
 @pytest.mark.parametrize("mode,first", [(SOLVER_DEFAULT | SOLVER_ORTH_SYSTEM, False), (SOLVER_DEFAULT | SOLVER_ORTH_SYSTEM, True),
                                         (SOLVER_DEFAULT | SOLVER_SVD, True), (SOLVER_DEFAULT | SOLVER_SVD | SOLVER_SVD_CUT7, True),
                                         (SOLVER_DEFAULT | SOLVER_SVD | SOLVER_ORTH_SYSTEM, False)])
-def test_solve_system_non_default_branches(pkg, window_small, mode, first):
+def test_solve_system_non_default_branches(pkg, win, mode, first):
     """the SVD / SVD_CUT7 / ORTHOGONALIZE_SYSTEM branches of solveSystemF (EnergyFunctional.cpp:832-900) with and without the
     gauge-fixing first frame in the window.  (The reference build's JacobiSVD is the stand-in Hestenes SVD, so these branches
     are pinned up to the SVD algorithm: x agrees to 1e-7, not to rounding.)"""
-    W = window_small
+    W = win
     pyr = [O.make_images(img, 1)[0][0] for img in W.images]
     inp = _solve_inputs(W) if first else _no_first_frame_inputs(W, pyr)
     Bo, Br = O.BA(W, pyr), O.BA(W, pyr, kind="ref")
@@ -279,9 +279,9 @@ def test_solve_system_non_default_branches(pkg, window_small, mode, first):
 
 
 @pytest.mark.parametrize("mode", [SOLVER_DEFAULT | SOLVER_ORTH_POINTMARG, SOLVER_DEFAULT | SOLVER_ORTH_FULL])
-def test_marginalize_points_orthogonalize_branches(pkg, window_small, mode):
+def test_marginalize_points_orthogonalize_branches(pkg, win, mode):
     """SOLVER_ORTHOGONALIZE_POINTMARG / _FULL of marginalizePointsF (EnergyFunctional.cpp:684-699), first frame gone"""
-    W = window_small
+    W = win
     pyr = [O.make_images(img, 1)[0][0] for img in W.images]
     inp = _solve_inputs(W)            # random "null-space" vectors: with the true ones H P ~ 0 and the projection is a no-op
     pflags = (np.arange(W.nP) % 3 == 1).astype(np.uint8)
