@@ -155,14 +155,15 @@ from test_oracle_vs_reference import (_no_first_frame_inputs, SOLVER_DEFAULT, SO
                                       SOLVER_ORTH_POINTMARG, SOLVER_ORTH_FULL)
 
 
-@pytest.mark.parametrize("mode,first", [(SOLVER_DEFAULT | SOLVER_ORTH_SYSTEM, False), (SOLVER_DEFAULT | SOLVER_ORTH_SYSTEM, True),
-                                        (SOLVER_DEFAULT | SOLVER_SVD, True), (SOLVER_DEFAULT | SOLVER_SVD | SOLVER_SVD_CUT7, True),
-                                        (SOLVER_DEFAULT | SOLVER_SVD | SOLVER_ORTH_SYSTEM, False)])
-def test_solve_non_default_branches(pkg, oracle, window_small, mode, first):
+@pytest.mark.parametrize("win_name,mode,first", [("small", SOLVER_DEFAULT | SOLVER_ORTH_SYSTEM, False), ("small", SOLVER_DEFAULT | SOLVER_ORTH_SYSTEM, True),
+                                                 ("small", SOLVER_DEFAULT | SOLVER_SVD, True), ("small", SOLVER_DEFAULT | SOLVER_SVD | SOLVER_SVD_CUT7, True),
+                                                 ("small", SOLVER_DEFAULT | SOLVER_SVD | SOLVER_ORTH_SYSTEM, False),
+                                                 ("vga", SOLVER_DEFAULT | SOLVER_SVD | SOLVER_ORTH_SYSTEM, False), ("vga", SOLVER_DEFAULT | SOLVER_SVD, True)])
+def test_solve_non_default_branches(pkg, oracle, request, win_name, mode, first):
     """SOLVER_ORTHOGONALIZE_SYSTEM / SOLVER_SVD / SOLVER_SVD_CUT7 of solveSystemF (EnergyFunctional.cpp:832-900) on the device
     vs the oracle (pinned against the reference build in test_oracle_vs_reference.py::test_solve_system_non_default_branches).
     HFinal / bFinal to the H_A / H_sc bar; x to the first-order image of the system difference, as in test_solve_parity."""
-    W = window_small
+    W = request.getfixturevalue("window_" + win_name)
     pyr = [oracle.make_images(img, 1)[0][0] for img in W.images]
     inp = _solve_inputs(W) if first else _no_first_frame_inputs(W, pyr)
     B, ctx = _setup(pkg, oracle, W)
@@ -175,7 +176,7 @@ def test_solve_non_default_branches(pkg, oracle, window_small, mode, first):
     _check_system(sg["HFinal"], sg["bFinal"], so["HFinal"], so["bFinal"])
     assert np.isfinite(sg["x"]).all()
     scale = np.abs(so["x"]).max()
-    assert np.abs(sg["x"] - so["x"]).max() <= 2e-3 * scale
+    assert np.abs(sg["x"] - so["x"]).max() <= (2e-3 if win_name == "small" else 1e-2) * scale
     if mode & SOLVER_SVD:
         # the device SVD on the device's own system against numpy's: same truncated pseudo-inverse
         H, b = sg["HFinal"], sg["bFinal"]
@@ -195,7 +196,7 @@ def test_solve_non_default_branches(pkg, oracle, window_small, mode, first):
             sg0 = ctx.ba_solve(0, 0.1, solver_mode=mode, debug=True)
             assert np.abs(sg0["x"] - xn).max() <= 1e-9 * np.abs(xn).max()
     good = np.abs(so["step"]) > 1e-3 * np.abs(so["step"]).max()
-    assert np.abs(sg["step"] - so["step"])[good].max() <= 1e-2 * np.abs(so["step"]).max()
+    assert np.abs(sg["step"] - so["step"])[good].max() <= (1e-2 if win_name == "small" else 3e-2) * np.abs(so["step"]).max()
     ctx.close()
 
 
